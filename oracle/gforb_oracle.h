@@ -1,0 +1,72 @@
+/* ORACLE -- TEST INFRASTRUCTURE ONLY.  C ABI over the CPU restatement so tests/ (ctypes) and bench.py's
+ * cpu_baseline leg can call it.  The product library (include/gforb.h) never links or loads this. */
+#ifndef GFORB_ORACLE_H
+#define GFORB_ORACLE_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct { float x, y, size, angle, response; int octave, class_id; } orc_keypoint; /* == cv::KeyPoint */
+typedef struct orc_extractor orc_extractor;
+
+/* primitives (cross-checked against cv2 in tests/test_oracle_cv2.py) */
+int   orc_cv_round_f(float v);
+int   orc_cv_round_d(double v);
+float orc_fast_atan2(float y, float x);
+void  orc_border_reflect101(const uint8_t* src, int w, int h, size_t spitch, uint8_t* dst, size_t dpitch, int border);
+void  orc_resize_linear_8u(const uint8_t* src, int sw, int sh, size_t spitch, uint8_t* dst, int dw, int dh, size_t dpitch);
+void  orc_gaussian_blur_7x7_s2(const uint8_t* src, int w, int h, size_t spitch, uint8_t* dst, size_t dpitch);
+/* xys: cap x 3 ints (x, y, score); returns the number found (may exceed cap; only cap are written) */
+int   orc_fast9_16(const uint8_t* img, int w, int h, size_t pitch, int threshold, int nonmax, int* xys, int cap);
+int   orc_hamming256(const uint8_t* a, const uint8_t* b);
+
+/* extractor */
+orc_extractor* orc_extractor_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST);
+void  orc_extractor_destroy(orc_extractor* ex);
+/* each out pointer may be NULL; arrays hold nlevels entries (umax: 16) */
+void  orc_extractor_tables(const orc_extractor* ex, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                           int* quota, int* umax);
+void  orc_extractor_pattern(const orc_extractor* ex, int8_t* xy1024);
+int   orc_compute_pyramid(orc_extractor* ex, const uint8_t* img, int w, int h, size_t pitch);
+/* level geometry; ptr = ROI origin inside the padded buffer (19-px REFLECT_101 frame around it) */
+int   orc_pyramid_level(const orc_extractor* ex, int level, const uint8_t** ptr, int* w, int* h, size_t* pitch);
+/* FAST candidates of one level after the cell loop (coords relative to the 16-px min border); xyr: cap x 3 */
+int   orc_detect_level(const orc_extractor* ex, int level, int* xyr, int cap);
+/* standalone quadtree: n candidates (x,y,response triples) -> kept indices in result order */
+int   orc_distribute_octree(const int* xyr, int n, int minX, int maxX, int minY, int maxY, int N, int* keep, int cap);
+/* full operator(): returns n (<= cap written); level_counts (nlevels) optional */
+int   orc_extract(orc_extractor* ex, const uint8_t* img, int w, int h, size_t pitch,
+                  orc_keypoint* kps, uint8_t* desc, int cap, int* level_counts);
+/* candidates kept from the last orc_extract call */
+int   orc_last_candidates(const orc_extractor* ex, int level, int* xyr, int cap);
+
+typedef struct {
+    float bf, b;
+    int mode;      /* 0 classic (SAD + parabola), 1 undistorted (Hamming only) */
+    int th_high, th_low;
+    float min_x;
+} orc_stereo_params;
+
+/* dbg_* optional (nL ints each).  min_d/max_d optional per-key windows (mode 1). */
+int   orc_stereo_match(const orc_extractor* exL, const orc_extractor* exR, const orc_stereo_params* prm,
+                       const orc_keypoint* kL, int nL, const uint8_t* dL,
+                       const orc_keypoint* kR, int nR, const uint8_t* dR,
+                       const float* min_d, const float* max_d,
+                       float* uRight, float* depth, int* dbg_best_dist, int* dbg_best_idx, int* dbg_sad);
+
+/* CPU baseline driver: runs `nframes` stereo frames (extract L + extract R [+ classic stereo match]) over
+ * the given images (frame f uses images[(2f) % nimg], images[(2f+1) % nimg], all w x h, tightly packed)
+ * on `nthreads` worker threads.  shape 0 = "all cores" (each worker runs whole frames),
+ * shape 1 = "reference-shaped" (one frame at a time, 2 threads = one per eye, serial match; src/Frame.cc:268-282).
+ * Returns wall seconds; *checksum accumulates keypoint/match counts so the work cannot be elided. */
+double orc_bench_stereo(const uint8_t* images, int nimg, int w, int h, int nframes, int nthreads, int shape,
+                        int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh,
+                        float bf, float b, int do_match, long long* checksum);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,244 @@
+"""ORACLE -- TEST INFRASTRUCTURE ONLY.
+
+ctypes binding of oracle/_build/libgforb_oracle.so (the CPU restatement of the reference's ORB
+front-end).  Importable only from tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs; the product package never imports it.
+"""
+import ctypes as C
+import os
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+_HERE = Path(__file__).resolve().parent
+_LIB = None
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+
+class StereoParams(C.Structure):
+    _fields_ = [("bf", C.c_float), ("b", C.c_float), ("mode", C.c_int),
+                ("th_high", C.c_int), ("th_low", C.c_int), ("min_x", C.c_float)]
+
+
+def build(force=False):
+    so = _HERE / "_build" / "libgforb_oracle.so"
+    if force or not so.exists():
+        subprocess.check_call(["make", "-C", str(_HERE)] + (["-B"] if force else []),
+                              stdout=subprocess.DEVNULL)
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    so = build()
+    try:
+        L = C.CDLL(str(so))
+    except OSError:
+        so = build(force=True)
+        L = C.CDLL(str(so))
+    u8p, ip, fp = C.c_void_p, C.c_void_p, C.c_void_p
+    sz = C.c_size_t
+    L.orc_cv_round_f.argtypes = [C.c_float]; L.orc_cv_round_f.restype = C.c_int
+    L.orc_cv_round_d.argtypes = [C.c_double]; L.orc_cv_round_d.restype = C.c_int
+    L.orc_fast_atan2.argtypes = [C.c_float, C.c_float]; L.orc_fast_atan2.restype = C.c_float
+    L.orc_border_reflect101.argtypes = [u8p, C.c_int, C.c_int, sz, u8p, sz, C.c_int]
+    L.orc_border_reflect101.restype = None
+    L.orc_resize_linear_8u.argtypes = [u8p, C.c_int, C.c_int, sz, u8p, C.c_int, C.c_int, sz]
+    L.orc_resize_linear_8u.restype = None
+    L.orc_gaussian_blur_7x7_s2.argtypes = [u8p, C.c_int, C.c_int, sz, u8p, sz]
+    L.orc_gaussian_blur_7x7_s2.restype = None
+    L.orc_fast9_16.argtypes = [u8p, C.c_int, C.c_int, sz, C.c_int, C.c_int, ip, C.c_int]
+    L.orc_fast9_16.restype = C.c_int
+    L.orc_hamming256.argtypes = [u8p, u8p]; L.orc_hamming256.restype = C.c_int
+    L.orc_extractor_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+    L.orc_extractor_create.restype = C.c_void_p
+    L.orc_extractor_destroy.argtypes = [C.c_void_p]; L.orc_extractor_destroy.restype = None
+    L.orc_extractor_tables.argtypes = [C.c_void_p, fp, fp, fp, fp, ip, ip]
+    L.orc_extractor_tables.restype = None
+    L.orc_extractor_pattern.argtypes = [C.c_void_p, C.c_void_p]; L.orc_extractor_pattern.restype = None
+    L.orc_compute_pyramid.argtypes = [C.c_void_p, u8p, C.c_int, C.c_int, sz]
+    L.orc_compute_pyramid.restype = C.c_int
+    L.orc_pyramid_level.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int),
+                                    C.POINTER(C.c_int), C.POINTER(sz)]
+    L.orc_pyramid_level.restype = C.c_int
+    L.orc_detect_level.argtypes = [C.c_void_p, C.c_int, ip, C.c_int]; L.orc_detect_level.restype = C.c_int
+    L.orc_distribute_octree.argtypes = [ip, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, ip, C.c_int]
+    L.orc_distribute_octree.restype = C.c_int
+    L.orc_extract.argtypes = [C.c_void_p, u8p, C.c_int, C.c_int, sz, C.c_void_p, u8p, C.c_int, ip]
+    L.orc_extract.restype = C.c_int
+    L.orc_last_candidates.argtypes = [C.c_void_p, C.c_int, ip, C.c_int]
+    L.orc_last_candidates.restype = C.c_int
+    L.orc_stereo_match.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(StereoParams),
+                                   C.c_void_p, C.c_int, u8p, C.c_void_p, C.c_int, u8p,
+                                   fp, fp, fp, fp, ip, ip, ip]
+    L.orc_stereo_match.restype = C.c_int
+    L.orc_bench_stereo.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                   C.c_int, C.c_float, C.c_int, C.c_int, C.c_int,
+                                   C.c_float, C.c_float, C.c_int, C.POINTER(C.c_longlong)]
+    L.orc_bench_stereo.restype = C.c_double
+    _LIB = L
+    return L
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _img(a):
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    assert a.ndim == 2
+    return a
+
+
+# ------------------------------------------------------------------ primitives
+def cv_round(v):
+    return lib().orc_cv_round_d(float(v))
+
+
+def cv_round_f(v):
+    return lib().orc_cv_round_f(float(np.float32(v)))
+
+
+def fast_atan2(y, x):
+    return np.float32(lib().orc_fast_atan2(float(np.float32(y)), float(np.float32(x))))
+
+
+def border_reflect101(img, border):
+    img = _img(img)
+    h, w = img.shape
+    out = np.empty((h + 2 * border, w + 2 * border), np.uint8)
+    lib().orc_border_reflect101(_p(img), w, h, img.strides[0], _p(out), out.strides[0], border)
+    return out
+
+
+def resize_linear(img, dw, dh):
+    img = _img(img)
+    h, w = img.shape
+    out = np.empty((dh, dw), np.uint8)
+    lib().orc_resize_linear_8u(_p(img), w, h, img.strides[0], _p(out), dw, dh, out.strides[0])
+    return out
+
+
+def gaussian_blur(img):
+    img = _img(img)
+    h, w = img.shape
+    out = np.empty((h, w), np.uint8)
+    lib().orc_gaussian_blur_7x7_s2(_p(img), w, h, img.strides[0], _p(out), out.strides[0])
+    return out
+
+
+def fast9(img, threshold, nonmax=True):
+    img = _img(img)
+    h, w = img.shape
+    cap = max(16, w * h)
+    buf = np.empty((cap, 3), np.int32)
+    n = lib().orc_fast9_16(_p(img), w, h, img.strides[0], threshold, int(nonmax), _p(buf), cap)
+    return buf[:n].copy()
+
+
+def hamming256(a, b):
+    a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+    return lib().orc_hamming256(_p(a), _p(b))
+
+
+def distribute_octree(xyr, minX, maxX, minY, maxY, N):
+    xyr = np.ascontiguousarray(xyr, np.int32).reshape(-1, 3)
+    keep = np.empty(max(len(xyr), 1), np.int32)
+    n = lib().orc_distribute_octree(_p(xyr), len(xyr), minX, maxX, minY, maxY, N, _p(keep), len(keep))
+    return keep[:n].copy()
+
+
+# ------------------------------------------------------------------ extractor
+class Extractor:
+    """Mirror of ORB_SLAM2::ORBextractor (include/ORBextractor.h:76-168 in the reference)."""
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7):
+        self.nfeatures, self.nlevels = nfeatures, nlevels
+        self.h = lib().orc_extractor_create(nfeatures, scale_factor, nlevels, ini_th, min_th)
+        if not self.h:
+            raise ValueError("bad extractor parameters")
+        n = nlevels
+        self.scale = np.empty(n, np.float32); self.inv_scale = np.empty(n, np.float32)
+        self.sigma2 = np.empty(n, np.float32); self.inv_sigma2 = np.empty(n, np.float32)
+        self.quota = np.empty(n, np.int32); self.umax = np.empty(16, np.int32)
+        lib().orc_extractor_tables(self.h, _p(self.scale), _p(self.inv_scale), _p(self.sigma2),
+                                   _p(self.inv_sigma2), _p(self.quota), _p(self.umax))
+        self.pattern = np.empty((512, 2), np.int8)
+        lib().orc_extractor_pattern(self.h, _p(self.pattern))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_extractor_destroy(self.h)
+            self.h = None
+
+    def compute_pyramid(self, img):
+        img = _img(img)
+        h, w = img.shape
+        rc = lib().orc_compute_pyramid(self.h, _p(img), w, h, img.strides[0])
+        assert rc == 0
+        return [self.level(l) for l in range(self.nlevels)]
+
+    def level(self, l, padded=False):
+        ptr = C.c_void_p(); w = C.c_int(); h = C.c_int(); pitch = C.c_size_t()
+        rc = lib().orc_pyramid_level(self.h, l, C.byref(ptr), C.byref(w), C.byref(h), C.byref(pitch))
+        assert rc == 0
+        W, H, P = w.value, h.value, pitch.value
+        base = ptr.value - 19 * P - 19
+        buf = np.ctypeslib.as_array((C.c_uint8 * (P * (H + 38))).from_address(base)).reshape(H + 38, P)
+        return buf.copy() if padded else buf[19:19 + H, 19:19 + W].copy()
+
+    def detect_level(self, l, cap=200000):
+        buf = np.empty((cap, 3), np.int32)
+        n = lib().orc_detect_level(self.h, l, _p(buf), cap)
+        assert n <= cap
+        return buf[:n].copy()
+
+    def last_candidates(self, l, cap=200000):
+        buf = np.empty((cap, 3), np.int32)
+        n = lib().orc_last_candidates(self.h, l, _p(buf), cap)
+        assert 0 <= n <= cap
+        return buf[:n].copy()
+
+    def extract(self, img, cap=None):
+        """operator()(image, mask, keypoints, descriptors): returns (kps[KP_DTYPE], desc[n,32], level_counts)."""
+        img = _img(img)
+        h, w = img.shape
+        cap = cap or (self.nfeatures * 2 + 64)
+        kps = np.zeros(cap, KP_DTYPE); desc = np.zeros((cap, 32), np.uint8)
+        lc = np.zeros(self.nlevels, np.int32)
+        n = lib().orc_extract(self.h, _p(img), w, h, img.strides[0], _p(kps), _p(desc), cap, _p(lc))
+        assert n <= cap, (n, cap)
+        return kps[:n].copy(), desc[:n].copy(), lc
+
+
+def stereo_match(exL, exR, kL, dL, kR, dR, bf, b, mode=0, th_high=100, th_low=50, min_x=0.0,
+                 min_d=None, max_d=None):
+    """Frame::ComputeStereoMatches (mode 0) / _Undistorted (mode 1). Returns dict."""
+    kL = np.ascontiguousarray(kL); kR = np.ascontiguousarray(kR)
+    dL = np.ascontiguousarray(dL, np.uint8); dR = np.ascontiguousarray(dR, np.uint8)
+    nL, nR = len(kL), len(kR)
+    u = np.empty(max(nL, 1), np.float32); z = np.empty(max(nL, 1), np.float32)
+    bd = np.empty(max(nL, 1), np.int32); bi = np.empty(max(nL, 1), np.int32); sad = np.empty(max(nL, 1), np.int32)
+    prm = StereoParams(bf, b, mode, th_high, th_low, min_x)
+    if min_d is not None:
+        min_d = np.ascontiguousarray(min_d, np.float32); max_d = np.ascontiguousarray(max_d, np.float32)
+    r = lib().orc_stereo_match(exL.h, exR.h, C.byref(prm), _p(kL), nL, _p(dL), _p(kR), nR, _p(dR),
+                               _p(min_d), _p(max_d), _p(u), _p(z), _p(bd), _p(bi), _p(sad))
+    return dict(ret=r, uRight=u[:nL], depth=z[:nL], best_dist=bd[:nL], best_idx=bi[:nL], sad=sad[:nL])
+
+
+def bench_stereo(images, nframes, nthreads, shape=0, nfeatures=1000, scale_factor=1.2, nlevels=8,
+                 ini_th=20, min_th=7, bf=47.90639384423901, b=47.90639384423901 / 435.2046959714599,
+                 do_match=True):
+    images = np.ascontiguousarray(images, np.uint8)
+    n, h, w = images.shape
+    chk = C.c_longlong(0)
+    secs = lib().orc_bench_stereo(_p(images), n, w, h, nframes, nthreads, shape, nfeatures, scale_factor,
+                                  nlevels, ini_th, min_th, bf, b, int(do_match), C.byref(chk))
+    return secs, chk.value

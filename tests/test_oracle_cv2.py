@@ -1,0 +1,98 @@
+"""Oracle primitives vs the real OpenCV (cv2 4.13.0, the only OpenCV in the image): bit-exact.
+
+Pins the restated OpenCV arithmetic the reference relies on: resize INTER_LINEAR 8U,
+copyMakeBorder REFLECT_101, FAST-9/16 + NMS + score, GaussianBlur 7x7 sigma 2, fastAtan2, cvRound.
+"""
+import numpy as np
+import pytest
+
+cv2 = pytest.importorskip("cv2")
+from oracle import pyoracle as O
+
+cv2.setNumThreads(1)
+
+
+def _cvfast(img, t):
+    f = cv2.FastFeatureDetector_create(threshold=t, nonmaxSuppression=True,
+                                       type=cv2.FAST_FEATURE_DETECTOR_TYPE_9_16)
+    return np.array([[int(p.pt[0]), int(p.pt[1]), int(p.response)] for p in f.detect(img, None)],
+                    np.int32).reshape(-1, 3)
+
+
+@pytest.mark.parametrize("dst", [(627, 400), (522, 333), (376, 240), (700, 401), (751, 479)])
+def test_resize_fixture(fixtures, dst):
+    im = fixtures["EuRoC_l"]
+    assert np.array_equal(O.resize_linear(im, *dst), cv2.resize(im, dst, interpolation=cv2.INTER_LINEAR))
+
+
+def test_resize_random_cascade():
+    rng = np.random.default_rng(1)
+    im = rng.integers(0, 256, (480, 640), dtype=np.uint8)
+    for (w, h) in [(533, 400), (444, 333), (370, 278), (309, 231), (257, 193), (214, 161), (179, 134)]:
+        a = O.resize_linear(im, w, h)
+        assert np.array_equal(a, cv2.resize(im, (w, h), interpolation=cv2.INTER_LINEAR))
+        im = a
+
+
+def test_resize_exact_half_is_area():
+    rng = np.random.default_rng(2)
+    im = rng.integers(0, 256, (96, 128), dtype=np.uint8)
+    assert np.array_equal(O.resize_linear(im, 64, 48), cv2.resize(im, (64, 48), interpolation=cv2.INTER_LINEAR))
+
+
+def test_border(fixtures):
+    im = fixtures["TUM_l"]
+    assert np.array_equal(O.border_reflect101(im, 19), cv2.copyMakeBorder(im, 19, 19, 19, 19, cv2.BORDER_REFLECT_101))
+
+
+@pytest.mark.parametrize("shape", [(480, 752), (134, 210), (31, 45), (9, 9)])
+def test_blur(shape):
+    rng = np.random.default_rng(shape[0])
+    for im in (rng.integers(0, 256, shape, dtype=np.uint8), np.full(shape, 255, np.uint8)):
+        ref = cv2.GaussianBlur(im, (7, 7), 2, sigmaY=2, borderType=cv2.BORDER_REFLECT_101)
+        assert np.array_equal(O.gaussian_blur(im), ref)
+
+
+def test_blur_fixture(fixtures):
+    for n in ("EuRoC_l", "TUM_r"):
+        im = fixtures[n]
+        assert np.array_equal(O.gaussian_blur(im), cv2.GaussianBlur(im, (7, 7), 2, sigmaY=2,
+                                                                     borderType=cv2.BORDER_REFLECT_101))
+
+
+def test_fast_atan2():
+    rng = np.random.default_rng(3)
+    ys = rng.integers(-3_000_000, 3_000_000, 20000).astype(np.float32)
+    xs = rng.integers(-3_000_000, 3_000_000, 20000).astype(np.float32)
+    ys[:50] = 0; xs[50:100] = 0; xs[100:150] = ys[100:150]
+    for y, x in zip(ys, xs):
+        assert O.fast_atan2(y, x) == np.float32(cv2.fastAtan2(float(y), float(x)))
+
+
+def test_cv_round_half_even():
+    for v, e in [(0.5, 0), (1.5, 2), (2.5, 2), (-0.5, 0), (-1.5, -2), (626.6667, 627), (3.4999, 3)]:
+        assert O.cv_round(v) == e
+    assert O.cv_round_f(np.float32(752) * (np.float32(1) / np.float32(1.2))) == 627
+
+
+@pytest.mark.parametrize("t", [20, 7])
+def test_fast_fixture_and_cells(fixtures, t):
+    im = fixtures["EuRoC_l"]
+    assert np.array_equal(O.fast9(im, t), _cvfast(im, t))
+    rng = np.random.default_rng(t)
+    for _ in range(40):  # cell-sized crops incl. the degenerate narrow/short ones the cell loop can produce
+        w, h = int(rng.integers(4, 44)), int(rng.integers(4, 44))
+        x, y = int(rng.integers(0, 752 - w)), int(rng.integers(0, 480 - h))
+        cell = np.ascontiguousarray(im[y:y + h, x:x + w])
+        assert np.array_equal(O.fast9(cell, t), _cvfast(cell, t))
+
+
+@pytest.mark.parametrize("t", [20, 7])
+def test_fast_random_noise(t):
+    rng = np.random.default_rng(10 + t)
+    for lo, hi in [(0, 256), (100, 140), (0, 2)]:
+        im = rng.integers(lo, hi, (40, 38), dtype=np.uint8)
+        assert np.array_equal(O.fast9(im, t), _cvfast(im, t))
+    # equal-score plateaus: strict NMS must drop both neighbours
+    im = np.full((20, 20), 100, np.uint8); im[8:12, 8:12] = 200
+    assert np.array_equal(O.fast9(im, t), _cvfast(im, t))
