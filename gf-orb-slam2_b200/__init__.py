@@ -1,0 +1,323 @@
+"""gforb -- B200-native ORB stereo front-end (host-side Python mirror of the reference interface).
+
+Thin ctypes binding of ``libgforb.so`` (C ABI in ``include/gforb.h``; hand-written sm_100a kernels in
+``csrc/``).  Class and method names follow the reference (qiaozhijian/gf-orb-slam2):
+
+* :class:`ORBextractor`  -- ``ORB_SLAM2::ORBextractor`` (include/ORBextractor.h:76-168)
+* :func:`DescriptorDistance` -- ``ORBmatcher::DescriptorDistance`` (src/ORBmatcher.cc:1768-1784)
+* :func:`ComputeStereoMatches` -- ``Frame::ComputeStereoMatches`` / ``_Undistorted`` (src/Frame.cc:889-1078, 1167-1316)
+* :class:`StereoBatch` -- the batched ``Frame::Frame(imLeft, imRight, ...)`` front-end (src/Frame.cc:248-326)
+
+There is no CPU fallback: a missing library raises at import, a missing CUDA device raises on first use.
+The package directory name contains '-', so import it with
+``importlib.import_module("gf-orb-slam2_b200")``.
+"""
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+_HERE = Path(__file__).resolve().parent
+_SO = _HERE / "libgforb.so"
+if not _SO.exists():
+    raise ImportError(f"{_SO} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                      "(nvcc, sm_100a).  gforb has no CPU fallback.")
+_L = C.CDLL(str(_SO))
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+TH_HIGH, TH_LOW = 100, 50
+STEREO_CLASSIC, STEREO_UNDISTORTED = 0, 1
+OK, ERR_ARG, ERR_CAPACITY, ERR_CUDA, ERR_STATE, ERR_OVERFLOW = 0, -1, -2, -3, -4, -5
+
+
+class GforbError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"gforb error {code}: {msg}")
+        self.code = code
+
+
+class Params(C.Structure):
+    _fields_ = [("nfeatures", C.c_int32), ("scale_factor", C.c_float), ("nlevels", C.c_int32),
+                ("ini_th_fast", C.c_int32), ("min_th_fast", C.c_int32)]
+
+
+class Limits(C.Structure):
+    _fields_ = [("max_candidates_per_level", C.c_int32)]
+
+
+class StereoParams(C.Structure):
+    _fields_ = [("bf", C.c_float), ("b", C.c_float), ("mode", C.c_int32), ("th_high", C.c_int32),
+                ("th_low", C.c_int32), ("min_x", C.c_float)]
+
+
+_vp, _i, _sz = C.c_void_p, C.c_int, C.c_size_t
+_SIGS = {
+    "gforb_last_error_string": (C.c_char_p, []),
+    "gforb_version": (_i, []),
+    "gforb_extractor_create": (_i, [C.POINTER(Params), C.POINTER(Limits), C.POINTER(_vp)]),
+    "gforb_extractor_destroy": (None, [_vp]),
+    "gforb_extractor_tables": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gforb_extractor_params": (_i, [_vp, C.POINTER(Params)]),
+    "gforb_extract": (_i, [_vp, _vp, _i, _i, _sz, _vp, _vp, _i, C.POINTER(_i)]),
+    "gforb_extractor_max_keypoints": (_i, [_vp, _i, _i]),
+    "gforb_compute_pyramid": (_i, [_vp, _vp, _i, _i, _sz]),
+    "gforb_pyramid_level": (_i, [_vp, _i, C.POINTER(_vp), C.POINTER(_i), C.POINTER(_i), C.POINTER(_sz)]),
+    "gforb_download_pyramid": (_i, [_vp, _i, _vp, _sz, _i]),
+    "gforb_debug_candidates": (_i, [_vp, _i, _vp, _i, C.POINTER(_i)]),
+    "gforb_debug_level_counts": (_i, [_vp, _vp]),
+    "gforb_hamming256": (_i, [_vp, _vp]),
+    "gforb_stereo_match": (_i, [_vp, _vp, C.POINTER(StereoParams), _vp, _i, _vp, _vp, _i, _vp, _vp, _vp,
+                                _vp, _vp, C.POINTER(_i)]),
+    "gforb_debug_stereo": (_i, [_vp, _i, _vp, _vp, _vp]),
+    "gforb_batch_create": (_i, [C.POINTER(Params), C.POINTER(Limits), _i, _i, _i, C.POINTER(_vp)]),
+    "gforb_batch_destroy": (None, [_vp]),
+    "gforb_batch_set_stream": (_i, [_vp, _vp]),
+    "gforb_batch_capacity": (_i, [_vp, C.POINTER(_i), C.POINTER(_i)]),
+    "gforb_batch_device_input": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz), C.POINTER(_sz)]),
+    "gforb_batch_upload": (_i, [_vp, _vp, _vp, _i]),
+    "gforb_batch_run": (_i, [_vp, _i, C.POINTER(StereoParams)]),
+    "gforb_batch_download": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp]),
+    "gforb_batch_sync": (_i, [_vp]),
+    "gforb_stereo_frames_batch": (_i, [_vp, _vp, _vp, _i, C.POINTER(StereoParams), _vp, _vp, _vp, _vp, _vp]),
+    "gforb_batch_launches_per_run": (_i, [_vp, _i]),
+    "gforb_batch_stage_timing": (_i, [_vp, _i]),
+    "gforb_batch_stage_times": (_i, [_vp, _vp]),
+    "gforb_host_alloc": (_i, [C.POINTER(_vp), _sz]),
+    "gforb_host_free": (None, [_vp]),
+}
+for _name, (_res, _args) in _SIGS.items():
+    _fn = getattr(_L, _name)       # AttributeError here = the library does not export a declared symbol
+    _fn.restype, _fn.argtypes = _res, _args
+
+lib = _L
+LIBRARY_PATH = str(_SO)
+
+
+def _check(rc):
+    if rc != 0:
+        raise GforbError(rc, _L.gforb_last_error_string().decode())
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _stereo_params(bf, b, mode, th_high, th_low, min_x):
+    return StereoParams(bf, b, mode, th_high, th_low, min_x)
+
+
+def DescriptorDistance(a, b):
+    """ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1768-1784)."""
+    a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+    assert a.size == 32 and b.size == 32
+    return _L.gforb_hamming256(_p(a), _p(b))
+
+
+class ORBextractor:
+    """ORB_SLAM2::ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST)."""
+
+    def __init__(self, nfeatures=1000, scaleFactor=1.2, nlevels=8, iniThFAST=20, minThFAST=7,
+                 max_candidates_per_level=0):
+        self._h = _vp()
+        prm = Params(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST)
+        lim = Limits(max_candidates_per_level)
+        _check(_L.gforb_extractor_create(C.byref(prm), C.byref(lim), C.byref(self._h)))
+        self.nfeatures, self.scaleFactor, self.nlevels = nfeatures, scaleFactor, nlevels
+        self.iniThFAST, self.minThFAST = iniThFAST, minThFAST
+        n = nlevels
+        self._scale = np.empty(n, np.float32); self._inv = np.empty(n, np.float32)
+        self._sig = np.empty(n, np.float32); self._isig = np.empty(n, np.float32)
+        self.mnFeaturesPerLevel = np.empty(n, np.int32); self.umax = np.empty(16, np.int32)
+        _check(_L.gforb_extractor_tables(self._h, _p(self._scale), _p(self._inv), _p(self._sig), _p(self._isig),
+                                         _p(self.mnFeaturesPerLevel), _p(self.umax)))
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            _L.gforb_extractor_destroy(h)
+            self._h = None
+
+    # getters, include/ORBextractor.h:93-119
+    def GetLevels(self): return self.nlevels
+    def GetScaleFactor(self): return self.scaleFactor
+    def GetInitThres(self): return self.iniThFAST
+    def GetMinThres(self): return self.minThFAST
+    def GetScaleFactors(self): return self._scale.copy()
+    def GetInverseScaleFactors(self): return self._inv.copy()
+    def GetScaleSigmaSquares(self): return self._sig.copy()
+    def GetInverseScaleSigmaSquares(self): return self._isig.copy()
+
+    def __call__(self, image, mask=None):
+        """operator()(image, mask, keypoints, descriptors) -> (keypoints[KP_DTYPE], descriptors[n,32] u8).
+        The mask is ignored, as in the reference."""
+        if image is None or image.size == 0:
+            return np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
+        if image.dtype != np.uint8 or image.ndim != 2:
+            raise GforbError(ERR_ARG, "image must be 2-D uint8 (CV_8UC1)")
+        if image.strides[1] != 1:
+            image = np.ascontiguousarray(image)
+        h, w = image.shape
+        cap = _L.gforb_extractor_max_keypoints(self._h, w, h)
+        if cap < 0:
+            _check(cap)
+        kps = np.empty(cap, KP_DTYPE); desc = np.empty((cap, 32), np.uint8)
+        n = _i(0)
+        _check(_L.gforb_extract(self._h, _p(image), w, h, image.strides[0], _p(kps), _p(desc), cap, C.byref(n)))
+        return kps[:n.value].copy(), desc[:n.value].copy()
+
+    def ComputePyramid(self, image):
+        if image.dtype != np.uint8 or image.ndim != 2:
+            raise GforbError(ERR_ARG, "image must be 2-D uint8 (CV_8UC1)")
+        if image.strides[1] != 1:
+            image = np.ascontiguousarray(image)
+        h, w = image.shape
+        _check(_L.gforb_compute_pyramid(self._h, _p(image), w, h, image.strides[0]))
+
+    def level_geometry(self, level):
+        ptr, w, h, pitch = _vp(), _i(), _i(), _sz()
+        _check(_L.gforb_pyramid_level(self._h, level, C.byref(ptr), C.byref(w), C.byref(h), C.byref(pitch)))
+        return ptr.value, w.value, h.value, pitch.value
+
+    def pyramid_level(self, level, with_border=False):
+        """Host copy of mvImagePyramid[level] (with its 19-px REFLECT_101 frame if asked)."""
+        _, w, h, _ = self.level_geometry(level)
+        if with_border:
+            w, h = w + 38, h + 38
+        out = np.empty((h, w), np.uint8)
+        _check(_L.gforb_download_pyramid(self._h, level, _p(out), out.strides[0], int(with_border)))
+        return out
+
+    @property
+    def mvImagePyramid(self):
+        return [self.pyramid_level(l) for l in range(self.nlevels)]
+
+    def debug_candidates(self, level, cap=400000):
+        buf = np.empty((cap, 3), np.int32); n = _i(0)
+        _check(_L.gforb_debug_candidates(self._h, level, _p(buf), cap, C.byref(n)))
+        return buf[:n.value].copy()
+
+    def debug_level_counts(self):
+        c = np.empty(self.nlevels, np.int32)
+        _check(_L.gforb_debug_level_counts(self._h, _p(c)))
+        return c
+
+
+def ComputeStereoMatches(exL, exR, kpsL, descL, kpsR, descR, bf, b, mode=STEREO_CLASSIC, th_high=TH_HIGH,
+                         th_low=TH_LOW, min_x=0.0, min_d=None, max_d=None, debug=False):
+    """Frame::ComputeStereoMatches (mode CLASSIC) / ComputeStereoMatches_Undistorted (mode UNDISTORTED).
+
+    Returns dict(mvuRight, mvDepth, nmatched[, best_dist, best_idx, sad])."""
+    kpsL = np.ascontiguousarray(kpsL, KP_DTYPE); kpsR = np.ascontiguousarray(kpsR, KP_DTYPE)
+    descL = np.ascontiguousarray(descL, np.uint8); descR = np.ascontiguousarray(descR, np.uint8)
+    nL, nR = len(kpsL), len(kpsR)
+    u = np.full(max(nL, 1), -1, np.float32); z = np.full(max(nL, 1), -1, np.float32)
+    if min_d is not None:
+        min_d = np.ascontiguousarray(min_d, np.float32); max_d = np.ascontiguousarray(max_d, np.float32)
+    prm = _stereo_params(bf, b, mode, th_high, th_low, min_x)
+    nm = _i(0)
+    _check(_L.gforb_stereo_match(exL._h, exR._h, C.byref(prm), _p(kpsL), nL, _p(descL), _p(kpsR), nR, _p(descR),
+                                 _p(min_d), _p(max_d), _p(u), _p(z), C.byref(nm)))
+    out = dict(mvuRight=u[:nL], mvDepth=z[:nL], nmatched=nm.value)
+    if debug and nL:
+        bd = np.empty(nL, np.int32); bi = np.empty(nL, np.int32); sad = np.empty(nL, np.int32)
+        _check(_L.gforb_debug_stereo(exL._h, nL, _p(bd), _p(bi), _p(sad)))
+        out.update(best_dist=bd, best_idx=bi, sad=sad)
+    return out
+
+
+class PinnedArray:
+    """numpy view over cudaHostAlloc'ed memory (for async H2D/D2H in StereoBatch)."""
+
+    def __init__(self, shape, dtype):
+        self.dtype = np.dtype(dtype)
+        self.nbytes = int(np.prod(shape)) * self.dtype.itemsize
+        self._ptr = _vp()
+        _check(_L.gforb_host_alloc(C.byref(self._ptr), max(self.nbytes, 16)))
+        buf = (C.c_uint8 * max(self.nbytes, 16)).from_address(self._ptr.value)
+        self.array = np.frombuffer(buf, dtype=self.dtype, count=int(np.prod(shape))).reshape(shape)
+
+    def __del__(self):
+        p = getattr(self, "_ptr", None)
+        if p:
+            self.array = None
+            _L.gforb_host_free(p)
+            self._ptr = None
+
+
+class StereoBatch:
+    """Batched stereo front-end: for each frame, ExtractORB(left), ExtractORB(right), ComputeStereoMatches
+    (src/Frame.cc:248-326), all on the device."""
+
+    def __init__(self, width, height, max_frames, nfeatures=1000, scaleFactor=1.2, nlevels=8, iniThFAST=20,
+                 minThFAST=7, max_candidates_per_level=0):
+        self._h = _vp()
+        prm = Params(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST)
+        lim = Limits(max_candidates_per_level)
+        _check(_L.gforb_batch_create(C.byref(prm), C.byref(lim), width, height, max_frames, C.byref(self._h)))
+        self.width, self.height, self.max_frames = width, height, max_frames
+        mf, K = _i(), _i()
+        _check(_L.gforb_batch_capacity(self._h, C.byref(mf), C.byref(K)))
+        self.K = K.value
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            _L.gforb_batch_destroy(h)
+            self._h = None
+
+    def set_stream(self, cuda_stream_ptr):
+        _check(_L.gforb_batch_set_stream(self._h, _vp(cuda_stream_ptr) if cuda_stream_ptr else None))
+
+    def device_input(self):
+        ptr, stride, pitch = _vp(), _sz(), _sz()
+        _check(_L.gforb_batch_device_input(self._h, C.byref(ptr), C.byref(stride), C.byref(pitch)))
+        return ptr.value, stride.value, pitch.value
+
+    def upload(self, left, right):
+        n = left.shape[0]
+        assert left.shape == right.shape == (n, self.height, self.width) and left.dtype == np.uint8
+        assert left.flags.c_contiguous and right.flags.c_contiguous
+        _check(_L.gforb_batch_upload(self._h, _p(left), _p(right), n))
+
+    def run(self, n_frames, bf=None, b=None, mode=STEREO_CLASSIC, th_high=TH_HIGH, th_low=TH_LOW, min_x=0.0):
+        prm = None if bf is None else C.byref(_stereo_params(bf, b, mode, th_high, th_low, min_x))
+        _check(_L.gforb_batch_run(self._h, n_frames, prm))
+
+    def launches_per_run(self, with_stereo=True):
+        return _L.gforb_batch_launches_per_run(self._h, int(with_stereo))
+
+    STAGES = ("pyramid", "fast", "quadtree", "blur", "describe", "stereo")
+
+    def stage_timing(self, enable=True):
+        _check(_L.gforb_batch_stage_timing(self._h, int(enable)))
+
+    def stage_times(self):
+        ms = np.zeros(6, np.float32)
+        _check(_L.gforb_batch_stage_times(self._h, _p(ms)))
+        return dict(zip(self.STAGES, ms.tolist()))
+
+    def alloc_outputs(self, n_frames, pinned=True):
+        K = self.K
+        shapes = dict(counts=((2 * n_frames,), np.int32), keypoints=((2 * n_frames, K), KP_DTYPE),
+                      descriptors=((2 * n_frames, K, 32), np.uint8), u_right=((n_frames, K), np.float32),
+                      depth=((n_frames, K), np.float32))
+        if pinned:
+            self._pins = {k: PinnedArray(s, d) for k, (s, d) in shapes.items()}
+            return {k: p.array for k, p in self._pins.items()}
+        return {k: np.empty(s, d) for k, (s, d) in shapes.items()}
+
+    def download(self, n_frames, out):
+        _check(_L.gforb_batch_download(self._h, n_frames, _p(out.get("counts")), _p(out.get("keypoints")),
+                                       _p(out.get("descriptors")), _p(out.get("u_right")), _p(out.get("depth"))))
+
+    def sync(self):
+        _check(_L.gforb_batch_sync(self._h))
+
+    def process(self, left, right, out, bf, b, mode=STEREO_CLASSIC):
+        """End-to-end: host images in, host results out (upload + run + download + sync)."""
+        n = left.shape[0]
+        prm = _stereo_params(bf, b, mode, TH_HIGH, TH_LOW, 0.0)
+        _check(_L.gforb_stereo_frames_batch(self._h, _p(left), _p(right), n, C.byref(prm), _p(out.get("counts")),
+                                            _p(out.get("keypoints")), _p(out.get("descriptors")),
+                                            _p(out.get("u_right")), _p(out.get("depth"))))

@@ -1,0 +1,464 @@
+// C ABI of libgforb.so (declared in include/gforb.h).
+#include <algorithm>
+#include <cstring>
+#include <memory>
+#include <new>
+
+#include "engine.hpp"
+
+using namespace gforb;
+
+struct gforb_extractor {
+    Tables tab;
+    gforb_limits lim{};
+    Engine eng;
+    cudaStream_t stream = nullptr;
+    int last_n = 0;
+    bool extracted = false;
+    // staging for host-provided key sets (gforb_stereo_match)
+    gforb_keypoint* st_k = nullptr; uint8_t* st_d = nullptr; int32_t* st_n = nullptr; float* st_win = nullptr;
+    int st_cap = 0;
+    float *st_u = nullptr, *st_z = nullptr; int32_t *st_bd = nullptr, *st_bi = nullptr, *st_sad = nullptr, *st_nm = nullptr;
+    ~gforb_extractor() {
+        free_stereo();
+        eng.release();
+        if (stream) cudaStreamDestroy(stream);
+    }
+    void free_stereo() {
+        auto fr = [](auto*& p) { if (p) cudaFree(p); p = nullptr; };
+        fr(st_k); fr(st_d); fr(st_n); fr(st_win); fr(st_u); fr(st_z); fr(st_bd); fr(st_bi); fr(st_sad); fr(st_nm);
+        st_cap = 0;
+    }
+};
+
+struct gforb_batch {
+    Tables tab;
+    gforb_limits lim{};
+    Engine eng;
+    cudaStream_t own = nullptr, stream = nullptr;
+    int max_frames = 0;
+    bool timing = false;
+    cudaEvent_t ev[7] = {};
+    ~gforb_batch() {
+        for (auto& e : ev) if (e) cudaEventDestroy(e);
+        eng.release();
+        if (own) cudaStreamDestroy(own);
+    }
+};
+
+namespace {
+int ensure_stream(cudaStream_t& s) {
+    if (s) return GFORB_OK;
+    cudaError_t e = cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaStreamCreate");
+    return GFORB_OK;
+}
+int ensure_engine(gforb_extractor* ex, int w, int h) {
+    int rc = ensure_stream(ex->stream);
+    if (rc) return rc;
+    if (ex->eng.ready && ex->eng.g.W == w && ex->eng.g.H == h) return GFORB_OK;
+    ex->extracted = false;
+    return ex->eng.init(ex->tab, ex->lim, w, h, 1, 1);
+}
+gforb_stereo_params norm_params(const gforb_stereo_params& p) {
+    gforb_stereo_params q = p;
+    if (q.th_high <= 0) q.th_high = GFORB_TH_HIGH;
+    if (q.th_low <= 0) q.th_low = GFORB_TH_LOW;
+    q.th_high = std::min(q.th_high, 256);
+    return q;
+}
+void fill_view_levels(StereoView& v, const Engine& L, const Engine& R, size_t frame_mul, size_t right_img_off) {
+    const Geom& g = L.g;
+    for (int l = 0; l < g.nlevels; ++l) {
+        const LevelGeom& a = g.lv[l];
+        const LevelGeom& c = R.g.lv[l];
+        v.pyrL[l] = L.b.pyr + a.off + (size_t)kEdge * a.pitch + kXPad;
+        v.pyrR[l] = R.b.pyr + c.off + right_img_off * c.img_stride + (size_t)kEdge * c.pitch + kXPad;
+        v.frame_stride[l] = frame_mul * a.img_stride;
+        v.pitch[l] = a.pitch; v.w[l] = a.w;
+        v.scale[l] = a.scale; v.inv_scale[l] = a.inv_scale;
+    }
+    v.nRows = g.lv[0].h;
+}
+}  // namespace
+
+extern "C" {
+
+const char* gforb_last_error_string(void) { return last_error(); }
+int gforb_version(void) { return GFORB_VERSION; }
+
+int gforb_hamming256(const void* a, const void* b) {
+    uint64_t x[4], y[4];
+    std::memcpy(x, a, 32); std::memcpy(y, b, 32);
+    int d = 0;
+    for (int i = 0; i < 4; ++i) d += __builtin_popcountll(x[i] ^ y[i]);
+    return d;
+}
+
+int gforb_host_alloc(void** ptr, size_t bytes) {
+    if (!ptr) return GFORB_ERR_ARG;
+    cudaError_t e = cudaHostAlloc(ptr, bytes, cudaHostAllocDefault);
+    return e == cudaSuccess ? GFORB_OK : cuda_fail(e, "cudaHostAlloc");
+}
+void gforb_host_free(void* ptr) { if (ptr) cudaFreeHost(ptr); }
+
+// --------------------------------------------------------------------------------------------- extractor
+int gforb_extractor_create(const gforb_params* p, const gforb_limits* lim, gforb_extractor** out) {
+    if (!p || !out) { set_error("gforb_extractor_create: null argument"); return GFORB_ERR_ARG; }
+    std::unique_ptr<gforb_extractor> ex(new (std::nothrow) gforb_extractor);
+    if (!ex) return GFORB_ERR_ARG;
+    int rc = make_tables(*p, ex->tab);
+    if (rc) return rc;
+    if (lim) ex->lim = *lim;
+    *out = ex.release();
+    return GFORB_OK;
+}
+void gforb_extractor_destroy(gforb_extractor* ex) { delete ex; }
+
+int gforb_extractor_tables(const gforb_extractor* ex, float* scale, float* inv_scale, float* sigma2,
+                           float* inv_sigma2, int32_t* fpl, int32_t* umax) {
+    if (!ex) return GFORB_ERR_ARG;
+    const size_t n = (size_t)ex->tab.prm.nlevels;
+    if (scale) std::memcpy(scale, ex->tab.scale.data(), n * 4);
+    if (inv_scale) std::memcpy(inv_scale, ex->tab.inv_scale.data(), n * 4);
+    if (sigma2) std::memcpy(sigma2, ex->tab.sigma2.data(), n * 4);
+    if (inv_sigma2) std::memcpy(inv_sigma2, ex->tab.inv_sigma2.data(), n * 4);
+    if (fpl) std::memcpy(fpl, ex->tab.quota.data(), n * 4);
+    if (umax) std::memcpy(umax, ex->tab.umax, 64);
+    return GFORB_OK;
+}
+int gforb_extractor_params(const gforb_extractor* ex, gforb_params* out) {
+    if (!ex || !out) return GFORB_ERR_ARG;
+    *out = ex->tab.prm;
+    return GFORB_OK;
+}
+int gforb_extractor_max_keypoints(const gforb_extractor* ex, int w, int h) {
+    if (!ex) return GFORB_ERR_ARG;
+    Geom g; std::vector<int32_t> tabs; size_t a, b;
+    int rc = make_geometry(ex->tab, ex->lim, w, h, 1, g, tabs, a, b);
+    return rc ? rc : g.K;
+}
+
+int gforb_compute_pyramid(gforb_extractor* ex, const uint8_t* image, int w, int h, size_t pitch) {
+    if (!ex) return GFORB_ERR_ARG;
+    if (!image || w <= 0 || h <= 0) return GFORB_OK;   // reference: no-op on empty input
+    if (pitch < (size_t)w) { set_error("gforb: pitch < width"); return GFORB_ERR_ARG; }
+    int rc = ensure_engine(ex, w, h);
+    if (rc) return rc;
+    rc = ex->eng.upload_images(image, pitch, 0, 1, 1, ex->stream);
+    if (rc) return rc;
+    rc = ex->eng.run_pyramid(1, ex->stream);
+    if (rc) return rc;
+    ex->extracted = false;
+    cudaError_t e = cudaStreamSynchronize(ex->stream);
+    return e == cudaSuccess ? GFORB_OK : cuda_fail(e, "cudaStreamSynchronize");
+}
+
+int gforb_extract(gforb_extractor* ex, const uint8_t* image, int w, int h, size_t pitch,
+                  gforb_keypoint* kps, uint8_t* desc, int cap, int* n) {
+    if (!ex || !n) { set_error("gforb_extract: null argument"); return GFORB_ERR_ARG; }
+    *n = 0;
+    if (!image || w <= 0 || h <= 0) return GFORB_OK;   // src/ORBextractor.cc:1115-1116
+    if (pitch < (size_t)w || cap < 0 || (cap > 0 && (!kps || !desc))) {
+        set_error("gforb_extract: bad pitch/capacity/buffers");
+        return GFORB_ERR_ARG;
+    }
+    int rc = ensure_engine(ex, w, h);
+    if (rc) return rc;
+    Engine& E = ex->eng;
+    rc = E.upload_images(image, pitch, 0, 1, 1, ex->stream);
+    if (rc) return rc;
+    rc = E.run_extract(1, ex->stream);
+    if (rc) return rc;
+    cudaError_t e = cudaMemcpyAsync(E.h_small + 4, E.b.nkp, 4, cudaMemcpyDeviceToHost, ex->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpyAsync(nkp)");
+    rc = E.check_errors(ex->stream);   // synchronises
+    if (rc) return rc;
+    const int cnt = E.h_small[4];
+    *n = cnt;
+    ex->last_n = cnt;
+    ex->extracted = true;
+    if (cnt > cap) { set_error("gforb_extract: keypoint capacity too small"); return GFORB_ERR_CAPACITY; }
+    if (cnt > 0) {
+        e = cudaMemcpyAsync(kps, E.b.kps, (size_t)cnt * sizeof(gforb_keypoint), cudaMemcpyDeviceToHost, ex->stream);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpyAsync(kps)");
+        e = cudaMemcpyAsync(desc, E.b.desc, (size_t)cnt * 32, cudaMemcpyDeviceToHost, ex->stream);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpyAsync(desc)");
+        e = cudaStreamSynchronize(ex->stream);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaStreamSynchronize");
+    }
+    return GFORB_OK;
+}
+
+int gforb_pyramid_level(const gforb_extractor* ex, int level, const uint8_t** dev_ptr, int* w, int* h, size_t* pitch) {
+    if (!ex || !ex->eng.ready || !ex->eng.pyramid_valid) { set_error("gforb: no pyramid yet"); return GFORB_ERR_STATE; }
+    if (level < 0 || level >= ex->eng.g.nlevels) return GFORB_ERR_ARG;
+    const LevelGeom& L = ex->eng.g.lv[level];
+    if (dev_ptr) *dev_ptr = ex->eng.b.pyr + L.off + (size_t)kEdge * L.pitch + kXPad;
+    if (w) *w = L.w;
+    if (h) *h = L.h;
+    if (pitch) *pitch = (size_t)L.pitch;
+    return GFORB_OK;
+}
+
+int gforb_download_pyramid(gforb_extractor* ex, int level, uint8_t* host, size_t host_pitch, int with_border) {
+    if (!ex || !host) return GFORB_ERR_ARG;
+    if (!ex->eng.ready || !ex->eng.pyramid_valid) { set_error("gforb: no pyramid yet"); return GFORB_ERR_STATE; }
+    if (level < 0 || level >= ex->eng.g.nlevels) return GFORB_ERR_ARG;
+    const LevelGeom& L = ex->eng.g.lv[level];
+    const int bw = with_border ? L.w + 2 * kEdge : L.w, bh = with_border ? L.h + 2 * kEdge : L.h;
+    if (host_pitch < (size_t)bw) return GFORB_ERR_ARG;
+    const uint8_t* src = ex->eng.b.pyr + L.off +
+                         (with_border ? (size_t)(kXPad - kEdge) : (size_t)kEdge * L.pitch + kXPad);
+    cudaError_t e = cudaMemcpy2DAsync(host, host_pitch, src, L.pitch, bw, bh, cudaMemcpyDeviceToHost, ex->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy2DAsync(pyramid)");
+    e = cudaStreamSynchronize(ex->stream);
+    return e == cudaSuccess ? GFORB_OK : cuda_fail(e, "cudaStreamSynchronize");
+}
+
+int gforb_debug_candidates(gforb_extractor* ex, int level, int32_t* xyr, int cap, int* n) {
+    if (!ex || !n) return GFORB_ERR_ARG;
+    if (!ex->eng.ready || !ex->extracted) { set_error("gforb: no extraction yet"); return GFORB_ERR_STATE; }
+    const Geom& g = ex->eng.g;
+    if (level < 0 || level >= g.nlevels) return GFORB_ERR_ARG;
+    const LevelGeom& L = g.lv[level];
+    std::vector<uint32_t> cnt((size_t)std::max(L.ncells, 1)), pts((size_t)std::max(L.ncells, 1) * g.cell_cap);
+    if (L.ncells > 0) {
+        cudaError_t e = cudaMemcpy(cnt.data(), ex->eng.b.cell_cnt + L.cell_base, (size_t)L.ncells * 4, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy(cell_cnt)");
+        e = cudaMemcpy(pts.data(), ex->eng.b.cell_pts + (size_t)L.cell_base * g.cell_cap,
+                       (size_t)L.ncells * g.cell_cap * 4, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy(cell_pts)");
+    }
+    int k = 0;
+    for (int c = 0; c < L.ncells; ++c)
+        for (uint32_t i = 0; i < cnt[c]; ++i, ++k)
+            if (k < cap && xyr) {
+                const uint32_t p = pts[(size_t)c * g.cell_cap + i];
+                xyr[3 * k] = cand_x(p); xyr[3 * k + 1] = cand_y(p); xyr[3 * k + 2] = cand_r(p);
+            }
+    *n = k;
+    return k > cap && xyr ? GFORB_ERR_CAPACITY : GFORB_OK;
+}
+
+int gforb_debug_level_counts(gforb_extractor* ex, int32_t* counts) {
+    if (!ex || !counts) return GFORB_ERR_ARG;
+    if (!ex->eng.ready || !ex->extracted) { set_error("gforb: no extraction yet"); return GFORB_ERR_STATE; }
+    cudaError_t e = cudaMemcpy(counts, ex->eng.b.lvl_cnt, (size_t)ex->eng.g.nlevels * 4, cudaMemcpyDeviceToHost);
+    return e == cudaSuccess ? GFORB_OK : cuda_fail(e, "cudaMemcpy(lvl_cnt)");
+}
+
+// ------------------------------------------------------------------------------------------------ stereo
+int gforb_stereo_match(gforb_extractor* exL, gforb_extractor* exR, const gforb_stereo_params* prm,
+                       const gforb_keypoint* kL, int nL, const uint8_t* dL,
+                       const gforb_keypoint* kR, int nR, const uint8_t* dR,
+                       const float* min_d, const float* max_d, float* u_right, float* depth, int* n_matched) {
+    if (!exL || !exR || !prm || nL < 0 || nR < 0 || (nL > 0 && (!kL || !dL || !u_right || !depth)) ||
+        (nR > 0 && (!kR || !dR)) || ((min_d == nullptr) != (max_d == nullptr))) {
+        set_error("gforb_stereo_match: bad arguments");
+        return GFORB_ERR_ARG;
+    }
+    if (!exL->eng.ready || !exR->eng.ready || !exL->eng.pyramid_valid || !exR->eng.pyramid_valid) {
+        set_error("gforb_stereo_match: both extractors need a pyramid (extract or compute_pyramid first)");
+        return GFORB_ERR_STATE;
+    }
+    const Geom& gl = exL->eng.g; const Geom& gr = exR->eng.g;
+    if (gl.W != gr.W || gl.H != gr.H || gl.nlevels != gr.nlevels) {
+        set_error("gforb_stereo_match: left/right pyramids differ in geometry");
+        return GFORB_ERR_ARG;
+    }
+    if (nL > 65535 || nR > 65535) { set_error("gforb_stereo_match: more than 65535 keys"); return GFORB_ERR_ARG; }
+    for (int i = 0; i < nL; ++i) if (kL[i].octave < 0 || kL[i].octave >= gl.nlevels) { set_error("gforb_stereo_match: bad octave"); return GFORB_ERR_ARG; }
+    for (int i = 0; i < nR; ++i) if (kR[i].octave < 0 || kR[i].octave >= gl.nlevels) { set_error("gforb_stereo_match: bad octave"); return GFORB_ERR_ARG; }
+    if (n_matched) *n_matched = 0;
+    if (nL == 0) return GFORB_OK;
+
+    const int need = std::max(std::max(nL, nR), 8);
+    cudaStream_t s = exL->stream;
+    cudaError_t e;
+    if (need > exL->st_cap) {
+        exL->free_stereo();
+        const size_t K = (size_t)need;
+#define GA(p, bytes) do { e = cudaMalloc(&(p), (bytes)); if (e != cudaSuccess) { exL->free_stereo(); return cuda_fail(e, "cudaMalloc(stereo staging)"); } } while (0)
+        GA(exL->st_k, 2 * K * sizeof(gforb_keypoint)); GA(exL->st_d, 2 * K * 32); GA(exL->st_n, 16);
+        GA(exL->st_win, 2 * K * 4); GA(exL->st_u, K * 4); GA(exL->st_z, K * 4); GA(exL->st_bd, K * 4);
+        GA(exL->st_bi, K * 4); GA(exL->st_sad, K * 4); GA(exL->st_nm, 16);
+#undef GA
+        exL->st_cap = need;
+    }
+    const size_t K = (size_t)exL->st_cap;
+    // the right pyramid is produced on exR's stream: make sure it is complete
+    e = cudaStreamSynchronize(exR->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaStreamSynchronize(right)");
+    int32_t nn[2] = {nL, nR};
+    cudaMemcpyAsync(exL->st_k, kL, (size_t)nL * sizeof(gforb_keypoint), cudaMemcpyHostToDevice, s);
+    cudaMemcpyAsync(exL->st_d, dL, (size_t)nL * 32, cudaMemcpyHostToDevice, s);
+    if (nR > 0) {
+        cudaMemcpyAsync(exL->st_k + K, kR, (size_t)nR * sizeof(gforb_keypoint), cudaMemcpyHostToDevice, s);
+        cudaMemcpyAsync(exL->st_d + K * 32, dR, (size_t)nR * 32, cudaMemcpyHostToDevice, s);
+    }
+    cudaMemcpyAsync(exL->st_n, nn, 8, cudaMemcpyHostToDevice, s);
+    if (min_d) {
+        cudaMemcpyAsync(exL->st_win, min_d, (size_t)nL * 4, cudaMemcpyHostToDevice, s);
+        cudaMemcpyAsync(exL->st_win + K, max_d, (size_t)nL * 4, cudaMemcpyHostToDevice, s);
+    }
+    StereoView v{};
+    v.kL = exL->st_k; v.kR = exL->st_k + K; v.dL = exL->st_d; v.dR = exL->st_d + K * 32;
+    v.nL = exL->st_n; v.nR = exL->st_n + 1; v.k_stride = 0; v.n_stride = 0;
+    fill_view_levels(v, exL->eng, exR->eng, 0, 0);
+    v.min_d = min_d ? exL->st_win : nullptr; v.max_d = min_d ? exL->st_win + K : nullptr;
+    v.uright = exL->st_u; v.depth = exL->st_z; v.best_dist = exL->st_bd; v.best_idx = exL->st_bi;
+    v.sad = exL->st_sad; v.nmatch = exL->st_nm; v.out_stride = 0;
+    launch_stereo(v, norm_params(*prm), 1, (int)K, s);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "stereo launch");
+    int32_t nm = 0;
+    cudaMemcpyAsync(u_right, exL->st_u, (size_t)nL * 4, cudaMemcpyDeviceToHost, s);
+    cudaMemcpyAsync(depth, exL->st_z, (size_t)nL * 4, cudaMemcpyDeviceToHost, s);
+    cudaMemcpyAsync(&nm, exL->st_nm, 4, cudaMemcpyDeviceToHost, s);
+    e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaStreamSynchronize(stereo)");
+    if (n_matched) *n_matched = nm;
+    return GFORB_OK;
+}
+
+int gforb_debug_stereo(gforb_extractor* exL, int nL, int32_t* bd, int32_t* bi, int32_t* sad) {
+    if (!exL || nL < 0 || nL > exL->st_cap) return GFORB_ERR_ARG;
+    cudaError_t e = cudaSuccess;
+    if (bd) e = cudaMemcpy(bd, exL->st_bd, (size_t)nL * 4, cudaMemcpyDeviceToHost);
+    if (bi && e == cudaSuccess) e = cudaMemcpy(bi, exL->st_bi, (size_t)nL * 4, cudaMemcpyDeviceToHost);
+    if (sad && e == cudaSuccess) e = cudaMemcpy(sad, exL->st_sad, (size_t)nL * 4, cudaMemcpyDeviceToHost);
+    return e == cudaSuccess ? GFORB_OK : cuda_fail(e, "cudaMemcpy(stereo debug)");
+}
+
+// ------------------------------------------------------------------------------------------------- batch
+int gforb_batch_create(const gforb_params* p, const gforb_limits* lim, int w, int h, int max_frames, gforb_batch** out) {
+    if (!p || !out || w <= 0 || h <= 0 || max_frames < 1 || max_frames > 32767) {
+        set_error("gforb_batch_create: bad arguments");
+        return GFORB_ERR_ARG;
+    }
+    std::unique_ptr<gforb_batch> b(new (std::nothrow) gforb_batch);
+    if (!b) return GFORB_ERR_ARG;
+    int rc = make_tables(*p, b->tab);
+    if (rc) return rc;
+    if (lim) b->lim = *lim;
+    rc = ensure_stream(b->own);
+    if (rc) return rc;
+    b->stream = b->own;
+    b->max_frames = max_frames;
+    rc = b->eng.init(b->tab, b->lim, w, h, 2 * max_frames, max_frames);
+    if (rc) return rc;
+    *out = b.release();
+    return GFORB_OK;
+}
+void gforb_batch_destroy(gforb_batch* b) { delete b; }
+
+int gforb_batch_set_stream(gforb_batch* b, void* s) {
+    if (!b) return GFORB_ERR_ARG;
+    b->stream = s ? (cudaStream_t)s : b->own;
+    return GFORB_OK;
+}
+int gforb_batch_capacity(const gforb_batch* b, int* max_frames, int* K) {
+    if (!b) return GFORB_ERR_ARG;
+    if (max_frames) *max_frames = b->max_frames;
+    if (K) *K = b->eng.g.K;
+    return GFORB_OK;
+}
+int gforb_batch_device_input(gforb_batch* b, uint8_t** dev_ptr, size_t* image_stride, size_t* pitch) {
+    if (!b) return GFORB_ERR_ARG;
+    if (dev_ptr) *dev_ptr = b->eng.b.in;
+    if (image_stride) *image_stride = (size_t)b->eng.g.W * b->eng.g.H;
+    if (pitch) *pitch = (size_t)b->eng.g.W;
+    return GFORB_OK;
+}
+int gforb_batch_upload(gforb_batch* b, const uint8_t* left, const uint8_t* right, int n) {
+    if (!b || !left || !right || n < 1 || n > b->max_frames) { set_error("gforb_batch_upload: bad arguments"); return GFORB_ERR_ARG; }
+    int rc = b->eng.upload_images(left, (size_t)b->eng.g.W, 0, 2, n, b->stream);
+    if (rc) return rc;
+    return b->eng.upload_images(right, (size_t)b->eng.g.W, 1, 2, n, b->stream);
+}
+
+int gforb_batch_run(gforb_batch* b, int n, const gforb_stereo_params* prm) {
+    if (!b || n < 1 || n > b->max_frames) { set_error("gforb_batch_run: bad frame count"); return GFORB_ERR_ARG; }
+    Engine& E = b->eng;
+    int rc = E.run_extract(2 * n, b->stream, b->timing ? b->ev : nullptr);
+    if (rc) return rc;
+    if (b->timing && !prm) cudaEventRecord(b->ev[6], b->stream);
+    if (prm) {
+        const size_t K = (size_t)E.g.K;
+        StereoView v{};
+        v.kL = E.b.kps; v.kR = E.b.kps + K; v.dL = E.b.desc; v.dR = E.b.desc + K * 32;
+        v.nL = E.b.nkp; v.nR = E.b.nkp + 1; v.k_stride = 2 * K; v.n_stride = 2;
+        fill_view_levels(v, E, E, 2, 1);
+        v.min_d = nullptr; v.max_d = nullptr;
+        v.uright = E.b.uright; v.depth = E.b.depth; v.best_dist = E.b.st_best_dist; v.best_idx = E.b.st_best_idx;
+        v.sad = E.b.st_sad; v.nmatch = E.b.st_nmatch; v.out_stride = K;
+        launch_stereo(v, norm_params(*prm), n, (int)K, b->stream);
+        if (b->timing) cudaEventRecord(b->ev[6], b->stream);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return cuda_fail(e, "stereo launch");
+    }
+    return GFORB_OK;
+}
+
+int gforb_batch_stage_timing(gforb_batch* b, int enable) {
+    if (!b) return GFORB_ERR_ARG;
+    if (enable) {
+        for (auto& e : b->ev)
+            if (!e) {
+                cudaError_t err = cudaEventCreate(&e);
+                if (err != cudaSuccess) return cuda_fail(err, "cudaEventCreate");
+            }
+    }
+    b->timing = enable != 0;
+    return GFORB_OK;
+}
+
+int gforb_batch_stage_times(gforb_batch* b, float* ms6) {
+    if (!b || !ms6 || !b->timing) { set_error("gforb_batch_stage_times: timing not enabled"); return GFORB_ERR_STATE; }
+    cudaError_t e = cudaEventSynchronize(b->ev[6]);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaEventSynchronize");
+    for (int i = 0; i < 6; ++i) {
+        e = cudaEventElapsedTime(&ms6[i], b->ev[i], b->ev[i + 1]);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaEventElapsedTime");
+    }
+    return GFORB_OK;
+}
+
+int gforb_batch_launches_per_run(const gforb_batch* b, int with_stereo) {
+    if (!b) return GFORB_ERR_ARG;
+    return b->eng.g.nlevels /* pyramid */ + 4 /* fast, quadtree, blur, describe */ + (with_stereo ? 1 : 0);
+}
+
+int gforb_batch_download(gforb_batch* b, int n, int32_t* counts, gforb_keypoint* kps, uint8_t* desc,
+                         float* u_right, float* depth) {
+    if (!b || n < 1 || n > b->max_frames) return GFORB_ERR_ARG;
+    Engine& E = b->eng;
+    const size_t K = (size_t)E.g.K, NI = 2 * (size_t)n;
+    cudaError_t e = cudaSuccess;
+    if (counts) e = cudaMemcpyAsync(counts, E.b.nkp, NI * 4, cudaMemcpyDeviceToHost, b->stream);
+    if (kps && e == cudaSuccess) e = cudaMemcpyAsync(kps, E.b.kps, NI * K * sizeof(gforb_keypoint), cudaMemcpyDeviceToHost, b->stream);
+    if (desc && e == cudaSuccess) e = cudaMemcpyAsync(desc, E.b.desc, NI * K * 32, cudaMemcpyDeviceToHost, b->stream);
+    if (u_right && e == cudaSuccess) e = cudaMemcpyAsync(u_right, E.b.uright, (size_t)n * K * 4, cudaMemcpyDeviceToHost, b->stream);
+    if (depth && e == cudaSuccess) e = cudaMemcpyAsync(depth, E.b.depth, (size_t)n * K * 4, cudaMemcpyDeviceToHost, b->stream);
+    return e == cudaSuccess ? GFORB_OK : cuda_fail(e, "cudaMemcpyAsync(batch download)");
+}
+
+int gforb_batch_sync(gforb_batch* b) {
+    if (!b) return GFORB_ERR_ARG;
+    return b->eng.check_errors(b->stream);
+}
+
+int gforb_stereo_frames_batch(gforb_batch* b, const uint8_t* left, const uint8_t* right, int n,
+                              const gforb_stereo_params* prm, int32_t* counts, gforb_keypoint* kps,
+                              uint8_t* desc, float* u_right, float* depth) {
+    int rc = gforb_batch_upload(b, left, right, n);
+    if (rc) return rc;
+    rc = gforb_batch_run(b, n, prm);
+    if (rc) return rc;
+    rc = gforb_batch_download(b, n, counts, kps, desc, u_right, depth);
+    if (rc) return rc;
+    return gforb_batch_sync(b);
+}
+
+}  // extern "C"

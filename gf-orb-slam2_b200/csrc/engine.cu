@@ -1,0 +1,295 @@
+// Host engine: constructor tables, level geometry, arenas, stage sequencing.
+#include "engine.hpp"
+
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+namespace gforb {
+
+namespace {
+thread_local std::string g_err = "";
+inline int cv_round(float v) { return (int)lrintf(v); }     // round-half-even, like cvRound
+inline int cv_round(double v) { return (int)lrint(v); }
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+}  // namespace
+
+void set_error(const std::string& msg) { g_err = msg; }
+const char* last_error() { return g_err.c_str(); }
+int cuda_fail(cudaError_t e, const char* what) {
+    set_error(std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")");
+    return GFORB_ERR_CUDA;
+}
+
+// reference src/ORBextractor.cc:409-469.  scaleFactor is a double member initialised from the float argument.
+int make_tables(const gforb_params& p, Tables& t) {
+    if (p.nlevels < 1 || p.nlevels > kMaxLevels || p.nfeatures < 0 || !(p.scale_factor > 1.0f) ||
+        p.nfeatures > 60000) {
+        set_error("gforb: bad extractor parameters (need 1<=nlevels<=12, scale_factor>1, 0<=nfeatures<=60000)");
+        return GFORB_ERR_ARG;
+    }
+    t.prm = p;
+    const int nl = p.nlevels;
+    const double sf = (double)p.scale_factor;
+    t.scale.assign(nl, 1.f); t.sigma2.assign(nl, 1.f);
+    for (int i = 1; i < nl; ++i) {
+        t.scale[i] = (float)(t.scale[i - 1] * sf);
+        t.sigma2[i] = t.scale[i] * t.scale[i];
+    }
+    t.inv_scale.resize(nl); t.inv_sigma2.resize(nl);
+    for (int i = 0; i < nl; ++i) { t.inv_scale[i] = 1.0f / t.scale[i]; t.inv_sigma2[i] = 1.0f / t.sigma2[i]; }
+
+    t.quota.assign(nl, 0);
+    const float factor = (float)(1.0f / sf);
+    float want = p.nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)nl));
+    int sum = 0;
+    for (int l = 0; l < nl - 1; ++l) {
+        t.quota[l] = cv_round(want);
+        sum += t.quota[l];
+        want *= factor;
+    }
+    t.quota[nl - 1] = std::max(p.nfeatures - sum, 0);
+
+    // rows of the radius-15 disc (:453-468)
+    std::memset(t.umax, 0, sizeof(t.umax));
+    const int vmax = (int)std::floor(kHalfPatch * std::sqrt(2.f) / 2 + 1);
+    const int vmin = (int)std::ceil(kHalfPatch * std::sqrt(2.f) / 2);
+    for (int v = 0; v <= vmax; ++v) t.umax[v] = cv_round(std::sqrt((double)(kHalfPatch * kHalfPatch) - v * v));
+    for (int v = kHalfPatch, v0 = 0; v >= vmin; --v) {
+        while (t.umax[v0] == t.umax[v0 + 1]) ++v0;
+        t.umax[v] = v0;
+        ++v0;
+    }
+    return GFORB_OK;
+}
+
+namespace {
+// cv::resize INTER_LINEAR per-axis table: source offset and the two 11-bit weights, packed for the kernel as
+// {ofs, (w1 << 16) | w0}.  Same arithmetic as OpenCV's resize(): fx = (float)((d+0.5)*scale-0.5) with
+// scale = 1/((double)dst/src); weights = saturate_cast<short>(f*2048) (round-half-even).
+void axis_table(int slen, int dlen, std::vector<int32_t>& out) {
+    const double scale = 1. / ((double)dlen / slen);
+    for (int d = 0; d < dlen; ++d) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)std::floor(f);
+        f -= (float)s;
+        if (s < 0) { f = 0.f; s = 0; }
+        if (s >= slen - 1) { f = 0.f; s = slen - 1; }
+        const int w0 = std::min(std::max(cv_round((1.f - f) * 2048.f), -32768), 32767);
+        const int w1 = std::min(std::max(cv_round(f * 2048.f), -32768), 32767);
+        out.push_back(s);
+        out.push_back((int32_t)(((uint32_t)w1 << 16) | ((uint32_t)w0 & 0xFFFFu)));
+    }
+}
+}  // namespace
+
+int make_geometry(const Tables& t, const gforb_limits& lim, int W, int H, int nimg, Geom& g,
+                  std::vector<int32_t>& tabs, size_t& pyr_bytes, size_t& blur_bytes) {
+    std::memset(&g, 0, sizeof(g));
+    tabs.clear();
+    const int nl = t.prm.nlevels;
+    g.nlevels = nl; g.W = W; g.H = H; g.nimg = nimg;
+    g.ini_th = t.prm.ini_th_fast; g.min_th = t.prm.min_th_fast;
+    if (W > 4096 + 32 || H > 4096 + 32 || nimg < 1 || nimg > 65535) {
+        set_error("gforb: image larger than 4128 px or bad batch size");
+        return GFORB_ERR_ARG;
+    }
+    size_t poff = 0, boff = 0;
+    int cell_base = 0, kbase = 0, btile = 0, cell_cap = 1, max_kcap = 0;
+    for (int l = 0; l < nl; ++l) {
+        LevelGeom& L = g.lv[l];
+        L.w = cv_round((float)W * t.inv_scale[l]);      // :1180-1181
+        L.h = cv_round((float)H * t.inv_scale[l]);
+        if (L.w < 40 || L.h < 40) {
+            char msg[160];
+            snprintf(msg, sizeof msg, "gforb: %dx%d image too small for %d pyramid levels (level %d is %dx%d, need >= 40)",
+                     W, H, nl, l, L.w, L.h);
+            set_error(msg);
+            return GFORB_ERR_ARG;
+        }
+        L.pitch = (int)align_up((size_t)kXPad + L.w + kEdge, 64);
+        L.rows = L.h + 2 * kEdge;
+        L.img_stride = (size_t)L.pitch * L.rows;
+        L.off = poff;
+        poff += L.img_stride * nimg;
+        L.bpitch = (int)align_up((size_t)L.w, 64);
+        L.bimg_stride = (size_t)L.bpitch * L.h;
+        L.boff = boff;
+        boff += L.bimg_stride * nimg;
+
+        // cell grid, float arithmetic as written (:771-783)
+        L.maxBX = L.w - kEdge + 3; L.maxBY = L.h - kEdge + 3;
+        const float width = (float)(L.maxBX - kMinBorder), height = (float)(L.maxBY - kMinBorder);
+        L.nCols = (int)(width / 30.f); L.nRows = (int)(height / 30.f);
+        if (L.nCols < 1 || L.nRows < 1) { L.nCols = L.nRows = 0; L.wCell = L.hCell = 1; }
+        else { L.wCell = (int)std::ceil(width / L.nCols); L.hCell = (int)std::ceil(height / L.nRows); }
+        L.cell_base = cell_base; L.ncells = L.nCols * L.nRows;
+        cell_base += L.ncells;
+        cell_cap = std::max(cell_cap, ((L.wCell + 1) / 2) * ((L.hCell + 1) / 2));
+
+        // quadtree (:543-546)
+        L.quota = t.quota[l];
+        L.nIni = (int)std::round((float)(L.maxBX - kMinBorder) / (float)(L.maxBY - kMinBorder));
+        L.hX = L.nIni > 0 ? (float)(L.maxBX - kMinBorder) / L.nIni : 1.f;
+        L.kcap = std::max(L.quota + 3, 4 * std::max(L.nIni, 1)) + 1;
+        L.kbase = kbase;
+        kbase += L.kcap;
+        max_kcap = std::max(max_kcap, L.kcap);
+
+        L.scale = t.scale[l]; L.inv_scale = t.inv_scale[l];
+        L.patch_size = (float)(int)(31 * t.scale[l]);    // :839
+
+        L.btile_base = btile; L.btiles_x = (L.w + 63) / 64;
+        btile += L.btiles_x * ((L.h + 15) / 16);
+
+        if (l > 0) {
+            const LevelGeom& P = g.lv[l - 1];
+            const double sx = 1. / ((double)L.w / P.w), sy = 1. / ((double)L.h / P.h);
+            L.area2x = (std::abs(sx - cv_round(sx)) < DBL_EPSILON && std::abs(sy - cv_round(sy)) < DBL_EPSILON &&
+                        cv_round(sx) == 2 && cv_round(sy) == 2) ? 1 : 0;
+            L.tab_x = (int)tabs.size(); axis_table(P.w, L.w, tabs);
+            L.tab_y = (int)tabs.size(); axis_table(P.h, L.h, tabs);
+        }
+    }
+    g.cells_total = cell_base;
+    g.cell_cap = cell_cap;
+    g.kstage = kbase;
+    g.K = (int)align_up((size_t)kbase, 8);
+    g.btiles_total = btile;
+    g.max_cand = lim.max_candidates_per_level > 0 ? lim.max_candidates_per_level : 12288;
+    g.max_cand = std::min(std::max(g.max_cand, 256), 65535);
+    g.max_nodes = std::max(256, max_kcap + 4);
+    if (g.K > 65535) { set_error("gforb: too many keypoints per image"); return GFORB_ERR_ARG; }
+    pyr_bytes = poff; blur_bytes = boff;
+    return GFORB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+Engine::~Engine() { release(); }
+
+void Engine::release() {
+    auto fr = [](auto*& p) { if (p) cudaFree(p); p = nullptr; };
+    fr(b.in); fr(b.pyr); fr(b.blur); fr(b.tabs); fr(b.cell_cnt); fr(b.cell_pts); fr(b.lvl_cnt); fr(b.lvl_pts);
+    fr(b.kps); fr(b.desc); fr(b.nkp); fr(b.uright); fr(b.depth); fr(b.st_best_dist); fr(b.st_best_idx);
+    fr(b.st_sad); fr(b.st_nmatch); fr(b.err);
+    if (h_small) cudaFreeHost(h_small);
+    h_small = nullptr;
+    ready = false; pyramid_valid = false;
+}
+
+#define GFORB_CUDA(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { release(); return cuda_fail(e_, #call); } } while (0)
+
+int Engine::init(const Tables& t, const gforb_limits& lim, int W, int H, int nimg, int nframes_stereo) {
+    release();
+    std::vector<int32_t> tabs;
+    size_t pyr_bytes = 0, blur_bytes = 0;
+    int rc = make_geometry(t, lim, W, H, nimg, g, tabs, pyr_bytes, blur_bytes);
+    if (rc != GFORB_OK) return rc;
+    nframes_cap = nframes_stereo;
+    const size_t K = (size_t)g.K, NI = (size_t)nimg, NF = (size_t)std::max(nframes_stereo, 1);
+
+    GFORB_CUDA(cudaMalloc(&b.in, NI * W * H));
+    GFORB_CUDA(cudaMalloc(&b.pyr, pyr_bytes));
+    GFORB_CUDA(cudaMalloc(&b.blur, blur_bytes));
+    GFORB_CUDA(cudaMalloc(&b.tabs, std::max<size_t>(tabs.size(), 2) * 4));
+    GFORB_CUDA(cudaMalloc(&b.cell_cnt, NI * g.cells_total * 4));
+    GFORB_CUDA(cudaMalloc(&b.cell_pts, NI * g.cells_total * (size_t)g.cell_cap * 4));
+    GFORB_CUDA(cudaMalloc(&b.lvl_cnt, NI * g.nlevels * 4));
+    GFORB_CUDA(cudaMalloc(&b.lvl_pts, NI * g.kstage * 4));
+    GFORB_CUDA(cudaMalloc(&b.kps, NI * K * sizeof(gforb_keypoint)));
+    GFORB_CUDA(cudaMalloc(&b.desc, NI * K * 32));
+    GFORB_CUDA(cudaMalloc(&b.nkp, NI * 4));
+    GFORB_CUDA(cudaMalloc(&b.uright, NF * K * 4));
+    GFORB_CUDA(cudaMalloc(&b.depth, NF * K * 4));
+    GFORB_CUDA(cudaMalloc(&b.st_best_dist, NF * K * 4));
+    GFORB_CUDA(cudaMalloc(&b.st_best_idx, NF * K * 4));
+    GFORB_CUDA(cudaMalloc(&b.st_sad, NF * K * 4));
+    GFORB_CUDA(cudaMalloc(&b.st_nmatch, NF * 4));
+    GFORB_CUDA(cudaMalloc(&b.err, 16));
+    GFORB_CUDA(cudaMemset(b.err, 0, 16));
+    GFORB_CUDA(cudaMemset(b.nkp, 0, NI * 4));
+    GFORB_CUDA(cudaMemset(b.lvl_cnt, 0, NI * g.nlevels * 4));
+    if (!tabs.empty()) GFORB_CUDA(cudaMemcpy(b.tabs, tabs.data(), tabs.size() * 4, cudaMemcpyHostToDevice));
+    h_small_ints = NI * (size_t)(g.nlevels + 1) + NF + 16;
+    GFORB_CUDA(cudaHostAlloc(&h_small, h_small_ints * 4, cudaHostAllocDefault));
+
+    const size_t osm = octree_smem_bytes(g);
+    if (osm > 227 * 1024) {
+        release();
+        set_error("gforb: quadtree working set exceeds 227 KB of shared memory; lower max_candidates_per_level or nfeatures");
+        return GFORB_ERR_ARG;
+    }
+    GFORB_CUDA((cudaError_t)octree_configure(g));
+    ready = true;
+    return GFORB_OK;
+}
+
+int Engine::upload_images(const uint8_t* host, size_t pitch, int first_img, int step, int count, cudaStream_t s) {
+    const size_t isz = (size_t)g.W * g.H;
+    if (step == 1 && pitch == (size_t)g.W) {
+        cudaError_t e = cudaMemcpyAsync(b.in + isz * first_img, host, isz * count, cudaMemcpyHostToDevice, s);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpyAsync(images)");
+        return GFORB_OK;
+    }
+    // strided destination (left/right interleave): one 2-D copy whose "rows" are whole images when tight
+    if (pitch == (size_t)g.W) {
+        cudaError_t e = cudaMemcpy2DAsync(b.in + isz * first_img, isz * step, host, isz, isz, count,
+                                          cudaMemcpyHostToDevice, s);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy2DAsync(images)");
+        return GFORB_OK;
+    }
+    for (int i = 0; i < count; ++i) {
+        cudaError_t e = cudaMemcpy2DAsync(b.in + isz * (first_img + (size_t)i * step), g.W,
+                                          host + (size_t)i * pitch * g.H, pitch, g.W, g.H, cudaMemcpyHostToDevice, s);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy2DAsync(image)");
+    }
+    return GFORB_OK;
+}
+
+int Engine::run_pyramid(int nimg, cudaStream_t s) {
+    launch_pyramid(g, b, nimg, s);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "pyramid launch");
+    pyramid_valid = true;
+    return GFORB_OK;
+}
+
+int Engine::run_extract(int nimg, cudaStream_t s, cudaEvent_t* ev) {
+    if (ev) cudaEventRecord(ev[0], s);
+    launch_pyramid(g, b, nimg, s);
+    if (ev) cudaEventRecord(ev[1], s);
+    launch_fast(g, b, nimg, s);
+    if (ev) cudaEventRecord(ev[2], s);
+    launch_octree(g, b, nimg, s);
+    if (ev) cudaEventRecord(ev[3], s);
+    launch_blur(g, b, nimg, s);
+    if (ev) cudaEventRecord(ev[4], s);
+    launch_describe(g, b, nimg, s);
+    if (ev) cudaEventRecord(ev[5], s);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "extract launch");
+    pyramid_valid = true;
+    return GFORB_OK;
+}
+
+int Engine::check_errors(cudaStream_t s) {
+    cudaError_t e = cudaMemcpyAsync(h_small, b.err, 4, cudaMemcpyDeviceToHost, s);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpyAsync(err)");
+    e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaStreamSynchronize");
+    const int bits = h_small[0];
+    if (bits) {
+        cudaMemsetAsync(b.err, 0, 4, s);
+        char msg[200];
+        snprintf(msg, sizeof msg, "gforb: device working set overflow (flags 0x%x:%s%s%s%s)", bits,
+                 bits & kErrCandOverflow ? " candidates-per-level" : "", bits & kErrCellOverflow ? " cell" : "",
+                 bits & kErrNodeOverflow ? " quadtree-nodes" : "", bits & kErrKpOverflow ? " keypoints" : "");
+        set_error(msg);
+        return GFORB_ERR_OVERFLOW;
+    }
+    return GFORB_OK;
+}
+
+}  // namespace gforb

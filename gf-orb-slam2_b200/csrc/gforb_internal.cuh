@@ -1,0 +1,120 @@
+// gforb internal declarations shared by the host engine and the sm_100a kernels.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstddef>
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/gforb.h"
+
+namespace gforb {
+
+constexpr int kMaxLevels = 12;
+constexpr int kEdge = 19;        // EDGE_THRESHOLD, src/ORBextractor.cc:74
+constexpr int kXPad = 32;        // bytes left of the ROI in every padded row (19 of them are the frame): ROI is 32B aligned
+constexpr int kMinBorder = 16;   // EDGE_THRESHOLD - 3, src/ORBextractor.cc:775
+constexpr int kHalfPatch = 15;
+constexpr int kMaxCellDim = 66;  // wCell < 60 always (nCols = floor(width/30)), +6 overlap
+
+// One pyramid level of the batch arena.  All images of a level are contiguous: [level][image][row][byte].
+struct LevelGeom {
+    int w, h;                 // ROI size (mvImagePyramid[l].cols/rows)
+    int pitch, rows;          // padded row pitch in bytes, padded row count (h + 38)
+    size_t img_stride;        // bytes between consecutive images of this level
+    size_t off;               // byte offset of (level, image 0, padded row 0) inside the pyramid arena
+    int bpitch;               // blurred image pitch (ROI only, no frame)
+    size_t bimg_stride, boff; // same for the blurred arena
+    // FAST cell grid (src/ORBextractor.cc:767-808)
+    int nCols, nRows, wCell, hCell, maxBX, maxBY;
+    int cell_base, ncells;    // index of this level's first cell within an image's cell table
+    // quadtree (src/ORBextractor.cc:539-570)
+    int quota, nIni;
+    float hX;
+    int kcap, kbase;          // staging slots of this level within an image's staging table
+    float scale, inv_scale;   // mvScaleFactor / mvInvScaleFactor
+    float patch_size;         // (float)(int)(31 * scale)
+    // resize tables (level >= 1): offsets into the table arena (ints)
+    int tab_x, tab_y;         // start of {ofs, coef01} pairs for x (w entries) and y (h entries)
+    int area2x;               // cv::resize's exact-2x INTER_AREA shortcut applies
+    int btile_base, btiles_x; // blur kernel: first tile index of this level, tiles per row
+};
+
+struct Geom {
+    int nlevels;
+    int W, H;                 // input size
+    int nimg;                 // images in the arena
+    int cells_total;          // cells per image over all levels
+    int cell_cap;             // survivor slots per cell (theoretical NMS maximum)
+    int kstage;               // staging slots per image (sum of kcap)
+    int K;                    // keypoint slots per image in the output arrays
+    int ini_th, min_th;
+    int max_cand;             // limit: candidates per (image, level) the quadtree kernel holds in smem
+    int max_nodes;            // node table capacity of the quadtree kernel
+    int btiles_total;         // blur tiles per image over all levels
+    LevelGeom lv[kMaxLevels];
+};
+
+// packed FAST survivor / staged keypoint: x:12 | y:12 | response:8, coordinates relative to the 16-px border
+__host__ __device__ inline uint32_t pack_cand(int x, int y, int r) {
+    return (uint32_t)x | ((uint32_t)y << 12) | ((uint32_t)r << 24);
+}
+__host__ __device__ inline int cand_x(uint32_t c) { return (int)(c & 0xFFFu); }
+__host__ __device__ inline int cand_y(uint32_t c) { return (int)((c >> 12) & 0xFFFu); }
+__host__ __device__ inline int cand_r(uint32_t c) { return (int)(c >> 24); }
+
+// Device arenas of one engine
+struct Buffers {
+    uint8_t* in = nullptr;        // nimg x H x W
+    uint8_t* pyr = nullptr;       // padded pyramid arena
+    uint8_t* blur = nullptr;      // blurred arena
+    int32_t* tabs = nullptr;      // resize tables
+    uint32_t* cell_cnt = nullptr; // nimg x cells_total
+    uint32_t* cell_pts = nullptr; // nimg x cells_total x cell_cap
+    int32_t* lvl_cnt = nullptr;   // nimg x nlevels   kept keypoints per level
+    uint32_t* lvl_pts = nullptr;  // nimg x kstage    staged kept keypoints (packed, level coords)
+    gforb_keypoint* kps = nullptr;   // nimg x K
+    uint8_t* desc = nullptr;         // nimg x K x 32
+    int32_t* nkp = nullptr;          // nimg
+    float* uright = nullptr;         // nframes x K
+    float* depth = nullptr;          // nframes x K
+    int32_t* st_best_dist = nullptr; // nframes x K
+    int32_t* st_best_idx = nullptr;  // nframes x K
+    int32_t* st_sad = nullptr;       // nframes x K
+    int32_t* st_nmatch = nullptr;    // nframes
+    int32_t* err = nullptr;          // [0] = sticky overflow flag bits
+};
+
+// stereo kernel view: where the two key sets and the two pyramids of frame f live
+struct StereoView {
+    const gforb_keypoint* kL; const gforb_keypoint* kR;   // frame 0
+    const uint8_t* dL; const uint8_t* dR;
+    const int32_t* nL; const int32_t* nR;
+    size_t k_stride;          // keypoints between consecutive frames (same for L and R)
+    size_t n_stride;          // ints between consecutive frames in nL/nR
+    const uint8_t* pyrL[kMaxLevels]; const uint8_t* pyrR[kMaxLevels];  // ROI origin (0,0) of frame 0
+    size_t frame_stride[kMaxLevels];  // bytes between consecutive frames in a level
+    int pitch[kMaxLevels], w[kMaxLevels];
+    float scale[kMaxLevels], inv_scale[kMaxLevels];
+    int nRows;                // rows of level 0
+    const float* min_d; const float* max_d;  // optional per-key windows (frame 0), may be null
+    float* uright; float* depth; int32_t* best_dist; int32_t* best_idx; int32_t* sad; int32_t* nmatch;
+    size_t out_stride;        // floats between frames in the outputs
+};
+
+enum ErrBits { kErrCandOverflow = 1, kErrCellOverflow = 2, kErrNodeOverflow = 4, kErrKpOverflow = 8 };
+
+// ---- kernel launchers (each enqueues on `s`; defined in the per-stage .cu files) ----
+void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);        // 1 + (nlevels-1) launches
+void launch_fast(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);           // 1 launch
+void launch_octree(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);         // 1 launch
+void launch_blur(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);           // 1 launch
+void launch_describe(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);       // 1 launch
+void launch_stereo(const StereoView& v, const gforb_stereo_params& p, int nframes, int K, cudaStream_t s);  // 1 launch
+size_t octree_smem_bytes(const Geom& g);
+int octree_configure(const Geom& g);   // opt in to large dynamic smem; returns cudaError_t as int
+
+void upload_constants();   // pattern + umax to __constant__ (once per process/device)
+
+}  // namespace gforb

@@ -1,0 +1,143 @@
+// Orientation + descriptor + final keypoint assembly, one warp per kept keypoint:
+//   IC_Angle / computeOrientation        (reference src/ORBextractor.cc:76-103, 472-479)  on the raw level
+//   computeOrbDescriptor                 (src/ORBextractor.cc:107-146)                    on the blurred level
+//   level-major concatenation, pt *= scale, size/octave fix-ups (src/ORBextractor.cc:839-849, 1141-1171)
+//
+// Moments are exact int32 sums (order-free), reduced with warp shuffles.  The angle is cv::fastAtan2's
+// polynomial evaluated with explicitly un-fused float ops (__fmul_rn/__fadd_rn) so it is bit-identical to
+// the CPU sequence.  cos/sin are taken in double and rounded to float (matches correctly-rounded cosf/sinf
+// except for astronomically rare double-rounding cases; DESIGN.md "descriptor parity").  Rotated pattern
+// coordinates use un-fused float ops and round-half-even (__float2int_rn == cvRound).
+// Lane i computes descriptor byte i (16 gathers, 8 compares); the 32 bytes leave as one coalesced store.
+// LSU/gather-bound (SURVEY.md 8d K4+K5): algorithmic bytes = 961 (31x31 raw) + 1369 (37x37 blurred) + 60 out per key.
+#include <cfloat>
+
+#include "gforb_internal.cuh"
+
+namespace gforb {
+
+namespace {
+__device__ const int8_t d_pattern[1024] = {
+#include "orb_pattern_31.inc"
+};
+// circular patch half-widths for HALF_PATCH_SIZE = 15 (src/ORBextractor.cc:453-468)
+__constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
+
+constexpr int kWarps = 8;
+
+// cv::fastAtan2 (OpenCV mathfuncs_core atan_f32), degrees
+__device__ __forceinline__ float fast_atan2_deg(float y, float x) {
+    constexpr float sc = (float)(180.0 / 3.14159265358979323846);
+    constexpr float p1 = 0.9997878412794807f * sc, p3 = -0.3258083974640975f * sc;
+    constexpr float p5 = 0.1555786518463281f * sc, p7 = -0.04432655554792128f * sc;
+    const float ax = fabsf(x), ay = fabsf(y);
+    float a, c, c2;
+    if (ax >= ay) {
+        c = __fdiv_rn(ay, __fadd_rn(ax, (float)DBL_EPSILON));
+        c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+    } else {
+        c = __fdiv_rn(ax, __fadd_rn(ay, (float)DBL_EPSILON));
+        c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+}  // namespace
+
+__global__ void __launch_bounds__(kWarps * 32)
+describe_kernel(const Geom g, const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
+                const int32_t* __restrict__ lvl_cnt, const uint32_t* __restrict__ lvl_pts,
+                gforb_keypoint* __restrict__ kps, uint8_t* __restrict__ desc, int32_t* __restrict__ nkp) {
+    __shared__ int8_t spx[16][32], spy[16][32];   // pattern transposed: [point within byte][byte] -> conflict-free
+    for (int t = threadIdx.x; t < 512; t += kWarps * 32) {
+        spx[t & 15][t >> 4] = d_pattern[2 * t];
+        spy[t & 15][t >> 4] = d_pattern[2 * t + 1];
+    }
+    __syncthreads();
+
+    const int img = blockIdx.y;
+    const int lane = threadIdx.x & 31;
+    const int slot = blockIdx.x * kWarps + (threadIdx.x >> 5);
+    if (slot >= g.kstage) return;
+
+    int l = 0;
+    while (l + 1 < g.nlevels && slot >= g.lv[l + 1].kbase) ++l;
+    const LevelGeom& L = g.lv[l];
+    const int k = slot - L.kbase;
+    const int32_t* cnt = lvl_cnt + (size_t)img * g.nlevels;
+    int before = 0, total = 0;
+    for (int i = 0; i < g.nlevels; ++i) {
+        const int c = cnt[i];
+        if (i < l) before += c;
+        total += c;
+    }
+    if (slot == 0 && lane == 0) nkp[img] = total;
+    if (k >= cnt[l]) return;
+
+    const uint32_t pk = lvl_pts[(size_t)img * g.kstage + slot];
+    const int x = cand_x(pk) + kMinBorder, y = cand_y(pk) + kMinBorder;   // pt += minBorder (:845-846)
+
+    // ---- intensity centroid over the 749-px disc ----
+    const uint8_t* ctr = pyr + L.off + (size_t)img * L.img_stride + (size_t)(kEdge + y) * L.pitch + kXPad + x;
+    const int u = lane - kHalfPatch;
+    int m10 = 0, m01 = 0;
+    if (lane < 31) {
+        const int au = abs(u);
+#pragma unroll 1
+        for (int v = -kHalfPatch; v <= kHalfPatch; ++v) {
+            if (au <= c_umax[abs(v)]) {
+                const int val = __ldg(ctr + (ptrdiff_t)v * L.pitch + u);
+                m10 += u * val;
+                m01 += v * val;
+            }
+        }
+    }
+    m10 = __reduce_add_sync(0xffffffffu, m10);
+    m01 = __reduce_add_sync(0xffffffffu, m01);
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+    // ---- rBRIEF on the blurred level ----
+    const float factorPI = (float)(3.14159265358979323846 / 180.0);
+    const float ang = __fmul_rn(angle, factorPI);
+    const float a = (float)cos((double)ang), b = (float)sin((double)ang);
+    const uint8_t* bc = blur + L.boff + (size_t)img * L.bimg_stride + (size_t)y * L.bpitch + x;
+    uint32_t val = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        int t[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const float px = (float)spx[2 * j + h][lane], py = (float)spy[2 * j + h][lane];
+            const int r = __float2int_rn(__fadd_rn(__fmul_rn(px, b), __fmul_rn(py, a)));
+            const int c = __float2int_rn(__fsub_rn(__fmul_rn(px, a), __fmul_rn(py, b)));
+            t[h] = __ldg(bc + (ptrdiff_t)r * L.bpitch + c);
+        }
+        val |= (uint32_t)(t[0] < t[1]) << j;
+    }
+    const size_t o = (size_t)img * g.K + before + k;
+    desc[o * 32 + lane] = (uint8_t)val;
+
+    if (lane == 0) {
+        gforb_keypoint kp;
+        kp.x = l ? __fmul_rn((float)x, L.scale) : (float)x;     // keypoint->pt *= scale (:1164-1170)
+        kp.y = l ? __fmul_rn((float)y, L.scale) : (float)y;
+        kp.size = L.patch_size;
+        kp.angle = angle;
+        kp.response = (float)cand_r(pk);
+        kp.octave = l;
+        kp.class_id = -1;
+        kps[o] = kp;
+    }
+}
+
+void launch_describe(const Geom& g, const Buffers& b, int nimg, cudaStream_t s) {
+    dim3 grd((g.kstage + kWarps - 1) / kWarps, nimg);
+    describe_kernel<<<grd, kWarps * 32, 0, s>>>(g, b.pyr, b.blur, b.lvl_cnt, b.lvl_pts, b.kps, b.desc, b.nkp);
+}
+
+void upload_constants() {}
+
+}  // namespace gforb

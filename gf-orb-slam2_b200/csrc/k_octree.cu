@@ -1,0 +1,337 @@
+// Quadtree keypoint culling: ORBextractor::DistributeOctTree + ExtractorNode::DivideNode
+// (reference src/ORBextractor.cc:481-763), reformulated for one CTA per (image, level).
+//
+// The reference walks a std::list, splitting nodes one at a time and copying KeyPoint vectors.  What its
+// result depends on is only (a) which node every point ends up in, (b) the order of the node list, and
+// (c) the order in which nodes are split once the "largest first" regime starts.  Reformulation:
+//   * points never move: each carries a node index; original candidate order is the index order, so
+//     "first strict max response" per node (:744-760) is an atomicMax on response + atomicMin on index;
+//   * the list is a table kept IN LIST ORDER.  A pass that creates children c_0..c_{C-1} (in creation
+//     order) and leaves U nodes unsplit yields the list [c_{C-1} .. c_0, unsplit nodes in old order],
+//     because children are push_front'ed and parents erased in place (:606-665, :688-727);
+//   * a pass = parallel speculative split of every splittable node (per-quadrant counts by smem atomics),
+//     then scans decide creation indices.  In the regular regime every node with >1 point splits, in list
+//     order.  In the "largest first" regime (:673-737) candidates are ordered by (count desc, newest
+//     first) and only the prefix up to the split that reaches N is committed.  The reference breaks count
+//     ties by heap address (:591,684); frozen as "newest first" = smaller table index.
+// Latency-bound bookkeeping: reported by time, not by a bandwidth roofline.
+#include "gforb_internal.cuh"
+
+namespace gforb {
+
+namespace {
+constexpr int kT = 256;
+
+struct Smem {
+    uint32_t* pts;      // [max_cand] packed x|y|resp
+    uint16_t* pnode;    // [max_cand]
+    short4* box[2];     // [NC] x0,x1,y0,y1 (ping-pong)
+    int* cnt[2];        // [NC]
+    int* cnt4;          // [4*NC] child counts, later best response
+    int* remap;         // [4*NC] child table index, later best index
+    int* keepmap;       // [NC]
+    int* a;             // [NC] scan scratch 1 (children per node / creation prefix)
+    int* b;             // [NC] scan scratch 2 (unsplit prefix / sorted increments)
+    uint32_t* key;      // [NC] sort keys
+    int* order;         // [NC] node index by sorted rank
+    uint8_t* split;     // [NC]
+    int* warp;          // [40] scan scratch
+};
+
+__device__ __forceinline__ Smem carve(uint8_t* base, int max_cand, int NC) {
+    Smem s;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { uint8_t* p = base + o; o += (bytes + 15) & ~(size_t)15; return p; };
+    s.pts = (uint32_t*)take(4 * (size_t)max_cand);
+    s.pnode = (uint16_t*)take(2 * (size_t)max_cand);
+    s.box[0] = (short4*)take(8 * (size_t)NC); s.box[1] = (short4*)take(8 * (size_t)NC);
+    s.cnt[0] = (int*)take(4 * (size_t)NC);    s.cnt[1] = (int*)take(4 * (size_t)NC);
+    s.cnt4 = (int*)take(16 * (size_t)NC);
+    s.remap = (int*)take(16 * (size_t)NC);
+    s.keepmap = (int*)take(4 * (size_t)NC);
+    s.a = (int*)take(4 * (size_t)NC);
+    s.b = (int*)take(4 * (size_t)NC);
+    s.key = (uint32_t*)take(4 * (size_t)NC);
+    s.order = (int*)take(4 * (size_t)NC);
+    s.split = (uint8_t*)take((size_t)NC);
+    s.warp = (int*)take(4 * 40);
+    return s;
+}
+
+// in-place exclusive scan of v[0..n) by the whole block; returns the total.  scratch: >= 34 ints.
+__device__ int block_excl_scan(int* v, int n, int* scratch) {
+    const int per = (n + kT - 1) / kT;
+    const int lo = min((int)threadIdx.x * per, n), hi = min(lo + per, n);
+    int sum = 0;
+    for (int i = lo; i < hi; ++i) sum += v[i];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    __syncthreads();                       // protects scratch reuse across calls
+    if (lane == 31) scratch[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        int w = lane < kT / 32 ? scratch[lane] : 0;
+        int winc = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, winc, o);
+            if (lane >= o) winc += t;
+        }
+        if (lane < kT / 32) scratch[lane] = winc - w;
+        if (lane == kT / 32 - 1) scratch[33] = winc;
+    }
+    __syncthreads();
+    int run = scratch[wid] + inc - sum;
+    for (int i = lo; i < hi; ++i) { const int t = v[i]; v[i] = run; run += t; }
+    const int total = scratch[33];
+    __syncthreads();
+    return total;
+}
+
+__device__ __forceinline__ int quadrant(uint32_t p, short4 bx) {
+    const int sx = bx.x + ((bx.y - bx.x + 1) >> 1);   // UL.x + ceil((UR.x-UL.x)/2)   (:483)
+    const int sy = bx.z + ((bx.w - bx.z + 1) >> 1);   // UL.y + ceil((BR.y-UL.y)/2)   (:484)
+    return (cand_x(p) >= sx ? 1 : 0) + (cand_y(p) >= sy ? 2 : 0);   // n1,n2,n3,n4 (:514-527)
+}
+__device__ __forceinline__ short4 child_box(short4 bx, int q) {
+    const short sx = (short)(bx.x + ((bx.y - bx.x + 1) >> 1));
+    const short sy = (short)(bx.z + ((bx.w - bx.z + 1) >> 1));
+    short4 c;
+    c.x = (q & 1) ? sx : bx.x;  c.y = (q & 1) ? bx.y : sx;
+    c.z = (q & 2) ? sy : bx.z;  c.w = (q & 2) ? bx.w : sy;
+    return c;
+}
+}  // namespace
+
+size_t octree_smem_bytes(const Geom& g) {
+    auto r = [](size_t b) { return (b + 15) & ~(size_t)15; };
+    const size_t mc = (size_t)g.max_cand, nc = (size_t)g.max_nodes;
+    return r(4 * mc) + r(2 * mc) + 2 * r(8 * nc) + 2 * r(4 * nc) + 2 * r(16 * nc) + 5 * r(4 * nc) + r(nc) + r(160);
+}
+
+__global__ void __launch_bounds__(kT)
+octree_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_t* __restrict__ cell_pts,
+              int32_t* __restrict__ lvl_cnt, uint32_t* __restrict__ lvl_pts, int32_t* __restrict__ err) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const int l = blockIdx.x, img = blockIdx.y;
+    const LevelGeom& L = g.lv[l];
+    const int NC = g.max_nodes;
+    Smem s = carve(smem_raw, g.max_cand, NC);
+    __shared__ int sh_n, sh_flag;
+
+    // ---- gather this level's FAST survivors in reference order (cell row-major, row-major inside) ----
+    const uint32_t* ccnt = cell_cnt + (size_t)img * g.cells_total + L.cell_base;
+    const uint32_t* cpts = cell_pts + ((size_t)img * g.cells_total + L.cell_base) * (size_t)g.cell_cap;
+    int n = 0;
+    for (int c0 = 0; c0 < L.ncells; c0 += kT) {
+        const int c = c0 + threadIdx.x;
+        const int mine = c < L.ncells ? (int)ccnt[c] : 0;
+        // block exclusive scan of `mine` through smem scratch s.a[0..kT)
+        s.a[threadIdx.x] = mine;
+        __syncthreads();
+        const int tot = block_excl_scan(s.a, kT, s.warp);
+        const int at = n + s.a[threadIdx.x];
+        if (n + tot <= g.max_cand)
+            for (int k = 0; k < mine; ++k) s.pts[at + k] = cpts[(size_t)c * g.cell_cap + k];
+        n += tot;
+        __syncthreads();
+    }
+    int32_t* out_cnt = lvl_cnt + (size_t)img * g.nlevels + l;
+    uint32_t* out_pts = lvl_pts + (size_t)img * g.kstage + L.kbase;
+    if (n > g.max_cand) {
+        if (threadIdx.x == 0) { atomicOr(err, kErrCandOverflow); *out_cnt = 0; }
+        return;
+    }
+    if (n == 0 || L.nIni <= 0) {
+        if (threadIdx.x == 0) *out_cnt = 0;
+        return;
+    }
+
+    // ---- initial nodes (:543-596) ----
+    const int N = L.quota;
+    const int H = L.maxBY - kMinBorder;           // maxY - minY
+    int cur = 0, S = 0;
+    for (int i = threadIdx.x; i < L.nIni; i += kT) {
+        short4 bx;
+        bx.x = (short)(int)__fmul_rn(L.hX, (float)i);
+        bx.y = (short)(int)__fmul_rn(L.hX, (float)(i + 1));
+        bx.z = 0; bx.w = (short)H;
+        s.box[1][i] = bx;          // staged in the other table, compacted below
+        s.cnt[1][i] = 0;
+    }
+    __syncthreads();
+    for (int p = threadIdx.x; p < n; p += kT) {
+        const int slot = (int)__fdiv_rn((float)cand_x(s.pts[p]), L.hX);   // vpIniNodes[kp.pt.x/hX] (:569)
+        s.pnode[p] = (uint16_t)slot;
+        atomicAdd(&s.cnt[1][slot], 1);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < L.nIni; i += kT) s.a[i] = s.cnt[1][i] > 0 ? 1 : 0;
+    __syncthreads();
+    S = block_excl_scan(s.a, L.nIni, s.warp);     // empty initial nodes are erased (:585-586)
+    for (int i = threadIdx.x; i < L.nIni; i += kT)
+        if (s.cnt[1][i] > 0) { s.box[0][s.a[i]] = s.box[1][i]; s.cnt[0][s.a[i]] = s.cnt[1][i]; }
+    __syncthreads();
+    for (int p = threadIdx.x; p < n; p += kT) s.pnode[p] = (uint16_t)s.a[s.pnode[p]];
+    __syncthreads();
+
+    // ---- split passes ----
+    bool largest_first = false;
+    for (;;) {
+        short4* box = s.box[cur]; int* cnt = s.cnt[cur];
+        short4* nbox = s.box[cur ^ 1]; int* ncnt = s.cnt[cur ^ 1];
+
+        // A. speculative child counts of every splittable node
+        for (int i = threadIdx.x; i < 4 * S; i += kT) s.cnt4[i] = 0;
+        __syncthreads();
+        for (int p = threadIdx.x; p < n; p += kT) {
+            const int nd = s.pnode[p];
+            if (cnt[nd] > 1) atomicAdd(&s.cnt4[4 * nd + quadrant(s.pts[p], box[nd])], 1);
+        }
+        __syncthreads();
+
+        // B. which nodes split, and in which creation order
+        int C, nsplit;
+        if (!largest_first) {
+            for (int i = threadIdx.x; i < S; i += kT) {
+                const bool sp = cnt[i] > 1;
+                s.split[i] = sp;
+                const int* c4 = s.cnt4 + 4 * i;
+                s.a[i] = sp ? (c4[0] > 0) + (c4[1] > 0) + (c4[2] > 0) + (c4[3] > 0) : 0;
+            }
+            __syncthreads();
+            C = block_excl_scan(s.a, S, s.warp);          // a[i] = children created before node i's
+        } else {
+            // candidates = nodes with >1 point (all were created by the previous pass), ordered by
+            // (count desc, newest = smaller index first)  (:684-686)
+            for (int i = threadIdx.x; i < S; i += kT) {
+                s.key[i] = cnt[i] > 1 ? ((uint32_t)cnt[i] << 16) | (uint32_t)(0xFFFF - i) : 0u;
+                s.split[i] = 0;
+            }
+            __syncthreads();
+            for (int i = threadIdx.x; i < S; i += kT) {
+                const uint32_t k = s.key[i];
+                if (k == 0) continue;
+                int rank = 0;
+                for (int j = 0; j < S; ++j) rank += s.key[j] > k;
+                s.order[rank] = i;
+            }
+            if (threadIdx.x == 0) sh_n = 0;
+            __syncthreads();
+            int m_local = 0;
+            for (int i = threadIdx.x; i < S; i += kT) m_local += s.key[i] != 0;
+            if (m_local) atomicAdd(&sh_n, m_local);
+            __syncthreads();
+            const int M = sh_n;
+            // size after committing sorted candidates 0..r = S + sum_{k<=r} (children_k - 1)
+            for (int r = threadIdx.x; r < M; r += kT) {
+                const int* c4 = s.cnt4 + 4 * s.order[r];
+                const int nch = (c4[0] > 0) + (c4[1] > 0) + (c4[2] > 0) + (c4[3] > 0);
+                s.a[r] = nch;
+                s.b[r] = nch - 1;
+            }
+            if (threadIdx.x == 0) sh_flag = M;            // first rank whose commit reaches N
+            __syncthreads();
+            block_excl_scan(s.b, M, s.warp);
+            for (int r = threadIdx.x; r < M; r += kT) {
+                const int after = S + s.b[r] + (s.a[r] - 1);
+                if (after >= N) atomicMin(&sh_flag, r);
+            }
+            __syncthreads();
+            nsplit = min(sh_flag + 1, M);                 // break right after the split that reaches N (:729-730)
+            for (int r = threadIdx.x; r < M; r += kT) if (r >= nsplit) s.a[r] = 0;
+            __syncthreads();
+            C = block_excl_scan(s.a, M, s.warp);          // a[r] = children created before rank r's
+            // scatter creation prefix back to node indexing (keepmap doubles as scratch here)
+            for (int r = threadIdx.x; r < nsplit; r += kT) { s.split[s.order[r]] = 1; s.keepmap[s.order[r]] = s.a[r]; }
+            __syncthreads();
+            for (int i = threadIdx.x; i < S; i += kT) s.a[i] = s.split[i] ? s.keepmap[i] : 0;
+            __syncthreads();
+        }
+        for (int i = threadIdx.x; i < S; i += kT) s.b[i] = s.split[i] ? 0 : 1;
+        __syncthreads();
+        const int U = block_excl_scan(s.b, S, s.warp);    // b[i] = unsplit nodes before i
+        const int S_new = C + U;
+        if (S_new > NC) {
+            if (threadIdx.x == 0) { atomicOr(err, kErrNodeOverflow); *out_cnt = 0; }
+            return;
+        }
+
+        // C. build the next table in list order: children reversed, then unsplit nodes in old order
+        if (threadIdx.x == 0) sh_n = 0;
+        __syncthreads();
+        int expand_local = 0;
+        for (int i = threadIdx.x; i < S; i += kT) {
+            if (s.split[i]) {
+                int c = s.a[i];
+                const short4 bx = box[i];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int k = s.cnt4[4 * i + q];
+                    if (k > 0) {
+                        const int idx = C - 1 - c;
+                        nbox[idx] = child_box(bx, q);
+                        ncnt[idx] = k;
+                        s.remap[4 * i + q] = idx;
+                        expand_local += k > 1;
+                        ++c;
+                    }
+                }
+            } else {
+                const int idx = C + s.b[i];
+                nbox[idx] = box[i];
+                ncnt[idx] = cnt[i];
+                s.keepmap[i] = idx;
+            }
+        }
+        if (expand_local) atomicAdd(&sh_n, expand_local);
+        __syncthreads();
+        // D. move the points
+        for (int p = threadIdx.x; p < n; p += kT) {
+            const int nd = s.pnode[p];
+            s.pnode[p] = (uint16_t)(s.split[nd] ? s.remap[4 * nd + quadrant(s.pts[p], box[nd])] : s.keepmap[nd]);
+        }
+        const int nToExpand = sh_n;
+        __syncthreads();
+
+        // E. termination (:667-672, :733-735)
+        const int prevSize = S;
+        S = S_new;
+        cur ^= 1;
+        if (S >= N || S == prevSize) break;
+        if (!largest_first && S + 3 * nToExpand > N) largest_first = true;
+    }
+
+    // ---- best response per node, first in candidate order wins ties (:744-760) ----
+    int* best_r = s.cnt4; int* best_i = s.remap;
+    for (int i = threadIdx.x; i < S; i += kT) { best_r[i] = -1; best_i[i] = 0x7fffffff; }
+    __syncthreads();
+    for (int p = threadIdx.x; p < n; p += kT) atomicMax(&best_r[s.pnode[p]], cand_r(s.pts[p]));
+    __syncthreads();
+    for (int p = threadIdx.x; p < n; p += kT)
+        if (cand_r(s.pts[p]) == best_r[s.pnode[p]]) atomicMin(&best_i[s.pnode[p]], p);
+    __syncthreads();
+    if (S > L.kcap) {
+        if (threadIdx.x == 0) { atomicOr(err, kErrKpOverflow); *out_cnt = 0; }
+        return;
+    }
+    for (int i = threadIdx.x; i < S; i += kT) out_pts[i] = s.pts[best_i[i]];
+    if (threadIdx.x == 0) *out_cnt = S;
+}
+
+int octree_configure(const Geom& g) {
+    return (int)cudaFuncSetAttribute(octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)octree_smem_bytes(g));
+}
+
+void launch_octree(const Geom& g, const Buffers& b, int nimg, cudaStream_t s) {
+    dim3 grd(g.nlevels, nimg);
+    octree_kernel<<<grd, kT, octree_smem_bytes(g), s>>>(g, b.cell_cnt, b.cell_pts, b.lvl_cnt, b.lvl_pts, b.err);
+}
+
+}  // namespace gforb

@@ -1,0 +1,206 @@
+/* gforb -- B200-native ORB stereo front-end: C ABI (drop-in boundary).
+ *
+ * This is the only boundary of the product library (gf-orb-slam2_b200/libgforb.so): plain pointers and
+ * sizes, no C++/torch/OpenCV types.  The reference (qiaozhijian/gf-orb-slam2) has no FFI layer; its boundary
+ * is the C++ class ABI of ORB_SLAM2::ORBextractor plus three Frame/ORBmatcher members.  Every entry point
+ * below names the reference interface it replaces (paths relative to the reference checkout).  The
+ * header-only C++ mirror with the reference's own class/method names is include/gforb/ORBextractor.hpp;
+ * the binding a reference maintainer adds is shown in INTEGRATION.md.
+ *
+ * All compute runs in hand-written sm_100a CUDA kernels.  There is no CPU fallback: without a CUDA device
+ * every compute entry returns GFORB_ERR_CUDA.
+ *
+ * Threading (mirrors src/Frame.cc:84-87): distinct handles may be used concurrently from different
+ * threads; one handle is not re-entrant.
+ */
+#ifndef GFORB_H
+#define GFORB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GFORB_VERSION 1
+
+#if defined(__GNUC__)
+#define GFORB_API __attribute__((visibility("default")))
+#else
+#define GFORB_API
+#endif
+
+/* ---- status codes (every entry returns one; 0 = ok). The reference has no error reporting at all
+ *      (empty image -> silent return, src/ORBextractor.cc:1115; asserts compiled out). ---- */
+enum {
+    GFORB_OK = 0,
+    GFORB_ERR_ARG = -1,        /* null pointer / bad size / bad parameter */
+    GFORB_ERR_CAPACITY = -2,   /* caller buffer or configured capacity too small (nothing truncated silently) */
+    GFORB_ERR_CUDA = -3,       /* CUDA runtime/driver error, or no device */
+    GFORB_ERR_STATE = -4,      /* call order (e.g. stereo before extraction) */
+    GFORB_ERR_OVERFLOW = -5    /* a device-side working set exceeded its configured bound (see gforb_limits) */
+};
+GFORB_API const char* gforb_last_error_string(void);      /* thread-local, never NULL */
+GFORB_API int gforb_version(void);
+
+/* Layout-identical to cv::KeyPoint (28 bytes) with the fields ORBextractor::operator() leaves in it
+ * (src/ORBextractor.cc:839-849,1164-1170): pt in level-0 pixels, size = (int)(31*scale), angle in degrees
+ * [0,360), response = FAST score, octave = level, class_id = -1. */
+typedef struct gforb_keypoint {
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+} gforb_keypoint;
+
+/* ORBextractor constructor arguments (include/ORBextractor.h:81-82; YAML keys ORBextractor.*,
+ * src/Tracking.cc:240-250). */
+typedef struct gforb_params {
+    int32_t nfeatures;
+    float scale_factor;
+    int32_t nlevels;
+    int32_t ini_th_fast;
+    int32_t min_th_fast;
+} gforb_params;
+
+/* Device-side bounds.  Zero = library default.  Exceeding one makes the call fail with GFORB_ERR_OVERFLOW. */
+typedef struct gforb_limits {
+    int32_t max_candidates_per_level; /* FAST survivors one (image, level) may hand to the quadtree; default 12288 */
+} gforb_limits;
+
+/* =====================================================================================================
+ * ORBextractor   (include/ORBextractor.h:76-168, src/ORBextractor.cc)
+ * ===================================================================================================== */
+typedef struct gforb_extractor gforb_extractor;
+
+/* ORBextractor::ORBextractor (src/ORBextractor.cc:409-469).  Device buffers are allocated lazily on the
+ * first image and re-allocated when the image size changes (the reference learns the size per call too).
+ * Uses the calling thread's current CUDA device. */
+GFORB_API int gforb_extractor_create(const gforb_params* params, const gforb_limits* limits_or_null, gforb_extractor** out);
+/* ~ORBextractor; Tracking deletes and re-creates extractors mid-run (src/Tracking.cc:298-320). */
+GFORB_API void gforb_extractor_destroy(gforb_extractor* ex);
+
+/* GetLevels/GetScaleFactor(s)/GetInverseScaleFactors/GetScaleSigmaSquares/GetInverseScaleSigmaSquares
+ * (include/ORBextractor.h:93-119) + mnFeaturesPerLevel + umax.  Any pointer may be NULL.  Arrays hold
+ * nlevels entries (umax: 16).  Host-side, no device needed. */
+GFORB_API int gforb_extractor_tables(const gforb_extractor* ex, float* scale, float* inv_scale, float* sigma2,
+                           float* inv_sigma2, int32_t* features_per_level, int32_t* umax16);
+GFORB_API int gforb_extractor_params(const gforb_extractor* ex, gforb_params* out);
+
+/* void operator()(InputArray image, InputArray mask, vector<KeyPoint>&, OutputArray descriptors)
+ * (include/ORBextractor.h:89-91, src/ORBextractor.cc:1112-1174).  image: 8-bit gray, `pitch` bytes per
+ * row, HOST memory; the mask is ignored by the reference and has no parameter here.  Writes *n keypoints
+ * (level-major order, within a level the quadtree list order) and n x 32 descriptor bytes.  An empty image
+ * (NULL / w<=0 / h<=0) is the reference's silent no-op: *n = 0, GFORB_OK.  If cap < n nothing is truncated:
+ * *n is set and GFORB_ERR_CAPACITY returned (gforb_extractor_max_keypoints gives a sufficient cap). */
+GFORB_API int gforb_extract(gforb_extractor* ex, const uint8_t* image, int w, int h, size_t pitch,
+                  gforb_keypoint* keypoints, uint8_t* descriptors, int cap, int* n);
+GFORB_API int gforb_extractor_max_keypoints(const gforb_extractor* ex, int w, int h);
+
+/* void ComputePyramid(cv::Mat) (include/ORBextractor.h:130-132, src/ORBextractor.cc:1176-1201), the
+ * pyramid-only entry used by the precomputed-detections Frame constructor (src/Frame.cc:182-183). */
+GFORB_API int gforb_compute_pyramid(gforb_extractor* ex, const uint8_t* image, int w, int h, size_t pitch);
+
+/* public member mvImagePyramid (include/ORBextractor.h:127): level geometry and DEVICE pointer to pixel
+ * (0,0) of the level; a 19-px BORDER_REFLECT_101 frame surrounds it in the same buffer.  Valid until the
+ * next extract/compute_pyramid on this handle. */
+GFORB_API int gforb_pyramid_level(const gforb_extractor* ex, int level, const uint8_t** dev_ptr, int* w, int* h, size_t* pitch);
+/* copy one level to HOST (with_border: (w+38) x (h+38) including the frame, else w x h) */
+GFORB_API int gforb_download_pyramid(gforb_extractor* ex, int level, uint8_t* host, size_t host_pitch, int with_border);
+
+/* stage-level introspection for parity tests: FAST survivors of `level` from the last extract, in the
+ * reference's emission order (src/ORBextractor.cc:791-829), as (x, y, response) int triples relative to the
+ * 16-px min border; and the per-level kept-keypoint counts. */
+GFORB_API int gforb_debug_candidates(gforb_extractor* ex, int level, int32_t* xyr, int cap, int* n);
+GFORB_API int gforb_debug_level_counts(gforb_extractor* ex, int32_t* counts);
+
+/* =====================================================================================================
+ * ORBmatcher::DescriptorDistance   (include/ORBmatcher.h:49, src/ORBmatcher.cc:1768-1784)
+ * ===================================================================================================== */
+GFORB_API int gforb_hamming256(const void* a32, const void* b32);   /* host inline-equivalent; 0..256 */
+#define GFORB_TH_HIGH 100   /* ORBmatcher::TH_HIGH, src/ORBmatcher.cc:37 */
+#define GFORB_TH_LOW 50     /* ORBmatcher::TH_LOW,  src/ORBmatcher.cc:38 */
+
+/* =====================================================================================================
+ * Frame::ComputeStereoMatches / ComputeStereoMatches_Undistorted
+ * (src/Frame.cc:889-1078, :1167-1316, include/Frame.h:230-263)
+ * ===================================================================================================== */
+enum { GFORB_STEREO_CLASSIC = 0, GFORB_STEREO_UNDISTORTED = 1 };
+
+typedef struct gforb_stereo_params {
+    float bf;          /* Frame::mbf */
+    float b;           /* Frame::mb -- the reference reads it before setting it (src/Frame.cc:920 vs :322); explicit here */
+    int32_t mode;      /* GFORB_STEREO_CLASSIC: Hamming + 11x11 SAD + parabola; _UNDISTORTED: Hamming only */
+    int32_t th_high;   /* 0 -> GFORB_TH_HIGH */
+    int32_t th_low;    /* 0 -> GFORB_TH_LOW  */
+    float min_x;       /* Frame::mnMinX, _UNDISTORTED only */
+} gforb_stereo_params;
+
+/* Operates on what the Frame holds after extraction: the two key/descriptor sets (HOST) and the two
+ * extractors' pyramids (device, from the last extract on exL / exR).  Writes mvuRight / mvDepth (-1 = none)
+ * for the nL left keys.  min_d/max_d: optional per-key disparity windows (mode _UNDISTORTED,
+ * src/Frame.cc:1220-1231), NULL = [0, bf/b).  *n_matched: keys that keep a depth (classic) or the
+ * reference's return value (_Undistorted). */
+GFORB_API int gforb_stereo_match(gforb_extractor* exL, gforb_extractor* exR, const gforb_stereo_params* prm,
+                       const gforb_keypoint* kL, int nL, const uint8_t* dL,
+                       const gforb_keypoint* kR, int nR, const uint8_t* dR,
+                       const float* min_d, const float* max_d,
+                       float* u_right, float* depth, int* n_matched);
+/* per-left-key intermediates of the last gforb_stereo_match on exL: best Hamming (th_high if none), its
+ * right index (-1), best SAD (-1 if not refined/accepted).  Any pointer may be NULL. */
+GFORB_API int gforb_debug_stereo(gforb_extractor* exL, int nL, int32_t* best_dist, int32_t* best_idx, int32_t* sad);
+
+/* =====================================================================================================
+ * Batched stereo front-end: Frame::Frame(imLeft, imRight, ...) for many frames at once
+ * (src/Frame.cc:248-326 = ExtractORB x2 threads + ComputeStereoMatches), never leaving the device between
+ * extraction and matching.  This is the throughput path; one batch = up to max_frames stereo frames of one
+ * fixed size, images [2f] = left, [2f+1] = right.
+ * ===================================================================================================== */
+typedef struct gforb_batch gforb_batch;
+
+GFORB_API int gforb_batch_create(const gforb_params* params, const gforb_limits* limits_or_null,
+                       int w, int h, int max_frames, gforb_batch** out);
+GFORB_API void gforb_batch_destroy(gforb_batch* b);
+/* run on a caller-owned cudaStream_t (e.g. torch's current stream); NULL restores the batch's own stream */
+GFORB_API int gforb_batch_set_stream(gforb_batch* b, void* cuda_stream);
+GFORB_API int gforb_batch_capacity(const gforb_batch* b, int* max_frames, int* max_keypoints_per_image);
+
+/* device-resident inputs: pointer to image 0, bytes between images and between rows (tightly packed w) */
+GFORB_API int gforb_batch_device_input(gforb_batch* b, uint8_t** dev_ptr, size_t* image_stride, size_t* pitch);
+/* async H2D of n_frames stereo pairs from (ideally pinned) host memory; left/right: n_frames x h x w, tight */
+GFORB_API int gforb_batch_upload(gforb_batch* b, const uint8_t* left, const uint8_t* right, int n_frames);
+
+/* enqueue the whole pipeline for frames [0, n_frames): pyramid, FAST, quadtree, orientation, blur,
+ * descriptors for both eyes, and (prm != NULL) stereo matching.  Asynchronous. */
+GFORB_API int gforb_batch_run(gforb_batch* b, int n_frames, const gforb_stereo_params* prm_or_null);
+
+/* async D2H of results into host buffers laid out with the batch's max_keypoints_per_image (K) stride:
+ * counts[2*n_frames]; keypoints[2*n_frames][K]; descriptors[2*n_frames][K][32]; u_right/depth[n_frames][K].
+ * Any pointer may be NULL.  Call gforb_batch_sync before reading. */
+GFORB_API int gforb_batch_download(gforb_batch* b, int n_frames, int32_t* counts, gforb_keypoint* keypoints,
+                         uint8_t* descriptors, float* u_right, float* depth);
+/* wait for the stream and report device-side overflow flags as GFORB_ERR_OVERFLOW */
+GFORB_API int gforb_batch_sync(gforb_batch* b);
+
+/* upload + run + download + sync in one call: the end-to-end entry (host buffers in, host buffers out) */
+GFORB_API int gforb_stereo_frames_batch(gforb_batch* b, const uint8_t* left, const uint8_t* right, int n_frames,
+                              const gforb_stereo_params* prm, int32_t* counts, gforb_keypoint* keypoints,
+                              uint8_t* descriptors, float* u_right, float* depth);
+
+/* number of kernel launches one gforb_batch_run enqueues (for bench.py's gpu_launches) and per-kernel
+ * algorithmic byte counts per stereo frame */
+GFORB_API int gforb_batch_launches_per_run(const gforb_batch* b, int with_stereo);
+
+/* Per-stage device timing of gforb_batch_run with CUDA events recorded on the batch's stream between the
+ * stages: ms6 = {pyramid, FAST, quadtree, blur, orientation+descriptor, stereo} of the LAST run (waits for it).
+ * Used by bench.py for the per-kernel roofline. */
+GFORB_API int gforb_batch_stage_timing(gforb_batch* b, int enable);
+GFORB_API int gforb_batch_stage_times(gforb_batch* b, float* ms6);
+
+/* pinned host memory helpers (cudaHostAlloc / cudaFreeHost) so callers can stage inputs for async copies */
+GFORB_API int gforb_host_alloc(void** ptr, size_t bytes);
+GFORB_API void gforb_host_free(void* ptr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GFORB_H */

@@ -1,0 +1,213 @@
+"""GPU parity: the CUDA path (through the C ABI) vs the CPU oracle and the committed golden vectors.
+
+Tolerances (BASELINE.json north_star): keypoint coordinates, octaves, responses, pyramid pixels, FAST
+candidates, Hamming distances: bit-exact.  Angles: <= 1e-3 rad (we assert bit-exact and report).  Descriptors:
+>= 99.9 % rows identical.  uRight / disparity: <= 1e-3 px.
+"""
+import importlib
+
+import numpy as np
+import pytest
+
+from conftest import B, BF
+from synth import synth_stereo
+
+pytestmark = pytest.mark.gpu
+NAMES = ("EuRoC_l", "EuRoC_r", "TUM_l", "TUM_r")
+
+
+@pytest.fixture(scope="module")
+def gf():
+    return importlib.import_module("gf-orb-slam2_b200")
+
+
+@pytest.fixture(scope="module")
+def O():
+    from oracle import pyoracle
+    return pyoracle
+
+
+def _assert_extract_equal(k, d, ok, od, what=""):
+    assert len(k) == len(ok), f"{what}: {len(k)} vs {len(ok)} keypoints"
+    for f in ("x", "y", "size", "response", "octave", "class_id"):
+        assert np.array_equal(k[f], ok[f]), f"{what}: field {f}"
+    dang = np.abs(k["angle"] - ok["angle"])
+    dang = np.minimum(dang, 360 - dang)
+    assert dang.max(initial=0) <= np.degrees(1e-3), f"{what}: angle diff {dang.max()}"
+    assert np.array_equal(k["angle"], ok["angle"]), f"{what}: angles not bit-exact"
+    same = (d == od).all(axis=1)
+    assert same.mean() >= 0.999 if len(k) else True, f"{what}: descriptors identical {same.mean()}"
+    return int((~same).sum())
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_pyramid_bit_exact(gf, O, fixtures, name):
+    im = fixtures[name]
+    ex = gf.ORBextractor(); ox = O.Extractor()
+    ex.ComputePyramid(im); ox.compute_pyramid(im)
+    for l in range(8):
+        assert np.array_equal(ex.pyramid_level(l), ox.level(l)), f"level {l} ROI"
+        assert np.array_equal(ex.pyramid_level(l, with_border=True), ox.level(l, padded=True)), f"level {l} frame"
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_fast_candidates_bit_exact(gf, O, fixtures, golden, name):
+    im = fixtures[name]
+    ex = gf.ORBextractor(); ox = O.Extractor()
+    ex(im); ox.extract(im)
+    for l in range(8):
+        assert np.array_equal(ex.debug_candidates(l), ox.last_candidates(l)), f"level {l}"
+    assert [len(ex.debug_candidates(l)) for l in range(8)] == list(golden[name]["cand_counts"])
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_extract_vs_oracle_and_golden(gf, O, fixtures, golden, name):
+    im = fixtures[name]
+    ex = gf.ORBextractor(); ox = O.Extractor()
+    k, d = ex(im)
+    ok, od, lc = ox.extract(im)
+    assert np.array_equal(ex.debug_level_counts(), lc)
+    _assert_extract_equal(k, d, ok, od, name)
+    g = golden[name]
+    bad = _assert_extract_equal(k, d, g["kps"], g["desc"], name + " golden")
+    assert bad == 0
+
+
+def test_extract_synthetic_and_sizes(gf, O):
+    for seed, (w, h) in enumerate([(752, 480), (640, 480), (512, 512), (480, 752), (333, 259)]):
+        l, r = synth_stereo(seed, w, h, nshapes=300)
+        ex = gf.ORBextractor(); ox = O.Extractor()
+        for im in (l, r):
+            k, d = ex(im)
+            ok, od, _ = ox.extract(im)
+            _assert_extract_equal(k, d, ok, od, f"synth {w}x{h}")
+
+
+def test_extract_other_parameters(gf, O, fixtures):
+    im = fixtures["EuRoC_l"]
+    for args in [(2000, 1.2, 8, 20, 7), (500, 1.5, 5, 15, 5), (300, 1.2, 8, 40, 12), (1000, 2.0, 3, 20, 7), (50, 1.2, 8, 20, 7)]:
+        ex = gf.ORBextractor(*args); ox = O.Extractor(*args)
+        k, d = ex(im)
+        ok, od, _ = ox.extract(im)
+        _assert_extract_equal(k, d, ok, od, str(args))
+
+
+def test_extract_edge_images(gf, O):
+    rng = np.random.default_rng(0)
+    flat = np.full((480, 752), 77, np.uint8)
+    noise = rng.integers(0, 256, (300, 400), dtype=np.uint8)      # dense corners: stresses cell capacity
+    lowc = rng.integers(120, 136, (300, 400), dtype=np.uint8)     # only the minTh retry fires
+    strided = np.ascontiguousarray(rng.integers(0, 256, (300, 512), dtype=np.uint8))[:, :400]   # pitch != width
+    for name, im in (("flat", flat), ("noise", noise), ("lowc", lowc), ("strided", strided)):
+        ex = gf.ORBextractor(); ox = O.Extractor()
+        k, d = ex(im)
+        ok, od, _ = ox.extract(np.ascontiguousarray(im))
+        _assert_extract_equal(k, d, ok, od, name)
+    assert len(gf.ORBextractor()(flat)[0]) == 0
+
+
+def test_extractor_reuse_and_resize(gf, O, fixtures):
+    ex = gf.ORBextractor(); ox = O.Extractor()
+    for name in ("EuRoC_l", "TUM_l", "EuRoC_r", "EuRoC_l"):
+        k, d = ex(fixtures[name])
+        ok, od, _ = ox.extract(fixtures[name])
+        _assert_extract_equal(k, d, ok, od, name)
+
+
+def test_candidate_overflow_is_loud(gf):
+    rng = np.random.default_rng(1)
+    noise = rng.integers(0, 256, (480, 752), dtype=np.uint8)
+    ex = gf.ORBextractor(max_candidates_per_level=300)
+    with pytest.raises(gf.GforbError) as e:
+        ex(noise)
+    assert e.value.code == gf.ERR_OVERFLOW
+    k, _ = gf.ORBextractor(max_candidates_per_level=30000)(noise)   # same image fits with a larger bound
+    assert len(k) > 900
+
+
+def _stereo_both(gf, O, l, r, mode=0, **kw):
+    exL, exR = gf.ORBextractor(), gf.ORBextractor()
+    oxL, oxR = O.Extractor(), O.Extractor()
+    kL, dL = exL(l); kR, dR = exR(r)
+    okL, odL, _ = oxL.extract(l); okR, odR, _ = oxR.extract(r)
+    # feed BOTH matchers the oracle's keys so the stage is compared on identical inputs
+    g = gf.ComputeStereoMatches(exL, exR, okL, odL, okR, odR, BF, B, mode=mode, debug=True, **kw)
+    o = O.stereo_match(oxL, oxR, okL, odL, okR, odR, BF, B, mode=mode, **kw)
+    return g, o
+
+
+@pytest.mark.parametrize("pair", ["EuRoC", "TUM"])
+def test_stereo_classic_fixtures(gf, O, fixtures, golden, pair):
+    g, o = _stereo_both(gf, O, fixtures[pair + "_l"], fixtures[pair + "_r"])
+    assert np.array_equal(g["best_dist"], o["best_dist"])          # Hamming distances bit-exact
+    assert np.array_equal(g["best_idx"], o["best_idx"])
+    assert np.array_equal(g["sad"], o["sad"])
+    assert np.array_equal(g["mvuRight"] >= 0, o["uRight"] >= 0)
+    assert np.abs(g["mvuRight"] - o["uRight"]).max() <= 1e-3
+    assert np.array_equal(g["mvuRight"], o["uRight"]) and np.array_equal(g["mvDepth"], o["depth"])
+    assert g["nmatched"] == o["ret"]
+    gold = golden["stereo_" + pair]
+    assert np.array_equal(g["mvuRight"], gold["uRight"]) and np.array_equal(g["mvDepth"], gold["depth"])
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_stereo_classic_synthetic_rectified(gf, O, seed):
+    l, r = synth_stereo(seed)
+    g, o = _stereo_both(gf, O, l, r)
+    assert (o["depth"] > 0).sum() > 100                            # the SAD/parabola path is really exercised
+    assert np.array_equal(g["best_dist"], o["best_dist"]) and np.array_equal(g["best_idx"], o["best_idx"])
+    assert np.array_equal(g["sad"], o["sad"])
+    assert np.abs(g["mvuRight"] - o["uRight"]).max() <= 1e-3
+    assert np.array_equal(g["mvuRight"], o["uRight"]) and np.array_equal(g["mvDepth"], o["depth"])
+    assert g["nmatched"] == o["ret"]
+
+
+def test_stereo_undistorted_mode(gf, O):
+    l, r = synth_stereo(3)
+    g, o = _stereo_both(gf, O, l, r, mode=1, min_x=0.0)
+    assert np.array_equal(g["best_dist"], o["best_dist"]) and np.array_equal(g["best_idx"], o["best_idx"])
+    assert np.array_equal(g["mvuRight"], o["uRight"]) and np.array_equal(g["mvDepth"], o["depth"])
+    assert g["nmatched"] == o["ret"]
+    n = len(g["mvuRight"])
+    rng = np.random.default_rng(0)
+    mind = rng.uniform(0, 20, n).astype(np.float32); maxd = (mind + rng.uniform(5, 60, n)).astype(np.float32)
+    g, o = _stereo_both(gf, O, l, r, mode=1, min_x=30.0, min_d=mind, max_d=maxd)
+    assert np.array_equal(g["mvuRight"], o["uRight"]) and np.array_equal(g["mvDepth"], o["depth"])
+    assert g["nmatched"] == o["ret"]
+
+
+def test_stereo_empty_sets(gf, fixtures):
+    exL, exR = gf.ORBextractor(), gf.ORBextractor()
+    kL, dL = exL(fixtures["EuRoC_l"]); exR(fixtures["EuRoC_r"])
+    none_k = np.zeros(0, gf.KP_DTYPE); none_d = np.zeros((0, 32), np.uint8)
+    g = gf.ComputeStereoMatches(exL, exR, kL, dL, none_k, none_d, BF, B)
+    assert (g["mvDepth"] == -1).all() and g["nmatched"] == 0
+    g = gf.ComputeStereoMatches(exL, exR, none_k, none_d, kL, dL, BF, B)
+    assert len(g["mvuRight"]) == 0
+
+
+def test_batch_matches_single_and_oracle(gf, O):
+    n = 4
+    pairs = [synth_stereo(10 + i) for i in range(n)]
+    left = np.stack([p[0] for p in pairs]); right = np.stack([p[1] for p in pairs])
+    sb = gf.StereoBatch(752, 480, n)
+    out = sb.alloc_outputs(n)
+    sb.process(left, right, out, BF, B)
+    K = sb.K
+    for f in range(n):
+        oxL, oxR = O.Extractor(), O.Extractor()
+        okL, odL, _ = oxL.extract(left[f]); okR, odR, _ = oxR.extract(right[f])
+        nL, nR = out["counts"][2 * f], out["counts"][2 * f + 1]
+        _assert_extract_equal(out["keypoints"][2 * f, :nL], out["descriptors"][2 * f, :nL], okL, odL, f"frame {f} L")
+        _assert_extract_equal(out["keypoints"][2 * f + 1, :nR], out["descriptors"][2 * f + 1, :nR], okR, odR, f"frame {f} R")
+        o = O.stereo_match(oxL, oxR, okL, odL, okR, odR, BF, B)
+        assert np.array_equal(out["u_right"][f, :nL], o["uRight"])
+        assert np.array_equal(out["depth"][f, :nL], o["depth"])
+    # size-independent properties at batch scale: idempotence of a re-run, independence from batch position
+    out2 = sb.alloc_outputs(n, pinned=False)
+    sb.process(left[::-1].copy(), right[::-1].copy(), out2, BF, B)
+    for f in range(n):
+        nL = out["counts"][2 * f]
+        assert out2["counts"][2 * (n - 1 - f)] == nL
+        assert np.array_equal(out2["descriptors"][2 * (n - 1 - f), :nL], out["descriptors"][2 * f, :nL])
+        assert np.array_equal(out2["depth"][n - 1 - f, :nL], out["depth"][f, :nL])
