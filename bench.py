@@ -1,0 +1,313 @@
+#!/usr/bin/env python3
+"""bench.py -- stereo frames/s of the ORB stereo front-end (extract L + extract R + ComputeStereoMatches)
+at 752x480, 1000 keypoints, 8 levels, scale 1.2, FAST 20/7 (BASELINE.json configs[1]).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--frames F] [--impl reference]
+
+A step = one pass of the whole hot path over one batch of F synthetic stereo frames.
+  value   : device-resident inputs, CUDA-event timed on the launching stream, max over ranks.
+  e2e     : the same through the C ABI with HOST (pinned) buffers: H2D of the images and D2H of
+            keypoints/descriptors/uRight/depth inside the timed region (gforb_stereo_frames_batch).
+  roofline: dominant kernel (by measured per-stage CUDA-event time) vs the measured HBM copy peak.
+  cpu_baseline: the CPU oracle (a port of the reference algorithm; the reference itself cannot be built here)
+            on the box's host cores, bounded sample, rank 0 at N=1 only.
+Multi-GPU: frames are independent -> each rank runs its own F frames (weak scaling), no collective on the
+data path; torch.distributed only provides the barrier and the max-over-ranks of the device time.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+
+W, H, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH = 752, 480, 1000, 1.2, 8, 20, 7
+BF = 47.90639384423901
+B = BF / 435.2046959714599
+METRIC = "stereo frames/s ORB extract+match @752x480x1000kp"
+UNIT = "stereo_frames/s"
+BASE_FRAMES = 16           # distinct generated stereo frames; the batch cycles them with shifts + fresh noise
+
+
+def make_frames(n, seed0=0):
+    """n distinct synthetic rectified stereo pairs (uint8 [n,H,W] x2)."""
+    from synth import synth_stereo
+    nb = min(n, BASE_FRAMES)
+    try:
+        from concurrent.futures import ProcessPoolExecutor
+        with ProcessPoolExecutor(max_workers=min(nb, os.cpu_count() or 1)) as ex:
+            base = list(ex.map(synth_stereo, range(seed0, seed0 + nb)))
+    except Exception:
+        base = [synth_stereo(seed0 + i) for i in range(nb)]
+    left = np.empty((n, H, W), np.uint8)
+    right = np.empty((n, H, W), np.uint8)
+    rng = np.random.default_rng(99 + seed0)
+    for i in range(n):
+        l, r = base[i % nb]
+        shift = 16 * (i // nb)
+        if shift:
+            l, r = np.roll(l, shift, axis=1), np.roll(r, shift, axis=1)
+            nz = rng.integers(-1, 2, (2, H, W), dtype=np.int16)
+            l = np.clip(l.astype(np.int16) + nz[0], 0, 255).astype(np.uint8)
+            r = np.clip(r.astype(np.int16) + nz[1], 0, 255).astype(np.uint8)
+        left[i], right[i] = l, r
+    return left, right
+
+
+def algorithmic_bytes(level_sizes, n_cand, n_kp):
+    """Per EYE image, SURVEY.md 8(d) (FAST survivors are 4 B packed here, not 8)."""
+    P = sum(w * h for w, h in level_sizes)
+    Ppad = sum((w + 38) * (h + 38) for w, h in level_sizes)
+    return {
+        "pyramid": W * H + Ppad,
+        "fast": P + 4 * n_cand,
+        "quadtree": 4 * n_cand + 4 * n_kp,
+        "blur": 2 * P,
+        "describe": (961 + 1369 + 60) * n_kp,
+    }
+
+
+class ClockSampler:
+    QUERY = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.QUERY}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except Exception:
+                continue
+            for n, v in zip(names, r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_baseline(left, right, threads, target_s=15.0):
+    """Oracle port on the host cores, 'all cores' shape: every worker runs whole stereo frames."""
+    from oracle import pyoracle as O
+    n = min(len(left), 8)
+    imgs = np.empty((2 * n, H, W), np.uint8)
+    imgs[0::2], imgs[1::2] = left[:n], right[:n]
+    secs, _ = O.bench_stereo(imgs, max(threads, 2), threads, 0, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, BF, B)
+    per_frame = secs / max(threads, 2) * threads            # thread-seconds per frame
+    nframes = int(max(threads * 2, min(4000, target_s * threads / max(per_frame, 1e-4))))
+    secs, chk = O.bench_stereo(imgs, nframes, threads, 0, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, BF, B)
+    return nframes / secs, nframes, secs, chk
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference algorithm's CPU path (oracle port; OpenCV C++ is not in the image so the
+    reference's own sources cannot be compiled) on all host threads, same config/metric."""
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    left, right = make_frames(8)
+    t0 = time.time()
+    vals, total_frames = [], 0
+    # bounded sample per step so the whole run ends within minutes
+    per_step_s = max(2.0, min(15.0, 150.0 / max(args.steps + args.warmup, 1)))
+    for i in range(args.warmup + args.steps):
+        fps, nframes, secs, _ = cpu_baseline(left, right, threads, target_s=per_step_s)
+        if i >= args.warmup:
+            vals.append((nframes, secs)); total_frames += nframes
+    tot_s = sum(s for _, s in vals)
+    value = total_frames / tot_s
+    sample = f"{total_frames} synthetic 752x480 stereo frames over {args.steps} steps, {threads} threads"
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1000.0 * tot_s / max(args.steps, 1), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "configs[1]: 752x480 stereo pair, 1000 kp, 8 levels, 1.2, FAST 20/7, classic stereo match",
+                       "frames_per_step": total_frames // max(args.steps, 1)},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "wall_s": time.time() - t0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--frames", type=int, default=256, help="stereo frames per step per GPU")
+    ap.add_argument("--impl", default="gforb", choices=["gforb", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "gforb" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; gforb has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    gf = importlib.import_module("gf-orb-slam2_b200")
+
+    F = args.frames
+    left, right = make_frames(F, seed0=1000 * rank)
+    sb = gf.StereoBatch(W, H, F, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH)
+    stream = torch.cuda.current_stream()
+    sb.set_stream(stream.cuda_stream)
+    out = sb.alloc_outputs(F)                       # pinned
+    pin_l = gf.PinnedArray((F, H, W), np.uint8); pin_r = gf.PinnedArray((F, H, W), np.uint8)
+    pin_l.array[:] = left; pin_r.array[:] = right
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------- device-resident arm ----------------
+    sb.upload(pin_l.array, pin_r.array)
+    torch.cuda.synchronize()
+    for _ in range(args.warmup):
+        sb.run(F, BF, B)
+    sb.sync()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        sb.run(F, BF, B)
+    e1.record(stream)
+    barrier()
+    sb.sync()
+    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    value = world * F * args.steps / (ms_total / 1e3)
+
+    # ---------------- per-stage times (same stream, CUDA events between the stages) ----------------
+    sb.stage_timing(True)
+    acc = {}
+    for _ in range(max(3, min(args.steps, 10))):
+        sb.run(F, BF, B)
+        for k, v in sb.stage_times().items():
+            acc.setdefault(k, []).append(v)
+    sb.stage_timing(False)
+    stage_ms = {k: float(np.mean(v)) for k, v in acc.items()}
+
+    # ---------------- end-to-end arm: host buffers in, host buffers out ----------------
+    for _ in range(2):
+        sb.process(pin_l.array, pin_r.array, out, BF, B)
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        sb.process(pin_l.array, pin_r.array, out, BF, B)
+    e1.record(stream)
+    barrier()
+    ms2 = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+    if world > 1:
+        dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
+    e2e_value = world * F * args.steps / (float(ms2.item()) / 1e3)
+    K = sb.K
+    h2d = 2 * F * W * H
+    d2h = 2 * F * 4 + 2 * F * K * 28 + 2 * F * K * 32 + 2 * F * K * 4
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    # ---------------- roofline of the dominant kernel ----------------
+    counts = out["counts"][: 2 * F]
+    n_kp = float(np.mean(counts))
+    ex = gf.ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH)
+    ex(left[0])
+    sizes = [ex.level_geometry(l)[1:3] for l in range(NLEVELS)]
+    n_cand = float(sum(len(ex.debug_candidates(l)) for l in range(NLEVELS)))
+    per_img = algorithmic_bytes(sizes, n_cand, n_kp)
+    per_launch = {k: v * 2 * F for k, v in per_img.items()}
+    per_launch["stereo"] = (60 * 2 * n_kp + 352 * n_kp + 8 * n_kp) * F
+    peaks_file = ROOT / "MEASURED_PEAKS.json"
+    if peaks_file.exists():
+        peak, peak_src = float(json.loads(peaks_file.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    dom = max(stage_ms, key=stage_ms.get)
+    stages = {}
+    for k, t in stage_ms.items():
+        gbs = per_launch[k] / (t * 1e-3) / 1e9 if t > 0 else 0.0
+        stages[k] = {"ms": round(t, 4), "share": round(t / sum(stage_ms.values()), 4),
+                     "alg_bytes": int(per_launch[k]), "gbs": round(gbs, 1), "frac_hbm": round(gbs / peak, 4)}
+    ach = stages[dom]["gbs"]
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": None, "peak_source": peak_src, "launches_in_stage": NLEVELS if dom == "pyramid" else 1,
+                "note": "FAST/quadtree/describe/stereo are integer/LSU/latency-bound (SURVEY.md 8d); the HBM fraction "
+                        "is reported for every stage under 'stages'"}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "configs[1]: 752x480 stereo pair, 1000 kp, 8 levels, 1.2, FAST 20/7, classic stereo match",
+                       "frames_per_step_per_gpu": F, "parallelism": f"frame-sharded x{world}, no collective",
+                       "l2": "inputs+intermediates per step (%d MB) exceed the 126 MB L2" % ((2 * F * (W * H + 3 * 1344493)) >> 20),
+                       "mean_keypoints_per_image": round(n_kp, 1), "fast_candidates_per_image": n_cand},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": sb.launches_per_run(True) * args.steps,
+            "clocks": clocks, "roofline": roofline, "stages": stages}
+    if not args.no_cpu_baseline and world == 1:
+        threads = os.cpu_count() or 1
+        fps, nframes, secs, _ = cpu_baseline(left, right, threads)
+        line["cpu_baseline"] = {"value": fps, "unit": UNIT, "cores": threads, "kind": "port",
+                                "sample": f"{nframes} synthetic 752x480 stereo frames (same generator), oracle port, "
+                                          f"{threads} threads each running whole frames, {secs:.1f} s"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

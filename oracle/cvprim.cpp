@@ -163,6 +163,23 @@ void fast9_16(const uint8_t* img, int w, int h, size_t pitch, int threshold, boo
                 const uint8_t* p = row + j;
                 const int v = p[0];
                 const int lo = v - threshold, hi = v + threshold;
+                // high-speed rejection, as OpenCV does it: a 9-arc contains one pixel of every opposite pair,
+                // so each pair must hold a darker (bit 0) / brighter (bit 1) pixel of the same polarity
+                auto cls = [&](int k) {
+                    const int x = p[(ptrdiff_t)kCircle[k][1] * (ptrdiff_t)pitch + kCircle[k][0]];
+                    return (x < lo ? 1 : 0) | (x > hi ? 2 : 0);
+                };
+                int d = cls(0) | cls(8);
+                if (d == 0) continue;
+                d &= cls(2) | cls(10);
+                d &= cls(4) | cls(12);
+                d &= cls(6) | cls(14);
+                if (d == 0) continue;
+                d &= cls(1) | cls(9);
+                d &= cls(3) | cls(11);
+                d &= cls(5) | cls(13);
+                d &= cls(7) | cls(15);
+                if (d == 0) continue;
                 // 9 contiguous strictly darker, or 9 contiguous strictly brighter
                 int run_d = 0, run_b = 0;
                 bool corner = false;

@@ -114,15 +114,18 @@ def test_extractor_reuse_and_resize(gf, O, fixtures):
         _assert_extract_equal(k, d, ok, od, name)
 
 
-def test_candidate_overflow_is_loud(gf):
+def test_candidate_overflow_is_loud(gf, O):
     rng = np.random.default_rng(1)
-    noise = rng.integers(0, 256, (480, 752), dtype=np.uint8)
+    noise = rng.integers(0, 256, (300, 400), dtype=np.uint8)      # ~9k FAST survivors on level 0
     ex = gf.ORBextractor(max_candidates_per_level=300)
     with pytest.raises(gf.GforbError) as e:
         ex(noise)
     assert e.value.code == gf.ERR_OVERFLOW
-    k, _ = gf.ORBextractor(max_candidates_per_level=30000)(noise)   # same image fits with a larger bound
-    assert len(k) > 900
+    k, d = ex(np.full((300, 400), 9, np.uint8))                    # the handle stays usable after the error
+    assert len(k) == 0
+    k, d = gf.ORBextractor(max_candidates_per_level=30000)(noise)  # same image fits with a larger bound
+    ok, od, _ = O.Extractor().extract(noise)
+    _assert_extract_equal(k, d, ok, od, "noise, large bound")
 
 
 def _stereo_both(gf, O, l, r, mode=0, **kw):
