@@ -193,7 +193,8 @@ def main():
     F = args.frames
     left, right = make_frames(F, seed0=1000 * rank)
     sb = gf.StereoBatch(W, H, F, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH)
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream()        # non-default: handle 0 (legacy default) would mean "library's own stream"
+    torch.cuda.set_stream(stream)
     sb.set_stream(stream.cuda_stream)
     out = sb.alloc_outputs(F)                       # pinned
     pin_l = gf.PinnedArray((F, H, W), np.uint8); pin_r = gf.PinnedArray((F, H, W), np.uint8)

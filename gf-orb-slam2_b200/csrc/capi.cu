@@ -19,6 +19,7 @@ struct gforb_extractor {
     gforb_keypoint* st_k = nullptr; uint8_t* st_d = nullptr; int32_t* st_n = nullptr; float* st_win = nullptr;
     int st_cap = 0;
     float *st_u = nullptr, *st_z = nullptr; int32_t *st_bd = nullptr, *st_bi = nullptr, *st_sad = nullptr, *st_nm = nullptr;
+    int32_t *st_cut = nullptr, *st_ticket = nullptr;
     ~gforb_extractor() {
         free_stereo();
         eng.release();
@@ -26,7 +27,7 @@ struct gforb_extractor {
     }
     void free_stereo() {
         auto fr = [](auto*& p) { if (p) cudaFree(p); p = nullptr; };
-        fr(st_k); fr(st_d); fr(st_n); fr(st_win); fr(st_u); fr(st_z); fr(st_bd); fr(st_bi); fr(st_sad); fr(st_nm);
+        fr(st_k); fr(st_d); fr(st_n); fr(st_win); fr(st_u); fr(st_z); fr(st_bd); fr(st_bi); fr(st_sad); fr(st_nm); fr(st_cut); fr(st_ticket);
         st_cap = 0;
     }
 };
@@ -283,6 +284,8 @@ int gforb_stereo_match(gforb_extractor* exL, gforb_extractor* exR, const gforb_s
         GA(exL->st_k, 2 * K * sizeof(gforb_keypoint)); GA(exL->st_d, 2 * K * 32); GA(exL->st_n, 16);
         GA(exL->st_win, 2 * K * 4); GA(exL->st_u, K * 4); GA(exL->st_z, K * 4); GA(exL->st_bd, K * 4);
         GA(exL->st_bi, K * 4); GA(exL->st_sad, K * 4); GA(exL->st_nm, 16);
+        GA(exL->st_cut, K * 4); GA(exL->st_ticket, 16);
+        cudaMemsetAsync(exL->st_ticket, 0, 16, s);
 #undef GA
         exL->st_cap = need;
     }
@@ -309,6 +312,7 @@ int gforb_stereo_match(gforb_extractor* exL, gforb_extractor* exR, const gforb_s
     v.min_d = min_d ? exL->st_win : nullptr; v.max_d = min_d ? exL->st_win + K : nullptr;
     v.uright = exL->st_u; v.depth = exL->st_z; v.best_dist = exL->st_bd; v.best_idx = exL->st_bi;
     v.sad = exL->st_sad; v.nmatch = exL->st_nm; v.out_stride = 0;
+    v.cut_dist = exL->st_cut; v.ticket = exL->st_ticket; v.proc_count = exL->st_ticket + 1;
     launch_stereo(v, norm_params(*prm), 1, (int)K, s);
     e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "stereo launch");
@@ -381,6 +385,7 @@ int gforb_batch_upload(gforb_batch* b, const uint8_t* left, const uint8_t* right
 int gforb_batch_run(gforb_batch* b, int n, const gforb_stereo_params* prm) {
     if (!b || n < 1 || n > b->max_frames) { set_error("gforb_batch_run: bad frame count"); return GFORB_ERR_ARG; }
     Engine& E = b->eng;
+    const int n_cap = b->max_frames;
     int rc = E.run_extract(2 * n, b->stream, b->timing ? b->ev : nullptr);
     if (rc) return rc;
     if (b->timing && !prm) cudaEventRecord(b->ev[6], b->stream);
@@ -393,6 +398,7 @@ int gforb_batch_run(gforb_batch* b, int n, const gforb_stereo_params* prm) {
         v.min_d = nullptr; v.max_d = nullptr;
         v.uright = E.b.uright; v.depth = E.b.depth; v.best_dist = E.b.st_best_dist; v.best_idx = E.b.st_best_idx;
         v.sad = E.b.st_sad; v.nmatch = E.b.st_nmatch; v.out_stride = K;
+        v.cut_dist = E.b.st_cut; v.ticket = E.b.st_ticket; v.proc_count = E.b.st_ticket + n_cap;
         launch_stereo(v, norm_params(*prm), n, (int)K, b->stream);
         if (b->timing) cudaEventRecord(b->ev[6], b->stream);
         cudaError_t e = cudaGetLastError();

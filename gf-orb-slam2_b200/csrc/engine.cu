@@ -1,5 +1,6 @@
 // Host engine: constructor tables, level geometry, arenas, stage sequencing.
 #include "engine.hpp"
+#include "tma.cuh"
 
 #include <algorithm>
 #include <cfloat>
@@ -128,6 +129,8 @@ int make_geometry(const Tables& t, const gforb_limits& lim, int W, int H, int ni
         L.cell_base = cell_base; L.ncells = L.nCols * L.nRows;
         cell_base += L.ncells;
         cell_cap = std::max(cell_cap, ((L.wCell + 1) / 2) * ((L.hCell + 1) / 2));
+        L.fast_bw = (int)align_up((size_t)L.wCell + 6 + 15, 16);   // TMA box: 16-byte multiple, start rounded down to 16
+        L.fast_bh = L.hCell + 6;
 
         // quadtree (:543-546)
         L.quota = t.quota[l];
@@ -141,8 +144,8 @@ int make_geometry(const Tables& t, const gforb_limits& lim, int W, int H, int ni
         L.scale = t.scale[l]; L.inv_scale = t.inv_scale[l];
         L.patch_size = (float)(int)(31 * t.scale[l]);    // :839
 
-        L.btile_base = btile; L.btiles_x = (L.w + 63) / 64;
-        btile += L.btiles_x * ((L.h + 15) / 16);
+        L.btile_base = btile; L.btiles_x = (L.w + 127) / 128;      // blur: 128 columns x (4 warps x 32 rows) per CTA
+        btile += L.btiles_x * ((L.h + 127) / 128);
 
         if (l > 0) {
             const LevelGeom& P = g.lv[l - 1];
@@ -167,13 +170,34 @@ int make_geometry(const Tables& t, const gforb_limits& lim, int W, int H, int ni
 }
 
 // ------------------------------------------------------------------------------------------------
+int encode_tile_map_u8(CUtensorMap* map, const void* base, uint64_t pitch, uint64_t rows, uint64_t nimg,
+                       uint32_t box_w, uint32_t box_h) {
+    typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                 const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                 CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || !p) return -1;
+        fn = (EncodeFn)p;
+    }
+    const cuuint64_t dims[3] = {pitch, rows, nimg};
+    const cuuint64_t strides[2] = {pitch, pitch * rows};
+    const cuuint32_t box[3] = {box_w, box_h, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    return (int)fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+}
+
 Engine::~Engine() { release(); }
 
 void Engine::release() {
     auto fr = [](auto*& p) { if (p) cudaFree(p); p = nullptr; };
     fr(b.in); fr(b.pyr); fr(b.blur); fr(b.tabs); fr(b.cell_cnt); fr(b.cell_pts); fr(b.lvl_cnt); fr(b.lvl_pts);
     fr(b.kps); fr(b.desc); fr(b.nkp); fr(b.uright); fr(b.depth); fr(b.st_best_dist); fr(b.st_best_idx);
-    fr(b.st_sad); fr(b.st_nmatch); fr(b.err);
+    fr(b.st_sad); fr(b.st_nmatch); fr(b.st_cut); fr(b.st_ticket); fr(b.err);
     if (h_small) cudaFreeHost(h_small);
     h_small = nullptr;
     ready = false; pyramid_valid = false;
@@ -207,6 +231,9 @@ int Engine::init(const Tables& t, const gforb_limits& lim, int W, int H, int nim
     GFORB_CUDA(cudaMalloc(&b.st_best_idx, NF * K * 4));
     GFORB_CUDA(cudaMalloc(&b.st_sad, NF * K * 4));
     GFORB_CUDA(cudaMalloc(&b.st_nmatch, NF * 4));
+    GFORB_CUDA(cudaMalloc(&b.st_cut, NF * K * 4));
+    GFORB_CUDA(cudaMalloc(&b.st_ticket, 2 * NF * 4));
+    GFORB_CUDA(cudaMemset(b.st_ticket, 0, 2 * NF * 4));
     GFORB_CUDA(cudaMalloc(&b.err, 16));
     GFORB_CUDA(cudaMemset(b.err, 0, 16));
     GFORB_CUDA(cudaMemset(b.nkp, 0, NI * 4));
@@ -222,6 +249,17 @@ int Engine::init(const Tables& t, const gforb_limits& lim, int W, int H, int nim
         return GFORB_ERR_ARG;
     }
     GFORB_CUDA((cudaError_t)octree_configure(g));
+    // TMA descriptors: one per level for the FAST cell tiles
+    for (int l = 0; l < g.nlevels; ++l) {
+        const LevelGeom& L = g.lv[l];
+        const int rcu = encode_tile_map_u8(&maps.fast[l], b.pyr + L.off, (uint64_t)L.pitch, (uint64_t)L.rows,
+                                           (uint64_t)nimg, (uint32_t)L.fast_bw, (uint32_t)L.fast_bh);
+        if (rcu != 0) {
+            release();
+            set_error("gforb: cuTensorMapEncodeTiled failed (" + std::to_string(rcu) + ")");
+            return GFORB_ERR_CUDA;
+        }
+    }
     ready = true;
     return GFORB_OK;
 }
@@ -260,7 +298,7 @@ int Engine::run_extract(int nimg, cudaStream_t s, cudaEvent_t* ev) {
     if (ev) cudaEventRecord(ev[0], s);
     launch_pyramid(g, b, nimg, s);
     if (ev) cudaEventRecord(ev[1], s);
-    launch_fast(g, b, nimg, s);
+    launch_fast(g, maps, b, nimg, s);
     if (ev) cudaEventRecord(ev[2], s);
     launch_octree(g, b, nimg, s);
     if (ev) cudaEventRecord(ev[3], s);

@@ -41,6 +41,7 @@ public:
     int check_errors(cudaStream_t s);
 
     Geom g{};
+    TileMaps maps{};
     Buffers b{};
     int nframes_cap = 0;
     bool ready = false;

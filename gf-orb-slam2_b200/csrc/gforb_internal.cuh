@@ -1,5 +1,6 @@
 // gforb internal declarations shared by the host engine and the sm_100a kernels.
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 #include <cstddef>
@@ -39,6 +40,7 @@ struct LevelGeom {
     int tab_x, tab_y;         // start of {ofs, coef01} pairs for x (w entries) and y (h entries)
     int area2x;               // cv::resize's exact-2x INTER_AREA shortcut applies
     int btile_base, btiles_x; // blur kernel: first tile index of this level, tiles per row
+    int fast_bw, fast_bh;     // FAST kernel: TMA box (bytes x rows) = shared tile pitch / height for this level
 };
 
 struct Geom {
@@ -54,6 +56,11 @@ struct Geom {
     int max_nodes;            // node table capacity of the quadtree kernel
     int btiles_total;         // blur tiles per image over all levels
     LevelGeom lv[kMaxLevels];
+};
+
+// TMA descriptors (kernel parameter, __grid_constant__): per-level padded pyramid as {pitch, rows, images}
+struct alignas(64) TileMaps {
+    CUtensorMap fast[kMaxLevels];
 };
 
 // packed FAST survivor / staged keypoint: x:12 | y:12 | response:8, coordinates relative to the 16-px border
@@ -83,6 +90,8 @@ struct Buffers {
     int32_t* st_best_idx = nullptr;  // nframes x K
     int32_t* st_sad = nullptr;       // nframes x K
     int32_t* st_nmatch = nullptr;    // nframes
+    int32_t* st_cut = nullptr;       // nframes x K
+    int32_t* st_ticket = nullptr;    // 2 x nframes (ticket, processed count), zero between launches
     int32_t* err = nullptr;          // [0] = sticky overflow flag bits
 };
 
@@ -100,6 +109,8 @@ struct StereoView {
     int nRows;                // rows of level 0
     const float* min_d; const float* max_d;  // optional per-key windows (frame 0), may be null
     float* uright; float* depth; int32_t* best_dist; int32_t* best_idx; int32_t* sad; int32_t* nmatch;
+    int32_t* cut_dist;        // per left key: distance entering the median cut (-1 = none), out_stride layout
+    int32_t* ticket; int32_t* proc_count;   // per frame, zero between launches
     size_t out_stride;        // floats between frames in the outputs
 };
 
@@ -107,7 +118,7 @@ enum ErrBits { kErrCandOverflow = 1, kErrCellOverflow = 2, kErrNodeOverflow = 4,
 
 // ---- kernel launchers (each enqueues on `s`; defined in the per-stage .cu files) ----
 void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);        // 1 + (nlevels-1) launches
-void launch_fast(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);           // 1 launch
+void launch_fast(const Geom& g, const TileMaps& m, const Buffers& b, int nimg, cudaStream_t s);   // 1 launch
 void launch_octree(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);         // 1 launch
 void launch_blur(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);           // 1 launch
 void launch_describe(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);       // 1 launch

@@ -13,54 +13,66 @@
 // keep@min.  Survivors leave in row-major order (the reference's emission order) via a per-row 64-bit
 // bitmap + popcount scan -- no atomics-ordered output.
 //
+// Data movement: the cell tile (<= 65x65 px) is fetched by ONE TMA request (cp.async.bulk.tensor.3d from the
+// padded pyramid {pitch, rows, images}) completing on an mbarrier.  Measured on B200: the innermost TMA
+// coordinate must be 16-byte aligned (an unaligned x raises "illegal instruction", tests/cpp/tma_probe.cu), so
+// the box starts at the 16-byte boundary below the cell and the cell sits `xoff` (0..15) bytes into the tile.
+// Compute: (1) every domain pixel takes the 4-pixel high-speed test at tlo, survivors are compacted into a
+// shared list with warp ballots; (2) list entries get the exact arc strength from a 3-input packed-s16x2
+// min/max network (VIMNMX3: both polarities in one register); (3) NMS walks the same list.
 // Integer/LSU-bound: algorithmic bytes = level pixels read once + 4 B per survivor.
 #include "gforb_internal.cuh"
+#include "tma.cuh"
 
 namespace gforb {
 
 namespace {
-constexpr int kTP = 72;                   // smem tile pitch
+constexpr int kMaxTP = 80;                // largest tile pitch: align16(59 + 6)
 constexpr int kTileRows = kMaxCellDim;    // 66
 constexpr int kThreads = 128;
+constexpr int kMaxDomain = 59 * 59;
 
-// Bresenham circle r=3 (src/FAST_NEON.cc:3-7)
-__device__ __forceinline__ int circle_off(int k) {
+// Bresenham circle r=3 (src/FAST_NEON.cc:3-7); tp = tile pitch
+__device__ __forceinline__ int circle_off(int k, int tp) {
     constexpr int dx[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
     constexpr int dy[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
-    return dy[k] * kTP + dx[k];
+    return dy[k] * tp + dx[k];
 }
 
-// max over arcs of min over 9 contiguous, for d (low half) and -d (high half) at once
-__device__ __forceinline__ int fast_arc_strength(const uint8_t* c, int v) {
+// max over the 16 arcs of min over 9 contiguous, for d = v-p (low half) and -d (high half) at once
+__device__ __forceinline__ int fast_arc_strength(const uint8_t* c, int v, int tp) {
     uint32_t p[16];
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
-        const int d = v - (int)c[circle_off(k)];
-        p[k] = ((uint32_t)d & 0xFFFFu) | ((uint32_t)(-d) << 16);
+        const int q = (int)c[circle_off(k, tp)];
+        p[k] = __byte_perm((uint32_t)(v - q), (uint32_t)(q - v), 0x5410);   // {lo16(v-q), lo16(q-v)}
     }
-    uint32_t m2[16], m4[16], m8[16];
+    uint32_t m3[16];
 #pragma unroll
-    for (int k = 0; k < 16; ++k) m2[k] = __vmins2(p[k], p[(k + 1) & 15]);
+    for (int k = 0; k < 16; ++k) m3[k] = __vimin3_s16x2(p[k], p[(k + 1) & 15], p[(k + 2) & 15]);
+    uint32_t m9[16];
 #pragma unroll
-    for (int k = 0; k < 16; ++k) m4[k] = __vmins2(m2[k], m2[(k + 2) & 15]);
-#pragma unroll
-    for (int k = 0; k < 16; ++k) m8[k] = __vmins2(m4[k], m4[(k + 4) & 15]);
-    uint32_t best = __vmins2(m8[0], p[8]);
-#pragma unroll
-    for (int k = 1; k < 16; ++k) best = __vmaxs2(best, __vmins2(m8[k], p[(k + 8) & 15]));
-    const int a = (short)(best & 0xFFFFu), b = (short)(best >> 16);
-    return max(a, b);
+    for (int k = 0; k < 16; ++k) m9[k] = __vimin3_s16x2(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]);
+    uint32_t b0 = __vimax3_s16x2(m9[0], m9[1], m9[2]), b1 = __vimax3_s16x2(m9[3], m9[4], m9[5]);
+    uint32_t b2 = __vimax3_s16x2(m9[6], m9[7], m9[8]), b3 = __vimax3_s16x2(m9[9], m9[10], m9[11]);
+    uint32_t b4 = __vimax3_s16x2(m9[12], m9[13], m9[14]);
+    b0 = __vimax3_s16x2(b0, b1, b2);
+    b3 = __vimax3_s16x2(b3, b4, m9[15]);
+    b0 = __vmaxs2(b0, b3);
+    return max((int)(short)(b0 & 0xFFFFu), (int)(short)(b0 >> 16));
 }
 }  // namespace
 
 __global__ void __launch_bounds__(kThreads)
-fast_cells_kernel(const Geom g, const uint8_t* __restrict__ pyr, uint32_t* __restrict__ cell_cnt,
+fast_cells_kernel(const Geom g, const __grid_constant__ TileMaps maps, uint32_t* __restrict__ cell_cnt,
                   uint32_t* __restrict__ cell_pts, int32_t* __restrict__ err) {
-    __shared__ __align__(16) uint8_t tile[kTileRows * kTP];
-    __shared__ __align__(16) uint8_t sc[kTileRows * kTP];
+    __shared__ __align__(128) uint8_t tile_raw[kTileRows * kMaxTP];
+    __shared__ __align__(16) uint8_t sc_raw[kTileRows * kMaxTP + 16];
+    __shared__ uint16_t list[kMaxDomain + 3];          // (y << 8) | x of pixels passing the high-speed test
     __shared__ unsigned long long keep_lo[64], keep_hi[64];
     __shared__ int row_base[64];
-    __shared__ int s_any_hi;
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ int s_any_hi, s_nlist;
 
     const int img = blockIdx.y;
     int cell = blockIdx.x;
@@ -73,59 +85,86 @@ fast_cells_kernel(const Geom g, const uint8_t* __restrict__ pyr, uint32_t* __res
 
     const int iniX = kMinBorder + cj * L.wCell, iniY = kMinBorder + ci * L.hCell;
     // src/ORBextractor.cc:796,805: asymmetric skip tests, as written
-    if (iniY >= L.maxBY - 3 || iniX >= L.maxBX - 6) {
-        if (threadIdx.x == 0) cell_cnt[out_cell] = 0;
-        return;
-    }
     const int cw = min(iniX + L.wCell + 6, L.maxBX) - iniX;
     const int ch = min(iniY + L.hCell + 6, L.maxBY) - iniY;
     const int dw = cw - 6, dh = ch - 6;   // FAST domain: rows/cols 3 .. dim-4 of the cell image
-    if (dw <= 0 || dh <= 0) {
+    if (iniY >= L.maxBY - 3 || iniX >= L.maxBX - 6 || dw <= 0 || dh <= 0) {
         if (threadIdx.x == 0) cell_cnt[out_cell] = 0;
         return;
     }
+    const int tp = L.fast_bw;
+    const int gx = kXPad + iniX, xoff = gx & 15;
+    const uint8_t* tile = tile_raw + xoff;    // cell pixel (0,0)
+    uint8_t* sc = sc_raw + xoff;
 
-    const uint8_t* src = pyr + L.off + (size_t)img * L.img_stride + (size_t)(kEdge + iniY) * L.pitch + kXPad + iniX;
-    for (int i = threadIdx.x; i < ch * cw; i += kThreads) {
-        const int y = i / cw, x = i - y * cw;
-        tile[y * kTP + x] = __ldg(src + (size_t)y * L.pitch + x);
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        s_any_hi = 0; s_nlist = 0;
     }
-    for (int i = threadIdx.x; i < kTileRows * kTP / 4; i += kThreads) reinterpret_cast<uint32_t*>(sc)[i] = 0;
-    if (threadIdx.x < 64) { keep_lo[threadIdx.x] = 0; keep_hi[threadIdx.x] = 0; }
-    if (threadIdx.x == 0) s_any_hi = 0;
     __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_expect_tx(&bar, (uint32_t)(tp * L.fast_bh));
+        tma_load_tile_3d(tile_raw, &maps.fast[l], gx - xoff, kEdge + iniY, img, &bar);
+    }
+    // while the tile is in flight: clear the score map rows we will touch and the row bitmaps
+    for (int i = threadIdx.x; i < (ch * tp + 16 + 3) / 4; i += kThreads) reinterpret_cast<uint32_t*>(sc_raw)[i] = 0;
+    if (threadIdx.x < 64) { keep_lo[threadIdx.x] = 0; keep_hi[threadIdx.x] = 0; }
 
     const int t_ini = min(max(g.ini_th, 0), 255), t_min = min(max(g.min_th, 0), 255);
     const int tlo = min(t_ini, t_min);
+    const int npx = dw * dh;
+    const int step_y = kThreads / dw, step_x = kThreads - step_y * dw;
+    int y = (int)threadIdx.x / dw, x = (int)threadIdx.x - y * dw;
+    const int lane = threadIdx.x & 31;
 
-    // pass 1: corner strength at the lower threshold
-    for (int i = threadIdx.x; i < dw * dh; i += kThreads) {
-        const int y = i / dw + 3, x = i - (y - 3) * dw + 3;
-        const uint8_t* c = tile + y * kTP + x;
-        const int v = c[0];
-        // high-speed reject: a 9-arc covers one of each opposite pair
-        const int d0 = v - c[circle_off(0)], d8 = v - c[circle_off(8)];
-        const int d4 = v - c[circle_off(4)], d12 = v - c[circle_off(12)];
-        const bool dark = (d0 > tlo || d8 > tlo) && (d4 > tlo || d12 > tlo);
-        const bool bright = (d0 < -tlo || d8 < -tlo) && (d4 < -tlo || d12 < -tlo);
-        if (!(dark || bright)) continue;
-        const int m = fast_arc_strength(c, v);
-        if (m > tlo) sc[y * kTP + x] = (uint8_t)(m - 1);
+    mbar_wait(&bar, 0);
+
+    // pass 1: high-speed test (a 9-arc covers one pixel of each opposite pair) + ballot compaction
+    for (int i0 = 0; i0 < npx; i0 += kThreads) {
+        bool pass = false;
+        if (i0 + (int)threadIdx.x < npx) {
+            const uint8_t* c = tile + (y + 3) * tp + x + 3;
+            const int v = c[0];
+            const int d0 = v - c[3 * tp], d8 = v - c[-3 * tp], d4 = v - c[3], d12 = v - c[-3];
+            const bool dark = (d0 > tlo || d8 > tlo) && (d4 > tlo || d12 > tlo);
+            const bool bright = (d0 < -tlo || d8 < -tlo) && (d4 < -tlo || d12 < -tlo);
+            pass = dark || bright;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, pass);
+        if (m) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(&s_nlist, __popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (pass) list[base + __popc(m & ((1u << lane) - 1))] = (uint16_t)(((y + 3) << 8) | (x + 3));
+        }
+        x += step_x; y += step_y;
+        if (x >= dw) { x -= dw; ++y; }
+    }
+    __syncthreads();
+    const int nlist = s_nlist;
+
+    // pass 2: exact corner strength of the listed pixels
+    for (int k = threadIdx.x; k < nlist; k += kThreads) {
+        const int e = list[k];
+        const int off = (e >> 8) * tp + (e & 0xFF);
+        const int m = fast_arc_strength(tile + off, tile[off], tp);
+        if (m > tlo) sc[off] = (uint8_t)(m - 1);
     }
     __syncthreads();
 
-    // pass 2: strict 3x3 NMS on the score map (zero outside the domain)
-    for (int i = threadIdx.x; i < dw * dh; i += kThreads) {
-        const int y = i / dw + 3, x = i - (y - 3) * dw + 3;
-        const uint8_t* q = sc + y * kTP + x;
+    // pass 3: strict 3x3 NMS on the score map (zero outside the domain), again only over the list
+    for (int k = threadIdx.x; k < nlist; k += kThreads) {
+        const int e = list[k];
+        const int py = e >> 8, px = e & 0xFF;
+        const uint8_t* q = sc + py * tp + px;
         const int s = q[0];
         if (s == 0) continue;
-        const bool keep = s > q[-1] && s > q[1] && s > q[-kTP - 1] && s > q[-kTP] && s > q[-kTP + 1] &&
-                          s > q[kTP - 1] && s > q[kTP] && s > q[kTP + 1];
+        const bool keep = s > q[-1] && s > q[1] && s > q[-tp - 1] && s > q[-tp] && s > q[-tp + 1] &&
+                          s > q[tp - 1] && s > q[tp] && s > q[tp + 1];
         if (!keep) continue;
-        const unsigned long long bit = 1ull << (x - 3);
-        atomicOr(&keep_lo[y - 3], bit);
-        if (s >= t_ini) { atomicOr(&keep_hi[y - 3], bit); s_any_hi = 1; }
+        const unsigned long long bit = 1ull << (px - 3);
+        atomicOr(&keep_lo[py - 3], bit);
+        if (s >= t_ini) { atomicOr(&keep_hi[py - 3], bit); s_any_hi = 1; }
     }
     __syncthreads();
 
@@ -139,7 +178,7 @@ fast_cells_kernel(const Geom g, const uint8_t* __restrict__ pyr, uint32_t* __res
                 unsigned long long f = 0;
                 for (unsigned long long r = m; r; r &= r - 1) {
                     const int bx = __ffsll((long long)r) - 1;
-                    if (sc[(threadIdx.x + 3) * kTP + bx + 3] >= t_min) f |= 1ull << bx;
+                    if (sc[(threadIdx.x + 3) * tp + bx + 3] >= t_min) f |= 1ull << bx;
                 }
                 m = f;
             }
@@ -148,28 +187,40 @@ fast_cells_kernel(const Geom g, const uint8_t* __restrict__ pyr, uint32_t* __res
         row_base[threadIdx.x] = __popcll(m);
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
-        int acc = 0;
-        for (int r = 0; r < dh; ++r) { const int c = row_base[r]; row_base[r] = acc; acc += c; }
-        if (acc > g.cell_cap) { atomicOr(err, kErrCellOverflow); acc = 0; }
-        cell_cnt[out_cell] = (uint32_t)acc;
-        s_any_hi = acc;
+    if (threadIdx.x < 32) {
+        // exclusive scan of the <= 59 row counts by one warp
+        const int c0 = row_base[lane], c1 = row_base[lane + 32];
+        int i0 = c0, i1 = c1;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t0 = __shfl_up_sync(0xffffffffu, i0, o), t1 = __shfl_up_sync(0xffffffffu, i1, o);
+            if (lane >= o) { i0 += t0; i1 += t1; }
+        }
+        const int tot0 = __shfl_sync(0xffffffffu, i0, 31), tot1 = __shfl_sync(0xffffffffu, i1, 31);
+        row_base[lane] = i0 - c0;
+        row_base[lane + 32] = tot0 + i1 - c1;
+        if (lane == 0) {
+            int total = tot0 + tot1;
+            if (total > g.cell_cap) { atomicOr(err, kErrCellOverflow); total = 0; }
+            cell_cnt[out_cell] = (uint32_t)total;
+            s_nlist = total;
+        }
     }
     __syncthreads();
-    if (s_any_hi == 0) return;
+    if (s_nlist == 0) return;
     if ((int)threadIdx.x < dh) {
         uint32_t* out = cell_pts + out_cell * (size_t)g.cell_cap + row_base[threadIdx.x];
-        const int y = threadIdx.x + 3;
+        const int yy = threadIdx.x + 3;
         for (unsigned long long r = keep_lo[threadIdx.x]; r; r &= r - 1) {
-            const int x = __ffsll((long long)r) - 1 + 3;
-            *out++ = pack_cand(cj * L.wCell + x, ci * L.hCell + y, sc[y * kTP + x]);
+            const int xx = __ffsll((long long)r) - 1 + 3;
+            *out++ = pack_cand(cj * L.wCell + xx, ci * L.hCell + yy, sc[yy * tp + xx]);
         }
     }
 }
 
-void launch_fast(const Geom& g, const Buffers& b, int nimg, cudaStream_t s) {
+void launch_fast(const Geom& g, const TileMaps& m, const Buffers& b, int nimg, cudaStream_t s) {
     dim3 grd(g.cells_total, nimg);
-    fast_cells_kernel<<<grd, kThreads, 0, s>>>(g, b.pyr, b.cell_cnt, b.cell_pts, b.err);
+    fast_cells_kernel<<<grd, kThreads, 0, s>>>(g, m, b.cell_cnt, b.cell_pts, b.err);
 }
 
 }  // namespace gforb

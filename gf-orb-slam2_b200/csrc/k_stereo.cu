@@ -2,7 +2,8 @@
 // Frame::ComputeStereoMatches_Undistorted + PrepareStereoCandidates (src/Frame.cc:1167-1316,
 // include/Frame.h:230-263), with ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1768-1784) as __popc.
 //
-// One CTA per stereo frame.  The reference builds a per-row table of right keys and scans it per left key;
+// kSlices CTAs per stereo frame (left keys are dealt round-robin to the slices; the last CTA of a frame to
+// finish -- ticket counter -- applies the median cut).  The reference builds a per-row table of right keys and scans it per left key;
 // since "best" is the lexicographic minimum of (Hamming distance, right index) over the gated candidates
 // (strict '<' while walking ascending iR), the table is replaced by a gate test of every right key
 // (row band, octave +-1, uR window) and a warp-wide packed-min reduction -- order-free and deterministic.
@@ -17,6 +18,7 @@ namespace gforb {
 
 namespace {
 constexpr int kT = 256;
+constexpr int kSlices = 8;
 struct RKey { short minr, maxr; int octave; float x; };
 
 __device__ __forceinline__ int hamming_u4(const uint4 a0, const uint4 a1, const uint8_t* b) {
@@ -32,9 +34,9 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     RKey* rk = reinterpret_cast<RKey*>(smem_raw);
     int* s_dist = reinterpret_cast<int*>(smem_raw + sizeof(RKey) * (size_t)K);
-    __shared__ int s_cnt, s_median, s_removed, s_processed;
+    __shared__ int s_cnt, s_median, s_removed, s_processed, s_last;
 
-    const int f = blockIdx.x;
+    const int f = blockIdx.x, slice = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const gforb_keypoint* kL = v.kL + (size_t)f * v.k_stride;
     const gforb_keypoint* kR = v.kR + (size_t)f * v.k_stride;
@@ -46,6 +48,7 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
     int32_t* o_bd = v.best_dist + (size_t)f * v.out_stride;
     int32_t* o_bi = v.best_idx + (size_t)f * v.out_stride;
     int32_t* o_sad = v.sad + (size_t)f * v.out_stride;
+    int32_t* o_cut = v.cut_dist + (size_t)f * v.out_stride;
 
     const bool classic = prm.mode == GFORB_STEREO_CLASSIC;
     const int th_high = prm.th_high, thOrbDist = (prm.th_high + prm.th_low) / 2;
@@ -62,12 +65,11 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
         q.minr = (short)(int)lo; q.maxr = (short)(int)hi; q.octave = k.octave; q.x = k.x;
         rk[i] = q;
     }
-    for (int i = threadIdx.x; i < nL; i += kT) s_dist[i] = -1;
     if (threadIdx.x == 0) { s_cnt = 0; s_removed = 0; s_processed = 0; }
     __syncthreads();
 
     const float minZ = prm.b;
-    for (int iL = warp; iL < nL; iL += kT / 32) {
+    for (int iL = slice + kSlices * warp; iL < nL; iL += kSlices * (kT / 32)) {
         const gforb_keypoint kp = kL[iL];
         float minD = 0.f, maxD = __fdiv_rn(prm.bf, minZ);
         const float vL = kp.y, uL = kp.x;
@@ -179,10 +181,25 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
         if (lane == 0) {
             uright[iL] = out_u; depth[iL] = out_z;
             o_bd[iL] = out_bd; o_bi[iL] = out_bi; o_sad[iL] = out_sad;
-            s_dist[iL] = out_dist;
-            if (out_dist >= 0) atomicAdd(&s_cnt, 1);
+            o_cut[iL] = out_dist;
             if (processed) atomicAdd(&s_processed, 1);
         }
+    }
+    __syncthreads();
+    // ---- frame-level hand-off: the last slice to arrive owns the median cut ----
+    if (threadIdx.x == 0) {
+        if (s_processed) atomicAdd(&v.proc_count[f], s_processed);
+        __threadfence();
+        const int ticket = atomicAdd(&v.ticket[f], 1);
+        s_last = ticket == kSlices - 1;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    for (int i = threadIdx.x; i < nL; i += kT) {
+        const int d = __ldcg(o_cut + i);
+        s_dist[i] = d;
+        if (d >= 0) atomicAdd(&s_cnt, 1);
     }
     __syncthreads();
 
@@ -214,7 +231,11 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
         }
         __syncthreads();
     }
-    if (threadIdx.x == 0) v.nmatch[f] = classic ? (n - s_removed) : (s_processed - s_removed);
+    if (threadIdx.x == 0) {
+        const int processed_all = atomicExch(&v.proc_count[f], 0);     // also re-arms the counters for the next launch
+        v.ticket[f] = 0;
+        v.nmatch[f] = classic ? (n - s_removed) : (processed_all - s_removed);
+    }
 }
 
 void launch_stereo(const StereoView& v, const gforb_stereo_params& p, int nframes, int K, cudaStream_t s) {
@@ -224,7 +245,7 @@ void launch_stereo(const StereoView& v, const gforb_stereo_params& p, int nframe
         cudaFuncSetAttribute(stereo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         configured = smem;
     }
-    stereo_kernel<<<nframes, kT, smem, s>>>(v, p, K);
+    stereo_kernel<<<dim3(nframes, kSlices), kT, smem, s>>>(v, p, K);
 }
 
 }  // namespace gforb
