@@ -189,6 +189,7 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     gf = importlib.import_module("gf-orb-slam2_b200")
+    from sharding import aggregate_throughput
 
     F = args.frames
     left, right = make_frames(F, seed0=1000 * rank)
@@ -224,10 +225,8 @@ def main():
     sb.sync()
     ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
     clocks = sampler.stop() if rank == 0 else None
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms_total = float(ms.item())
-    value = world * F * args.steps / (ms_total / 1e3)
+    value = aggregate_throughput(F, args.steps, ms, world, dist)          # all ranks' frames / slowest rank's time
+    ms_total = world * F * args.steps / value * 1e3
 
     # ---------------- per-stage times (same stream, CUDA events between the stages) ----------------
     sb.stage_timing(True)
@@ -249,9 +248,7 @@ def main():
     e1.record(stream)
     barrier()
     ms2 = torch.tensor([e0.elapsed_time(e1)], device="cuda")
-    if world > 1:
-        dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
-    e2e_value = world * F * args.steps / (float(ms2.item()) / 1e3)
+    e2e_value = aggregate_throughput(F, args.steps, ms2, world, dist)
     K = sb.K
     h2d = 2 * F * W * H
     d2h = 2 * F * 4 + 2 * F * K * 28 + 2 * F * K * 32 + 2 * F * K * 4

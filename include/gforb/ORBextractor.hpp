@@ -1,0 +1,154 @@
+// Header-only C++ mirror of the reference's interface for this path, over the C ABI in gforb.h.
+// Names, argument meaning and error behaviour follow the reference so its call sites compile unchanged:
+//   ORB_SLAM2::ORBextractor            include/ORBextractor.h:76-168   (ctor, operator(), ComputePyramid, Get*, mvImagePyramid)
+//   ORB_SLAM2::ORBmatcher::DescriptorDistance / TH_HIGH / TH_LOW        include/ORBmatcher.h:49,  src/ORBmatcher.cc:37-38
+//   Frame::ComputeStereoMatches / ComputeStereoMatches_Undistorted      src/Frame.cc:889-1078, 1167-1316
+// Define GFORB_WITH_OPENCV (and have OpenCV headers) to get the cv::InputArray / cv::KeyPoint / cv::Mat
+// overloads the reference's Frame.cc / Tracking.cc use; without it the same calls take plain buffers.
+// Like the reference, nothing here throws for an empty image (silent no-op); CUDA/argument failures throw
+// std::runtime_error carrying gforb_last_error_string() (the reference's CUDA variant exit()s instead).
+#pragma once
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../gforb.h"
+
+#ifdef GFORB_WITH_OPENCV
+#include <opencv2/core/core.hpp>
+#endif
+
+namespace gforb {
+
+inline void check(int rc, const char* what) {
+    if (rc != GFORB_OK) throw std::runtime_error(std::string(what) + ": " + gforb_last_error_string());
+}
+
+class ORBextractor {
+public:
+    enum { HARRIS_SCORE = 0, FAST_SCORE = 1 };
+
+    ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST)
+        : nfeatures(nfeatures), scaleFactor(scaleFactor), nlevels(nlevels), iniThFAST(iniThFAST), minThFAST(minThFAST) {
+        gforb_params p{nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST};
+        check(gforb_extractor_create(&p, nullptr, &h_), "ORBextractor");
+        mvScaleFactor.resize(nlevels); mvInvScaleFactor.resize(nlevels);
+        mvLevelSigma2.resize(nlevels); mvInvLevelSigma2.resize(nlevels); mnFeaturesPerLevel.resize(nlevels);
+        umax.resize(16);
+        check(gforb_extractor_tables(h_, mvScaleFactor.data(), mvInvScaleFactor.data(), mvLevelSigma2.data(),
+                                     mvInvLevelSigma2.data(), mnFeaturesPerLevel.data(), umax.data()), "tables");
+    }
+    ~ORBextractor() { gforb_extractor_destroy(h_); }
+    ORBextractor(const ORBextractor&) = delete;
+    ORBextractor& operator=(const ORBextractor&) = delete;
+
+    // operator()(image, mask, keypoints, descriptors) on plain buffers; mask ignored as in the reference
+    void operator()(const uint8_t* image, int w, int h, size_t pitch, std::vector<gforb_keypoint>& keypoints,
+                    std::vector<uint8_t>& descriptors) {
+        if (!image || w <= 0 || h <= 0) return;                       // src/ORBextractor.cc:1115-1116
+        const int cap = gforb_extractor_max_keypoints(h_, w, h);
+        if (cap < 0) check(cap, "operator()");
+        keypoints.resize(cap);
+        descriptors.resize((size_t)cap * 32);
+        int n = 0;
+        check(gforb_extract(h_, image, w, h, pitch, keypoints.data(), descriptors.data(), cap, &n), "operator()");
+        keypoints.resize(n);
+        descriptors.resize((size_t)n * 32);
+    }
+    void ComputePyramid(const uint8_t* image, int w, int h, size_t pitch) {
+        check(gforb_compute_pyramid(h_, image, w, h, pitch), "ComputePyramid");
+    }
+
+#ifdef GFORB_WITH_OPENCV
+    static_assert(sizeof(cv::KeyPoint) == sizeof(gforb_keypoint), "gforb_keypoint must mirror cv::KeyPoint");
+    // exact reference signature (include/ORBextractor.h:89-91)
+    void operator()(cv::InputArray _image, cv::InputArray /*mask*/, std::vector<cv::KeyPoint>& _keypoints,
+                    cv::OutputArray _descriptors) {
+        if (_image.empty()) return;
+        cv::Mat image = _image.getMat();
+        CV_Assert(image.type() == CV_8UC1);
+        const int cap = gforb_extractor_max_keypoints(h_, image.cols, image.rows);
+        if (cap < 0) check(cap, "operator()");
+        _keypoints.resize(cap);
+        cv::Mat desc(cap, 32, CV_8U);
+        int n = 0;
+        check(gforb_extract(h_, image.data, image.cols, image.rows, image.step,
+                            reinterpret_cast<gforb_keypoint*>(_keypoints.data()), desc.data, cap, &n), "operator()");
+        _keypoints.resize(n);
+        if (n == 0) _descriptors.release();                            // src/ORBextractor.cc:1133-1134
+        else desc.rowRange(0, n).copyTo(_descriptors);
+        pyramid_stale_ = true;
+    }
+    void ComputePyramid(cv::Mat image) {                               // include/ORBextractor.h:130-132
+        ComputePyramid(image.data, image.cols, image.rows, image.step);
+        pyramid_stale_ = true;
+    }
+    // mvImagePyramid (include/ORBextractor.h:127): host views, downloaded on demand (19-px frame included in
+    // the parent buffer, ROI view returned -- same shape as the reference's Mats)
+    const std::vector<cv::Mat>& ImagePyramid() {
+        if (pyramid_stale_) {
+            mvImagePyramid.resize(nlevels);
+            for (int l = 0; l < nlevels; ++l) {
+                int w, h; size_t pitch; const uint8_t* dev;
+                check(gforb_pyramid_level(h_, l, &dev, &w, &h, &pitch), "mvImagePyramid");
+                cv::Mat padded(h + 38, w + 38, CV_8U);
+                check(gforb_download_pyramid(h_, l, padded.data, padded.step, 1), "mvImagePyramid");
+                mvImagePyramid[l] = padded(cv::Rect(19, 19, w, h));
+            }
+            pyramid_stale_ = false;
+        }
+        return mvImagePyramid;
+    }
+    std::vector<cv::Mat> mvImagePyramid;
+#endif
+
+    int inline GetLevels() { return nlevels; }
+    float inline GetScaleFactor() { return scaleFactor; }
+    int inline GetInitThres() { return iniThFAST; }
+    int inline GetMinThres() { return minThFAST; }
+    std::vector<float> inline GetScaleFactors() { return mvScaleFactor; }
+    std::vector<float> inline GetInverseScaleFactors() { return mvInvScaleFactor; }
+    std::vector<float> inline GetScaleSigmaSquares() { return mvLevelSigma2; }
+    std::vector<float> inline GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
+
+    gforb_extractor* handle() { return h_; }
+
+protected:
+    int nfeatures;
+    double scaleFactor;
+    int nlevels, iniThFAST, minThFAST;
+    std::vector<int32_t> mnFeaturesPerLevel, umax;
+    std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
+    gforb_extractor* h_ = nullptr;
+    bool pyramid_stale_ = true;
+};
+
+class ORBmatcher {
+public:
+    static const int TH_LOW = GFORB_TH_LOW;
+    static const int TH_HIGH = GFORB_TH_HIGH;
+    static int DescriptorDistance(const uint8_t* a, const uint8_t* b) { return gforb_hamming256(a, b); }
+#ifdef GFORB_WITH_OPENCV
+    static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b) { return gforb_hamming256(a.data, b.data); }
+#endif
+};
+
+// Frame::ComputeStereoMatches(): fills mvuRight / mvDepth from the Frame's members (src/Frame.cc:889-1078).
+inline int ComputeStereoMatches(ORBextractor& left, ORBextractor& right, const std::vector<gforb_keypoint>& mvKeys,
+                                const std::vector<uint8_t>& mDescriptors, const std::vector<gforb_keypoint>& mvKeysRight,
+                                const std::vector<uint8_t>& mDescriptorsRight, float mbf, float mb,
+                                std::vector<float>& mvuRight, std::vector<float>& mvDepth,
+                                int mode = GFORB_STEREO_CLASSIC, float mnMinX = 0.f) {
+    const int N = (int)mvKeys.size();
+    mvuRight.assign(N, -1.0f);
+    mvDepth.assign(N, -1.0f);
+    gforb_stereo_params prm{mbf, mb, mode, GFORB_TH_HIGH, GFORB_TH_LOW, mnMinX};
+    int nmatched = 0;
+    check(gforb_stereo_match(left.handle(), right.handle(), &prm, mvKeys.data(), N, mDescriptors.data(),
+                             mvKeysRight.data(), (int)mvKeysRight.size(), mDescriptorsRight.data(), nullptr, nullptr,
+                             mvuRight.data(), mvDepth.data(), &nmatched), "ComputeStereoMatches");
+    return nmatched;
+}
+
+}  // namespace gforb

@@ -1,0 +1,54 @@
+// Exercises the C++ mirror (include/gforb/ORBextractor.hpp) the way Frame::Frame does (src/Frame.cc:248-326):
+// two extractors, one thread per eye, then ComputeStereoMatches.  Prints counts and FNV hashes so the pytest
+// wrapper can compare them with the ctypes path.  usage: shim_test left.pgm right.pgm
+#include <cstdio>
+#include <fstream>
+#include <sstream>
+#include <thread>
+#include "../../include/gforb/ORBextractor.hpp"
+
+static std::vector<uint8_t> read_pgm(const char* path, int& w, int& h) {
+    std::ifstream f(path, std::ios::binary);
+    std::string magic; int maxv;
+    f >> magic >> w >> h >> maxv;
+    f.get();
+    std::vector<uint8_t> px((size_t)w * h);
+    f.read(reinterpret_cast<char*>(px.data()), px.size());
+    return px;
+}
+static uint64_t fnv(const void* p, size_t n) {
+    uint64_t hsh = 1469598103934665603ull;
+    for (size_t i = 0; i < n; ++i) { hsh ^= static_cast<const uint8_t*>(p)[i]; hsh *= 1099511628211ull; }
+    return hsh;
+}
+
+int main(int argc, char** argv) {
+    if (argc < 3) return 2;
+    try {
+        int w, h, w2, h2;
+        std::vector<uint8_t> imL = read_pgm(argv[1], w, h), imR = read_pgm(argv[2], w2, h2);
+        gforb::ORBextractor exL(1000, 1.2f, 8, 20, 7), exR(1000, 1.2f, 8, 20, 7);
+        std::vector<gforb_keypoint> kL, kR;
+        std::vector<uint8_t> dL, dR;
+        std::thread tl([&] { exL(imL.data(), w, h, (size_t)w, kL, dL); });      // Frame::ExtractORB(0, imLeft)
+        std::thread tr([&] { exR(imR.data(), w2, h2, (size_t)w2, kR, dR); });   // Frame::ExtractORB(1, imRight)
+        tl.join(); tr.join();
+        std::vector<float> u, z;
+        const float bf = 47.90639384423901f, b = bf / 435.2046959714599f;
+        const int nm = gforb::ComputeStereoMatches(exL, exR, kL, dL, kR, dR, bf, b, u, z);
+        printf("nL=%zu nR=%zu nmatched=%d levels=%d dist=%d\n", kL.size(), kR.size(), nm, exL.GetLevels(),
+               gforb::ORBmatcher::DescriptorDistance(dL.data(), dR.data()));
+        printf("hash kL=%016llx dL=%016llx kR=%016llx dR=%016llx u=%016llx z=%016llx\n",
+               (unsigned long long)fnv(kL.data(), kL.size() * sizeof(gforb_keypoint)), (unsigned long long)fnv(dL.data(), dL.size()),
+               (unsigned long long)fnv(kR.data(), kR.size() * sizeof(gforb_keypoint)), (unsigned long long)fnv(dR.data(), dR.size()),
+               (unsigned long long)fnv(u.data(), u.size() * 4), (unsigned long long)fnv(z.data(), z.size() * 4));
+        // an empty image is the reference's silent no-op
+        std::vector<gforb_keypoint> k0; std::vector<uint8_t> d0;
+        exL(nullptr, 0, 0, 0, k0, d0);
+        printf("empty ok=%d\n", (int)(k0.empty() && d0.empty()));
+    } catch (const std::exception& e) {
+        printf("EXCEPTION %s\n", e.what());
+        return 1;
+    }
+    return 0;
+}

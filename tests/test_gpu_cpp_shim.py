@@ -1,0 +1,48 @@
+"""GPU: the header-only C++ mirror (include/gforb/ORBextractor.hpp) driven like Frame::Frame (two threads, then
+ComputeStereoMatches) must give byte-identical results to the ctypes path; plus the TMA helper probe."""
+import importlib
+import re
+import subprocess
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from conftest import B, BF
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def _fnv(a):
+    h = 1469598103934665603
+    for b in np.ascontiguousarray(a).view(np.uint8).ravel().tolist():
+        h = ((h ^ b) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
+    return h
+
+
+def test_cpp_shim_matches_ctypes(fixtures):
+    exe = ROOT / "tests/cpp/_build/shim_test"
+    assert exe.exists(), "run __graft_entry__.build() first"
+    out = subprocess.run([str(exe), str(ROOT / "tests/data/EuRoC_l.pgm"), str(ROOT / "tests/data/EuRoC_r.pgm")],
+                         capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stdout + out.stderr
+    m = re.search(r"nL=(\d+) nR=(\d+) nmatched=(\d+) levels=(\d+) dist=(\d+)", out.stdout)
+    hs = dict(re.findall(r"(\w+)=([0-9a-f]{16})", out.stdout))
+    gf = importlib.import_module("gf-orb-slam2_b200")
+    exL, exR = gf.ORBextractor(), gf.ORBextractor()
+    kL, dL = exL(fixtures["EuRoC_l"]); kR, dR = exR(fixtures["EuRoC_r"])
+    s = gf.ComputeStereoMatches(exL, exR, kL, dL, kR, dR, np.float32(BF), np.float32(np.float32(BF) / np.float32(435.2046959714599)))
+    assert (int(m[1]), int(m[2]), int(m[3]), int(m[4])) == (len(kL), len(kR), s["nmatched"], 8)
+    assert int(m[5]) == gf.DescriptorDistance(dL[0], dR[0])
+    assert int(hs["kL"], 16) == _fnv(kL) and int(hs["dL"], 16) == _fnv(dL)
+    assert int(hs["kR"], 16) == _fnv(kR) and int(hs["dR"], 16) == _fnv(dR)
+    assert int(hs["u"], 16) == _fnv(s["mvuRight"]) and int(hs["z"], 16) == _fnv(s["mvDepth"])
+    assert "empty ok=1" in out.stdout
+
+
+def test_tma_probe():
+    exe = ROOT / "tests/cpp/_build/tma_probe"
+    assert exe.exists(), "run __graft_entry__.build() first"
+    out = subprocess.run([str(exe)], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0 and "TMA PROBE OK" in out.stdout, out.stdout + out.stderr
