@@ -170,6 +170,7 @@ def main():
     ap.add_argument("--frames", type=int, default=256, help="stereo frames per step per GPU")
     ap.add_argument("--impl", default="gforb", choices=["gforb", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--chunk", type=int, default=0, help="frames per pipeline chunk of the end-to-end arm")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "gforb" else args.warmup
 
@@ -224,6 +225,7 @@ def main():
     barrier()
     sb.sync()
     ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+    launches_value = sb.last_launches() * args.steps          # kernels inside the timed region of `value`
     clocks = sampler.stop() if rank == 0 else None
     value = aggregate_throughput(F, args.steps, ms, world, dist)          # all ranks' frames / slowest rank's time
     ms_total = world * F * args.steps / value * 1e3
@@ -239,6 +241,7 @@ def main():
     stage_ms = {k: float(np.mean(v)) for k, v in acc.items()}
 
     # ---------------- end-to-end arm: host buffers in, host buffers out ----------------
+    sb.set_chunk(args.chunk)
     for _ in range(2):
         sb.process(pin_l.array, pin_r.array, out, BF, B)
     barrier()
@@ -248,6 +251,7 @@ def main():
     e1.record(stream)
     barrier()
     ms2 = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+    launches_e2e = sb.last_launches() * args.steps
     e2e_value = aggregate_throughput(F, args.steps, ms2, world, dist)
     K = sb.K
     h2d = 2 * F * W * H
@@ -292,8 +296,10 @@ def main():
                        "frames_per_step_per_gpu": F, "parallelism": f"frame-sharded x{world}, no collective",
                        "l2": "inputs+intermediates per step (%d MB) exceed the 126 MB L2" % ((2 * F * (W * H + 3 * 1344493)) >> 20),
                        "mean_keypoints_per_image": round(n_kp, 1), "fast_candidates_per_image": n_cand},
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-            "gpu_launches": sb.launches_per_run(True) * args.steps,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "gpu_launches": launches_e2e,
+                    "pipeline": "chunks of %s frames: H2D / kernels / D2H of successive chunks overlap (2 copy + 2 kernel streams)" % (args.chunk or "16 (auto)")},
+            "gpu_launches": launches_value,
             "clocks": clocks, "roofline": roofline, "stages": stages}
     if not args.no_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1

@@ -81,6 +81,8 @@ _SIGS = {
     "gforb_batch_sync": (_i, [_vp]),
     "gforb_stereo_frames_batch": (_i, [_vp, _vp, _vp, _i, C.POINTER(StereoParams), _vp, _vp, _vp, _vp, _vp]),
     "gforb_batch_launches_per_run": (_i, [_vp, _i]),
+    "gforb_batch_last_launches": (_i, [_vp]),
+    "gforb_batch_set_chunk": (_i, [_vp, _i]),
     "gforb_batch_stage_timing": (_i, [_vp, _i]),
     "gforb_batch_stage_times": (_i, [_vp, _vp]),
     "gforb_host_alloc": (_i, [C.POINTER(_vp), _sz]),
@@ -287,6 +289,14 @@ class StereoBatch:
     def launches_per_run(self, with_stereo=True):
         return _L.gforb_batch_launches_per_run(self._h, int(with_stereo))
 
+    def last_launches(self):
+        """kernels enqueued by the last run()/process() call"""
+        return _L.gforb_batch_last_launches(self._h)
+
+    def set_chunk(self, frames):
+        """process() pipelines H2D / kernels / D2H in chunks of `frames` stereo frames (0 = automatic)"""
+        _check(_L.gforb_batch_set_chunk(self._h, int(frames)))
+
     STAGES = ("pyramid", "fast", "quadtree", "blur", "describe", "stereo")
 
     def stage_timing(self, enable=True):
@@ -303,8 +313,9 @@ class StereoBatch:
                       descriptors=((2 * n_frames, K, 32), np.uint8), u_right=((n_frames, K), np.float32),
                       depth=((n_frames, K), np.float32))
         if pinned:
-            self._pins = {k: PinnedArray(s, d) for k, (s, d) in shapes.items()}
-            return {k: p.array for k, p in self._pins.items()}
+            pins = {k: PinnedArray(s, d) for k, (s, d) in shapes.items()}
+            self.__dict__.setdefault("_pins", []).append(pins)      # pinned buffers live as long as the batch
+            return {k: p.array for k, p in pins.items()}
         return {k: np.empty(s, d) for k, (s, d) in shapes.items()}
 
     def download(self, n_frames, out):

@@ -3,6 +3,7 @@
 #include <cstring>
 #include <memory>
 #include <new>
+#include <vector>
 
 #include "engine.hpp"
 
@@ -40,9 +41,22 @@ struct gforb_batch {
     int max_frames = 0;
     bool timing = false;
     cudaEvent_t ev[7] = {};
+    // chunked end-to-end pipeline (gforb_stereo_frames_batch): H2D, kernels and D2H of successive chunks overlap
+    cudaStream_t s_up = nullptr, s_down = nullptr, s_alt = nullptr;   // s_alt: second kernel stream (odd chunks)
+    std::vector<cudaEvent_t> ev_up, ev_done;
+    cudaEvent_t ev_start = nullptr, ev_down = nullptr;
+    int chunk_frames = 0;        // 0 = automatic
+    int last_launches = 0;       // kernels enqueued by the last run / frames_batch call
     ~gforb_batch() {
         for (auto& e : ev) if (e) cudaEventDestroy(e);
+        for (auto& e : ev_up) if (e) cudaEventDestroy(e);
+        for (auto& e : ev_done) if (e) cudaEventDestroy(e);
+        if (ev_start) cudaEventDestroy(ev_start);
+        if (ev_down) cudaEventDestroy(ev_down);
         eng.release();
+        if (s_up) cudaStreamDestroy(s_up);
+        if (s_down) cudaStreamDestroy(s_down);
+        if (s_alt) cudaStreamDestroy(s_alt);
         if (own) cudaStreamDestroy(own);
     }
 };
@@ -382,29 +396,40 @@ int gforb_batch_upload(gforb_batch* b, const uint8_t* left, const uint8_t* right
     return b->eng.upload_images(right, (size_t)b->eng.g.W, 1, 2, n, b->stream);
 }
 
-int gforb_batch_run(gforb_batch* b, int n, const gforb_stereo_params* prm) {
-    if (!b || n < 1 || n > b->max_frames) { set_error("gforb_batch_run: bad frame count"); return GFORB_ERR_ARG; }
+namespace {
+// kernels for frames [f0, f0 + n) on stream s
+int enqueue_frames(gforb_batch* b, int f0, int n, const gforb_stereo_params* prm, cudaStream_t s, bool timing) {
     Engine& E = b->eng;
     const int n_cap = b->max_frames;
-    int rc = E.run_extract(2 * n, b->stream, b->timing ? b->ev : nullptr);
+    int rc = E.run_extract(2 * n, s, timing ? b->ev : nullptr, 2 * f0);
     if (rc) return rc;
-    if (b->timing && !prm) cudaEventRecord(b->ev[6], b->stream);
+    b->last_launches += E.g.nlevels + 4;
+    if (timing && !prm) cudaEventRecord(b->ev[6], s);
     if (prm) {
         const size_t K = (size_t)E.g.K;
         StereoView v{};
         v.kL = E.b.kps; v.kR = E.b.kps + K; v.dL = E.b.desc; v.dR = E.b.desc + K * 32;
         v.nL = E.b.nkp; v.nR = E.b.nkp + 1; v.k_stride = 2 * K; v.n_stride = 2;
         fill_view_levels(v, E, E, 2, 1);
+        v.f0 = f0;
         v.min_d = nullptr; v.max_d = nullptr;
         v.uright = E.b.uright; v.depth = E.b.depth; v.best_dist = E.b.st_best_dist; v.best_idx = E.b.st_best_idx;
         v.sad = E.b.st_sad; v.nmatch = E.b.st_nmatch; v.out_stride = K;
         v.cut_dist = E.b.st_cut; v.ticket = E.b.st_ticket; v.proc_count = E.b.st_ticket + n_cap;
-        launch_stereo(v, norm_params(*prm), n, (int)K, b->stream);
-        if (b->timing) cudaEventRecord(b->ev[6], b->stream);
+        launch_stereo(v, norm_params(*prm), n, (int)K, s);
+        b->last_launches += 1;
+        if (timing) cudaEventRecord(b->ev[6], s);
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return cuda_fail(e, "stereo launch");
     }
     return GFORB_OK;
+}
+}  // namespace
+
+int gforb_batch_run(gforb_batch* b, int n, const gforb_stereo_params* prm) {
+    if (!b || n < 1 || n > b->max_frames) { set_error("gforb_batch_run: bad frame count"); return GFORB_ERR_ARG; }
+    b->last_launches = 0;
+    return enqueue_frames(b, 0, n, prm, b->stream, b->timing);
 }
 
 int gforb_batch_stage_timing(gforb_batch* b, int enable) {
@@ -435,6 +460,7 @@ int gforb_batch_launches_per_run(const gforb_batch* b, int with_stereo) {
     if (!b) return GFORB_ERR_ARG;
     return b->eng.g.nlevels /* pyramid */ + 4 /* fast, quadtree, blur, describe */ + (with_stereo ? 1 : 0);
 }
+int gforb_batch_last_launches(const gforb_batch* b) { return b ? b->last_launches : GFORB_ERR_ARG; }
 
 int gforb_batch_download(gforb_batch* b, int n, int32_t* counts, gforb_keypoint* kps, uint8_t* desc,
                          float* u_right, float* depth) {
@@ -455,15 +481,73 @@ int gforb_batch_sync(gforb_batch* b) {
     return b->eng.check_errors(b->stream);
 }
 
+int gforb_batch_set_chunk(gforb_batch* b, int frames) {
+    if (!b || frames < 0) return GFORB_ERR_ARG;
+    b->chunk_frames = frames;
+    return GFORB_OK;
+}
+
+// Host buffers in, host buffers out.  The batch is cut into chunks; chunk c's H2D copy (upload stream), its
+// kernels (the batch's stream) and its D2H copy (download stream) are chained with events, so the copy engines
+// and the SMs work on different chunks at any time (kernels of even/odd chunks on two streams).  Results are complete when this returns.
 int gforb_stereo_frames_batch(gforb_batch* b, const uint8_t* left, const uint8_t* right, int n,
                               const gforb_stereo_params* prm, int32_t* counts, gforb_keypoint* kps,
                               uint8_t* desc, float* u_right, float* depth) {
-    int rc = gforb_batch_upload(b, left, right, n);
-    if (rc) return rc;
-    rc = gforb_batch_run(b, n, prm);
-    if (rc) return rc;
-    rc = gforb_batch_download(b, n, counts, kps, desc, u_right, depth);
-    if (rc) return rc;
+    if (!b || !left || !right || n < 1 || n > b->max_frames) { set_error("gforb_stereo_frames_batch: bad arguments"); return GFORB_ERR_ARG; }
+    int chunk = b->chunk_frames > 0 ? b->chunk_frames : (n >= 48 ? 16 : n);
+    chunk = std::min(chunk, n);
+    const int nchunks = (n + chunk - 1) / chunk;
+    Engine& E = b->eng;
+    cudaError_t e;
+#define GB(call, what) do { e = (call); if (e != cudaSuccess) return cuda_fail(e, what); } while (0)
+    if (!b->s_up) GB(cudaStreamCreateWithFlags(&b->s_up, cudaStreamNonBlocking), "cudaStreamCreate(upload)");
+    if (!b->s_down) GB(cudaStreamCreateWithFlags(&b->s_down, cudaStreamNonBlocking), "cudaStreamCreate(download)");
+    if (!b->s_alt) GB(cudaStreamCreateWithFlags(&b->s_alt, cudaStreamNonBlocking), "cudaStreamCreate(kernels 2)");
+    if (!b->ev_start) GB(cudaEventCreateWithFlags(&b->ev_start, cudaEventDisableTiming), "cudaEventCreate");
+    if (!b->ev_down) GB(cudaEventCreateWithFlags(&b->ev_down, cudaEventDisableTiming), "cudaEventCreate");
+    while ((int)b->ev_up.size() < nchunks) {
+        cudaEvent_t a = nullptr, d = nullptr;
+        GB(cudaEventCreateWithFlags(&a, cudaEventDisableTiming), "cudaEventCreate");
+        b->ev_up.push_back(a);
+        GB(cudaEventCreateWithFlags(&d, cudaEventDisableTiming), "cudaEventCreate");
+        b->ev_done.push_back(d);
+    }
+    const size_t K = (size_t)E.g.K, isz = (size_t)E.g.W * E.g.H;
+    b->last_launches = 0;
+    // the copy streams start after whatever the caller already queued on the batch's stream
+    GB(cudaEventRecord(b->ev_start, b->stream), "cudaEventRecord");
+    GB(cudaStreamWaitEvent(b->s_up, b->ev_start, 0), "cudaStreamWaitEvent");
+    GB(cudaStreamWaitEvent(b->s_down, b->ev_start, 0), "cudaStreamWaitEvent");
+    GB(cudaStreamWaitEvent(b->s_alt, b->ev_start, 0), "cudaStreamWaitEvent");
+    for (int c = 0; c < nchunks; ++c) {
+        const int f0 = c * chunk, m = std::min(chunk, n - f0);
+        GB(cudaMemcpy2DAsync(E.b.in + isz * (2 * (size_t)f0), 2 * isz, left + isz * f0, isz, isz, m,
+                             cudaMemcpyHostToDevice, b->s_up), "cudaMemcpy2DAsync(left)");
+        GB(cudaMemcpy2DAsync(E.b.in + isz * (2 * (size_t)f0 + 1), 2 * isz, right + isz * f0, isz, isz, m,
+                             cudaMemcpyHostToDevice, b->s_up), "cudaMemcpy2DAsync(right)");
+        GB(cudaEventRecord(b->ev_up[c], b->s_up), "cudaEventRecord");
+    }
+    for (int c = 0; c < nchunks; ++c) {
+        const int f0 = c * chunk, m = std::min(chunk, n - f0);
+        // even chunks on the batch's stream, odd chunks on a second one: the tail of one chunk's low-occupancy
+        // kernels (quadtree, stereo) is filled by the next chunk's streaming kernels
+        cudaStream_t sk = (c & 1) ? b->s_alt : b->stream;
+        GB(cudaStreamWaitEvent(sk, b->ev_up[c], 0), "cudaStreamWaitEvent");
+        int rc = enqueue_frames(b, f0, m, prm, sk, false);
+        if (rc) return rc;
+        GB(cudaEventRecord(b->ev_done[c], sk), "cudaEventRecord");
+        GB(cudaStreamWaitEvent(b->s_down, b->ev_done[c], 0), "cudaStreamWaitEvent");
+        const size_t i0 = 2 * (size_t)f0, ni = 2 * (size_t)m;
+        if (counts) GB(cudaMemcpyAsync(counts + i0, E.b.nkp + i0, ni * 4, cudaMemcpyDeviceToHost, b->s_down), "D2H counts");
+        if (kps) GB(cudaMemcpyAsync(kps + i0 * K, E.b.kps + i0 * K, ni * K * sizeof(gforb_keypoint), cudaMemcpyDeviceToHost, b->s_down), "D2H keypoints");
+        if (desc) GB(cudaMemcpyAsync(desc + i0 * K * 32, E.b.desc + i0 * K * 32, ni * K * 32, cudaMemcpyDeviceToHost, b->s_down), "D2H descriptors");
+        if (prm && u_right) GB(cudaMemcpyAsync(u_right + (size_t)f0 * K, E.b.uright + (size_t)f0 * K, (size_t)m * K * 4, cudaMemcpyDeviceToHost, b->s_down), "D2H uRight");
+        if (prm && depth) GB(cudaMemcpyAsync(depth + (size_t)f0 * K, E.b.depth + (size_t)f0 * K, (size_t)m * K * 4, cudaMemcpyDeviceToHost, b->s_down), "D2H depth");
+    }
+    // rejoin: work queued on the batch's stream after this call is ordered after the last download
+    GB(cudaEventRecord(b->ev_down, b->s_down), "cudaEventRecord");
+    GB(cudaStreamWaitEvent(b->stream, b->ev_down, 0), "cudaStreamWaitEvent");
+#undef GB
     return gforb_batch_sync(b);
 }
 

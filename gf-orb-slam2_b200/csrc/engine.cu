@@ -91,7 +91,7 @@ int make_geometry(const Tables& t, const gforb_limits& lim, int W, int H, int ni
     std::memset(&g, 0, sizeof(g));
     tabs.clear();
     const int nl = t.prm.nlevels;
-    g.nlevels = nl; g.W = W; g.H = H; g.nimg = nimg;
+    g.nlevels = nl; g.W = W; g.H = H; g.nimg = nimg; g.img0 = 0;
     g.ini_th = t.prm.ini_th_fast; g.min_th = t.prm.min_th_fast;
     if (W > 4096 + 32 || H > 4096 + 32 || nimg < 1 || nimg > 65535) {
         set_error("gforb: image larger than 4128 px or bad batch size");
@@ -287,6 +287,7 @@ int Engine::upload_images(const uint8_t* host, size_t pitch, int first_img, int 
 }
 
 int Engine::run_pyramid(int nimg, cudaStream_t s) {
+    g.img0 = 0;
     launch_pyramid(g, b, nimg, s);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "pyramid launch");
@@ -294,7 +295,8 @@ int Engine::run_pyramid(int nimg, cudaStream_t s) {
     return GFORB_OK;
 }
 
-int Engine::run_extract(int nimg, cudaStream_t s, cudaEvent_t* ev) {
+int Engine::run_extract(int nimg, cudaStream_t s, cudaEvent_t* ev, int img0) {
+    g.img0 = img0;   // Geom travels by value as a kernel parameter
     if (ev) cudaEventRecord(ev[0], s);
     launch_pyramid(g, b, nimg, s);
     if (ev) cudaEventRecord(ev[1], s);
@@ -306,6 +308,7 @@ int Engine::run_extract(int nimg, cudaStream_t s, cudaEvent_t* ev) {
     if (ev) cudaEventRecord(ev[4], s);
     launch_describe(g, b, nimg, s);
     if (ev) cudaEventRecord(ev[5], s);
+    g.img0 = 0;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "extract launch");
     pyramid_valid = true;

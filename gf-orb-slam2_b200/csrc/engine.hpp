@@ -36,7 +36,8 @@ public:
     int upload_images(const uint8_t* host, size_t pitch, int first_img, int step, int count, cudaStream_t s);
     // pyramid only / full extraction for images [0, nimg)
     int run_pyramid(int nimg, cudaStream_t s);
-    int run_extract(int nimg, cudaStream_t s, cudaEvent_t* stage_events = nullptr);   // 6 events when given
+    // images [img0, img0 + nimg); 6 stage events when given
+    int run_extract(int nimg, cudaStream_t s, cudaEvent_t* stage_events = nullptr, int img0 = 0);
     // read + clear the sticky device error word (synchronises `s`)
     int check_errors(cudaStream_t s);
 

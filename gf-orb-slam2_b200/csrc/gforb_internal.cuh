@@ -47,6 +47,7 @@ struct Geom {
     int nlevels;
     int W, H;                 // input size
     int nimg;                 // images in the arena
+    int img0;                 // first image of this launch (chunked batches); kernels index image img0 + blockIdx
     int cells_total;          // cells per image over all levels
     int cell_cap;             // survivor slots per cell (theoretical NMS maximum)
     int kstage;               // staging slots per image (sum of kcap)
@@ -107,6 +108,7 @@ struct StereoView {
     int pitch[kMaxLevels], w[kMaxLevels];
     float scale[kMaxLevels], inv_scale[kMaxLevels];
     int nRows;                // rows of level 0
+    int f0;                   // first frame of this launch (chunked batches)
     const float* min_d; const float* max_d;  // optional per-key windows (frame 0), may be null
     float* uright; float* depth; int32_t* best_dist; int32_t* best_idx; int32_t* sad; int32_t* nmatch;
     int32_t* cut_dist;        // per left key: distance entering the median cut (-1 = none), out_stride layout
@@ -117,7 +119,7 @@ struct StereoView {
 enum ErrBits { kErrCandOverflow = 1, kErrCellOverflow = 2, kErrNodeOverflow = 4, kErrKpOverflow = 8 };
 
 // ---- kernel launchers (each enqueues on `s`; defined in the per-stage .cu files) ----
-void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);        // 1 + (nlevels-1) launches
+void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);   // images [g.img0, g.img0+nimg)
 void launch_fast(const Geom& g, const TileMaps& m, const Buffers& b, int nimg, cudaStream_t s);   // 1 launch
 void launch_octree(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);         // 1 launch
 void launch_blur(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);           // 1 launch

@@ -33,7 +33,7 @@ __device__ __forceinline__ void row_sums(const uint8_t* row, int (&o)[4]) {
 
 __global__ void __launch_bounds__(kWarps * 32)
 blur_kernel(const Geom g, const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur) {
-    const int img = blockIdx.y;
+    const int img = g.img0 + blockIdx.y;
     int t = blockIdx.x, l = 0;
     while (l + 1 < g.nlevels && t >= g.lv[l + 1].btile_base) ++l;
     const LevelGeom& L = g.lv[l];

@@ -58,7 +58,7 @@ describe_kernel(const Geom g, const uint8_t* __restrict__ pyr, const uint8_t* __
     }
     __syncthreads();
 
-    const int img = blockIdx.y;
+    const int img = g.img0 + blockIdx.y;
     const int lane = threadIdx.x & 31;
     const int slot = blockIdx.x * kWarps + (threadIdx.x >> 5);
     if (slot >= g.kstage) return;

@@ -74,7 +74,7 @@ fast_cells_kernel(const Geom g, const __grid_constant__ TileMaps maps, uint32_t*
     __shared__ __align__(8) uint64_t bar;
     __shared__ int s_any_hi, s_nlist;
 
-    const int img = blockIdx.y;
+    const int img = g.img0 + blockIdx.y;
     int cell = blockIdx.x;
     int l = 0;
     while (l + 1 < g.nlevels && cell >= g.lv[l + 1].cell_base) ++l;

@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(kT)
 octree_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_t* __restrict__ cell_pts,
               int32_t* __restrict__ lvl_cnt, uint32_t* __restrict__ lvl_pts, int32_t* __restrict__ err) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
-    const int l = blockIdx.x, img = blockIdx.y;
+    const int l = blockIdx.x, img = g.img0 + blockIdx.y;
     const LevelGeom& L = g.lv[l];
     const int NC = g.max_nodes;
     Smem s = carve(smem_raw, g.max_cand, NC);

@@ -21,8 +21,8 @@ __device__ __forceinline__ int reflect101(int p, int len) {
 
 __global__ void __launch_bounds__(256)
 pyr_level0_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int W, int H, int pitch, int rows,
-                  size_t img_stride) {
-    const int img = blockIdx.z;
+                  size_t img_stride, int img0) {
+    const int img = img0 + blockIdx.z;
     const int py = blockIdx.y * blockDim.y + threadIdx.y;
     const int px4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
     if (py >= rows || px4 >= pitch) return;
@@ -42,8 +42,8 @@ pyr_level0_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int
 __global__ void __launch_bounds__(256)
 pyr_resize_kernel(const uint8_t* __restrict__ src_roi, int spitch, size_t simg_stride,
                   uint8_t* __restrict__ out, int w, int h, int pitch, int rows, size_t img_stride,
-                  const int2* __restrict__ tab_x, const int2* __restrict__ tab_y, int area2x) {
-    const int img = blockIdx.z;
+                  const int2* __restrict__ tab_x, const int2* __restrict__ tab_y, int area2x, int img0) {
+    const int img = img0 + blockIdx.z;
     const int py = blockIdx.y * blockDim.y + threadIdx.y;
     const int px4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
     if (py >= rows || px4 >= pitch) return;
@@ -91,7 +91,7 @@ void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s) {
     {
         const LevelGeom& L = g.lv[0];
         dim3 grd((L.pitch / 4 + blk.x - 1) / blk.x, (L.rows + blk.y - 1) / blk.y, nimg);
-        pyr_level0_kernel<<<grd, blk, 0, s>>>(b.in, b.pyr + L.off, g.W, g.H, L.pitch, L.rows, L.img_stride);
+        pyr_level0_kernel<<<grd, blk, 0, s>>>(b.in, b.pyr + L.off, g.W, g.H, L.pitch, L.rows, L.img_stride, g.img0);
     }
     for (int l = 1; l < g.nlevels; ++l) {
         const LevelGeom& P = g.lv[l - 1];
@@ -101,7 +101,7 @@ void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s) {
         pyr_resize_kernel<<<grd, blk, 0, s>>>(src_roi, P.pitch, P.img_stride, b.pyr + L.off, L.w, L.h, L.pitch,
                                               L.rows, L.img_stride,
                                               reinterpret_cast<const int2*>(b.tabs + L.tab_x),
-                                              reinterpret_cast<const int2*>(b.tabs + L.tab_y), L.area2x);
+                                              reinterpret_cast<const int2*>(b.tabs + L.tab_y), L.area2x, g.img0);
     }
 }
 

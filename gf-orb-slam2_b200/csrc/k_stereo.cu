@@ -36,7 +36,7 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
     int* s_dist = reinterpret_cast<int*>(smem_raw + sizeof(RKey) * (size_t)K);
     __shared__ int s_cnt, s_median, s_removed, s_processed, s_last;
 
-    const int f = blockIdx.x, slice = blockIdx.y;
+    const int f = v.f0 + blockIdx.x, slice = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const gforb_keypoint* kL = v.kL + (size_t)f * v.k_stride;
     const gforb_keypoint* kR = v.kR + (size_t)f * v.k_stride;

@@ -186,6 +186,12 @@ GFORB_API int gforb_stereo_frames_batch(gforb_batch* b, const uint8_t* left, con
                               const gforb_stereo_params* prm, int32_t* counts, gforb_keypoint* keypoints,
                               uint8_t* descriptors, float* u_right, float* depth);
 
+/* gforb_stereo_frames_batch pipelines the batch in chunks of `frames` stereo frames (H2D of chunk c+1, kernels of
+ * chunk c and D2H of chunk c-1 overlap on separate streams); 0 = automatic (16 when the batch has >= 48 frames) */
+GFORB_API int gforb_batch_set_chunk(gforb_batch* b, int frames);
+/* kernels actually enqueued by the last gforb_batch_run / gforb_stereo_frames_batch call */
+GFORB_API int gforb_batch_last_launches(const gforb_batch* b);
+
 /* number of kernel launches one gforb_batch_run enqueues (for bench.py's gpu_launches) and per-kernel
  * algorithmic byte counts per stereo frame */
 GFORB_API int gforb_batch_launches_per_run(const gforb_batch* b, int with_stereo);

@@ -214,3 +214,34 @@ def test_batch_matches_single_and_oracle(gf, O):
         assert out2["counts"][2 * (n - 1 - f)] == nL
         assert np.array_equal(out2["descriptors"][2 * (n - 1 - f), :nL], out["descriptors"][2 * f, :nL])
         assert np.array_equal(out2["depth"][n - 1 - f, :nL], out["depth"][f, :nL])
+
+
+def test_chunked_pipeline_equals_whole_batch(gf):
+    """gforb_stereo_frames_batch overlaps H2D / kernels / D2H in chunks: any chunking (ragged last chunk included)
+    must give byte-identical host outputs to one un-chunked pass, and report its kernel count."""
+    n = 7
+    pairs = [synth_stereo(40 + i, nshapes=200) for i in range(n)]
+    left = np.stack([p[0] for p in pairs]); right = np.stack([p[1] for p in pairs])
+    sb = gf.StereoBatch(752, 480, n)
+    ref = sb.alloc_outputs(n)
+    sb.set_chunk(n)
+    sb.process(left, right, ref, BF, B)
+    per = sb.launches_per_run(True)
+    assert sb.last_launches() == per
+    for chunk in (1, 2, 3, 0):
+        out = sb.alloc_outputs(n, pinned=(chunk != 2))
+        for v in out.values():
+            v[...] = 0
+        sb.set_chunk(chunk)
+        sb.process(left, right, out, BF, B)
+        nch = 1 if chunk == 0 else -(-n // chunk)
+        assert sb.last_launches() == per * nch
+        assert np.array_equal(out["counts"], ref["counts"])
+        for i in range(2 * n):
+            c = ref["counts"][i]
+            assert out["keypoints"][i, :c].tobytes() == ref["keypoints"][i, :c].tobytes()
+            assert np.array_equal(out["descriptors"][i, :c], ref["descriptors"][i, :c])
+        for f in range(n):
+            c = ref["counts"][2 * f]
+            assert np.array_equal(out["u_right"][f, :c], ref["u_right"][f, :c])
+            assert np.array_equal(out["depth"][f, :c], ref["depth"][f, :c])
