@@ -195,7 +195,7 @@ Engine::~Engine() { release(); }
 
 void Engine::release() {
     auto fr = [](auto*& p) { if (p) cudaFree(p); p = nullptr; };
-    fr(b.in); fr(b.pyr); fr(b.blur); fr(b.tabs); fr(b.cell_cnt); fr(b.cell_pts); fr(b.lvl_cnt); fr(b.lvl_pts);
+    fr(b.in); fr(b.cell_tab); fr(b.pyr); fr(b.blur); fr(b.tabs); fr(b.cell_cnt); fr(b.cell_pts); fr(b.lvl_cnt); fr(b.lvl_pts);
     fr(b.kps); fr(b.desc); fr(b.nkp); fr(b.uright); fr(b.depth); fr(b.st_best_dist); fr(b.st_best_idx);
     fr(b.st_sad); fr(b.st_nmatch); fr(b.st_cut); fr(b.st_ticket); fr(b.err);
     if (h_small) cudaFreeHost(h_small);
@@ -219,6 +219,12 @@ int Engine::init(const Tables& t, const gforb_limits& lim, int W, int H, int nim
     GFORB_CUDA(cudaMalloc(&b.blur, blur_bytes));
     GFORB_CUDA(cudaMalloc(&b.tabs, std::max<size_t>(tabs.size(), 2) * 4));
     GFORB_CUDA(cudaMalloc(&b.cell_cnt, NI * g.cells_total * 4));
+    {
+        std::vector<uint32_t> ct;
+        build_fast_cell_table(g, ct);
+        GFORB_CUDA(cudaMalloc(&b.cell_tab, std::max<size_t>(ct.size(), 8) * 4));
+        if (!ct.empty()) GFORB_CUDA(cudaMemcpy(b.cell_tab, ct.data(), ct.size() * 4, cudaMemcpyHostToDevice));
+    }
     GFORB_CUDA(cudaMalloc(&b.cell_pts, NI * g.cells_total * (size_t)g.cell_cap * 4));
     GFORB_CUDA(cudaMalloc(&b.lvl_cnt, NI * g.nlevels * 4));
     GFORB_CUDA(cudaMalloc(&b.lvl_pts, NI * g.kstage * 4));

@@ -78,6 +78,7 @@ struct Buffers {
     uint8_t* pyr = nullptr;       // padded pyramid arena
     uint8_t* blur = nullptr;      // blurred arena
     int32_t* tabs = nullptr;      // resize tables
+    uint32_t* cell_tab = nullptr; // cells_total x 8 words: FAST per-cell geometry (k_fast.cu)
     uint32_t* cell_cnt = nullptr; // nimg x cells_total
     uint32_t* cell_pts = nullptr; // nimg x cells_total x cell_cap
     int32_t* lvl_cnt = nullptr;   // nimg x nlevels   kept keypoints per level
@@ -125,6 +126,7 @@ void launch_octree(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);  
 void launch_blur(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);           // 1 launch
 void launch_describe(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);       // 1 launch
 void launch_stereo(const StereoView& v, const gforb_stereo_params& p, int nframes, int K, cudaStream_t s);  // 1 launch
+void build_fast_cell_table(const Geom& g, std::vector<uint32_t>& tab);
 size_t octree_smem_bytes(const Geom& g);
 int octree_configure(const Geom& g);   // opt in to large dynamic smem; returns cudaError_t as int
 
