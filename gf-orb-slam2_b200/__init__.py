@@ -6,6 +6,8 @@ Thin ctypes binding of ``libgforb.so`` (C ABI in ``include/gforb.h``; hand-writt
 * :class:`ORBextractor`  -- ``ORB_SLAM2::ORBextractor`` (include/ORBextractor.h:76-168)
 * :func:`DescriptorDistance` -- ``ORBmatcher::DescriptorDistance`` (src/ORBmatcher.cc:1768-1784)
 * :func:`ComputeStereoMatches` -- ``Frame::ComputeStereoMatches`` / ``_Undistorted`` (src/Frame.cc:889-1078, 1167-1316)
+* :class:`ORBmatcher` -- ``ORB_SLAM2::ORBmatcher(nnratio, checkOri)`` (include/ORBmatcher.h:46): brute-force
+  best / second-best search with the ratio and threshold tests of src/ORBmatcher.cc:562-576
 * :class:`StereoBatch` -- the batched ``Frame::Frame(imLeft, imRight, ...)`` front-end (src/Frame.cc:248-326)
 
 There is no CPU fallback: a missing library raises at import, a missing CUDA device raises on first use.
@@ -85,6 +87,14 @@ _SIGS = {
     "gforb_batch_set_chunk": (_i, [_vp, _i]),
     "gforb_batch_stage_timing": (_i, [_vp, _i]),
     "gforb_batch_stage_times": (_i, [_vp, _vp]),
+    "gforb_matcher_create": (_i, [C.c_float, C.POINTER(_vp)]),
+    "gforb_matcher_destroy": (None, [_vp]),
+    "gforb_match_bruteforce": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp]),
+    "gforb_match_bruteforce_device": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "gforb_matcher_sync": (_i, [_vp, C.POINTER(C.c_float)]),
+    "gforb_device_alloc": (_i, [C.POINTER(_vp), _sz]),
+    "gforb_device_free": (None, [_vp]),
+    "gforb_device_copy": (_i, [_vp, _vp, _sz, _i]),
     "gforb_host_alloc": (_i, [C.POINTER(_vp), _sz]),
     "gforb_host_free": (None, [_vp]),
 }
@@ -114,6 +124,83 @@ def DescriptorDistance(a, b):
     a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
     assert a.size == 32 and b.size == 32
     return _L.gforb_hamming256(_p(a), _p(b))
+
+
+class DeviceArray:
+    """cudaMalloc'ed buffer with numpy upload/download (device-resident inputs for ORBmatcher / benches)."""
+
+    def __init__(self, shape, dtype):
+        self.shape, self.dtype = tuple(shape), np.dtype(dtype)
+        self.nbytes = int(np.prod(self.shape)) * self.dtype.itemsize
+        self._ptr = _vp()
+        _check(_L.gforb_device_alloc(C.byref(self._ptr), self.nbytes))
+
+    @property
+    def ptr(self):
+        return self._ptr.value
+
+    @classmethod
+    def from_host(cls, a):
+        a = np.ascontiguousarray(a)
+        d = cls(a.shape, a.dtype)
+        if a.nbytes:
+            _check(_L.gforb_device_copy(d._ptr, _p(a), a.nbytes, 0))
+        return d
+
+    def to_host(self):
+        out = np.empty(self.shape, self.dtype)
+        if self.nbytes:
+            _check(_L.gforb_device_copy(_p(out), self._ptr, self.nbytes, 1))
+        return out
+
+    def __del__(self):
+        p = getattr(self, "_ptr", None)
+        if p:
+            _L.gforb_device_free(p)
+            self._ptr = None
+
+
+class ORBmatcher:
+    """ORB_SLAM2::ORBmatcher(float nnratio = 0.6, bool checkOri = true) (include/ORBmatcher.h:46).  Carries
+    mfNNratio; BruteForce() is the matcher's nearest / second-nearest loop (src/ORBmatcher.cc:562-576) over all
+    train descriptors, on the device."""
+    TH_HIGH, TH_LOW = TH_HIGH, TH_LOW
+    DescriptorDistance = staticmethod(DescriptorDistance)
+
+    def __init__(self, nnratio=0.6, checkOri=True):
+        self.mfNNratio, self.mbCheckOrientation = float(nnratio), bool(checkOri)
+        self._h = _vp()
+        _check(_L.gforb_matcher_create(self.mfNNratio, C.byref(self._h)))
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            _L.gforb_matcher_destroy(h)
+            self._h = None
+
+    def BruteForce(self, desc_a, desc_b, th=TH_LOW):
+        """host arrays [nA,32], [nB,32] u8 -> dict(best_idx, best_dist, second_dist, match) (int32[nA])"""
+        a = np.ascontiguousarray(desc_a, np.uint8).reshape(-1, 32); b = np.ascontiguousarray(desc_b, np.uint8).reshape(-1, 32)
+        n = len(a)
+        out = {k: np.empty(n, np.int32) for k in ("best_idx", "best_dist", "second_dist", "match")}
+        _check(_L.gforb_match_bruteforce(self._h, _p(a) if n else None, n, _p(b) if len(b) else None, len(b), th,
+                                         _p(out["best_idx"]), _p(out["best_dist"]), _p(out["second_dist"]),
+                                         _p(out["match"])))
+        return out
+
+    def BruteForceDevice(self, dev_a, n_a, dev_b, n_b, th, dev_best_idx, dev_best_dist, dev_second_dist, dev_match,
+                         stream=None):
+        """device pointers (ints or DeviceArray); asynchronous on `stream` (a cudaStream_t value) or the matcher's own"""
+        ptr = lambda x: None if x is None else _vp(x.ptr if isinstance(x, DeviceArray) else x)
+        _check(_L.gforb_match_bruteforce_device(self._h, ptr(dev_a), n_a, ptr(dev_b), n_b, th, ptr(dev_best_idx),
+                                                ptr(dev_best_dist), ptr(dev_second_dist), ptr(dev_match),
+                                                _vp(stream) if stream else None))
+
+    def sync(self):
+        """wait for the last BruteForceDevice; returns its device time in ms"""
+        ms = C.c_float(0)
+        _check(_L.gforb_matcher_sync(self._h, C.byref(ms)))
+        return ms.value
 
 
 class ORBextractor:

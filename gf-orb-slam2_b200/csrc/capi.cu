@@ -61,6 +61,31 @@ struct gforb_batch {
     }
 };
 
+struct gforb_matcher {
+    float ratio = 0.6f;
+    int sms = 148;
+    cudaStream_t stream = nullptr, last = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+    void* scratch = nullptr; size_t scratch_bytes = 0;   // per-segment partial results
+    void* io = nullptr; size_t io_bytes = 0;             // staging of the host-pointer form
+    int reserve(void*& p, size_t& have, size_t want) {
+        if (want <= have) return GFORB_OK;
+        if (p) { cudaFree(p); p = nullptr; have = 0; }
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc(matcher)");
+        have = want;
+        return GFORB_OK;
+    }
+    ~gforb_matcher() {
+        if (scratch) cudaFree(scratch);
+        if (io) cudaFree(io);
+        if (ev0) cudaEventDestroy(ev0);
+        if (ev1) cudaEventDestroy(ev1);
+        if (stream) cudaStreamDestroy(stream);
+    }
+};
+
 namespace {
 int ensure_stream(cudaStream_t& s) {
     if (s) return GFORB_OK;
@@ -347,6 +372,89 @@ int gforb_debug_stereo(gforb_extractor* exL, int nL, int32_t* bd, int32_t* bi, i
     if (bi && e == cudaSuccess) e = cudaMemcpy(bi, exL->st_bi, (size_t)nL * 4, cudaMemcpyDeviceToHost);
     if (sad && e == cudaSuccess) e = cudaMemcpy(sad, exL->st_sad, (size_t)nL * 4, cudaMemcpyDeviceToHost);
     return e == cudaSuccess ? GFORB_OK : cuda_fail(e, "cudaMemcpy(stereo debug)");
+}
+
+// ----------------------------------------------------------------------------------------------- matcher
+#define M_CUDA(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return cuda_fail(e_, #call); } while (0)
+
+int gforb_matcher_create(float nnratio, gforb_matcher** out) {
+    if (!out || !(nnratio > 0.f)) { set_error("gforb_matcher_create: bad arguments"); return GFORB_ERR_ARG; }
+    int dev = 0, sms = 0;
+    M_CUDA(cudaGetDevice(&dev));
+    M_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    std::unique_ptr<gforb_matcher> m(new (std::nothrow) gforb_matcher);
+    if (!m) return GFORB_ERR_ARG;
+    m->ratio = nnratio; m->sms = sms;
+    int rc = ensure_stream(m->stream);
+    if (rc) return rc;
+    M_CUDA(cudaEventCreate(&m->ev0));
+    M_CUDA(cudaEventCreate(&m->ev1));
+    *out = m.release();
+    return GFORB_OK;
+}
+void gforb_matcher_destroy(gforb_matcher* m) { delete m; }
+
+int gforb_match_bruteforce_device(gforb_matcher* m, const uint8_t* dA, int nA, const uint8_t* dB, int nB, int threshold,
+                                  int32_t* best_idx, int32_t* best_dist, int32_t* second_dist, int32_t* match,
+                                  void* cuda_stream) {
+    if (!m || nA < 0 || nB < 0 || (nA > 0 && !dA) || (nB > 0 && !dB)) { set_error("gforb_match_bruteforce: bad arguments"); return GFORB_ERR_ARG; }
+    if (nB > match_max_train()) { set_error("gforb_match_bruteforce: n_b exceeds 4,194,304"); return GFORB_ERR_CAPACITY; }
+    if (((uintptr_t)dA | (uintptr_t)dB) & 15) { set_error("gforb_match_bruteforce: descriptor arrays must be 16-byte aligned"); return GFORB_ERR_ARG; }
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : m->stream;
+    m->last = s;
+    const int nseg = match_segments(nA, nB, m->sms);
+    int rc = m->reserve(m->scratch, m->scratch_bytes, match_scratch_bytes(nA, nseg));
+    if (rc) return rc;
+    M_CUDA(cudaEventRecord(m->ev0, s));
+    launch_match(dA, nA, dB, nB, m->ratio, threshold, nseg, m->scratch, best_idx, best_dist, second_dist, match, s);
+    M_CUDA(cudaEventRecord(m->ev1, s));
+    M_CUDA(cudaGetLastError());
+    m->timed = true;
+    return GFORB_OK;
+}
+
+int gforb_matcher_sync(gforb_matcher* m, float* last_ms) {
+    if (!m) return GFORB_ERR_ARG;
+    M_CUDA(cudaStreamSynchronize(m->last ? m->last : m->stream));
+    if (last_ms) {
+        *last_ms = 0.f;
+        if (m->timed) M_CUDA(cudaEventElapsedTime(last_ms, m->ev0, m->ev1));
+    }
+    return GFORB_OK;
+}
+
+int gforb_match_bruteforce(gforb_matcher* m, const uint8_t* a, int nA, const uint8_t* b, int nB, int threshold,
+                           int32_t* best_idx, int32_t* best_dist, int32_t* second_dist, int32_t* match) {
+    if (!m || nA < 0 || nB < 0 || (nA > 0 && !a) || (nB > 0 && !b)) { set_error("gforb_match_bruteforce: bad arguments"); return GFORB_ERR_ARG; }
+    if (nA == 0) return GFORB_OK;
+    const size_t ba = (size_t)nA * 32, bb = (size_t)std::max(nB, 1) * 32, bo = (size_t)nA * 4;
+    int rc = m->reserve(m->io, m->io_bytes, ba + bb + 4 * bo + 64);
+    if (rc) return rc;
+    uint8_t* dA = static_cast<uint8_t*>(m->io);
+    uint8_t* dB = dA + ((ba + 15) & ~(size_t)15);
+    int32_t* o = reinterpret_cast<int32_t*>(dB + ((bb + 15) & ~(size_t)15));
+    cudaStream_t s = m->stream;
+    M_CUDA(cudaMemcpyAsync(dA, a, ba, cudaMemcpyHostToDevice, s));
+    if (nB > 0) M_CUDA(cudaMemcpyAsync(dB, b, (size_t)nB * 32, cudaMemcpyHostToDevice, s));
+    rc = gforb_match_bruteforce_device(m, dA, nA, dB, nB, threshold, o, o + nA, o + 2 * (size_t)nA, o + 3 * (size_t)nA, nullptr);
+    if (rc) return rc;
+    int32_t* outs[4] = {best_idx, best_dist, second_dist, match};
+    for (int i = 0; i < 4; ++i)
+        if (outs[i]) M_CUDA(cudaMemcpyAsync(outs[i], o + (size_t)i * nA, bo, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaStreamSynchronize(s));
+    return GFORB_OK;
+}
+
+int gforb_device_alloc(void** p, size_t bytes) {
+    if (!p) return GFORB_ERR_ARG;
+    M_CUDA(cudaMalloc(p, std::max<size_t>(bytes, 16)));
+    return GFORB_OK;
+}
+void gforb_device_free(void* p) { if (p) cudaFree(p); }
+int gforb_device_copy(void* dst, const void* src, size_t bytes, int dir) {
+    if ((!dst || !src) && bytes) return GFORB_ERR_ARG;
+    M_CUDA(cudaMemcpy(dst, src, bytes, dir == 0 ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost));
+    return GFORB_OK;
 }
 
 // ------------------------------------------------------------------------------------------------- batch

@@ -127,6 +127,13 @@ void launch_blur(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);    
 void launch_describe(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);       // 1 launch
 void launch_stereo(const StereoView& v, const gforb_stereo_params& p, int nframes, int K, cudaStream_t s);  // 1 launch
 void build_fast_cell_table(const Geom& g, std::vector<uint32_t>& tab);
+// brute-force matcher (k_match.cu): 2 launches
+int match_segments(int nA, int nB, int sm_count);
+size_t match_scratch_bytes(int nA, int nseg);
+int match_max_train();
+void launch_match(const uint8_t* dA, int nA, const uint8_t* dB, int nB, float ratio, int threshold, int nseg,
+                  void* scratch, int32_t* best_idx, int32_t* best_dist, int32_t* second_dist, int32_t* match,
+                  cudaStream_t s);
 size_t octree_smem_bytes(const Geom& g);
 int octree_configure(const Geom& g);   // opt in to large dynamic smem; returns cudaError_t as int
 

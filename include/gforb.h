@@ -120,6 +120,33 @@ GFORB_API int gforb_hamming256(const void* a32, const void* b32);   /* host inli
 #define GFORB_TH_HIGH 100   /* ORBmatcher::TH_HIGH, src/ORBmatcher.cc:37 */
 #define GFORB_TH_LOW 50     /* ORBmatcher::TH_LOW,  src/ORBmatcher.cc:38 */
 
+/* Brute-force nearest / second-nearest search over 256-bit descriptors with the reference's acceptance tests
+ * (BASELINE.json configs[3]).  This is the loop every ORBmatcher search runs per query -- best / second-best
+ * update src/ORBmatcher.cc:562-571 (also :183-197, :316-332), then `bestDist <= TH` and
+ * `bestDist < (float)bestDist2 * mfNNratio` (:574-576) -- taken over ALL nB train descriptors.
+ * gforb_matcher mirrors ORBmatcher(float nnratio = 0.6, bool checkOri) (include/ORBmatcher.h:46): it carries
+ * mfNNratio plus the device scratch and stream.  Outputs per query i (any pointer may be NULL):
+ *   best_idx[i]    index of the nearest train descriptor (lowest index among equal distances, as `<` gives; -1 if nB = 0)
+ *   best_dist[i]   its distance (INT32_MAX if nB = 0, the reference's initial value)
+ *   second_dist[i] second smallest distance of the multiset (INT32_MAX if nB < 2)
+ *   match[i]       best_idx[i] if it passes both tests, else -1
+ * nB <= 4,194,304.  Host-pointer and device-pointer (asynchronous, on `cuda_stream` or the matcher's own) forms. */
+typedef struct gforb_matcher gforb_matcher;
+GFORB_API int gforb_matcher_create(float nnratio, gforb_matcher** out);
+GFORB_API void gforb_matcher_destroy(gforb_matcher* m);
+GFORB_API int gforb_match_bruteforce(gforb_matcher* m, const uint8_t* desc_a, int n_a, const uint8_t* desc_b, int n_b,
+                           int threshold, int32_t* best_idx, int32_t* best_dist, int32_t* second_dist, int32_t* match);
+GFORB_API int gforb_match_bruteforce_device(gforb_matcher* m, const uint8_t* dev_desc_a, int n_a, const uint8_t* dev_desc_b,
+                                  int n_b, int threshold, int32_t* dev_best_idx, int32_t* dev_best_dist,
+                                  int32_t* dev_second_dist, int32_t* dev_match, void* cuda_stream);
+/* wait for the last device-form call and return its device time (CUDA events around its two kernels) */
+GFORB_API int gforb_matcher_sync(gforb_matcher* m, float* last_ms_or_null);
+/* device memory helpers for callers without a CUDA runtime of their own (tests, bench): cudaMalloc / cudaFree /
+ * synchronous cudaMemcpy; dir 0 = host->device, 1 = device->host */
+GFORB_API int gforb_device_alloc(void** dev_ptr, size_t bytes);
+GFORB_API void gforb_device_free(void* dev_ptr);
+GFORB_API int gforb_device_copy(void* dst, const void* src, size_t bytes, int dir);
+
 /* =====================================================================================================
  * Frame::ComputeStereoMatches / ComputeStereoMatches_Undistorted
  * (src/Frame.cc:889-1078, :1167-1316, include/Frame.h:230-263)

@@ -1,4 +1,5 @@
 // ORACLE -- TEST INFRASTRUCTURE ONLY.  C ABI + CPU baseline driver over the restatement.
+#include <climits>
 #include <atomic>
 #include <chrono>
 #include <cstring>
@@ -182,6 +183,28 @@ double orc_bench_stereo(const uint8_t* images, int nimg, int w, int h, int nfram
     auto t1 = std::chrono::steady_clock::now();
     if (checksum) *checksum = sum.load();
     return std::chrono::duration<double>(t1 - t0).count();
+}
+
+void orc_match_bruteforce(const uint8_t* a, int nA, const uint8_t* b, int nB, float ratio, int threshold,
+                          int* best_idx, int* best_dist, int* second_dist, int* match, int nthreads) {
+    auto run = [&](int q0, int q1) {
+        for (int i = q0; i < q1; ++i) {
+            int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx = -1;   // src/ORBmatcher.cc:544-546
+            for (int j = 0; j < nB; ++j) {
+                const int dist = orc_hamming256(a + (size_t)i * 32, b + (size_t)j * 32);
+                if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx = j; }
+                else if (dist < bestDist2) bestDist2 = dist;
+            }
+            if (best_idx) best_idx[i] = bestIdx;
+            if (best_dist) best_dist[i] = bestDist;
+            if (second_dist) second_dist[i] = bestDist2;
+            if (match) match[i] = (bestIdx >= 0 && bestDist <= threshold && bestDist < (float)bestDist2 * ratio) ? bestIdx : -1;
+        }
+    };
+    if (nthreads <= 1) { run(0, nA); return; }
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nthreads; ++t) pool.emplace_back(run, (int)((long long)nA * t / nthreads), (int)((long long)nA * (t + 1) / nthreads));
+    for (auto& t : pool) t.join();
 }
 
 }  // extern "C"

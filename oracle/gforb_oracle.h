@@ -66,6 +66,13 @@ double orc_bench_stereo(const uint8_t* images, int nimg, int w, int h, int nfram
                         int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh,
                         float bf, float b, int do_match, long long* checksum);
 
+/* Brute-force nearest / second-nearest search exactly as the reference's matcher loops write it
+ * (src/ORBmatcher.cc:562-576): bestDist = bestDist2 = INT_MAX; for j in order: dist < bestDist -> shift,
+ * else dist < bestDist2 -> second; accepted when bestDist <= threshold && bestDist < (float)bestDist2 * ratio.
+ * Outputs as include/gforb.h gforb_match_bruteforce.  nthreads splits the QUERIES (results independent). */
+void  orc_match_bruteforce(const uint8_t* a, int nA, const uint8_t* b, int nB, float ratio, int threshold,
+                           int* best_idx, int* best_dist, int* second_dist, int* match, int nthreads);
+
 #ifdef __cplusplus
 }
 #endif

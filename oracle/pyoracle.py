@@ -82,6 +82,8 @@ def lib():
                                    C.c_int, C.c_float, C.c_int, C.c_int, C.c_int,
                                    C.c_float, C.c_float, C.c_int, C.POINTER(C.c_longlong)]
     L.orc_bench_stereo.restype = C.c_double
+    L.orc_match_bruteforce.argtypes = [u8p, C.c_int, u8p, C.c_int, C.c_float, C.c_int, ip, ip, ip, ip, C.c_int]
+    L.orc_match_bruteforce.restype = None
     _LIB = L
     return L
 
@@ -242,3 +244,13 @@ def bench_stereo(images, nframes, nthreads, shape=0, nfeatures=1000, scale_facto
     secs = lib().orc_bench_stereo(_p(images), n, w, h, nframes, nthreads, shape, nfeatures, scale_factor,
                                   nlevels, ini_th, min_th, bf, b, int(do_match), C.byref(chk))
     return secs, chk.value
+
+
+def match_bruteforce(desc_a, desc_b, ratio=0.6, threshold=50, nthreads=1):
+    """The reference's best / second-best loop + acceptance tests (src/ORBmatcher.cc:562-576) over all of desc_b."""
+    a = np.ascontiguousarray(desc_a, np.uint8).reshape(-1, 32); b = np.ascontiguousarray(desc_b, np.uint8).reshape(-1, 32)
+    n = max(len(a), 1)
+    bi = np.empty(n, np.int32); bd = np.empty(n, np.int32); sd = np.empty(n, np.int32); m = np.empty(n, np.int32)
+    lib().orc_match_bruteforce(_p(a), len(a), _p(b), len(b), ratio, threshold, _p(bi), _p(bd), _p(sd), _p(m), nthreads)
+    k = len(a)
+    return dict(best_idx=bi[:k], best_dist=bd[:k], second_dist=sd[:k], match=m[:k])

@@ -96,3 +96,19 @@ def test_fast_random_noise(t):
     # equal-score plateaus: strict NMS must drop both neighbours
     im = np.full((20, 20), 100, np.uint8); im[8:12, 8:12] = 200
     assert np.array_equal(O.fast9(im, t), _cvfast(im, t))
+
+
+def test_match_bruteforce_oracle_vs_numpy():
+    """pins the oracle's restatement of the matcher loop (src/ORBmatcher.cc:562-576) against an independent numpy
+    formulation: nearest = argmin (first index), second = second smallest of the multiset, then both tests"""
+    rng = np.random.default_rng(11)
+    for n, m, ratio, th in [(300, 400, 0.6, 50), (50, 1, 0.9, 100), (64, 200, 0.75, 80)]:
+        a = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+        b = a[rng.integers(0, n, m)] ^ np.packbits(rng.random((m, 256)) < 0.1, axis=1)
+        r = O.match_bruteforce(a, b, ratio, th, nthreads=3)
+        d = np.unpackbits(a[:, None, :] ^ b[None, :, :], axis=2).sum(2).astype(np.int64)
+        best = d.min(1); idx = d.argmin(1)
+        second = np.sort(d, 1)[:, 1] if m > 1 else np.full(n, np.iinfo(np.int32).max)
+        ok = (best <= th) & (best.astype(np.float32) < second.astype(np.float32) * np.float32(ratio))
+        assert np.array_equal(r["best_idx"], idx) and np.array_equal(r["best_dist"], best)
+        assert np.array_equal(r["second_dist"], second) and np.array_equal(r["match"], np.where(ok, idx, -1))
