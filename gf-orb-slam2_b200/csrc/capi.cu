@@ -511,7 +511,7 @@ int enqueue_frames(gforb_batch* b, int f0, int n, const gforb_stereo_params* prm
     const int n_cap = b->max_frames;
     int rc = E.run_extract(2 * n, s, timing ? b->ev : nullptr, 2 * f0);
     if (rc) return rc;
-    b->last_launches += E.g.nlevels + 4;
+    b->last_launches += extract_launches(E.g);
     if (timing && !prm) cudaEventRecord(b->ev[6], s);
     if (prm) {
         const size_t K = (size_t)E.g.K;
@@ -566,7 +566,7 @@ int gforb_batch_stage_times(gforb_batch* b, float* ms6) {
 
 int gforb_batch_launches_per_run(const gforb_batch* b, int with_stereo) {
     if (!b) return GFORB_ERR_ARG;
-    return b->eng.g.nlevels /* pyramid */ + 4 /* fast, quadtree, blur, describe */ + (with_stereo ? 1 : 0);
+    return extract_launches(b->eng.g) + (with_stereo ? 1 : 0);
 }
 int gforb_batch_last_launches(const gforb_batch* b) { return b ? b->last_launches : GFORB_ERR_ARG; }
 

@@ -84,6 +84,36 @@ void axis_table(int slen, int dlen, std::vector<int32_t>& out) {
         out.push_back((int32_t)(((uint32_t)w1 << 16) | ((uint32_t)w0 & 0xFFFFu)));
     }
 }
+
+// 4-pixel-group table of the fast resize kernel (k_pyramid.cu): per group of 4 adjacent output pixels
+// {aligned source byte offset wb, PRMT selector for pixels 0-1 out of source words (w0,w1), two selectors for
+// pixels 2-3 out of (w0,w1) then w2, 4 x packed weights}.  Returns false when a group's taps do not fit the
+// 12-byte window (scale factors above ~2.3): that level then runs the generic kernel.
+bool group_table(const std::vector<int32_t>& tabs, int tab_x, int dlen, std::vector<int32_t>& out) {
+    const int ng = (dlen + 3) / 4;
+    for (int gi = 0; gi < ng; ++gi) {
+        int sx[4], cf[4];
+        for (int k = 0; k < 4; ++k) {
+            const int x = std::min(4 * gi + k, dlen - 1);
+            sx[k] = tabs[tab_x + 2 * x];
+            cf[k] = tabs[tab_x + 2 * x + 1];
+            if ((cf[k] & 0xFFFF) > 2048 || ((uint32_t)cf[k] >> 16) > 2048) return false;   // weights must be plain u16
+        }
+        const int wb = sx[0] & ~3;
+        const int o[4] = {sx[0] - wb, sx[1] - wb, sx[2] - wb, sx[3] - wb};
+        if (o[1] < o[0] || o[1] + 1 > 7 || o[2] < 0 || o[3] < o[2] || o[3] + 1 > 11) return false;
+        const uint32_t selA = (uint32_t)o[0] | ((uint32_t)(o[0] + 1) << 4) | ((uint32_t)o[1] << 8) | ((uint32_t)(o[1] + 1) << 12);
+        const int q[4] = {o[2], o[2] + 1, o[3], o[3] + 1};
+        uint32_t s1 = 0, s2 = 0;
+        for (int i = 0; i < 4; ++i) {
+            s1 |= (uint32_t)(q[i] <= 7 ? q[i] : 0) << (4 * i);
+            s2 |= (uint32_t)(q[i] <= 7 ? i : 4 + (q[i] - 8)) << (4 * i);
+        }
+        out.push_back(wb); out.push_back((int32_t)selA); out.push_back((int32_t)s1); out.push_back((int32_t)s2);
+        for (int k = 0; k < 4; ++k) out.push_back(cf[k]);
+    }
+    return true;
+}
 }  // namespace
 
 int make_geometry(const Tables& t, const gforb_limits& lim, int W, int H, int nimg, Geom& g,
@@ -154,6 +184,27 @@ int make_geometry(const Tables& t, const gforb_limits& lim, int W, int H, int ni
                         cv_round(sx) == 2 && cv_round(sy) == 2) ? 1 : 0;
             L.tab_x = (int)tabs.size(); axis_table(P.w, L.w, tabs);
             L.tab_y = (int)tabs.size(); axis_table(P.h, L.h, tabs);
+            while (tabs.size() % 4) tabs.push_back(0);           // group entries are read as 2 x uint4
+            std::vector<int32_t> grp;
+            L.tab_g = -1;
+            if (!L.area2x && group_table(tabs, L.tab_x, L.w, grp)) {
+                L.tab_g = (int)tabs.size();
+                tabs.insert(tabs.end(), grp.begin(), grp.end());
+                // TMA box of the source level that covers any 128-pixel x 32-row output tile
+                const int ng = (L.w + 3) / 4;
+                int bw = 0, bh = 0;
+                for (int bx = 0; bx * 32 < ng; ++bx) {
+                    const int g0 = std::min(bx * 32, std::max(ng - 32, 0));     // last warp column is shifted left
+                    const int gl = std::min(g0 + 31, ng - 1);
+                    const int xb = grp[8 * g0] & ~15;
+                    bw = std::max(bw, (int)align_up((size_t)(grp[8 * gl] + 12 - xb), 16));
+                }
+                for (int y0 = 0; y0 < L.h; y0 += 32) {
+                    const int yl = std::min(y0 + 31, L.h - 1);
+                    bh = std::max(bh, tabs[L.tab_y + 2 * yl] + 2 - tabs[L.tab_y + 2 * y0]);
+                }
+                if (bw <= 256 && bh <= 256) { L.rs_bw = bw; L.rs_bh = bh; }
+            }
         }
     }
     g.cells_total = cell_base;
@@ -215,7 +266,9 @@ int Engine::init(const Tables& t, const gforb_limits& lim, int W, int H, int nim
     const size_t K = (size_t)g.K, NI = (size_t)nimg, NF = (size_t)std::max(nframes_stereo, 1);
 
     GFORB_CUDA(cudaMalloc(&b.in, NI * W * H));
+    pyr_bytes += 64;    // the right frame word of a row may run 2 bytes past the pitch (into row padding)
     GFORB_CUDA(cudaMalloc(&b.pyr, pyr_bytes));
+    GFORB_CUDA(cudaMemset(b.pyr, 0, pyr_bytes));     // alignment bytes outside the 19-px frame are never written
     GFORB_CUDA(cudaMalloc(&b.blur, blur_bytes));
     GFORB_CUDA(cudaMalloc(&b.tabs, std::max<size_t>(tabs.size(), 2) * 4));
     GFORB_CUDA(cudaMalloc(&b.cell_cnt, NI * g.cells_total * 4));
@@ -266,6 +319,18 @@ int Engine::init(const Tables& t, const gforb_limits& lim, int W, int H, int nim
             return GFORB_ERR_CUDA;
         }
     }
+    for (int l = 1; l < g.nlevels; ++l) {
+        const LevelGeom& L = g.lv[l];
+        const LevelGeom& P = g.lv[l - 1];
+        if (!L.rs_bw) continue;
+        const int rcu = encode_tile_map_u8(&rsmaps[l], b.pyr + P.off, (uint64_t)P.pitch, (uint64_t)P.rows,
+                                           (uint64_t)nimg, (uint32_t)L.rs_bw, (uint32_t)L.rs_bh);
+        if (rcu != 0) {
+            release();
+            set_error("gforb: cuTensorMapEncodeTiled(resize) failed (" + std::to_string(rcu) + ")");
+            return GFORB_ERR_CUDA;
+        }
+    }
     ready = true;
     return GFORB_OK;
 }
@@ -294,7 +359,7 @@ int Engine::upload_images(const uint8_t* host, size_t pitch, int first_img, int 
 
 int Engine::run_pyramid(int nimg, cudaStream_t s) {
     g.img0 = 0;
-    launch_pyramid(g, b, nimg, s);
+    launch_pyramid(g, b, nimg, s, rsmaps);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "pyramid launch");
     pyramid_valid = true;
@@ -304,7 +369,7 @@ int Engine::run_pyramid(int nimg, cudaStream_t s) {
 int Engine::run_extract(int nimg, cudaStream_t s, cudaEvent_t* ev, int img0) {
     g.img0 = img0;   // Geom travels by value as a kernel parameter
     if (ev) cudaEventRecord(ev[0], s);
-    launch_pyramid(g, b, nimg, s);
+    launch_pyramid(g, b, nimg, s, rsmaps);
     if (ev) cudaEventRecord(ev[1], s);
     launch_fast(g, maps, b, nimg, s);
     if (ev) cudaEventRecord(ev[2], s);

@@ -43,6 +43,7 @@ public:
 
     Geom g{};
     TileMaps maps{};
+    CUtensorMap rsmaps[kMaxLevels]{};   // resize source tiles (k_pyramid.cu)
     Buffers b{};
     int nframes_cap = 0;
     bool ready = false;

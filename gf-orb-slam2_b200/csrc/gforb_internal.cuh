@@ -39,6 +39,8 @@ struct LevelGeom {
     // resize tables (level >= 1): offsets into the table arena (ints)
     int tab_x, tab_y;         // start of {ofs, coef01} pairs for x (w entries) and y (h entries)
     int area2x;               // cv::resize's exact-2x INTER_AREA shortcut applies
+    int tab_g;                // start of the 4-pixel-group table (8 ints per group, k_pyramid.cu), -1: generic kernel only
+    int rs_bw, rs_bh;         // resize kernel: TMA box over the SOURCE level (bytes x rows) per 128x32 output tile; 0: no TMA
     int btile_base, btiles_x; // blur kernel: first tile index of this level, tiles per row
     int fast_bw, fast_bh;     // FAST kernel: TMA box (bytes x rows) = shared tile pitch / height for this level
 };
@@ -120,7 +122,10 @@ struct StereoView {
 enum ErrBits { kErrCandOverflow = 1, kErrCellOverflow = 2, kErrNodeOverflow = 4, kErrKpOverflow = 8 };
 
 // ---- kernel launchers (each enqueues on `s`; defined in the per-stage .cu files) ----
-void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);   // images [g.img0, g.img0+nimg)
+// images [g.img0, g.img0+nimg); rsmaps[l] = TMA map of level l-1 with level l's resize box (null: no TMA path)
+void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s, const CUtensorMap* rsmaps = nullptr);
+// kernels one extraction enqueues: nlevels pyramid + fast, quadtree, blur, describe
+inline int extract_launches(const Geom& g) { return g.nlevels + 4; }
 void launch_fast(const Geom& g, const TileMaps& m, const Buffers& b, int nimg, cudaStream_t s);   // 1 launch
 void launch_octree(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);         // 1 launch
 void launch_blur(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);           // 1 launch

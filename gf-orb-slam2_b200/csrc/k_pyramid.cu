@@ -10,6 +10,7 @@
 // of 64 and the ROI starts 32 bytes into the row, so stores are aligned and coalesced.  HBM-bound:
 // algorithmic bytes per image = W*H read + sum_l (w_l+38)(h_l+38) written.
 #include "gforb_internal.cuh"
+#include "tma.cuh"
 
 namespace gforb {
 
@@ -86,17 +87,237 @@ pyr_resize_kernel(const uint8_t* __restrict__ src_roi, int spitch, size_t simg_s
     *reinterpret_cast<uint32_t*>(out + (size_t)img * img_stride + (size_t)py * pitch + px4) = word;
 }
 
-void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s) {
+
+// ------------------------------------------------------------------------------------------------
+// Fast path (v2).  A thread owns 4 horizontally adjacent ROI pixels (one aligned 32-bit word) and walks down
+// kRowsPerThread rows; a warp owns 32 adjacent groups.  The frame is not computed: frame pixel == ROI pixel at
+// the REFLECT_101 coordinate (copyMakeBorder after resize, src/ORBextractor.cc:1189-1197), so
+//  * every word is also stored at its mirror rows inside the top/bottom frame;
+//  * the warp that holds the left edge builds the five frame words left of the ROI from its own words
+//    (SHFL.DOWN + PRMT), the warp that holds the right edge builds the frame words right of it (SHFL.UP + PRMT);
+//    the last warp column is shifted left to start at group ng-32, so the right edge never straddles two warps
+//    (the overlap recomputes identical words).
+// Every store is an aligned 32-bit word; interior warps run no edge code at all.
+namespace {
+constexpr int kRowsPerThread = 8;
+
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {   // selector nibbles <= 7 only
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+    return d;
+}
+
+struct RowStore {
+    uint8_t* p;            // this thread's word on ROI row 0
+    int pitch, h;
+    int loff, roff;        // byte offset of the left / right frame word this thread writes, relative to p
+    uint32_t sel_main, sel_r;
+    bool valid, lon, ron;  // thread owns ROI pixels / writes a left / right frame word
+    bool ledge, redge;     // warp-uniform: warp holds the left / right ROI edge
+    bool yedge;            // warp-uniform: strip touches the top or bottom frame
+
+    // gx = group index (may be >= ng: idle lane kept alive for the shuffles), g0 = first group of the warp
+    __device__ __forceinline__ void init(uint8_t* lvl, int pitch_, int gx, int g0, int w, int h_, int y0, int y1) {
+        const int ng = (w + 3) >> 2, X = gx * 4, q = 2 * (w - 1);
+        pitch = pitch_; h = h_;
+        p = lvl + (size_t)kEdge * pitch_ + kXPad + X;
+        valid = gx < ng;
+        ledge = g0 == 0;
+        redge = g0 + 32 >= ng;
+        yedge = y0 <= kEdge || y1 - 1 >= h - 1 - kEdge;
+        // left: group j in 0..4 writes columns [-4(j+1), -4j-1] = pixels 4(j+1), 4j+3, 4j+2, 4j+1
+        lon = ledge && gx < 5;
+        loff = -(8 * gx + 4);
+        // right: group gx writes frame word d = (q >> 2) - gx = pixels 4gx+e-i (i = 0..3), e = q & 3, from (prev, own)
+        const int d = (q >> 2) - gx;
+        ron = redge && valid && 4 * d >= w && 4 * d <= w + kEdge - 1;
+        roff = 4 * d - X;
+        sel_r = (q & 3) ? 0x3456u : 0x1234u;
+        // the last group when w % 4 != 0: its word runs into the frame; those bytes take their mirrored pixels
+        sel_main = 0x7654u;
+        if (valid && X + 3 >= w) {
+            sel_main = 0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int c = X + i;
+                sel_main |= (uint32_t)(c < w ? 4 + i : q - c - (X - 4)) << (4 * i);
+            }
+        }
+    }
+    __device__ __forceinline__ void rows(int y, uint32_t m, uint32_t lw, uint32_t rw) const {
+        uint8_t* r = p + (ptrdiff_t)y * pitch;
+        if (valid) *reinterpret_cast<uint32_t*>(r) = m;
+        if (lon) *reinterpret_cast<uint32_t*>(r + loff) = lw;
+        if (ron) *reinterpret_cast<uint32_t*>(r + roff) = rw;
+    }
+    // all 32 lanes of the warp must call this together (shuffles)
+    __device__ __forceinline__ void store(int y, uint32_t own) const {
+        uint32_t m = own, lw = 0, rw = 0;
+        if (ledge) lw = prmt(own, __shfl_down_sync(0xffffffffu, own, 1), 0x1234u);
+        if (redge) {
+            const uint32_t prev = __shfl_up_sync(0xffffffffu, own, 1);
+            m = prmt(prev, own, sel_main);
+            rw = prmt(prev, own, sel_r);
+        }
+        rows(y, m, lw, rw);
+        if (yedge) {
+            if (y >= 1 && y <= kEdge) rows(-y, m, lw, rw);
+            if (y >= h - 1 - kEdge && y <= h - 2) rows(2 * (h - 1) - y, m, lw, rw);
+        }
+    }
+};
+}  // namespace
+
+// level 0: input (tight, W % 4 == 0) -> padded level; thread = 4 pixels x kRowsPerThread rows
+__global__ void __launch_bounds__(128)
+pyr_level0_fast_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int W, int H, int pitch,
+                       size_t img_stride, int img0) {
+    const int img = img0 + blockIdx.z;
+    const int ng = W >> 2;
+    const int g0 = min((int)blockIdx.x * 32, max(ng - 32, 0));
+    const int gx = g0 + threadIdx.x;
+    const int y0 = (blockIdx.y * 4 + threadIdx.y) * kRowsPerThread;
+    if (y0 >= H) return;
+    const int y1 = min(y0 + kRowsPerThread, H);
+    const uint8_t* src = in + (size_t)img * W * H + 4 * min(gx, ng - 1);
+    RowStore st;
+    st.init(out + (size_t)img * img_stride, pitch, gx, g0, W, H, y0, y1);
+    uint32_t v[kRowsPerThread];
+#pragma unroll
+    for (int r = 0; r < kRowsPerThread; ++r)
+        v[r] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)min(y0 + r, H - 1) * W));
+#pragma unroll
+    for (int r = 0; r < kRowsPerThread; ++r)
+        if (y0 + r < y1) st.store(y0 + r, v[r]);
+}
+
+__device__ __forceinline__ void lds3(uint32_t addr, uint32_t& a, uint32_t& b, uint32_t& c) {
+    asm volatile("ld.shared.u32 %0, [%3];\n\tld.shared.u32 %1, [%3+4];\n\tld.shared.u32 %2, [%3+8];"
+                 : "=r"(a), "=r"(b), "=r"(c) : "r"(addr));
+}
+__device__ __forceinline__ void resize_hrow(uint32_t w0, uint32_t w1, uint32_t w2, const uint4& sel,
+                                            const uint32_t (&cf)[4], uint32_t (&s)[4]) {
+    const uint32_t A = prmt(w0, w1, sel.y);
+    const uint32_t B = prmt(prmt(w0, w1, sel.z), w2, sel.w);
+    s[0] = __dp2a_lo(cf[0], A, 0u) >> 4;
+    s[1] = __dp2a_hi(cf[1], A, 0u) >> 4;
+    s[2] = __dp2a_lo(cf[2], B, 0u) >> 4;
+    s[3] = __dp2a_hi(cf[3], B, 0u) >> 4;
+}
+
+// level l >= 1 (not the exact-2x case): cv::resize INTER_LINEAR 8U, thread = 4 pixels x kRowsPerThread rows,
+// CTA = 128 pixels x 32 rows.  kTma: the source rows/columns the tile needs arrive as ONE TMA box
+// (cp.async.bulk.tensor.3d of the padded source level) on an mbarrier; the row table entries are fetched while it
+// is in flight.  Consecutive output rows share source rows (scale 1.2: the lower tap row of y is usually the
+// upper tap row of y+1), so a source row's horizontal pass is reused when the row table says so.  Weights are in
+// [0, 2048], so every intermediate is non-negative: (b * s) >> 16 is one IMAD.HI with b pre-shifted by 16, and
+// the saturating cast of cv::resize can never clip.
+template <bool kTma>
+__global__ void __launch_bounds__(128)
+pyr_resize_fast_kernel(const __grid_constant__ CUtensorMap smap, const uint8_t* __restrict__ src_roi, int spitch,
+                       size_t simg_stride, uint8_t* __restrict__ out, int w, int h, int pitch, size_t img_stride,
+                       const uint4* __restrict__ tab_g, const int2* __restrict__ tab_y, int bw, int bh, int img0) {
+    extern __shared__ __align__(128) uint8_t tile[];
+    __shared__ __align__(8) uint64_t bar;
+    const int img = img0 + blockIdx.z;
+    const int ng = (w + 3) >> 2;
+    const int g0 = min((int)blockIdx.x * 32, max(ng - 32, 0));
+    const int gx = g0 + threadIdx.x;
+    const int ty0 = blockIdx.y * 32;
+    const int y0 = ty0 + threadIdx.y * kRowsPerThread;
+    int xb = 0, sy0 = 0;
+    if (kTma) {
+        xb = (int)__ldg(tab_g + 2 * g0).x & ~15;     // tile's first source byte, 16-byte aligned (TMA rule)
+        sy0 = __ldg(tab_y + ty0).x;
+        if (threadIdx.x == 0 && threadIdx.y == 0) {
+            mbar_init(&bar, 1);
+            mbar_expect_tx(&bar, (uint32_t)(bw * bh));
+            tma_load_tile_3d(tile, &smap, kXPad + xb, kEdge + sy0, img, &bar);
+        }
+        __syncthreads();     // barrier initialised before anyone polls it
+    }
+    if (y0 >= h) return;     // whole warps only: idle lanes (gx >= ng) stay for the edge shuffles
+    const int y1 = min(y0 + kRowsPerThread, h);
+    const int gc = min(gx, ng - 1);
+    const uint4 ga = __ldg(tab_g + 2 * gc), gb = __ldg(tab_g + 2 * gc + 1);
+    const uint32_t cf[4] = {gb.x, gb.y, gb.z, gb.w};
+    int2 ty[kRowsPerThread];
+#pragma unroll
+    for (int r = 0; r < kRowsPerThread; ++r) ty[r] = __ldg(tab_y + min(y0 + r, h - 1));
+    RowStore st;
+    st.init(out + (size_t)img * img_stride, pitch, gx, g0, w, h, y0, y1);
+    const uint8_t* s = src_roi + (size_t)img * simg_stride + ga.x;          // !kTma: global source
+    const uint32_t sa = smem_u32(tile) + (uint32_t)((int)ga.x - xb);        // kTma: shared byte address of this group
+    if (kTma) mbar_wait(&bar, 0);
+
+    uint32_t s0[4], s1[4] = {0u, 0u, 0u, 0u};
+    int have = -1;
+#pragma unroll
+    for (int r = 0; r < kRowsPerThread; ++r) {
+        const int y = y0 + r;
+        if (y < y1) {
+            const int sy = ty[r].x;
+            const uint32_t b0 = (uint32_t)ty[r].y << 16, b1 = (uint32_t)ty[r].y & 0xFFFF0000u;
+            uint32_t w0, w1, w2;
+            if (sy == have) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) s0[k] = s1[k];
+            } else {
+                if (kTma) lds3(sa + (uint32_t)((sy - sy0) * bw), w0, w1, w2);
+                else {
+                    const uint32_t* p0 = reinterpret_cast<const uint32_t*>(s + (size_t)sy * spitch);
+                    w0 = __ldg(p0); w1 = __ldg(p0 + 1); w2 = __ldg(p0 + 2);
+                }
+                resize_hrow(w0, w1, w2, ga, cf, s0);
+            }
+            if (kTma) lds3(sa + (uint32_t)((sy + 1 - sy0) * bw), w0, w1, w2);
+            else {
+                const uint32_t* p1 = reinterpret_cast<const uint32_t*>(s + (size_t)(sy + 1) * spitch);
+                w0 = __ldg(p1); w1 = __ldg(p1 + 1); w2 = __ldg(p1 + 2);
+            }
+            resize_hrow(w0, w1, w2, ga, cf, s1);
+            have = sy + 1;
+            uint32_t t[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) t[k] = __umulhi(b0, s0[k]) + __umulhi(b1, s1[k]) + 2u;   // <= 1022
+            // (t >> 2) of pixels k, k+1 land in bytes 0 and 2 of ((t[k+1] << 16) | t[k]) >> 2
+            const uint32_t u01 = (t[1] * 65536u + t[0]) >> 2, u23 = (t[3] * 65536u + t[2]) >> 2;
+            st.store(y, prmt(u01, u23, 0x6420));
+        }
+    }
+}
+
+void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s, const CUtensorMap* rsmaps) {
     const dim3 blk(32, 8);
+    const dim3 fblk(32, 4);
     {
         const LevelGeom& L = g.lv[0];
-        dim3 grd((L.pitch / 4 + blk.x - 1) / blk.x, (L.rows + blk.y - 1) / blk.y, nimg);
-        pyr_level0_kernel<<<grd, blk, 0, s>>>(b.in, b.pyr + L.off, g.W, g.H, L.pitch, L.rows, L.img_stride, g.img0);
+        if (g.W % 4 == 0) {
+            dim3 grd((g.W / 4 + 31) / 32, (g.H + 4 * kRowsPerThread - 1) / (4 * kRowsPerThread), nimg);
+            pyr_level0_fast_kernel<<<grd, fblk, 0, s>>>(b.in, b.pyr + L.off, g.W, g.H, L.pitch, L.img_stride, g.img0);
+        } else {
+            dim3 grd((L.pitch / 4 + blk.x - 1) / blk.x, (L.rows + blk.y - 1) / blk.y, nimg);
+            pyr_level0_kernel<<<grd, blk, 0, s>>>(b.in, b.pyr + L.off, g.W, g.H, L.pitch, L.rows, L.img_stride, g.img0);
+        }
     }
     for (int l = 1; l < g.nlevels; ++l) {
         const LevelGeom& P = g.lv[l - 1];
         const LevelGeom& L = g.lv[l];
         const uint8_t* src_roi = b.pyr + P.off + (size_t)kEdge * P.pitch + kXPad;
+        if (L.tab_g >= 0) {
+            dim3 grd(((L.w + 3) / 4 + 31) / 32, (L.h + 4 * kRowsPerThread - 1) / (4 * kRowsPerThread), nimg);
+            const uint4* tg = reinterpret_cast<const uint4*>(b.tabs + L.tab_g);
+            const int2* ty = reinterpret_cast<const int2*>(b.tabs + L.tab_y);
+            if (rsmaps && L.rs_bw)
+                pyr_resize_fast_kernel<true><<<grd, fblk, (size_t)L.rs_bw * L.rs_bh, s>>>(
+                    rsmaps[l], src_roi, P.pitch, P.img_stride, b.pyr + L.off, L.w, L.h, L.pitch, L.img_stride, tg, ty,
+                    L.rs_bw, L.rs_bh, g.img0);
+            else
+                pyr_resize_fast_kernel<false><<<grd, fblk, 0, s>>>(
+                    CUtensorMap{}, src_roi, P.pitch, P.img_stride, b.pyr + L.off, L.w, L.h, L.pitch, L.img_stride, tg, ty,
+                    0, 0, g.img0);
+            continue;
+        }
         dim3 grd((L.pitch / 4 + blk.x - 1) / blk.x, (L.rows + blk.y - 1) / blk.y, nimg);
         pyr_resize_kernel<<<grd, blk, 0, s>>>(src_roi, P.pitch, P.img_stride, b.pyr + L.off, L.w, L.h, L.pitch,
                                               L.rows, L.img_stride,

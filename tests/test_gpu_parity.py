@@ -50,6 +50,18 @@ def test_pyramid_bit_exact(gf, O, fixtures, name):
         assert np.array_equal(ex.pyramid_level(l, with_border=True), ox.level(l, padded=True)), f"level {l} frame"
 
 
+def test_pyramid_sizes_and_scales(gf, O):
+    """fast 4-pixel-group resize path, exact-2x path, generic fallback (odd widths, scale > 2.3), incl. the frame"""
+    rng = np.random.default_rng(5)
+    for (w, h), (scale, nl) in [((640, 480), (1.2, 8)), ((333, 259), (1.2, 6)), ((752, 480), (1.5, 5)), ((404, 300), (1.9, 3)),
+                                ((752, 480), (2.0, 3)), ((756, 484), (2.5, 3)), ((1280, 720), (1.2, 8)), ((84, 90), (1.1, 4))]:
+        im = rng.integers(0, 256, (h, w), dtype=np.uint8)
+        ex = gf.ORBextractor(500, scale, nl, 20, 7); ox = O.Extractor(500, scale, nl, 20, 7)
+        ex.ComputePyramid(im); ox.compute_pyramid(im)
+        for l in range(nl):
+            assert np.array_equal(ex.pyramid_level(l, with_border=True), ox.level(l, padded=True)), (w, h, scale, l)
+
+
 @pytest.mark.parametrize("name", NAMES)
 def test_fast_candidates_bit_exact(gf, O, fixtures, golden, name):
     im = fixtures[name]
