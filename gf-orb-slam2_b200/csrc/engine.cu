@@ -308,6 +308,7 @@ int Engine::init(const Tables& t, const gforb_limits& lim, int W, int H, int nim
         return GFORB_ERR_ARG;
     }
     GFORB_CUDA((cudaError_t)octree_configure(g));
+    GFORB_CUDA((cudaError_t)fast_configure(g));
     // TMA descriptors: one per level for the FAST cell tiles
     for (int l = 0; l < g.nlevels; ++l) {
         const LevelGeom& L = g.lv[l];

@@ -140,6 +140,7 @@ void launch_match(const uint8_t* dA, int nA, const uint8_t* dB, int nB, float ra
                   void* scratch, int32_t* best_idx, int32_t* best_dist, int32_t* second_dist, int32_t* match,
                   cudaStream_t s);
 size_t octree_smem_bytes(const Geom& g);
+int fast_configure(const Geom& g);     // opt in to the FAST kernel's dynamic smem; returns cudaError_t as int
 int octree_configure(const Geom& g);   // opt in to large dynamic smem; returns cudaError_t as int
 
 void upload_constants();   // pattern + umax to __constant__ (once per process/device)

@@ -82,114 +82,116 @@ __device__ __forceinline__ uint32_t gt_lanes2(uint32_t a, uint32_t b, uint32_t k
 }  // namespace
 
 struct FastArgs {
-    int img0, cells_total, cell_cap, t_ini, t_min;
+    int img0, nimg, cells_total, cell_cap, t_ini, t_min;
+    int tile_bytes, list_cap;      // per-warp shared layout: [tile][score map][row bitmaps][list]
     const uint4* cell_tab;
     uint32_t* cell_cnt; uint32_t* cell_pts; int32_t* err;
 };
 
-__global__ void __launch_bounds__(kThreads)
-fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
-    __shared__ __align__(128) uint8_t tile[kTileRows * kMaxTP];
-    __shared__ __align__(16) uint8_t sc[kTileRows * kMaxTP + 32];   // corner scores, same coordinates as `tile`
-    __shared__ uint16_t list[kMaxDomain + 3];          // (row << 8) | tile column of pixels passing the prefilter
-    __shared__ unsigned long long keep_lo[64], keep_hi[64];
-    __shared__ int row_base[64];
-    __shared__ __align__(8) uint64_t bar;
-    __shared__ int s_any_hi, s_nlist;
+namespace {
+constexpr int kWarpsPerCta = 4;
+constexpr int kBitmapBytes = 64 * 2 * 4 * 2;     // keep@min and keep@ini, 64 rows x 2 x 32 bits each
+__host__ __device__ inline int warp_smem_bytes(int tile_bytes, int list_cap) {
+    return 2 * tile_bytes + 128 + kBitmapBytes + ((list_cap * 2 + 127) & ~127);
+}
+// per-byte "x != 0" for words whose bytes have bit 0 clear: bit 7 of each lane
+__device__ __forceinline__ uint32_t nz_lanes(uint32_t x) { return (x >> 1) + 0x7f7f7f7fu; }
+}  // namespace
 
-    const int img = a.img0 + blockIdx.y;
-    const size_t out_cell = (size_t)img * a.cells_total + blockIdx.x;
-    const uint4 ca = __ldg(a.cell_tab + 2 * blockIdx.x), cb = __ldg(a.cell_tab + 2 * blockIdx.x + 1);
+// One WARP per (image, cell): no block barriers, no block-wide atomics; the four warps of a CTA are independent.
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ __align__(8) uint64_t bars[kWarpsPerCta];
+
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const long long gcell = (long long)blockIdx.x * kWarpsPerCta + wid;      // (image, cell) pair
+    if (gcell >= (long long)a.nimg * a.cells_total) return;
+    const int iimg = (int)(gcell / a.cells_total), cell = (int)(gcell - (long long)iimg * a.cells_total);
+    const int img = a.img0 + iimg;
+    const size_t out_cell = (size_t)img * a.cells_total + cell;
+    const uint4 ca = __ldg(a.cell_tab + 2 * cell), cb = __ldg(a.cell_tab + 2 * cell + 1);
     const int cw = (ca.y >> 8) & 0xFF, ch = (ca.y >> 16) & 0xFF;
     if (cw == 0) {                                      // cell skipped by the reference (:796,805) or degenerate
-        if (threadIdx.x == 0) a.cell_cnt[out_cell] = 0;
+        if (lane == 0) a.cell_cnt[out_cell] = 0;
         return;
     }
-    const int xoff = ca.y & 0xFF, l = ca.y >> 24;
-    const int tp = ca.w & 0xFF, th = (ca.w >> 8) & 0xFF, R = (ca.w >> 16) & 0xFF, nw = ca.w >> 24;
-    const int dw = cw - 6, dh = ch - 6;                 // FAST domain: rows/cols 3 .. dim-4 of the cell image
-    const int lane = threadIdx.x & 31;
+    uint8_t* wbase = smem + (size_t)wid * warp_smem_bytes(a.tile_bytes, a.list_cap);
+    uint8_t* tile = wbase;
+    uint8_t* sc = wbase + a.tile_bytes;                                   // corner scores, same coordinates as `tile`
+    uint32_t* keep_lo = reinterpret_cast<uint32_t*>(sc + a.tile_bytes + 128);   // [row][2]
+    uint32_t* keep_hi = keep_lo + 128;
+    uint16_t* list = reinterpret_cast<uint16_t*>(keep_hi + 128);          // (row << 8) | tile column
+    uint64_t* bar = &bars[wid];
 
-    if (threadIdx.x == 0) {
-        mbar_init(&bar, 1);
-        s_any_hi = 0; s_nlist = 0;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        mbar_expect_tx(&bar, (uint32_t)(tp * th));
-        tma_load_tile_3d(tile, &maps.fast[l], (int)(ca.x & 0xFFFF), (int)(ca.x >> 16), img, &bar);
+    const int xoff = ca.y & 0xFF, l = ca.y >> 24;
+    const int tp = ca.w & 0xFF, th = (ca.w >> 8) & 0xFF, nw = ca.w >> 24;
+    const int dw = cw - 6, dh = ch - 6;                 // FAST domain: rows/cols 3 .. dim-4 of the cell image
+
+    if (lane == 0) {
+        mbar_init(bar, 1);
+        mbar_expect_tx(bar, (uint32_t)(tp * th));
+        tma_load_tile_3d(tile, &maps.fast[l], (int)(ca.x & 0xFFFF), (int)(ca.x >> 16), img, bar);
     }
     // while the tile is in flight: clear the score rows NMS will touch and the row bitmaps
     {
         const int n16 = (ch * tp + 31) >> 4;
-        for (int i = threadIdx.x; i < n16; i += kThreads) reinterpret_cast<uint4*>(sc)[i] = make_uint4(0, 0, 0, 0);
-        if (threadIdx.x < 64) { keep_lo[threadIdx.x] = 0; keep_hi[threadIdx.x] = 0; }
+        for (int i = lane; i < n16; i += 32) reinterpret_cast<uint4*>(sc)[i] = make_uint4(0, 0, 0, 0);
+        reinterpret_cast<uint4*>(keep_lo)[lane] = make_uint4(0, 0, 0, 0);
+        reinterpret_cast<uint4*>(keep_hi)[lane] = make_uint4(0, 0, 0, 0);
     }
     const int t_ini = min(max(a.t_ini, 0), 255), t_min = min(max(a.t_min, 0), 255);
     const int tlo = min(t_ini, t_min);
-    const uint32_t kadd = (uint32_t)(0x7f - min(tlo, 126)) * 0x01010101u;   // a lower prefilter threshold stays a superset
+    // prefilter threshold: the largest 2^k - 1 <= tlo (a lower threshold stays a superset); |d| > 2^k - 1 <=> d & ~(2^k - 1) != 0,
+    // and (|d1| | |d2|) & mask != 0 <=> either exceeds it -- exact for the default tlo = 7
+    const uint32_t pmask = (~(uint32_t)((1 << (31 - __clz(min(tlo, 127) + 1))) - 1) & 0xFFu) * 0x01010101u;
     const int tpw = tp >> 2;
     const int xlo = xoff + 3, xhi = xlo + dw;           // domain columns [xlo, xhi) in tile bytes
     const int w0 = xlo >> 2;
-    const int items = (int)cb.y, rcp = (int)cb.x;       // items = strips x nw; rcp = ceil(65536 / nw)
+    const int nitems = dh * nw;                         // item = one 32-bit word of a domain row
+    const int qs = (int)(cb.y & 0xFF), rs = (int)(cb.y >> 8);         // 32 = qs * nw + rs
+    int ir = (lane * (int)cb.x) >> 16, iw = lane - ir * nw;           // cb.x = ceil(65536 / nw): lane -> (row, word)
+    const uint32_t cm_first = 0xFFFFFFFFu << (8 * (xlo & 3));
+    const uint32_t cm_last = 0xFFFFFFFFu >> (8 * (3 - ((xhi - 1) & 3)));
+    const uint32_t lt = (1u << lane) - 1u;
+    __syncwarp();                                       // barrier init + clears visible to the whole warp
+    mbar_wait(bar, 0);
 
-    mbar_wait(&bar, 0);
-
-    // ---- pass 1: 4-pixel prefilter + compaction ----
-    const uint32_t* tw = reinterpret_cast<const uint32_t*>(tile);
-    for (int i0 = 0; i0 < items; i0 += kThreads) {
-        const int i = i0 + threadIdx.x;
-        uint32_t F = 0;                                 // bit 8k + (8 - R) + r  <->  pixel k of the word, strip row r
-        int s = 0, w = 0;
-        if (i < items) {
-            s = (i * rcp) >> 16; w = i - s * nw;
-            const int row0 = 3 + s * R;
-            const uint32_t* p = tw + row0 * tpw + w0 + w;
-            for (int r = 0; r < R; ++r, p += tpw) {
-                uint32_t f = 0;
-                if (row0 + r < 3 + dh) {
-                    const uint32_t C = p[0], Wm = p[-1], Wp = p[1], U = p[-3 * tpw], D = p[3 * tpw];
-                    const uint32_t Lw = __funnelshift_r(Wm, C, 8), Rw = __funnelshift_r(C, Wp, 24);
-                    const uint32_t v = gt_lanes2(__vabsdiffu4(C, U), __vabsdiffu4(C, D), kadd);
-                    const uint32_t h = gt_lanes2(__vabsdiffu4(C, Lw), __vabsdiffu4(C, Rw), kadd);
-                    f = v & h & 0x80808080u;
-                }
-                F = (F >> 1) | f;
+    // ---- pass 1: 4-pixel prefilter, 32 words per step, ballot compaction (list order is irrelevant) ----
+    const uint32_t* tw = reinterpret_cast<const uint32_t*>(tile) + 3 * tpw + w0;
+    int nlist = 0;
+    for (int i0 = 0; i0 < nitems; i0 += 32) {
+        uint32_t f = 0;
+        if (i0 + lane < nitems) {
+            if (tlo == 0) f = 0x80808080u;              // "> 0" has no cleared-low-bit form: list the whole domain
+            else {
+                const uint32_t* p = tw + ir * tpw + iw;
+                const uint32_t C = p[0], Wm = p[-1], Wp = p[1], U = p[-3 * tpw], D = p[3 * tpw];
+                const uint32_t Lw = __funnelshift_r(Wm, C, 8), Rw = __funnelshift_r(C, Wp, 24);
+                const uint32_t v = (__vabsdiffu4(C, U) | __vabsdiffu4(C, D)) & pmask;
+                const uint32_t h = (__vabsdiffu4(C, Lw) | __vabsdiffu4(C, Rw)) & pmask;
+                f = nz_lanes(v) & nz_lanes(h) & 0x80808080u;
             }
             // columns outside [xlo, xhi) (first / last word of the row)
-            const int x0 = (w0 + w) << 2;
-            uint32_t cm = 0xFFFFFFFFu;
-            if (x0 < xlo) cm <<= 8 * (xlo - x0);
-            if (x0 + 4 > xhi) cm &= 0xFFFFFFFFu >> (8 * (x0 + 4 - xhi));
-            F &= cm;
+            if (iw == 0) f &= cm_first;
+            if (iw == nw - 1) f &= cm_last;
         }
-        const int c = __popc(F);
-        int inc = c;
+        if (__any_sync(0xffffffffu, f != 0)) {
+            const uint32_t e = (uint32_t)(((3 + ir) << 8) | ((w0 + iw) << 2));
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += t;
-        }
-        const int tot = __shfl_sync(0xffffffffu, inc, 31);
-        if (tot) {
-            int base = 0;
-            if (lane == 31) base = atomicAdd(&s_nlist, tot);
-            base = __shfl_sync(0xffffffffu, base, 31);
-            uint16_t* out = list + base + inc - c;
-            // entry = (row << 8) | column with row = 3 + s*R + r, r = (bit & 7) - (8 - R), column = x0 + (bit >> 3)
-            const int ebase = ((3 + s * R - (8 - R)) << 8) | ((w0 + w) << 2);
-            while (F) {
-                const int bit = 31 - __clz(F);
-                F ^= 1u << bit;
-                *out++ = (uint16_t)(ebase + ((bit & 7) << 8) + (bit >> 3));
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t m = __ballot_sync(0xffffffffu, f & (0x80u << (8 * k)));
+                if (f & (0x80u << (8 * k))) list[nlist + __popc(m & lt)] = (uint16_t)(e + k);
+                nlist += __popc(m);
             }
         }
+        iw += rs; ir += qs;
+        if (iw >= nw) { iw -= nw; ++ir; }
     }
-    __syncthreads();
-    const int nlist = s_nlist;
+    __syncwarp();
 
     // ---- pass 2: exact corner strength of the listed pixels ----
-    for (int k = threadIdx.x; k < nlist; k += kThreads) {
+    for (int k = lane; k < nlist; k += 32) {
         const int e = list[k];
         const int off = (e >> 8) * tp + (e & 0xFF);
         const uint8_t* c = tile + off;
@@ -197,69 +199,76 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
         const int m = fast_arc_strength(rows, c[0]);
         if (m > tlo) sc[off] = (uint8_t)(m - 1);
     }
-    __syncthreads();
+    __syncwarp();
 
     // ---- pass 3: strict 3x3 NMS on the score map (zero outside the domain), again only over the list ----
-    for (int k = threadIdx.x; k < nlist; k += kThreads) {
+    bool hi = false;
+    for (int k = lane; k < nlist; k += 32) {
         const int e = list[k];
         const int py = e >> 8, px = e & 0xFF;
         const uint8_t* q = sc + py * tp + px;
         const int s = q[0];
-        if (s == 0) continue;
-        const bool keep = s > q[-1] && s > q[1] && s > q[-tp - 1] && s > q[-tp] && s > q[-tp + 1] &&
-                          s > q[tp - 1] && s > q[tp] && s > q[tp + 1];
-        if (!keep) continue;
-        const unsigned long long bit = 1ull << (px - xlo);
-        atomicOr(&keep_lo[py - 3], bit);
-        if (s >= t_ini) { atomicOr(&keep_hi[py - 3], bit); s_any_hi = 1; }
+        const int n0 = max(max(q[-tp - 1], q[-tp]), q[-tp + 1]), n1 = max(q[-1], q[1]);
+        const int n2 = max(max(q[tp - 1], q[tp]), q[tp + 1]);
+        if (s > max(max(n0, n1), n2)) {                 // s > 0 implied: neighbours are >= 0
+            const int bx = px - xlo;
+            const int wi = 2 * (py - 3) + (bx >> 5);
+            const uint32_t bit = 1u << (bx & 31);
+            atomicOr(&keep_lo[wi], bit);
+            if (s >= t_ini) { atomicOr(&keep_hi[wi], bit); hi = true; }
+        }
     }
-    __syncthreads();
-
     // keep@ini if it found anything, else keep@min (s >= t_min filter applies when t_min > tlo)
-    const bool use_hi = s_any_hi != 0;
-    if (threadIdx.x < 64) {
-        unsigned long long m = 0;
-        if ((int)threadIdx.x < dh) {
-            m = use_hi ? keep_hi[threadIdx.x] : keep_lo[threadIdx.x];
-            if (!use_hi && t_min > tlo) {   // iniTh < minTh configuration: retry threshold is the higher one
-                unsigned long long f = 0;
-                for (unsigned long long r = m; r; r &= r - 1) {
-                    const int bx = __ffsll((long long)r) - 1;
-                    if (sc[(threadIdx.x + 3) * tp + bx + xlo] >= t_min) f |= 1ull << bx;
-                }
-                m = f;
+    const bool use_hi = __any_sync(0xffffffffu, hi);
+    __syncwarp();
+    unsigned long long m0 = 0, m1 = 0;                  // rows lane and lane + 32
+    {
+        const uint32_t* km = use_hi ? keep_hi : keep_lo;
+        if (lane < dh) m0 = (unsigned long long)km[2 * lane] | ((unsigned long long)km[2 * lane + 1] << 32);
+        if (lane + 32 < dh) m1 = (unsigned long long)km[2 * lane + 64] | ((unsigned long long)km[2 * lane + 65] << 32);
+        if (!use_hi && t_min > tlo) {                   // iniTh < minTh configuration: retry threshold is the higher one
+            unsigned long long f0 = 0, f1 = 0;
+            for (unsigned long long r = m0; r; r &= r - 1) {
+                const int bx = __ffsll((long long)r) - 1;
+                if (sc[(lane + 3) * tp + bx + xlo] >= t_min) f0 |= 1ull << bx;
             }
+            for (unsigned long long r = m1; r; r &= r - 1) {
+                const int bx = __ffsll((long long)r) - 1;
+                if (sc[(lane + 35) * tp + bx + xlo] >= t_min) f1 |= 1ull << bx;
+            }
+            m0 = f0; m1 = f1;
         }
-        keep_lo[threadIdx.x] = m;
-        row_base[threadIdx.x] = __popcll(m);
     }
-    __syncthreads();
-    if (threadIdx.x < 32) {
-        // exclusive scan of the <= 59 row counts by one warp
-        const int c0 = row_base[lane], c1 = row_base[lane + 32];
-        int i0 = c0, i1 = c1;
+    // exclusive scan of the <= 59 row counts
+    const int c0 = __popcll(m0), c1 = __popcll(m1);
+    int i0 = c0, i1 = c1;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t0 = __shfl_up_sync(0xffffffffu, i0, o), t1 = __shfl_up_sync(0xffffffffu, i1, o);
-            if (lane >= o) { i0 += t0; i1 += t1; }
-        }
-        const int tot0 = __shfl_sync(0xffffffffu, i0, 31), tot1 = __shfl_sync(0xffffffffu, i1, 31);
-        row_base[lane] = i0 - c0;
-        row_base[lane + 32] = tot0 + i1 - c1;
-        if (lane == 0) {
-            int total = tot0 + tot1;
-            if (total > a.cell_cap) { atomicOr(a.err, kErrCellOverflow); total = 0; }
-            a.cell_cnt[out_cell] = (uint32_t)total;
-            s_nlist = total;
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t0 = __shfl_up_sync(0xffffffffu, i0, o), t1 = __shfl_up_sync(0xffffffffu, i1, o);
+        if (lane >= o) { i0 += t0; i1 += t1; }
+    }
+    const int tot0 = __shfl_sync(0xffffffffu, i0, 31), tot1 = __shfl_sync(0xffffffffu, i1, 31);
+    int total = tot0 + tot1;
+    if (total > a.cell_cap) {
+        if (lane == 0) atomicOr(a.err, kErrCellOverflow);
+        total = 0;
+    }
+    if (lane == 0) a.cell_cnt[out_cell] = (uint32_t)total;
+    if (total == 0) return;
+    const int ox = (int)(ca.z & 0xFFFF), oy = (int)(ca.z >> 16);          // j*wCell, i*hCell (:824-825)
+    uint32_t* out0 = a.cell_pts + out_cell * (size_t)a.cell_cap;
+    {
+        uint32_t* out = out0 + (i0 - c0);
+        const int yy = lane + 3;
+        for (unsigned long long r = m0; r; r &= r - 1) {
+            const int bx = __ffsll((long long)r) - 1;
+            *out++ = pack_cand(ox + bx + 3, oy + yy, sc[yy * tp + bx + xlo]);
         }
     }
-    __syncthreads();
-    if (s_nlist == 0) return;
-    if ((int)threadIdx.x < dh) {
-        uint32_t* out = a.cell_pts + out_cell * (size_t)a.cell_cap + row_base[threadIdx.x];
-        const int yy = threadIdx.x + 3;
-        const int ox = (int)(ca.z & 0xFFFF), oy = (int)(ca.z >> 16);      // j*wCell, i*hCell (:824-825)
-        for (unsigned long long r = keep_lo[threadIdx.x]; r; r &= r - 1) {
+    if (c1) {
+        uint32_t* out = out0 + tot0 + (i1 - c1);
+        const int yy = lane + 35;
+        for (unsigned long long r = m1; r; r &= r - 1) {
             const int bx = __ffsll((long long)r) - 1;
             *out++ = pack_cand(ox + bx + 3, oy + yy, sc[yy * tp + bx + xlo]);
         }
@@ -282,26 +291,48 @@ void build_fast_cell_table(const Geom& g, std::vector<uint32_t>& tab) {
             if (iniY >= L.maxBY - 3 || iniX >= L.maxBX - 6 || dw <= 0 || dh <= 0) continue;   // cw = 0: skipped
             const int gx = kXPad + iniX, xoff = gx & 15;
             const int xlo = xoff + 3, xhi = xlo + dw;
-            const int nw = ((xhi - 1) >> 2) - (xlo >> 2) + 1;
-            const int R = std::min(std::max((dh * nw + kThreads - 1) / kThreads, 1), 8);
-            const int strips = (dh + R - 1) / R;
+            const int nw = ((xhi - 1) >> 2) - (xlo >> 2) + 1;           // <= 16 word columns
+            const int R = 0;     // (unused since the warp-per-cell kernel)
             e[0] = (uint32_t)(gx - xoff) | ((uint32_t)(kEdge + iniY) << 16);
             e[1] = (uint32_t)xoff | ((uint32_t)cw << 8) | ((uint32_t)ch << 16) | ((uint32_t)l << 24);
             e[2] = (uint32_t)(cj * L.wCell) | ((uint32_t)(ci * L.hCell) << 16);
             e[3] = (uint32_t)L.fast_bw | ((uint32_t)L.fast_bh << 8) | ((uint32_t)R << 16) | ((uint32_t)nw << 24);
             e[4] = (uint32_t)((65536 + nw - 1) / nw);
-            e[5] = (uint32_t)(strips * nw);
+            e[5] = (uint32_t)(32 / nw) | ((uint32_t)(32 % nw) << 8);
         }
     }
 }
 
+namespace {
+void fast_smem_layout(const Geom& g, int& tile_bytes, int& list_cap) {
+    tile_bytes = 128; list_cap = 64;
+    for (int l = 0; l < g.nlevels; ++l) {
+        const LevelGeom& L = g.lv[l];
+        if (L.ncells == 0) continue;
+        tile_bytes = std::max(tile_bytes, (L.fast_bw * L.fast_bh + 127) & ~127);
+        list_cap = std::max(list_cap, L.wCell * L.hCell);
+    }
+}
+}  // namespace
+
+int fast_configure(const Geom& g) {
+    int tb, lc;
+    fast_smem_layout(g, tb, lc);
+    return (int)cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     kWarpsPerCta * warp_smem_bytes(tb, lc));
+}
+
 void launch_fast(const Geom& g, const TileMaps& m, const Buffers& b, int nimg, cudaStream_t s) {
     FastArgs a;
-    a.img0 = g.img0; a.cells_total = g.cells_total; a.cell_cap = g.cell_cap; a.t_ini = g.ini_th; a.t_min = g.min_th;
+    a.img0 = g.img0; a.nimg = nimg; a.cells_total = g.cells_total; a.cell_cap = g.cell_cap;
+    a.t_ini = g.ini_th; a.t_min = g.min_th;
+    fast_smem_layout(g, a.tile_bytes, a.list_cap);
     a.cell_tab = reinterpret_cast<const uint4*>(b.cell_tab);
     a.cell_cnt = b.cell_cnt; a.cell_pts = b.cell_pts; a.err = b.err;
-    dim3 grd(g.cells_total, nimg);
-    fast_cells_kernel<<<grd, kThreads, 0, s>>>(a, m);
+    const long long ncell = (long long)nimg * g.cells_total;
+    if (ncell == 0) return;
+    const unsigned grd = (unsigned)((ncell + kWarpsPerCta - 1) / kWarpsPerCta);
+    fast_cells_kernel<<<grd, kWarpsPerCta * 32, (size_t)kWarpsPerCta * warp_smem_bytes(a.tile_bytes, a.list_cap), s>>>(a, m);
 }
 
 }  // namespace gforb
