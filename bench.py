@@ -298,7 +298,7 @@ def main():
                        "mean_keypoints_per_image": round(n_kp, 1), "fast_candidates_per_image": n_cand},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "gpu_launches": launches_e2e,
-                    "pipeline": "chunks of %s frames: H2D / kernels / D2H of successive chunks overlap (2 copy + 2 kernel streams)" % (args.chunk or "16 (auto)")},
+                    "pipeline": "chunks of %s frames: H2D / kernels / D2H of successive chunks overlap (2 copy + 4 kernel streams)" % (args.chunk or "8,24,32..,16,8 (auto)")},
             "gpu_launches": launches_value,
             "clocks": clocks, "roofline": roofline, "stages": stages}
     if not args.no_cpu_baseline and world == 1:

@@ -328,7 +328,7 @@ class PinnedArray:
 
     def __del__(self):
         p = getattr(self, "_ptr", None)
-        if p:
+        if p and _L is not None:        # _L is None while the interpreter shuts down: the OS reclaims the pages
             self.array = None
             _L.gforb_host_free(p)
             self._ptr = None

@@ -1,5 +1,6 @@
 // C ABI of libgforb.so (declared in include/gforb.h).
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <new>
@@ -42,7 +43,9 @@ struct gforb_batch {
     bool timing = false;
     cudaEvent_t ev[7] = {};
     // chunked end-to-end pipeline (gforb_stereo_frames_batch): H2D, kernels and D2H of successive chunks overlap
-    cudaStream_t s_up = nullptr, s_down = nullptr, s_alt = nullptr;   // s_alt: second kernel stream (odd chunks)
+    cudaStream_t s_up = nullptr, s_down = nullptr;
+    cudaStream_t s_alt[3] = {nullptr, nullptr, nullptr};   // extra kernel streams: chunks rotate over stream + s_alt[]
+    int kstreams = 4;            // kernel streams the chunk pipeline rotates over (1..4); measured best on B200
     std::vector<cudaEvent_t> ev_up, ev_done;
     cudaEvent_t ev_start = nullptr, ev_down = nullptr;
     int chunk_frames = 0;        // 0 = automatic
@@ -56,7 +59,7 @@ struct gforb_batch {
         eng.release();
         if (s_up) cudaStreamDestroy(s_up);
         if (s_down) cudaStreamDestroy(s_down);
-        if (s_alt) cudaStreamDestroy(s_alt);
+        for (auto& sa : s_alt) if (sa) cudaStreamDestroy(sa);
         if (own) cudaStreamDestroy(own);
     }
 };
@@ -472,6 +475,7 @@ int gforb_batch_create(const gforb_params* p, const gforb_limits* lim, int w, in
     if (rc) return rc;
     b->stream = b->own;
     b->max_frames = max_frames;
+    if (const char* ks = std::getenv("GFORB_KSTREAMS")) b->kstreams = std::min(std::max(std::atoi(ks), 1), 4);   // tuning knob
     rc = b->eng.init(b->tab, b->lim, w, h, 2 * max_frames, max_frames);
     if (rc) return rc;
     *out = b.release();
@@ -602,15 +606,29 @@ int gforb_stereo_frames_batch(gforb_batch* b, const uint8_t* left, const uint8_t
                               const gforb_stereo_params* prm, int32_t* counts, gforb_keypoint* kps,
                               uint8_t* desc, float* u_right, float* depth) {
     if (!b || !left || !right || n < 1 || n > b->max_frames) { set_error("gforb_stereo_frames_batch: bad arguments"); return GFORB_ERR_ARG; }
-    int chunk = b->chunk_frames > 0 ? b->chunk_frames : (n >= 48 ? 16 : n);
-    chunk = std::min(chunk, n);
-    const int nchunks = (n + chunk - 1) / chunk;
+    // chunk schedule: fixed size when the caller set one; otherwise a short first chunk (the pipeline fills after
+    // 8 frames' worth of H2D), 32-frame chunks in the middle, and a short tail (its kernels + D2H are exposed)
+    std::vector<int> csz;
+    if (b->chunk_frames > 0 || n < 64) {
+        const int chunk = std::min(b->chunk_frames > 0 ? b->chunk_frames : (n >= 48 ? 16 : n), n);
+        for (int f = 0; f < n; f += chunk) csz.push_back(std::min(chunk, n - f));
+    } else {
+        csz.push_back(8); csz.push_back(24);
+        int mid = n - 56;
+        for (; mid >= 32; mid -= 32) csz.push_back(32);
+        if (mid > 0) csz.push_back(mid);
+        csz.push_back(16); csz.push_back(8);
+    }
+    const int nchunks = (int)csz.size();
+    std::vector<int> cf0(nchunks, 0);
+    for (int c = 1; c < nchunks; ++c) cf0[c] = cf0[c - 1] + csz[c - 1];
     Engine& E = b->eng;
     cudaError_t e;
 #define GB(call, what) do { e = (call); if (e != cudaSuccess) return cuda_fail(e, what); } while (0)
     if (!b->s_up) GB(cudaStreamCreateWithFlags(&b->s_up, cudaStreamNonBlocking), "cudaStreamCreate(upload)");
     if (!b->s_down) GB(cudaStreamCreateWithFlags(&b->s_down, cudaStreamNonBlocking), "cudaStreamCreate(download)");
-    if (!b->s_alt) GB(cudaStreamCreateWithFlags(&b->s_alt, cudaStreamNonBlocking), "cudaStreamCreate(kernels 2)");
+    for (auto& sa : b->s_alt)
+        if (!sa) GB(cudaStreamCreateWithFlags(&sa, cudaStreamNonBlocking), "cudaStreamCreate(kernels)");
     if (!b->ev_start) GB(cudaEventCreateWithFlags(&b->ev_start, cudaEventDisableTiming), "cudaEventCreate");
     if (!b->ev_down) GB(cudaEventCreateWithFlags(&b->ev_down, cudaEventDisableTiming), "cudaEventCreate");
     while ((int)b->ev_up.size() < nchunks) {
@@ -626,9 +644,9 @@ int gforb_stereo_frames_batch(gforb_batch* b, const uint8_t* left, const uint8_t
     GB(cudaEventRecord(b->ev_start, b->stream), "cudaEventRecord");
     GB(cudaStreamWaitEvent(b->s_up, b->ev_start, 0), "cudaStreamWaitEvent");
     GB(cudaStreamWaitEvent(b->s_down, b->ev_start, 0), "cudaStreamWaitEvent");
-    GB(cudaStreamWaitEvent(b->s_alt, b->ev_start, 0), "cudaStreamWaitEvent");
+    for (auto& sa : b->s_alt) GB(cudaStreamWaitEvent(sa, b->ev_start, 0), "cudaStreamWaitEvent");
     for (int c = 0; c < nchunks; ++c) {
-        const int f0 = c * chunk, m = std::min(chunk, n - f0);
+        const int f0 = cf0[c], m = csz[c];
         GB(cudaMemcpy2DAsync(E.b.in + isz * (2 * (size_t)f0), 2 * isz, left + isz * f0, isz, isz, m,
                              cudaMemcpyHostToDevice, b->s_up), "cudaMemcpy2DAsync(left)");
         GB(cudaMemcpy2DAsync(E.b.in + isz * (2 * (size_t)f0 + 1), 2 * isz, right + isz * f0, isz, isz, m,
@@ -636,10 +654,11 @@ int gforb_stereo_frames_batch(gforb_batch* b, const uint8_t* left, const uint8_t
         GB(cudaEventRecord(b->ev_up[c], b->s_up), "cudaEventRecord");
     }
     for (int c = 0; c < nchunks; ++c) {
-        const int f0 = c * chunk, m = std::min(chunk, n - f0);
+        const int f0 = cf0[c], m = csz[c];
         // even chunks on the batch's stream, odd chunks on a second one: the tail of one chunk's low-occupancy
         // kernels (quadtree, stereo) is filled by the next chunk's streaming kernels
-        cudaStream_t sk = (c & 1) ? b->s_alt : b->stream;
+        const int ks = c % b->kstreams;
+        cudaStream_t sk = ks ? b->s_alt[ks - 1] : b->stream;
         GB(cudaStreamWaitEvent(sk, b->ev_up[c], 0), "cudaStreamWaitEvent");
         int rc = enqueue_frames(b, f0, m, prm, sk, false);
         if (rc) return rc;
