@@ -63,37 +63,45 @@ describe_kernel(const Geom g, const uint8_t* __restrict__ pyr, const uint8_t* __
     const int slot = blockIdx.x * kWarps + (threadIdx.x >> 5);
     if (slot >= g.kstage) return;
 
-    int l = 0;
-    while (l + 1 < g.nlevels && slot >= g.lv[l + 1].kbase) ++l;
+    // level of this staging slot and the keypoint counts, one level per lane (no serial search)
+    const bool lv_ok = lane < g.nlevels;
+    const int l = __popc(__ballot_sync(0xffffffffu, lv_ok && slot >= g.lv[lv_ok ? lane : 0].kbase)) - 1;
+    const int c_l = lv_ok ? lvl_cnt[(size_t)img * g.nlevels + lane] : 0;
+    const int total = __reduce_add_sync(0xffffffffu, c_l);
+    const int before = __reduce_add_sync(0xffffffffu, lane < l ? c_l : 0);
+    const int cnt_l = __shfl_sync(0xffffffffu, c_l, l);
     const LevelGeom& L = g.lv[l];
     const int k = slot - L.kbase;
-    const int32_t* cnt = lvl_cnt + (size_t)img * g.nlevels;
-    int before = 0, total = 0;
-    for (int i = 0; i < g.nlevels; ++i) {
-        const int c = cnt[i];
-        if (i < l) before += c;
-        total += c;
-    }
     if (slot == 0 && lane == 0) nkp[img] = total;
-    if (k >= cnt[l]) return;
+    if (k >= cnt_l) return;
 
     const uint32_t pk = lvl_pts[(size_t)img * g.kstage + slot];
     const int x = cand_x(pk) + kMinBorder, y = cand_y(pk) + kMinBorder;   // pt += minBorder (:845-846)
 
     // ---- intensity centroid over the 749-px disc ----
-    const uint8_t* ctr = pyr + L.off + (size_t)img * L.img_stride + (size_t)(kEdge + y) * L.pitch + kXPad + x;
+    // lane = column u; the disc is symmetric (umax[|u|] is also the last row of column u), so the column's rows are
+    // |v| <= umax[|u|].  All 31 byte loads are issued before any is used (fully unrolled, predicated);
+    // m10 = u * column sum, m01 = sum_v v * (I(+v) - I(-v)): exact int32, order-free.
+    const int pitch = L.pitch;
+    const uint8_t* ctr = pyr + L.off + (size_t)img * L.img_stride + (size_t)(kEdge + y) * pitch + kXPad + x;
     const int u = lane - kHalfPatch;
     int m10 = 0, m01 = 0;
-    if (lane < 31) {
-        const int au = abs(u);
-#pragma unroll 1
-        for (int v = -kHalfPatch; v <= kHalfPatch; ++v) {
-            if (au <= c_umax[abs(v)]) {
-                const int val = __ldg(ctr + (ptrdiff_t)v * L.pitch + u);
-                m10 += u * val;
-                m01 += v * val;
-            }
+    {
+        const int vl = lane < 31 ? c_umax[abs(u)] : -1;
+        const uint8_t* col = ctr + u;
+        int up[kHalfPatch + 1], dn[kHalfPatch + 1];
+#pragma unroll
+        for (int v = 0; v <= kHalfPatch; ++v) {
+            up[v] = v <= vl ? (int)__ldg(col - (ptrdiff_t)v * pitch) : 0;
+            dn[v] = (v >= 1 && v <= vl) ? (int)__ldg(col + (ptrdiff_t)v * pitch) : 0;
         }
+        int sum = up[0];
+#pragma unroll
+        for (int v = 1; v <= kHalfPatch; ++v) {
+            sum += up[v] + dn[v];
+            m01 += v * (dn[v] - up[v]);
+        }
+        m10 = u * sum;
     }
     m10 = __reduce_add_sync(0xffffffffu, m10);
     m01 = __reduce_add_sync(0xffffffffu, m01);
