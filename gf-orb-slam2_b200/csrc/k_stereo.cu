@@ -19,7 +19,7 @@ namespace gforb {
 namespace {
 constexpr int kT = 256;
 constexpr int kSlices = 8;
-struct RKey { short minr, maxr; int octave; float x; };
+struct RKey { short minr, maxr; uint32_t oi; float x; };   // oi = octave << 16 | original index
 
 __device__ __forceinline__ int hamming_u4(const uint4 a0, const uint4 a1, const uint8_t* b) {
     const uint4 b0 = __ldg(reinterpret_cast<const uint4*>(b));
@@ -27,14 +27,70 @@ __device__ __forceinline__ int hamming_u4(const uint4 a0, const uint4 a1, const 
     return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
            __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
+// (PTX vabsdiff.s32.add is emulated with 64-bit arithmetic on sm_100a, ~9 SASS instructions: the SAD uses IABS)
+__device__ __forceinline__ RKey make_rkey(const gforb_keypoint& k, int i, const float* scale, int nRows) {
+    const float r = __fmul_rn(2.0f, scale[k.octave]);
+    float hi = ceilf(__fadd_rn(k.y, r)), lo = floorf(__fsub_rn(k.y, r));
+    hi = fminf(hi, (float)(nRows - 1));   // classic reference indexes unclamped (keys sit >= 19*scale inside)
+    lo = fmaxf(lo, 0.0f);
+    RKey q;
+    q.minr = (short)(int)lo; q.maxr = (short)(int)hi; q.oi = ((uint32_t)k.octave << 16) | (uint32_t)i; q.x = k.x;
+    return q;
+}
+__device__ __forceinline__ int row_bin(float y, int nRows) { return min(max((int)floorf(y), 0), nRows - 1); }
+
+// k-th smallest (0-based) of the non-negative entries of d[0..n) that are < 2^16, by two 256-bin histogram passes.
+// All kT threads call it; hist = 256 ints of shared memory; s_tmp = 2 ints.
+__device__ int select_kth(const int* d, int n, int k, int* hist, int* s_tmp) {
+    int prefix = 0;
+    for (int pass = 0; pass < 2; ++pass) {
+        const int shift = pass ? 0 : 8;
+        hist[threadIdx.x] = 0;
+        __syncthreads();
+        for (int i = threadIdx.x; i < n; i += kT) {
+            const int e = d[i];
+            if (e >= 0 && (pass == 0 || (e >> 8) == prefix)) atomicAdd(&hist[(e >> shift) & 255], 1);
+        }
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            const int lane = threadIdx.x;
+            int loc[8], sum = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { loc[j] = hist[8 * lane + j]; sum += loc[j]; }
+            int inc = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += t;
+            }
+            int run = inc - sum;
+            if (run <= k && k < inc) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    if (run <= k && k < run + loc[j]) { s_tmp[0] = 8 * lane + j; s_tmp[1] = k - run; }
+                    run += loc[j];
+                }
+            }
+        }
+        __syncthreads();
+        prefix = pass ? ((prefix << 8) | s_tmp[0]) : s_tmp[0];
+        k = s_tmp[1];
+        __syncthreads();
+    }
+    return prefix;
+}
 }  // namespace
 
 __global__ void __launch_bounds__(kT)
-stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
+stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K, int band) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
-    RKey* rk = reinterpret_cast<RKey*>(smem_raw);
-    int* s_dist = reinterpret_cast<int*>(smem_raw + sizeof(RKey) * (size_t)K);
-    __shared__ int s_cnt, s_median, s_removed, s_processed, s_last;
+    // [rs: K sorted right keys][binstart: nRows + 1][s_dist: K (aliases rs once the matching is done)]
+    RKey* rs = reinterpret_cast<RKey*>(smem_raw);
+    int* binstart = reinterpret_cast<int*>(smem_raw + sizeof(RKey) * (size_t)K);
+    int* s_dist = reinterpret_cast<int*>(smem_raw);
+    __shared__ int s_hist[256];
+    __shared__ int s_tmp[2];
+    __shared__ int s_cnt, s_removed, s_processed, s_last;
 
     const int f = v.f0 + blockIdx.x, slice = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -54,19 +110,41 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
     const int th_high = prm.th_high, thOrbDist = (prm.th_high + prm.th_low) / 2;
     const int nRows = v.nRows;
 
-    // right keys: row band of radius 2*scale[octave] (:906-916 / Frame.h:246-257)
-    for (int i = threadIdx.x; i < nR; i += kT) {
-        const gforb_keypoint k = kR[i];
-        const float r = __fmul_rn(2.0f, v.scale[k.octave]);
-        float hi = ceilf(__fadd_rn(k.y, r)), lo = floorf(__fsub_rn(k.y, r));
-        hi = fminf(hi, (float)(nRows - 1));   // classic reference indexes unclamped (keys sit >= 19*scale inside)
-        lo = fmaxf(lo, 0.0f);
-        RKey q;
-        q.minr = (short)(int)lo; q.maxr = (short)(int)hi; q.octave = k.octave; q.x = k.x;
-        rk[i] = q;
-    }
+    // ---- right keys sorted by centre row (counting sort): a left key then scans only rows row-band .. row+band.
+    // The reference's per-row candidate table (:906-916 / Frame.h:246-257) holds key i on rows minr..maxr with
+    // |row - y| < 2*scale + 1, so the centre-row window is a superset and the exact gate test below decides.
+    for (int i = threadIdx.x; i <= nRows; i += kT) binstart[i] = 0;
     if (threadIdx.x == 0) { s_cnt = 0; s_removed = 0; s_processed = 0; }
     __syncthreads();
+    for (int i = threadIdx.x; i < nR; i += kT) atomicAdd(&binstart[row_bin(kR[i].y, nRows) + 1], 1);
+    __syncthreads();
+    {   // inclusive scan of binstart[1..nRows] (binstart[0] = 0): contiguous chunk per thread + block scan of chunk sums
+        const int per = (nRows + kT - 1) / kT, b0 = 1 + threadIdx.x * per, b1 = min(b0 + per, nRows + 1);
+        int sum = 0;
+        for (int i = b0; i < b1; ++i) sum += binstart[i];
+        int inc = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_hist[warp] = inc;
+        __syncthreads();
+        int base = 0;
+        for (int w = 0; w < warp; ++w) base += s_hist[w];
+        int run = base + inc - sum;
+        for (int i = b0; i < b1; ++i) { run += binstart[i]; binstart[i] = run; }
+        __syncthreads();
+    }
+    // scatter from the back of each bin: binstart[b + 1] is decremented down to the bin's start, i.e. afterwards
+    // binstart[b + 1] = first slot of bin b  ->  shift the view by one: bin b occupies [bs[b + 1], bs[b + 2])
+    for (int i = threadIdx.x; i < nR; i += kT) {
+        const gforb_keypoint k = kR[i];
+        const int slot = atomicSub(&binstart[row_bin(k.y, nRows) + 1], 1) - 1;
+        rs[slot] = make_rkey(k, i, v.scale, nRows);
+    }
+    __syncthreads();
+    // now bin b = [binstart[b + 1], b + 1 < nRows ? binstart[b + 2] : nR)
 
     const float minZ = prm.b;
     for (int iL = slice + kSlices * warp; iL < nL; iL += kSlices * (kT / 32)) {
@@ -90,13 +168,17 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
             unsigned best = ((unsigned)th_high << 16) | 0xFFFFu;
             bool any_row = false;
             const bool range_ok = classic ? !(maxU < 0) : !(maxU < prm.min_x);
-            for (int iR = lane; iR < nR; iR += 32) {
-                const RKey q = rk[iR];
+            const int blo = max(row - band, 0), bhi = min(row + band, nRows - 1);
+            const int jend = bhi + 1 < nRows ? binstart[bhi + 2] : nR;
+            for (int j = binstart[blo + 1] + lane; j < jend; j += 32) {
+                const RKey q = rs[j];
                 if (row < q.minr || row > q.maxr) continue;
                 any_row = true;
                 if (!range_ok) continue;
-                if (q.octave < levelL - 1 || q.octave > levelL + 1) continue;
+                const int oct = (int)(q.oi >> 16);
+                if (oct < levelL - 1 || oct > levelL + 1) continue;
                 if (q.x >= minU && q.x <= maxU) {
+                    const int iR = (int)(q.oi & 0xFFFFu);
                     const int d = hamming_u4(a0, a1, dR + (size_t)iR * 32);
                     if (d < th_high) best = min(best, ((unsigned)d << 16) | (unsigned)iR);
                 }
@@ -131,19 +213,16 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
                             const uint8_t* pL = v.pyrL[levelL] + (size_t)f * v.frame_stride[levelL] + (ptrdiff_t)cv * pitch + cu;
                             const uint8_t* pR = v.pyrR[levelL] + (size_t)f * v.frame_stride[levelL] + (ptrdiff_t)cv * pitch + cr;
                             const int cL = __ldg(pL);
-                            int acc[11];
+                            int acc[11], dlt[11];      // dlt[s] = (right centre at shift s) - (left centre)
 #pragma unroll
-                            for (int s = 0; s < 11; ++s) acc[s] = 0;
+                            for (int s = 0; s < 11; ++s) { acc[s] = 0; dlt[s] = (int)__ldg(pR + s - 5) - cL; }
                             for (int p = lane; p < 121; p += 32) {
                                 const int dy = p / 11 - 5, dx = p - (dy + 5) * 11 - 5;
-                                const int lv = (int)__ldg(pL + dy * pitch + dx) - cL;
-                                const uint8_t* rrow = pR + dy * pitch + dx;
+                                const int lpx = (int)__ldg(pL + dy * pitch + dx);
+                                const uint8_t* rrow = pR + dy * pitch + dx - 5;
+                                // |(L - cL) - (R - cR_s)| = |L + (cR_s - cL) - R|: IADD3 + IABS + IADD per pixel and shift
 #pragma unroll
-                                for (int s = 0; s < 11; ++s) {
-                                    const int inc = s - 5;
-                                    const int rv = (int)__ldg(rrow + inc) - (int)__ldg(pR + inc);
-                                    acc[s] += abs(lv - rv);
-                                }
+                                for (int s = 0; s < 11; ++s) acc[s] += abs(lpx + dlt[s] - (int)__ldg(rrow + s));
                             }
                             int bestSad = 0x7fffffff, bestInc = 0;
                             float dists[11];
@@ -204,24 +283,12 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
     __syncthreads();
 
     // ---- median cut (:1064-1077 / :1291-1313): drop matches with dist >= 1.5*1.4*median ----
+    // only the value of the (n/2)-th smallest distance matters: radix selection (SAD <= 121*255 < 2^16)
     const int n = s_cnt;
     if (n > 0) {
-        const int m = n / 2;
-        for (int i = threadIdx.x; i < nL; i += kT) {
-            const int d = s_dist[i];
-            if (d < 0) continue;
-            int lt = 0, le = 0;
-            for (int j = 0; j < nL; ++j) {
-                const int e = s_dist[j];
-                if (e < 0) continue;
-                lt += e < d;
-                le += e <= d;
-            }
-            if (lt <= m && m < le) s_median = d;   // every writer holds the same value
-        }
-        __syncthreads();
+        const int median = select_kth(s_dist, nL, n / 2, s_hist, s_tmp);
         const float c = 1.5f * 1.4f;
-        const float thDist = __fmul_rn(c, (float)s_median);
+        const float thDist = __fmul_rn(c, (float)median);
         for (int i = threadIdx.x; i < nL; i += kT) {
             const int d = s_dist[i];
             if (d >= 0 && !((float)d < thDist)) {
@@ -239,13 +306,17 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
 }
 
 void launch_stereo(const StereoView& v, const gforb_stereo_params& p, int nframes, int K, cudaStream_t s) {
-    const size_t smem = (sizeof(RKey) + sizeof(int)) * (size_t)K;
+    const size_t smem = sizeof(RKey) * (size_t)K + sizeof(int) * ((size_t)v.nRows + 2);
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
         cudaFuncSetAttribute(stereo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         configured = smem;
     }
-    stereo_kernel<<<dim3(nframes, kSlices), kT, smem, s>>>(v, p, K);
+    // centre-row window that covers every band: |row - y| < 2*scale + 1  =>  |row - floor(y)| < 2*scale + 2
+    float smax = 1.f;
+    for (int l = 0; l < kMaxLevels; ++l) smax = v.scale[l] > smax ? v.scale[l] : smax;
+    const int band = (int)(2.f * smax) + 3;
+    stereo_kernel<<<dim3(nframes, kSlices), kT, smem, s>>>(v, p, K, band);
 }
 
 }  // namespace gforb
