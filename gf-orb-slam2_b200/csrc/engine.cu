@@ -174,8 +174,11 @@ int make_geometry(const Tables& t, const gforb_limits& lim, int W, int H, int ni
         L.scale = t.scale[l]; L.inv_scale = t.inv_scale[l];
         L.patch_size = (float)(int)(31 * t.scale[l]);    // :839
 
-        L.btile_base = btile; L.btiles_x = (L.w + 127) / 128;      // blur: 128 columns x (4 warps x 32 rows) per CTA
-        btile += L.btiles_x * ((L.h + 127) / 128);
+        // blur: a warp task = 128 columns x one strip; strips are balanced so that none exceeds 56 rows
+        L.btile_base = btile; L.btiles_x = (L.w + 127) / 128;
+        const int nstrips = (L.h + 55) / 56;
+        L.bstrip_rows = (L.h + nstrips - 1) / nstrips;
+        btile += L.btiles_x * nstrips;
 
         if (l > 0) {
             const LevelGeom& P = g.lv[l - 1];

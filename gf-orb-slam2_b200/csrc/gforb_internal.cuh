@@ -41,7 +41,8 @@ struct LevelGeom {
     int area2x;               // cv::resize's exact-2x INTER_AREA shortcut applies
     int tab_g;                // start of the 4-pixel-group table (8 ints per group, k_pyramid.cu), -1: generic kernel only
     int rs_bw, rs_bh;         // resize kernel: TMA box over the SOURCE level (bytes x rows) per 128x32 output tile; 0: no TMA
-    int btile_base, btiles_x; // blur kernel: first tile index of this level, tiles per row
+    int btile_base, btiles_x; // blur kernel: first warp task of this level, 128-column tasks per strip
+    int bstrip_rows;          // blur kernel: output rows per warp task (balanced strips of <= 56 rows)
     int fast_bw, fast_bh;     // FAST kernel: TMA box (bytes x rows) = shared tile pitch / height for this level
 };
 
@@ -57,7 +58,7 @@ struct Geom {
     int ini_th, min_th;
     int max_cand;             // limit: candidates per (image, level) the quadtree kernel holds in smem
     int max_nodes;            // node table capacity of the quadtree kernel
-    int btiles_total;         // blur tiles per image over all levels
+    int btiles_total;         // blur warp tasks per image over all levels
     LevelGeom lv[kMaxLevels];
 };
 
