@@ -249,7 +249,7 @@ Engine::~Engine() { release(); }
 
 void Engine::release() {
     auto fr = [](auto*& p) { if (p) cudaFree(p); p = nullptr; };
-    fr(b.in); fr(b.cell_tab); fr(b.pyr); fr(b.blur); fr(b.tabs); fr(b.cell_cnt); fr(b.cell_pts); fr(b.lvl_cnt); fr(b.lvl_pts);
+    fr(b.in); fr(b.cell_tab); fr(b.pyr); fr(b.blur); fr(b.tabs); fr(b.cell_cnt); fr(b.cell_pts); fr(b.lvl_cnt); fr(b.oct_retry); fr(b.lvl_pts);
     fr(b.kps); fr(b.desc); fr(b.nkp); fr(b.uright); fr(b.depth); fr(b.st_best_dist); fr(b.st_best_idx);
     fr(b.st_sad); fr(b.st_nmatch); fr(b.st_cut); fr(b.st_ticket); fr(b.err);
     if (h_small) cudaFreeHost(h_small);
@@ -283,6 +283,8 @@ int Engine::init(const Tables& t, const gforb_limits& lim, int W, int H, int nim
     }
     GFORB_CUDA(cudaMalloc(&b.cell_pts, NI * g.cells_total * (size_t)g.cell_cap * 4));
     GFORB_CUDA(cudaMalloc(&b.lvl_cnt, NI * g.nlevels * 4));
+    GFORB_CUDA(cudaMalloc(&b.oct_retry, NI * g.nlevels * 4));
+    GFORB_CUDA(cudaMemset(b.oct_retry, 0, NI * g.nlevels * 4));
     GFORB_CUDA(cudaMalloc(&b.lvl_pts, NI * g.kstage * 4));
     GFORB_CUDA(cudaMalloc(&b.kps, NI * K * sizeof(gforb_keypoint)));
     GFORB_CUDA(cudaMalloc(&b.desc, NI * K * 32));

@@ -97,6 +97,7 @@ struct Buffers {
     int32_t* st_nmatch = nullptr;    // nframes
     int32_t* st_cut = nullptr;       // nframes x K
     int32_t* st_ticket = nullptr;    // 2 x nframes (ticket, processed count), zero between launches
+    int32_t* oct_retry = nullptr;    // nimg x nlevels: quadtree pairs to redo with the full working set (k_octree.cu)
     int32_t* err = nullptr;          // [0] = sticky overflow flag bits
 };
 
@@ -125,8 +126,9 @@ enum ErrBits { kErrCandOverflow = 1, kErrCellOverflow = 2, kErrNodeOverflow = 4,
 // ---- kernel launchers (each enqueues on `s`; defined in the per-stage .cu files) ----
 // images [g.img0, g.img0+nimg); rsmaps[l] = TMA map of level l-1 with level l's resize box (null: no TMA path)
 void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s, const CUtensorMap* rsmaps = nullptr);
-// kernels one extraction enqueues: nlevels pyramid + fast, quadtree, blur, describe
-inline int extract_launches(const Geom& g) { return g.nlevels + 4; }
+int octree_small_cap(const Geom& g);
+// kernels one extraction enqueues: nlevels pyramid + fast, quadtree (2 tiers when max_cand exceeds the small cap), blur, describe
+inline int extract_launches(const Geom& g) { return g.nlevels + 4 + (octree_small_cap(g) < g.max_cand ? 1 : 0); }
 void launch_fast(const Geom& g, const TileMaps& m, const Buffers& b, int nimg, cudaStream_t s);   // 1 launch
 void launch_octree(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);         // 1 launch
 void launch_blur(const Geom& g, const Buffers& b, int nimg, cudaStream_t s);           // 1 launch

@@ -108,20 +108,36 @@ __device__ __forceinline__ short4 child_box(short4 bx, int q) {
 }
 }  // namespace
 
-size_t octree_smem_bytes(const Geom& g) {
+namespace {
+size_t smem_bytes_for(int cap, int max_nodes) {
     auto r = [](size_t b) { return (b + 15) & ~(size_t)15; };
-    const size_t mc = (size_t)g.max_cand, nc = (size_t)g.max_nodes;
+    const size_t mc = (size_t)cap, nc = (size_t)max_nodes;
     return r(4 * mc) + r(2 * mc) + 2 * r(8 * nc) + 2 * r(4 * nc) + 2 * r(16 * nc) + 5 * r(4 * nc) + r(nc) + r(160);
 }
+}  // namespace
+
+// Two tiers: every (image, level) first runs with room for kSmallCap candidates (about 44 KB of shared memory: five
+// CTAs per SM instead of two -- the kernel is latency-bound, so residency is throughput); the rare pair that holds
+// more flags itself and is redone by a second launch with the full max_cand working set.
+constexpr int kSmallCap = 4096;
+int octree_small_cap(const Geom& g) { return g.max_cand > kSmallCap ? kSmallCap : g.max_cand; }
+size_t octree_smem_bytes(const Geom& g) { return smem_bytes_for(g.max_cand, g.max_nodes); }
 
 __global__ void __launch_bounds__(kT)
 octree_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_t* __restrict__ cell_pts,
-              int32_t* __restrict__ lvl_cnt, uint32_t* __restrict__ lvl_pts, int32_t* __restrict__ err) {
+              int32_t* __restrict__ lvl_cnt, uint32_t* __restrict__ lvl_pts, int32_t* __restrict__ err,
+              int32_t* __restrict__ retry, int cap, int tier) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int l = blockIdx.x, img = g.img0 + blockIdx.y;
+    int32_t* my_retry = retry + (size_t)img * g.nlevels + l;
+    if (tier == 1) {                      // second tier: only the pairs the first one could not hold
+        if (*my_retry == 0) return;
+        __syncthreads();
+        if (threadIdx.x == 0) *my_retry = 0;
+    }
     const LevelGeom& L = g.lv[l];
     const int NC = g.max_nodes;
-    Smem s = carve(smem_raw, g.max_cand, NC);
+    Smem s = carve(smem_raw, cap, NC);
     __shared__ int sh_n, sh_flag;
 
     // ---- gather this level's FAST survivors in reference order (cell row-major, row-major inside) ----
@@ -136,15 +152,18 @@ octree_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_
         __syncthreads();
         const int tot = block_excl_scan(s.a, kT, s.warp);
         const int at = n + s.a[threadIdx.x];
-        if (n + tot <= g.max_cand)
+        if (n + tot <= cap)
             for (int k = 0; k < mine; ++k) s.pts[at + k] = cpts[(size_t)c * g.cell_cap + k];
         n += tot;
         __syncthreads();
     }
     int32_t* out_cnt = lvl_cnt + (size_t)img * g.nlevels + l;
     uint32_t* out_pts = lvl_pts + (size_t)img * g.kstage + L.kbase;
-    if (n > g.max_cand) {
-        if (threadIdx.x == 0) { atomicOr(err, kErrCandOverflow); *out_cnt = 0; }
+    if (n > cap) {
+        if (threadIdx.x == 0) {
+            if (cap < g.max_cand) *my_retry = 1;          // redo with the full working set (tier 1)
+            else { atomicOr(err, kErrCandOverflow); *out_cnt = 0; }
+        }
         return;
     }
     if (n == 0 || L.nIni <= 0) {
@@ -331,7 +350,12 @@ int octree_configure(const Geom& g) {
 
 void launch_octree(const Geom& g, const Buffers& b, int nimg, cudaStream_t s) {
     dim3 grd(g.nlevels, nimg);
-    octree_kernel<<<grd, kT, octree_smem_bytes(g), s>>>(g, b.cell_cnt, b.cell_pts, b.lvl_cnt, b.lvl_pts, b.err);
+    const int small = octree_small_cap(g);
+    octree_kernel<<<grd, kT, smem_bytes_for(small, g.max_nodes), s>>>(g, b.cell_cnt, b.cell_pts, b.lvl_cnt, b.lvl_pts, b.err,
+                                                                    b.oct_retry, small, 0);
+    if (small < g.max_cand)
+        octree_kernel<<<grd, kT, octree_smem_bytes(g), s>>>(g, b.cell_cnt, b.cell_pts, b.lvl_cnt, b.lvl_pts, b.err,
+                                                           b.oct_retry, g.max_cand, 1);
 }
 
 }  // namespace gforb
