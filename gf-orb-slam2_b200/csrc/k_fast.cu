@@ -83,7 +83,7 @@ __device__ __forceinline__ uint32_t gt_lanes2(uint32_t a, uint32_t b, uint32_t k
 
 struct FastArgs {
     int img0, nimg, cells_total, cell_cap, t_ini, t_min;
-    int tile_bytes, list_cap;      // per-warp shared layout: [tile][score map][row bitmaps][list]
+    int tile_bytes, sc_bytes, plist_bytes, wlist_bytes;   // per-warp shared layout (all multiples of 128), see fast_smem_layout
     const uint4* cell_tab;
     uint32_t* cell_cnt; uint32_t* cell_pts; int32_t* err;
 };
@@ -91,8 +91,12 @@ struct FastArgs {
 namespace {
 constexpr int kWarpsPerCta = 4;
 constexpr int kBitmapBytes = 64 * 2 * 4 * 2;     // keep@min and keep@ini, 64 rows x 2 x 32 bits each
-__host__ __device__ inline int warp_smem_bytes(int tile_bytes, int list_cap) {
-    return 2 * tile_bytes + 128 + kBitmapBytes + ((list_cap * 2 + 127) & ~127);
+// Per-warp shared layout: [tile][score map][row bitmaps 1 KB][pixel list][word list].  The score map covers the FAST
+// domain plus a one-pixel zero ring ((dh + 2) rows of align4(dw + 2) bytes), not the whole tile.  The word list is
+// dead before the row bitmaps are first used, so it lives in the bitmaps' 1 KB when it fits (wlist_bytes = 0; true
+// for every level of a 752x480 pyramid); only very large cells get a region of their own.
+__host__ __device__ inline int warp_smem_bytes(int tile_bytes, int sc_bytes, int plist_bytes, int wlist_bytes) {
+    return tile_bytes + sc_bytes + kBitmapBytes + plist_bytes + wlist_bytes;
 }
 // per-byte "x != 0" for words whose bytes have bit 0 clear: bit 7 of each lane
 __device__ __forceinline__ uint32_t nz_lanes(uint32_t x) { return (x >> 1) + 0x7f7f7f7fu; }
@@ -116,12 +120,13 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
         if (lane == 0) a.cell_cnt[out_cell] = 0;
         return;
     }
-    uint8_t* wbase = smem + (size_t)wid * warp_smem_bytes(a.tile_bytes, a.list_cap);
+    uint8_t* wbase = smem + (size_t)wid * warp_smem_bytes(a.tile_bytes, a.sc_bytes, a.plist_bytes, a.wlist_bytes);
     uint8_t* tile = wbase;
-    uint8_t* sc = wbase + a.tile_bytes;                                   // corner scores, same coordinates as `tile`
-    uint32_t* keep_lo = reinterpret_cast<uint32_t*>(sc + a.tile_bytes + 128);   // [row][2]
+    uint8_t* sc = wbase + a.tile_bytes;                                   // corner scores: domain + 1-px zero ring, pitch sp
+    uint32_t* keep_lo = reinterpret_cast<uint32_t*>(sc + a.sc_bytes);     // [row][2]
     uint32_t* keep_hi = keep_lo + 128;
     uint16_t* list = reinterpret_cast<uint16_t*>(keep_hi + 128);          // (row << 8) | tile column
+    uint16_t* wlist = a.wlist_bytes ? list + a.plist_bytes / 2 : reinterpret_cast<uint16_t*>(keep_lo);
     uint64_t* bar = &bars[wid];
 
     const int xoff = ca.y & 0xFF, l = ca.y >> 24;
@@ -133,12 +138,11 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
         mbar_expect_tx(bar, (uint32_t)(tp * th));
         tma_load_tile_3d(tile, &maps.fast[l], (int)(ca.x & 0xFFFF), (int)(ca.x >> 16), img, bar);
     }
-    // while the tile is in flight: clear the score rows NMS will touch and the row bitmaps
+    // while the tile is in flight: clear the score map (domain + zero ring)
+    const int sp = (dw + 2 + 3) & ~3;                   // score map pitch
     {
-        const int n16 = (ch * tp + 31) >> 4;
+        const int n16 = ((dh + 2) * sp + 15) >> 4;
         for (int i = lane; i < n16; i += 32) reinterpret_cast<uint4*>(sc)[i] = make_uint4(0, 0, 0, 0);
-        reinterpret_cast<uint4*>(keep_lo)[lane] = make_uint4(0, 0, 0, 0);
-        reinterpret_cast<uint4*>(keep_hi)[lane] = make_uint4(0, 0, 0, 0);
     }
     const int t_ini = min(max(a.t_ini, 0), 255), t_min = min(max(a.t_min, 0), 255);
     const int tlo = min(t_ini, t_min);
@@ -148,6 +152,7 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
     const int tpw = tp >> 2;
     const int xlo = xoff + 3, xhi = xlo + dw;           // domain columns [xlo, xhi) in tile bytes
     const int w0 = xlo >> 2;
+    uint8_t* scb = sc - 2 * sp - xlo + 1;               // scb[row * sp + col] = score of tile pixel (row, col)
     const int nitems = dh * nw;                         // item = one 32-bit word of a domain row
     const int qs = (int)(cb.y & 0xFF), rs = (int)(cb.y >> 8);         // 32 = qs * nw + rs
     int ir = (lane * (int)cb.x) >> 16, iw = lane - ir * nw;           // cb.x = ceil(65536 / nw): lane -> (row, word)
@@ -157,15 +162,16 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
     __syncwarp();                                       // barrier init + clears visible to the whole warp
     mbar_wait(bar, 0);
 
-    // ---- pass 1: 4-pixel prefilter, 32 words per step, ballot compaction (list order is irrelevant) ----
-    const uint32_t* tw = reinterpret_cast<const uint32_t*>(tile) + 3 * tpw + w0;
-    int nlist = 0;
+    // ---- pass 1a: 4-pixel prefilter, 32 words per step; words with any flagged pixel are compacted by ONE ballot
+    //      into a word list (row << 9 | word column << 4 | 4-bit pixel mask) ----
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(tile) + (3 + ir) * tpw + w0 + iw;
+    const int pstep = qs * tpw + rs, pwrap = tpw - nw;
+    int nwl = 0;
     for (int i0 = 0; i0 < nitems; i0 += 32) {
         uint32_t f = 0;
         if (i0 + lane < nitems) {
             if (tlo == 0) f = 0x80808080u;              // "> 0" has no cleared-low-bit form: list the whole domain
             else {
-                const uint32_t* p = tw + ir * tpw + iw;
                 const uint32_t C = p[0], Wm = p[-1], Wp = p[1], U = p[-3 * tpw], D = p[3 * tpw];
                 const uint32_t Lw = __funnelshift_r(Wm, C, 8), Rw = __funnelshift_r(C, Wp, 24);
                 const uint32_t v = (__vabsdiffu4(C, U) | __vabsdiffu4(C, D)) & pmask;
@@ -176,19 +182,36 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
             if (iw == 0) f &= cm_first;
             if (iw == nw - 1) f &= cm_last;
         }
-        if (__any_sync(0xffffffffu, f != 0)) {
-            const uint32_t e = (uint32_t)(((3 + ir) << 8) | ((w0 + iw) << 2));
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const uint32_t m = __ballot_sync(0xffffffffu, f & (0x80u << (8 * k)));
-                if (f & (0x80u << (8 * k))) list[nlist + __popc(m & lt)] = (uint16_t)(e + k);
-                nlist += __popc(m);
-            }
+        const uint32_t m = __ballot_sync(0xffffffffu, f != 0);
+        if (f != 0) {
+            // flag bits 7, 15, 23, 31 -> mask bits 0..3
+            const uint32_t m4 = ((f >> 7) & 1u) | ((f >> 14) & 2u) | ((f >> 21) & 4u) | ((f >> 28) & 8u);
+            wlist[nwl + __popc(m & lt)] = (uint16_t)(((3 + ir) << 9) | ((w0 + iw) << 4) | m4);
         }
-        iw += rs; ir += qs;
-        if (iw >= nw) { iw -= nw; ++ir; }
+        nwl += __popc(m);
+        iw += rs; ir += qs; p += pstep;
+        if (iw >= nw) { iw -= nw; ++ir; p += pwrap; }
     }
     __syncwarp();
+    // ---- pass 1b: expand the word list into the pixel list ((row << 8) | tile column); order is irrelevant.
+    //      Per-lane counts are <= 4: three ballots give the exclusive prefix ----
+    int nlist = 0;
+    for (int k0 = 0; k0 < nwl; k0 += 32) {
+        const uint32_t we = k0 + lane < nwl ? wlist[k0 + lane] : 0u;
+        const int c = __popc(we & 15u);
+        const uint32_t b0 = __ballot_sync(0xffffffffu, c & 1), b1 = __ballot_sync(0xffffffffu, c & 2);
+        const uint32_t b2 = __ballot_sync(0xffffffffu, c & 4);
+        uint16_t* out = list + nlist + __popc(b0 & lt) + 2 * __popc(b1 & lt) + 4 * __popc(b2 & lt);
+        nlist += __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
+        const uint32_t e = ((we >> 9) << 8) | (((we >> 4) & 31u) << 2);
+        if (we & 1u) *out++ = (uint16_t)e;
+        if (we & 2u) *out++ = (uint16_t)(e + 1);
+        if (we & 4u) *out++ = (uint16_t)(e + 2);
+        if (we & 8u) *out++ = (uint16_t)(e + 3);
+    }
+    __syncwarp();
+    reinterpret_cast<uint4*>(keep_lo)[lane] = make_uint4(0, 0, 0, 0);     // row bitmaps (the word list is dead now)
+    reinterpret_cast<uint4*>(keep_hi)[lane] = make_uint4(0, 0, 0, 0);
 
     // ---- pass 2: exact corner strength of the listed pixels ----
     for (int k = lane; k < nlist; k += 32) {
@@ -197,7 +220,7 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
         const uint8_t* c = tile + off;
         const uint8_t* const rows[7] = {c - 3 * tp, c - 2 * tp, c - tp, c, c + tp, c + 2 * tp, c + 3 * tp};
         const int m = fast_arc_strength(rows, c[0]);
-        if (m > tlo) sc[off] = (uint8_t)(m - 1);
+        if (m > tlo) scb[(e >> 8) * sp + (e & 0xFF)] = (uint8_t)(m - 1);
     }
     __syncwarp();
 
@@ -206,10 +229,10 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
     for (int k = lane; k < nlist; k += 32) {
         const int e = list[k];
         const int py = e >> 8, px = e & 0xFF;
-        const uint8_t* q = sc + py * tp + px;
+        const uint8_t* q = scb + py * sp + px;
         const int s = q[0];
-        const int n0 = max(max(q[-tp - 1], q[-tp]), q[-tp + 1]), n1 = max(q[-1], q[1]);
-        const int n2 = max(max(q[tp - 1], q[tp]), q[tp + 1]);
+        const int n0 = max(max(q[-sp - 1], q[-sp]), q[-sp + 1]), n1 = max(q[-1], q[1]);
+        const int n2 = max(max(q[sp - 1], q[sp]), q[sp + 1]);
         if (s > max(max(n0, n1), n2)) {                 // s > 0 implied: neighbours are >= 0
             const int bx = px - xlo;
             const int wi = 2 * (py - 3) + (bx >> 5);
@@ -230,11 +253,11 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
             unsigned long long f0 = 0, f1 = 0;
             for (unsigned long long r = m0; r; r &= r - 1) {
                 const int bx = __ffsll((long long)r) - 1;
-                if (sc[(lane + 3) * tp + bx + xlo] >= t_min) f0 |= 1ull << bx;
+                if (scb[(lane + 3) * sp + bx + xlo] >= t_min) f0 |= 1ull << bx;
             }
             for (unsigned long long r = m1; r; r &= r - 1) {
                 const int bx = __ffsll((long long)r) - 1;
-                if (sc[(lane + 35) * tp + bx + xlo] >= t_min) f1 |= 1ull << bx;
+                if (scb[(lane + 35) * sp + bx + xlo] >= t_min) f1 |= 1ull << bx;
             }
             m0 = f0; m1 = f1;
         }
@@ -262,7 +285,7 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
         const int yy = lane + 3;
         for (unsigned long long r = m0; r; r &= r - 1) {
             const int bx = __ffsll((long long)r) - 1;
-            *out++ = pack_cand(ox + bx + 3, oy + yy, sc[yy * tp + bx + xlo]);
+            *out++ = pack_cand(ox + bx + 3, oy + yy, scb[yy * sp + bx + xlo]);
         }
     }
     if (c1) {
@@ -270,7 +293,7 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
         const int yy = lane + 35;
         for (unsigned long long r = m1; r; r &= r - 1) {
             const int bx = __ffsll((long long)r) - 1;
-            *out++ = pack_cand(ox + bx + 3, oy + yy, sc[yy * tp + bx + xlo]);
+            *out++ = pack_cand(ox + bx + 3, oy + yy, scb[yy * sp + bx + xlo]);
         }
     }
 }
@@ -304,35 +327,46 @@ void build_fast_cell_table(const Geom& g, std::vector<uint32_t>& tab) {
 }
 
 namespace {
-void fast_smem_layout(const Geom& g, int& tile_bytes, int& list_cap) {
-    tile_bytes = 128; list_cap = 64;
+struct FastLayout { int tile_bytes, sc_bytes, plist_bytes, wlist_bytes; };
+FastLayout fast_smem_layout(const Geom& g) {
+    auto up128 = [](int v) { return (v + 127) & ~127; };
+    int tile = 128, scm = 128, pl = 64, wl = 32;
     for (int l = 0; l < g.nlevels; ++l) {
         const LevelGeom& L = g.lv[l];
         if (L.ncells == 0) continue;
-        tile_bytes = std::max(tile_bytes, (L.fast_bw * L.fast_bh + 127) & ~127);
-        list_cap = std::max(list_cap, L.wCell * L.hCell);
+        tile = std::max(tile, L.fast_bw * L.fast_bh);
+        const int dwm = L.wCell, dhm = L.hCell;                       // largest FAST domain of the level
+        scm = std::max(scm, (dhm + 2) * ((dwm + 2 + 3) & ~3) + 16);
+        pl = std::max(pl, dwm * dhm);
+        wl = std::max(wl, dhm * ((dwm + 3) / 4 + 1));                 // a row of dw pixels spans <= ceil(dw / 4) + 1 words
     }
+    FastLayout f;
+    f.tile_bytes = up128(tile); f.sc_bytes = up128(scm); f.plist_bytes = up128(2 * pl);
+    f.wlist_bytes = 2 * wl <= kBitmapBytes ? 0 : up128(2 * wl);
+    return f;
+}
+size_t fast_cta_smem(const FastLayout& f) {
+    return (size_t)kWarpsPerCta * warp_smem_bytes(f.tile_bytes, f.sc_bytes, f.plist_bytes, f.wlist_bytes);
 }
 }  // namespace
 
 int fast_configure(const Geom& g) {
-    int tb, lc;
-    fast_smem_layout(g, tb, lc);
     return (int)cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     kWarpsPerCta * warp_smem_bytes(tb, lc));
+                                     (int)fast_cta_smem(fast_smem_layout(g)));
 }
 
 void launch_fast(const Geom& g, const TileMaps& m, const Buffers& b, int nimg, cudaStream_t s) {
     FastArgs a;
     a.img0 = g.img0; a.nimg = nimg; a.cells_total = g.cells_total; a.cell_cap = g.cell_cap;
     a.t_ini = g.ini_th; a.t_min = g.min_th;
-    fast_smem_layout(g, a.tile_bytes, a.list_cap);
+    const FastLayout f = fast_smem_layout(g);
+    a.tile_bytes = f.tile_bytes; a.sc_bytes = f.sc_bytes; a.plist_bytes = f.plist_bytes; a.wlist_bytes = f.wlist_bytes;
     a.cell_tab = reinterpret_cast<const uint4*>(b.cell_tab);
     a.cell_cnt = b.cell_cnt; a.cell_pts = b.cell_pts; a.err = b.err;
     const long long ncell = (long long)nimg * g.cells_total;
     if (ncell == 0) return;
     const unsigned grd = (unsigned)((ncell + kWarpsPerCta - 1) / kWarpsPerCta);
-    fast_cells_kernel<<<grd, kWarpsPerCta * 32, (size_t)kWarpsPerCta * warp_smem_bytes(a.tile_bytes, a.list_cap), s>>>(a, m);
+    fast_cells_kernel<<<grd, kWarpsPerCta * 32, fast_cta_smem(f), s>>>(a, m);
 }
 
 }  // namespace gforb
