@@ -83,21 +83,19 @@ __device__ __forceinline__ uint32_t gt_lanes2(uint32_t a, uint32_t b, uint32_t k
 
 struct FastArgs {
     int img0, nimg, cells_total, cell_cap, t_ini, t_min;
-    int tile_bytes, sc_bytes, plist_bytes, wlist_bytes;   // per-warp shared layout (all multiples of 128), see fast_smem_layout
+    int tile_bytes, sc_bytes, plist_bytes, warp_bytes;    // per-warp shared layout, see fast_smem_layout
     const uint4* cell_tab;
     uint32_t* cell_cnt; uint32_t* cell_pts; int32_t* err;
 };
 
 namespace {
 constexpr int kWarpsPerCta = 4;
-constexpr int kBitmapBytes = 64 * 2 * 4 * 2;     // keep@min and keep@ini, 64 rows x 2 x 32 bits each
-// Per-warp shared layout: [tile][score map][row bitmaps 1 KB][pixel list][word list].  The score map covers the FAST
-// domain plus a one-pixel zero ring ((dh + 2) rows of align4(dw + 2) bytes), not the whole tile.  The word list is
-// dead before the row bitmaps are first used, so it lives in the bitmaps' 1 KB when it fits (wlist_bytes = 0; true
-// for every level of a 752x480 pyramid); only very large cells get a region of their own.
-__host__ __device__ inline int warp_smem_bytes(int tile_bytes, int sc_bytes, int plist_bytes, int wlist_bytes) {
-    return tile_bytes + sc_bytes + kBitmapBytes + plist_bytes + wlist_bytes;
-}
+constexpr int kBitmapBytes = 64 * 2 * 4;         // keep@tlo, 64 rows x 2 x 32 bits
+// Per-warp shared layout: [tile (TMA, 128-byte aligned)][score map][row bitmap 512 B][pixel list][mbarrier 8 B],
+// regions rounded to 16 bytes, the whole to 128.  The score map covers the FAST domain plus a one-pixel zero ring
+// ((dh + 2) rows of align4(dw + 2) bytes), not the whole tile.  The word list of pass 1 is dead before the score map
+// is first written, so it lives there (a cell has <= dh * (dw / 4 + 2) words: always fits).  At 752x480 this is
+// 7,040 B per warp: 8 CTAs x 4 warps per SM.
 // per-byte "x != 0" for words whose bytes have bit 0 clear: bit 7 of each lane
 __device__ __forceinline__ uint32_t nz_lanes(uint32_t x) { return (x >> 1) + 0x7f7f7f7fu; }
 }  // namespace
@@ -106,7 +104,6 @@ __device__ __forceinline__ uint32_t nz_lanes(uint32_t x) { return (x >> 1) + 0x7
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ __align__(8) uint64_t bars[kWarpsPerCta];
 
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const long long gcell = (long long)blockIdx.x * kWarpsPerCta + wid;      // (image, cell) pair
@@ -120,14 +117,13 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
         if (lane == 0) a.cell_cnt[out_cell] = 0;
         return;
     }
-    uint8_t* wbase = smem + (size_t)wid * warp_smem_bytes(a.tile_bytes, a.sc_bytes, a.plist_bytes, a.wlist_bytes);
+    uint8_t* wbase = smem + (size_t)wid * a.warp_bytes;
     uint8_t* tile = wbase;
     uint8_t* sc = wbase + a.tile_bytes;                                   // corner scores: domain + 1-px zero ring, pitch sp
-    uint32_t* keep_lo = reinterpret_cast<uint32_t*>(sc + a.sc_bytes);     // [row][2]
-    uint32_t* keep_hi = keep_lo + 128;
-    uint16_t* list = reinterpret_cast<uint16_t*>(keep_hi + 128);          // (row << 8) | tile column
-    uint16_t* wlist = a.wlist_bytes ? list + a.plist_bytes / 2 : reinterpret_cast<uint16_t*>(keep_lo);
-    uint64_t* bar = &bars[wid];
+    uint32_t* keep_lo = reinterpret_cast<uint32_t*>(sc + a.sc_bytes);     // [row][2]: survivors of NMS at threshold tlo
+    uint16_t* list = reinterpret_cast<uint16_t*>(keep_lo + 128);          // (row << 8) | tile column
+    uint16_t* wlist = reinterpret_cast<uint16_t*>(sc);                    // pass 1 only (before the score map is cleared)
+    uint64_t* bar = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(list) + a.plist_bytes);
 
     const int xoff = ca.y & 0xFF, l = ca.y >> 24;
     const int tp = ca.w & 0xFF, th = (ca.w >> 8) & 0xFF, nw = ca.w >> 24;
@@ -138,12 +134,8 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
         mbar_expect_tx(bar, (uint32_t)(tp * th));
         tma_load_tile_3d(tile, &maps.fast[l], (int)(ca.x & 0xFFFF), (int)(ca.x >> 16), img, bar);
     }
-    // while the tile is in flight: clear the score map (domain + zero ring)
     const int sp = (dw + 2 + 3) & ~3;                   // score map pitch
-    {
-        const int n16 = ((dh + 2) * sp + 15) >> 4;
-        for (int i = lane; i < n16; i += 32) reinterpret_cast<uint4*>(sc)[i] = make_uint4(0, 0, 0, 0);
-    }
+    reinterpret_cast<uint4*>(keep_lo)[lane] = make_uint4(0, 0, 0, 0);     // row bitmaps
     const int t_ini = min(max(a.t_ini, 0), 255), t_min = min(max(a.t_min, 0), 255);
     const int tlo = min(t_ini, t_min);
     // prefilter threshold: the largest 2^k - 1 <= tlo (a lower threshold stays a superset); |d| > 2^k - 1 <=> d & ~(2^k - 1) != 0,
@@ -210,8 +202,11 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
         if (we & 8u) *out++ = (uint16_t)(e + 3);
     }
     __syncwarp();
-    reinterpret_cast<uint4*>(keep_lo)[lane] = make_uint4(0, 0, 0, 0);     // row bitmaps (the word list is dead now)
-    reinterpret_cast<uint4*>(keep_hi)[lane] = make_uint4(0, 0, 0, 0);
+    {   // the word list is dead: clear the score map (domain + zero ring) it shared
+        const int n16 = ((dh + 2) * sp + 15) >> 4;
+        for (int i = lane; i < n16; i += 32) reinterpret_cast<uint4*>(sc)[i] = make_uint4(0, 0, 0, 0);
+    }
+    __syncwarp();
 
     // ---- pass 2: exact corner strength of the listed pixels ----
     for (int k = lane; k < nlist; k += 32) {
@@ -238,26 +233,27 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
             const int wi = 2 * (py - 3) + (bx >> 5);
             const uint32_t bit = 1u << (bx & 31);
             atomicOr(&keep_lo[wi], bit);
-            if (s >= t_ini) { atomicOr(&keep_hi[wi], bit); hi = true; }
+            hi |= s >= t_ini;
         }
     }
-    // keep@ini if it found anything, else keep@min (s >= t_min filter applies when t_min > tlo)
+    // keep@ini if it found anything, else keep@min: keep@t(p) = keep@tlo(p) && s(p) >= t, so the rows' bitmaps are
+    // filtered by score whenever the selected threshold is above tlo
     const bool use_hi = __any_sync(0xffffffffu, hi);
     __syncwarp();
     unsigned long long m0 = 0, m1 = 0;                  // rows lane and lane + 32
     {
-        const uint32_t* km = use_hi ? keep_hi : keep_lo;
-        if (lane < dh) m0 = (unsigned long long)km[2 * lane] | ((unsigned long long)km[2 * lane + 1] << 32);
-        if (lane + 32 < dh) m1 = (unsigned long long)km[2 * lane + 64] | ((unsigned long long)km[2 * lane + 65] << 32);
-        if (!use_hi && t_min > tlo) {                   // iniTh < minTh configuration: retry threshold is the higher one
+        if (lane < dh) m0 = (unsigned long long)keep_lo[2 * lane] | ((unsigned long long)keep_lo[2 * lane + 1] << 32);
+        if (lane + 32 < dh) m1 = (unsigned long long)keep_lo[2 * lane + 64] | ((unsigned long long)keep_lo[2 * lane + 65] << 32);
+        const int tsel = use_hi ? t_ini : t_min;
+        if (tsel > tlo) {
             unsigned long long f0 = 0, f1 = 0;
             for (unsigned long long r = m0; r; r &= r - 1) {
                 const int bx = __ffsll((long long)r) - 1;
-                if (scb[(lane + 3) * sp + bx + xlo] >= t_min) f0 |= 1ull << bx;
+                if (scb[(lane + 3) * sp + bx + xlo] >= tsel) f0 |= 1ull << bx;
             }
             for (unsigned long long r = m1; r; r &= r - 1) {
                 const int bx = __ffsll((long long)r) - 1;
-                if (scb[(lane + 35) * sp + bx + xlo] >= t_min) f1 |= 1ull << bx;
+                if (scb[(lane + 35) * sp + bx + xlo] >= tsel) f1 |= 1ull << bx;
             }
             m0 = f0; m1 = f1;
         }
@@ -327,27 +323,25 @@ void build_fast_cell_table(const Geom& g, std::vector<uint32_t>& tab) {
 }
 
 namespace {
-struct FastLayout { int tile_bytes, sc_bytes, plist_bytes, wlist_bytes; };
+struct FastLayout { int tile_bytes, sc_bytes, plist_bytes, warp_bytes; };
 FastLayout fast_smem_layout(const Geom& g) {
-    auto up128 = [](int v) { return (v + 127) & ~127; };
-    int tile = 128, scm = 128, pl = 64, wl = 32;
+    auto up = [](int v, int a) { return (v + a - 1) / a * a; };
+    int tile = 128, scm = 128, pl = 64;
     for (int l = 0; l < g.nlevels; ++l) {
         const LevelGeom& L = g.lv[l];
         if (L.ncells == 0) continue;
         tile = std::max(tile, L.fast_bw * L.fast_bh);
         const int dwm = L.wCell, dhm = L.hCell;                       // largest FAST domain of the level
-        scm = std::max(scm, (dhm + 2) * ((dwm + 2 + 3) & ~3) + 16);
+        const int words = dhm * ((dwm + 3) / 4 + 1);                  // a row of dw pixels spans <= ceil(dw / 4) + 1 words
+        scm = std::max(scm, std::max((dhm + 2) * ((dwm + 2 + 3) & ~3) + 16, 2 * words));
         pl = std::max(pl, dwm * dhm);
-        wl = std::max(wl, dhm * ((dwm + 3) / 4 + 1));                 // a row of dw pixels spans <= ceil(dw / 4) + 1 words
     }
     FastLayout f;
-    f.tile_bytes = up128(tile); f.sc_bytes = up128(scm); f.plist_bytes = up128(2 * pl);
-    f.wlist_bytes = 2 * wl <= kBitmapBytes ? 0 : up128(2 * wl);
+    f.tile_bytes = up(tile, 16); f.sc_bytes = up(scm, 16); f.plist_bytes = up(2 * pl, 16);
+    f.warp_bytes = up(f.tile_bytes + f.sc_bytes + kBitmapBytes + f.plist_bytes + 8, 128);
     return f;
 }
-size_t fast_cta_smem(const FastLayout& f) {
-    return (size_t)kWarpsPerCta * warp_smem_bytes(f.tile_bytes, f.sc_bytes, f.plist_bytes, f.wlist_bytes);
-}
+size_t fast_cta_smem(const FastLayout& f) { return (size_t)kWarpsPerCta * f.warp_bytes; }
 }  // namespace
 
 int fast_configure(const Geom& g) {
@@ -360,7 +354,7 @@ void launch_fast(const Geom& g, const TileMaps& m, const Buffers& b, int nimg, c
     a.img0 = g.img0; a.nimg = nimg; a.cells_total = g.cells_total; a.cell_cap = g.cell_cap;
     a.t_ini = g.ini_th; a.t_min = g.min_th;
     const FastLayout f = fast_smem_layout(g);
-    a.tile_bytes = f.tile_bytes; a.sc_bytes = f.sc_bytes; a.plist_bytes = f.plist_bytes; a.wlist_bytes = f.wlist_bytes;
+    a.tile_bytes = f.tile_bytes; a.sc_bytes = f.sc_bytes; a.plist_bytes = f.plist_bytes; a.warp_bytes = f.warp_bytes;
     a.cell_tab = reinterpret_cast<const uint4*>(b.cell_tab);
     a.cell_cnt = b.cell_cnt; a.cell_pts = b.cell_pts; a.err = b.err;
     const long long ncell = (long long)nimg * g.cells_total;
