@@ -92,6 +92,11 @@ _SIGS = {
     "gforb_match_bruteforce": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "gforb_match_bruteforce_device": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "gforb_matcher_sync": (_i, [_vp, C.POINTER(C.c_float)]),
+    "gforb_assign_features_to_grid": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
+    "gforb_features_in_area": (_i, [_vp, _vp, _vp, _i, _vp, _i, _vp, _vp, _i]),
+    "gforb_search_for_initialization": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _vp, C.POINTER(_i)]),
+    "gforb_search_for_initialization_batch_device": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i,
+                                                          _vp, _vp, _vp]),
     "gforb_device_alloc": (_i, [C.POINTER(_vp), _sz]),
     "gforb_device_free": (None, [_vp]),
     "gforb_device_copy": (_i, [_vp, _vp, _sz, _i]),
@@ -197,10 +202,83 @@ class ORBmatcher:
                                                 _vp(stream) if stream else None))
 
     def sync(self):
-        """wait for the last BruteForceDevice; returns its device time in ms"""
+        """wait for the last device-form call; returns its device time in ms"""
         ms = C.c_float(0)
         _check(_L.gforb_matcher_sync(self._h, C.byref(ms)))
         return ms.value
+
+    def SearchForInitialization(self, keys1, desc1, keys2, desc2, vbPrevMatched, windowSize=10, bounds=None,
+                                width=None, height=None):
+        """ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)
+        (src/ORBmatcher.cc:520-633).  keysX/descX = FX.mvKeysUn / FX.mDescriptors; vbPrevMatched [n1,2] float32 is
+        updated in place like the reference's vector.  Returns (nmatches, vnMatches12)."""
+        b = _bounds(bounds, width, height)
+        k1 = np.ascontiguousarray(keys1, KP_DTYPE); k2 = np.ascontiguousarray(keys2, KP_DTYPE)
+        d1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32); d2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+        assert len(d1) == len(k1) and len(d2) == len(k2)
+        assert vbPrevMatched.dtype == np.float32 and vbPrevMatched.shape == (len(k1), 2) and vbPrevMatched.flags.c_contiguous
+        m12 = np.full(len(k1), -1, np.int32)
+        n = _i(0)
+        _check(_L.gforb_search_for_initialization(self._h, _p(b), _p(k1) if len(k1) else None, _p(d1) if len(k1) else None,
+                                                  len(k1), _p(k2) if len(k2) else None, _p(d2) if len(k2) else None, len(k2),
+                                                  _p(vbPrevMatched) if len(k1) else None, int(windowSize),
+                                                  int(self.mbCheckOrientation), _p(m12) if len(k1) else None, C.byref(n)))
+        return n.value, m12
+
+    def SearchForInitializationBatchDevice(self, bounds, n_pairs, dev_k1, dev_d1, dev_n1, stride1, dev_k2, dev_d2, dev_n2,
+                                           stride2, dev_prev, windowSize, dev_m12, dev_nm, stream=None):
+        """device pointers (ints or DeviceArray), one CTA per frame pair; asynchronous"""
+        ptr = lambda x: None if x is None else _vp(x.ptr if isinstance(x, DeviceArray) else x)
+        b = _bounds(bounds, None, None)
+        _check(_L.gforb_search_for_initialization_batch_device(
+            self._h, _p(b), n_pairs, ptr(dev_k1), ptr(dev_d1), ptr(dev_n1), stride1, ptr(dev_k2), ptr(dev_d2), ptr(dev_n2),
+            stride2, ptr(dev_prev), int(windowSize), int(self.mbCheckOrientation), ptr(dev_m12), ptr(dev_nm),
+            _vp(stream) if stream else None))
+
+
+FRAME_GRID_COLS, FRAME_GRID_ROWS = 64, 48      # include/Frame.h:92-93
+
+
+def _bounds(bounds, width, height):
+    """{mnMinX, mnMaxX, mnMinY, mnMaxY}; without distortion the image rectangle (src/Frame.cc:760-887)."""
+    if bounds is None:
+        bounds = (0.0, float(width), 0.0, float(height))
+    return np.ascontiguousarray(bounds, np.float32)
+
+
+class FrameGrid:
+    """The feature grid of ORB_SLAM2::Frame: AssignFeaturesToGrid (src/Frame.cc:461-476) at construction,
+    GetFeaturesInArea (src/Frame.cc:593-643) as a batch of queries.  mGrid[ix][iy] == cell(ix, iy)."""
+
+    def __init__(self, keys, bounds=None, width=None, height=None, matcher=None):
+        self._m = matcher or ORBmatcher()
+        self._b = _bounds(bounds, width, height)
+        self._keys = np.ascontiguousarray(keys, KP_DTYPE)
+        n = len(self._keys)
+        self.cell_start = np.zeros(FRAME_GRID_COLS * FRAME_GRID_ROWS + 1, np.int32)
+        idx = np.zeros(max(n, 1), np.int32)
+        _check(_L.gforb_assign_features_to_grid(self._m._h, _p(self._b), _p(self._keys) if n else None, n,
+                                                _p(self.cell_start), _p(idx)))
+        self.cell_idx = idx[: self.cell_start[-1]]
+
+    def cell(self, ix, iy):
+        c = ix * FRAME_GRID_ROWS + iy
+        return self.cell_idx[self.cell_start[c]: self.cell_start[c + 1]]
+
+    def GetFeaturesInArea(self, queries, cap=None):
+        """queries: iterable of (x, y, r[, minLevel, maxLevel]) -> list of int32 index arrays (reference order)"""
+        q = np.zeros(len(queries), AREA_QUERY_DTYPE)
+        for i, t in enumerate(queries):
+            q[i] = tuple(t) + (-1, -1) if len(t) == 3 else tuple(t)
+        n, nq = len(self._keys), len(q)
+        cap = max(int(cap if cap is not None else nq * max(n, 1)), 1)
+        start = np.zeros(nq + 1, np.int32); out = np.zeros(cap, np.int32)
+        _check(_L.gforb_features_in_area(self._m._h, _p(self._b), _p(self._keys) if n else None, n, _p(q) if nq else None, nq,
+                                         _p(start), _p(out), cap))
+        return [out[start[i]: start[i + 1]] for i in range(nq)]
+
+
+AREA_QUERY_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("r", "<f4"), ("min_level", "<i4"), ("max_level", "<i4")])
 
 
 class ORBextractor:

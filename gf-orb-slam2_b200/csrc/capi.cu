@@ -448,6 +448,166 @@ int gforb_match_bruteforce(gforb_matcher* m, const uint8_t* a, int nA, const uin
     return GFORB_OK;
 }
 
+// ------------------------------------------------------------------------ frame grid + SearchForInitialization
+namespace {
+int check_bounds(const gforb_frame_bounds* b, const char* who) {
+    if (!b || !(b->max_x > b->min_x) || !(b->max_y > b->min_y)) { set_error(std::string(who) + ": bad image bounds"); return GFORB_ERR_ARG; }
+    return GFORB_OK;
+}
+inline size_t al16(size_t v) { return (v + 15) & ~(size_t)15; }
+}  // namespace
+
+int gforb_assign_features_to_grid(gforb_matcher* m, const gforb_frame_bounds* bounds, const gforb_keypoint* keys, int n,
+                                  int32_t* cell_start, int32_t* cell_idx) {
+    if (!m || n < 0 || (n > 0 && (!keys || !cell_idx)) || !cell_start) { set_error("gforb_assign_features_to_grid: bad arguments"); return GFORB_ERR_ARG; }
+    int rc = check_bounds(bounds, "gforb_assign_features_to_grid");
+    if (rc) return rc;
+    if (n > gridmatch_max_keys()) { set_error("gforb_assign_features_to_grid: more than 8192 keys"); return GFORB_ERR_CAPACITY; }
+    const int cells = gridmatch_cells();
+    const size_t bk = al16((size_t)std::max(n, 1) * sizeof(gforb_keypoint)), bs = al16((size_t)(cells + 1) * 4), bi = al16((size_t)std::max(n, 1) * 4);
+    rc = m->reserve(m->io, m->io_bytes, bk + bs + bi);
+    if (rc) return rc;
+    uint8_t* base = static_cast<uint8_t*>(m->io);
+    gforb_keypoint* dk = reinterpret_cast<gforb_keypoint*>(base);
+    int32_t* ds = reinterpret_cast<int32_t*>(base + bk);
+    int32_t* di = reinterpret_cast<int32_t*>(base + bk + bs);
+    cudaStream_t s = m->stream;
+    const float bb[4] = {bounds->min_x, bounds->max_x, bounds->min_y, bounds->max_y};
+    if (n > 0) M_CUDA(cudaMemcpyAsync(dk, keys, (size_t)n * sizeof(gforb_keypoint), cudaMemcpyHostToDevice, s));
+    launch_grid_build(dk, nullptr, n, std::max(n, 1), 1, bb, ds, di, s);
+    M_CUDA(cudaGetLastError());
+    M_CUDA(cudaMemcpyAsync(cell_start, ds, (size_t)(cells + 1) * 4, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaStreamSynchronize(s));
+    const int inside = cell_start[cells];
+    if (inside > 0) M_CUDA(cudaMemcpy(cell_idx, di, (size_t)inside * 4, cudaMemcpyDeviceToHost));
+    return GFORB_OK;
+}
+
+int gforb_features_in_area(gforb_matcher* m, const gforb_frame_bounds* bounds, const gforb_keypoint* keys, int n,
+                           const gforb_area_query* queries, int nq, int32_t* out_start, int32_t* out_idx, int cap) {
+    if (!m || n < 0 || nq < 0 || cap < 0 || (n > 0 && !keys) || (nq > 0 && !queries) || !out_start || (cap > 0 && !out_idx)) {
+        set_error("gforb_features_in_area: bad arguments");
+        return GFORB_ERR_ARG;
+    }
+    int rc = check_bounds(bounds, "gforb_features_in_area");
+    if (rc) return rc;
+    if (n > gridmatch_max_keys()) { set_error("gforb_features_in_area: more than 8192 keys"); return GFORB_ERR_CAPACITY; }
+    out_start[0] = 0;
+    if (nq == 0) return GFORB_OK;
+    const int cells = gridmatch_cells();
+    const size_t bk = al16((size_t)std::max(n, 1) * sizeof(gforb_keypoint)), bs = al16((size_t)(cells + 1) * 4), bi = al16((size_t)std::max(n, 1) * 4);
+    const size_t bq = al16((size_t)nq * sizeof(gforb_area_query)), bc = al16((size_t)(nq + 1) * 4), bo = al16((size_t)std::max(cap, 1) * 4);
+    rc = m->reserve(m->io, m->io_bytes, bk + bs + bi + bq + bc + bo);
+    if (rc) return rc;
+    uint8_t* base = static_cast<uint8_t*>(m->io);
+    gforb_keypoint* dk = reinterpret_cast<gforb_keypoint*>(base);
+    int32_t* ds = reinterpret_cast<int32_t*>(base + bk);
+    int32_t* di = reinterpret_cast<int32_t*>(base + bk + bs);
+    void* dq = base + bk + bs + bi;
+    int32_t* dc = reinterpret_cast<int32_t*>(base + bk + bs + bi + bq);
+    int32_t* dout = reinterpret_cast<int32_t*>(base + bk + bs + bi + bq + bc);
+    cudaStream_t s = m->stream;
+    const float bb[4] = {bounds->min_x, bounds->max_x, bounds->min_y, bounds->max_y};
+    if (n > 0) M_CUDA(cudaMemcpyAsync(dk, keys, (size_t)n * sizeof(gforb_keypoint), cudaMemcpyHostToDevice, s));
+    M_CUDA(cudaMemcpyAsync(dq, queries, (size_t)nq * sizeof(gforb_area_query), cudaMemcpyHostToDevice, s));
+    launch_grid_build(dk, nullptr, n, std::max(n, 1), 1, bb, ds, di, s);
+    launch_area_query(dk, bb, ds, di, dq, nq, dc, nullptr, nullptr, s);                 // pass 1: counts
+    M_CUDA(cudaGetLastError());
+    M_CUDA(cudaMemcpyAsync(out_start + 1, dc, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaStreamSynchronize(s));
+    long long total = 0;
+    for (int q = 0; q < nq; ++q) { total += out_start[q + 1]; out_start[q + 1] = (int32_t)std::min<long long>(total, INT32_MAX); }
+    if (total > cap) { set_error("gforb_features_in_area: output capacity too small (out_start holds the sizes)"); return GFORB_ERR_CAPACITY; }
+    if (total == 0) return GFORB_OK;
+    M_CUDA(cudaMemcpyAsync(dc, out_start, (size_t)(nq + 1) * 4, cudaMemcpyHostToDevice, s));
+    launch_area_query(dk, bb, ds, di, dq, nq, nullptr, dc, dout, s);                    // pass 2: ordered fill
+    M_CUDA(cudaGetLastError());
+    M_CUDA(cudaMemcpyAsync(out_idx, dout, (size_t)total * 4, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaStreamSynchronize(s));
+    return GFORB_OK;
+}
+
+int gforb_search_for_initialization_batch_device(gforb_matcher* m, const gforb_frame_bounds* bounds, int n_pairs,
+                                    const gforb_keypoint* k1, const uint8_t* d1, const int32_t* n1, int stride1,
+                                    const gforb_keypoint* k2, const uint8_t* d2, const int32_t* n2, int stride2,
+                                    float* prev_xy, int window_size, int check_orientation,
+                                    int32_t* matches12, int32_t* nmatches, void* cuda_stream) {
+    if (!m || n_pairs < 0 || stride1 < 0 || stride2 < 0 || !nmatches || (stride1 > 0 && (!k1 || !d1 || !prev_xy || !matches12)) ||
+        (stride2 > 0 && (!k2 || !d2))) {
+        set_error("gforb_search_for_initialization: bad arguments");
+        return GFORB_ERR_ARG;
+    }
+    int rc = check_bounds(bounds, "gforb_search_for_initialization");
+    if (rc) return rc;
+    if (stride1 > gridmatch_max_keys() || stride2 > gridmatch_max_keys()) { set_error("gforb_search_for_initialization: more than 8192 keys per frame"); return GFORB_ERR_CAPACITY; }
+    if (((uintptr_t)d1 | (uintptr_t)d2) & 15) { set_error("gforb_search_for_initialization: descriptor arrays must be 16-byte aligned"); return GFORB_ERR_ARG; }
+    if (n_pairs == 0) return GFORB_OK;
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : m->stream;
+    m->last = s;
+    const int cells = gridmatch_cells(), st2 = std::max(stride2, 1);
+    const size_t bs = al16((size_t)n_pairs * (cells + 1) * 4), bi = al16((size_t)n_pairs * st2 * 4);
+    rc = m->reserve(m->scratch, m->scratch_bytes, bs + bi);
+    if (rc) return rc;
+    int32_t* ds = static_cast<int32_t*>(m->scratch);
+    int32_t* di = reinterpret_cast<int32_t*>(static_cast<uint8_t*>(m->scratch) + bs);
+    const float bb[4] = {bounds->min_x, bounds->max_x, bounds->min_y, bounds->max_y};
+    M_CUDA(cudaEventRecord(m->ev0, s));
+    launch_grid_build(k2, n2, stride2, st2, n_pairs, bb, ds, di, s);
+    InitSearchArgs a{};
+    a.k1 = k1; a.d1 = d1; a.n1 = n1; a.k2 = k2; a.d2 = d2; a.n2 = n2;
+    a.n1_fixed = stride1; a.n2_fixed = stride2; a.stride1 = stride1; a.stride2 = st2;
+    a.cell_start = ds; a.cell_idx = di;
+    a.prev_xy = prev_xy; a.window = (float)window_size; a.ratio = m->ratio;
+    a.check_ori = check_orientation ? 1 : 0; a.th_low = GFORB_TH_LOW;
+    a.matches12 = matches12; a.nmatches = nmatches;
+    if (launch_init_search(a, bb, n_pairs, s)) { set_error("gforb_search_for_initialization: shared-memory opt-in failed"); return GFORB_ERR_CUDA; }
+    M_CUDA(cudaEventRecord(m->ev1, s));
+    M_CUDA(cudaGetLastError());
+    m->timed = true;
+    return GFORB_OK;
+}
+
+int gforb_search_for_initialization(gforb_matcher* m, const gforb_frame_bounds* bounds, const gforb_keypoint* keys1,
+                                    const uint8_t* desc1, int n1, const gforb_keypoint* keys2, const uint8_t* desc2, int n2,
+                                    float* prev_xy, int window_size, int check_orientation, int32_t* matches12, int* nmatches) {
+    if (!m || n1 < 0 || n2 < 0 || !nmatches || (n1 > 0 && (!keys1 || !desc1 || !prev_xy || !matches12)) || (n2 > 0 && (!keys2 || !desc2))) {
+        set_error("gforb_search_for_initialization: bad arguments");
+        return GFORB_ERR_ARG;
+    }
+    *nmatches = 0;
+    if (n1 == 0) return check_bounds(bounds, "gforb_search_for_initialization");
+    const size_t k1b = al16((size_t)n1 * sizeof(gforb_keypoint)), k2b = al16((size_t)std::max(n2, 1) * sizeof(gforb_keypoint));
+    const size_t d1b = al16((size_t)n1 * 32), d2b = al16((size_t)std::max(n2, 1) * 32), pb = al16((size_t)n1 * 8), mb = al16((size_t)n1 * 4);
+    int rc = m->reserve(m->io, m->io_bytes, k1b + k2b + d1b + d2b + pb + mb + 16);
+    if (rc) return rc;
+    uint8_t* base = static_cast<uint8_t*>(m->io);
+    gforb_keypoint* dk1 = reinterpret_cast<gforb_keypoint*>(base);
+    gforb_keypoint* dk2 = reinterpret_cast<gforb_keypoint*>(base + k1b);
+    uint8_t* dd1 = base + k1b + k2b;
+    uint8_t* dd2 = dd1 + d1b;
+    float* dp = reinterpret_cast<float*>(dd2 + d2b);
+    int32_t* dm = reinterpret_cast<int32_t*>(dd2 + d2b + pb);
+    int32_t* dn = reinterpret_cast<int32_t*>(dd2 + d2b + pb + mb);
+    cudaStream_t s = m->stream;
+    M_CUDA(cudaMemcpyAsync(dk1, keys1, (size_t)n1 * sizeof(gforb_keypoint), cudaMemcpyHostToDevice, s));
+    M_CUDA(cudaMemcpyAsync(dd1, desc1, (size_t)n1 * 32, cudaMemcpyHostToDevice, s));
+    M_CUDA(cudaMemcpyAsync(dp, prev_xy, (size_t)n1 * 8, cudaMemcpyHostToDevice, s));
+    if (n2 > 0) {
+        M_CUDA(cudaMemcpyAsync(dk2, keys2, (size_t)n2 * sizeof(gforb_keypoint), cudaMemcpyHostToDevice, s));
+        M_CUDA(cudaMemcpyAsync(dd2, desc2, (size_t)n2 * 32, cudaMemcpyHostToDevice, s));
+    }
+    rc = gforb_search_for_initialization_batch_device(m, bounds, 1, dk1, dd1, nullptr, n1, dk2, dd2, nullptr, n2, dp, window_size,
+                                                      check_orientation, dm, dn, nullptr);
+    if (rc) return rc;
+    int32_t nm = 0;
+    M_CUDA(cudaMemcpyAsync(matches12, dm, (size_t)n1 * 4, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaMemcpyAsync(prev_xy, dp, (size_t)n1 * 8, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaMemcpyAsync(&nm, dn, 4, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaStreamSynchronize(s));
+    *nmatches = nm;
+    return GFORB_OK;
+}
+
 int gforb_device_alloc(void** p, size_t bytes) {
     if (!p) return GFORB_ERR_ARG;
     M_CUDA(cudaMalloc(p, std::max<size_t>(bytes, 16)));

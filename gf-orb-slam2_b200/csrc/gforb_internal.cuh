@@ -142,6 +142,29 @@ int match_max_train();
 void launch_match(const uint8_t* dA, int nA, const uint8_t* dB, int nB, float ratio, int threshold, int nseg,
                   void* scratch, int32_t* best_idx, int32_t* best_dist, int32_t* second_dist, int32_t* match,
                   cudaStream_t s);
+// frame feature grid + SearchForInitialization (k_gridmatch.cu)
+struct InitSearchArgs {
+    const gforb_keypoint* k1; const uint8_t* d1; const int32_t* n1;    // per pair p: k1 + p * stride1, n1[p] (or n1_fixed)
+    const gforb_keypoint* k2; const uint8_t* d2; const int32_t* n2;
+    int n1_fixed, n2_fixed, stride1, stride2;
+    const int32_t* cell_start; const int32_t* cell_idx;                 // frame-2 grids, one per pair
+    float min_x, min_y, w_inv, h_inv;
+    float* prev_xy;              // [pair][stride1][2] in/out (vbPrevMatched)
+    float window, ratio;
+    int check_ori, th_low;
+    int32_t* matches12;          // [pair][stride1]
+    int32_t* nmatches;           // [pair]
+};
+int gridmatch_max_keys();   // 8192 keys per frame
+int gridmatch_cells();      // 64 * 48
+// bounds = {mnMinX, mnMaxX, mnMinY, mnMaxY}; counts == nullptr: every frame has n_fixed keys.  1 launch.
+void launch_grid_build(const gforb_keypoint* keys, const int32_t* counts, int n_fixed, int key_stride, int nframes,
+                       const float* bounds, int32_t* cell_start, int32_t* cell_idx, cudaStream_t s);
+// queries: nq x {float x, y, r; int32 min_level, max_level}; out_start == nullptr counts, else fills.  1 launch.
+void launch_area_query(const gforb_keypoint* keys, const float* bounds, const int32_t* cell_start, const int32_t* cell_idx,
+                       const void* queries, int nq, int32_t* out_count, const int32_t* out_start, int32_t* out_idx,
+                       cudaStream_t s);
+int launch_init_search(const InitSearchArgs& a, const float* bounds, int npairs, cudaStream_t s);   // 1 launch; -1: smem opt-in failed
 size_t octree_smem_bytes(const Geom& g);
 int fast_configure(const Geom& g);     // opt in to the FAST kernel's dynamic smem; returns cudaError_t as int
 int octree_configure(const Geom& g);   // opt in to large dynamic smem; returns cudaError_t as int

@@ -1,0 +1,346 @@
+// Frame feature grid + windowed initialisation matcher.
+//
+// Reference:
+//   Frame::AssignFeaturesToGrid / PosInGrid   src/Frame.cc:461-476, 645-656   (64 x 48 cells, include/Frame.h:92-93)
+//   Frame::GetFeaturesInArea                  src/Frame.cc:593-643
+//   ORBmatcher::SearchForInitialization       src/ORBmatcher.cc:520-633
+//   ORBmatcher::ComputeThreeMaxima            src/ORBmatcher.cc:1723-1764
+//
+// Grid layout in HBM: the reference keeps mGrid[ix][iy] as 3,072 std::vector<size_t>, filled by push_back in
+// ascending key index.  Here it is one CSR: `cell_idx` = key indices sorted by (ix, iy, index) and `cell_start`
+// (3,073 offsets, cell id = ix * 48 + iy).  GetFeaturesInArea walks ix ascending, then iy ascending, then the cell
+// in push_back order -- which is exactly ascending CSR position, and for one ix the cells iy0..iy1 are ONE
+// contiguous CSR run.  So "candidate order" (it decides which of two equal Hamming minima wins) is the CSR position
+// and needs no per-query list, no ballot and no atomics.
+//
+// SearchForInitialization is sequential in the reference: query i1 ignores a target i2 that an earlier query already
+// holds with a distance <= its own (vMatchedDistance), and may take a target over.  Parallel restatement:
+//   phase 1 (all warps, one level-0 query per warp): best / second-best over the window IGNORING the claim table;
+//   phase 2 (one warp, queries in order): the speculative pair is the sequential answer unless the claim table
+//            hides its best or its second-best target (hiding any other candidate cannot change the two smallest);
+//            only then the warp re-walks that query's window with the claim filter.  Claims, take-overs and the
+//            rotation-bin of each accepted query are recorded exactly as the reference does;
+//   phase 3 (all threads): 30-bin rotation histogram (counts include matches that were later taken over, as
+//            rotHist[].push_back does), three maxima, removal, vbPrevMatched update, match count.
+// One CTA per frame pair; frame pairs are independent (batch dimension = grid).
+#include "gforb_internal.cuh"
+
+namespace gforb {
+
+namespace {
+constexpr int kGCols = 64, kGRows = 48, kGCells = kGCols * kGRows;
+constexpr int kHisto = 30;                      // HISTO_LENGTH, src/ORBmatcher.cc:39
+constexpr int kPosBits = 13;                    // CSR position bits inside a key: n <= 8192
+constexpr uint32_t kNone = 0xFFFFFFFFu;
+constexpr int kGridThreads = 256, kSearchThreads = 256;
+
+struct GridView {
+    const int32_t* start;      // [kGCells + 1]
+    const int32_t* idx;        // [n] key indices in (ix, iy, index) order
+    float min_x, min_y, w_inv, h_inv;
+};
+
+__device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1) {
+    return (__popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z)) +
+           (__popc(a0.w ^ b0.w) + __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y)) +
+           (__popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w));
+}
+
+// cell window of GetFeaturesInArea (src/Frame.cc:598-612); false = the reference returns an empty vector
+__device__ __forceinline__ bool area_window(const GridView& g, float x, float y, float r, int& x0, int& x1, int& y0, int& y1) {
+    x0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, g.min_x), r), g.w_inv)));
+    if (x0 >= kGCols) return false;
+    x1 = min(kGCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, g.min_x), r), g.w_inv)));
+    if (x1 < 0) return false;
+    y0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, g.min_y), r), g.h_inv)));
+    if (y0 >= kGRows) return false;
+    y1 = min(kGRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, g.min_y), r), g.h_inv)));
+    return y1 >= 0;
+}
+
+// level + square-window test of one grid entry (src/Frame.cc:623-637)
+__device__ __forceinline__ bool area_accepts(const gforb_keypoint* __restrict__ keys, int i, float x, float y, float r,
+                                             int lo, int hi) {
+    const int oct = __ldg(&keys[i].octave);
+    if (lo > 0 || hi >= 0) {
+        if (oct < lo) return false;
+        if (hi >= 0 && oct > hi) return false;
+    }
+    const float dx = __fsub_rn(__ldg(&keys[i].x), x), dy = __fsub_rn(__ldg(&keys[i].y), y);
+    return fabsf(dx) < r && fabsf(dy) < r;
+}
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------- grid build
+// One CTA per frame.  keys = (cell << 13 | index) bitonic-sorted in shared memory; keys outside the grid
+// (PosInGrid false, src/Frame.cc:652-653) sort to the end and are dropped.
+__global__ void __launch_bounds__(kGridThreads)
+grid_build_kernel(const gforb_keypoint* __restrict__ keys, const int32_t* __restrict__ counts, int n_fixed, int key_stride,
+                  float min_x, float min_y, float w_inv, float h_inv, int32_t* __restrict__ cell_start,
+                  int32_t* __restrict__ cell_idx, int npow2) {
+    extern __shared__ uint32_t skey[];
+    const int f = blockIdx.x;
+    const int n = counts ? min(counts[f], key_stride) : n_fixed;
+    const gforb_keypoint* k = keys + (size_t)f * key_stride;
+    int32_t* start = cell_start + (size_t)f * (kGCells + 1);
+    int32_t* idx = cell_idx + (size_t)f * key_stride;
+    for (int i = threadIdx.x; i < npow2; i += kGridThreads) {
+        uint32_t key = kNone;
+        if (i < n) {
+            const int px = (int)roundf(__fmul_rn(__fsub_rn(__ldg(&k[i].x), min_x), w_inv));
+            const int py = (int)roundf(__fmul_rn(__fsub_rn(__ldg(&k[i].y), min_y), h_inv));
+            if (px >= 0 && px < kGCols && py >= 0 && py < kGRows) key = ((uint32_t)(px * kGRows + py) << kPosBits) | (uint32_t)i;
+        }
+        skey[i] = key;
+    }
+    __syncthreads();
+    for (int size = 2; size <= npow2; size <<= 1)
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int t = threadIdx.x; t < (npow2 >> 1); t += kGridThreads) {
+                const int lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
+                const uint32_t a = skey[lo], b = skey[hi];
+                const bool up = (lo & size) == 0;
+                if ((a > b) == up) { skey[lo] = b; skey[hi] = a; }
+            }
+            __syncthreads();
+        }
+    for (int i = threadIdx.x; i < n; i += kGridThreads) {
+        const uint32_t key = skey[i];
+        if (key != kNone) idx[i] = (int32_t)(key & ((1u << kPosBits) - 1));
+    }
+    // cell_start[c] = first sorted position whose cell id >= c
+    for (int c = threadIdx.x; c <= kGCells; c += kGridThreads) {
+        int lo = 0, hi = n;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            const uint32_t key = skey[mid];
+            if (key != kNone && (int)(key >> kPosBits) < c) lo = mid + 1; else hi = mid;
+        }
+        // keys outside the grid sit at the end: clamp the terminal offset to the number of in-grid keys
+        start[c] = lo;
+    }
+}
+
+// ---------------------------------------------------------------------------------------- GetFeaturesInArea batch
+struct AreaQuery { float x, y, r; int32_t min_level, max_level; };
+
+// warp per query.  out_start == nullptr: write the count to out_count[q]; else write the indices at out_start[q].
+__global__ void __launch_bounds__(256)
+area_query_kernel(const gforb_keypoint* __restrict__ keys, GridView g, const AreaQuery* __restrict__ qs, int nq,
+                  int32_t* __restrict__ out_count, const int32_t* __restrict__ out_start, int32_t* __restrict__ out_idx) {
+    const int lane = threadIdx.x & 31;
+    const int q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (q >= nq) return;
+    const AreaQuery a = qs[q];
+    int x0, x1, y0, y1, total = 0;
+    const int base = out_start ? out_start[q] : 0;
+    if (area_window(g, a.x, a.y, a.r, x0, x1, y0, y1)) {
+        for (int ix = x0; ix <= x1; ++ix) {
+            const int j0 = __ldg(g.start + ix * kGRows + y0), j1 = __ldg(g.start + ix * kGRows + y1 + 1);
+            for (int jb = j0; jb < j1; jb += 32) {                       // warp-uniform trip count (ballot inside)
+                const int j = jb + lane;
+                int i = -1;
+                bool ok = false;
+                if (j < j1) { i = __ldg(g.idx + j); ok = area_accepts(keys, i, a.x, a.y, a.r, a.min_level, a.max_level); }
+                const uint32_t m = __ballot_sync(0xFFFFFFFFu, ok);
+                if (ok && out_start) out_idx[base + total + __popc(m & ((1u << lane) - 1))] = i;
+                total += __popc(m);
+            }
+        }
+    }
+    if (!out_start && lane == 0) out_count[q] = total;
+}
+
+// ------------------------------------------------------------------------------------ SearchForInitialization
+
+namespace {
+struct Cand { uint32_t best, second; };      // keys: dist << 13 | CSR position
+
+// best / second-best of query (x, y, descriptor a) over its window, lanes striding each CSR run.
+// kFiltered: skip targets whose claim distance is <= the candidate's (src/ORBmatcher.cc:559-560).
+template <bool kFiltered>
+__device__ __forceinline__ Cand scan_window(const GridView& g, const gforb_keypoint* __restrict__ k2,
+                                            const uint4* __restrict__ d2, float x, float y, float r, const uint4& a0,
+                                            const uint4& a1, const uint32_t* claim, int lane) {
+    uint32_t best = kNone, second = kNone;
+    int x0, x1, y0, y1;
+    if (area_window(g, x, y, r, x0, x1, y0, y1)) {
+        for (int ix = x0; ix <= x1; ++ix) {
+            const int j0 = __ldg(g.start + ix * kGRows + y0), j1 = __ldg(g.start + ix * kGRows + y1 + 1);
+            for (int j = j0 + lane; j < j1; j += 32) {
+                const int i2 = __ldg(g.idx + j);
+                if (!area_accepts(k2, i2, x, y, r, 0, 0)) continue;        // level1 == 0: minLevel = maxLevel = 0
+                const int dist = hamming256(a0, a1, __ldg(d2 + 2 * (size_t)i2), __ldg(d2 + 2 * (size_t)i2 + 1));
+                if (kFiltered && (int)(claim[i2] >> 16) <= dist) continue;
+                const uint32_t key = ((uint32_t)dist << kPosBits) | (uint32_t)j;
+                second = min(second, max(best, key));
+                best = min(best, key);
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const uint32_t ob = __shfl_xor_sync(0xFFFFFFFFu, best, o), os = __shfl_xor_sync(0xFFFFFFFFu, second, o);
+        second = min(min(second, os), max(best, ob));
+        best = min(best, ob);
+    }
+    return {best, second};
+}
+}  // namespace
+
+// dynamic shared: claim[n2cap] u32 (dist << 16 | owner, 0xFFFFFFFF = free) | spec[n1cap] Cand | bin[n1cap] u8
+__global__ void __launch_bounds__(kSearchThreads)
+init_search_kernel(const InitSearchArgs a, int n1cap, int n2cap) {
+    extern __shared__ __align__(16) uint8_t sm_raw[];
+    uint32_t* claim = reinterpret_cast<uint32_t*>(sm_raw);
+    Cand* spec = reinterpret_cast<Cand*>(claim + n2cap);
+    uint8_t* bin = reinterpret_cast<uint8_t*>(spec + n1cap);
+    __shared__ int hist[kHisto];
+    __shared__ int keep_bin[3];
+    __shared__ int total;
+
+    const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int n1 = a.n1 ? min(a.n1[p], a.stride1) : a.n1_fixed;
+    const int n2 = a.n2 ? min(a.n2[p], a.stride2) : a.n2_fixed;
+    const gforb_keypoint* k1 = a.k1 + (size_t)p * a.stride1;
+    const gforb_keypoint* k2 = a.k2 + (size_t)p * a.stride2;
+    const uint4* d1 = reinterpret_cast<const uint4*>(a.d1) + 2 * (size_t)p * a.stride1;
+    const uint4* d2 = reinterpret_cast<const uint4*>(a.d2) + 2 * (size_t)p * a.stride2;
+    float* prev = a.prev_xy + 2 * (size_t)p * a.stride1;
+    int32_t* m12 = a.matches12 + (size_t)p * a.stride1;
+    GridView g{a.cell_start + (size_t)p * (kGCells + 1), a.cell_idx + (size_t)p * a.stride2, a.min_x, a.min_y, a.w_inv, a.h_inv};
+
+    for (int i = tid; i < n2; i += kSearchThreads) claim[i] = kNone;
+    for (int i = tid; i < n1; i += kSearchThreads) { bin[i] = 0xFF; m12[i] = -1; }
+    if (tid < kHisto) hist[tid] = 0;
+    if (tid == 0) total = 0;
+
+    // phase 1: speculative best / second-best, one warp per level-0 query
+    for (int q = wid; q < n1; q += kSearchThreads / 32) {
+        Cand c{kNone, kNone};
+        if (n2 > 0 && __ldg(&k1[q].octave) <= 0) {
+            const uint4 a0 = __ldg(d1 + 2 * (size_t)q), a1 = __ldg(d1 + 2 * (size_t)q + 1);
+            c = scan_window<false>(g, k2, d2, prev[2 * q], prev[2 * q + 1], a.window, a0, a1, nullptr, lane);
+        }
+        if (lane == 0) spec[q] = c;
+    }
+    __syncthreads();
+
+    // phase 2: the reference's sequential claim rule, queries in order, warp 0
+    if (wid == 0) {
+        for (int q = 0; q < n1; ++q) {
+            Cand c = spec[q];
+            if (c.best == kNone) continue;                                  // level > 0 or empty window
+            int ib = __ldg(g.idx + (c.best & ((1u << kPosBits) - 1)));
+            const int is = c.second == kNone ? -1 : __ldg(g.idx + (c.second & ((1u << kPosBits) - 1)));
+            const bool hidden = (int)(claim[ib] >> 16) <= (int)(c.best >> kPosBits) ||
+                                (is >= 0 && (int)(claim[is] >> 16) <= (int)(c.second >> kPosBits));
+            if (hidden) {
+                const uint4 a0 = __ldg(d1 + 2 * (size_t)q), a1 = __ldg(d1 + 2 * (size_t)q + 1);
+                c = scan_window<true>(g, k2, d2, prev[2 * q], prev[2 * q + 1], a.window, a0, a1, claim, lane);
+                if (c.best == kNone) continue;                              // bestDist stays INT_MAX
+                ib = __ldg(g.idx + (c.best & ((1u << kPosBits) - 1)));
+            }
+            const int bd = (int)(c.best >> kPosBits);
+            const int sd = c.second == kNone ? INT32_MAX : (int)(c.second >> kPosBits);
+            // src/ORBmatcher.cc:574-576
+            if (bd <= a.th_low && (float)bd < __fmul_rn((float)sd, a.ratio)) {
+                if (lane == 0) {
+                    const uint32_t old = claim[ib];
+                    if (old != kNone) m12[old & 0xFFFFu] = -1;              // take-over (:578-582)
+                    m12[q] = ib;
+                    claim[ib] = ((uint32_t)bd << 16) | (uint32_t)q;
+                    if (a.check_ori) {                                      // :588-597
+                        float rot = __fsub_rn(__ldg(&k1[q].angle), __ldg(&k2[ib].angle));
+                        if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+                        int b = (int)roundf(__fmul_rn(rot, 1.0f / kHisto));
+                        if (b == kHisto) b = 0;
+                        bin[q] = (uint8_t)b;
+                    }
+                }
+                __syncwarp();
+            }
+        }
+    }
+    __syncthreads();
+
+    // phase 3: rotation consistency (:601-622), vbPrevMatched update (:625-627), match count
+    if (a.check_ori) {
+        for (int q = tid; q < n1; q += kSearchThreads)
+            if (bin[q] != 0xFF) atomicAdd(&hist[bin[q]], 1);
+        __syncthreads();
+        if (tid == 0) {                                                     // ComputeThreeMaxima, :1723-1764
+            int max1 = 0, max2 = 0, max3 = 0, i1 = -1, i2 = -1, i3 = -1;
+            for (int i = 0; i < kHisto; ++i) {
+                const int s = hist[i];
+                if (s > max1) { max3 = max2; max2 = max1; max1 = s; i3 = i2; i2 = i1; i1 = i; }
+                else if (s > max2) { max3 = max2; max2 = s; i3 = i2; i2 = i; }
+                else if (s > max3) { max3 = s; i3 = i; }
+            }
+            if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { i2 = -1; i3 = -1; }
+            else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { i3 = -1; }
+            keep_bin[0] = i1; keep_bin[1] = i2; keep_bin[2] = i3;
+        }
+        __syncthreads();
+    }
+    int mine = 0;
+    for (int q = tid; q < n1; q += kSearchThreads) {
+        int m = m12[q];
+        if (m >= 0 && a.check_ori) {
+            const int b = bin[q];
+            if (b != keep_bin[0] && b != keep_bin[1] && b != keep_bin[2]) { m = -1; m12[q] = -1; }
+        }
+        if (m >= 0) {
+            prev[2 * q] = __ldg(&k2[m].x);
+            prev[2 * q + 1] = __ldg(&k2[m].y);
+            ++mine;
+        }
+    }
+    mine = __reduce_add_sync(0xFFFFFFFFu, mine);
+    if (lane == 0 && mine) atomicAdd(&total, mine);
+    __syncthreads();
+    if (tid == 0) a.nmatches[p] = total;
+}
+
+// --------------------------------------------------------------------------------------------------- launchers
+int gridmatch_max_keys() { return 1 << kPosBits; }
+int gridmatch_cells() { return kGCells; }
+
+static int pow2_at_least(int n) { int p = 2; while (p < n) p <<= 1; return p; }
+
+void launch_grid_build(const gforb_keypoint* keys, const int32_t* counts, int n_fixed, int key_stride, int nframes,
+                       const float* bounds, int32_t* cell_start, int32_t* cell_idx, cudaStream_t s) {
+    const float w_inv = 64.0f / (bounds[1] - bounds[0]), h_inv = 48.0f / (bounds[3] - bounds[2]);   // src/Frame.cc:129-130
+    const int np2 = pow2_at_least(std::max(counts ? key_stride : n_fixed, 2));
+    static bool attr = false;
+    if (!attr) { cudaFuncSetAttribute(grid_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << kPosBits); attr = true; }
+    grid_build_kernel<<<nframes, kGridThreads, (size_t)np2 * 4, s>>>(keys, counts, n_fixed, key_stride, bounds[0], bounds[2],
+                                                                     w_inv, h_inv, cell_start, cell_idx, np2);
+}
+
+void launch_area_query(const gforb_keypoint* keys, const float* bounds, const int32_t* cell_start, const int32_t* cell_idx,
+                       const void* queries, int nq, int32_t* out_count, const int32_t* out_start, int32_t* out_idx,
+                       cudaStream_t s) {
+    if (nq <= 0) return;
+    GridView g{cell_start, cell_idx, bounds[0], bounds[2], 64.0f / (bounds[1] - bounds[0]), 48.0f / (bounds[3] - bounds[2])};
+    area_query_kernel<<<(nq + 7) / 8, 256, 0, s>>>(keys, g, static_cast<const AreaQuery*>(queries), nq, out_count, out_start, out_idx);
+}
+
+size_t init_search_smem(int n1cap, int n2cap) { return (size_t)n2cap * 4 + (size_t)n1cap * 8 + (size_t)n1cap + 16; }
+
+int launch_init_search(const InitSearchArgs& a, const float* bounds, int npairs, cudaStream_t s) {
+    InitSearchArgs b = a;
+    b.min_x = bounds[0]; b.min_y = bounds[2];
+    b.w_inv = 64.0f / (bounds[1] - bounds[0]); b.h_inv = 48.0f / (bounds[3] - bounds[2]);
+    const int n1cap = std::max(a.n1 ? a.stride1 : a.n1_fixed, 1), n2cap = std::max(a.n2 ? a.stride2 : a.n2_fixed, 1);
+    const size_t smem = init_search_smem(n1cap, n2cap);
+    static size_t attr_have = 0;
+    if (smem > attr_have) {
+        if (cudaFuncSetAttribute(init_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
+        attr_have = smem;
+    }
+    init_search_kernel<<<npairs, kSearchThreads, smem, s>>>(b, n1cap, n2cap);
+    return 0;
+}
+
+}  // namespace gforb

@@ -141,6 +141,50 @@ GFORB_API int gforb_match_bruteforce_device(gforb_matcher* m, const uint8_t* dev
                                   int32_t* dev_second_dist, int32_t* dev_match, void* cuda_stream);
 /* wait for the last device-form call and return its device time (CUDA events around its two kernels) */
 GFORB_API int gforb_matcher_sync(gforb_matcher* m, float* last_ms_or_null);
+/* =====================================================================================================
+ * Frame feature grid and ORBmatcher::SearchForInitialization   
+ *   Frame::AssignFeaturesToGrid / PosInGrid   src/Frame.cc:461-476, 645-656; mGrid include/Frame.h:369
+ *   Frame::GetFeaturesInArea                  src/Frame.cc:593-643
+ *   ORBmatcher::SearchForInitialization       src/ORBmatcher.cc:520-633 (+ ComputeThreeMaxima :1723-1764)
+ * The grid is the reference's FRAME_GRID_COLS x FRAME_GRID_ROWS = 64 x 48 (include/Frame.h:92-93) over the image
+ * bounds mnMinX..mnMaxY (src/Frame.cc:760-887; without distortion {0, cols, 0, rows}).  mGrid[ix][iy] is returned
+ * as one CSR: cell_idx = key indices ordered by (ix, iy, push_back order), cell_start[ix * 48 + iy] = first entry of
+ * the cell, cell_start[64 * 48] = number of keys inside the grid.  At most 8,192 keys per frame (GFORB_ERR_CAPACITY).
+ * All float arithmetic is the reference's (float, un-fused); results are bit-identical, candidate order included.
+ * ===================================================================================================== */
+#define GFORB_FRAME_GRID_COLS 64
+#define GFORB_FRAME_GRID_ROWS 48
+typedef struct gforb_frame_bounds { float min_x, max_x, min_y, max_y; } gforb_frame_bounds;   /* mnMinX, mnMaxX, mnMinY, mnMaxY */
+/* one GetFeaturesInArea(x, y, r, minLevel, maxLevel) call; pass -1, -1 for the reference's default levels */
+typedef struct gforb_area_query { float x, y, r; int32_t min_level, max_level; } gforb_area_query;
+
+/* Frame::AssignFeaturesToGrid.  cell_start: 64*48+1 ints, cell_idx: n ints (host). */
+GFORB_API int gforb_assign_features_to_grid(gforb_matcher* m, const gforb_frame_bounds* bounds, const gforb_keypoint* keys,
+                                  int n, int32_t* cell_start, int32_t* cell_idx);
+/* nq independent Frame::GetFeaturesInArea calls on one frame: query q's indices (in the reference's vIndices order) are
+ * out_idx[out_start[q] .. out_start[q+1]).  out_start: nq+1 ints.  GFORB_ERR_CAPACITY (nothing truncated) if the total
+ * exceeds `cap`; out_start is still complete then, so the caller can size the retry. */
+GFORB_API int gforb_features_in_area(gforb_matcher* m, const gforb_frame_bounds* bounds, const gforb_keypoint* keys, int n,
+                           const gforb_area_query* queries, int nq, int32_t* out_start, int32_t* out_idx, int cap);
+/* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) with mfNNratio = the matcher's
+ * ratio and mbCheckOrientation = check_orientation.  keys1/desc1 = F1.mvKeysUn / F1.mDescriptors (n1 rows), keys2/desc2
+ * = F2's; the grid of F2 is built internally.  prev_matched_xy: n1 x 2 floats, in/out (vbPrevMatched: window centres
+ * in, matched F2 positions out).  matches12: n1 ints out (-1 = none).  *nmatches = the reference's return value. */
+GFORB_API int gforb_search_for_initialization(gforb_matcher* m, const gforb_frame_bounds* bounds,
+                                    const gforb_keypoint* keys1, const uint8_t* desc1, int n1,
+                                    const gforb_keypoint* keys2, const uint8_t* desc2, int n2,
+                                    float* prev_matched_xy, int window_size, int check_orientation,
+                                    int32_t* matches12, int* nmatches);
+/* Batched device form: n_pairs independent frame pairs, one CTA each, asynchronous on `cuda_stream` (or the matcher's
+ * own).  Pair p reads keys at dev_keysX + p * strideX (elements), descriptors at dev_descX + p * strideX * 32, counts
+ * dev_nX[p] (<= strideX; NULL = every pair has strideX keys) -- the layout gforb_batch keeps its keypoints in.
+ * dev_prev_xy: [pair][stride1][2] in/out, dev_matches12: [pair][stride1], dev_nmatches: [pair].  Descriptor arrays
+ * must be 16-byte aligned.  2 launches (grid build, search); gforb_matcher_sync returns their device time. */
+GFORB_API int gforb_search_for_initialization_batch_device(gforb_matcher* m, const gforb_frame_bounds* bounds, int n_pairs,
+                                    const gforb_keypoint* dev_keys1, const uint8_t* dev_desc1, const int32_t* dev_n1, int stride1,
+                                    const gforb_keypoint* dev_keys2, const uint8_t* dev_desc2, const int32_t* dev_n2, int stride2,
+                                    float* dev_prev_xy, int window_size, int check_orientation,
+                                    int32_t* dev_matches12, int32_t* dev_nmatches, void* cuda_stream);
 /* device memory helpers for callers without a CUDA runtime of their own (tests, bench): cudaMalloc / cudaFree /
  * synchronous cudaMemcpy; dir 0 = host->device, 1 = device->host */
 GFORB_API int gforb_device_alloc(void** dev_ptr, size_t bytes);

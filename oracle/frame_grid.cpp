@@ -1,0 +1,172 @@
+// ORACLE -- TEST INFRASTRUCTURE ONLY.  CPU restatement of the Frame feature grid and of
+// ORBmatcher::SearchForInitialization, written as the reference writes them (sequential loops, std::vector
+// push_back order), so the CUDA path's parallel reformulation can be checked against the literal algorithm.
+//
+//   Frame::AssignFeaturesToGrid   /root/reference/src/Frame.cc:461-476
+//   Frame::PosInGrid              /root/reference/src/Frame.cc:645-656
+//   Frame::GetFeaturesInArea      /root/reference/src/Frame.cc:593-643
+//   grid constants                /root/reference/include/Frame.h:92-93 (64 x 48), src/Frame.cc:129-130
+//   ORBmatcher::SearchForInitialization   /root/reference/src/ORBmatcher.cc:520-633
+//   ORBmatcher::ComputeThreeMaxima        /root/reference/src/ORBmatcher.cc:1723-1764
+//   HISTO_LENGTH = 30, TH_LOW = 50        /root/reference/src/ORBmatcher.cc:37-39
+//
+// Parity note: the reference's own tests hold no vectors for these functions (parity unpinned by the reference);
+// tests/test_oracle_grid.py checks this file against an independent pure-numpy restatement.
+#include <climits>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+#include "gforb_oracle.h"
+
+namespace {
+constexpr int kCols = 64, kRows = 48, kHisto = 30;
+
+struct Grid {
+    float minX, minY, wInv, hInv;
+    std::vector<int> cell[kCols][kRows];
+};
+
+// src/Frame.cc:129-130: static_cast<float>(FRAME_GRID_COLS) / (mnMaxX - mnMinX), all float
+void grid_scales(const float* bounds, float* wInv, float* hInv) {
+    *wInv = static_cast<float>(kCols) / (bounds[1] - bounds[0]);
+    *hInv = static_cast<float>(kRows) / (bounds[3] - bounds[2]);
+}
+
+// src/Frame.cc:645-656: round() on float (half away from zero), then the range test
+bool pos_in_grid(const Grid& g, const orc_keypoint& kp, int* px, int* py) {
+    *px = (int)std::round((kp.x - g.minX) * g.wInv);
+    *py = (int)std::round((kp.y - g.minY) * g.hInv);
+    return !(*px < 0 || *px >= kCols || *py < 0 || *py >= kRows);
+}
+
+void build_grid(Grid& g, const orc_keypoint* keys, int n, const float* bounds) {
+    g.minX = bounds[0]; g.minY = bounds[2];
+    grid_scales(bounds, &g.wInv, &g.hInv);
+    for (int i = 0; i < n; ++i) {                      // src/Frame.cc:468-475: ascending i, push_back
+        int px, py;
+        if (pos_in_grid(g, keys[i], &px, &py)) g.cell[px][py].push_back(i);
+    }
+}
+
+// src/Frame.cc:593-643, statement for statement
+std::vector<int> features_in_area(const Grid& g, const orc_keypoint* keys, float x, float y, float r, int minLevel,
+                                  int maxLevel) {
+    std::vector<int> out;
+    const int nMinCellX = std::max(0, (int)std::floor((x - g.minX - r) * g.wInv));
+    if (nMinCellX >= kCols) return out;
+    const int nMaxCellX = std::min(kCols - 1, (int)std::ceil((x - g.minX + r) * g.wInv));
+    if (nMaxCellX < 0) return out;
+    const int nMinCellY = std::max(0, (int)std::floor((y - g.minY - r) * g.hInv));
+    if (nMinCellY >= kRows) return out;
+    const int nMaxCellY = std::min(kRows - 1, (int)std::ceil((y - g.minY + r) * g.hInv));
+    if (nMaxCellY < 0) return out;
+    const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+    for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+        for (int iy = nMinCellY; iy <= nMaxCellY; iy++)
+            for (int idx : g.cell[ix][iy]) {
+                const orc_keypoint& kp = keys[idx];
+                if (bCheckLevels) {
+                    if (kp.octave < minLevel) continue;
+                    if (maxLevel >= 0 && kp.octave > maxLevel) continue;
+                }
+                const float distx = kp.x - x, disty = kp.y - y;
+                if (std::fabs(distx) < r && std::fabs(disty) < r) out.push_back(idx);
+            }
+    return out;
+}
+
+// src/ORBmatcher.cc:1723-1764 (sizes instead of vectors)
+void three_maxima(const int* size, int L, int& ind1, int& ind2, int& ind3) {
+    int max1 = 0, max2 = 0, max3 = 0;
+    for (int i = 0; i < L; i++) {
+        const int s = size[i];
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+        else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+}
+}  // namespace
+
+extern "C" {
+
+int orc_assign_features_to_grid(const orc_keypoint* keys, int n, const float* bounds, int* cell_start, int* cell_idx) {
+    Grid g;
+    build_grid(g, keys, n, bounds);
+    int k = 0;
+    for (int ix = 0; ix < kCols; ++ix)
+        for (int iy = 0; iy < kRows; ++iy) {
+            cell_start[ix * kRows + iy] = k;
+            for (int idx : g.cell[ix][iy]) cell_idx[k++] = idx;
+        }
+    cell_start[kCols * kRows] = k;
+    return k;
+}
+
+int orc_features_in_area(const orc_keypoint* keys, int n, const float* bounds, float x, float y, float r, int minLevel,
+                         int maxLevel, int* out, int cap) {
+    Grid g;
+    build_grid(g, keys, n, bounds);
+    std::vector<int> v = features_in_area(g, keys, x, y, r, minLevel, maxLevel);
+    for (int i = 0; i < (int)v.size() && i < cap; ++i) out[i] = v[i];
+    return (int)v.size();
+}
+
+int orc_search_for_initialization(const orc_keypoint* k1, const uint8_t* d1, int n1, const orc_keypoint* k2,
+                                  const uint8_t* d2, int n2, const float* bounds, float* prev_xy, int windowSize,
+                                  float nnratio, int checkOri, int* matches12) {
+    Grid g;
+    build_grid(g, k2, n2, bounds);
+    int nmatches = 0;
+    for (int i = 0; i < n1; ++i) matches12[i] = -1;
+    std::vector<int> rotHist[kHisto];
+    const float factor = 1.0f / kHisto;
+    std::vector<int> vMatchedDistance(n2, INT_MAX), vnMatches21(n2, -1);
+    for (int i1 = 0; i1 < n1; i1++) {
+        const int level1 = k1[i1].octave;
+        if (level1 > 0) continue;
+        std::vector<int> vIndices2 =
+            features_in_area(g, k2, prev_xy[2 * i1], prev_xy[2 * i1 + 1], (float)windowSize, level1, level1);
+        if (vIndices2.empty()) continue;
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (int i2 : vIndices2) {
+            const int dist = orc_hamming256(d1 + 32 * (size_t)i1, d2 + 32 * (size_t)i2);
+            if (vMatchedDistance[i2] <= dist) continue;
+            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+            else if (dist < bestDist2) bestDist2 = dist;
+        }
+        if (bestDist <= 50) {
+            if (bestDist < (float)bestDist2 * nnratio) {
+                if (vnMatches21[bestIdx2] >= 0) { matches12[vnMatches21[bestIdx2]] = -1; nmatches--; }
+                matches12[i1] = bestIdx2;
+                vnMatches21[bestIdx2] = i1;
+                vMatchedDistance[bestIdx2] = bestDist;
+                nmatches++;
+                if (checkOri) {
+                    float rot = k1[i1].angle - k2[bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)std::round(rot * factor);
+                    if (bin == kHisto) bin = 0;
+                    rotHist[bin].push_back(i1);
+                }
+            }
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1, sizes[kHisto];
+        for (int i = 0; i < kHisto; ++i) sizes[i] = (int)rotHist[i].size();
+        three_maxima(sizes, kHisto, ind1, ind2, ind3);
+        for (int i = 0; i < kHisto; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx1 : rotHist[i])
+                if (matches12[idx1] >= 0) { matches12[idx1] = -1; nmatches--; }
+        }
+    }
+    for (int i1 = 0; i1 < n1; i1++)
+        if (matches12[i1] >= 0) { prev_xy[2 * i1] = k2[matches12[i1]].x; prev_xy[2 * i1 + 1] = k2[matches12[i1]].y; }
+    return nmatches;
+}
+
+}  // extern "C"

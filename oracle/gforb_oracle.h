@@ -73,6 +73,17 @@ double orc_bench_stereo(const uint8_t* images, int nimg, int w, int h, int nfram
 void  orc_match_bruteforce(const uint8_t* a, int nA, const uint8_t* b, int nB, float ratio, int threshold,
                            int* best_idx, int* best_dist, int* second_dist, int* match, int nthreads);
 
+/* Frame feature grid + ORBmatcher::SearchForInitialization (oracle/frame_grid.cpp; reference src/Frame.cc:461-476,
+ * 593-656, src/ORBmatcher.cc:520-633,1723-1764).  bounds = {mnMinX, mnMaxX, mnMinY, mnMaxY}; the grid is the
+ * reference's 64 x 48.  cell_start: 64*48+1 ints in (ix, iy) order (ix major, as mGrid[ix][iy]); cell_idx: n ints. */
+int   orc_assign_features_to_grid(const orc_keypoint* keys, int n, const float* bounds, int* cell_start, int* cell_idx);
+int   orc_features_in_area(const orc_keypoint* keys, int n, const float* bounds, float x, float y, float r,
+                           int minLevel, int maxLevel, int* out, int cap);
+/* prev_xy: n1 x 2 floats, in/out (vbPrevMatched); matches12: n1 ints out; returns nmatches */
+int   orc_search_for_initialization(const orc_keypoint* k1, const uint8_t* d1, int n1, const orc_keypoint* k2,
+                                    const uint8_t* d2, int n2, const float* bounds, float* prev_xy, int windowSize,
+                                    float nnratio, int checkOri, int* matches12);
+
 #ifdef __cplusplus
 }
 #endif

@@ -84,6 +84,14 @@ def lib():
     L.orc_bench_stereo.restype = C.c_double
     L.orc_match_bruteforce.argtypes = [u8p, C.c_int, u8p, C.c_int, C.c_float, C.c_int, ip, ip, ip, ip, C.c_int]
     L.orc_match_bruteforce.restype = None
+    L.orc_assign_features_to_grid.argtypes = [C.c_void_p, C.c_int, fp, ip, ip]
+    L.orc_assign_features_to_grid.restype = C.c_int
+    L.orc_features_in_area.argtypes = [C.c_void_p, C.c_int, fp, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int,
+                                       ip, C.c_int]
+    L.orc_features_in_area.restype = C.c_int
+    L.orc_search_for_initialization.argtypes = [C.c_void_p, u8p, C.c_int, C.c_void_p, u8p, C.c_int, fp, fp, C.c_int,
+                                                C.c_float, C.c_int, ip]
+    L.orc_search_for_initialization.restype = C.c_int
     _LIB = L
     return L
 
@@ -254,3 +262,37 @@ def match_bruteforce(desc_a, desc_b, ratio=0.6, threshold=50, nthreads=1):
     lib().orc_match_bruteforce(_p(a), len(a), _p(b), len(b), ratio, threshold, _p(bi), _p(bd), _p(sd), _p(m), nthreads)
     k = len(a)
     return dict(best_idx=bi[:k], best_dist=bd[:k], second_dist=sd[:k], match=m[:k])
+
+
+GRID_COLS, GRID_ROWS = 64, 48
+
+
+def _bounds(bounds):
+    return np.ascontiguousarray(bounds, dtype=np.float32)
+
+
+def assign_features_to_grid(keys, bounds):
+    """Frame::AssignFeaturesToGrid (src/Frame.cc:461-476) as CSR over mGrid[ix][iy] (ix major)."""
+    keys = np.ascontiguousarray(keys); b = _bounds(bounds)
+    start = np.zeros(GRID_COLS * GRID_ROWS + 1, np.int32); idx = np.zeros(max(len(keys), 1), np.int32)
+    n = lib().orc_assign_features_to_grid(_p(keys), len(keys), _p(b), _p(start), _p(idx))
+    return start, idx[:n]
+
+
+def features_in_area(keys, bounds, x, y, r, min_level=-1, max_level=-1):
+    """Frame::GetFeaturesInArea (src/Frame.cc:593-643)."""
+    keys = np.ascontiguousarray(keys); b = _bounds(bounds)
+    out = np.zeros(max(len(keys), 1), np.int32)
+    n = lib().orc_features_in_area(_p(keys), len(keys), _p(b), x, y, r, min_level, max_level, _p(out), len(out))
+    return out[:n]
+
+
+def search_for_initialization(k1, d1, k2, d2, bounds, prev_xy, window_size=100, nnratio=0.9, check_ori=True):
+    """ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:520-633).  Returns (nmatches, matches12, prev_xy')."""
+    k1 = np.ascontiguousarray(k1); k2 = np.ascontiguousarray(k2)
+    d1 = np.ascontiguousarray(d1, dtype=np.uint8); d2 = np.ascontiguousarray(d2, dtype=np.uint8)
+    prev = np.array(prev_xy, dtype=np.float32, order="C", copy=True).reshape(len(k1), 2)
+    m12 = np.full(max(len(k1), 1), -1, np.int32)
+    n = lib().orc_search_for_initialization(_p(k1), _p(d1), len(k1), _p(k2), _p(d2), len(k2), _p(_bounds(bounds)),
+                                            _p(prev), int(window_size), nnratio, int(bool(check_ori)), _p(m12))
+    return n, m12[:len(k1)], prev

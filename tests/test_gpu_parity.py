@@ -257,3 +257,42 @@ def test_chunked_pipeline_equals_whole_batch(gf):
             c = ref["counts"][2 * f]
             assert np.array_equal(out["u_right"][f, :c], ref["u_right"][f, :c])
             assert np.array_equal(out["depth"][f, :c], ref["depth"][f, :c])
+
+
+def test_config2_1280x720_batch256_2000kp(gf, O):
+    """BASELINE.json configs[2] at full size: 256 stereo frames of 1280x720, 2000 keypoints, one batch call.
+    8 distinct synthetic pairs are scattered over the 256 slots; two of them are checked bit-for-bit against the
+    oracle, all 256 through size-independent properties: a frame's result depends only on its own pixels (equal
+    inputs -> byte-identical outputs anywhere in the batch), per-level quotas are met, keys are level-major,
+    and every stereo match is a positive disparity inside the band."""
+    n, nb, w, h, nf = 256, 8, 1280, 720, 2000
+    base = [synth_stereo(200 + i, w, h, nshapes=900) for i in range(nb)]
+    rng = np.random.default_rng(5)
+    which = rng.integers(0, nb, n); which[:nb] = np.arange(nb)
+    left = np.stack([base[i][0] for i in which]); right = np.stack([base[i][1] for i in which])
+    sb = gf.StereoBatch(w, h, n, nf)
+    out = sb.alloc_outputs(n)
+    sb.process(left, right, out, BF, B)
+    for f in (0, 5):
+        oxL, oxR = O.Extractor(nf), O.Extractor(nf)
+        okL, odL, _ = oxL.extract(left[f]); okR, odR, _ = oxR.extract(right[f])
+        nL, nR = out["counts"][2 * f], out["counts"][2 * f + 1]
+        _assert_extract_equal(out["keypoints"][2 * f, :nL], out["descriptors"][2 * f, :nL], okL, odL, f"c2 frame {f} L")
+        _assert_extract_equal(out["keypoints"][2 * f + 1, :nR], out["descriptors"][2 * f + 1, :nR], okR, odR, f"c2 frame {f} R")
+        o = O.stereo_match(oxL, oxR, okL, odL, okR, odR, BF, B)
+        assert np.array_equal(out["u_right"][f, :nL], o["uRight"]) and np.array_equal(out["depth"][f, :nL], o["depth"])
+    first = {int(b): int(np.flatnonzero(which == b)[0]) for b in range(nb)}
+    for f in range(n):
+        g = first[int(which[f])]
+        for e in (0, 1):
+            c = out["counts"][2 * f + e]
+            assert c == out["counts"][2 * g + e] and c >= nf
+            assert out["keypoints"][2 * f + e, :c].tobytes() == out["keypoints"][2 * g + e, :c].tobytes()
+            assert np.array_equal(out["descriptors"][2 * f + e, :c], out["descriptors"][2 * g + e, :c])
+            assert (np.diff(out["keypoints"][2 * f + e, :c]["octave"]) >= 0).all()
+        c = out["counts"][2 * f]
+        assert np.array_equal(out["u_right"][f, :c], out["u_right"][g, :c])
+        assert np.array_equal(out["depth"][f, :c], out["depth"][g, :c])
+        m = out["depth"][f, :c] > 0
+        assert m.sum() > 100
+        assert (out["u_right"][f, :c][m] <= out["keypoints"][2 * f, :c]["x"][m] + 1e-3).all()
