@@ -252,7 +252,33 @@ def main():
     barrier()
     ms2 = torch.tensor([e0.elapsed_time(e1)], device="cuda")
     launches_e2e = sb.last_launches() * args.steps
-    e2e_value = aggregate_throughput(F, args.steps, ms2, world, dist)
+    e2e_blocking = aggregate_throughput(F, args.steps, ms2, world, dist)
+
+    # ---------------- end-to-end arm, streaming form: two batch handles used alternately ----------------
+    # gforb_stereo_frames_batch_async: step i is submitted on handle i % 2 after that handle's previous step has
+    # completed, so the exposed tail of one step (last kernels + downloads) overlaps the uploads of the next.  Every
+    # step still moves its own inputs host->device and its own results device->host inside the timed region; all
+    # results are on the host when the clock stops.
+    sb2 = gf.StereoBatch(W, H, F, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH)
+    sb2.set_stream(torch.cuda.Stream().cuda_stream)
+    sb2.set_chunk(args.chunk)
+    out2 = sb2.alloc_outputs(F)
+    hs, outs = (sb, sb2), (out, out2)
+    for i in range(4):
+        hs[i % 2].sync(); hs[i % 2].submit(pin_l.array, pin_r.array, outs[i % 2], BF, B)
+    sb.sync(); sb2.sync()
+    barrier()
+    t_e2e = time.perf_counter()
+    e0.record(stream)
+    for i in range(args.steps):
+        hs[i % 2].sync(); hs[i % 2].submit(pin_l.array, pin_r.array, outs[i % 2], BF, B)
+    sb2.sync(); sb.sync()              # sb last: its stream carries e1
+    e1.record(stream)
+    barrier()
+    wall_ms = (time.perf_counter() - t_e2e) * 1e3
+    ms3 = torch.tensor([max(e0.elapsed_time(e1), 0.0)], device="cuda")
+    e2e_value = aggregate_throughput(F, args.steps, ms3, world, dist)
+    assert np.array_equal(out["counts"], out2["counts"]) and np.array_equal(out["depth"], out2["depth"])
     K = sb.K
     h2d = 2 * F * W * H
     d2h = 2 * F * 4 + 2 * F * K * 28 + 2 * F * K * 32 + 2 * F * K * 4
@@ -283,11 +309,29 @@ def main():
         gbs = per_launch[k] / (t * 1e-3) / 1e9 if t > 0 else 0.0
         stages[k] = {"ms": round(t, 4), "share": round(t / sum(stage_ms.values()), 4),
                      "alg_bytes": int(per_launch[k]), "gbs": round(gbs, 1), "frac_hbm": round(gbs / peak, 4)}
+    # DRAM traffic and issue-slot utilisation per stage from the committed ncu capture of this same command
+    # (profiles/ncu_latest.json, written by tools/ncu_to_json.py; only meaningful at the captured batch size)
+    prof_file = ROOT / "profiles" / "ncu_latest.json"
+    if prof_file.exists():
+        prof = json.loads(prof_file.read_text())
+        if prof.get("frames_per_step") == F:
+            kmap = {"pyramid": ("pyr_level0_fast_kernel", "pyr_resize_fast_kernel"), "fast": ("fast_cells_kernel",),
+                    "quadtree": ("octree_kernel",), "blur": ("blur_kernel",), "describe": ("describe_kernel",),
+                    "stereo": ("stereo_kernel",)}
+            for k, names in kmap.items():
+                ks = [prof["kernels"][n] for n in names if n in prof["kernels"]]
+                if k in stages and len(ks) == len(names):
+                    tt = sum(x["time_us"] for x in ks)
+                    stages[k]["ncu_dram_bytes"] = int(sum(x["dram_bytes"] for x in ks))
+                    stages[k]["ncu_issue_active_pct"] = round(sum(x["issue_active_pct"] * x["time_us"] for x in ks) / tt, 1)
     ach = stages[dom]["gbs"]
     roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": None, "peak_source": peak_src, "launches_in_stage": NLEVELS if dom == "pyramid" else 1,
-                "note": "FAST/quadtree/describe/stereo are integer/LSU/latency-bound (SURVEY.md 8d); the HBM fraction "
-                        "is reported for every stage under 'stages'"}
+                "traffic": stages[dom].get("ncu_dram_bytes"), "issue_active_pct": stages[dom].get("ncu_issue_active_pct"),
+                "peak_source": peak_src, "launches_in_stage": NLEVELS if dom == "pyramid" else 1,
+                "note": "FAST/quadtree/describe/stereo are integer/LSU/latency-bound (SURVEY.md 8d): their ceiling is the "
+                        "warp-instruction issue rate (issue_active_pct, ncu smsp__issue_active of the committed capture), "
+                        "not HBM; the HBM fraction is still reported for every stage under 'stages'; traffic = "
+                        "dram__bytes_read+write per launch from profiles/ncu_latest.json"}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -298,6 +342,8 @@ def main():
                        "mean_keypoints_per_image": round(n_kp, 1), "fast_candidates_per_image": n_cand},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "gpu_launches": launches_e2e,
+                    "api": "gforb_stereo_frames_batch_async on two batch handles used alternately + gforb_batch_sync",
+                    "blocking_single_handle": e2e_blocking, "wall_ms_per_step": wall_ms / args.steps,
                     "pipeline": "chunks of %s frames: H2D / kernels / D2H of successive chunks overlap (2 copy + 4 kernel streams)" % (args.chunk or "8,24,32..,16,8 (auto)")},
             "gpu_launches": launches_value,
             "clocks": clocks, "roofline": roofline, "stages": stages}

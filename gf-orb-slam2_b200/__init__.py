@@ -82,6 +82,7 @@ _SIGS = {
     "gforb_batch_download": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp]),
     "gforb_batch_sync": (_i, [_vp]),
     "gforb_stereo_frames_batch": (_i, [_vp, _vp, _vp, _i, C.POINTER(StereoParams), _vp, _vp, _vp, _vp, _vp]),
+    "gforb_stereo_frames_batch_async": (_i, [_vp, _vp, _vp, _i, C.POINTER(StereoParams), _vp, _vp, _vp, _vp, _vp]),
     "gforb_batch_launches_per_run": (_i, [_vp, _i]),
     "gforb_batch_last_launches": (_i, [_vp]),
     "gforb_batch_set_chunk": (_i, [_vp, _i]),
@@ -497,3 +498,13 @@ class StereoBatch:
         _check(_L.gforb_stereo_frames_batch(self._h, _p(left), _p(right), n, C.byref(prm), _p(out.get("counts")),
                                             _p(out.get("keypoints")), _p(out.get("descriptors")),
                                             _p(out.get("u_right")), _p(out.get("depth"))))
+
+    def submit(self, left, right, out, bf, b, mode=STEREO_CLASSIC):
+        """process() without the final wait (gforb_stereo_frames_batch_async): `left`, `right` and `out` must stay
+        alive and untouched until sync() returns.  Alternate two StereoBatch objects to overlap consecutive batches."""
+        n = left.shape[0]
+        prm = _stereo_params(bf, b, mode, TH_HIGH, TH_LOW, 0.0)
+        self._inflight = (left, right, out)
+        _check(_L.gforb_stereo_frames_batch_async(self._h, _p(left), _p(right), n, C.byref(prm), _p(out.get("counts")),
+                                                  _p(out.get("keypoints")), _p(out.get("descriptors")),
+                                                  _p(out.get("u_right")), _p(out.get("depth"))))

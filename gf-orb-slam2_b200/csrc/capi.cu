@@ -787,9 +787,9 @@ int gforb_batch_set_chunk(gforb_batch* b, int frames) {
 // Host buffers in, host buffers out.  The batch is cut into chunks; chunk c's H2D copy (upload stream), its
 // kernels (the batch's stream) and its D2H copy (download stream) are chained with events, so the copy engines
 // and the SMs work on different chunks at any time (kernels of even/odd chunks on two streams).  Results are complete when this returns.
-int gforb_stereo_frames_batch(gforb_batch* b, const uint8_t* left, const uint8_t* right, int n,
-                              const gforb_stereo_params* prm, int32_t* counts, gforb_keypoint* kps,
-                              uint8_t* desc, float* u_right, float* depth) {
+int gforb_stereo_frames_batch_async(gforb_batch* b, const uint8_t* left, const uint8_t* right, int n,
+                                    const gforb_stereo_params* prm, int32_t* counts, gforb_keypoint* kps,
+                                    uint8_t* desc, float* u_right, float* depth) {
     if (!b || !left || !right || n < 1 || n > b->max_frames) { set_error("gforb_stereo_frames_batch: bad arguments"); return GFORB_ERR_ARG; }
     // chunk schedule: fixed size when the caller set one; otherwise a short first chunk (the pipeline fills after
     // 8 frames' worth of H2D), 32-frame chunks in the middle, and a short tail (its kernels + D2H are exposed)
@@ -848,7 +848,14 @@ int gforb_stereo_frames_batch(gforb_batch* b, const uint8_t* left, const uint8_t
     GB(cudaEventRecord(b->ev_down, b->s_down), "cudaEventRecord");
     GB(cudaStreamWaitEvent(b->stream, b->ev_down, 0), "cudaStreamWaitEvent");
 #undef GB
-    return gforb_batch_sync(b);
+    return GFORB_OK;
+}
+
+int gforb_stereo_frames_batch(gforb_batch* b, const uint8_t* left, const uint8_t* right, int n,
+                              const gforb_stereo_params* prm, int32_t* counts, gforb_keypoint* kps,
+                              uint8_t* desc, float* u_right, float* depth) {
+    const int rc = gforb_stereo_frames_batch_async(b, left, right, n, prm, counts, kps, desc, u_right, depth);
+    return rc ? rc : gforb_batch_sync(b);
 }
 
 }  // extern "C"

@@ -257,6 +257,15 @@ GFORB_API int gforb_stereo_frames_batch(gforb_batch* b, const uint8_t* left, con
                               const gforb_stereo_params* prm, int32_t* counts, gforb_keypoint* keypoints,
                               uint8_t* descriptors, float* u_right, float* depth);
 
+/* The same without the final wait: returns once everything is enqueued; outputs are complete (and the overflow flags
+ * checked) when gforb_batch_sync(b) returns.  The host buffers must stay untouched until then and should be pinned
+ * (gforb_host_alloc), otherwise the copies serialise.  Two batch handles used alternately (submit A, submit B, sync A,
+ * submit A, ...) keep the PCIe link busy across consecutive batches: the tail of one batch (its last kernels and
+ * downloads) overlaps the uploads of the next. */
+GFORB_API int gforb_stereo_frames_batch_async(gforb_batch* b, const uint8_t* left, const uint8_t* right, int n_frames,
+                                    const gforb_stereo_params* prm, int32_t* counts, gforb_keypoint* keypoints,
+                                    uint8_t* descriptors, float* u_right, float* depth);
+
 /* gforb_stereo_frames_batch pipelines the batch in chunks of `frames` stereo frames (H2D of chunk c+1, kernels of
  * chunk c and D2H of chunk c-1 overlap on separate streams); 0 = automatic (16 when the batch has >= 48 frames) */
 GFORB_API int gforb_batch_set_chunk(gforb_batch* b, int frames);

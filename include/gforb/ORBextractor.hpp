@@ -3,6 +3,7 @@
 //   ORB_SLAM2::ORBextractor            include/ORBextractor.h:76-168   (ctor, operator(), ComputePyramid, Get*, mvImagePyramid)
 //   ORB_SLAM2::ORBmatcher::DescriptorDistance / TH_HIGH / TH_LOW        include/ORBmatcher.h:49,  src/ORBmatcher.cc:37-38
 //   Frame::ComputeStereoMatches / ComputeStereoMatches_Undistorted      src/Frame.cc:889-1078, 1167-1316
+//   ORBmatcher::SearchForInitialization, Frame::AssignFeaturesToGrid / GetFeaturesInArea   src/ORBmatcher.cc:520-633, src/Frame.cc:461-476,593-643
 // Define GFORB_WITH_OPENCV (and have OpenCV headers) to get the cv::InputArray / cv::KeyPoint / cv::Mat
 // overloads the reference's Frame.cc / Tracking.cc use; without it the same calls take plain buffers.
 // Like the reference, nothing here throws for an empty image (silent no-op); CUDA/argument failures throw
@@ -124,14 +125,83 @@ protected:
     bool pyramid_stale_ = true;
 };
 
+// The members of ORB_SLAM2::Frame that the matcher searches read (include/Frame.h:279-296,358-369): undistorted keys,
+// descriptors (N x 32, row stride 32) and the image bounds the 64 x 48 feature grid spans.
+struct Point2f { float x, y; };                 // layout of cv::Point2f
+struct FrameView {
+    const std::vector<gforb_keypoint>* mvKeysUn;
+    const uint8_t* mDescriptors;
+    gforb_frame_bounds bounds;                  // mnMinX, mnMaxX, mnMinY, mnMaxY
+};
+
 class ORBmatcher {
 public:
     static const int TH_LOW = GFORB_TH_LOW;
     static const int TH_HIGH = GFORB_TH_HIGH;
+    static const int HISTO_LENGTH = 30;
     static int DescriptorDistance(const uint8_t* a, const uint8_t* b) { return gforb_hamming256(a, b); }
 #ifdef GFORB_WITH_OPENCV
     static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b) { return gforb_hamming256(a.data, b.data); }
 #endif
+    // include/ORBmatcher.h:46
+    ORBmatcher(float nnratio = 0.6f, bool checkOri = true) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
+    ~ORBmatcher() { if (h_) gforb_matcher_destroy(h_); }
+    ORBmatcher(const ORBmatcher&) = delete;
+    ORBmatcher& operator=(const ORBmatcher&) = delete;
+
+    // src/ORBmatcher.cc:520-633.  PointT = cv::Point2f or gforb::Point2f.
+    template <class PointT>
+    int SearchForInitialization(const FrameView& F1, const FrameView& F2, std::vector<PointT>& vbPrevMatched,
+                                std::vector<int>& vnMatches12, int windowSize = 10) {
+        static_assert(sizeof(PointT) == 2 * sizeof(float), "vbPrevMatched must hold {float x, y}");
+        const int n1 = (int)F1.mvKeysUn->size(), n2 = (int)F2.mvKeysUn->size();
+        vnMatches12.assign(n1, -1);
+        if ((int)vbPrevMatched.size() < n1) throw std::runtime_error("SearchForInitialization: vbPrevMatched too short");
+        int nmatches = 0;
+        check(gforb_search_for_initialization(handle(), &F2.bounds, F1.mvKeysUn->data(), F1.mDescriptors, n1,
+                                              F2.mvKeysUn->data(), F2.mDescriptors, n2,
+                                              reinterpret_cast<float*>(vbPrevMatched.data()), windowSize,
+                                              mbCheckOrientation ? 1 : 0, vnMatches12.data(), &nmatches),
+              "SearchForInitialization");
+        return nmatches;
+    }
+    gforb_matcher* handle() {
+        if (!h_) check(gforb_matcher_create(mfNNratio, &h_), "ORBmatcher");
+        return h_;
+    }
+
+protected:
+    float mfNNratio;
+    bool mbCheckOrientation;
+    gforb_matcher* h_ = nullptr;
+};
+
+// Frame::AssignFeaturesToGrid + GetFeaturesInArea (src/Frame.cc:461-476, 593-643): mGrid as one CSR.
+class FrameGrid {
+public:
+    FrameGrid(ORBmatcher& m, const std::vector<gforb_keypoint>& mvKeysUn, const gforb_frame_bounds& b)
+        : m_(m), keys_(mvKeysUn), b_(b), start_(GFORB_FRAME_GRID_COLS * GFORB_FRAME_GRID_ROWS + 1), idx_(mvKeysUn.size() + 1) {
+        check(gforb_assign_features_to_grid(m_.handle(), &b_, keys_.data(), (int)keys_.size(), start_.data(), idx_.data()),
+              "AssignFeaturesToGrid");
+    }
+    // mGrid[ix][iy]
+    std::vector<size_t> cell(int ix, int iy) const {
+        const int c = ix * GFORB_FRAME_GRID_ROWS + iy;
+        return std::vector<size_t>(idx_.begin() + start_[c], idx_.begin() + start_[c + 1]);
+    }
+    std::vector<size_t> GetFeaturesInArea(float x, float y, float r, int minLevel = -1, int maxLevel = -1) const {
+        gforb_area_query q{x, y, r, minLevel, maxLevel};
+        std::vector<int32_t> st(2), out(keys_.size() + 1);
+        check(gforb_features_in_area(m_.handle(), &b_, keys_.data(), (int)keys_.size(), &q, 1, st.data(), out.data(),
+                                     (int)out.size()), "GetFeaturesInArea");
+        return std::vector<size_t>(out.begin(), out.begin() + st[1]);
+    }
+
+private:
+    ORBmatcher& m_;
+    const std::vector<gforb_keypoint>& keys_;
+    gforb_frame_bounds b_;
+    std::vector<int32_t> start_, idx_;
 };
 
 // Frame::ComputeStereoMatches(): fills mvuRight / mvDepth from the Frame's members (src/Frame.cc:889-1078).

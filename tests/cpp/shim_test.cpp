@@ -42,6 +42,18 @@ int main(int argc, char** argv) {
                (unsigned long long)fnv(kL.data(), kL.size() * sizeof(gforb_keypoint)), (unsigned long long)fnv(dL.data(), dL.size()),
                (unsigned long long)fnv(kR.data(), kR.size() * sizeof(gforb_keypoint)), (unsigned long long)fnv(dR.data(), dR.size()),
                (unsigned long long)fnv(u.data(), u.size() * 4), (unsigned long long)fnv(z.data(), z.size() * 4));
+        // the two eyes as two frames: SearchForInitialization + the feature grid through the C++ mirror
+        gforb::ORBmatcher matcher(0.9f, true);
+        gforb::FrameView F1{&kL, dL.data(), {0.f, (float)w, 0.f, (float)h}}, F2{&kR, dR.data(), {0.f, (float)w2, 0.f, (float)h2}};
+        std::vector<gforb::Point2f> prev(kL.size());
+        for (size_t i = 0; i < kL.size(); ++i) prev[i] = {kL[i].x, kL[i].y};
+        std::vector<int> m12;
+        const int ninit = matcher.SearchForInitialization(F1, F2, prev, m12, 100);
+        gforb::FrameGrid grid(matcher, kR, F2.bounds);
+        const std::vector<size_t> area = grid.GetFeaturesInArea(w2 / 2.f, h2 / 2.f, 60.f, 0, 2);
+        printf("init nmatches=%d m12=%016llx prev=%016llx area=%zu area_hash=%016llx\n", ninit,
+               (unsigned long long)fnv(m12.data(), m12.size() * 4), (unsigned long long)fnv(prev.data(), prev.size() * 8),
+               area.size(), (unsigned long long)fnv(area.data(), area.size() * sizeof(size_t)));
         // an empty image is the reference's silent no-op
         std::vector<gforb_keypoint> k0; std::vector<uint8_t> d0;
         exL(nullptr, 0, 0, 0, k0, d0);

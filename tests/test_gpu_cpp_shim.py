@@ -39,6 +39,14 @@ def test_cpp_shim_matches_ctypes(fixtures):
     assert int(hs["kR"], 16) == _fnv(kR) and int(hs["dR"], 16) == _fnv(dR)
     assert int(hs["u"], 16) == _fnv(s["mvuRight"]) and int(hs["z"], 16) == _fnv(s["mvDepth"])
     assert "empty ok=1" in out.stdout
+    # SearchForInitialization + feature grid through the C++ mirror == the ctypes mirror
+    mi = re.search(r"init nmatches=(\d+) .* area=(\d+) ", out.stdout)
+    prev = np.stack([kL["x"], kL["y"]], axis=1).astype(np.float32)
+    n, m12 = gf.ORBmatcher(0.9, True).SearchForInitialization(kL, dL, kR, dR, prev, 100, width=752, height=480)
+    area = gf.FrameGrid(kR, width=752, height=480).GetFeaturesInArea([(376.0, 240.0, 60.0, 0, 2)])[0]
+    assert (int(mi[1]), int(mi[2])) == (n, len(area)) and n > 0 and len(area) > 0
+    assert int(hs["m12"], 16) == _fnv(m12) and int(hs["prev"], 16) == _fnv(prev)
+    assert int(hs["area_hash"], 16) == _fnv(area.astype(np.uint64))
 
 
 def test_tma_probe():

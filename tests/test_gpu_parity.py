@@ -296,3 +296,40 @@ def test_config2_1280x720_batch256_2000kp(gf, O):
         m = out["depth"][f, :c] > 0
         assert m.sum() > 100
         assert (out["u_right"][f, :c][m] <= out["keypoints"][2 * f, :c]["x"][m] + 1e-3).all()
+
+
+def test_async_submit_on_two_handles_equals_blocking(gf):
+    """gforb_stereo_frames_batch_async: batches submitted alternately on two handles (consecutive batches overlap on
+    the device) give byte-identical host outputs to the blocking call."""
+    n = 5
+    sets = []
+    for s in range(3):
+        pairs = [synth_stereo(60 + 10 * s + i, nshapes=200) for i in range(n)]
+        sets.append((np.stack([p[0] for p in pairs]), np.stack([p[1] for p in pairs])))
+    a, b = gf.StereoBatch(752, 480, n), gf.StereoBatch(752, 480, n)
+    ref = []
+    for l, r in sets:
+        o = a.alloc_outputs(n, pinned=False)
+        a.process(l, r, o, BF, B)
+        ref.append(o)
+    hs = (a, b)
+    pins = [(gf.PinnedArray(l.shape, np.uint8), gf.PinnedArray(r.shape, np.uint8)) for l, r in sets]
+    outs = [hs[i % 2].alloc_outputs(n) for i in range(3)]
+    for i, (l, r) in enumerate(sets):
+        pins[i][0].array[:] = l; pins[i][1].array[:] = r
+        for v in outs[i].values():
+            v[...] = 0
+    for i in range(3):
+        hs[i % 2].sync()
+        hs[i % 2].submit(pins[i][0].array, pins[i][1].array, outs[i], BF, B)
+    a.sync(); b.sync()
+    for i in range(3):
+        assert np.array_equal(outs[i]["counts"], ref[i]["counts"])
+        for j in range(2 * n):
+            c = ref[i]["counts"][j]
+            assert outs[i]["keypoints"][j, :c].tobytes() == ref[i]["keypoints"][j, :c].tobytes()
+            assert np.array_equal(outs[i]["descriptors"][j, :c], ref[i]["descriptors"][j, :c])
+        for f in range(n):
+            c = ref[i]["counts"][2 * f]
+            assert np.array_equal(outs[i]["u_right"][f, :c], ref[i]["u_right"][f, :c])
+            assert np.array_equal(outs[i]["depth"][f, :c], ref[i]["depth"][f, :c])
