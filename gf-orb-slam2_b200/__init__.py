@@ -98,6 +98,11 @@ _SIGS = {
     "gforb_search_for_initialization": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _vp, C.POINTER(_i)]),
     "gforb_search_for_initialization_batch_device": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i,
                                                           _vp, _vp, _vp]),
+    "gforb_rectifier_create": (_i, [_vp, _vp, _i, _i, C.POINTER(_vp)]),
+    "gforb_rectifier_destroy": (None, [_vp]),
+    "gforb_preprocess": (_i, [_vp, _vp, _i, _i, _sz, _i, _vp, _sz]),
+    "gforb_preprocess_batch_device": (_i, [_vp, _vp, _i, _i, _sz, _sz, _i, _i, _vp, _sz, _sz, _vp]),
+    "gforb_rectifier_sync": (_i, [_vp, C.POINTER(C.c_float)]),
     "gforb_device_alloc": (_i, [C.POINTER(_vp), _sz]),
     "gforb_device_free": (None, [_vp]),
     "gforb_device_copy": (_i, [_vp, _vp, _sz, _i]),
@@ -161,7 +166,7 @@ class DeviceArray:
 
     def __del__(self):
         p = getattr(self, "_ptr", None)
-        if p:
+        if p and _L is not None:
             _L.gforb_device_free(p)
             self._ptr = None
 
@@ -180,7 +185,7 @@ class ORBmatcher:
 
     def __del__(self):
         h = getattr(self, "_h", None)
-        if h:
+        if h and _L is not None:
             _L.gforb_matcher_destroy(h)
             self._h = None
 
@@ -302,7 +307,7 @@ class ORBextractor:
 
     def __del__(self):
         h = getattr(self, "_h", None)
-        if h:
+        if h and _L is not None:
             _L.gforb_extractor_destroy(h)
             self._h = None
 
@@ -430,7 +435,7 @@ class StereoBatch:
 
     def __del__(self):
         h = getattr(self, "_h", None)
-        if h:
+        if h and _L is not None:
             _L.gforb_batch_destroy(h)
             self._h = None
 
@@ -508,3 +513,51 @@ class StereoBatch:
         _check(_L.gforb_stereo_frames_batch_async(self._h, _p(left), _p(right), n, C.byref(prm), _p(out.get("counts")),
                                                   _p(out.get("keypoints")), _p(out.get("descriptors")),
                                                   _p(out.get("u_right")), _p(out.get("depth"))))
+
+
+PIX_GRAY8, PIX_GRAY16, PIX_RGB8, PIX_BGR8, PIX_RGBA8, PIX_BGRA8 = range(6)
+_PIX_BPP = (1, 2, 3, 3, 4, 4)
+
+
+class Rectifier:
+    """The pre-processing the reference runs in front of the extractor, fused: [16-bit -> high byte] -> cv::remap(M1, M2,
+    INTER_LINEAR) (ros_stereo.cc:290-295, test_Stereo.cpp:197-210) -> cvtColor(*2GRAY) (src/Tracking.cc:366-382).
+    M1/M2: float32 [h, w] maps of one camera (None: no remap)."""
+
+    def __init__(self, M1=None, M2=None):
+        self._h = _vp()
+        self.shape = None
+        if M1 is not None:
+            M1 = np.ascontiguousarray(M1, np.float32); M2 = np.ascontiguousarray(M2, np.float32)
+            assert M1.shape == M2.shape and M1.ndim == 2
+            self.shape = M1.shape
+            _check(_L.gforb_rectifier_create(_p(M1), _p(M2), M1.shape[1], M1.shape[0], C.byref(self._h)))
+        else:
+            _check(_L.gforb_rectifier_create(None, None, 0, 0, C.byref(self._h)))
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h and _L is not None:
+            _L.gforb_rectifier_destroy(h)
+            self._h = None
+
+    def __call__(self, image, pixel_format=PIX_GRAY8):
+        """host image [h, w] (gray8 / gray16) or [h, w, 3|4] u8 -> rectified 8-bit gray image"""
+        assert image.strides[-1] == image.itemsize and (image.ndim == 2 or image.strides[1] == image.shape[2])
+        sh, sw = image.shape[:2]
+        assert image.itemsize * (image.shape[2] if image.ndim == 3 else 1) == _PIX_BPP[pixel_format]
+        dh, dw = self.shape or (sh, sw)
+        out = np.empty((dh, dw), np.uint8)
+        _check(_L.gforb_preprocess(self._h, _p(image), sw, sh, image.strides[0], pixel_format, _p(out), dw))
+        return out
+
+    def batch_device(self, dev_src, src_w, src_h, src_pitch, src_stride, pixel_format, n, dev_dst, dst_pitch, dst_stride,
+                     stream=None):
+        ptr = lambda x: None if x is None else _vp(x.ptr if isinstance(x, DeviceArray) else x)
+        _check(_L.gforb_preprocess_batch_device(self._h, ptr(dev_src), src_w, src_h, src_pitch, src_stride, pixel_format, n,
+                                                ptr(dev_dst), dst_pitch, dst_stride, _vp(stream) if stream else None))
+
+    def sync(self):
+        ms = C.c_float(0)
+        _check(_L.gforb_rectifier_sync(self._h, C.byref(ms)))
+        return ms.value

@@ -608,6 +608,97 @@ int gforb_search_for_initialization(gforb_matcher* m, const gforb_frame_bounds* 
     return GFORB_OK;
 }
 
+// ------------------------------------------------------------------------------------------- pre-processing
+struct gforb_rectifier {
+    int w = 0, h = 0;
+    float* mapx = nullptr; float* mapy = nullptr;
+    cudaStream_t stream = nullptr, last = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+    void* io = nullptr; size_t io_bytes = 0;
+    ~gforb_rectifier() {
+        if (mapx) cudaFree(mapx);
+        if (mapy) cudaFree(mapy);
+        if (io) cudaFree(io);
+        if (ev0) cudaEventDestroy(ev0);
+        if (ev1) cudaEventDestroy(ev1);
+        if (stream) cudaStreamDestroy(stream);
+    }
+};
+
+int gforb_rectifier_create(const float* map_x, const float* map_y, int w, int h, gforb_rectifier** out) {
+    if (!out || (map_x == nullptr) != (map_y == nullptr) || (map_x && (w <= 0 || h <= 0))) { set_error("gforb_rectifier_create: bad arguments"); return GFORB_ERR_ARG; }
+    std::unique_ptr<gforb_rectifier> r(new (std::nothrow) gforb_rectifier);
+    if (!r) return GFORB_ERR_ARG;
+    int rc = ensure_stream(r->stream);
+    if (rc) return rc;
+    M_CUDA(cudaEventCreate(&r->ev0));
+    M_CUDA(cudaEventCreate(&r->ev1));
+    if (map_x) {
+        r->w = w; r->h = h;
+        const size_t bytes = (size_t)w * h * sizeof(float);
+        M_CUDA(cudaMalloc(&r->mapx, bytes));
+        M_CUDA(cudaMalloc(&r->mapy, bytes));
+        M_CUDA(cudaMemcpy(r->mapx, map_x, bytes, cudaMemcpyHostToDevice));
+        M_CUDA(cudaMemcpy(r->mapy, map_y, bytes, cudaMemcpyHostToDevice));
+    }
+    *out = r.release();
+    return GFORB_OK;
+}
+void gforb_rectifier_destroy(gforb_rectifier* r) { delete r; }
+
+int gforb_preprocess_batch_device(gforb_rectifier* r, const void* src, int sw, int sh, size_t spitch, size_t sstride, int fmt,
+                                  int n, uint8_t* dst, size_t dpitch, size_t dstride, void* cuda_stream) {
+    const int bpp = preprocess_bytes_per_pixel(fmt);
+    if (!r || !src || !dst || sw <= 0 || sh <= 0 || n < 0 || n > 65535 || bpp == 0 || spitch < (size_t)sw * bpp) { set_error("gforb_preprocess: bad arguments"); return GFORB_ERR_ARG; }
+    const int dw = r->mapx ? r->w : sw, dh = r->mapx ? r->h : sh;
+    if (dpitch < (size_t)dw) { set_error("gforb_preprocess: dst_pitch < output width"); return GFORB_ERR_ARG; }
+    if ((unsigned long long)spitch * (unsigned long long)sh > 0xFFFFFFFFull) { set_error("gforb_preprocess: source image larger than 4 GB"); return GFORB_ERR_ARG; }
+    if (fmt == GFORB_PIX_GRAY16 && (((uintptr_t)src | spitch | sstride) & 1)) { set_error("gforb_preprocess: 16-bit source must be 2-byte aligned"); return GFORB_ERR_ARG; }
+    if (n == 0) return GFORB_OK;
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : r->stream;
+    r->last = s;
+    M_CUDA(cudaEventRecord(r->ev0, s));
+    launch_preprocess(static_cast<const uint8_t*>(src), sw, sh, spitch, sstride, fmt, r->mapx, r->mapy, dst, dw, dh, dpitch, dstride, n, s);
+    M_CUDA(cudaEventRecord(r->ev1, s));
+    M_CUDA(cudaGetLastError());
+    r->timed = true;
+    return GFORB_OK;
+}
+
+int gforb_rectifier_sync(gforb_rectifier* r, float* last_ms) {
+    if (!r) return GFORB_ERR_ARG;
+    M_CUDA(cudaStreamSynchronize(r->last ? r->last : r->stream));
+    if (last_ms) {
+        *last_ms = 0.f;
+        if (r->timed) M_CUDA(cudaEventElapsedTime(last_ms, r->ev0, r->ev1));
+    }
+    return GFORB_OK;
+}
+
+int gforb_preprocess(gforb_rectifier* r, const void* src, int sw, int sh, size_t spitch, int fmt, uint8_t* dst, size_t dpitch) {
+    const int bpp = preprocess_bytes_per_pixel(fmt);
+    if (!r || !src || !dst || sw <= 0 || sh <= 0 || bpp == 0 || spitch < (size_t)sw * bpp) { set_error("gforb_preprocess: bad arguments"); return GFORB_ERR_ARG; }
+    const int dw = r->mapx ? r->w : sw, dh = r->mapx ? r->h : sh;
+    if (dpitch < (size_t)dw) { set_error("gforb_preprocess: dst_pitch < output width"); return GFORB_ERR_ARG; }
+    const size_t srow = ((size_t)sw * bpp + 15) & ~(size_t)15, drow = ((size_t)dw + 15) & ~(size_t)15;
+    const size_t need = srow * sh + drow * dh;
+    if (need > r->io_bytes) {
+        if (r->io) { cudaFree(r->io); r->io = nullptr; r->io_bytes = 0; }
+        M_CUDA(cudaMalloc(&r->io, need));
+        r->io_bytes = need;
+    }
+    uint8_t* dsrc = static_cast<uint8_t*>(r->io);
+    uint8_t* ddst = dsrc + srow * sh;
+    cudaStream_t s = r->stream;
+    M_CUDA(cudaMemcpy2DAsync(dsrc, srow, src, spitch, (size_t)sw * bpp, sh, cudaMemcpyHostToDevice, s));
+    int rc = gforb_preprocess_batch_device(r, dsrc, sw, sh, srow, 0, fmt, 1, ddst, drow, 0, nullptr);
+    if (rc) return rc;
+    M_CUDA(cudaMemcpy2DAsync(dst, dpitch, ddst, drow, (size_t)dw, dh, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaStreamSynchronize(s));
+    return GFORB_OK;
+}
+
 int gforb_device_alloc(void** p, size_t bytes) {
     if (!p) return GFORB_ERR_ARG;
     M_CUDA(cudaMalloc(p, std::max<size_t>(bytes, 16)));

@@ -165,6 +165,10 @@ void launch_area_query(const gforb_keypoint* keys, const float* bounds, const in
                        const void* queries, int nq, int32_t* out_count, const int32_t* out_start, int32_t* out_idx,
                        cudaStream_t s);
 int launch_init_search(const InitSearchArgs& a, const float* bounds, int npairs, cudaStream_t s);   // 1 launch; -1: smem opt-in failed
+// input pre-processing (k_preprocess.cu): [16 -> 8 bit] -> remap -> gray; 1 launch.  fmt: gforb.h GFORB_PIX_*
+int preprocess_bytes_per_pixel(int fmt);
+void launch_preprocess(const uint8_t* src, int sw, int sh, size_t spitch, size_t sstride, int fmt, const float* mapx,
+                       const float* mapy, uint8_t* dst, int dw, int dh, size_t dpitch, size_t dstride, int nimg, cudaStream_t s);
 size_t octree_smem_bytes(const Geom& g);
 int fast_configure(const Geom& g);     // opt in to the FAST kernel's dynamic smem; returns cudaError_t as int
 int octree_configure(const Geom& g);   // opt in to large dynamic smem; returns cudaError_t as int

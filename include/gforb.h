@@ -185,6 +185,32 @@ GFORB_API int gforb_search_for_initialization_batch_device(gforb_matcher* m, con
                                     const gforb_keypoint* dev_keys2, const uint8_t* dev_desc2, const int32_t* dev_n2, int stride2,
                                     float* dev_prev_xy, int window_size, int check_orientation,
                                     int32_t* dev_matches12, int32_t* dev_nmatches, void* cuda_stream);
+/* =====================================================================================================
+ * Input pre-processing in front of ORBextractor::operator()   (SURVEY.md 8f row 3), one fused kernel:
+ *   16-bit -> 8-bit   cv::imread(IMREAD_GRAYSCALE) of 16-bit PNGs keeps the high byte   test/test_Stereo.cpp:100-106
+ *   rectification     cv::remap(src, dst, M1, M2, cv::INTER_LINEAR), CV_32F maps, BORDER_CONSTANT 0
+ *                     Examples/ROS/GF_ORB_SLAM2/src/ros_stereo.cc:290-295; test/test_Stereo.cpp:197-210
+ *   colour -> gray    cv::cvtColor(CV_RGB2GRAY | CV_BGR2GRAY | CV_RGBA2GRAY | CV_BGRA2GRAY)   src/Tracking.cc:366-382
+ * in that order (the reference rectifies in the caller and converts inside Tracking).  Bit-identical to OpenCV's 8U
+ * fixed-point paths (5 fractional bits per axis in remap, Q15 gray weights).  gforb_rectifier carries one camera's
+ * maps M1 (x) and M2 (y) on the device -- what cv::initUndistortRectifyMap(..., CV_32F, M1, M2) returns, dst_w x dst_h
+ * floats each, tightly packed; NULL maps = no remap (then the output has the source size).
+ * ===================================================================================================== */
+enum { GFORB_PIX_GRAY8 = 0, GFORB_PIX_GRAY16 = 1, GFORB_PIX_RGB8 = 2, GFORB_PIX_BGR8 = 3, GFORB_PIX_RGBA8 = 4, GFORB_PIX_BGRA8 = 5 };
+typedef struct gforb_rectifier gforb_rectifier;
+GFORB_API int gforb_rectifier_create(const float* map_x, const float* map_y, int dst_w, int dst_h, gforb_rectifier** out);
+GFORB_API void gforb_rectifier_destroy(gforb_rectifier* r);
+/* one host image in, one host 8-bit gray image out (dst_w x dst_h, or src size without maps) */
+GFORB_API int gforb_preprocess(gforb_rectifier* r, const void* src, int src_w, int src_h, size_t src_pitch, int pixel_format,
+                     uint8_t* dst, size_t dst_pitch);
+/* n_images device-resident images (image i at dev_src + i * src_image_stride bytes) -> device gray images, e.g.
+ * straight into gforb_batch_device_input's buffer; asynchronous on cuda_stream (NULL: the rectifier's own).  1 launch. */
+GFORB_API int gforb_preprocess_batch_device(gforb_rectifier* r, const void* dev_src, int src_w, int src_h, size_t src_pitch,
+                                  size_t src_image_stride, int pixel_format, int n_images, uint8_t* dev_dst,
+                                  size_t dst_pitch, size_t dst_image_stride, void* cuda_stream);
+/* wait for the last device-form call; *last_ms = its device time */
+GFORB_API int gforb_rectifier_sync(gforb_rectifier* r, float* last_ms_or_null);
+
 /* device memory helpers for callers without a CUDA runtime of their own (tests, bench): cudaMalloc / cudaFree /
  * synchronous cudaMemcpy; dir 0 = host->device, 1 = device->host */
 GFORB_API int gforb_device_alloc(void** dev_ptr, size_t bytes);

@@ -84,6 +84,12 @@ int   orc_search_for_initialization(const orc_keypoint* k1, const uint8_t* d1, i
                                     const uint8_t* d2, int n2, const float* bounds, float* prev_xy, int windowSize,
                                     float nnratio, int checkOri, int* matches12);
 
+/* Pre-processing in front of the extractor (oracle/preprocess.cpp): [16-bit -> high byte] -> cv::remap(INTER_LINEAR,
+ * BORDER_CONSTANT 0, CV_32F maps; NULL maps = none, then dw x dh must equal the source size) -> cvtColor(*2GRAY).
+ * fmt: 0 gray8, 1 gray16, 2 RGB8, 3 BGR8, 4 RGBA8, 5 BGRA8. */
+int   orc_preprocess(const void* src, int sw, int sh, size_t spitch, int fmt, const float* mapx, const float* mapy,
+                     int dw, int dh, uint8_t* dst, size_t dpitch);
+
 #ifdef __cplusplus
 }
 #endif

@@ -92,6 +92,8 @@ def lib():
     L.orc_search_for_initialization.argtypes = [C.c_void_p, u8p, C.c_int, C.c_void_p, u8p, C.c_int, fp, fp, C.c_int,
                                                 C.c_float, C.c_int, ip]
     L.orc_search_for_initialization.restype = C.c_int
+    L.orc_preprocess.argtypes = [C.c_void_p, C.c_int, C.c_int, sz, C.c_int, fp, fp, C.c_int, C.c_int, u8p, sz]
+    L.orc_preprocess.restype = C.c_int
     _LIB = L
     return L
 
@@ -296,3 +298,21 @@ def search_for_initialization(k1, d1, k2, d2, bounds, prev_xy, window_size=100, 
     n = lib().orc_search_for_initialization(_p(k1), _p(d1), len(k1), _p(k2), _p(d2), len(k2), _p(_bounds(bounds)),
                                             _p(prev), int(window_size), nnratio, int(bool(check_ori)), _p(m12))
     return n, m12[:len(k1)], prev
+
+
+PIX_GRAY8, PIX_GRAY16, PIX_RGB8, PIX_BGR8, PIX_RGBA8, PIX_BGRA8 = range(6)
+
+
+def preprocess(src, fmt, mapx=None, mapy=None):
+    """[16-bit -> 8-bit] -> cv::remap(INTER_LINEAR, constant 0 border) -> cvtColor(*2GRAY); see oracle/preprocess.cpp."""
+    src = np.ascontiguousarray(src)
+    sh, sw = src.shape[:2]
+    if mapx is not None:
+        mapx = np.ascontiguousarray(mapx, np.float32); mapy = np.ascontiguousarray(mapy, np.float32)
+        dh, dw = mapx.shape
+    else:
+        dh, dw = sh, sw
+    dst = np.empty((dh, dw), np.uint8)
+    rc = lib().orc_preprocess(_p(src), sw, sh, src.strides[0], fmt, _p(mapx), _p(mapy), dw, dh, _p(dst), dw)
+    assert rc == 0
+    return dst

@@ -54,3 +54,17 @@ def synth_stereo(seed, w=752, h=480, nshapes=400, dmin=2.0, dmax=60.0):
     left = base + rng.normal(0, 2.0, base.shape)
     right = right + rng.normal(0, 2.0, base.shape)
     return (np.clip(np.rint(left), 0, 255).astype(np.uint8), np.clip(np.rint(right), 0, 255).astype(np.uint8))
+
+
+def rectify_maps(w, h, k1=-0.28, k2=0.07, tilt=0.012, shift=(3.25, -2.5), scale=1.04):
+    """Deterministic float32 rectification maps (M1 = x, M2 = y) of a radial-distortion + small-rotation camera, using
+    only correctly-rounded float32 operations (+ - * /), so every machine computes identical bits.  Parts of the
+    destination map outside the source on purpose (constant-0 border of cv::remap)."""
+    f = np.float32
+    yy, xx = np.meshgrid(np.arange(h, dtype=np.float32), np.arange(w, dtype=np.float32), indexing="ij")
+    cx, cy, fl = f(w / 2 - 0.5), f(h / 2 - 0.5), f(0.6 * w)
+    x = (xx - cx) / fl * f(scale); y = (yy - cy) / fl * f(scale)
+    xr = x - f(tilt) * y; yr = y + f(tilt) * x
+    r2 = xr * xr + yr * yr
+    d = f(1) + f(k1) * r2 + f(k2) * r2 * r2
+    return (xr * d * fl + cx + f(shift[0])).astype(np.float32), (yr * d * fl + cy + f(shift[1])).astype(np.float32)

@@ -112,3 +112,45 @@ def test_match_bruteforce_oracle_vs_numpy():
         ok = (best <= th) & (best.astype(np.float32) < second.astype(np.float32) * np.float32(ratio))
         assert np.array_equal(r["best_idx"], idx) and np.array_equal(r["best_dist"], best)
         assert np.array_equal(r["second_dist"], second) and np.array_equal(r["match"], np.where(ok, idx, -1))
+
+
+# ---- pre-processing (oracle/preprocess.cpp) against the genuine cv2.remap / cv2.cvtColor ----
+def _maps_cases(w, h):
+    from synth import rectify_maps
+    rng = np.random.default_rng(5)
+    yield rectify_maps(w, h)
+    yield rectify_maps(w, h, k1=0.35, k2=-0.1, tilt=-0.05, shift=(-40.0, 25.5), scale=1.3)      # large out-of-source areas
+    mx = (rng.random((h, w), dtype=np.float32) * (w + 40) - 20).astype(np.float32)               # random gather, all fractions
+    my = (rng.random((h, w), dtype=np.float32) * (h + 40) - 20).astype(np.float32)
+    mx[:4, :64] = (np.arange(64, dtype=np.float32) / 32 - 1.5); my[:4, :64] = np.float32(-0.5)  # 1/32 steps around the border
+    mx[4:8, :64] = np.float32(w) - np.arange(64, dtype=np.float32) / 32; my[4:8, :64] = np.float32(h) - np.arange(64, dtype=np.float32) / 64
+    yield mx, my
+
+
+def test_preprocess_remap_gray8_vs_cv2(fixtures):
+    im = fixtures["EuRoC_l"]
+    h, w = im.shape
+    for mx, my in _maps_cases(w, h):
+        assert np.array_equal(O.preprocess(im, O.PIX_GRAY8, mx, my), cv2.remap(im, mx, my, cv2.INTER_LINEAR))
+    mx, my = next(_maps_cases(320, 200))                       # destination smaller than the source
+    assert np.array_equal(O.preprocess(im, O.PIX_GRAY8, mx, my), cv2.remap(im, mx, my, cv2.INTER_LINEAR))
+
+
+def test_preprocess_colour_and_16bit_vs_cv2():
+    rng = np.random.default_rng(6)
+    h, w = 120, 168
+    mx, my = next(_maps_cases(w, h))
+    for fmt, code, ch in ((O.PIX_RGB8, cv2.COLOR_RGB2GRAY, 3), (O.PIX_BGR8, cv2.COLOR_BGR2GRAY, 3),
+                          (O.PIX_RGBA8, cv2.COLOR_RGBA2GRAY, 4), (O.PIX_BGRA8, cv2.COLOR_BGRA2GRAY, 4)):
+        im = rng.integers(0, 256, (h, w, ch), dtype=np.uint8)
+        assert np.array_equal(O.preprocess(im, fmt), cv2.cvtColor(im, code))
+        # reference order: remap in the caller (per channel), cvtColor inside Tracking
+        assert np.array_equal(O.preprocess(im, fmt, mx, my), cv2.cvtColor(cv2.remap(im, mx, my, cv2.INTER_LINEAR), code))
+    im16 = rng.integers(0, 65536, (h, w), dtype=np.uint16)
+    hi = (im16 >> 8).astype(np.uint8)
+    assert np.array_equal(O.preprocess(im16, O.PIX_GRAY16), hi)
+    assert np.array_equal(O.preprocess(im16, O.PIX_GRAY16, mx, my), cv2.remap(hi, mx, my, cv2.INTER_LINEAR))
+    # every (R, G, B) on a coarse lattice + the extremes
+    lat = np.stack(np.meshgrid(np.arange(0, 256, 5), np.arange(0, 256, 3), np.arange(0, 256, 7), indexing="ij"), -1)
+    lat = np.ascontiguousarray(lat.reshape(1, -1, 3).astype(np.uint8))
+    assert np.array_equal(O.preprocess(lat, O.PIX_RGB8), cv2.cvtColor(lat, cv2.COLOR_RGB2GRAY))
