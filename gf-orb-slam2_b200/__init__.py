@@ -103,6 +103,9 @@ _SIGS = {
     "gforb_preprocess": (_i, [_vp, _vp, _i, _i, _sz, _i, _vp, _sz]),
     "gforb_preprocess_batch_device": (_i, [_vp, _vp, _i, _i, _sz, _sz, _i, _i, _vp, _sz, _sz, _vp]),
     "gforb_rectifier_sync": (_i, [_vp, C.POINTER(C.c_float)]),
+    "gforb_undistort_keypoints": (_i, [_vp, _vp, _vp, _i, _vp]),
+    "gforb_undistort_keypoints_batch_device": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp]),
+    "gforb_compute_image_bounds": (_i, [_vp, _vp, _i, _i, _vp]),
     "gforb_device_alloc": (_i, [C.POINTER(_vp), _sz]),
     "gforb_device_free": (None, [_vp]),
     "gforb_device_copy": (_i, [_vp, _vp, _sz, _i]),
@@ -561,3 +564,34 @@ class Rectifier:
         ms = C.c_float(0)
         _check(_L.gforb_rectifier_sync(self._h, C.byref(ms)))
         return ms.value
+
+
+class Camera(C.Structure):
+    """gforb_camera: mK, mDistCoef (k1 k2 p1 p2 k3 k4 k5 k6), mR, left 3x3 of mP -- doubles, row-major."""
+    _fields_ = [("K", C.c_double * 9), ("dist", C.c_double * 8), ("R", C.c_double * 9), ("P", C.c_double * 9)]
+
+    @classmethod
+    def make(cls, K, dist, R=None, P=None):
+        K = np.asarray(K, np.float64).reshape(3, 3)
+        d = np.zeros(8); dd = np.asarray(dist, np.float64).ravel(); d[:len(dd)] = dd
+        R = np.eye(3) if R is None else np.asarray(R, np.float64).reshape(3, 3)
+        P = K if P is None else np.asarray(P, np.float64)[:3, :3]          # Frame::UndistortKeyPoints passes P = mK
+        c = cls()
+        c.K[:] = K.ravel().tolist(); c.dist[:] = d.tolist(); c.R[:] = R.ravel().tolist(); c.P[:] = np.ascontiguousarray(P).ravel().tolist()
+        return c
+
+
+def UndistortKeyPoints(matcher, camera, keys):
+    """Frame::UndistortKeyPoints / UndistortKeyPointsStereo (src/Frame.cc:670-758): mvKeys -> mvKeysUn."""
+    keys = np.ascontiguousarray(keys, KP_DTYPE)
+    out = np.empty_like(keys)
+    _check(_L.gforb_undistort_keypoints(matcher._h, C.byref(camera), _p(keys) if len(keys) else None, len(keys),
+                                        _p(out) if len(keys) else None))
+    return out
+
+
+def ComputeImageBounds(matcher, camera, cols, rows):
+    """Frame::ComputeImageBounds[Stereo] (src/Frame.cc:760-887) -> (mnMinX, mnMaxX, mnMinY, mnMaxY)."""
+    b = np.zeros(4, np.float32)
+    _check(_L.gforb_compute_image_bounds(matcher._h, C.byref(camera), cols, rows, _p(b)))
+    return tuple(float(v) for v in b)

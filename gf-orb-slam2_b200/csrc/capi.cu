@@ -699,6 +699,77 @@ int gforb_preprocess(gforb_rectifier* r, const void* src, int sw, int sh, size_t
     return GFORB_OK;
 }
 
+// --------------------------------------------------------------------------------- undistortion + image bounds
+namespace {
+int check_camera(const gforb_camera* c, const char* who) {
+    if (!c || !(c->K[0] != 0.0) || !(c->K[4] != 0.0)) { set_error(std::string(who) + ": bad camera"); return GFORB_ERR_ARG; }
+    return GFORB_OK;
+}
+}  // namespace
+
+int gforb_undistort_keypoints_batch_device(gforb_matcher* m, const gforb_camera* cam, const gforb_keypoint* keys,
+                                           const int32_t* counts, int stride, int n_images, gforb_keypoint* out, void* cuda_stream) {
+    if (!m || stride < 0 || n_images < 0 || n_images > 65535 || (stride > 0 && n_images > 0 && (!keys || !out))) { set_error("gforb_undistort_keypoints: bad arguments"); return GFORB_ERR_ARG; }
+    int rc = check_camera(cam, "gforb_undistort_keypoints");
+    if (rc) return rc;
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : m->stream;
+    m->last = s;
+    M_CUDA(cudaEventRecord(m->ev0, s));
+    launch_undistort_keys(cam->K, cam->dist, cam->R, cam->P, keys, counts, stride, stride, n_images, out, s);
+    M_CUDA(cudaEventRecord(m->ev1, s));
+    M_CUDA(cudaGetLastError());
+    m->timed = true;
+    return GFORB_OK;
+}
+
+int gforb_undistort_keypoints(gforb_matcher* m, const gforb_camera* cam, const gforb_keypoint* keys, int n, gforb_keypoint* out) {
+    if (!m || n < 0 || (n > 0 && (!keys || !out))) { set_error("gforb_undistort_keypoints: bad arguments"); return GFORB_ERR_ARG; }
+    int rc = check_camera(cam, "gforb_undistort_keypoints");
+    if (rc || n == 0) return rc;
+    const size_t bytes = (size_t)n * sizeof(gforb_keypoint);
+    rc = m->reserve(m->io, m->io_bytes, bytes);
+    if (rc) return rc;
+    gforb_keypoint* d = static_cast<gforb_keypoint*>(m->io);
+    cudaStream_t s = m->stream;
+    M_CUDA(cudaMemcpyAsync(d, keys, bytes, cudaMemcpyHostToDevice, s));
+    rc = gforb_undistort_keypoints_batch_device(m, cam, d, nullptr, n, 1, d, nullptr);
+    if (rc) return rc;
+    M_CUDA(cudaMemcpyAsync(out, d, bytes, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaStreamSynchronize(s));
+    return GFORB_OK;
+}
+
+int gforb_compute_image_bounds(gforb_matcher* m, const gforb_camera* cam, int cols, int rows, gforb_frame_bounds* out) {
+    if (!m || !out || cols <= 0 || rows <= 0) { set_error("gforb_compute_image_bounds: bad arguments"); return GFORB_ERR_ARG; }
+    int rc = check_camera(cam, "gforb_compute_image_bounds");
+    if (rc) return rc;
+    if ((float)cam->dist[0] == 0.0f) {                      // src/Frame.cc:822-828
+        out->min_x = 0.0f; out->max_x = (float)cols; out->min_y = 0.0f; out->max_y = (float)rows;
+        return GFORB_OK;
+    }
+    const float c = (float)cols, r = (float)rows, hc = (float)((float)cols / 2.0), hr = (float)((float)rows / 2.0);
+    float pts[16] = {0.f, 0.f, c, 0.f, 0.f, r, c, r, 0.f, hr, hc, 0.f, hc, r, c, hr};     // src/Frame.cc:770-787
+    rc = m->reserve(m->io, m->io_bytes, sizeof(pts));
+    if (rc) return rc;
+    float* d = static_cast<float*>(m->io);
+    cudaStream_t s = m->stream;
+    M_CUDA(cudaMemcpyAsync(d, pts, sizeof(pts), cudaMemcpyHostToDevice, s));
+    launch_undistort_xy(cam->K, cam->dist, cam->R, cam->P, d, 8, d, s);
+    M_CUDA(cudaGetLastError());
+    M_CUDA(cudaMemcpyAsync(pts, d, sizeof(pts), cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaStreamSynchronize(s));
+    // src/Frame.cc:803-818: float members initialised from INT_MAX / INT_MIN, floor / ceil applied on update
+    float mnx = (float)INT_MAX, mxx = (float)INT_MIN, mny = (float)INT_MAX, mxy = (float)INT_MIN;
+    for (int i = 0; i < 8; ++i) {
+        if (mnx > pts[2 * i]) mnx = floorf(pts[2 * i]);
+        if (mny > pts[2 * i + 1]) mny = floorf(pts[2 * i + 1]);
+        if (mxx < pts[2 * i]) mxx = ceilf(pts[2 * i]);
+        if (mxy < pts[2 * i + 1]) mxy = ceilf(pts[2 * i + 1]);
+    }
+    out->min_x = mnx; out->max_x = mxx; out->min_y = mny; out->max_y = mxy;
+    return GFORB_OK;
+}
+
 int gforb_device_alloc(void** p, size_t bytes) {
     if (!p) return GFORB_ERR_ARG;
     M_CUDA(cudaMalloc(p, std::max<size_t>(bytes, 16)));

@@ -169,6 +169,11 @@ int launch_init_search(const InitSearchArgs& a, const float* bounds, int npairs,
 int preprocess_bytes_per_pixel(int fmt);
 void launch_preprocess(const uint8_t* src, int sw, int sh, size_t spitch, size_t sstride, int fmt, const float* mapx,
                        const float* mapy, uint8_t* dst, int dw, int dh, size_t dpitch, size_t dstride, int nimg, cudaStream_t s);
+// keypoint undistortion (k_undistort.cu): cv::undistortPoints in double; K[9], dist[8], R[9], P[9] row-major.  1 launch each.
+void launch_undistort_keys(const double* K, const double* dist, const double* R, const double* P, const gforb_keypoint* in,
+                           const int32_t* counts, int n_fixed, int stride, int nimg, gforb_keypoint* out, cudaStream_t s);
+void launch_undistort_xy(const double* K, const double* dist, const double* R, const double* P, const float* in, int n,
+                         float* out, cudaStream_t s);
 size_t octree_smem_bytes(const Geom& g);
 int fast_configure(const Geom& g);     // opt in to the FAST kernel's dynamic smem; returns cudaError_t as int
 int octree_configure(const Geom& g);   // opt in to large dynamic smem; returns cudaError_t as int

@@ -211,6 +211,27 @@ GFORB_API int gforb_preprocess_batch_device(gforb_rectifier* r, const void* dev_
 /* wait for the last device-form call; *last_ms = its device time */
 GFORB_API int gforb_rectifier_sync(gforb_rectifier* r, float* last_ms_or_null);
 
+/* =====================================================================================================
+ * Keypoint undistortion and image bounds   
+ *   Frame::UndistortKeyPoints / UndistortKeyPointsStereo   src/Frame.cc:670-758
+ *   Frame::ComputeImageBounds / ComputeImageBoundsStereo   src/Frame.cc:760-887
+ * Both run cv::undistortPoints(mat, mat, K, distCoef, R, P) (5 fixed iterations, double precision, float in/out);
+ * bit-identical to OpenCV.  gforb_camera carries what the Frame members hold: K = mK (mK_ori for the stereo form),
+ * dist = mDistCoef as k1 k2 p1 p2 k3 k4 k5 k6 (unused = 0), R = mR (identity for the monocular form), P = left 3x3 of
+ * mP (= K for the monocular form, src/Frame.cc:745).  dist[0] == 0 is the reference's "no distortion" switch: keys
+ * are copied unchanged and the bounds are the image rectangle.
+ * ===================================================================================================== */
+typedef struct gforb_camera { double K[9], dist[8], R[9], P[9]; } gforb_camera;
+GFORB_API int gforb_undistort_keypoints(gforb_matcher* m, const gforb_camera* cam, const gforb_keypoint* keys, int n,
+                              gforb_keypoint* keys_un);
+/* n_images device-resident key arrays (image i at dev_keys + i * stride, dev_counts[i] keys or `stride` if NULL), the
+ * layout gforb_batch keeps its keypoints in; in place allowed; asynchronous on cuda_stream (NULL: the matcher's).  1 launch. */
+GFORB_API int gforb_undistort_keypoints_batch_device(gforb_matcher* m, const gforb_camera* cam, const gforb_keypoint* dev_keys,
+                                           const int32_t* dev_counts, int stride, int n_images,
+                                           gforb_keypoint* dev_keys_un, void* cuda_stream);
+/* mnMinX, mnMaxX, mnMinY, mnMaxY from the 8 undistorted border points (floor / ceil as the reference applies them) */
+GFORB_API int gforb_compute_image_bounds(gforb_matcher* m, const gforb_camera* cam, int cols, int rows, gforb_frame_bounds* out);
+
 /* device memory helpers for callers without a CUDA runtime of their own (tests, bench): cudaMalloc / cudaFree /
  * synchronous cudaMemcpy; dir 0 = host->device, 1 = device->host */
 GFORB_API int gforb_device_alloc(void** dev_ptr, size_t bytes);

@@ -204,6 +204,40 @@ private:
     std::vector<int32_t> start_, idx_;
 };
 
+// Frame::UndistortKeyPoints / UndistortKeyPointsStereo (src/Frame.cc:670-758): mvKeys -> mvKeysUn through
+// cv::undistortPoints(K, distCoef, R, P).  cam.dist[0] == 0 copies the keys, like the reference.
+inline void UndistortKeyPoints(ORBmatcher& m, const gforb_camera& cam, const std::vector<gforb_keypoint>& mvKeys,
+                               std::vector<gforb_keypoint>& mvKeysUn) {
+    mvKeysUn.resize(mvKeys.size());
+    check(gforb_undistort_keypoints(m.handle(), &cam, mvKeys.data(), (int)mvKeys.size(), mvKeysUn.data()), "UndistortKeyPoints");
+}
+// Frame::ComputeImageBounds / ComputeImageBoundsStereo (src/Frame.cc:760-887): mnMinX, mnMaxX, mnMinY, mnMaxY
+inline gforb_frame_bounds ComputeImageBounds(ORBmatcher& m, const gforb_camera& cam, int cols, int rows) {
+    gforb_frame_bounds b{};
+    check(gforb_compute_image_bounds(m.handle(), &cam, cols, rows, &b), "ComputeImageBounds");
+    return b;
+}
+
+// The pre-processing in front of the extractor: [16-bit -> 8-bit] -> cv::remap(M1, M2, INTER_LINEAR) -> cvtColor(*2GRAY)
+// (ros_stereo.cc:290-295, test_Stereo.cpp:197-210, src/Tracking.cc:366-382).  M1/M2: CV_32F maps of one camera.
+class Rectifier {
+public:
+    Rectifier(const float* M1, const float* M2, int w, int h) : w_(w), h_(h) { check(gforb_rectifier_create(M1, M2, w, h, &h_r), "Rectifier"); }
+    ~Rectifier() { if (h_r) gforb_rectifier_destroy(h_r); }
+    Rectifier(const Rectifier&) = delete;
+    Rectifier& operator=(const Rectifier&) = delete;
+    // dst: w x h (the maps' size) 8-bit gray, tightly packed
+    void operator()(const void* src, int src_w, int src_h, size_t src_pitch, int pixel_format, std::vector<uint8_t>& dst) {
+        const int dw = w_ > 0 ? w_ : src_w, dh = h_ > 0 ? h_ : src_h;
+        dst.resize((size_t)dw * dh);
+        check(gforb_preprocess(h_r, src, src_w, src_h, src_pitch, pixel_format, dst.data(), (size_t)dw), "remap");
+    }
+    gforb_rectifier* handle() { return h_r; }
+private:
+    int w_, h_;
+    gforb_rectifier* h_r = nullptr;
+};
+
 // Frame::ComputeStereoMatches(): fills mvuRight / mvDepth from the Frame's members (src/Frame.cc:889-1078).
 inline int ComputeStereoMatches(ORBextractor& left, ORBextractor& right, const std::vector<gforb_keypoint>& mvKeys,
                                 const std::vector<uint8_t>& mDescriptors, const std::vector<gforb_keypoint>& mvKeysRight,

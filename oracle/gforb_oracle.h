@@ -90,6 +90,12 @@ int   orc_search_for_initialization(const orc_keypoint* k1, const uint8_t* d1, i
 int   orc_preprocess(const void* src, int sw, int sh, size_t spitch, int fmt, const float* mapx, const float* mapy,
                      int dw, int dh, uint8_t* dst, size_t dpitch);
 
+/* cv::undistortPoints as Frame::UndistortKeyPoints[Stereo] calls it (oracle/undistort.cpp; src/Frame.cc:670-758).
+ * K9: camera matrix row-major; dist8: k1 k2 p1 p2 k3 k4 k5 k6 (unused = 0); RR = P(3x3) * R from orc_undistort_matrix
+ * (R = identity and P = K for the monocular form).  xy: n x 2 floats. */
+void  orc_undistort_matrix(const double* P9, const double* R9, double* RR);
+void  orc_undistort_points(const float* xy_in, int n, const double* K9, const double* dist8, const double* RR, float* xy_out);
+
 #ifdef __cplusplus
 }
 #endif

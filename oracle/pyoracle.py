@@ -94,6 +94,9 @@ def lib():
     L.orc_search_for_initialization.restype = C.c_int
     L.orc_preprocess.argtypes = [C.c_void_p, C.c_int, C.c_int, sz, C.c_int, fp, fp, C.c_int, C.c_int, u8p, sz]
     L.orc_preprocess.restype = C.c_int
+    L.orc_undistort_matrix.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]; L.orc_undistort_matrix.restype = None
+    L.orc_undistort_points.argtypes = [fp, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, fp]
+    L.orc_undistort_points.restype = None
     _LIB = L
     return L
 
@@ -316,3 +319,18 @@ def preprocess(src, fmt, mapx=None, mapy=None):
     rc = lib().orc_preprocess(_p(src), sw, sh, src.strides[0], fmt, _p(mapx), _p(mapy), dw, dh, _p(dst), dw)
     assert rc == 0
     return dst
+
+
+def undistort_points(xy, K, dist, R=None, P=None):
+    """cv::undistortPoints(xy, xy, K, dist, R, P) on n x 2 float32 points (src/Frame.cc:688,710,745); P = None -> K
+    is NOT implied: pass P=K for Frame::UndistortKeyPoints (identity new camera matrix otherwise, as OpenCV does)."""
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    K9 = np.ascontiguousarray(np.asarray(K, np.float64).reshape(3, 3))
+    d8 = np.zeros(8, np.float64); dd = np.asarray(dist, np.float64).ravel(); d8[:len(dd)] = dd
+    R9 = np.eye(3) if R is None else np.ascontiguousarray(np.asarray(R, np.float64).reshape(3, 3))
+    P9 = np.eye(3) if P is None else np.ascontiguousarray(np.asarray(P, np.float64)[:3, :3])
+    RR = np.zeros(9, np.float64)
+    lib().orc_undistort_matrix(_p(np.ascontiguousarray(P9)), _p(np.ascontiguousarray(R9)), _p(RR))
+    out = np.empty_like(xy)
+    lib().orc_undistort_points(_p(xy), len(xy), _p(K9), _p(d8), _p(RR), _p(out))
+    return out
