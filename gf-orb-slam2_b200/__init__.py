@@ -15,12 +15,13 @@ The package directory name contains '-', so import it with
 ``importlib.import_module("gf-orb-slam2_b200")``.
 """
 import ctypes as C
+import os
 from pathlib import Path
 
 import numpy as np
 
 _HERE = Path(__file__).resolve().parent
-_SO = _HERE / "libgforb.so"
+_SO = Path(os.environ["GFORB_LIBRARY"]) if os.environ.get("GFORB_LIBRARY") else _HERE / "libgforb.so"   # override: A/B builds of kernel variants (tools/build_variant.sh)
 if not _SO.exists():
     raise ImportError(f"{_SO} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
                       "(nvcc, sm_100a).  gforb has no CPU fallback.")

@@ -832,10 +832,10 @@ int gforb_batch_upload(gforb_batch* b, const uint8_t* left, const uint8_t* right
 
 namespace {
 // kernels for frames [f0, f0 + n) on stream s
-int enqueue_frames(gforb_batch* b, int f0, int n, const gforb_stereo_params* prm, cudaStream_t s, bool timing) {
+int enqueue_frames(gforb_batch* b, int f0, int n, const gforb_stereo_params* prm, cudaStream_t s, bool timing, bool fork_blur = false) {
     Engine& E = b->eng;
     const int n_cap = b->max_frames;
-    int rc = E.run_extract(2 * n, s, timing ? b->ev : nullptr, 2 * f0);
+    int rc = E.run_extract(2 * n, s, timing ? b->ev : nullptr, 2 * f0, fork_blur);
     if (rc) return rc;
     b->last_launches += extract_launches(E.g);
     if (timing && !prm) cudaEventRecord(b->ev[6], s);
@@ -888,7 +888,8 @@ int ensure_pipeline(gforb_batch* b, int nchunks) {
 int gforb_batch_run(gforb_batch* b, int n, const gforb_stereo_params* prm) {
     if (!b || n < 1 || n > b->max_frames) { set_error("gforb_batch_run: bad frame count"); return GFORB_ERR_ARG; }
     b->last_launches = 0;
-    return enqueue_frames(b, 0, n, prm, b->stream, b->timing);
+    static const bool no_fork = getenv("GFORB_NO_FORK") != nullptr;      // A/B switch for measurements
+    return enqueue_frames(b, 0, n, prm, b->stream, b->timing, !no_fork);
 }
 
 int gforb_batch_stage_timing(gforb_batch* b, int enable) {

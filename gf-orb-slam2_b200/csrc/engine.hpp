@@ -37,7 +37,7 @@ public:
     // pyramid only / full extraction for images [0, nimg)
     int run_pyramid(int nimg, cudaStream_t s);
     // images [img0, img0 + nimg); 6 stage events when given
-    int run_extract(int nimg, cudaStream_t s, cudaEvent_t* stage_events = nullptr, int img0 = 0);
+    int run_extract(int nimg, cudaStream_t s, cudaEvent_t* stage_events = nullptr, int img0 = 0, bool fork_blur = false);
     // read + clear the sticky device error word (synchronises `s`)
     int check_errors(cudaStream_t s);
 
@@ -48,6 +48,8 @@ public:
     int nframes_cap = 0;
     bool ready = false;
     bool pyramid_valid = false;
+    cudaStream_t s_aux = nullptr;          // side stream of run_extract(fork_blur)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int32_t* h_small = nullptr;   // pinned: counts / flags read-back
     size_t h_small_ints = 0;
 };

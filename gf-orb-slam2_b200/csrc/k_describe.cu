@@ -9,6 +9,11 @@
 // except for astronomically rare double-rounding cases; DESIGN.md "descriptor parity").  Rotated pattern
 // coordinates use un-fused float ops and round-half-even (__float2int_rn == cvRound).
 // Lane i computes descriptor byte i (16 gathers, 8 compares); the 32 bytes leave as one coalesced store.
+// Measured alternative (round 1, B200): a warp owning 8-32 keys, doing the per-key scalar work (level lookup, fastAtan2,
+// double cos/sin: ~275 of the ~960 warp-instructions per key here) once with one key per lane and only the two pixel
+// passes warp-per-key, is bit-identical but SLOWER -- 0.70-0.95 ms against 0.61 ms per 512 images -- because the
+// per-warp chain of dependent gathers leaves too few loads in flight at 64-125 registers; warp-per-key wins on
+// memory-level parallelism.
 // LSU/gather-bound (SURVEY.md 8d K4+K5): algorithmic bytes = 961 (31x31 raw) + 1369 (37x37 blurred) + 60 out per key.
 #include <cfloat>
 
