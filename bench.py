@@ -162,6 +162,37 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def bind_to_gpu_numa_node(index):
+    """Pin this rank (and the pinned host buffers it is about to allocate: first touch) to the NUMA node its GPU hangs
+    off, so that the end-to-end arm's H2D / D2H traffic does not cross the socket interconnect.  Best effort: returns
+    the node or None when the topology cannot be read (single-socket boxes report -1)."""
+    try:
+        q = subprocess.run(["nvidia-smi", "-i", str(index), "--query-gpu=pci.bus_id", "--format=csv,noheader"],
+                           capture_output=True, text=True, timeout=20).stdout.strip().lower()
+        bus = q[-12:] if len(q) >= 12 else q                       # sysfs uses a 4-digit domain: 0000:1b:00.0
+        node = int(Path(f"/sys/bus/pci/devices/{bus}/numa_node").read_text())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in Path(f"/sys/devices/system/node/node{node}/cpulist").read_text().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        try:                                                        # prefer that node's memory for what we allocate next
+            import ctypes
+            numa = ctypes.CDLL("libnuma.so.1")
+            if numa.numa_available() >= 0:
+                numa.numa_set_preferred(node)
+        except OSError:
+            pass
+        return node
+    except Exception:
+        return None
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -188,12 +219,15 @@ def main():
     torch.cuda.set_device(local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     gf = importlib.import_module("gf-orb-slam2_b200")
     from sharding import aggregate_throughput
 
     F = args.frames
     left, right = make_frames(F, seed0=1000 * rank)
+    full_affinity = os.sched_getaffinity(0)
+    numa_node = bind_to_gpu_numa_node(local_rank)     # before the pinned buffers are allocated
     sb = gf.StereoBatch(W, H, F, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH)
     stream = torch.cuda.Stream()        # non-default: handle 0 (legacy default) would mean "library's own stream"
     torch.cuda.set_stream(stream)
@@ -324,12 +358,16 @@ def main():
                     tt = sum(x["time_us"] for x in ks)
                     stages[k]["ncu_dram_bytes"] = int(sum(x["dram_bytes"] for x in ks))
                     stages[k]["ncu_issue_active_pct"] = round(sum(x["issue_active_pct"] * x["time_us"] for x in ks) / tt, 1)
+                    stages[k]["ncu_pipe_alu_pct"] = round(sum(x["pipe_alu_pct"] * x["time_us"] for x in ks) / tt, 1)
+                    stages[k]["ncu_pipe_lsu_pct"] = round(sum(x["pipe_lsu_pct"] * x["time_us"] for x in ks) / tt, 1)
     ach = stages[dom]["gbs"]
     roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                 "traffic": stages[dom].get("ncu_dram_bytes"), "issue_active_pct": stages[dom].get("ncu_issue_active_pct"),
+                "int_pipe_alu_pct": stages[dom].get("ncu_pipe_alu_pct"),
                 "peak_source": peak_src, "launches_in_stage": NLEVELS if dom == "pyramid" else 1,
                 "note": "FAST/quadtree/describe/stereo are integer/LSU/latency-bound (SURVEY.md 8d): their ceiling is the "
-                        "warp-instruction issue rate (issue_active_pct, ncu smsp__issue_active of the committed capture), "
+                        "warp-instruction issue rate (issue_active_pct = ncu smsp__issue_active; int_pipe_alu_pct = share of the INT ALU "
+                        "pipe's 64 lanes/clk/SM, measured in profiles/int_peaks_r1.json, that the kernel keeps busy), "
                         "not HBM; the HBM fraction is still reported for every stage under 'stages'; traffic = "
                         "dram__bytes_read+write per launch from profiles/ncu_latest.json"}
 
@@ -343,11 +381,12 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "gpu_launches": launches_e2e,
                     "api": "gforb_stereo_frames_batch_async on two batch handles used alternately + gforb_batch_sync",
-                    "blocking_single_handle": e2e_blocking, "wall_ms_per_step": wall_ms / args.steps,
+                    "blocking_single_handle": e2e_blocking, "numa_node_rank0": numa_node, "wall_ms_per_step": wall_ms / args.steps,
                     "pipeline": "chunks of %s frames: H2D / kernels / D2H of successive chunks overlap (2 copy + 4 kernel streams)" % (args.chunk or "8,24,32..,16,8 (auto)")},
             "gpu_launches": launches_value,
             "clocks": clocks, "roofline": roofline, "stages": stages}
     if not args.no_cpu_baseline and world == 1:
+        os.sched_setaffinity(0, full_affinity)          # the CPU baseline gets every host core back
         threads = os.cpu_count() or 1
         fps, nframes, secs, _ = cpu_baseline(left, right, threads)
         line["cpu_baseline"] = {"value": fps, "unit": UNIT, "cores": threads, "kind": "port",

@@ -107,6 +107,7 @@ _SIGS = {
     "gforb_undistort_keypoints": (_i, [_vp, _vp, _vp, _i, _vp]),
     "gforb_undistort_keypoints_batch_device": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp]),
     "gforb_compute_image_bounds": (_i, [_vp, _vp, _i, _i, _vp]),
+    "gforb_distinctive_descriptors": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "gforb_device_alloc": (_i, [C.POINTER(_vp), _sz]),
     "gforb_device_free": (None, [_vp]),
     "gforb_device_copy": (_i, [_vp, _vp, _sz, _i]),
@@ -596,3 +597,13 @@ def ComputeImageBounds(matcher, camera, cols, rows):
     b = np.zeros(4, np.float32)
     _check(_L.gforb_compute_image_bounds(matcher._h, C.byref(camera), cols, rows, _p(b)))
     return tuple(float(v) for v in b)
+
+
+def ComputeDistinctiveDescriptors(matcher, desc, set_start):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:397-458) for many map points at once: set p = rows
+    set_start[p]:set_start[p+1] of desc.  Returns (best_idx within each set, best_median)."""
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); ss = np.ascontiguousarray(set_start, np.int32)
+    n = len(ss) - 1
+    bi = np.empty(max(n, 1), np.int32); bm = np.empty(max(n, 1), np.int32)
+    _check(_L.gforb_distinctive_descriptors(matcher._h, _p(desc) if len(desc) else None, _p(ss), n, _p(bi), _p(bm)))
+    return bi[:n], bm[:n]

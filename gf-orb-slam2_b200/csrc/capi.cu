@@ -770,6 +770,40 @@ int gforb_compute_image_bounds(gforb_matcher* m, const gforb_camera* cam, int co
     return GFORB_OK;
 }
 
+int gforb_distinctive_descriptors(gforb_matcher* m, const uint8_t* desc, const int32_t* set_start, int n, int32_t* best_idx,
+                                  int32_t* best_median) {
+    if (!m || n < 0 || !set_start || (n > 0 && (!best_idx || !best_median))) { set_error("gforb_distinctive_descriptors: bad arguments"); return GFORB_ERR_ARG; }
+    if (n == 0) return GFORB_OK;
+    int max_n = 0;
+    for (int p = 0; p < n; ++p) {
+        if (set_start[p + 1] < set_start[p] || set_start[p] < 0) { set_error("gforb_distinctive_descriptors: set_start must be non-decreasing"); return GFORB_ERR_ARG; }
+        max_n = std::max(max_n, set_start[p + 1] - set_start[p]);
+    }
+    if (max_n > distinctive_max_set()) { set_error("gforb_distinctive_descriptors: more than 1024 descriptors in one set"); return GFORB_ERR_CAPACITY; }
+    const size_t total = (size_t)set_start[n];
+    if (total > 0 && !desc) { set_error("gforb_distinctive_descriptors: null descriptors"); return GFORB_ERR_ARG; }
+    const size_t bd = al16(std::max<size_t>(total, 1) * 32), bs = al16((size_t)(n + 1) * 4), bo = al16((size_t)n * 4);
+    int rc = m->reserve(m->io, m->io_bytes, bd + bs + 2 * bo);
+    if (rc) return rc;
+    uint8_t* base = static_cast<uint8_t*>(m->io);
+    int32_t* ds = reinterpret_cast<int32_t*>(base + bd);
+    int32_t* di = reinterpret_cast<int32_t*>(base + bd + bs);
+    int32_t* dm = reinterpret_cast<int32_t*>(base + bd + bs + bo);
+    cudaStream_t s = m->stream;
+    m->last = s;
+    if (total) M_CUDA(cudaMemcpyAsync(base, desc, total * 32, cudaMemcpyHostToDevice, s));
+    M_CUDA(cudaMemcpyAsync(ds, set_start, (size_t)(n + 1) * 4, cudaMemcpyHostToDevice, s));
+    M_CUDA(cudaEventRecord(m->ev0, s));
+    if (launch_distinctive(base, ds, n, max_n, di, dm, s)) { set_error("gforb_distinctive_descriptors: shared-memory opt-in failed"); return GFORB_ERR_CUDA; }
+    M_CUDA(cudaEventRecord(m->ev1, s));
+    M_CUDA(cudaGetLastError());
+    m->timed = true;
+    M_CUDA(cudaMemcpyAsync(best_idx, di, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaMemcpyAsync(best_median, dm, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaStreamSynchronize(s));
+    return GFORB_OK;
+}
+
 int gforb_device_alloc(void** p, size_t bytes) {
     if (!p) return GFORB_ERR_ARG;
     M_CUDA(cudaMalloc(p, std::max<size_t>(bytes, 16)));

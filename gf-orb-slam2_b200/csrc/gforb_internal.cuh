@@ -174,6 +174,10 @@ void launch_undistort_keys(const double* K, const double* dist, const double* R,
                            const int32_t* counts, int n_fixed, int stride, int nimg, gforb_keypoint* out, cudaStream_t s);
 void launch_undistort_xy(const double* K, const double* dist, const double* R, const double* P, const float* in, int n,
                          float* out, cudaStream_t s);
+// MapPoint::ComputeDistinctiveDescriptors (k_match.cu): 1 launch; -1 = shared-memory opt-in failed
+int distinctive_max_set();
+int launch_distinctive(const uint8_t* desc, const int32_t* set_start, int npoints, int max_n, int32_t* best_idx,
+                       int32_t* best_median, cudaStream_t s);
 size_t octree_smem_bytes(const Geom& g);
 int fast_configure(const Geom& g);     // opt in to the FAST kernel's dynamic smem; returns cudaError_t as int
 int octree_configure(const Geom& g);   // opt in to large dynamic smem; returns cudaError_t as int

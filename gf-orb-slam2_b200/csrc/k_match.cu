@@ -104,4 +104,59 @@ void launch_match(const uint8_t* dA, int nA, const uint8_t* dB, int nB, float ra
                                                         best_idx, best_dist, second_dist, match);
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// MapPoint::ComputeDistinctiveDescriptors (reference src/MapPoint.cc:397-458), the descriptor part: per map point, the
+// N observed descriptors' pairwise distances, per row the median sorted[int(0.5 * (N - 1))] (the row includes its own
+// 0), and the first row with the least median.  One warp per map point, the set staged in shared memory; lane = row.
+// A row's median is found without sorting: distances are 0..256, so the k-th smallest is the least v with
+// #{j : d_ij <= v} > k -- 9 bisection steps, each re-scanning the row against broadcast shared-memory reads.
+namespace {
+constexpr int kDdWarps = 4;
+}
+__global__ void __launch_bounds__(kDdWarps * 32)
+distinctive_kernel(const uint4* __restrict__ desc, const int32_t* __restrict__ set_start, int npoints, int max_n,
+                   int32_t* __restrict__ best_idx, int32_t* __restrict__ best_median) {
+    extern __shared__ uint4 dd_tile[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int p = blockIdx.x * kDdWarps + wid;
+    if (p >= npoints) return;
+    const int s0 = set_start[p], n = set_start[p + 1] - s0;
+    if (n <= 0) { if (lane == 0) { best_idx[p] = -1; best_median[p] = INT32_MAX; } return; }
+    uint4* t = dd_tile + (size_t)wid * max_n * 2;
+    for (int i = lane; i < 2 * n; i += 32) t[i] = __ldg(desc + 2 * (size_t)s0 + i);
+    __syncwarp();
+    const int k = (int)(0.5 * (n - 1));
+    uint32_t best = kNoKey;                        // median << 16 | row: least median, then first row
+    for (int i = lane; i < n; i += 32) {
+        const uint4 a0 = t[2 * i], a1 = t[2 * i + 1];
+        int lo = 0, hi = 256;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            int c = 0;
+            for (int j = 0; j < n; ++j) c += hamming8(a0, a1, t[2 * j], t[2 * j + 1]) <= mid ? 1 : 0;
+            if (c > k) hi = mid; else lo = mid + 1;
+        }
+        best = min(best, ((uint32_t)lo << 16) | (uint32_t)i);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xFFFFFFFFu, best, o));
+    if (lane == 0) { best_idx[p] = (int)(best & 0xFFFFu); best_median[p] = (int)(best >> 16); }
+}
+
+int distinctive_max_set() { return 1024; }          // rows per set: 4 warps x 1024 x 32 B = 128 KB of shared memory
+
+int launch_distinctive(const uint8_t* desc, const int32_t* set_start, int npoints, int max_n, int32_t* best_idx,
+                       int32_t* best_median, cudaStream_t s) {
+    if (npoints <= 0) return 0;
+    const size_t smem = (size_t)kDdWarps * std::max(max_n, 1) * 32;
+    static size_t have = 48 * 1024;
+    if (smem > have) {
+        if (cudaFuncSetAttribute(distinctive_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
+        have = smem;
+    }
+    distinctive_kernel<<<(npoints + kDdWarps - 1) / kDdWarps, kDdWarps * 32, smem, s>>>(
+        reinterpret_cast<const uint4*>(desc), set_start, npoints, std::max(max_n, 1), best_idx, best_median);
+    return 0;
+}
+
 }  // namespace gforb

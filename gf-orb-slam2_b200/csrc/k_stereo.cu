@@ -18,7 +18,13 @@ namespace gforb {
 
 namespace {
 constexpr int kT = 256;
-constexpr int kSlices = 8;
+#ifndef GFORB_ST_SLICES
+#define GFORB_ST_SLICES 8
+#endif
+#ifndef GFORB_ST_MINB
+#define GFORB_ST_MINB 4
+#endif
+constexpr int kSlices = GFORB_ST_SLICES;
 struct RKey { short minr, maxr; uint32_t oi; float x; };   // oi = octave << 16 | original index
 
 __device__ __forceinline__ int hamming_u4(const uint4 a0, const uint4 a1, const uint8_t* b) {
@@ -81,7 +87,7 @@ __device__ int select_kth(const int* d, int n, int k, int* hist, int* s_tmp) {
 }
 }  // namespace
 
-__global__ void __launch_bounds__(kT)
+__global__ void __launch_bounds__(kT, GFORB_ST_MINB)
 stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K, int band) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     // [rs: K sorted right keys][binstart: nRows + 1][s_dist: K (aliases rs once the matching is done)]

@@ -232,6 +232,14 @@ GFORB_API int gforb_undistort_keypoints_batch_device(gforb_matcher* m, const gfo
 /* mnMinX, mnMaxX, mnMinY, mnMaxY from the 8 undistorted border points (floor / ceil as the reference applies them) */
 GFORB_API int gforb_compute_image_bounds(gforb_matcher* m, const gforb_camera* cam, int cols, int rows, gforb_frame_bounds* out);
 
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:397-458), the descriptor part, for
+ * n_points map points at once: point p's observed descriptors are rows set_start[p] .. set_start[p+1] of `desc`
+ * (what the reference gathers into vDescriptors).  best_idx[p] = the row WITHIN the set with the least median distance
+ * to the others (first such row; -1 for an empty set), best_median[p] = that median (sorted[int(0.5 * (N - 1))], the
+ * row's own 0 included; INT32_MAX for an empty set).  At most 1,024 descriptors per point (GFORB_ERR_CAPACITY). */
+GFORB_API int gforb_distinctive_descriptors(gforb_matcher* m, const uint8_t* desc, const int32_t* set_start, int n_points,
+                                  int32_t* best_idx, int32_t* best_median);
+
 /* device memory helpers for callers without a CUDA runtime of their own (tests, bench): cudaMalloc / cudaFree /
  * synchronous cudaMemcpy; dir 0 = host->device, 1 = device->host */
 GFORB_API int gforb_device_alloc(void** dev_ptr, size_t bytes);

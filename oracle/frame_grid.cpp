@@ -170,3 +170,36 @@ int orc_search_for_initialization(const orc_keypoint* k1, const uint8_t* d1, int
 }
 
 }  // extern "C"
+
+// MapPoint::ComputeDistinctiveDescriptors (/root/reference/src/MapPoint.cc:397-458), the descriptor part: for each
+// map point, given the descriptors of its observations (set p = rows set_start[p] .. set_start[p+1]), all pairwise
+// distances, per row the median = sorted[int(0.5 * (N - 1))], and the FIRST row with the least median.
+#include <algorithm>
+extern "C" void orc_distinctive_descriptors(const uint8_t* desc, const int* set_start, int npoints, int* best_idx,
+                                            int* best_median) {
+    for (int p = 0; p < npoints; ++p) {
+        const uint8_t* d = desc + 32 * (size_t)set_start[p];
+        const int N = set_start[p + 1] - set_start[p];
+        best_idx[p] = N > 0 ? 0 : -1;
+        best_median[p] = INT_MAX;
+        if (N <= 0) continue;
+        std::vector<float> D((size_t)N * N);
+        for (int i = 0; i < N; i++) {
+            D[(size_t)i * N + i] = 0;
+            for (int j = i + 1; j < N; j++) {
+                const int distij = orc_hamming256(d + 32 * (size_t)i, d + 32 * (size_t)j);
+                D[(size_t)i * N + j] = (float)distij;
+                D[(size_t)j * N + i] = (float)distij;
+            }
+        }
+        int BestMedian = INT_MAX, BestIdx = 0;
+        for (int i = 0; i < N; i++) {
+            std::vector<int> vDists(D.begin() + (size_t)i * N, D.begin() + (size_t)(i + 1) * N);
+            std::sort(vDists.begin(), vDists.end());
+            const int median = vDists[(size_t)(0.5 * (N - 1))];
+            if (median < BestMedian) { BestMedian = median; BestIdx = i; }
+        }
+        best_idx[p] = BestIdx;
+        best_median[p] = BestMedian;
+    }
+}

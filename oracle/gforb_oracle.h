@@ -96,6 +96,10 @@ int   orc_preprocess(const void* src, int sw, int sh, size_t spitch, int fmt, co
 void  orc_undistort_matrix(const double* P9, const double* R9, double* RR);
 void  orc_undistort_points(const float* xy_in, int n, const double* K9, const double* dist8, const double* RR, float* xy_out);
 
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:397-458) over npoints descriptor sets (CSR set_start);
+ * best_idx = row within the set (-1 for an empty set), best_median = its median distance */
+void  orc_distinctive_descriptors(const uint8_t* desc, const int* set_start, int npoints, int* best_idx, int* best_median);
+
 #ifdef __cplusplus
 }
 #endif

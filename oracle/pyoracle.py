@@ -97,6 +97,7 @@ def lib():
     L.orc_undistort_matrix.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]; L.orc_undistort_matrix.restype = None
     L.orc_undistort_points.argtypes = [fp, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, fp]
     L.orc_undistort_points.restype = None
+    L.orc_distinctive_descriptors.argtypes = [u8p, ip, C.c_int, ip, ip]; L.orc_distinctive_descriptors.restype = None
     _LIB = L
     return L
 
@@ -334,3 +335,12 @@ def undistort_points(xy, K, dist, R=None, P=None):
     out = np.empty_like(xy)
     lib().orc_undistort_points(_p(xy), len(xy), _p(K9), _p(d8), _p(RR), _p(out))
     return out
+
+
+def distinctive_descriptors(desc, set_start):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:397-458) -> (best_idx, best_median) per set."""
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); ss = np.ascontiguousarray(set_start, np.int32)
+    n = len(ss) - 1
+    bi = np.empty(max(n, 1), np.int32); bm = np.empty(max(n, 1), np.int32)
+    lib().orc_distinctive_descriptors(_p(desc), _p(ss), n, _p(bi), _p(bm))
+    return bi[:n], bm[:n]

@@ -88,3 +88,24 @@ def test_bruteforce_device_form_and_on_extracted_descriptors(gf, O, fixtures):
     # distances agree with the host DescriptorDistance
     i = int(np.argmax(ref["match"] >= 0))
     assert gf.DescriptorDistance(dL[i], dR[ref["best_idx"][i]]) == ref["best_dist"][i]
+
+
+def test_distinctive_descriptors_vs_oracle(gf, O):
+    """MapPoint::ComputeDistinctiveDescriptors over many map points (SURVEY.md 8f row 4): bit-exact incl. median ties"""
+    rng = np.random.default_rng(17)
+    sizes = [1, 2, 3, 4, 5, 0, 7, 32, 33, 64, 100, 2, 0, 257, 1024] + [int(v) for v in rng.integers(1, 60, 300)]
+    start = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    desc = np.zeros((start[-1], 32), np.uint8)
+    for p, n in enumerate(sizes):                                   # a cluster per point: base + a few flipped bits, some duplicates
+        base = rng.integers(0, 256, 32, dtype=np.uint8)
+        d = base ^ np.packbits(rng.random((n, 256)) < rng.choice([0.02, 0.1, 0.3]), axis=1)
+        if n > 3:
+            d[n // 2] = d[0]
+        desc[start[p]:start[p + 1]] = d
+    m = gf.ORBmatcher()
+    bi, bm = gf.ComputeDistinctiveDescriptors(m, desc, start)
+    obi, obm = O.distinctive_descriptors(desc, start)
+    assert np.array_equal(bi, obi) and np.array_equal(bm, obm)
+    assert bi[5] == -1 and bm[5] == np.iinfo(np.int32).max
+    with pytest.raises(gf.GforbError):
+        gf.ComputeDistinctiveDescriptors(m, np.zeros((1025, 32), np.uint8), np.array([0, 1025], np.int32))
