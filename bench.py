@@ -159,7 +159,7 @@ def run_reference(args, rank, world):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": time.time() - t0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def bind_to_gpu_numa_node(index):
@@ -193,6 +193,27 @@ def bind_to_gpu_numa_node(index):
         return None
 
 
+_RESULT_FD = None
+
+
+def quiet_stdout():
+    """Library chatter (NCCL prints its version banner on stdout when NCCL_DEBUG is set in the environment) must not
+    share stdout with the ONE JSON line: fd 1 is pointed at stderr for the run, the result goes to the saved fd."""
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_RESULT_FD, data)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -203,6 +224,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--chunk", type=int, default=0, help="frames per pipeline chunk of the end-to-end arm")
     args = ap.parse_args()
+    quiet_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == "gforb" else args.warmup
 
     rank = int(os.environ.get("RANK", "0"))
@@ -392,7 +414,7 @@ def main():
         line["cpu_baseline"] = {"value": fps, "unit": UNIT, "cores": threads, "kind": "port",
                                 "sample": f"{nframes} synthetic 752x480 stereo frames (same generator), oracle port, "
                                           f"{threads} threads each running whole frames, {secs:.1f} s"}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
