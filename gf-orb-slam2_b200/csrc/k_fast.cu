@@ -137,126 +137,126 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
     const int sp = (dw + 2 + 3) & ~3;                   // score map pitch
     reinterpret_cast<uint4*>(keep_lo)[lane] = make_uint4(0, 0, 0, 0);     // row bitmaps
     const int t_ini = min(max(a.t_ini, 0), 255), t_min = min(max(a.t_min, 0), 255);
-    const int tlo = min(t_ini, t_min);
-    // prefilter threshold: the largest 2^k - 1 <= tlo (a lower threshold stays a superset); |d| > 2^k - 1 <=> d & ~(2^k - 1) != 0,
-    // and (|d1| | |d2|) & mask != 0 <=> either exceeds it -- exact for the default tlo = 7
-    const uint32_t pmask = (~(uint32_t)((1 << (31 - __clz(min(tlo, 127) + 1))) - 1) & 0xFFu) * 0x01010101u;
     const int tpw = tp >> 2;
     const int xlo = xoff + 3, xhi = xlo + dw;           // domain columns [xlo, xhi) in tile bytes
     const int w0 = xlo >> 2;
     uint8_t* scb = sc - 2 * sp - xlo + 1;               // scb[row * sp + col] = score of tile pixel (row, col)
     const int nitems = dh * nw;                         // item = one 32-bit word of a domain row
     const int qs = (int)(cb.y & 0xFF), rs = (int)(cb.y >> 8);         // 32 = qs * nw + rs
-    int ir = (lane * (int)cb.x) >> 16, iw = lane - ir * nw;           // cb.x = ceil(65536 / nw): lane -> (row, word)
+    const int ir0 = (lane * (int)cb.x) >> 16, iw0 = lane - ir0 * nw;  // cb.x = ceil(65536 / nw): lane -> (row, word)
     const uint32_t cm_first = 0xFFFFFFFFu << (8 * (xlo & 3));
     const uint32_t cm_last = 0xFFFFFFFFu >> (8 * (3 - ((xhi - 1) & 3)));
     const uint32_t lt = (1u << lane) - 1u;
+    const int pstep = qs * tpw + rs, pwrap = tpw - nw;
     __syncwarp();                                       // barrier init + clears visible to the whole warp
     mbar_wait(bar, 0);
 
-    // ---- pass 1a: 4-pixel prefilter, 32 words per step; words with any flagged pixel are compacted by ONE ballot
-    //      into a word list (row << 9 | word column << 4 | 4-bit pixel mask) ----
-    const uint32_t* p = reinterpret_cast<const uint32_t*>(tile) + (3 + ir) * tpw + w0 + iw;
-    const int pstep = qs * tpw + rs, pwrap = tpw - nw;
-    int nwl = 0;
-    for (int i0 = 0; i0 < nitems; i0 += 32) {
-        uint32_t f = 0;
-        if (i0 + lane < nitems) {
-            if (tlo == 0) f = 0x80808080u;              // "> 0" has no cleared-low-bit form: list the whole domain
-            else {
-                const uint32_t C = p[0], Wm = p[-1], Wp = p[1], U = p[-3 * tpw], D = p[3 * tpw];
-                const uint32_t Lw = __funnelshift_r(Wm, C, 8), Rw = __funnelshift_r(C, Wp, 24);
-                const uint32_t v = (__vabsdiffu4(C, U) | __vabsdiffu4(C, D)) & pmask;
-                const uint32_t h = (__vabsdiffu4(C, Lw) | __vabsdiffu4(C, Rw)) & pmask;
-                f = nz_lanes(v) & nz_lanes(h) & 0x80808080u;
+    // The reference's control flow, literally: cv::FAST(cell, iniThFAST); only if that leaves NO keypoint after NMS,
+    // cv::FAST(cell, minThFAST) (src/ORBextractor.cc:811-817).  v6: the second threshold is a second trip through the
+    // passes below instead of being folded into one trip at min(ini, min): a textured cell (about half of them) is done
+    // after the cheap trip at 20 -- far fewer pixels survive the prefilter and reach the exact arc test than at 7 -- and
+    // only the low-contrast cells pay for both.
+    unsigned long long m0 = 0, m1 = 0;                  // NMS survivors of rows lane and lane + 32
+    for (int trip = 0; trip < 2; ++trip) {
+        const int tc = trip ? t_min : t_ini;
+        // prefilter threshold: the largest 2^k - 1 <= tc (a lower threshold stays a superset); |d| > 2^k - 1 <=> d & ~(2^k - 1) != 0,
+        // and (|d1| | |d2|) & mask != 0 <=> either exceeds it
+        const uint32_t pmask = (~(uint32_t)((1 << (31 - __clz(min(tc, 127) + 1))) - 1) & 0xFFu) * 0x01010101u;
+
+        // ---- pass 1a: 4-pixel prefilter, 32 words per step; words with any flagged pixel are compacted by ONE ballot
+        //      into a word list (row << 9 | word column << 4 | 4-bit pixel mask) ----
+        int ir = ir0, iw = iw0;
+        const uint32_t* p = reinterpret_cast<const uint32_t*>(tile) + (3 + ir) * tpw + w0 + iw;
+        int nwl = 0;
+        for (int i0 = 0; i0 < nitems; i0 += 32) {
+            uint32_t f = 0;
+            if (i0 + lane < nitems) {
+                if (tc == 0) f = 0x80808080u;           // "> 0" has no cleared-low-bit form: list the whole domain
+                else {
+                    const uint32_t C = p[0], Wm = p[-1], Wp = p[1], U = p[-3 * tpw], D = p[3 * tpw];
+                    const uint32_t Lw = __funnelshift_r(Wm, C, 8), Rw = __funnelshift_r(C, Wp, 24);
+                    const uint32_t v = (__vabsdiffu4(C, U) | __vabsdiffu4(C, D)) & pmask;
+                    const uint32_t h = (__vabsdiffu4(C, Lw) | __vabsdiffu4(C, Rw)) & pmask;
+                    f = nz_lanes(v) & nz_lanes(h) & 0x80808080u;
+                }
+                // columns outside [xlo, xhi) (first / last word of the row)
+                if (iw == 0) f &= cm_first;
+                if (iw == nw - 1) f &= cm_last;
             }
-            // columns outside [xlo, xhi) (first / last word of the row)
-            if (iw == 0) f &= cm_first;
-            if (iw == nw - 1) f &= cm_last;
+            const uint32_t m = __ballot_sync(0xffffffffu, f != 0);
+            if (f != 0) {
+                // flag bits 7, 15, 23, 31 -> mask bits 0..3
+                const uint32_t m4 = ((f >> 7) & 1u) | ((f >> 14) & 2u) | ((f >> 21) & 4u) | ((f >> 28) & 8u);
+                wlist[nwl + __popc(m & lt)] = (uint16_t)(((3 + ir) << 9) | ((w0 + iw) << 4) | m4);
+            }
+            nwl += __popc(m);
+            iw += rs; ir += qs; p += pstep;
+            if (iw >= nw) { iw -= nw; ++ir; p += pwrap; }
         }
-        const uint32_t m = __ballot_sync(0xffffffffu, f != 0);
-        if (f != 0) {
-            // flag bits 7, 15, 23, 31 -> mask bits 0..3
-            const uint32_t m4 = ((f >> 7) & 1u) | ((f >> 14) & 2u) | ((f >> 21) & 4u) | ((f >> 28) & 8u);
-            wlist[nwl + __popc(m & lt)] = (uint16_t)(((3 + ir) << 9) | ((w0 + iw) << 4) | m4);
+        __syncwarp();
+        // ---- pass 1b: expand the word list into the pixel list ((row << 8) | tile column); order is irrelevant.
+        //      Per-lane counts are <= 4: three ballots give the exclusive prefix ----
+        int nlist = 0;
+        for (int k0 = 0; k0 < nwl; k0 += 32) {
+            const uint32_t we = k0 + lane < nwl ? wlist[k0 + lane] : 0u;
+            const int c = __popc(we & 15u);
+            const uint32_t b0 = __ballot_sync(0xffffffffu, c & 1), b1 = __ballot_sync(0xffffffffu, c & 2);
+            const uint32_t b2 = __ballot_sync(0xffffffffu, c & 4);
+            uint16_t* out = list + nlist + __popc(b0 & lt) + 2 * __popc(b1 & lt) + 4 * __popc(b2 & lt);
+            nlist += __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
+            const uint32_t e = ((we >> 9) << 8) | (((we >> 4) & 31u) << 2);
+            if (we & 1u) *out++ = (uint16_t)e;
+            if (we & 2u) *out++ = (uint16_t)(e + 1);
+            if (we & 4u) *out++ = (uint16_t)(e + 2);
+            if (we & 8u) *out++ = (uint16_t)(e + 3);
         }
-        nwl += __popc(m);
-        iw += rs; ir += qs; p += pstep;
-        if (iw >= nw) { iw -= nw; ++ir; p += pwrap; }
-    }
-    __syncwarp();
-    // ---- pass 1b: expand the word list into the pixel list ((row << 8) | tile column); order is irrelevant.
-    //      Per-lane counts are <= 4: three ballots give the exclusive prefix ----
-    int nlist = 0;
-    for (int k0 = 0; k0 < nwl; k0 += 32) {
-        const uint32_t we = k0 + lane < nwl ? wlist[k0 + lane] : 0u;
-        const int c = __popc(we & 15u);
-        const uint32_t b0 = __ballot_sync(0xffffffffu, c & 1), b1 = __ballot_sync(0xffffffffu, c & 2);
-        const uint32_t b2 = __ballot_sync(0xffffffffu, c & 4);
-        uint16_t* out = list + nlist + __popc(b0 & lt) + 2 * __popc(b1 & lt) + 4 * __popc(b2 & lt);
-        nlist += __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
-        const uint32_t e = ((we >> 9) << 8) | (((we >> 4) & 31u) << 2);
-        if (we & 1u) *out++ = (uint16_t)e;
-        if (we & 2u) *out++ = (uint16_t)(e + 1);
-        if (we & 4u) *out++ = (uint16_t)(e + 2);
-        if (we & 8u) *out++ = (uint16_t)(e + 3);
-    }
-    __syncwarp();
-    {   // the word list is dead: clear the score map (domain + zero ring) it shared
-        const int n16 = ((dh + 2) * sp + 15) >> 4;
-        for (int i = lane; i < n16; i += 32) reinterpret_cast<uint4*>(sc)[i] = make_uint4(0, 0, 0, 0);
-    }
-    __syncwarp();
+        __syncwarp();
+        {   // the word list is dead: clear the score map (domain + zero ring) it shared
+            const int n16 = ((dh + 2) * sp + 15) >> 4;
+            for (int i = lane; i < n16; i += 32) reinterpret_cast<uint4*>(sc)[i] = make_uint4(0, 0, 0, 0);
+        }
+        __syncwarp();
 
-    // ---- pass 2: exact corner strength of the listed pixels ----
-    for (int k = lane; k < nlist; k += 32) {
-        const int e = list[k];
-        const int off = (e >> 8) * tp + (e & 0xFF);
-        const uint8_t* c = tile + off;
-        const uint8_t* const rows[7] = {c - 3 * tp, c - 2 * tp, c - tp, c, c + tp, c + 2 * tp, c + 3 * tp};
-        const int m = fast_arc_strength(rows, c[0]);
-        if (m > tlo) scb[(e >> 8) * sp + (e & 0xFF)] = (uint8_t)(m - 1);
-    }
-    __syncwarp();
-
-    // ---- pass 3: strict 3x3 NMS on the score map (zero outside the domain), again only over the list ----
-    bool hi = false;
-    for (int k = lane; k < nlist; k += 32) {
-        const int e = list[k];
-        const int py = e >> 8, px = e & 0xFF;
-        const uint8_t* q = scb + py * sp + px;
-        const int s = q[0];
-        const int n0 = max(max(q[-sp - 1], q[-sp]), q[-sp + 1]), n1 = max(q[-1], q[1]);
-        const int n2 = max(max(q[sp - 1], q[sp]), q[sp + 1]);
-        if (s > max(max(n0, n1), n2)) {                 // s > 0 implied: neighbours are >= 0
-            const int bx = px - xlo;
-            const int wi = 2 * (py - 3) + (bx >> 5);
-            const uint32_t bit = 1u << (bx & 31);
-            atomicOr(&keep_lo[wi], bit);
-            hi |= s >= t_ini;
+        // ---- pass 2: exact corner strength of the listed pixels; corner <=> strength > tc, score = strength - 1.
+        //      Corners are compacted in place to the front of the list (ballot), so that NMS visits corners only ----
+        int ncorner = 0;
+        for (int k0 = 0; k0 < nlist; k0 += 32) {
+            const int k = k0 + lane;
+            int e = 0, m = 0;
+            if (k < nlist) {
+                e = list[k];
+                const uint8_t* c = tile + (e >> 8) * tp + (e & 0xFF);
+                const uint8_t* const rows[7] = {c - 3 * tp, c - 2 * tp, c - tp, c, c + tp, c + 2 * tp, c + 3 * tp};
+                m = fast_arc_strength(rows, c[0]);
+            }
+            const bool corner = k < nlist && m > tc;
+            const uint32_t cm = __ballot_sync(0xffffffffu, corner);
+            __syncwarp();                                // every lane has read its entry before the slots are reused
+            if (corner) {
+                scb[(e >> 8) * sp + (e & 0xFF)] = (uint8_t)(m - 1);
+                list[ncorner + __popc(cm & lt)] = (uint16_t)e;
+            }
+            ncorner += __popc(cm);
         }
-    }
-    // keep@ini if it found anything, else keep@min: keep@t(p) = keep@tlo(p) && s(p) >= t, so the rows' bitmaps are
-    // filtered by score whenever the selected threshold is above tlo
-    const bool use_hi = __any_sync(0xffffffffu, hi);
-    __syncwarp();
-    unsigned long long m0 = 0, m1 = 0;                  // rows lane and lane + 32
-    {
+        __syncwarp();
+
+        // ---- pass 3: strict 3x3 NMS on the score map (zero outside the domain) over the corners ----
+        for (int k = lane; k < ncorner; k += 32) {
+            const int e = list[k];
+            const int py = e >> 8, px = e & 0xFF;
+            const uint8_t* q = scb + py * sp + px;
+            const int s = q[0];
+            const int n0 = max(max(q[-sp - 1], q[-sp]), q[-sp + 1]), n1 = max(q[-1], q[1]);
+            const int n2 = max(max(q[sp - 1], q[sp]), q[sp + 1]);
+            if (s > max(max(n0, n1), n2)) {
+                const int bx = px - xlo;
+                atomicOr(&keep_lo[2 * (py - 3) + (bx >> 5)], 1u << (bx & 31));
+            }
+        }
+        __syncwarp();
         if (lane < dh) m0 = (unsigned long long)keep_lo[2 * lane] | ((unsigned long long)keep_lo[2 * lane + 1] << 32);
         if (lane + 32 < dh) m1 = (unsigned long long)keep_lo[2 * lane + 64] | ((unsigned long long)keep_lo[2 * lane + 65] << 32);
-        const int tsel = use_hi ? t_ini : t_min;
-        if (tsel > tlo) {
-            unsigned long long f0 = 0, f1 = 0;
-            for (unsigned long long r = m0; r; r &= r - 1) {
-                const int bx = __ffsll((long long)r) - 1;
-                if (scb[(lane + 3) * sp + bx + xlo] >= tsel) f0 |= 1ull << bx;
-            }
-            for (unsigned long long r = m1; r; r &= r - 1) {
-                const int bx = __ffsll((long long)r) - 1;
-                if (scb[(lane + 35) * sp + bx + xlo] >= tsel) f1 |= 1ull << bx;
-            }
-            m0 = f0; m1 = f1;
-        }
+        if (__any_sync(0xffffffffu, (m0 | m1) != 0) || t_min == t_ini) break;     // keypoints found: no retry (:813)
     }
     // exclusive scan of the <= 59 row counts
     const int c0 = __popcll(m0), c1 = __popcll(m1);
