@@ -14,6 +14,8 @@
 // passes warp-per-key, is bit-identical but SLOWER -- 0.70-0.95 ms against 0.61 ms per 512 images -- because the
 // per-warp chain of dependent gathers leaves too few loads in flight at 64-125 registers; warp-per-key wins on
 // memory-level parallelism.
+// Also measured: the pattern as float in shared memory plus one 32-bit offset per gather -- 32 fewer I2F and ~50 fewer
+// address instructions per key, yet 0.59 ms against 0.54 ms (kept: int8 pattern, 64-bit IMAD.WIDE addressing).
 // LSU/gather-bound (SURVEY.md 8d K4+K5): algorithmic bytes = 961 (31x31 raw) + 1369 (37x37 blurred) + 60 out per key.
 #include <cfloat>
 
@@ -95,10 +97,16 @@ describe_kernel(const Geom g, const uint8_t* __restrict__ pyr, const uint8_t* __
         const int vl = lane < 31 ? c_umax[abs(u)] : -1;
         const uint8_t* col = ctr + u;
         int up[kHalfPatch + 1], dn[kHalfPatch + 1];
+        // running row pointers (one 64-bit add per load) instead of col +- v * pitch re-derived from the kernel arguments
+        const uint8_t* pu = col;
+        const uint8_t* pd = col;
+        up[0] = 0 <= vl ? (int)__ldg(col) : 0;
+        dn[0] = 0;
 #pragma unroll
-        for (int v = 0; v <= kHalfPatch; ++v) {
-            up[v] = v <= vl ? (int)__ldg(col - (ptrdiff_t)v * pitch) : 0;
-            dn[v] = (v >= 1 && v <= vl) ? (int)__ldg(col + (ptrdiff_t)v * pitch) : 0;
+        for (int v = 1; v <= kHalfPatch; ++v) {
+            pu -= pitch; pd += pitch;
+            up[v] = v <= vl ? (int)__ldg(pu) : 0;
+            dn[v] = v <= vl ? (int)__ldg(pd) : 0;
         }
         int sum = up[0];
 #pragma unroll
@@ -115,7 +123,9 @@ describe_kernel(const Geom g, const uint8_t* __restrict__ pyr, const uint8_t* __
     // ---- rBRIEF on the blurred level ----
     const float factorPI = (float)(3.14159265358979323846 / 180.0);
     const float ang = __fmul_rn(angle, factorPI);
-    const float a = (float)cos((double)ang), b = (float)sin((double)ang);
+    double sd, cd;
+    sincos((double)ang, &sd, &cd);                     // one shared range reduction; each result correctly rounded to float below
+    const float a = (float)cd, b = (float)sd;
     const uint8_t* bc = blur + L.boff + (size_t)img * L.bimg_stride + (size_t)y * L.bpitch + x;
     uint32_t val = 0;
 #pragma unroll
