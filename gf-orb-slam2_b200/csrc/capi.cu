@@ -50,7 +50,14 @@ struct gforb_batch {
     cudaEvent_t ev_start = nullptr, ev_down = nullptr;
     int chunk_frames = 0;        // 0 = automatic
     int last_launches = 0;       // kernels enqueued by the last run / frames_batch call
+    // Single-chunk calls (a frame or a few at a time: what a live Tracking does) are launch-bound -- 15 kernels, 7 copies
+    // and a dozen event operations for ~0.25 ms of device work -- so their whole H2D -> kernels -> D2H sequence is
+    // captured once into a CUDA graph per distinct argument set and replayed with one cudaGraphLaunch.
+    struct GraphSlot { const void* args[8]; int n; gforb_stereo_params prm; bool has_prm; cudaGraphExec_t exec; int launches; };
+    std::vector<GraphSlot> graphs;
+    bool use_graphs = true;
     ~gforb_batch() {
+        for (auto& gs : graphs) if (gs.exec) cudaGraphExecDestroy(gs.exec);
         for (auto& e : ev) if (e) cudaEventDestroy(e);
         for (auto& e : ev_up) if (e) cudaEventDestroy(e);
         for (auto& e : ev_done) if (e) cudaEventDestroy(e);
@@ -984,13 +991,64 @@ int gforb_batch_set_chunk(gforb_batch* b, int frames) {
 // Host buffers in, host buffers out.  The batch is cut into chunks; chunk c's H2D copy (upload stream), its
 // kernels (the batch's stream) and its D2H copy (download stream) are chained with events, so the copy engines
 // and the SMs work on different chunks at any time (kernels of even/odd chunks on two streams).  Results are complete when this returns.
+namespace {
+int frames_chunks(const gforb_batch* b, int n, std::vector<int>& csz);
+int frames_enqueue(gforb_batch* b, const uint8_t* left, const uint8_t* right, int n,
+                   const gforb_stereo_params* prm, int32_t* counts, gforb_keypoint* kps,
+                   uint8_t* desc, float* u_right, float* depth);
+}  // namespace
+
 int gforb_stereo_frames_batch_async(gforb_batch* b, const uint8_t* left, const uint8_t* right, int n,
                                     const gforb_stereo_params* prm, int32_t* counts, gforb_keypoint* kps,
                                     uint8_t* desc, float* u_right, float* depth) {
     if (!b || !left || !right || n < 1 || n > b->max_frames) { set_error("gforb_stereo_frames_batch: bad arguments"); return GFORB_ERR_ARG; }
-    // chunk schedule: fixed size when the caller set one; otherwise a short first chunk (the pipeline fills after
-    // 8 frames' worth of H2D), 32-frame chunks in the middle, and a short tail (its kernels + D2H are exposed)
+    static const bool graphs_off = getenv("GFORB_NO_GRAPH") != nullptr;     // A/B switch for measurements
     std::vector<int> csz;
+    if (graphs_off || !b->use_graphs || frames_chunks(b, n, csz) != 1)
+        return frames_enqueue(b, left, right, n, prm, counts, kps, desc, u_right, depth);
+    const void* args[8] = {left, right, counts, kps, desc, u_right, depth, nullptr};
+    for (auto& gs : b->graphs) {
+        if (gs.n == n && gs.has_prm == (prm != nullptr) && std::memcmp(gs.args, args, sizeof args) == 0 &&
+            (!prm || std::memcmp(&gs.prm, prm, sizeof *prm) == 0)) {
+            cudaError_t e = cudaGraphLaunch(gs.exec, b->stream);
+            if (e != cudaSuccess) return cuda_fail(e, "cudaGraphLaunch");
+            b->last_launches = gs.launches;
+            return GFORB_OK;
+        }
+    }
+    // first call with these arguments: capture it (the streams and events of the pipeline exist before the capture starts)
+    { const int rcp = ensure_pipeline(b, 1); if (rcp) return rcp; }
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    bool ok = cudaStreamBeginCapture(b->stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+    int rc = GFORB_OK;
+    if (ok) {
+        rc = frames_enqueue(b, left, right, n, prm, counts, kps, desc, u_right, depth);
+        ok = cudaStreamEndCapture(b->stream, &graph) == cudaSuccess && rc == GFORB_OK && graph != nullptr;
+    }
+    if (ok) ok = cudaGraphInstantiate(&exec, graph, 0) == cudaSuccess;
+    if (graph) cudaGraphDestroy(graph);
+    if (!ok) {                     // e.g. pageable host buffers cannot be captured: fall back to plain enqueue for this handle
+        (void)cudaGetLastError();
+        b->use_graphs = false;
+        return frames_enqueue(b, left, right, n, prm, counts, kps, desc, u_right, depth);
+    }
+    if (b->graphs.size() >= 8) { cudaGraphExecDestroy(b->graphs.front().exec); b->graphs.erase(b->graphs.begin()); }
+    gforb_batch::GraphSlot gs{};
+    std::memcpy(gs.args, args, sizeof args);
+    gs.n = n; gs.has_prm = prm != nullptr; if (prm) gs.prm = *prm;
+    gs.exec = exec; gs.launches = b->last_launches;
+    b->graphs.push_back(gs);
+    cudaError_t e = cudaGraphLaunch(exec, b->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGraphLaunch");
+    return GFORB_OK;
+}
+
+namespace {
+// chunk schedule: fixed size when the caller set one; otherwise a short first chunk (the pipeline fills after
+// 8 frames' worth of H2D), 32-frame chunks in the middle, and a short tail (its kernels + D2H are exposed)
+int frames_chunks(const gforb_batch* b, int n, std::vector<int>& csz) {
+    csz.clear();
     if (b->chunk_frames > 0 || n < 64) {
         const int chunk = std::min(b->chunk_frames > 0 ? b->chunk_frames : (n >= 48 ? 16 : n), n);
         for (int f = 0; f < n; f += chunk) csz.push_back(std::min(chunk, n - f));
@@ -1001,7 +1059,15 @@ int gforb_stereo_frames_batch_async(gforb_batch* b, const uint8_t* left, const u
         if (mid > 0) csz.push_back(mid);
         csz.push_back(16); csz.push_back(8);
     }
-    const int nchunks = (int)csz.size();
+    return (int)csz.size();
+}
+
+int frames_enqueue(gforb_batch* b, const uint8_t* left, const uint8_t* right, int n,
+                   const gforb_stereo_params* prm, int32_t* counts, gforb_keypoint* kps,
+                   uint8_t* desc, float* u_right, float* depth) {
+    if (!b || !left || !right || n < 1 || n > b->max_frames) { set_error("gforb_stereo_frames_batch: bad arguments"); return GFORB_ERR_ARG; }
+    std::vector<int> csz;
+    const int nchunks = frames_chunks(b, n, csz);
     std::vector<int> cf0(nchunks, 0);
     for (int c = 1; c < nchunks; ++c) cf0[c] = cf0[c - 1] + csz[c - 1];
     Engine& E = b->eng;
@@ -1014,7 +1080,8 @@ int gforb_stereo_frames_batch_async(gforb_batch* b, const uint8_t* left, const u
     GB(cudaEventRecord(b->ev_start, b->stream), "cudaEventRecord");
     GB(cudaStreamWaitEvent(b->s_up, b->ev_start, 0), "cudaStreamWaitEvent");
     GB(cudaStreamWaitEvent(b->s_down, b->ev_start, 0), "cudaStreamWaitEvent");
-    for (auto& sa : b->s_alt) GB(cudaStreamWaitEvent(sa, b->ev_start, 0), "cudaStreamWaitEvent");
+    if (nchunks > 1)     // a single chunk runs on the batch's own stream only (and must not leave unjoined work in a capture)
+        for (auto& sa : b->s_alt) GB(cudaStreamWaitEvent(sa, b->ev_start, 0), "cudaStreamWaitEvent");
     for (int c = 0; c < nchunks; ++c) {
         const int f0 = cf0[c], m = csz[c];
         GB(cudaMemcpy2DAsync(E.b.in + isz * (2 * (size_t)f0), 2 * isz, left + isz * f0, isz, isz, m,
@@ -1047,6 +1114,7 @@ int gforb_stereo_frames_batch_async(gforb_batch* b, const uint8_t* left, const u
 #undef GB
     return GFORB_OK;
 }
+}  // namespace
 
 int gforb_stereo_frames_batch(gforb_batch* b, const uint8_t* left, const uint8_t* right, int n,
                               const gforb_stereo_params* prm, int32_t* counts, gforb_keypoint* kps,

@@ -333,3 +333,41 @@ def test_async_submit_on_two_handles_equals_blocking(gf):
             c = ref[i]["counts"][2 * f]
             assert np.array_equal(outs[i]["u_right"][f, :c], ref[i]["u_right"][f, :c])
             assert np.array_equal(outs[i]["depth"][f, :c], ref[i]["depth"][f, :c])
+
+
+def test_graph_replay_of_single_chunk_calls(gf, O):
+    """A one-frame (single-chunk) gforb_stereo_frames_batch call is captured into a CUDA graph on first use and replayed
+    afterwards: new pixels in the same pinned buffers must give the new frame's result (== oracle), a different
+    argument set gets its own graph, and pageable buffers fall back to plain launches."""
+    frames = [synth_stereo(80 + i, nshapes=250) for i in range(4)]
+    sb = gf.StereoBatch(752, 480, 2)
+    pl, pr = gf.PinnedArray((1, 480, 752), np.uint8), gf.PinnedArray((1, 480, 752), np.uint8)
+    out = sb.alloc_outputs(1)
+
+    def check(o, l, r, f=0):
+        oxL, oxR = O.Extractor(), O.Extractor()
+        kL, dL, _ = oxL.extract(l); kR, dR, _ = oxR.extract(r)
+        ref = O.stereo_match(oxL, oxR, kL, dL, kR, dR, BF, B)
+        nL = o["counts"][2 * f]
+        _assert_extract_equal(o["keypoints"][2 * f, :nL], o["descriptors"][2 * f, :nL], kL, dL, "graph")
+        assert np.array_equal(o["u_right"][f, :nL], ref["uRight"]) and np.array_equal(o["depth"][f, :nL], ref["depth"])
+
+    for i in (0, 1, 2, 1):                       # first call captures, the rest replay the same graph
+        pl.array[0], pr.array[0] = frames[i]
+        sb.process(pl.array, pr.array, out, BF, B)
+        assert sb.last_launches() == sb.launches_per_run(True)
+        check(out, *frames[i])
+    out2 = sb.alloc_outputs(2)                   # another argument set (2 frames, other outputs): its own graph
+    l2 = gf.PinnedArray((2, 480, 752), np.uint8); r2 = gf.PinnedArray((2, 480, 752), np.uint8)
+    for rep in range(2):
+        l2.array[0], r2.array[0] = frames[3 - rep]; l2.array[1], r2.array[1] = frames[rep]
+        sb.process(l2.array, r2.array, out2, BF, B)
+        check(out2, *frames[3 - rep], f=0); check(out2, *frames[rep], f=1)
+    pl.array[0], pr.array[0] = frames[3]         # the first graph is still valid
+    sb.process(pl.array, pr.array, out, BF, B)
+    check(out, *frames[3])
+    sb2 = gf.StereoBatch(752, 480, 1)            # pageable buffers: capture is refused, plain path, same result
+    outp = sb2.alloc_outputs(1, pinned=False)
+    for i in (0, 2):
+        sb2.process(np.ascontiguousarray(frames[i][0][None]), np.ascontiguousarray(frames[i][1][None]), outp, BF, B)
+        check(outp, *frames[i])
