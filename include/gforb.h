@@ -307,7 +307,11 @@ GFORB_API int gforb_batch_download(gforb_batch* b, int n_frames, int32_t* counts
 /* wait for the stream and report device-side overflow flags as GFORB_ERR_OVERFLOW */
 GFORB_API int gforb_batch_sync(gforb_batch* b);
 
-/* upload + run + download + sync in one call: the end-to-end entry (host buffers in, host buffers out) */
+/* upload + run + download + sync in one call: the end-to-end entry (host buffers in, host buffers out).
+ * Calls small enough to be one pipeline chunk (< 48 frames: a live tracker's one frame at a time) are launch-bound, so
+ * their whole copy -> kernels -> copy sequence is captured into a CUDA graph the first time an argument set (pointers,
+ * n_frames, parameters) is seen and replayed with a single launch afterwards; up to 8 argument sets are kept per handle.
+ * Pageable host buffers cannot be captured: the handle then stays on plain launches.  Results are identical. */
 GFORB_API int gforb_stereo_frames_batch(gforb_batch* b, const uint8_t* left, const uint8_t* right, int n_frames,
                               const gforb_stereo_params* prm, int32_t* counts, gforb_keypoint* keypoints,
                               uint8_t* descriptors, float* u_right, float* depth);
