@@ -133,6 +133,16 @@ def cpu_baseline(left, right, threads, target_s=15.0):
     return nframes / secs, nframes, secs, chk
 
 
+def cpu_reference_shaped(left, right, nframes=48):
+    """The reference's own shape (src/Frame.cc:268-282): one frame at a time, one thread per eye, serial match."""
+    from oracle import pyoracle as O
+    n = min(len(left), 8)
+    imgs = np.empty((2 * n, H, W), np.uint8)
+    imgs[0::2], imgs[1::2] = left[:n], right[:n]
+    secs, _ = O.bench_stereo(imgs, nframes, 2, 1, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, BF, B)
+    return nframes / secs
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference algorithm's CPU path (oracle port; OpenCV C++ is not in the image so the
     reference's own sources cannot be compiled) on all host threads, same config/metric."""
@@ -412,6 +422,7 @@ def main():
         threads = os.cpu_count() or 1
         fps, nframes, secs, _ = cpu_baseline(left, right, threads)
         line["cpu_baseline"] = {"value": fps, "unit": UNIT, "cores": threads, "kind": "port",
+                                "reference_shaped_2_threads": round(cpu_reference_shaped(left, right), 1),
                                 "sample": f"{nframes} synthetic 752x480 stereo frames (same generator), oracle port, "
                                           f"{threads} threads each running whole frames, {secs:.1f} s"}
     emit(line)
