@@ -165,33 +165,33 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
 
         // ---- pass 1a: 4-pixel prefilter, 32 words per step; words with any flagged pixel are compacted by ONE ballot
         //      into a word list (row << 9 | word column << 4 | 4-bit pixel mask) ----
-        int ir = ir0, iw = iw0;
-        const uint32_t* p = reinterpret_cast<const uint32_t*>(tile) + (3 + ir) * tpw + w0 + iw;
+        int iw = iw0;
+        uint32_t ent = ((uint32_t)(3 + ir0) << 9) | ((uint32_t)(w0 + iw0) << 4);      // word-list entry of the lane's current item
+        const uint32_t ent_step = ((uint32_t)qs << 9) + ((uint32_t)rs << 4), ent_wrap = (1u << 9) - ((uint32_t)nw << 4);
+        const uint32_t* p = reinterpret_cast<const uint32_t*>(tile) + (3 + ir0) * tpw + w0 + iw0;
+        const bool list_all = tc == 0;                  // "> 0" has no cleared-low-bit form: list the whole domain
         int nwl = 0;
         for (int i0 = 0; i0 < nitems; i0 += 32) {
             uint32_t f = 0;
             if (i0 + lane < nitems) {
-                if (tc == 0) f = 0x80808080u;           // "> 0" has no cleared-low-bit form: list the whole domain
-                else {
-                    const uint32_t C = p[0], Wm = p[-1], Wp = p[1], U = p[-3 * tpw], D = p[3 * tpw];
-                    const uint32_t Lw = __funnelshift_r(Wm, C, 8), Rw = __funnelshift_r(C, Wp, 24);
-                    const uint32_t v = (__vabsdiffu4(C, U) | __vabsdiffu4(C, D)) & pmask;
-                    const uint32_t h = (__vabsdiffu4(C, Lw) | __vabsdiffu4(C, Rw)) & pmask;
-                    f = nz_lanes(v) & nz_lanes(h) & 0x80808080u;
-                }
+                const uint32_t C = p[0], Wm = p[-1], Wp = p[1], U = p[-3 * tpw], D = p[3 * tpw];
+                const uint32_t Lw = __funnelshift_r(Wm, C, 8), Rw = __funnelshift_r(C, Wp, 24);
+                const uint32_t v = (__vabsdiffu4(C, U) | __vabsdiffu4(C, D)) & pmask;
+                const uint32_t h = (__vabsdiffu4(C, Lw) | __vabsdiffu4(C, Rw)) & pmask;
+                f = list_all ? 0x80808080u : (nz_lanes(v) & nz_lanes(h) & 0x80808080u);
                 // columns outside [xlo, xhi) (first / last word of the row)
                 if (iw == 0) f &= cm_first;
                 if (iw == nw - 1) f &= cm_last;
             }
             const uint32_t m = __ballot_sync(0xffffffffu, f != 0);
             if (f != 0) {
-                // flag bits 7, 15, 23, 31 -> mask bits 0..3
-                const uint32_t m4 = ((f >> 7) & 1u) | ((f >> 14) & 2u) | ((f >> 21) & 4u) | ((f >> 28) & 8u);
-                wlist[nwl + __popc(m & lt)] = (uint16_t)(((3 + ir) << 9) | ((w0 + iw) << 4) | m4);
+                // flag bits 7, 15, 23, 31 -> mask bits 0..3: the four 0/1 bytes times 0x01020408 meet in the top byte
+                const uint32_t m4 = (((f >> 7) & 0x01010101u) * 0x01020408u) >> 24;
+                wlist[nwl + __popc(m & lt)] = (uint16_t)(ent | m4);
             }
             nwl += __popc(m);
-            iw += rs; ir += qs; p += pstep;
-            if (iw >= nw) { iw -= nw; ++ir; p += pwrap; }
+            iw += rs; p += pstep; ent += ent_step;
+            if (iw >= nw) { iw -= nw; p += pwrap; ent += ent_wrap; }
         }
         __syncwarp();
         // ---- pass 1b: expand the word list into the pixel list ((row << 8) | tile column); order is irrelevant.
