@@ -99,6 +99,9 @@ _SIGS = {
     "gforb_search_for_initialization": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _vp, C.POINTER(_i)]),
     "gforb_search_for_initialization_batch_device": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i,
                                                           _vp, _vp, _vp]),
+    "gforb_search_by_projection": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, C.POINTER(_i)]),
+    "gforb_search_by_projection_batch_device": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _i,
+                                                     _vp, _vp, _vp, _vp, _vp]),
     "gforb_rectifier_create": (_i, [_vp, _vp, _i, _i, C.POINTER(_vp)]),
     "gforb_rectifier_destroy": (None, [_vp]),
     "gforb_preprocess": (_i, [_vp, _vp, _i, _i, _sz, _i, _vp, _sz]),
@@ -245,6 +248,48 @@ class ORBmatcher:
             self._h, _p(b), n_pairs, ptr(dev_k1), ptr(dev_d1), ptr(dev_n1), stride1, ptr(dev_k2), ptr(dev_d2), ptr(dev_n2),
             stride2, ptr(dev_prev), int(windowSize), int(self.mbCheckOrientation), ptr(dev_m12), ptr(dev_nm),
             _vp(stream) if stream else None))
+
+    def SearchByProjection(self, keys, desc, queries, query_desc, u_right=None, occupied=None, th_dist=TH_HIGH,
+                           use_ratio=True, check_ori=None, bounds=None, width=None, height=None):
+        """ORBmatcher::SearchByProjection, the three per-frame forms (src/ORBmatcher.cc:155-241, 1440-1593, 1595-1721)
+        over already-projected queries (PROJ_QUERY_DTYPE records in the reference's iteration order; include/gforb.h
+        says how each caller fills them).  keys/desc/u_right = F.mvKeysUn / mDescriptors / mvuRight; occupied[k] != 0
+        where mvpMapPoints[k] already blocks.  check_ori None = the matcher's mbCheckOrientation (frame forms); the
+        map form (use_ratio=True) has no rotation check in the reference: pass check_ori=False there.
+        Returns (nmatches, key_query, key_dist, query_key)."""
+        b = _bounds(bounds, width, height)
+        k = np.ascontiguousarray(keys, KP_DTYPE); d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        q = np.ascontiguousarray(queries, PROJ_QUERY_DTYPE); qd = np.ascontiguousarray(query_desc, np.uint8).reshape(-1, 32)
+        assert len(d) == len(k) and len(qd) == len(q)
+        ur = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+        oc = None if occupied is None else np.ascontiguousarray(occupied, np.uint8)
+        assert (ur is None or len(ur) == len(k)) and (oc is None or len(oc) == len(k))
+        n, nq = len(k), len(q)
+        kq = np.empty(n, np.int32); kd = np.empty(n, np.int32); qk = np.empty(nq, np.int32)
+        nm = _i(0)
+        ori = self.mbCheckOrientation if check_ori is None else bool(check_ori)
+        _check(_L.gforb_search_by_projection(self._h, _p(b), _p(k) if n else None, _p(d) if n else None,
+                                             _p(ur) if (n and ur is not None) else None, _p(oc) if (n and oc is not None) else None,
+                                             n, _p(q) if nq else None, _p(qd) if nq else None, nq, int(th_dist), int(bool(use_ratio)),
+                                             int(ori), _p(kq) if n else None, _p(kd) if n else None, _p(qk) if nq else None,
+                                             C.byref(nm)))
+        return nm.value, kq, kd, qk
+
+    def SearchByProjectionBatchDevice(self, bounds, n_frames, dev_keys, dev_desc, dev_u_right, dev_occupied, dev_n, key_stride,
+                                      dev_queries, dev_qdesc, dev_nq, query_stride, th_dist, use_ratio, check_ori,
+                                      dev_key_query, dev_key_dist, dev_query_key, dev_nmatches, stream=None):
+        """device pointers (ints or DeviceArray); frame f at + f * stride; asynchronous (3 launches)"""
+        ptr = lambda x: None if x is None else _vp(x.ptr if isinstance(x, DeviceArray) else x)
+        b = _bounds(bounds, None, None)
+        _check(_L.gforb_search_by_projection_batch_device(
+            self._h, _p(b), n_frames, ptr(dev_keys), ptr(dev_desc), ptr(dev_u_right), ptr(dev_occupied), ptr(dev_n), key_stride,
+            ptr(dev_queries), ptr(dev_qdesc), ptr(dev_nq), query_stride, int(th_dist), int(bool(use_ratio)), int(bool(check_ori)),
+            ptr(dev_key_query), ptr(dev_key_dist), ptr(dev_query_key), ptr(dev_nmatches), _vp(stream) if stream else None))
+
+
+PROJ_QUERY_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("r", "<f4"), ("xr", "<f4"), ("angle", "<f4"),
+                             ("min_level", "<i4"), ("max_level", "<i4"), ("flags", "<i4")])
+PQ_ACTIVE, PQ_BLOCKS, PQ_RIGHT_GATE = 1, 2, 4
 
 
 FRAME_GRID_COLS, FRAME_GRID_ROWS = 64, 48      # include/Frame.h:92-93

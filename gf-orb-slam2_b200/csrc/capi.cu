@@ -615,6 +615,110 @@ int gforb_search_for_initialization(gforb_matcher* m, const gforb_frame_bounds* 
     return GFORB_OK;
 }
 
+int gforb_search_by_projection_batch_device(gforb_matcher* m, const gforb_frame_bounds* bounds, int n_frames,
+                                    const gforb_keypoint* keys, const uint8_t* desc, const float* u_right,
+                                    const uint8_t* occupied, const int32_t* n, int key_stride,
+                                    const gforb_proj_query* queries, const uint8_t* qdesc, const int32_t* nq, int q_stride,
+                                    int th_dist, int use_ratio, int check_orientation,
+                                    int32_t* key_query, int32_t* key_dist, int32_t* query_key, int32_t* nmatches,
+                                    void* cuda_stream) {
+    const char* fn = "gforb_search_by_projection";
+    if (!m || n_frames < 0 || key_stride < 0 || q_stride < 0 || !nmatches ||
+        (key_stride > 0 && (!keys || !desc || !key_query || !key_dist)) || (q_stride > 0 && (!queries || !qdesc || !query_key))) {
+        set_error(std::string(fn) + ": bad arguments");
+        return GFORB_ERR_ARG;
+    }
+    if (th_dist < 0 || th_dist > 255) { set_error(std::string(fn) + ": th_dist outside 0..255"); return GFORB_ERR_ARG; }
+    int rc = check_bounds(bounds, fn);
+    if (rc) return rc;
+    if (key_stride > gridmatch_max_keys() || q_stride > gridmatch_max_keys()) {
+        set_error(std::string(fn) + ": more than 8192 keys or queries per frame");
+        return GFORB_ERR_CAPACITY;
+    }
+    if (((uintptr_t)desc | (uintptr_t)qdesc) & 15) { set_error(std::string(fn) + ": descriptor arrays must be 16-byte aligned"); return GFORB_ERR_ARG; }
+    if (n_frames == 0) return GFORB_OK;
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : m->stream;
+    m->last = s;
+    const int cells = gridmatch_cells(), ks = std::max(key_stride, 1), qs = std::max(q_stride, 1);
+    const size_t bs = al16((size_t)n_frames * (cells + 1) * 4), bi = al16((size_t)n_frames * ks * 4), bp = (size_t)n_frames * qs * 32;
+    rc = m->reserve(m->scratch, m->scratch_bytes, bs + bi + bp);
+    if (rc) return rc;
+    uint8_t* base = static_cast<uint8_t*>(m->scratch);
+    int32_t* ds = reinterpret_cast<int32_t*>(base);
+    int32_t* di = reinterpret_cast<int32_t*>(base + bs);
+    const float bb[4] = {bounds->min_x, bounds->max_x, bounds->min_y, bounds->max_y};
+    M_CUDA(cudaEventRecord(m->ev0, s));
+    launch_grid_build(keys, n, key_stride, ks, n_frames, bb, ds, di, s);
+    ProjSearchArgs a{};
+    a.keys = keys; a.desc = desc; a.u_right = u_right; a.occupied = occupied; a.n = n;
+    a.q = queries; a.qdesc = qdesc; a.nq = nq;
+    a.n_fixed = key_stride; a.key_stride = ks; a.nq_fixed = q_stride; a.q_stride = qs;
+    a.cell_start = ds; a.cell_idx = di;
+    a.ratio = m->ratio; a.th_dist = th_dist; a.use_ratio = use_ratio ? 1 : 0; a.check_ori = check_orientation ? 1 : 0;
+    a.spec = reinterpret_cast<uint4*>(base + bs + bi);
+    a.key_query = key_query; a.key_dist = key_dist; a.query_key = query_key; a.nmatches = nmatches;
+    if (launch_proj_search(a, bb, n_frames, s)) { set_error(std::string(fn) + ": shared-memory opt-in failed"); return GFORB_ERR_CUDA; }
+    M_CUDA(cudaEventRecord(m->ev1, s));
+    M_CUDA(cudaGetLastError());
+    m->timed = true;
+    return GFORB_OK;
+}
+
+int gforb_search_by_projection(gforb_matcher* m, const gforb_frame_bounds* bounds, const gforb_keypoint* keys,
+                               const uint8_t* desc, const float* u_right, const uint8_t* occupied, int n,
+                               const gforb_proj_query* queries, const uint8_t* qdesc, int nq, int th_dist, int use_ratio,
+                               int check_orientation, int32_t* key_query, int32_t* key_dist, int32_t* query_key,
+                               int* nmatches) {
+    if (!m || n < 0 || nq < 0 || !nmatches || (n > 0 && (!keys || !desc || !key_query || !key_dist)) ||
+        (nq > 0 && (!queries || !qdesc || !query_key))) {
+        set_error("gforb_search_by_projection: bad arguments");
+        return GFORB_ERR_ARG;
+    }
+    *nmatches = 0;
+    const int n1 = std::max(n, 1), q1 = std::max(nq, 1);
+    const size_t kb = al16((size_t)n1 * sizeof(gforb_keypoint)), db = al16((size_t)n1 * 32), ub = al16((size_t)n1 * 4),
+                 ob = al16((size_t)n1), qb = al16((size_t)q1 * sizeof(gforb_proj_query)), qdb = al16((size_t)q1 * 32),
+                 kqb = al16((size_t)n1 * 4), qkb = al16((size_t)q1 * 4);
+    int rc = m->reserve(m->io, m->io_bytes, kb + db + ub + ob + qb + qdb + 2 * kqb + qkb + 16);
+    if (rc) return rc;
+    uint8_t* p = static_cast<uint8_t*>(m->io);
+    gforb_keypoint* dk = reinterpret_cast<gforb_keypoint*>(p); p += kb;
+    uint8_t* dd = p; p += db;
+    float* du = reinterpret_cast<float*>(p); p += ub;
+    uint8_t* docc = p; p += ob;
+    gforb_proj_query* dq = reinterpret_cast<gforb_proj_query*>(p); p += qb;
+    uint8_t* dqd = p; p += qdb;
+    int32_t* dkq = reinterpret_cast<int32_t*>(p); p += kqb;
+    int32_t* dkd = reinterpret_cast<int32_t*>(p); p += kqb;
+    int32_t* dqk = reinterpret_cast<int32_t*>(p); p += qkb;
+    int32_t* dn = reinterpret_cast<int32_t*>(p);
+    cudaStream_t s = m->stream;
+    if (n > 0) {
+        M_CUDA(cudaMemcpyAsync(dk, keys, (size_t)n * sizeof(gforb_keypoint), cudaMemcpyHostToDevice, s));
+        M_CUDA(cudaMemcpyAsync(dd, desc, (size_t)n * 32, cudaMemcpyHostToDevice, s));
+        if (u_right) M_CUDA(cudaMemcpyAsync(du, u_right, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+        if (occupied) M_CUDA(cudaMemcpyAsync(docc, occupied, (size_t)n, cudaMemcpyHostToDevice, s));
+    }
+    if (nq > 0) {
+        M_CUDA(cudaMemcpyAsync(dq, queries, (size_t)nq * sizeof(gforb_proj_query), cudaMemcpyHostToDevice, s));
+        M_CUDA(cudaMemcpyAsync(dqd, qdesc, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
+    }
+    rc = gforb_search_by_projection_batch_device(m, bounds, 1, dk, dd, u_right ? du : nullptr, occupied ? docc : nullptr, nullptr, n,
+                                                 dq, dqd, nullptr, nq, th_dist, use_ratio, check_orientation, dkq, dkd, dqk, dn,
+                                                 nullptr);
+    if (rc) return rc;
+    int32_t nm = 0;
+    if (n > 0) {
+        M_CUDA(cudaMemcpyAsync(key_query, dkq, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+        M_CUDA(cudaMemcpyAsync(key_dist, dkd, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+    }
+    if (nq > 0) M_CUDA(cudaMemcpyAsync(query_key, dqk, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaMemcpyAsync(&nm, dn, 4, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaStreamSynchronize(s));
+    *nmatches = nm;
+    return GFORB_OK;
+}
+
 // ------------------------------------------------------------------------------------------- pre-processing
 struct gforb_rectifier {
     int w = 0, h = 0;

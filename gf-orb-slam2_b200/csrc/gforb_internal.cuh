@@ -155,6 +155,23 @@ struct InitSearchArgs {
     int32_t* matches12;          // [pair][stride1]
     int32_t* nmatches;           // [pair]
 };
+// ORBmatcher::SearchByProjection over already-projected queries (k_gridmatch.cu); frame f reads keys + f * key_stride,
+// queries + f * q_stride; n / nq == nullptr: every frame has n_fixed / nq_fixed entries
+struct ProjSearchArgs {
+    const gforb_keypoint* keys; const uint8_t* desc; const float* u_right; const uint8_t* occupied; const int32_t* n;
+    const gforb_proj_query* q; const uint8_t* qdesc; const int32_t* nq;
+    int n_fixed, key_stride, nq_fixed, q_stride;
+    const int32_t* cell_start; const int32_t* cell_idx;
+    float min_x, min_y, w_inv, h_inv;
+    float ratio;
+    int th_dist, use_ratio, check_ori;
+    uint4* spec;                 // [frame][q_stride][2] scratch: each query's 8 smallest candidates, packed
+    int32_t* key_query;          // [frame][key_stride]
+    int32_t* key_dist;           // [frame][key_stride]
+    int32_t* query_key;          // [frame][q_stride]
+    int32_t* nmatches;           // [frame]
+};
+int launch_proj_search(const ProjSearchArgs& a, const float* bounds, int nframes, cudaStream_t s);   // 2 launches; -1: smem opt-in failed
 int gridmatch_max_keys();   // 8192 keys per frame
 int gridmatch_cells();      // 64 * 48
 // bounds = {mnMinX, mnMaxX, mnMinY, mnMaxY}; counts == nullptr: every frame has n_fixed keys.  1 launch.

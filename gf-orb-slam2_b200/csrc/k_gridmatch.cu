@@ -302,6 +302,252 @@ init_search_kernel(const InitSearchArgs a, int n1cap, int n2cap) {
     if (tid == 0) a.nmatches[p] = total;
 }
 
+// ------------------------------------------------------------------------------------------ SearchByProjection
+// src/ORBmatcher.cc:155-241 (map points), :1440-1593 (last frame), :1595-1721 (key frame), folded as include/gforb.h
+// describes.  Sequential rule in the reference: a key taken by a query whose map point has observations is skipped by
+// every later query.  Parallel restatement in two kernels:
+//   proj_scan_kernel     warp per query, whole grid: the query's kTopK smallest candidates (distance, then window
+//                        order) against the INITIAL occupancy, each packed as dist << 19 | CSR position << 6 | level;
+//   proj_resolve_kernel  CTA per frame, lists + claims + flags in shared memory, claims indexed by CSR POSITION so the
+//                        replay chases no global pointer.  Warp 0 replays the queries in order, 32 per step: a lane
+//                        walks its list past the positions already claimed; its answer is the sequential one unless
+//                        an earlier lane of the same step takes its best (or, with the ratio test, second-best)
+//                        position.  The lanes in front of the first such lane commit together and the step restarts
+//                        AT that lane, which as lane 0 sees every claim.  Only a query whose list ran out before the
+//                        answer was complete is re-scanned (whole warp, current claims).
+//                        Then rotation histogram, three maxima and removal by all threads.
+namespace {
+constexpr int kTopK = 8;
+constexpr int kLvlBits = 6;                                     // levels < 64
+constexpr int kDistShift = kPosBits + kLvlBits;
+constexpr uint32_t kTrunc = 0xFFFFFFFEu;                        // "more candidates may follow": list cut here
+
+__device__ __forceinline__ int key_pos(uint32_t e) { return (int)((e >> kLvlBits) & ((1u << kPosBits) - 1)); }
+
+// kByPos: `blocked` is indexed by CSR position (the replay's claims), else by key index (the caller's occupancy)
+template <bool kByPos>
+__device__ __forceinline__ void proj_scan(const GridView& g, const gforb_keypoint* __restrict__ keys,
+                                          const uint4* __restrict__ desc, const float* __restrict__ u_right,
+                                          const uint8_t* blocked, const gforb_proj_query& q, const uint4& a0,
+                                          const uint4& a1, int lane, uint32_t (&top)[kTopK]) {
+    uint32_t best = kNone, second = kNone;
+    int cnt = 0;
+    const bool gate = (q.flags & GFORB_PQ_RIGHT_GATE) && u_right;
+    int x0, x1, y0, y1;
+    if (area_window(g, q.x, q.y, q.r, x0, x1, y0, y1)) {
+        for (int ix = x0; ix <= x1; ++ix) {
+            const int j0 = __ldg(g.start + ix * kGRows + y0), j1 = __ldg(g.start + ix * kGRows + y1 + 1);
+            for (int j = j0 + lane; j < j1; j += 32) {
+                const int i = __ldg(g.idx + j);
+                if (!area_accepts(keys, i, q.x, q.y, q.r, q.min_level, q.max_level)) continue;
+                if (blocked && blocked[kByPos ? j : i]) continue;                      // :197-199, :1519-1521, :1662
+                if (gate) {                                                            // :201-206, :1523-1529
+                    const float ur = __ldg(u_right + i);
+                    if (ur > 0.0f && fabsf(__fsub_rn(q.xr, ur)) > q.r) continue;
+                }
+                const int dist = hamming256(a0, a1, __ldg(desc + 2 * (size_t)i), __ldg(desc + 2 * (size_t)i + 1));
+                if (dist >= 256) continue;                                             // never below the initial 256
+                const uint32_t key = ((uint32_t)dist << kDistShift) | ((uint32_t)j << kLvlBits) |
+                                     ((uint32_t)__ldg(&keys[i].octave) & ((1u << kLvlBits) - 1));
+                ++cnt;
+                second = min(second, max(best, key));
+                best = min(best, key);
+            }
+        }
+    }
+    // the warp's kTopK smallest, popped from the lanes' two smallest; a lane that gave both and had seen more may hide
+    // the next one: the list is cut there
+    bool trunc = false;
+#pragma unroll
+    for (int k = 0; k < kTopK; ++k) {
+        uint32_t m = __reduce_min_sync(0xFFFFFFFFu, best);
+        if (trunc) m = kTrunc;
+        top[k] = m;
+        bool spent = false;
+        if (m < kTrunc && best == m) { best = second; second = kNone; spent = best == kNone && cnt > 2; }
+        trunc = trunc || __any_sync(0xFFFFFFFFu, spent);
+    }
+}
+
+__device__ __forceinline__ GridView proj_grid(const ProjSearchArgs& a, int f) {
+    return GridView{a.cell_start + (size_t)f * (kGCells + 1), a.cell_idx + (size_t)f * a.key_stride, a.min_x, a.min_y,
+                    a.w_inv, a.h_inv};
+}
+}  // namespace
+
+__global__ void __launch_bounds__(256)
+proj_scan_kernel(const ProjSearchArgs a) {
+    const int f = blockIdx.y, lane = threadIdx.x & 31;
+    const int qi = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int nq = a.nq ? min(a.nq[f], a.q_stride) : a.nq_fixed;
+    if (qi >= nq) return;
+    const int n = a.n ? min(a.n[f], a.key_stride) : a.n_fixed;
+    const gforb_proj_query q = a.q[(size_t)f * a.q_stride + qi];
+    uint32_t top[kTopK];
+#pragma unroll
+    for (int k = 0; k < kTopK; ++k) top[k] = kNone;
+    if (n > 0 && (q.flags & GFORB_PQ_ACTIVE)) {
+        const uint4* qd = reinterpret_cast<const uint4*>(a.qdesc) + 2 * ((size_t)f * a.q_stride + qi);
+        const uint4 a0 = __ldg(qd), a1 = __ldg(qd + 1);
+        proj_scan<false>(proj_grid(a, f), a.keys + (size_t)f * a.key_stride,
+                         reinterpret_cast<const uint4*>(a.desc) + 2 * (size_t)f * a.key_stride,
+                         a.u_right ? a.u_right + (size_t)f * a.key_stride : nullptr,
+                         a.occupied ? a.occupied + (size_t)f * a.key_stride : nullptr, q, a0, a1, lane, top);
+    }
+    if (lane == 0) {
+        uint4* o = a.spec + 2 * ((size_t)f * a.q_stride + qi);
+        o[0] = make_uint4(top[0], top[1], top[2], top[3]);
+        o[1] = make_uint4(top[4], top[5], top[6], top[7]);
+    }
+}
+
+// dynamic shared: lists[nq_cap][topk] u32
+__global__ void __launch_bounds__(kSearchThreads)
+proj_resolve_kernel(const ProjSearchArgs a, int topk) {
+    extern __shared__ uint32_t lists[];
+    __shared__ uint8_t claimed[1 << kPosBits];                  // by CSR position
+    __shared__ uint8_t bin[1 << kPosBits];
+    __shared__ uint8_t qflag[1 << kPosBits];
+    __shared__ int hist[kHisto];
+    __shared__ int keep_bin[3];
+    __shared__ int total;
+    const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int n = a.n ? min(a.n[f], a.key_stride) : a.n_fixed;
+    const int nq = a.nq ? min(a.nq[f], a.q_stride) : a.nq_fixed;
+    const GridView g = proj_grid(a, f);
+    const gforb_keypoint* keys = a.keys + (size_t)f * a.key_stride;
+    const uint8_t* occ = a.occupied ? a.occupied + (size_t)f * a.key_stride : nullptr;
+    const gforb_proj_query* qs = a.q + (size_t)f * a.q_stride;
+    const uint32_t* spec = reinterpret_cast<const uint32_t*>(a.spec + 2 * (size_t)f * a.q_stride);
+    int32_t* key_query = a.key_query + (size_t)f * a.key_stride;
+    int32_t* key_dist = a.key_dist + (size_t)f * a.key_stride;
+    int32_t* query_key = a.query_key + (size_t)f * a.q_stride;
+
+    const int n_in = n > 0 ? __ldg(g.start + kGCells) : 0;      // keys inside the grid = CSR length
+    for (int j = tid; j < n_in; j += kSearchThreads) claimed[j] = occ ? (occ[__ldg(g.idx + j)] != 0) : 0;
+    for (int i = tid; i < n; i += kSearchThreads) { key_query[i] = -1; key_dist[i] = 0; }
+    for (int i = tid; i < nq; i += kSearchThreads) { bin[i] = 0xFF; query_key[i] = -1; qflag[i] = (uint8_t)qs[i].flags; }
+    for (int t = tid; t < nq * topk; t += kSearchThreads) {
+        const int qi = t / topk, k = t - qi * topk;
+        lists[t] = spec[qi * kTopK + k];
+    }
+    if (tid < kHisto) hist[tid] = 0;
+    if (tid == 0) total = 0;
+    __syncthreads();
+
+    if (wid == 0) {
+        const uint32_t full = 0xFFFFFFFFu;
+        // threshold (:228, :1532, :1674) and the same-level ratio test (:230) on packed entries
+        auto accepts = [&](uint32_t b, uint32_t s2) {
+            if (b >= kTrunc) return false;
+            const int bd = (int)(b >> kDistShift);
+            if (bd > a.th_dist) return false;
+            if (!a.use_ratio || s2 >= kTrunc) return true;                              // bestLevel2 = -1
+            const bool same_level = ((b ^ s2) & ((1u << kLvlBits) - 1)) == 0;
+            return !(same_level && (float)bd > __fmul_rn(a.ratio, (float)(s2 >> kDistShift)));
+        };
+        auto take = [&](int qi, uint32_t b, bool blocks) {                              // :232-236, :1534-1563
+            const int pos = key_pos(b), ib = __ldg(g.idx + pos);
+            query_key[qi] = ib;
+            if (blocks) claimed[pos] = 1;
+            if (a.check_ori) {                                                          // :1553-1562, :1681-1690
+                float rot = __fsub_rn(qs[qi].angle, __ldg(&keys[ib].angle));
+                if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+                int bb = (int)roundf(__fmul_rn(rot, 1.0f / kHisto));
+                bin[qi] = (uint8_t)(bb == kHisto ? 0 : bb);
+            }
+            return ib;
+        };
+        int base = 0;
+        while (base < nq) {
+            const int qi = base + lane;
+            const bool valid = qi < nq;
+            uint32_t b = kNone, s2 = kNone;
+            bool need = false;                                   // list ran out before the answer was complete
+            if (valid) {
+                int k = 0;
+                for (; k < topk; ++k) {
+                    const uint32_t e = lists[qi * topk + k];
+                    if (e == kNone) break;
+                    if (e == kTrunc) { need = true; break; }
+                    if (claimed[key_pos(e)]) continue;
+                    if (b == kNone) { b = e; if (!a.use_ratio) break; }
+                    else { s2 = e; break; }
+                }
+                if (k == topk) need = true;
+            }
+            if (__shfl_sync(full, (int)need, 0)) {               // lane 0 = query `base`: whole-warp re-scan
+                const gforb_proj_query q = qs[base];
+                const uint4* qd = reinterpret_cast<const uint4*>(a.qdesc) + 2 * ((size_t)f * a.q_stride + base);
+                const uint4 a0 = __ldg(qd), a1 = __ldg(qd + 1);
+                uint32_t top[kTopK];
+                proj_scan<true>(g, keys, reinterpret_cast<const uint4*>(a.desc) + 2 * (size_t)f * a.key_stride,
+                                a.u_right ? a.u_right + (size_t)f * a.key_stride : nullptr, claimed, q, a0, a1, lane, top);
+                if (lane == 0 && accepts(top[0], top[1])) {
+                    const int ib = take(base, top[0], q.flags & GFORB_PQ_BLOCKS);
+                    key_query[ib] = base; key_dist[ib] = (int)(top[0] >> kDistShift);
+                }
+                __syncwarp();
+                base += 1;
+                continue;
+            }
+            const bool acc = valid && !need && accepts(b, s2);
+            const bool blocks = acc && (qflag[valid ? qi : 0] & GFORB_PQ_BLOCKS);
+            const int bpos = b < kTrunc ? key_pos(b) : -2, spos = (a.use_ratio && s2 < kTrunc) ? key_pos(s2) : -2;
+            bool bad = need;
+            const int mine = blocks ? bpos : -1;
+            for (int o = 0; o < 31; ++o) {
+                const int op = __shfl_sync(full, mine, o);
+                if (o < lane && op >= 0 && (op == bpos || op == spos)) bad = true;
+            }
+            const uint32_t badm = __ballot_sync(full, bad);      // bit 0 is clear here
+            const int nb = badm ? __ffs(badm) - 1 : 32;
+            const bool commit = lane < nb && acc;
+            // equal positions among committing lanes: the earlier ones did not block, the last one holds the key
+            const uint32_t same = __match_any_sync(full, commit ? bpos : -3 - lane);
+            if (commit) {
+                const int ib = take(qi, b, blocks);
+                if ((same >> lane) == 1u) { key_query[ib] = qi; key_dist[ib] = (int)(b >> kDistShift); }
+            }
+            __syncwarp();
+            base += nb;
+        }
+    }
+    __syncthreads();
+
+    if (a.check_ori) {                                                       // :1568-1590, :1696-1718
+        for (int q = tid; q < nq; q += kSearchThreads)
+            if (bin[q] != 0xFF) atomicAdd(&hist[bin[q]], 1);
+        __syncthreads();
+        if (tid == 0) {                                                      // ComputeThreeMaxima, :1723-1764
+            int max1 = 0, max2 = 0, max3 = 0, i1 = -1, i2 = -1, i3 = -1;
+            for (int i = 0; i < kHisto; ++i) {
+                const int s = hist[i];
+                if (s > max1) { max3 = max2; max2 = max1; max1 = s; i3 = i2; i2 = i1; i1 = i; }
+                else if (s > max2) { max3 = max2; max2 = s; i3 = i2; i2 = i; }
+                else if (s > max3) { max3 = s; i3 = i; }
+            }
+            if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { i2 = -1; i3 = -1; }
+            else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { i3 = -1; }
+            keep_bin[0] = i1; keep_bin[1] = i2; keep_bin[2] = i3;
+        }
+        __syncthreads();
+    }
+    int mine = 0;
+    for (int q = tid; q < nq; q += kSearchThreads) {
+        int k = query_key[q];
+        if (k >= 0 && a.check_ori) {
+            const int b = bin[q];
+            if (b != keep_bin[0] && b != keep_bin[1] && b != keep_bin[2]) { key_query[k] = -2; query_key[q] = -1; k = -1; }
+        }
+        mine += k >= 0;
+    }
+    mine = __reduce_add_sync(0xFFFFFFFFu, mine);
+    if (lane == 0 && mine) atomicAdd(&total, mine);
+    __syncthreads();
+    if (tid == 0) a.nmatches[f] = total;
+}
+
 // --------------------------------------------------------------------------------------------------- launchers
 int gridmatch_max_keys() { return 1 << kPosBits; }
 int gridmatch_cells() { return kGCells; }
@@ -340,6 +586,23 @@ int launch_init_search(const InitSearchArgs& a, const float* bounds, int npairs,
         attr_have = smem;
     }
     init_search_kernel<<<npairs, kSearchThreads, smem, s>>>(b, n1cap, n2cap);
+    return 0;
+}
+
+int launch_proj_search(const ProjSearchArgs& a, const float* bounds, int nframes, cudaStream_t s) {
+    ProjSearchArgs b = a;
+    b.min_x = bounds[0]; b.min_y = bounds[2];
+    b.w_inv = 64.0f / (bounds[1] - bounds[0]); b.h_inv = 48.0f / (bounds[3] - bounds[2]);
+    const int qcap = a.nq ? a.q_stride : a.nq_fixed;
+    if (qcap > 0) proj_scan_kernel<<<dim3((qcap + 7) / 8, nframes), 256, 0, s>>>(b);
+    const int topk = qcap <= 4096 ? kTopK : kTopK / 2;           // lists stay within 128 KB of shared memory
+    const size_t smem = (size_t)std::max(qcap, 1) * topk * 4;
+    static size_t attr_have = 0;                                 // static shared memory takes 24 KB of the un-opted 48 KB
+    if (smem > attr_have) {
+        if (cudaFuncSetAttribute(proj_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
+        attr_have = smem;
+    }
+    proj_resolve_kernel<<<nframes, kSearchThreads, smem, s>>>(b, topk);
     return 0;
 }
 

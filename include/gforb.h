@@ -185,6 +185,55 @@ GFORB_API int gforb_search_for_initialization_batch_device(gforb_matcher* m, con
                                     const gforb_keypoint* dev_keys2, const uint8_t* dev_desc2, const int32_t* dev_n2, int stride2,
                                     float* dev_prev_xy, int window_size, int check_orientation,
                                     int32_t* dev_matches12, int32_t* dev_nmatches, void* cuda_stream);
+/* ORBmatcher::SearchByProjection -- the reference's three per-frame forms behind one entry:
+ *   SearchByProjection(Frame&, const vector<MapPoint*>&, th)                     src/ORBmatcher.cc:155-241
+ *   SearchByProjection(CurrentFrame, LastFrame, th, bMono)                       src/ORBmatcher.cc:1440-1593
+ *   SearchByProjection(CurrentFrame, KeyFrame*, sAlreadyFound, th, ORBdist)      src/ORBmatcher.cc:1595-1721
+ * All three walk their queries IN ORDER; per query: GetFeaturesInArea(x, y, r, minLevel, maxLevel), skip keys that
+ * already hold a map point, skip keys whose mvuRight is off by more than r, best (and second-best) Hamming distance,
+ * threshold, [ratio test when best and second sit on the same level], assign -- and, in the two frame forms, the
+ * 30-bin rotation histogram that clears the keys of all but the three largest bins.  What differs is how a query is
+ * derived from a MapPoint and a pose (projection, PredictScale, RadiusByViewingCos): that stays with the caller, who
+ * hands over one gforb_proj_query per candidate, in the reference's iteration order:
+ *   x, y        mTrackProjX/Y (:179) | u, v (:1481-1482, :1629-1630)
+ *   r           r * F.mvScaleFactors[nPredictedLevel] (:179) | th * mvScaleFactors[level] (:1495, :1648); also the
+ *               bound of the right-coordinate test (:204, :1527)
+ *   xr          mTrackProjXR (:203) | u - mbf * invzc (:1525)
+ *   angle       the query keypoint's angle for the rotation check (:1555, :1683)
+ *   min_level, max_level   as passed to GetFeaturesInArea (:179 | :1501-1506 | :1651)
+ *   flags       GFORB_PQ_ACTIVE      0 = the reference `continue`s before the window (:164-168, :1469-1489, :1617-1644)
+ *               GFORB_PQ_BLOCKS      pMP->Observations() > 0: later queries skip the key this one takes (:197-199,
+ *                                    :1519-1521); always set for the key-frame form (:1662-1663)
+ *               GFORB_PQ_RIGHT_GATE  apply the mvuRight test (map and last-frame forms)
+ * Frame side: keys = mvKeysUn, desc = mDescriptors, u_right = mvuRight (NULL: monocular), occupied[k] != 0 where
+ * mvpMapPoints[k] already blocks (has observations; key-frame form: is non-NULL) (NULL: none).  th_dist = TH_HIGH or
+ * ORBdist, 0..255 (bestDist starts at 256 with bestIdx = -1: a larger bound indexes [-1] in the reference); use_ratio = 1 for the map form (:230, mfNNratio = the matcher's ratio).
+ * Out: key_query[k] = index of the query whose map point key k holds on return (-1: untouched, -2: set to NULL by
+ * the rotation check), key_dist[k] = mvpMatchScore (:235), query_key[q] = key taken by query q (-1: none or removed),
+ * *nmatches = the reference's return value.  <= 8,192 keys and <= 8,192 queries per frame (GFORB_ERR_CAPACITY).
+ * The sequential dependence (a taken key disappears from later windows) is resolved on the device: every query's
+ * best / second-best is computed in parallel against the initial state, then one warp replays the queries in order,
+ * 32 at a time, re-scanning only those whose best or second-best key was taken meanwhile -- bit-identical results. */
+typedef struct gforb_proj_query { float x, y, r, xr, angle; int32_t min_level, max_level, flags; } gforb_proj_query;
+enum { GFORB_PQ_ACTIVE = 1, GFORB_PQ_BLOCKS = 2, GFORB_PQ_RIGHT_GATE = 4 };
+GFORB_API int gforb_search_by_projection(gforb_matcher* m, const gforb_frame_bounds* bounds,
+                                    const gforb_keypoint* keys, const uint8_t* desc, const float* u_right,
+                                    const uint8_t* occupied, int n,
+                                    const gforb_proj_query* queries, const uint8_t* query_desc, int nq,
+                                    int th_dist, int use_ratio, int check_orientation,
+                                    int32_t* key_query, int32_t* key_dist, int32_t* query_key, int* nmatches);
+/* Batched device form: frame f reads keys / u_right / occupied at + f * key_stride (descriptors * 32), queries at
+ * + f * query_stride, counts dev_n[f] / dev_nq[f] (NULL = every frame has key_stride / query_stride entries); outputs
+ * laid out the same way.  Descriptor arrays 16-byte aligned.  Asynchronous on `cuda_stream` (or the matcher's own);
+ * 3 launches (grid build, window scan, in-order resolution); gforb_matcher_sync returns their device time. */
+GFORB_API int gforb_search_by_projection_batch_device(gforb_matcher* m, const gforb_frame_bounds* bounds, int n_frames,
+                                    const gforb_keypoint* dev_keys, const uint8_t* dev_desc, const float* dev_u_right,
+                                    const uint8_t* dev_occupied, const int32_t* dev_n, int key_stride,
+                                    const gforb_proj_query* dev_queries, const uint8_t* dev_query_desc,
+                                    const int32_t* dev_nq, int query_stride,
+                                    int th_dist, int use_ratio, int check_orientation,
+                                    int32_t* dev_key_query, int32_t* dev_key_dist, int32_t* dev_query_key,
+                                    int32_t* dev_nmatches, void* cuda_stream);
 /* =====================================================================================================
  * Input pre-processing in front of ORBextractor::operator()   (SURVEY.md 8f row 3), one fused kernel:
  *   16-bit -> 8-bit   cv::imread(IMREAD_GRAYSCALE) of 16-bit PNGs keeps the high byte   test/test_Stereo.cpp:100-106

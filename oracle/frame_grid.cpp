@@ -169,6 +169,85 @@ int orc_search_for_initialization(const orc_keypoint* k1, const uint8_t* d1, int
     return nmatches;
 }
 
+
+// ORBmatcher::SearchByProjection, the three per-frame forms of the reference folded into one loop:
+//   (Frame&, vector<MapPoint*>, th)                       /root/reference/src/ORBmatcher.cc:155-241  (ratio test :230)
+//   (CurrentFrame, LastFrame, th, bMono)                  /root/reference/src/ORBmatcher.cc:1440-1593 (rotation check)
+//   (CurrentFrame, KeyFrame*, sAlreadyFound, th, ORBdist) /root/reference/src/ORBmatcher.cc:1595-1721 (rotation check)
+// What differs between them is data, not control flow, and comes in through the query record:
+//   x, y, r, min_level, max_level  the GetFeaturesInArea call (:179, :1501-1506, :1651)
+//   ACTIVE      the guards in front of the window (mbTrackInView / isBad :164-168; pMP, outlier, invzc, bounds :1469-1489)
+//   BLOCKS      pMP->Observations() > 0: a key this query takes is skipped by later queries (:197-199, :1519-1521);
+//               the third form skips ANY assigned key (:1662-1663) = every query blocks, every assigned key occupied
+//   RIGHT_GATE  the mvuRight test (:201-206, :1523-1529); its bound equals r in both forms (r * scale; radius)
+// Pose projection, PredictScale and RadiusByViewingCos stay with the caller (they read MapPoint / pose state).
+// key_query[k]: query holding key k when the call returns (-1 untouched, -2 set to NULL by the rotation check);
+// key_dist[k]: mvpMatchScore (:235); query_key[q]: key taken by query q (-1 none / removed).  Returns nmatches.
+int orc_search_by_projection(const orc_keypoint* keys, const uint8_t* desc, const float* u_right,
+                             const uint8_t* occupied, int n, const float* bounds, const orc_proj_query* qs,
+                             const uint8_t* qdesc, int nq, int th_dist, float nnratio, int use_ratio, int checkOri,
+                             int* key_query, int* key_dist, int* query_key) {
+    if (th_dist > 255) return -1;      // bestDist starts at 256 with bestIdx = -1 (:183, :1510): the reference would index [-1]
+    Grid g;
+    build_grid(g, keys, n, bounds);
+    int nmatches = 0;
+    std::vector<uint8_t> blocked(n, 0);
+    for (int k = 0; k < n; ++k) { key_query[k] = -1; key_dist[k] = 0; blocked[k] = occupied ? (occupied[k] != 0) : 0; }
+    for (int q = 0; q < nq; ++q) query_key[q] = -1;
+    std::vector<int> rotHist[kHisto], rotQuery[kHisto];
+    const float factor = 1.0f / kHisto;
+    for (int iq = 0; iq < nq; ++iq) {
+        const orc_proj_query& q = qs[iq];
+        if (!(q.flags & 1)) continue;
+        std::vector<int> vIndices = features_in_area(g, keys, q.x, q.y, q.r, q.min_level, q.max_level);
+        if (vIndices.empty()) continue;
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (int idx : vIndices) {
+            if (blocked[idx]) continue;
+            if ((q.flags & 4) && u_right && u_right[idx] > 0) {
+                const float er = std::fabs(q.xr - u_right[idx]);
+                if (er > q.r) continue;
+            }
+            const int dist = orc_hamming256(qdesc + 32 * (size_t)iq, desc + 32 * (size_t)idx);
+            if (dist < bestDist) {
+                bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = keys[idx].octave; bestIdx = idx;
+            } else if (dist < bestDist2) {
+                bestLevel2 = keys[idx].octave; bestDist2 = dist;
+            }
+        }
+        if (bestDist <= th_dist) {
+            if (use_ratio && bestLevel == bestLevel2 && (float)bestDist > nnratio * (float)bestDist2) continue;
+            key_query[bestIdx] = iq;
+            key_dist[bestIdx] = bestDist;
+            query_key[iq] = bestIdx;
+            if (q.flags & 2) blocked[bestIdx] = 1;
+            nmatches++;
+            if (checkOri) {
+                float rot = q.angle - keys[bestIdx].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = (int)std::round(rot * factor);
+                if (bin == kHisto) bin = 0;
+                rotHist[bin].push_back(bestIdx);
+                rotQuery[bin].push_back(iq);
+            }
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1, sizes[kHisto];
+        for (int i = 0; i < kHisto; ++i) sizes[i] = (int)rotHist[i].size();
+        three_maxima(sizes, kHisto, ind1, ind2, ind3);
+        for (int i = 0; i < kHisto; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0; j < rotHist[i].size(); ++j) {
+                key_query[rotHist[i][j]] = -2;
+                query_key[rotQuery[i][j]] = -1;
+                nmatches--;
+            }
+        }
+    }
+    return nmatches;
+}
+
 }  // extern "C"
 
 // MapPoint::ComputeDistinctiveDescriptors (/root/reference/src/MapPoint.cc:397-458), the descriptor part: for each

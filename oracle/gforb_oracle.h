@@ -84,6 +84,15 @@ int   orc_search_for_initialization(const orc_keypoint* k1, const uint8_t* d1, i
                                     const uint8_t* d2, int n2, const float* bounds, float* prev_xy, int windowSize,
                                     float nnratio, int checkOri, int* matches12);
 
+/* ORBmatcher::SearchByProjection, the three per-frame forms (src/ORBmatcher.cc:155-241, 1440-1593, 1595-1721) as one
+ * loop over already-projected queries; see oracle/frame_grid.cpp.  flags: 1 active, 2 blocks later queries,
+ * 4 right-coordinate gate.  u_right / occupied may be NULL. */
+typedef struct orc_proj_query { float x, y, r, xr, angle; int32_t min_level, max_level, flags; } orc_proj_query;
+int   orc_search_by_projection(const orc_keypoint* keys, const uint8_t* desc, const float* u_right,
+                               const uint8_t* occupied, int n, const float* bounds, const orc_proj_query* qs,
+                               const uint8_t* qdesc, int nq, int th_dist, float nnratio, int use_ratio, int checkOri,
+                               int* key_query, int* key_dist, int* query_key);
+
 /* Pre-processing in front of the extractor (oracle/preprocess.cpp): [16-bit -> high byte] -> cv::remap(INTER_LINEAR,
  * BORDER_CONSTANT 0, CV_32F maps; NULL maps = none, then dw x dh must equal the source size) -> cvtColor(*2GRAY).
  * fmt: 0 gray8, 1 gray16, 2 RGB8, 3 BGR8, 4 RGBA8, 5 BGRA8. */

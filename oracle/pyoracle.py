@@ -92,6 +92,9 @@ def lib():
     L.orc_search_for_initialization.argtypes = [C.c_void_p, u8p, C.c_int, C.c_void_p, u8p, C.c_int, fp, fp, C.c_int,
                                                 C.c_float, C.c_int, ip]
     L.orc_search_for_initialization.restype = C.c_int
+    L.orc_search_by_projection.argtypes = [C.c_void_p, u8p, fp, u8p, C.c_int, fp, C.c_void_p, u8p, C.c_int, C.c_int,
+                                           C.c_float, C.c_int, C.c_int, ip, ip, ip]
+    L.orc_search_by_projection.restype = C.c_int
     L.orc_preprocess.argtypes = [C.c_void_p, C.c_int, C.c_int, sz, C.c_int, fp, fp, C.c_int, C.c_int, u8p, sz]
     L.orc_preprocess.restype = C.c_int
     L.orc_undistort_matrix.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]; L.orc_undistort_matrix.restype = None
@@ -344,3 +347,23 @@ def distinctive_descriptors(desc, set_start):
     bi = np.empty(max(n, 1), np.int32); bm = np.empty(max(n, 1), np.int32)
     lib().orc_distinctive_descriptors(_p(desc), _p(ss), n, _p(bi), _p(bm))
     return bi[:n], bm[:n]
+
+
+PROJ_QUERY = np.dtype([("x", "<f4"), ("y", "<f4"), ("r", "<f4"), ("xr", "<f4"), ("angle", "<f4"),
+                       ("min_level", "<i4"), ("max_level", "<i4"), ("flags", "<i4")])
+PQ_ACTIVE, PQ_BLOCKS, PQ_RIGHT_GATE = 1, 2, 4
+
+
+def search_by_projection(keys, desc, u_right, occupied, bounds, queries, qdesc, th_dist=100, nnratio=0.8, use_ratio=True,
+                         check_ori=False):
+    """ORBmatcher::SearchByProjection over already-projected queries (src/ORBmatcher.cc:155-241, 1440-1593, 1595-1721;
+    oracle/frame_grid.cpp).  Returns (nmatches, key_query, key_dist, query_key)."""
+    keys = np.ascontiguousarray(keys); desc = np.ascontiguousarray(desc, np.uint8)
+    queries = np.ascontiguousarray(queries, PROJ_QUERY); qdesc = np.ascontiguousarray(qdesc, np.uint8)
+    ur = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+    oc = None if occupied is None else np.ascontiguousarray(occupied, np.uint8)
+    n, nq = len(keys), len(queries)
+    kq = np.empty(max(n, 1), np.int32); kd = np.empty(max(n, 1), np.int32); qk = np.empty(max(nq, 1), np.int32)
+    nm = lib().orc_search_by_projection(_p(keys), _p(desc), _p(ur), _p(oc), n, _p(_bounds(bounds)), _p(queries), _p(qdesc), nq,
+                                        int(th_dist), nnratio, int(bool(use_ratio)), int(bool(check_ori)), _p(kq), _p(kd), _p(qk))
+    return nm, kq[:n], kd[:n], qk[:nq]

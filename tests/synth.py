@@ -68,3 +68,69 @@ def rectify_maps(w, h, k1=-0.28, k2=0.07, tilt=0.012, shift=(3.25, -2.5), scale=
     r2 = xr * xr + yr * yr
     d = f(1) + f(k1) * r2 + f(k2) * r2 * r2
     return (xr * d * fl + cx + f(shift[0])).astype(np.float32), (yr * d * fl + cy + f(shift[1])).astype(np.float32)
+
+
+KEYPOINT = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+PROJ_QUERY = np.dtype([("x", "<f4"), ("y", "<f4"), ("r", "<f4"), ("xr", "<f4"), ("angle", "<f4"),
+                       ("min_level", "<i4"), ("max_level", "<i4"), ("flags", "<i4")])
+
+
+def projection_case(seed, n, nq, w=752, h=480, form="map", th=1.0, flip=0.07, p_dup=0.2, p_free=0.15, p_occupied=0.1,
+                    stereo=True):
+    """One SearchByProjection call's inputs: a frame (keys, descriptors, mvuRight, occupied keys) and nq already
+    projected queries that mostly re-observe the frame's keys (moved a few pixels, noisy descriptor, predicted level
+    off by one now and then), with deliberate competition: p_dup of the queries copy another query's target, p_free of
+    them do not block (Observations() == 0).  form: "map" (:155-241), "last" (:1440-1593) or "keyframe" (:1595-1721)
+    chooses how radius, level range and flags are derived, as the reference's three callers derive them."""
+    rng = np.random.default_rng(9000 + seed)
+    F = np.float32
+    scale = (F(1.2) ** np.arange(8)).astype(F)
+    keys = np.zeros(n, KEYPOINT)
+    keys["x"] = (rng.random(n) * (w + 40) - 20).astype(F); keys["y"] = (rng.random(n) * (h + 40) - 20).astype(F)
+    keys["angle"] = (rng.random(n) * 360).astype(F)
+    keys["octave"] = np.minimum(rng.geometric(0.35, n) - 1, 7)
+    keys["size"], keys["class_id"] = 31, -1
+    desc = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    u_right = np.where(rng.random(n) < (0.7 if stereo else 0.0), keys["x"] - (rng.random(n) * 50 + 1).astype(F), F(-1)).astype(F)
+    occupied = (rng.random(n) < p_occupied).astype(np.uint8)
+    q = np.zeros(nq, PROJ_QUERY)
+    qdesc = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
+    if n and nq:
+        tgt = rng.integers(0, n, nq)
+        dup = np.nonzero(rng.random(nq) < p_dup)[0]
+        tgt[dup] = tgt[rng.integers(0, nq, len(dup))]
+        sig = 1.5 if form == "map" else 4.0
+        q["x"] = keys["x"][tgt] + rng.normal(0, sig, nq).astype(F); q["y"] = keys["y"][tgt] + rng.normal(0, sig, nq).astype(F)
+        lvl = np.clip(keys["octave"][tgt] + rng.choice([0, 0, 0, 1, -1], nq), 0, 7)
+        q["angle"] = np.mod(keys["angle"][tgt] + rng.normal(12, 4, nq), 360).astype(F)
+        wild = rng.random(nq) < 0.12
+        q["angle"][wild] = (rng.random(int(wild.sum())) * 360).astype(F)
+        qdesc[:] = desc[tgt] ^ np.packbits(rng.random((nq, 256)) < flip, axis=1)
+        far = rng.random(nq) < 0.1                                     # descriptors that should fail the threshold
+        qdesc[far] = rng.integers(0, 256, (int(far.sum()), 32), dtype=np.uint8)
+        ur = u_right[tgt]
+        q["xr"] = np.where(rng.random(nq) < 0.85, ur + rng.normal(0, 1.0, nq), ur + 80).astype(F)
+        if form == "map":
+            r = np.where(rng.random(nq) < 0.5, F(2.5), F(4.0)).astype(F)          # RadiusByViewingCos, :243-249
+            if th != 1.0:
+                r = r * F(th)
+            q["r"] = r * scale[lvl]
+            q["min_level"], q["max_level"] = lvl - 1, lvl
+            q["flags"] = 1 | 4 | np.where(rng.random(nq) < p_free, 0, 2)
+        elif form == "last":
+            q["r"] = F(th) * scale[lvl]
+            mode = rng.integers(0, 3)                                             # bForward / bBackward / neither
+            if mode == 0:
+                q["min_level"], q["max_level"] = lvl, -1
+            elif mode == 1:
+                q["min_level"], q["max_level"] = 0, lvl
+            else:
+                q["min_level"], q["max_level"] = lvl - 1, lvl + 1
+            q["flags"] = 1 | 4 | np.where(rng.random(nq) < p_free, 0, 2)
+        else:
+            q["r"] = F(th) * scale[lvl]
+            q["min_level"], q["max_level"] = lvl - 1, lvl + 1
+            q["flags"] = 1 | 2
+        q["flags"] &= np.where(rng.random(nq) < 0.06, ~1, ~0)                     # not in view / bad / outlier
+    return keys, desc, u_right, occupied, q, qdesc
