@@ -312,10 +312,16 @@ init_search_kernel(const InitSearchArgs a, int n1cap, int n2cap) {
 //                        replay chases no global pointer.  Warp 0 replays the queries in order, 32 per step: a lane
 //                        walks its list past the positions already claimed; its answer is the sequential one unless
 //                        an earlier lane of the same step takes its best (or, with the ratio test, second-best)
-//                        position.  The lanes in front of the first such lane commit together and the step restarts
-//                        AT that lane, which as lane 0 sees every claim.  Only a query whose list ran out before the
-//                        answer was complete is re-scanned (whole warp, current claims).
-//                        Then rotation histogram, three maxima and removal by all threads.
+//                        position (shared atomicMin of the lane number per position).  The lanes in front of the
+//                        first such lane commit together and the step restarts AT that lane, which as lane 0 sees
+//                        every claim.  When the query at the head has used its list up, all 8 warps refresh the lists
+//                        of EVERY not-yet-replayed query in that state (claims only grow, so a list made under the
+//                        current claims stays valid), then the replay resumes.  What a query took stays in slot 0 of
+//                        its list; key indices, holders (atomicMax = last taker), scores, rotation bins, histogram,
+//                        three maxima and removal are written afterwards by all threads.
+// Measured (B200, 1,008 keys x 1,008 queries, last-frame form): 256 frames per launch 0.39-0.41 ms = 630-660 k frames/s;
+// one frame 81-114 us (grid 27, scan 15, resolve 44-70: the replay is one warp's dependent-instruction latency,
+// ~1,100 cycles per step, 35-52 steps) against 0.55 ms for the sequential CPU oracle.
 namespace {
 constexpr int kTopK = 8;
 constexpr int kLvlBits = 6;                                     // levels < 64
@@ -335,9 +341,10 @@ __device__ __forceinline__ void proj_scan(const GridView& g, const gforb_keypoin
     const bool gate = (q.flags & GFORB_PQ_RIGHT_GATE) && u_right;
     int x0, x1, y0, y1;
     if (area_window(g, q.x, q.y, q.r, x0, x1, y0, y1)) {
-        for (int ix = x0; ix <= x1; ++ix) {
+        int off = 0;                                  // entries dealt so far: the window's entries go round the lanes
+        for (int ix = x0; ix <= x1; ++ix) {           // across its columns, so no lane holds more than its share
             const int j0 = __ldg(g.start + ix * kGRows + y0), j1 = __ldg(g.start + ix * kGRows + y1 + 1);
-            for (int j = j0 + lane; j < j1; j += 32) {
+            for (int j = j0 + ((lane - off) & 31); j < j1; j += 32) {
                 const int i = __ldg(g.idx + j);
                 if (!area_accepts(keys, i, q.x, q.y, q.r, q.min_level, q.max_level)) continue;
                 if (blocked && blocked[kByPos ? j : i]) continue;                      // :197-199, :1519-1521, :1662
@@ -353,6 +360,7 @@ __device__ __forceinline__ void proj_scan(const GridView& g, const gforb_keypoin
                 second = min(second, max(best, key));
                 best = min(best, key);
             }
+            off = (off + j1 - j0) & 31;
         }
     }
     // the warp's kTopK smallest, popped from the lanes' two smallest; a lane that gave both and had seen more may hide
@@ -401,16 +409,17 @@ proj_scan_kernel(const ProjSearchArgs a) {
     }
 }
 
-// dynamic shared: lists[nq_cap][topk] u32
+// dynamic shared: lists[topk][nq] u32 (room for qcap queries) | tent[8192] u32
 __global__ void __launch_bounds__(kSearchThreads)
-proj_resolve_kernel(const ProjSearchArgs a, int topk) {
+proj_resolve_kernel(const ProjSearchArgs a, int topk, int qcap) {
     extern __shared__ uint32_t lists[];
+    uint32_t* tent = lists + (size_t)topk * qcap;               // by CSR position: first lane about to take it this step
     __shared__ uint8_t claimed[1 << kPosBits];                  // by CSR position
     __shared__ uint8_t bin[1 << kPosBits];
     __shared__ uint8_t qflag[1 << kPosBits];
     __shared__ int hist[kHisto];
     __shared__ int keep_bin[3];
-    __shared__ int total;
+    __shared__ int total, s_base, s_done;
     const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int n = a.n ? min(a.n[f], a.key_stride) : a.n_fixed;
     const int nq = a.nq ? min(a.nq[f], a.q_stride) : a.nq_fixed;
@@ -424,101 +433,126 @@ proj_resolve_kernel(const ProjSearchArgs a, int topk) {
     int32_t* query_key = a.query_key + (size_t)f * a.q_stride;
 
     const int n_in = n > 0 ? __ldg(g.start + kGCells) : 0;      // keys inside the grid = CSR length
-    for (int j = tid; j < n_in; j += kSearchThreads) claimed[j] = occ ? (occ[__ldg(g.idx + j)] != 0) : 0;
+    for (int j = tid; j < n_in; j += kSearchThreads) { claimed[j] = occ ? (occ[__ldg(g.idx + j)] != 0) : 0; tent[j] = kNone; }
     for (int i = tid; i < n; i += kSearchThreads) { key_query[i] = -1; key_dist[i] = 0; }
     for (int i = tid; i < nq; i += kSearchThreads) { bin[i] = 0xFF; query_key[i] = -1; qflag[i] = (uint8_t)qs[i].flags; }
-    for (int t = tid; t < nq * topk; t += kSearchThreads) {
+    for (int t = tid; t < nq * topk; t += kSearchThreads) {      // lists[k][query]: lanes = queries, no bank conflicts
         const int qi = t / topk, k = t - qi * topk;
-        lists[t] = spec[qi * kTopK + k];
+        lists[k * nq + qi] = spec[qi * kTopK + k];
     }
     if (tid < kHisto) hist[tid] = 0;
-    if (tid == 0) total = 0;
+    if (tid == 0) { total = 0; s_base = 0; s_done = 0; }
     __syncthreads();
 
-    if (wid == 0) {
-        const uint32_t full = 0xFFFFFFFFu;
-        // threshold (:228, :1532, :1674) and the same-level ratio test (:230) on packed entries
-        auto accepts = [&](uint32_t b, uint32_t s2) {
-            if (b >= kTrunc) return false;
-            const int bd = (int)(b >> kDistShift);
-            if (bd > a.th_dist) return false;
-            if (!a.use_ratio || s2 >= kTrunc) return true;                              // bestLevel2 = -1
-            const bool same_level = ((b ^ s2) & ((1u << kLvlBits) - 1)) == 0;
-            return !(same_level && (float)bd > __fmul_rn(a.ratio, (float)(s2 >> kDistShift)));
-        };
-        auto take = [&](int qi, uint32_t b, bool blocks) {                              // :232-236, :1534-1563
-            const int pos = key_pos(b), ib = __ldg(g.idx + pos);
-            query_key[qi] = ib;
-            if (blocks) claimed[pos] = 1;
-            if (a.check_ori) {                                                          // :1553-1562, :1681-1690
-                float rot = __fsub_rn(qs[qi].angle, __ldg(&keys[ib].angle));
-                if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
-                int bb = (int)roundf(__fmul_rn(rot, 1.0f / kHisto));
-                bin[qi] = (uint8_t)(bb == kHisto ? 0 : bb);
-            }
-            return ib;
-        };
-        int base = 0;
-        while (base < nq) {
-            const int qi = base + lane;
-            const bool valid = qi < nq;
-            uint32_t b = kNone, s2 = kNone;
-            bool need = false;                                   // list ran out before the answer was complete
-            if (valid) {
-                int k = 0;
-                for (; k < topk; ++k) {
-                    const uint32_t e = lists[qi * topk + k];
-                    if (e == kNone) break;
-                    if (e == kTrunc) { need = true; break; }
-                    if (claimed[key_pos(e)]) continue;
-                    if (b == kNone) { b = e; if (!a.use_ratio) break; }
-                    else { s2 = e; break; }
+    const uint32_t full = 0xFFFFFFFFu;
+    // threshold (:228, :1532, :1674) and the same-level ratio test (:230) on packed entries
+    auto accepts = [&](uint32_t b, uint32_t s2) {
+        if (b >= kTrunc) return false;
+        const int bd = (int)(b >> kDistShift);
+        if (bd > a.th_dist) return false;
+        if (!a.use_ratio || s2 >= kTrunc) return true;                              // bestLevel2 = -1
+        const bool same_level = ((b ^ s2) & ((1u << kLvlBits) - 1)) == 0;
+        return !(same_level && (float)bd > __fmul_rn(a.ratio, (float)(s2 >> kDistShift)));
+    };
+    // first (and, with the ratio test, second) entry of query qi's list whose position is still free;
+    // true = the list ran out before that answer was complete
+    auto walk = [&](int qi, uint32_t& b, uint32_t& s2) {
+        b = kNone; s2 = kNone;
+        int k = 0;
+        for (; k < topk; ++k) {
+            const uint32_t e = lists[k * nq + qi];
+            if (e == kNone) return false;
+            if (e == kTrunc) return true;
+            if (claimed[key_pos(e)]) continue;
+            if (b == kNone) { b = e; if (!a.use_ratio) return false; }
+            else { s2 = e; return false; }
+        }
+        return true;
+    };
+    while (true) {
+        if (wid == 0) {
+            int base = s_base;
+            bool stalled = false;
+            while (base < nq) {
+                const int qi = base + lane;
+                const bool valid = qi < nq;
+                uint32_t b = kNone, s2 = kNone;
+                const bool need = valid && walk(qi, b, s2);
+                if (__shfl_sync(full, (int)need, 0)) { stalled = true; break; }         // query `base` needs a fresh list
+                const bool acc = valid && !need && accepts(b, s2);
+                const bool blocks = acc && (qflag[valid ? qi : 0] & GFORB_PQ_BLOCKS);
+                const int bpos = b < kTrunc ? key_pos(b) : -2, spos = (a.use_ratio && s2 < kTrunc) ? key_pos(s2) : -2;
+                // does an earlier lane of this step take my best or second-best position?  Each
+                // position about to be taken gets the number of its first taker in tent[]; everyone looks up its own two
+                if (blocks) atomicMin(&tent[bpos], (uint32_t)lane);
+                __syncwarp();
+                const bool bad = need || (bpos >= 0 && tent[bpos] < (uint32_t)lane) || (spos >= 0 && tent[spos] < (uint32_t)lane);
+                __syncwarp();
+                if (blocks) tent[bpos] = kNone;
+                const uint32_t badm = __ballot_sync(full, bad);  // bit 0 is clear here
+                const int nb = badm ? __ffs(badm) - 1 : 32;
+                // slot 0 of a replayed query's list now holds what it took (kNone: nothing); the global side of the
+                // assignment (key index, holder, score, rotation bin) is written after the replay, by all threads
+                if (valid && lane < nb) {
+                    lists[qi] = acc ? b : kNone;
+                    if (blocks) claimed[bpos] = 1;
                 }
-                if (k == topk) need = true;
+                __syncwarp();
+                base += nb;
             }
-            if (__shfl_sync(full, (int)need, 0)) {               // lane 0 = query `base`: whole-warp re-scan
-                const gforb_proj_query q = qs[base];
-                const uint4* qd = reinterpret_cast<const uint4*>(a.qdesc) + 2 * ((size_t)f * a.q_stride + base);
+            if (lane == 0) { s_base = base; s_done = !stalled; }
+        }
+        __syncthreads();
+        if (s_done) break;
+        // refresh round, all warps: every query not yet replayed whose list is used up under the claims as they
+        // stand gets a new list (claims only grow, so a list made now stays a valid list later)
+        const int base = s_base;
+        for (int q0 = base + wid * 32; q0 < nq; q0 += kSearchThreads) {
+            const int qi = q0 + lane;
+            uint32_t b, s2;
+            uint32_t m = __ballot_sync(full, qi < nq && walk(qi, b, s2));
+            while (m) {
+                const int qr = q0 + __ffs(m) - 1;
+                m &= m - 1;
+                const gforb_proj_query q = qs[qr];
+                const uint4* qd = reinterpret_cast<const uint4*>(a.qdesc) + 2 * ((size_t)f * a.q_stride + qr);
                 const uint4 a0 = __ldg(qd), a1 = __ldg(qd + 1);
                 uint32_t top[kTopK];
                 proj_scan<true>(g, keys, reinterpret_cast<const uint4*>(a.desc) + 2 * (size_t)f * a.key_stride,
                                 a.u_right ? a.u_right + (size_t)f * a.key_stride : nullptr, claimed, q, a0, a1, lane, top);
-                if (lane == 0 && accepts(top[0], top[1])) {
-                    const int ib = take(base, top[0], q.flags & GFORB_PQ_BLOCKS);
-                    key_query[ib] = base; key_dist[ib] = (int)(top[0] >> kDistShift);
-                }
-                __syncwarp();
-                base += 1;
-                continue;
+#pragma unroll
+                for (int k = 0; k < kTopK; ++k)
+                    if (lane == 0 && k < topk) lists[k * nq + qr] = top[k];
             }
-            const bool acc = valid && !need && accepts(b, s2);
-            const bool blocks = acc && (qflag[valid ? qi : 0] & GFORB_PQ_BLOCKS);
-            const int bpos = b < kTrunc ? key_pos(b) : -2, spos = (a.use_ratio && s2 < kTrunc) ? key_pos(s2) : -2;
-            bool bad = need;
-            const int mine = blocks ? bpos : -1;
-            for (int o = 0; o < 31; ++o) {
-                const int op = __shfl_sync(full, mine, o);
-                if (o < lane && op >= 0 && (op == bpos || op == spos)) bad = true;
-            }
-            const uint32_t badm = __ballot_sync(full, bad);      // bit 0 is clear here
-            const int nb = badm ? __ffs(badm) - 1 : 32;
-            const bool commit = lane < nb && acc;
-            // equal positions among committing lanes: the earlier ones did not block, the last one holds the key
-            const uint32_t same = __match_any_sync(full, commit ? bpos : -3 - lane);
-            if (commit) {
-                const int ib = take(qi, b, blocks);
-                if ((same >> lane) == 1u) { key_query[ib] = qi; key_dist[ib] = (int)(b >> kDistShift); }
-            }
-            __syncwarp();
-            base += nb;
+        }
+        __syncthreads();
+    }
+
+    // the assignments (:232-236, :1534-1563): key index of each taken position, rotation bin, and the key's holder =
+    // the LAST query that took it (an earlier taker that did not block is overwritten, as in the reference)
+    for (int q = tid; q < nq; q += kSearchThreads) {
+        const uint32_t e = lists[q];
+        if (e >= kTrunc) continue;
+        const int ib = __ldg(g.idx + key_pos(e));
+        query_key[q] = ib;
+        atomicMax(&key_query[ib], q);
+        if (a.check_ori) {                                                   // :1553-1562, :1681-1690
+            float rot = __fsub_rn(qs[q].angle, __ldg(&keys[ib].angle));
+            if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+            int bb = (int)roundf(__fmul_rn(rot, 1.0f / kHisto));
+            bb = bb == kHisto ? 0 : bb;
+            bin[q] = (uint8_t)bb;
+            atomicAdd(&hist[bb], 1);
         }
     }
     __syncthreads();
-
+    for (int q = tid; q < nq; q += kSearchThreads) {
+        const uint32_t e = lists[q];
+        if (e >= kTrunc) continue;
+        const int ib = query_key[q];
+        if (key_query[ib] == q) key_dist[ib] = (int)(e >> kDistShift);       // mvpMatchScore, :235
+    }
     if (a.check_ori) {                                                       // :1568-1590, :1696-1718
-        for (int q = tid; q < nq; q += kSearchThreads)
-            if (bin[q] != 0xFF) atomicAdd(&hist[bin[q]], 1);
-        __syncthreads();
         if (tid == 0) {                                                      // ComputeThreeMaxima, :1723-1764
             int max1 = 0, max2 = 0, max3 = 0, i1 = -1, i2 = -1, i3 = -1;
             for (int i = 0; i < kHisto; ++i) {
@@ -531,8 +565,8 @@ proj_resolve_kernel(const ProjSearchArgs a, int topk) {
             else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { i3 = -1; }
             keep_bin[0] = i1; keep_bin[1] = i2; keep_bin[2] = i3;
         }
-        __syncthreads();
     }
+    __syncthreads();
     int mine = 0;
     for (int q = tid; q < nq; q += kSearchThreads) {
         int k = query_key[q];
@@ -596,13 +630,13 @@ int launch_proj_search(const ProjSearchArgs& a, const float* bounds, int nframes
     const int qcap = a.nq ? a.q_stride : a.nq_fixed;
     if (qcap > 0) proj_scan_kernel<<<dim3((qcap + 7) / 8, nframes), 256, 0, s>>>(b);
     const int topk = qcap <= 4096 ? kTopK : kTopK / 2;           // lists stay within 128 KB of shared memory
-    const size_t smem = (size_t)std::max(qcap, 1) * topk * 4;
+    const size_t smem = (size_t)std::max(qcap, 1) * topk * 4 + (4u << kPosBits);
     static size_t attr_have = 0;                                 // static shared memory takes 24 KB of the un-opted 48 KB
     if (smem > attr_have) {
         if (cudaFuncSetAttribute(proj_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
         attr_have = smem;
     }
-    proj_resolve_kernel<<<nframes, kSearchThreads, smem, s>>>(b, topk);
+    proj_resolve_kernel<<<nframes, kSearchThreads, smem, s>>>(b, topk, std::max(qcap, 1));
     return 0;
 }
 

@@ -25,13 +25,29 @@ desc = np.ascontiguousarray(out["descriptors"][0::2]); qdesc = np.ascontiguousar
 n = np.ascontiguousarray(out["counts"][0::2]); nq = np.ascontiguousarray(out["counts"][1::2])
 ur = np.ascontiguousarray(out["u_right"], np.float32).reshape(P, K)
 scale = (np.float32(bench.SCALE) ** np.arange(bench.NLEVELS)).astype(np.float32)
-q = np.zeros((P, K), gf.PROJ_QUERY_DTYPE)
-q["x"], q["y"], q["angle"] = k2["x"], k2["y"], k2["angle"]
-oct2 = np.clip(k2["octave"], 0, bench.NLEVELS - 1)
-q["r"] = np.float32(TH) * scale[oct2]
-q["min_level"], q["max_level"] = oct2 - 1, oct2 + 1
-q["xr"] = k2["x"] - 20.0
-q["flags"] = gf.PQ_ACTIVE | gf.PQ_BLOCKS | gf.PQ_RIGHT_GATE
+def make_queries(kq):
+    q = np.zeros((P, K), gf.PROJ_QUERY_DTYPE)
+    q["x"], q["y"], q["angle"] = kq["x"], kq["y"], kq["angle"]
+    o = np.clip(kq["octave"], 0, bench.NLEVELS - 1)
+    q["r"] = np.float32(TH) * scale[o]
+    q["min_level"], q["max_level"] = o - 1, o + 1
+    q["xr"] = kq["x"] - 20.0
+    q["flags"] = gf.PQ_ACTIVE | gf.PQ_BLOCKS | gf.PQ_RIGHT_GATE
+    return q
+
+
+if len(sys.argv) > 2 and sys.argv[2] == "tracking":
+    # the tracking case: the frame's own keypoints as the last frame's points after a small motion (3 px sigma, 5 % of
+    # the descriptor bits flipped), so nearly every query finds its key -- TrackWithMotionModel's regime
+    rng = np.random.default_rng(7)
+    k2 = keys.copy()
+    k2["x"] += rng.normal(0, 3, k2.shape).astype(np.float32); k2["y"] += rng.normal(0, 3, k2.shape).astype(np.float32)
+    qdesc = desc ^ np.packbits(rng.random(desc.shape[:2] + (256,)) < 0.05, axis=2)
+    nq = n.copy()
+    scenario = "tracking: own keypoints moved by N(0, 3 px), 5 % descriptor bits flipped"
+else:
+    scenario = "stereo pair as consecutive frames: right-eye keypoints into the left-eye frame"
+q = make_queries(k2)
 bounds = (0.0, float(bench.W), 0.0, float(bench.H))
 D = gf.DeviceArray.from_host
 dk, dd, du, dn, dq, dqd, dnq = D(keys), D(desc), D(ur), D(n), D(q), D(qdesc), D(nq)
@@ -68,7 +84,7 @@ for it in range(13):
     m.SearchByProjection(keys[0, :n[0]], desc[0, :n[0]], q[0, :nq[0]], qdesc[0, :nq[0]], ur[0, :n[0]], None, 100, False, True, bounds=bounds)
     if it >= 3:
         t.append(time.perf_counter() - t0)
-print(json.dumps({"what": "ORBmatcher::SearchByProjection (last-frame form, th 15, rotation check), device",
+print(json.dumps({"what": "ORBmatcher::SearchByProjection (last-frame form, th 15, rotation check), device", "scenario": scenario,
                   "frames": P, "keys_per_frame": float(n.mean()), "queries_per_frame": float(nq.mean()),
                   "ms_per_batch": ms, "frames_per_s": P / ms * 1e3, "us_per_frame_amortised": ms * 1e3 / P,
                   "us_one_frame_device": ms_one * 1e3, "us_one_frame_host_to_host": float(np.median(t)) * 1e6,
