@@ -165,6 +165,30 @@ public:
               "SearchForInitialization");
         return nmatches;
     }
+    // The per-frame SearchByProjection forms (src/ORBmatcher.cc:155-241, 1440-1593, 1595-1721) over queries the caller
+    // has projected (one gforb_proj_query + 32 descriptor bytes per MapPoint, in the reference's iteration order; gforb.h
+    // says how each form fills them).  mvuRight / occupied may be NULL.  vpMatchedQuery[k] = index of the query whose
+    // MapPoint F.mvpMapPoints[k] becomes (-1: leave as is, -2: set to NULL), vMatchScore[k] = F.mvpMatchScore[k].
+    //   map form:        SearchByProjection(F, ..., queries, qdesc, TH_HIGH, true,  false, ...)
+    //   last-frame form: SearchByProjection(F, ..., queries, qdesc, TH_HIGH, false, mbCheckOrientation, ...)
+    //   key-frame form:  SearchByProjection(F, ..., queries, qdesc, ORBdist, false, mbCheckOrientation, ...)
+    int SearchByProjection(const FrameView& F, const float* mvuRight, const uint8_t* occupied,
+                           const std::vector<gforb_proj_query>& queries, const uint8_t* queryDescriptors, int thDist,
+                           bool ratioTest, bool checkOrientation, std::vector<int>& vpMatchedQuery,
+                           std::vector<int>* vMatchScore = nullptr, std::vector<int>* vQueryKey = nullptr) {
+        const int n = (int)F.mvKeysUn->size(), nq = (int)queries.size();
+        vpMatchedQuery.assign(n, -1);
+        std::vector<int> score(n > 0 ? n : 1), qkey(nq > 0 ? nq : 1);
+        int nmatches = 0;
+        check(gforb_search_by_projection(handle(), &F.bounds, F.mvKeysUn->data(), F.mDescriptors, mvuRight, occupied, n,
+                                         queries.data(), queryDescriptors, nq, thDist, ratioTest ? 1 : 0,
+                                         checkOrientation ? 1 : 0, vpMatchedQuery.data(), score.data(), qkey.data(), &nmatches),
+              "SearchByProjection");
+        if (vMatchScore) vMatchScore->assign(score.begin(), score.begin() + n);
+        if (vQueryKey) vQueryKey->assign(qkey.begin(), qkey.begin() + nq);
+        return nmatches;
+    }
+    bool checkOrientation() const { return mbCheckOrientation; }
     gforb_matcher* handle() {
         if (!h_) check(gforb_matcher_create(mfNNratio, &h_), "ORBmatcher");
         return h_;

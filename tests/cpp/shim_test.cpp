@@ -54,6 +54,20 @@ int main(int argc, char** argv) {
         printf("init nmatches=%d m12=%016llx prev=%016llx area=%zu area_hash=%016llx\n", ninit,
                (unsigned long long)fnv(m12.data(), m12.size() * 4), (unsigned long long)fnv(prev.data(), prev.size() * 8),
                area.size(), (unsigned long long)fnv(area.data(), area.size() * sizeof(size_t)));
+        // last-frame SearchByProjection (src/ORBmatcher.cc:1440-1593): the right eye's keypoints as the last frame's
+        // points projected into the left frame, th = 15, stereo gate against the mvuRight just computed
+        std::vector<gforb_proj_query> pq(kR.size());
+        for (size_t i = 0; i < kR.size(); ++i) {
+            float sc = 1.f;
+            for (int l = 0; l < kR[i].octave; ++l) sc *= 1.2f;
+            pq[i] = {kR[i].x, kR[i].y, 15.f * sc, kR[i].x - 20.f, kR[i].angle, kR[i].octave - 1, kR[i].octave + 1,
+                     GFORB_PQ_ACTIVE | GFORB_PQ_BLOCKS | GFORB_PQ_RIGHT_GATE};
+        }
+        std::vector<int> kq, kd, qk;
+        const int nproj = matcher.SearchByProjection(F1, u.data(), nullptr, pq, dR.data(), gforb::ORBmatcher::TH_HIGH, false,
+                                                     matcher.checkOrientation(), kq, &kd, &qk);
+        printf("proj nmatches=%d kq=%016llx kd=%016llx qk=%016llx\n", nproj, (unsigned long long)fnv(kq.data(), kq.size() * 4),
+               (unsigned long long)fnv(kd.data(), kd.size() * 4), (unsigned long long)fnv(qk.data(), qk.size() * 4));
         // an empty image is the reference's silent no-op
         std::vector<gforb_keypoint> k0; std::vector<uint8_t> d0;
         exL(nullptr, 0, 0, 0, k0, d0);

@@ -47,6 +47,21 @@ def test_cpp_shim_matches_ctypes(fixtures):
     assert (int(mi[1]), int(mi[2])) == (n, len(area)) and n > 0 and len(area) > 0
     assert int(hs["m12"], 16) == _fnv(m12) and int(hs["prev"], 16) == _fnv(prev)
     assert int(hs["area_hash"], 16) == _fnv(area.astype(np.uint64))
+    # last-frame SearchByProjection through the C++ mirror == the ctypes mirror
+    mp = re.search(r"proj nmatches=(\d+) ", out.stdout)
+    q = np.zeros(len(kR), gf.PROJ_QUERY_DTYPE)
+    sc = np.ones(len(kR), np.float32)
+    for lvl in range(1, 8):
+        sc[kR["octave"] >= lvl] *= np.float32(1.2)
+    q["x"], q["y"], q["angle"] = kR["x"], kR["y"], kR["angle"]
+    q["r"] = np.float32(15.0) * sc
+    q["xr"] = kR["x"] - np.float32(20.0)
+    q["min_level"], q["max_level"] = kR["octave"] - 1, kR["octave"] + 1
+    q["flags"] = gf.PQ_ACTIVE | gf.PQ_BLOCKS | gf.PQ_RIGHT_GATE
+    nm, kq, kd, qk = gf.ORBmatcher(0.9, True).SearchByProjection(kL, dL, q, dR, s["mvuRight"], None, 100, False, True,
+                                                                 width=752, height=480)
+    assert int(mp[1]) == nm > 0
+    assert int(hs["kq"], 16) == _fnv(kq) and int(hs["kd"], 16) == _fnv(kd) and int(hs["qk"], 16) == _fnv(qk)
 
 
 def test_tma_probe():
