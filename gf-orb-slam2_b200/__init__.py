@@ -102,6 +102,10 @@ _SIGS = {
     "gforb_search_by_projection": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, C.POINTER(_i)]),
     "gforb_search_by_projection_batch_device": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _i,
                                                      _vp, _vp, _vp, _vp, _vp]),
+    "gforb_search_by_bow": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _vp,
+                                 C.POINTER(_i)]),
+    "gforb_search_by_bow_device": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _vp,
+                                        _vp, _vp]),
     "gforb_rectifier_create": (_i, [_vp, _vp, _i, _i, C.POINTER(_vp)]),
     "gforb_rectifier_destroy": (None, [_vp]),
     "gforb_preprocess": (_i, [_vp, _vp, _i, _i, _sz, _i, _vp, _sz]),
@@ -285,6 +289,37 @@ class ORBmatcher:
             self._h, _p(b), n_frames, ptr(dev_keys), ptr(dev_desc), ptr(dev_u_right), ptr(dev_occupied), ptr(dev_n), key_stride,
             ptr(dev_queries), ptr(dev_qdesc), ptr(dev_nq), query_stride, int(th_dist), int(bool(use_ratio)), int(bool(check_ori)),
             ptr(dev_key_query), ptr(dev_key_dist), ptr(dev_query_key), ptr(dev_nmatches), _vp(stream) if stream else None))
+
+    def SearchByBoW(self, keys1, desc1, valid1, featvec1, keys2, desc2, valid2, featvec2, th_dist=TH_LOW):
+        """ORBmatcher::SearchByBoW (src/ORBmatcher.cc:270-404: valid2=None, th_dist=TH_LOW; :635-768: th_dist=TH_LOW - 1).
+        featvecX = DBoW2::FeatureVector as {node id: [feature indices]} or an already flattened
+        (node_ids, node_start, node_idx) triple.  Returns (nmatches, matches12)."""
+        k1 = np.ascontiguousarray(keys1, KP_DTYPE); k2 = np.ascontiguousarray(keys2, KP_DTYPE)
+        d1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32); d2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+        assert len(d1) == len(k1) and len(d2) == len(k2)
+        v1 = None if valid1 is None else np.ascontiguousarray(valid1, np.uint8)
+        v2 = None if valid2 is None else np.ascontiguousarray(valid2, np.uint8)
+        i1, s1, x1 = flatten_feature_vector(featvec1); i2, s2, x2 = flatten_feature_vector(featvec2)
+        n1, n2 = len(k1), len(k2)
+        m12 = np.full(n1, -1, np.int32)
+        nm = _i(0)
+        opt = lambda a: _p(a) if (a is not None and len(a)) else None
+        _check(_L.gforb_search_by_bow(self._h, opt(k1), opt(d1), opt(v1), n1, opt(i1), opt(s1) if len(i1) else None, opt(x1), len(i1),
+                                      opt(k2), opt(d2), opt(v2), n2, opt(i2), opt(s2) if len(i2) else None, opt(x2), len(i2),
+                                      int(th_dist), int(self.mbCheckOrientation), opt(m12), C.byref(nm)))
+        return nm.value, m12
+
+
+def flatten_feature_vector(fv):
+    """DBoW2::FeatureVector ({node id: [feature indices]}) -> (node_ids ascending, node_start CSR, node_idx) int32 arrays"""
+    if isinstance(fv, tuple):
+        return tuple(np.ascontiguousarray(a, np.int32) for a in fv)
+    ids = np.array(sorted(fv), np.int32)
+    start = np.zeros(len(ids) + 1, np.int32)
+    if len(ids):
+        start[1:] = np.cumsum([len(fv[i]) for i in ids])
+    idx = np.array([j for i in ids for j in fv[i]], np.int32)
+    return ids, start, idx
 
 
 PROJ_QUERY_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("r", "<f4"), ("xr", "<f4"), ("angle", "<f4"),

@@ -719,6 +719,82 @@ int gforb_search_by_projection(gforb_matcher* m, const gforb_frame_bounds* bound
     return GFORB_OK;
 }
 
+int gforb_search_by_bow_device(gforb_matcher* m, const gforb_keypoint* k1, const uint8_t* d1, const uint8_t* valid1, int n1,
+                               const int32_t* node_id1, const int32_t* node_start1, const int32_t* node_idx1, int nn1,
+                               const gforb_keypoint* k2, const uint8_t* d2, const uint8_t* valid2, int n2,
+                               const int32_t* node_id2, const int32_t* node_start2, const int32_t* node_idx2, int nn2,
+                               int th_dist, int check_orientation, int32_t* matches12, int32_t* nmatches, void* cuda_stream) {
+    const char* fn = "gforb_search_by_bow";
+    if (!m || n1 < 0 || n2 < 0 || nn1 < 0 || nn2 < 0 || !nmatches || (n1 > 0 && (!k1 || !d1 || !matches12)) || (n2 > 0 && (!k2 || !d2)) ||
+        (nn1 > 0 && (!node_id1 || !node_start1 || !node_idx1)) || (nn2 > 0 && (!node_id2 || !node_start2 || !node_idx2))) {
+        set_error(std::string(fn) + ": bad arguments");
+        return GFORB_ERR_ARG;
+    }
+    if (th_dist < 0 || th_dist > 255) { set_error(std::string(fn) + ": th_dist outside 0..255"); return GFORB_ERR_ARG; }
+    if (((uintptr_t)d1 | (uintptr_t)d2) & 15) { set_error(std::string(fn) + ": descriptor arrays must be 16-byte aligned"); return GFORB_ERR_ARG; }
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : m->stream;
+    m->last = s;
+    int rc = m->reserve(m->scratch, m->scratch_bytes, al16((size_t)std::max(n2, 1)));
+    if (rc) return rc;
+    BowSearchArgs a{};
+    a.k1 = k1; a.d1 = d1; a.valid1 = valid1; a.n1 = n1; a.node_id1 = node_id1; a.node_start1 = node_start1; a.node_idx1 = node_idx1; a.nn1 = nn1;
+    a.k2 = k2; a.d2 = d2; a.valid2 = valid2; a.n2 = n2; a.node_id2 = node_id2; a.node_start2 = node_start2; a.node_idx2 = node_idx2; a.nn2 = nn2;
+    a.th_dist = th_dist; a.ratio = m->ratio; a.check_ori = check_orientation ? 1 : 0;
+    a.matched2 = static_cast<uint8_t*>(m->scratch); a.matches12 = matches12; a.nmatches = nmatches;
+    M_CUDA(cudaEventRecord(m->ev0, s));
+    launch_bow_search(a, s);
+    M_CUDA(cudaEventRecord(m->ev1, s));
+    M_CUDA(cudaGetLastError());
+    m->timed = true;
+    return GFORB_OK;
+}
+
+int gforb_search_by_bow(gforb_matcher* m, const gforb_keypoint* k1, const uint8_t* d1, const uint8_t* valid1, int n1,
+                        const int32_t* node_id1, const int32_t* node_start1, const int32_t* node_idx1, int nn1,
+                        const gforb_keypoint* k2, const uint8_t* d2, const uint8_t* valid2, int n2,
+                        const int32_t* node_id2, const int32_t* node_start2, const int32_t* node_idx2, int nn2,
+                        int th_dist, int check_orientation, int32_t* matches12, int* nmatches) {
+    const char* fn = "gforb_search_by_bow";
+    if (!m || n1 < 0 || n2 < 0 || nn1 < 0 || nn2 < 0 || !nmatches || (n1 > 0 && (!k1 || !d1 || !matches12)) || (n2 > 0 && (!k2 || !d2)) ||
+        (nn1 > 0 && (!node_id1 || !node_start1 || !node_idx1)) || (nn2 > 0 && (!node_id2 || !node_start2 || !node_idx2))) {
+        set_error(std::string(fn) + ": bad arguments");
+        return GFORB_ERR_ARG;
+    }
+    *nmatches = 0;
+    const int e1 = nn1 > 0 ? node_start1[nn1] : 0, e2 = nn2 > 0 ? node_start2[nn2] : 0;      // feature-vector entries
+    for (int i = 0; i < e1; ++i) if (node_idx1[i] < 0 || node_idx1[i] >= n1) { set_error(std::string(fn) + ": feature index out of range"); return GFORB_ERR_ARG; }
+    for (int i = 0; i < e2; ++i) if (node_idx2[i] < 0 || node_idx2[i] >= n2) { set_error(std::string(fn) + ": feature index out of range"); return GFORB_ERR_ARG; }
+    struct Seg { const void* src; size_t bytes; size_t off; };
+    Seg seg[14] = {{k1, (size_t)n1 * sizeof(gforb_keypoint), 0}, {d1, (size_t)n1 * 32, 0}, {valid1, valid1 ? (size_t)n1 : 0, 0},
+                   {node_id1, (size_t)nn1 * 4, 0}, {node_start1, nn1 > 0 ? (size_t)(nn1 + 1) * 4 : 0, 0}, {node_idx1, (size_t)e1 * 4, 0},
+                   {k2, (size_t)n2 * sizeof(gforb_keypoint), 0}, {d2, (size_t)n2 * 32, 0}, {valid2, valid2 ? (size_t)n2 : 0, 0},
+                   {node_id2, (size_t)nn2 * 4, 0}, {node_start2, nn2 > 0 ? (size_t)(nn2 + 1) * 4 : 0, 0}, {node_idx2, (size_t)e2 * 4, 0},
+                   {nullptr, (size_t)std::max(n1, 1) * 4, 0}, {nullptr, 16, 0}};
+    size_t total = 0;
+    for (Seg& g : seg) { g.off = total; total += al16(g.bytes ? g.bytes : 16); }
+    int rc = m->reserve(m->io, m->io_bytes, total);
+    if (rc) return rc;
+    uint8_t* base = static_cast<uint8_t*>(m->io);
+    cudaStream_t s = m->stream;
+    for (int i = 0; i < 12; ++i)
+        if (seg[i].bytes) M_CUDA(cudaMemcpyAsync(base + seg[i].off, seg[i].src, seg[i].bytes, cudaMemcpyHostToDevice, s));
+    auto at = [&](int i) { return base + seg[i].off; };
+    int32_t* dm = reinterpret_cast<int32_t*>(at(12));
+    int32_t* dn = reinterpret_cast<int32_t*>(at(13));
+    rc = gforb_search_by_bow_device(m, reinterpret_cast<gforb_keypoint*>(at(0)), at(1), valid1 ? at(2) : nullptr, n1,
+                                    reinterpret_cast<int32_t*>(at(3)), reinterpret_cast<int32_t*>(at(4)), reinterpret_cast<int32_t*>(at(5)), nn1,
+                                    reinterpret_cast<gforb_keypoint*>(at(6)), at(7), valid2 ? at(8) : nullptr, n2,
+                                    reinterpret_cast<int32_t*>(at(9)), reinterpret_cast<int32_t*>(at(10)), reinterpret_cast<int32_t*>(at(11)), nn2,
+                                    th_dist, check_orientation, dm, dn, nullptr);
+    if (rc) return rc;
+    int32_t nm = 0;
+    if (n1 > 0) M_CUDA(cudaMemcpyAsync(matches12, dm, (size_t)n1 * 4, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaMemcpyAsync(&nm, dn, 4, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaStreamSynchronize(s));
+    *nmatches = nm;
+    return GFORB_OK;
+}
+
 // ------------------------------------------------------------------------------------------- pre-processing
 struct gforb_rectifier {
     int w = 0, h = 0;

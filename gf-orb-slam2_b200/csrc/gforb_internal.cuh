@@ -172,6 +172,18 @@ struct ProjSearchArgs {
     int32_t* nmatches;           // [frame]
 };
 int launch_proj_search(const ProjSearchArgs& a, const float* bounds, int nframes, cudaStream_t s);   // 2 launches; -1: smem opt-in failed
+// ORBmatcher::SearchByBoW over flattened DBoW2 feature vectors (k_gridmatch.cu); all pointers device
+struct BowSearchArgs {
+    const gforb_keypoint* k1; const uint8_t* d1; const uint8_t* valid1; int n1;
+    const int32_t* node_id1; const int32_t* node_start1; const int32_t* node_idx1; int nn1;
+    const gforb_keypoint* k2; const uint8_t* d2; const uint8_t* valid2; int n2;
+    const int32_t* node_id2; const int32_t* node_start2; const int32_t* node_idx2; int nn2;
+    int th_dist; float ratio; int check_ori;
+    uint8_t* matched2;           // [n2] scratch
+    int32_t* matches12;          // [n1]
+    int32_t* nmatches;           // [1]
+};
+void launch_bow_search(const BowSearchArgs& a, cudaStream_t s);   // 2 memsets + 2 launches
 int gridmatch_max_keys();   // 8192 keys per frame
 int gridmatch_cells();      // 64 * 48
 // bounds = {mnMinX, mnMaxX, mnMinY, mnMaxY}; counts == nullptr: every frame has n_fixed keys.  1 launch.

@@ -582,6 +582,111 @@ proj_resolve_kernel(const ProjSearchArgs a, int topk, int qcap) {
     if (tid == 0) a.nmatches[f] = total;
 }
 
+// -------------------------------------------------------------------------------------------------- SearchByBoW
+// src/ORBmatcher.cc:270-404 (key frame against a frame) and :635-768 (key frame against key frame) over flattened
+// DBoW2 feature vectors.  A feature sits in exactly one vocabulary node, so the reference's one sequential rule -- a
+// matched candidate is skipped by later queries -- never crosses a node: nodes run in parallel, one warp per node of
+// frame 1 (binary search for the same id in frame 2: the reference's merge with lower_bound visits exactly the ids
+// both maps hold), the node's queries in order inside the warp, lanes over the node's candidates.
+__global__ void __launch_bounds__(256)
+bow_match_kernel(const BowSearchArgs a) {
+    const int lane = threadIdx.x & 31, node = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (node >= a.nn1) return;
+    const int id = __ldg(a.node_id1 + node);
+    int lo = 0, hi = a.nn2;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(a.node_id2 + mid) < id) lo = mid + 1; else hi = mid;
+    }
+    if (lo == a.nn2 || __ldg(a.node_id2 + lo) != id) return;
+    const int b0 = __ldg(a.node_start2 + lo), b1 = __ldg(a.node_start2 + lo + 1);
+    const uint4* d1 = reinterpret_cast<const uint4*>(a.d1);
+    const uint4* d2 = reinterpret_cast<const uint4*>(a.d2);
+    volatile uint8_t* matched2 = a.matched2;
+    constexpr int kListBits = 22;                                       // position inside the node's candidate list
+    for (int i = __ldg(a.node_start1 + node); i < __ldg(a.node_start1 + node + 1); ++i) {
+        const int idx1 = __ldg(a.node_idx1 + i);
+        if (a.valid1 && !__ldg(a.valid1 + idx1)) continue;              // :300-306, :679-684
+        const uint4 a0 = __ldg(d1 + 2 * (size_t)idx1), a1 = __ldg(d1 + 2 * (size_t)idx1 + 1);
+        uint32_t best = kNone, second = kNone;
+        for (int b = b0 + lane; b < b1; b += 32) {
+            const int idx2 = __ldg(a.node_idx2 + b);
+            if (matched2[idx2] || (a.valid2 && !__ldg(a.valid2 + idx2))) continue;      // :321, :701-706
+            const int dist = hamming256(a0, a1, __ldg(d2 + 2 * (size_t)idx2), __ldg(d2 + 2 * (size_t)idx2 + 1));
+            if (dist >= 256) continue;                                                   // never below the initial 256
+            const uint32_t key = ((uint32_t)dist << kListBits) | (uint32_t)(b - b0);
+            second = min(second, max(best, key));
+            best = min(best, key);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const uint32_t ob = __shfl_xor_sync(0xFFFFFFFFu, best, o), os = __shfl_xor_sync(0xFFFFFFFFu, second, o);
+            second = min(min(second, os), max(best, ob));
+            best = min(best, ob);
+        }
+        if (best != kNone && lane == 0) {
+            const int bd = (int)(best >> kListBits), sd = second == kNone ? 256 : (int)(second >> kListBits);
+            if (bd <= a.th_dist && (float)bd < __fmul_rn(a.ratio, (float)sd)) {          // :337-339, :718-720
+                const int idx2 = __ldg(a.node_idx2 + b0 + (int)(best & ((1u << kListBits) - 1)));
+                a.matches12[idx1] = idx2;
+                matched2[idx2] = 1;
+            }
+        }
+        __syncwarp();
+    }
+}
+
+// rotation histogram over the matches, three maxima, removal, count (:378-401, :745-766)
+__global__ void __launch_bounds__(256)
+bow_finish_kernel(const BowSearchArgs a) {
+    __shared__ int hist[kHisto];
+    __shared__ int keep_bin[3];
+    __shared__ int total;
+    const int tid = threadIdx.x, lane = tid & 31;
+    if (tid < kHisto) hist[tid] = 0;
+    if (tid == 0) total = 0;
+    __syncthreads();
+    auto rotation_bin = [&](int i1, int i2) {
+        float rot = __fsub_rn(__ldg(&a.k1[i1].angle), __ldg(&a.k2[i2].angle));
+        if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+        const int b = (int)roundf(__fmul_rn(rot, 1.0f / kHisto));
+        return b == kHisto ? 0 : b;
+    };
+    if (a.check_ori) {
+        for (int i = tid; i < a.n1; i += 256) {
+            const int m = a.matches12[i];
+            if (m >= 0) atomicAdd(&hist[rotation_bin(i, m)], 1);
+        }
+        __syncthreads();
+        if (tid == 0) {                                                      // ComputeThreeMaxima, :1723-1764
+            int max1 = 0, max2 = 0, max3 = 0, i1 = -1, i2 = -1, i3 = -1;
+            for (int i = 0; i < kHisto; ++i) {
+                const int s = hist[i];
+                if (s > max1) { max3 = max2; max2 = max1; max1 = s; i3 = i2; i2 = i1; i1 = i; }
+                else if (s > max2) { max3 = max2; max2 = s; i3 = i2; i2 = i; }
+                else if (s > max3) { max3 = s; i3 = i; }
+            }
+            if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { i2 = -1; i3 = -1; }
+            else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { i3 = -1; }
+            keep_bin[0] = i1; keep_bin[1] = i2; keep_bin[2] = i3;
+        }
+        __syncthreads();
+    }
+    int mine = 0;
+    for (int i = tid; i < a.n1; i += 256) {
+        int m = a.matches12[i];
+        if (m >= 0 && a.check_ori) {
+            const int b = rotation_bin(i, m);
+            if (b != keep_bin[0] && b != keep_bin[1] && b != keep_bin[2]) { a.matches12[i] = -1; m = -1; }
+        }
+        mine += m >= 0;
+    }
+    mine = __reduce_add_sync(0xFFFFFFFFu, mine);
+    if (lane == 0 && mine) atomicAdd(&total, mine);
+    __syncthreads();
+    if (tid == 0) *a.nmatches = total;
+}
+
 // --------------------------------------------------------------------------------------------------- launchers
 int gridmatch_max_keys() { return 1 << kPosBits; }
 int gridmatch_cells() { return kGCells; }
@@ -638,6 +743,13 @@ int launch_proj_search(const ProjSearchArgs& a, const float* bounds, int nframes
     }
     proj_resolve_kernel<<<nframes, kSearchThreads, smem, s>>>(b, topk, std::max(qcap, 1));
     return 0;
+}
+
+void launch_bow_search(const BowSearchArgs& a, cudaStream_t s) {
+    if (a.n1 > 0) cudaMemsetAsync(a.matches12, 0xFF, (size_t)a.n1 * 4, s);
+    if (a.n2 > 0) cudaMemsetAsync(a.matched2, 0, (size_t)a.n2, s);
+    if (a.nn1 > 0 && a.nn2 > 0) bow_match_kernel<<<(a.nn1 + 7) / 8, 256, 0, s>>>(a);
+    bow_finish_kernel<<<1, 256, 0, s>>>(a);
 }
 
 }  // namespace gforb

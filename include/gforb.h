@@ -234,6 +234,37 @@ GFORB_API int gforb_search_by_projection_batch_device(gforb_matcher* m, const gf
                                     int th_dist, int use_ratio, int check_orientation,
                                     int32_t* dev_key_query, int32_t* dev_key_dist, int32_t* dev_query_key,
                                     int32_t* dev_nmatches, void* cuda_stream);
+/* ORBmatcher::SearchByBoW, both forms:
+ *   SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches)        src/ORBmatcher.cc:270-404
+ *   SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12)       src/ORBmatcher.cc:635-768
+ * Frame 1 = the key frame whose features are the queries; frame 2 = the Frame / second key frame whose features are
+ * the candidates.  mFeatVec (DBoW2::FeatureVector = std::map<NodeId, std::vector<unsigned>>,
+ * Thirdparty/DBoW2/DBoW2/FeatureVector.h; computing it needs the vocabulary and stays with the caller) arrives
+ * flattened: node_id ascending (the map's order), node_start CSR offsets (n_nodes + 1), node_idx = the vectors' feature
+ * indices in their order.  valid1[i] != 0 where the query's MapPoint exists and is not bad (:300-306, :679-684; NULL =
+ * all); valid2[j] the same for the candidates of the key-frame form (:700-706; NULL for the Frame form).  th_dist is
+ * inclusive, 0..255: GFORB_TH_LOW for the Frame form (`<=`, :337), GFORB_TH_LOW - 1 for the key-frame form (`<`, :718);
+ * mfNNratio = the matcher's ratio; check_orientation = mbCheckOrientation.
+ * Out: matches12[i] = index in frame 2 matched to feature i of frame 1, -1 = none -- vpMatches12 of the key-frame
+ * form; for the Frame form vpMapPointMatches[matches12[i]] = pKF's MapPoint i (a candidate is matched at most once, so
+ * the two views are each other's inverse and the rotation check removes the same pairs).  *nmatches = the reference's
+ * return value.  A feature belongs to one node, so the reference's skip-once-matched rule never crosses a node: one
+ * warp per node, the node's queries in order inside it -- bit-identical results.  2 launches + 2 memsets. */
+GFORB_API int gforb_search_by_bow(gforb_matcher* m,
+                                  const gforb_keypoint* keys1, const uint8_t* desc1, const uint8_t* valid1, int n1,
+                                  const int32_t* node_id1, const int32_t* node_start1, const int32_t* node_idx1, int n_nodes1,
+                                  const gforb_keypoint* keys2, const uint8_t* desc2, const uint8_t* valid2, int n2,
+                                  const int32_t* node_id2, const int32_t* node_start2, const int32_t* node_idx2, int n_nodes2,
+                                  int th_dist, int check_orientation, int32_t* matches12, int* nmatches);
+/* device-pointer form (every array on the device, descriptors 16-byte aligned), asynchronous on `cuda_stream` or the
+ * matcher's own; gforb_matcher_sync returns its device time */
+GFORB_API int gforb_search_by_bow_device(gforb_matcher* m,
+                                  const gforb_keypoint* dev_keys1, const uint8_t* dev_desc1, const uint8_t* dev_valid1, int n1,
+                                  const int32_t* dev_node_id1, const int32_t* dev_node_start1, const int32_t* dev_node_idx1, int n_nodes1,
+                                  const gforb_keypoint* dev_keys2, const uint8_t* dev_desc2, const uint8_t* dev_valid2, int n2,
+                                  const int32_t* dev_node_id2, const int32_t* dev_node_start2, const int32_t* dev_node_idx2, int n_nodes2,
+                                  int th_dist, int check_orientation, int32_t* dev_matches12, int32_t* dev_nmatches,
+                                  void* cuda_stream);
 /* =====================================================================================================
  * Input pre-processing in front of ORBextractor::operator()   (SURVEY.md 8f row 3), one fused kernel:
  *   16-bit -> 8-bit   cv::imread(IMREAD_GRAYSCALE) of 16-bit PNGs keeps the high byte   test/test_Stereo.cpp:100-106

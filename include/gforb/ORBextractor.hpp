@@ -188,6 +188,25 @@ public:
         if (vQueryKey) vQueryKey->assign(qkey.begin(), qkey.begin() + nq);
         return nmatches;
     }
+    // SearchByBoW (src/ORBmatcher.cc:270-404: valid2 = NULL, thDist = TH_LOW; :635-768: thDist = TH_LOW - 1).
+    // FeatVecT = DBoW2::FeatureVector or any ordered map NodeId -> vector<unsigned>.  valid1 / valid2: one byte per
+    // feature, != 0 where the MapPoint exists and is not bad (NULL = all).  vnMatches12[i] = feature of frame 2 matched
+    // to feature i of frame 1 (-1 none); for the Frame form vpMapPointMatches[vnMatches12[i]] = vpMapPointsKF[i].
+    template <class FeatVecT>
+    int SearchByBoW(const FrameView& F1, const uint8_t* valid1, const FeatVecT& featVec1, const FrameView& F2,
+                    const uint8_t* valid2, const FeatVecT& featVec2, std::vector<int>& vnMatches12, int thDist = TH_LOW) {
+        std::vector<int32_t> id1, st1, ix1, id2, st2, ix2;
+        flatten(featVec1, id1, st1, ix1);
+        flatten(featVec2, id2, st2, ix2);
+        const int n1 = (int)F1.mvKeysUn->size(), n2 = (int)F2.mvKeysUn->size();
+        vnMatches12.assign(n1, -1);
+        int nmatches = 0;
+        check(gforb_search_by_bow(handle(), F1.mvKeysUn->data(), F1.mDescriptors, valid1, n1, id1.data(), st1.data(), ix1.data(),
+                                  (int)id1.size(), F2.mvKeysUn->data(), F2.mDescriptors, valid2, n2, id2.data(), st2.data(),
+                                  ix2.data(), (int)id2.size(), thDist, mbCheckOrientation ? 1 : 0, vnMatches12.data(), &nmatches),
+              "SearchByBoW");
+        return nmatches;
+    }
     bool checkOrientation() const { return mbCheckOrientation; }
     gforb_matcher* handle() {
         if (!h_) check(gforb_matcher_create(mfNNratio, &h_), "ORBmatcher");
@@ -195,6 +214,16 @@ public:
     }
 
 protected:
+    template <class FeatVecT>
+    static void flatten(const FeatVecT& fv, std::vector<int32_t>& id, std::vector<int32_t>& start, std::vector<int32_t>& idx) {
+        start.push_back(0);
+        for (const auto& node : fv) {
+            id.push_back((int32_t)node.first);
+            for (const auto i : node.second) idx.push_back((int32_t)i);
+            start.push_back((int32_t)idx.size());
+        }
+        if (idx.empty()) idx.push_back(0);               // keep data() non-null for empty vectors
+    }
     float mfNNratio;
     bool mbCheckOrientation;
     gforb_matcher* h_ = nullptr;

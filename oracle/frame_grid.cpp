@@ -12,6 +12,7 @@
 //
 // Parity note: the reference's own tests hold no vectors for these functions (parity unpinned by the reference);
 // tests/test_oracle_grid.py checks this file against an independent pure-numpy restatement.
+#include <algorithm>
 #include <climits>
 #include <cmath>
 #include <cstring>
@@ -243,6 +244,73 @@ int orc_search_by_projection(const orc_keypoint* keys, const uint8_t* desc, cons
                 query_key[rotQuery[i][j]] = -1;
                 nmatches--;
             }
+        }
+    }
+    return nmatches;
+}
+
+
+// ORBmatcher::SearchByBoW, both forms:
+//   (KeyFrame* pKF, Frame& F, vpMapPointMatches)        /root/reference/src/ORBmatcher.cc:270-404   bestDist1 <= TH_LOW
+//   (KeyFrame* pKF1, KeyFrame* pKF2, vpMatches12)       /root/reference/src/ORBmatcher.cc:635-768   bestDist1 <  TH_LOW
+// DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned>>, Thirdparty/DBoW2/DBoW2/FeatureVector.h) arrives
+// flattened: node ids ascending, CSR offsets, feature indices in the vector's order.  valid1[i] = the query's MapPoint
+// exists and is not bad (:300-306, :679-684); valid2[j] = the same for the second key frame's candidates (:700-706;
+// NULL for the Frame form, which has no such test).  A candidate that has been matched is skipped from then on
+// (vpMapPointMatches[realIdxF] :321, vbMatched2 :701).  Both forms reduce to matches12[idx1] = idx2: the Frame form's
+// vpMapPointMatches[idx2] = pMP(idx1) is its inverse (a candidate is matched once), and its rotation histogram, which
+// holds idx2, removes the same pairs.  th_dist is inclusive: TH_LOW for the first form, TH_LOW - 1 for the second.
+int orc_search_by_bow(const orc_keypoint* k1, const uint8_t* d1, const uint8_t* valid1, int n1, const int* node_id1,
+                      const int* node_start1, const int* node_idx1, int nn1, const orc_keypoint* k2, const uint8_t* d2,
+                      const uint8_t* valid2, int n2, const int* node_id2, const int* node_start2, const int* node_idx2,
+                      int nn2, int th_dist, float nnratio, int checkOri, int* matches12) {
+    for (int i = 0; i < n1; ++i) matches12[i] = -1;
+    std::vector<uint8_t> matched2(n2 > 0 ? n2 : 1, 0);
+    std::vector<int> rotHist[kHisto];
+    const float factor = 1.0f / kHisto;
+    int nmatches = 0, it1 = 0, it2 = 0;
+    while (it1 != nn1 && it2 != nn2) {
+        if (node_id1[it1] == node_id2[it2]) {
+            for (int a = node_start1[it1]; a < node_start1[it1 + 1]; ++a) {
+                const int idx1 = node_idx1[a];
+                if (valid1 && !valid1[idx1]) continue;
+                int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+                for (int b = node_start2[it2]; b < node_start2[it2 + 1]; ++b) {
+                    const int idx2 = node_idx2[b];
+                    if (matched2[idx2] || (valid2 && !valid2[idx2])) continue;
+                    const int dist = orc_hamming256(d1 + 32 * (size_t)idx1, d2 + 32 * (size_t)idx2);
+                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx2 = idx2; }
+                    else if (dist < bestDist2) bestDist2 = dist;
+                }
+                if (bestDist1 <= th_dist) {
+                    if ((float)bestDist1 < nnratio * (float)bestDist2) {
+                        matches12[idx1] = bestIdx2;
+                        matched2[bestIdx2] = 1;
+                        if (checkOri) {
+                            float rot = k1[idx1].angle - k2[bestIdx2].angle;
+                            if (rot < 0.0) rot += 360.0f;
+                            int bin = (int)std::round(rot * factor);
+                            if (bin == kHisto) bin = 0;
+                            rotHist[bin].push_back(idx1);
+                        }
+                        nmatches++;
+                    }
+                }
+            }
+            it1++; it2++;
+        } else if (node_id1[it1] < node_id2[it2]) {
+            it1 = (int)(std::lower_bound(node_id1 + it1, node_id1 + nn1, node_id2[it2]) - node_id1);
+        } else {
+            it2 = (int)(std::lower_bound(node_id2 + it2, node_id2 + nn2, node_id1[it1]) - node_id2);
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1, sizes[kHisto];
+        for (int i = 0; i < kHisto; ++i) sizes[i] = (int)rotHist[i].size();
+        three_maxima(sizes, kHisto, ind1, ind2, ind3);
+        for (int i = 0; i < kHisto; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx1 : rotHist[i]) { matches12[idx1] = -1; nmatches--; }
         }
     }
     return nmatches;

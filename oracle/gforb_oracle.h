@@ -93,6 +93,13 @@ int   orc_search_by_projection(const orc_keypoint* keys, const uint8_t* desc, co
                                const uint8_t* qdesc, int nq, int th_dist, float nnratio, int use_ratio, int checkOri,
                                int* key_query, int* key_dist, int* query_key);
 
+/* ORBmatcher::SearchByBoW, both forms (src/ORBmatcher.cc:270-404, 635-768) over flattened DBoW2 feature vectors
+ * (node ids ascending, CSR offsets, feature indices); see oracle/frame_grid.cpp.  valid1 / valid2 may be NULL. */
+int   orc_search_by_bow(const orc_keypoint* k1, const uint8_t* d1, const uint8_t* valid1, int n1, const int* node_id1,
+                        const int* node_start1, const int* node_idx1, int nn1, const orc_keypoint* k2, const uint8_t* d2,
+                        const uint8_t* valid2, int n2, const int* node_id2, const int* node_start2, const int* node_idx2,
+                        int nn2, int th_dist, float nnratio, int checkOri, int* matches12);
+
 /* Pre-processing in front of the extractor (oracle/preprocess.cpp): [16-bit -> high byte] -> cv::remap(INTER_LINEAR,
  * BORDER_CONSTANT 0, CV_32F maps; NULL maps = none, then dw x dh must equal the source size) -> cvtColor(*2GRAY).
  * fmt: 0 gray8, 1 gray16, 2 RGB8, 3 BGR8, 4 RGBA8, 5 BGRA8. */

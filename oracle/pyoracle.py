@@ -95,6 +95,9 @@ def lib():
     L.orc_search_by_projection.argtypes = [C.c_void_p, u8p, fp, u8p, C.c_int, fp, C.c_void_p, u8p, C.c_int, C.c_int,
                                            C.c_float, C.c_int, C.c_int, ip, ip, ip]
     L.orc_search_by_projection.restype = C.c_int
+    L.orc_search_by_bow.argtypes = [C.c_void_p, u8p, u8p, C.c_int, ip, ip, ip, C.c_int, C.c_void_p, u8p, u8p, C.c_int, ip, ip, ip,
+                                    C.c_int, C.c_int, C.c_float, C.c_int, ip]
+    L.orc_search_by_bow.restype = C.c_int
     L.orc_preprocess.argtypes = [C.c_void_p, C.c_int, C.c_int, sz, C.c_int, fp, fp, C.c_int, C.c_int, u8p, sz]
     L.orc_preprocess.restype = C.c_int
     L.orc_undistort_matrix.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]; L.orc_undistort_matrix.restype = None
@@ -367,3 +370,27 @@ def search_by_projection(keys, desc, u_right, occupied, bounds, queries, qdesc, 
     nm = lib().orc_search_by_projection(_p(keys), _p(desc), _p(ur), _p(oc), n, _p(_bounds(bounds)), _p(queries), _p(qdesc), nq,
                                         int(th_dist), nnratio, int(bool(use_ratio)), int(bool(check_ori)), _p(kq), _p(kd), _p(qk))
     return nm, kq[:n], kd[:n], qk[:nq]
+
+
+def flatten_feature_vector(fv):
+    """DBoW2::FeatureVector as {node id: [feature indices]} -> (node_ids ascending, node_start CSR, node_idx)"""
+    ids = np.array(sorted(fv), np.int32)
+    start = np.zeros(len(ids) + 1, np.int32)
+    if len(ids):
+        start[1:] = np.cumsum([len(fv[i]) for i in ids])
+    idx = np.array([j for i in ids for j in fv[i]], np.int32)
+    return ids, start, idx
+
+
+def search_by_bow(k1, d1, valid1, fv1, k2, d2, valid2, fv2, th_dist=50, nnratio=0.7, check_ori=True):
+    """ORBmatcher::SearchByBoW (src/ORBmatcher.cc:270-404 with valid2=None, th_dist=TH_LOW; :635-768 with TH_LOW - 1).
+    fvX = flatten_feature_vector(...) triples.  Returns (nmatches, matches12)."""
+    k1 = np.ascontiguousarray(k1); k2 = np.ascontiguousarray(k2)
+    d1 = np.ascontiguousarray(d1, np.uint8); d2 = np.ascontiguousarray(d2, np.uint8)
+    v1 = None if valid1 is None else np.ascontiguousarray(valid1, np.uint8)
+    v2 = None if valid2 is None else np.ascontiguousarray(valid2, np.uint8)
+    i1, s1, x1 = (np.ascontiguousarray(a, np.int32) for a in fv1); i2, s2, x2 = (np.ascontiguousarray(a, np.int32) for a in fv2)
+    m12 = np.empty(max(len(k1), 1), np.int32)
+    nm = lib().orc_search_by_bow(_p(k1), _p(d1), _p(v1), len(k1), _p(i1), _p(s1), _p(x1), len(i1), _p(k2), _p(d2), _p(v2), len(k2),
+                                 _p(i2), _p(s2), _p(x2), len(i2), int(th_dist), nnratio, int(bool(check_ori)), _p(m12))
+    return nm, m12[:len(k1)]

@@ -3,6 +3,7 @@
 // wrapper can compare them with the ctypes path.  usage: shim_test left.pgm right.pgm
 #include <cstdio>
 #include <fstream>
+#include <map>
 #include <sstream>
 #include <thread>
 #include "../../include/gforb/ORBextractor.hpp"
@@ -68,6 +69,14 @@ int main(int argc, char** argv) {
                                                      matcher.checkOrientation(), kq, &kd, &qk);
         printf("proj nmatches=%d kq=%016llx kd=%016llx qk=%016llx\n", nproj, (unsigned long long)fnv(kq.data(), kq.size() * 4),
                (unsigned long long)fnv(kd.data(), kd.size() * 4), (unsigned long long)fnv(qk.data(), qk.size() * 4));
+        // SearchByBoW (src/ORBmatcher.cc:270-404) with the first descriptor byte's high nibble standing in for the node id
+        std::map<unsigned, std::vector<unsigned>> fvL, fvR;
+        for (size_t i = 0; i < kL.size(); ++i) fvL[dL[32 * i] & 0xF0u].push_back((unsigned)i);
+        for (size_t i = 0; i < kR.size(); ++i) fvR[dR[32 * i] & 0xF0u].push_back((unsigned)i);
+        gforb::ORBmatcher bow(0.7f, true);
+        std::vector<int> mb;
+        const int nbow = bow.SearchByBoW(F1, nullptr, fvL, F2, nullptr, fvR, mb);
+        printf("bow nmatches=%d mb=%016llx\n", nbow, (unsigned long long)fnv(mb.data(), mb.size() * 4));
         // an empty image is the reference's silent no-op
         std::vector<gforb_keypoint> k0; std::vector<uint8_t> d0;
         exL(nullptr, 0, 0, 0, k0, d0);

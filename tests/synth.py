@@ -134,3 +134,44 @@ def projection_case(seed, n, nq, w=752, h=480, form="map", th=1.0, flip=0.07, p_
             q["flags"] = 1 | 2
         q["flags"] &= np.where(rng.random(nq) < 0.06, ~1, ~0)                     # not in view / bad / outlier
     return keys, desc, u_right, occupied, q, qdesc
+
+
+def bow_case(seed, n1, n2, nodes=400, flip=0.06, p_valid1=0.8, p_valid2=0.85, dup=0.25):
+    """Inputs of one ORBmatcher::SearchByBoW call: two frames whose first min(n1, n2) features are re-observations
+    (noisy descriptor, rotated a little), every feature quantised into one of `nodes` vocabulary nodes (a re-observed
+    feature lands in its partner's node 9 times out of 10), near-duplicate descriptors inside nodes so that several
+    queries compete for one candidate, and node ids that exist in only one frame so the merge has to skip.
+    Returns (k1, d1, valid1, fv1, k2, d2, valid2, fv2); fvX = {node id: [feature indices in insertion order]}."""
+    rng = np.random.default_rng(7000 + seed)
+    F = np.float32
+
+    def keys(n):
+        k = np.zeros(n, KEYPOINT)
+        k["x"] = (rng.random(n) * 752).astype(F); k["y"] = (rng.random(n) * 480).astype(F)
+        k["angle"] = (rng.random(n) * 360).astype(F); k["octave"] = rng.integers(0, 8, n); k["size"], k["class_id"] = 31, -1
+        return k
+    k1, k2 = keys(n1), keys(n2)
+    d1 = rng.integers(0, 256, (n1, 32), dtype=np.uint8); d2 = rng.integers(0, 256, (n2, 32), dtype=np.uint8)
+    node1 = rng.integers(0, max(nodes, 1), n1) * 7 + 3
+    node2 = rng.integers(0, max(nodes, 1), n2) * 7 + 3 + (rng.random(n2) < 0.2)          # some ids frame 1 never has
+    m = min(n1, n2)
+    if m:
+        nd = int(m * dup)
+        src = rng.integers(0, m, nd); dst = rng.integers(0, m, nd)
+        d1[dst] = d1[src] ^ np.packbits(rng.random((nd, 256)) < 0.02, axis=1); node1[dst] = node1[src]
+        d2[:m] = d1[:m] ^ np.packbits(rng.random((m, 256)) < flip, axis=1)
+        same = rng.random(m) < 0.9
+        node2[:m] = np.where(same, node1[:m], node2[:m])
+        k2["angle"][:m] = np.mod(k1["angle"][:m] + rng.normal(10, 4, m), 360).astype(F)
+        wild = rng.random(m) < 0.12
+        k2["angle"][:m][wild] = (rng.random(int(wild.sum())) * 360).astype(F)
+    p2 = rng.permutation(n2)
+    k2, d2, node2 = k2[p2], d2[p2], node2[p2]
+
+    def featvec(node, n):
+        fv = {}
+        for i in rng.permutation(n):                  # DBoW2 pushes features in descriptor order; any order must work
+            fv.setdefault(int(node[i]), []).append(int(i))
+        return fv
+    valid1 = (rng.random(n1) < p_valid1).astype(np.uint8); valid2 = (rng.random(n2) < p_valid2).astype(np.uint8)
+    return k1, d1, valid1, featvec(node1, n1), k2, d2, valid2, featvec(node2, n2)

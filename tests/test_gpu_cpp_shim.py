@@ -62,6 +62,16 @@ def test_cpp_shim_matches_ctypes(fixtures):
                                                                  width=752, height=480)
     assert int(mp[1]) == nm > 0
     assert int(hs["kq"], 16) == _fnv(kq) and int(hs["kd"], 16) == _fnv(kd) and int(hs["qk"], 16) == _fnv(qk)
+    # SearchByBoW through the C++ mirror == the ctypes mirror
+    mbw = re.search(r"bow nmatches=(\d+) ", out.stdout)
+
+    def fv(d):
+        o = {}
+        for i, row in enumerate(d):
+            o.setdefault(int(row[0] & 0xF0), []).append(i)
+        return o
+    nb, mb = gf.ORBmatcher(0.7, True).SearchByBoW(kL, dL, None, fv(dL), kR, dR, None, fv(dR))
+    assert int(mbw[1]) == nb > 0 and int(hs["mb"], 16) == _fnv(mb)
 
 
 def test_tma_probe():
