@@ -78,6 +78,8 @@ _SIGS = {
     "gforb_batch_set_stream": (_i, [_vp, _vp]),
     "gforb_batch_capacity": (_i, [_vp, C.POINTER(_i), C.POINTER(_i)]),
     "gforb_batch_device_input": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz), C.POINTER(_sz)]),
+    "gforb_batch_device_results": (_i, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp),
+                                        C.POINTER(_i)]),
     "gforb_batch_upload": (_i, [_vp, _vp, _vp, _i]),
     "gforb_batch_run": (_i, [_vp, _i, C.POINTER(StereoParams)]),
     "gforb_batch_download": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _vp]),
@@ -531,6 +533,13 @@ class StereoBatch:
         ptr, stride, pitch = _vp(), _sz(), _sz()
         _check(_L.gforb_batch_device_input(self._h, C.byref(ptr), C.byref(stride), C.byref(pitch)))
         return ptr.value, stride.value, pitch.value
+
+    def device_results(self):
+        """device pointers of the results of the last run, in gforb_batch_download's layout:
+        dict(counts, keypoints, descriptors, u_right, depth -> int addresses, K -> key stride)"""
+        c, k, d, u, z, K = _vp(), _vp(), _vp(), _vp(), _vp(), _i(0)
+        _check(_L.gforb_batch_device_results(self._h, C.byref(c), C.byref(k), C.byref(d), C.byref(u), C.byref(z), C.byref(K)))
+        return dict(counts=c.value, keypoints=k.value, descriptors=d.value, u_right=u.value, depth=z.value, K=K.value)
 
     def upload(self, left, right):
         n = left.shape[0]

@@ -1157,6 +1157,19 @@ int gforb_batch_download(gforb_batch* b, int n, int32_t* counts, gforb_keypoint*
     return e == cudaSuccess ? GFORB_OK : cuda_fail(e, "cudaMemcpyAsync(batch download)");
 }
 
+int gforb_batch_device_results(gforb_batch* b, const int32_t** counts, const gforb_keypoint** kps, const uint8_t** desc,
+                               const float** u_right, const float** depth, int* K) {
+    if (!b || !b->eng.ready) { set_error("gforb_batch_device_results: batch not initialised"); return GFORB_ERR_ARG; }
+    Engine& E = b->eng;
+    if (counts) *counts = E.b.nkp;
+    if (kps) *kps = E.b.kps;
+    if (desc) *desc = E.b.desc;
+    if (u_right) *u_right = E.b.uright;
+    if (depth) *depth = E.b.depth;
+    if (K) *K = E.g.K;
+    return GFORB_OK;
+}
+
 int gforb_batch_sync(gforb_batch* b) {
     if (!b) return GFORB_ERR_ARG;
     return b->eng.check_errors(b->stream);

@@ -384,6 +384,13 @@ GFORB_API int gforb_batch_run(gforb_batch* b, int n_frames, const gforb_stereo_p
  * Any pointer may be NULL.  Call gforb_batch_sync before reading. */
 GFORB_API int gforb_batch_download(gforb_batch* b, int n_frames, int32_t* counts, gforb_keypoint* keypoints,
                          uint8_t* descriptors, float* u_right, float* depth);
+/* device-resident results, valid after gforb_batch_run on the batch's stream (or after gforb_batch_sync): the arrays
+ * gforb_batch_download copies, in the same layout -- counts[2F], keypoints[2F][K], descriptors[2F][K][32] (image 2f =
+ * left eye of frame f, 2f+1 = right eye), u_right / depth[F][K].  They feed the *_batch_device entries of the matcher
+ * (key stride K, counts as they are) without a trip through the host.  Any out-pointer may be NULL. */
+GFORB_API int gforb_batch_device_results(gforb_batch* b, const int32_t** dev_counts, const gforb_keypoint** dev_keypoints,
+                               const uint8_t** dev_descriptors, const float** dev_u_right, const float** dev_depth,
+                               int* max_keypoints_per_image);
 /* wait for the stream and report device-side overflow flags as GFORB_ERR_OVERFLOW */
 GFORB_API int gforb_batch_sync(gforb_batch* b);
 

@@ -151,3 +151,46 @@ def test_batched_device_form_equals_single(gf, O):
         on, okq, okd, oqk = ref[p]
         assert nm[p] == on and np.array_equal(kq[p, :n[p]], okq) and np.array_equal(qk[p, :nq[p]], oqk), p
         assert np.array_equal(kd[p, :n[p]], okd), p
+
+
+def test_device_resident_chain_from_the_batch_extractor(gf, O):
+    """extract on the device -> search on the device: the frame side (counts, keypoints, descriptors) is read where
+    gforb_batch left it (gforb_batch_device_results), every eye image as a frame, the other eye's keypoints as queries"""
+    from synth import synth_stereo
+    F, W, H = 3, 752, 480
+    frames = [synth_stereo(200 + f, W, H) for f in range(F)]
+    left = np.ascontiguousarray(np.stack([a for a, _ in frames])); right = np.ascontiguousarray(np.stack([b for _, b in frames]))
+    sb = gf.StereoBatch(W, H, F, 1000, 1.2, 8, 20, 7)
+    out = sb.alloc_outputs(F, pinned=False)
+    sb.process(left, right, out, 47.9, 0.11)
+    K = sb.K
+    dev = sb.device_results()
+    assert dev["K"] == K and all(dev[k] for k in ("counts", "keypoints", "descriptors", "u_right", "depth"))
+    P = 2 * F
+    n = out["counts"]
+    scale = (F32(1.2) ** np.arange(8)).astype(F32)
+    q = np.zeros((P, K), gf.PROJ_QUERY_DTYPE); qd = np.zeros((P, K, 32), np.uint8); nq = np.zeros(P, np.int32)
+    for i in range(P):
+        o = i ^ 1
+        ko = out["keypoints"][o, :n[o]]
+        nq[i] = n[o]
+        for name in ("x", "y", "angle"):
+            q[name][i, :n[o]] = ko[name]
+        q["r"][i, :n[o]] = F32(15.0) * scale[ko["octave"]]
+        q["min_level"][i, :n[o]] = ko["octave"] - 1; q["max_level"][i, :n[o]] = ko["octave"] + 1
+        q["flags"][i, :n[o]] = gf.PQ_ACTIVE | gf.PQ_BLOCKS
+        qd[i, :n[o]] = out["descriptors"][o, :n[o]]
+    D = gf.DeviceArray.from_host
+    dq, dqd, dnq = D(q), D(qd), D(nq)
+    dkq = gf.DeviceArray((P, K), np.int32); dkd = gf.DeviceArray((P, K), np.int32)
+    dqk = gf.DeviceArray((P, K), np.int32); dnm = gf.DeviceArray((P,), np.int32)
+    m = gf.ORBmatcher(0.9, True)
+    bounds = (0.0, float(W), 0.0, float(H))
+    m.SearchByProjectionBatchDevice(bounds, P, dev["keypoints"], dev["descriptors"], None, None, dev["counts"], K, dq, dqd, dnq, K,
+                                    100, False, True, dkq, dkd, dqk, dnm)
+    assert m.sync() > 0
+    kq, qk, nm = dkq.to_host(), dqk.to_host(), dnm.to_host()
+    for i in range(P):
+        want = O.search_by_projection(out["keypoints"][i, :n[i]], out["descriptors"][i, :n[i]], None, None, bounds,
+                                      q[i, :nq[i]], qd[i, :nq[i]], 100, 0.9, False, True)
+        assert nm[i] == want[0] > 20 and np.array_equal(kq[i, :n[i]], want[1]) and np.array_equal(qk[i, :nq[i]], want[3]), i
