@@ -79,6 +79,15 @@ struct gforb_matcher {
     bool timed = false;
     void* scratch = nullptr; size_t scratch_bytes = 0;   // per-segment partial results
     void* io = nullptr; size_t io_bytes = 0;             // staging of the host-pointer form
+    void* pin = nullptr; size_t pin_bytes = 0;           // its pinned host mirror: one H2D and one D2H copy per call
+    int reserve_pin(size_t want) {
+        if (want <= pin_bytes) return GFORB_OK;
+        if (pin) { cudaFreeHost(pin); pin = nullptr; pin_bytes = 0; }
+        cudaError_t e = cudaHostAlloc(&pin, want, cudaHostAllocDefault);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaHostAlloc(matcher)");
+        pin_bytes = want;
+        return GFORB_OK;
+    }
     int reserve(void*& p, size_t& have, size_t want) {
         if (want <= have) return GFORB_OK;
         if (p) { cudaFree(p); p = nullptr; have = 0; }
@@ -90,6 +99,7 @@ struct gforb_matcher {
     ~gforb_matcher() {
         if (scratch) cudaFree(scratch);
         if (io) cudaFree(io);
+        if (pin) cudaFreeHost(pin);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
         if (stream) cudaStreamDestroy(stream);
@@ -675,47 +685,37 @@ int gforb_search_by_projection(gforb_matcher* m, const gforb_frame_bounds* bound
         return GFORB_ERR_ARG;
     }
     *nmatches = 0;
-    const int n1 = std::max(n, 1), q1 = std::max(nq, 1);
-    const size_t kb = al16((size_t)n1 * sizeof(gforb_keypoint)), db = al16((size_t)n1 * 32), ub = al16((size_t)n1 * 4),
-                 ob = al16((size_t)n1), qb = al16((size_t)q1 * sizeof(gforb_proj_query)), qdb = al16((size_t)q1 * 32),
-                 kqb = al16((size_t)n1 * 4), qkb = al16((size_t)q1 * 4);
-    int rc = m->reserve(m->io, m->io_bytes, kb + db + ub + ob + qb + qdb + 2 * kqb + qkb + 16);
+    // inputs and outputs are packed into one block each, mirrored in pinned host memory: one H2D, one D2H per call
+    struct Seg { const void* src; size_t bytes, off; };
+    Seg in[6] = {{keys, (size_t)n * sizeof(gforb_keypoint), 0}, {desc, (size_t)n * 32, 0}, {u_right, u_right ? (size_t)n * 4 : 0, 0},
+                 {occupied, occupied ? (size_t)n : 0, 0}, {queries, (size_t)nq * sizeof(gforb_proj_query), 0}, {qdesc, (size_t)nq * 32, 0}};
+    size_t total = 0;
+    for (Seg& g : in) { g.off = total; total += al16(std::max<size_t>(g.bytes, 16)); }
+    const size_t in_bytes = total, okq = total, okd = okq + al16((size_t)std::max(n, 1) * 4), oqk = okd + al16((size_t)std::max(n, 1) * 4),
+                 onm = oqk + al16((size_t)std::max(nq, 1) * 4);
+    total = onm + 16;
+    int rc = m->reserve(m->io, m->io_bytes, total);
     if (rc) return rc;
-    uint8_t* p = static_cast<uint8_t*>(m->io);
-    gforb_keypoint* dk = reinterpret_cast<gforb_keypoint*>(p); p += kb;
-    uint8_t* dd = p; p += db;
-    float* du = reinterpret_cast<float*>(p); p += ub;
-    uint8_t* docc = p; p += ob;
-    gforb_proj_query* dq = reinterpret_cast<gforb_proj_query*>(p); p += qb;
-    uint8_t* dqd = p; p += qdb;
-    int32_t* dkq = reinterpret_cast<int32_t*>(p); p += kqb;
-    int32_t* dkd = reinterpret_cast<int32_t*>(p); p += kqb;
-    int32_t* dqk = reinterpret_cast<int32_t*>(p); p += qkb;
-    int32_t* dn = reinterpret_cast<int32_t*>(p);
+    rc = m->reserve_pin(total);
+    if (rc) return rc;
+    uint8_t* dev = static_cast<uint8_t*>(m->io);
+    uint8_t* pin = static_cast<uint8_t*>(m->pin);
+    for (const Seg& g : in)
+        if (g.bytes) std::memcpy(pin + g.off, g.src, g.bytes);
     cudaStream_t s = m->stream;
-    if (n > 0) {
-        M_CUDA(cudaMemcpyAsync(dk, keys, (size_t)n * sizeof(gforb_keypoint), cudaMemcpyHostToDevice, s));
-        M_CUDA(cudaMemcpyAsync(dd, desc, (size_t)n * 32, cudaMemcpyHostToDevice, s));
-        if (u_right) M_CUDA(cudaMemcpyAsync(du, u_right, (size_t)n * 4, cudaMemcpyHostToDevice, s));
-        if (occupied) M_CUDA(cudaMemcpyAsync(docc, occupied, (size_t)n, cudaMemcpyHostToDevice, s));
-    }
-    if (nq > 0) {
-        M_CUDA(cudaMemcpyAsync(dq, queries, (size_t)nq * sizeof(gforb_proj_query), cudaMemcpyHostToDevice, s));
-        M_CUDA(cudaMemcpyAsync(dqd, qdesc, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
-    }
-    rc = gforb_search_by_projection_batch_device(m, bounds, 1, dk, dd, u_right ? du : nullptr, occupied ? docc : nullptr, nullptr, n,
-                                                 dq, dqd, nullptr, nq, th_dist, use_ratio, check_orientation, dkq, dkd, dqk, dn,
-                                                 nullptr);
+    M_CUDA(cudaMemcpyAsync(dev, pin, in_bytes, cudaMemcpyHostToDevice, s));
+    rc = gforb_search_by_projection_batch_device(
+        m, bounds, 1, reinterpret_cast<gforb_keypoint*>(dev + in[0].off), dev + in[1].off,
+        u_right ? reinterpret_cast<float*>(dev + in[2].off) : nullptr, occupied ? dev + in[3].off : nullptr, nullptr, n,
+        reinterpret_cast<gforb_proj_query*>(dev + in[4].off), dev + in[5].off, nullptr, nq, th_dist, use_ratio, check_orientation,
+        reinterpret_cast<int32_t*>(dev + okq), reinterpret_cast<int32_t*>(dev + okd), reinterpret_cast<int32_t*>(dev + oqk),
+        reinterpret_cast<int32_t*>(dev + onm), nullptr);
     if (rc) return rc;
-    int32_t nm = 0;
-    if (n > 0) {
-        M_CUDA(cudaMemcpyAsync(key_query, dkq, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
-        M_CUDA(cudaMemcpyAsync(key_dist, dkd, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
-    }
-    if (nq > 0) M_CUDA(cudaMemcpyAsync(query_key, dqk, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));
-    M_CUDA(cudaMemcpyAsync(&nm, dn, 4, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaMemcpyAsync(pin + in_bytes, dev + in_bytes, total - in_bytes, cudaMemcpyDeviceToHost, s));
     M_CUDA(cudaStreamSynchronize(s));
-    *nmatches = nm;
+    if (n > 0) { std::memcpy(key_query, pin + okq, (size_t)n * 4); std::memcpy(key_dist, pin + okd, (size_t)n * 4); }
+    if (nq > 0) std::memcpy(query_key, pin + oqk, (size_t)nq * 4);
+    *nmatches = *reinterpret_cast<const int32_t*>(pin + onm);
     return GFORB_OK;
 }
 
@@ -764,34 +764,35 @@ int gforb_search_by_bow(gforb_matcher* m, const gforb_keypoint* k1, const uint8_
     const int e1 = nn1 > 0 ? node_start1[nn1] : 0, e2 = nn2 > 0 ? node_start2[nn2] : 0;      // feature-vector entries
     for (int i = 0; i < e1; ++i) if (node_idx1[i] < 0 || node_idx1[i] >= n1) { set_error(std::string(fn) + ": feature index out of range"); return GFORB_ERR_ARG; }
     for (int i = 0; i < e2; ++i) if (node_idx2[i] < 0 || node_idx2[i] >= n2) { set_error(std::string(fn) + ": feature index out of range"); return GFORB_ERR_ARG; }
-    struct Seg { const void* src; size_t bytes; size_t off; };
-    Seg seg[14] = {{k1, (size_t)n1 * sizeof(gforb_keypoint), 0}, {d1, (size_t)n1 * 32, 0}, {valid1, valid1 ? (size_t)n1 : 0, 0},
-                   {node_id1, (size_t)nn1 * 4, 0}, {node_start1, nn1 > 0 ? (size_t)(nn1 + 1) * 4 : 0, 0}, {node_idx1, (size_t)e1 * 4, 0},
-                   {k2, (size_t)n2 * sizeof(gforb_keypoint), 0}, {d2, (size_t)n2 * 32, 0}, {valid2, valid2 ? (size_t)n2 : 0, 0},
-                   {node_id2, (size_t)nn2 * 4, 0}, {node_start2, nn2 > 0 ? (size_t)(nn2 + 1) * 4 : 0, 0}, {node_idx2, (size_t)e2 * 4, 0},
-                   {nullptr, (size_t)std::max(n1, 1) * 4, 0}, {nullptr, 16, 0}};
+    struct Seg { const void* src; size_t bytes, off; };
+    Seg in[12] = {{k1, (size_t)n1 * sizeof(gforb_keypoint), 0}, {d1, (size_t)n1 * 32, 0}, {valid1, valid1 ? (size_t)n1 : 0, 0},
+                  {node_id1, (size_t)nn1 * 4, 0}, {node_start1, nn1 > 0 ? (size_t)(nn1 + 1) * 4 : 0, 0}, {node_idx1, (size_t)e1 * 4, 0},
+                  {k2, (size_t)n2 * sizeof(gforb_keypoint), 0}, {d2, (size_t)n2 * 32, 0}, {valid2, valid2 ? (size_t)n2 : 0, 0},
+                  {node_id2, (size_t)nn2 * 4, 0}, {node_start2, nn2 > 0 ? (size_t)(nn2 + 1) * 4 : 0, 0}, {node_idx2, (size_t)e2 * 4, 0}};
     size_t total = 0;
-    for (Seg& g : seg) { g.off = total; total += al16(g.bytes ? g.bytes : 16); }
+    for (Seg& g : in) { g.off = total; total += al16(std::max<size_t>(g.bytes, 16)); }
+    const size_t in_bytes = total, om = total, on = om + al16((size_t)std::max(n1, 1) * 4);
+    total = on + 16;
     int rc = m->reserve(m->io, m->io_bytes, total);
     if (rc) return rc;
-    uint8_t* base = static_cast<uint8_t*>(m->io);
-    cudaStream_t s = m->stream;
-    for (int i = 0; i < 12; ++i)
-        if (seg[i].bytes) M_CUDA(cudaMemcpyAsync(base + seg[i].off, seg[i].src, seg[i].bytes, cudaMemcpyHostToDevice, s));
-    auto at = [&](int i) { return base + seg[i].off; };
-    int32_t* dm = reinterpret_cast<int32_t*>(at(12));
-    int32_t* dn = reinterpret_cast<int32_t*>(at(13));
-    rc = gforb_search_by_bow_device(m, reinterpret_cast<gforb_keypoint*>(at(0)), at(1), valid1 ? at(2) : nullptr, n1,
-                                    reinterpret_cast<int32_t*>(at(3)), reinterpret_cast<int32_t*>(at(4)), reinterpret_cast<int32_t*>(at(5)), nn1,
-                                    reinterpret_cast<gforb_keypoint*>(at(6)), at(7), valid2 ? at(8) : nullptr, n2,
-                                    reinterpret_cast<int32_t*>(at(9)), reinterpret_cast<int32_t*>(at(10)), reinterpret_cast<int32_t*>(at(11)), nn2,
-                                    th_dist, check_orientation, dm, dn, nullptr);
+    rc = m->reserve_pin(total);
     if (rc) return rc;
-    int32_t nm = 0;
-    if (n1 > 0) M_CUDA(cudaMemcpyAsync(matches12, dm, (size_t)n1 * 4, cudaMemcpyDeviceToHost, s));
-    M_CUDA(cudaMemcpyAsync(&nm, dn, 4, cudaMemcpyDeviceToHost, s));
+    uint8_t* dev = static_cast<uint8_t*>(m->io);
+    uint8_t* pin = static_cast<uint8_t*>(m->pin);
+    for (const Seg& g : in)
+        if (g.bytes) std::memcpy(pin + g.off, g.src, g.bytes);
+    cudaStream_t s = m->stream;
+    M_CUDA(cudaMemcpyAsync(dev, pin, in_bytes, cudaMemcpyHostToDevice, s));
+    auto i32 = [&](int i) { return reinterpret_cast<int32_t*>(dev + in[i].off); };
+    rc = gforb_search_by_bow_device(m, reinterpret_cast<gforb_keypoint*>(dev + in[0].off), dev + in[1].off, valid1 ? dev + in[2].off : nullptr, n1,
+                                    i32(3), i32(4), i32(5), nn1, reinterpret_cast<gforb_keypoint*>(dev + in[6].off), dev + in[7].off,
+                                    valid2 ? dev + in[8].off : nullptr, n2, i32(9), i32(10), i32(11), nn2, th_dist, check_orientation,
+                                    reinterpret_cast<int32_t*>(dev + om), reinterpret_cast<int32_t*>(dev + on), nullptr);
+    if (rc) return rc;
+    M_CUDA(cudaMemcpyAsync(pin + in_bytes, dev + in_bytes, total - in_bytes, cudaMemcpyDeviceToHost, s));
     M_CUDA(cudaStreamSynchronize(s));
-    *nmatches = nm;
+    if (n1 > 0) std::memcpy(matches12, pin + om, (size_t)n1 * 4);
+    *nmatches = *reinterpret_cast<const int32_t*>(pin + on);
     return GFORB_OK;
 }
 
