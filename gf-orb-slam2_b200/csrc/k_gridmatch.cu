@@ -72,52 +72,73 @@ __device__ __forceinline__ bool area_accepts(const gforb_keypoint* __restrict__ 
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------------- grid build
-// One CTA per frame.  keys = (cell << 13 | index) bitonic-sorted in shared memory; keys outside the grid
-// (PosInGrid false, src/Frame.cc:652-653) sort to the end and are dropped.
+// One CTA per frame, a counting sort by cell: histogram of cell ids (shared atomics), exclusive scan = cell_start,
+// scatter into the cells in any order, then every entry finds its place inside its cell by counting the smaller key
+// indices there (cells hold a handful of keys, so this is a few compares; the count is what "push_back in ascending i",
+// src/Frame.cc:468-475, produces).  Keys outside the grid (PosInGrid false, :652-653) are dropped.
+// dynamic shared: cell_of[n] u16 | slot[n] u16
 __global__ void __launch_bounds__(kGridThreads)
 grid_build_kernel(const gforb_keypoint* __restrict__ keys, const int32_t* __restrict__ counts, int n_fixed, int key_stride,
                   float min_x, float min_y, float w_inv, float h_inv, int32_t* __restrict__ cell_start,
-                  int32_t* __restrict__ cell_idx, int npow2) {
-    extern __shared__ uint32_t skey[];
-    const int f = blockIdx.x;
+                  int32_t* __restrict__ cell_idx, int ncap) {
+    extern __shared__ uint16_t gsm[];
+    __shared__ int start[kGCells + 1];
+    __shared__ int fill[kGCells];
+    __shared__ int warp_tot[kGridThreads / 32];
+    uint16_t* cell_of = gsm;
+    uint16_t* slot = gsm + ncap;
+    const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int n = counts ? min(counts[f], key_stride) : n_fixed;
     const gforb_keypoint* k = keys + (size_t)f * key_stride;
-    int32_t* start = cell_start + (size_t)f * (kGCells + 1);
-    int32_t* idx = cell_idx + (size_t)f * key_stride;
-    for (int i = threadIdx.x; i < npow2; i += kGridThreads) {
-        uint32_t key = kNone;
-        if (i < n) {
-            const int px = (int)roundf(__fmul_rn(__fsub_rn(__ldg(&k[i].x), min_x), w_inv));
-            const int py = (int)roundf(__fmul_rn(__fsub_rn(__ldg(&k[i].y), min_y), h_inv));
-            if (px >= 0 && px < kGCols && py >= 0 && py < kGRows) key = ((uint32_t)(px * kGRows + py) << kPosBits) | (uint32_t)i;
-        }
-        skey[i] = key;
+    int32_t* gstart = cell_start + (size_t)f * (kGCells + 1);
+    int32_t* gidx = cell_idx + (size_t)f * key_stride;
+    for (int c = tid; c < kGCells; c += kGridThreads) fill[c] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += kGridThreads) {
+        const int px = (int)roundf(__fmul_rn(__fsub_rn(__ldg(&k[i].x), min_x), w_inv));
+        const int py = (int)roundf(__fmul_rn(__fsub_rn(__ldg(&k[i].y), min_y), h_inv));
+        const bool in = px >= 0 && px < kGCols && py >= 0 && py < kGRows;
+        cell_of[i] = in ? (uint16_t)(px * kGRows + py) : (uint16_t)0xFFFF;
+        if (in) atomicAdd(&fill[px * kGRows + py], 1);
     }
     __syncthreads();
-    for (int size = 2; size <= npow2; size <<= 1)
-        for (int stride = size >> 1; stride > 0; stride >>= 1) {
-            for (int t = threadIdx.x; t < (npow2 >> 1); t += kGridThreads) {
-                const int lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
-                const uint32_t a = skey[lo], b = skey[hi];
-                const bool up = (lo & size) == 0;
-                if ((a > b) == up) { skey[lo] = b; skey[hi] = a; }
-            }
-            __syncthreads();
-        }
-    for (int i = threadIdx.x; i < n; i += kGridThreads) {
-        const uint32_t key = skey[i];
-        if (key != kNone) idx[i] = (int32_t)(key & ((1u << kPosBits) - 1));
+    // exclusive scan of the 3,072 counts: 12 consecutive cells per thread, warp scan, scan of the 8 warp totals
+    constexpr int kPer = kGCells / kGridThreads;
+    int local = 0;
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) local += fill[tid * kPer + j];
+    int incl = local;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o) incl += v;
     }
-    // cell_start[c] = first sorted position whose cell id >= c
-    for (int c = threadIdx.x; c <= kGCells; c += kGridThreads) {
-        int lo = 0, hi = n;
-        while (lo < hi) {
-            const int mid = (lo + hi) >> 1;
-            const uint32_t key = skey[mid];
-            if (key != kNone && (int)(key >> kPosBits) < c) lo = mid + 1; else hi = mid;
-        }
-        // keys outside the grid sit at the end: clamp the terminal offset to the number of in-grid keys
-        start[c] = lo;
+    if (lane == 31) warp_tot[wid] = incl;
+    __syncthreads();
+    int base = incl - local;
+    for (int w = 0; w < wid; ++w) base += warp_tot[w];
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+        const int c = tid * kPer + j, cnt = fill[c];
+        start[c] = base;
+        gstart[c] = base;
+        fill[c] = base;                                   // running fill pointer of the cell
+        base += cnt;
+    }
+    if (tid == kGridThreads - 1) { start[kGCells] = base; gstart[kGCells] = base; }    // keys inside the grid
+    __syncthreads();
+    for (int i = tid; i < n; i += kGridThreads) {
+        const int c = cell_of[i];
+        if (c != 0xFFFF) slot[atomicAdd(&fill[c], 1)] = (uint16_t)i;
+    }
+    __syncthreads();
+    const int n_in = start[kGCells];
+    for (int p = tid; p < n_in; p += kGridThreads) {
+        const int e = slot[p], c = cell_of[e];
+        const int s0 = start[c], s1 = start[c + 1];
+        int r = 0;
+        for (int j = s0; j < s1; ++j) r += slot[j] < e;
+        gidx[s0 + r] = e;
     }
 }
 
@@ -319,8 +340,8 @@ init_search_kernel(const InitSearchArgs a, int n1cap, int n2cap) {
 //                        current claims stays valid), then the replay resumes.  What a query took stays in slot 0 of
 //                        its list; key indices, holders (atomicMax = last taker), scores, rotation bins, histogram,
 //                        three maxima and removal are written afterwards by all threads.
-// Measured (B200, 1,008 keys x 1,008 queries, last-frame form): 256 frames per launch 0.39-0.41 ms = 630-660 k frames/s;
-// one frame 81-114 us (grid 27, scan 15, resolve 44-70: the replay is one warp's dependent-instruction latency,
+// Measured (B200, 1,008 keys x 1,008 queries, last-frame form): 256 frames per launch 0.37-0.39 ms = 660-700 k frames/s;
+// one frame 67-97 us (grid 7, scan 15, resolve 44-70: the replay is one warp's dependent-instruction latency,
 // ~1,100 cycles per step, 35-52 steps) against 0.55 ms for the sequential CPU oracle.
 namespace {
 constexpr int kTopK = 8;
@@ -691,16 +712,15 @@ bow_finish_kernel(const BowSearchArgs a) {
 int gridmatch_max_keys() { return 1 << kPosBits; }
 int gridmatch_cells() { return kGCells; }
 
-static int pow2_at_least(int n) { int p = 2; while (p < n) p <<= 1; return p; }
 
 void launch_grid_build(const gforb_keypoint* keys, const int32_t* counts, int n_fixed, int key_stride, int nframes,
                        const float* bounds, int32_t* cell_start, int32_t* cell_idx, cudaStream_t s) {
     const float w_inv = 64.0f / (bounds[1] - bounds[0]), h_inv = 48.0f / (bounds[3] - bounds[2]);   // src/Frame.cc:129-130
-    const int np2 = pow2_at_least(std::max(counts ? key_stride : n_fixed, 2));
+    const int ncap = std::max(counts ? key_stride : n_fixed, 2);
     static bool attr = false;
     if (!attr) { cudaFuncSetAttribute(grid_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << kPosBits); attr = true; }
-    grid_build_kernel<<<nframes, kGridThreads, (size_t)np2 * 4, s>>>(keys, counts, n_fixed, key_stride, bounds[0], bounds[2],
-                                                                     w_inv, h_inv, cell_start, cell_idx, np2);
+    grid_build_kernel<<<nframes, kGridThreads, (size_t)ncap * 4, s>>>(keys, counts, n_fixed, key_stride, bounds[0], bounds[2],
+                                                                      w_inv, h_inv, cell_start, cell_idx, ncap);
 }
 
 void launch_area_query(const gforb_keypoint* keys, const float* bounds, const int32_t* cell_start, const int32_t* cell_idx,
