@@ -476,19 +476,28 @@ proj_resolve_kernel(const ProjSearchArgs a, int topk, int qcap) {
         return !(same_level && (float)bd > __fmul_rn(a.ratio, (float)(s2 >> kDistShift)));
     };
     // first (and, with the ratio test, second) entry of query qi's list whose position is still free;
-    // true = the list ran out before that answer was complete
+    // true = the list ran out before that answer was complete.  All entries and then all their claim flags are
+    // fetched at once (two shared-memory latencies), the selection itself runs in registers.
     auto walk = [&](int qi, uint32_t& b, uint32_t& s2) {
+        uint32_t e[kTopK];
+        bool cl[kTopK];
+#pragma unroll
+        for (int k = 0; k < kTopK; ++k) e[k] = k < topk ? lists[k * nq + qi] : kTrunc;
+#pragma unroll
+        for (int k = 0; k < kTopK; ++k) cl[k] = e[k] < kTrunc && claimed[key_pos(e[k])];
         b = kNone; s2 = kNone;
-        int k = 0;
-        for (; k < topk; ++k) {
-            const uint32_t e = lists[k * nq + qi];
-            if (e == kNone) return false;
-            if (e == kTrunc) return true;
-            if (claimed[key_pos(e)]) continue;
-            if (b == kNone) { b = e; if (!a.use_ratio) return false; }
-            else { s2 = e; return false; }
+        bool need = false, done = false;
+#pragma unroll
+        for (int k = 0; k < kTopK; ++k) {
+            if (done) continue;
+            if (e[k] == kNone) done = true;
+            else if (e[k] == kTrunc) { need = true; done = true; }
+            else if (!cl[k]) {
+                if (b == kNone) { b = e[k]; done = !a.use_ratio; }
+                else { s2 = e[k]; done = true; }
+            }
         }
-        return true;
+        return need || !done;
     };
     while (true) {
         if (wid == 0) {
