@@ -189,7 +189,8 @@ GFORB_API int gforb_search_for_initialization_batch_device(gforb_matcher* m, con
  *   SearchByProjection(Frame&, const vector<MapPoint*>&, th)                     src/ORBmatcher.cc:155-241
  *   SearchByProjection(CurrentFrame, LastFrame, th, bMono)                       src/ORBmatcher.cc:1440-1593
  *   SearchByProjection(CurrentFrame, KeyFrame*, sAlreadyFound, th, ORBdist)      src/ORBmatcher.cc:1595-1721
- * All three walk their queries IN ORDER; per query: GetFeaturesInArea(x, y, r, minLevel, maxLevel), skip keys that
+ *   SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th)  (loop closing)  src/ORBmatcher.cc:406-518
+ * All of them walk their queries IN ORDER; per query: GetFeaturesInArea(x, y, r, minLevel, maxLevel), skip keys that
  * already hold a map point, skip keys whose mvuRight is off by more than r, best (and second-best) Hamming distance,
  * threshold, [ratio test when best and second sit on the same level], assign -- and, in the two frame forms, the
  * 30-bin rotation histogram that clears the keys of all but the three largest bins.  What differs is how a query is
@@ -205,6 +206,9 @@ GFORB_API int gforb_search_for_initialization_batch_device(gforb_matcher* m, con
  *               GFORB_PQ_BLOCKS      pMP->Observations() > 0: later queries skip the key this one takes (:197-199,
  *                                    :1519-1521); always set for the key-frame form (:1662-1663)
  *               GFORB_PQ_RIGHT_GATE  apply the mvuRight test (map and last-frame forms)
+ * The loop-closing form is: levels nPredictedLevel - 1 .. nPredictedLevel (its in-loop level test :493-496 equals the
+ * level filter of GetFeaturesInArea), every query blocking, no right gate, occupied[k] = (vpMatched[k] != NULL),
+ * th_dist = TH_LOW, use_ratio = 0, check_orientation = 0.
  * Frame side: keys = mvKeysUn, desc = mDescriptors, u_right = mvuRight (NULL: monocular), occupied[k] != 0 where
  * mvpMapPoints[k] already blocks (has observations; key-frame form: is non-NULL) (NULL: none).  th_dist = TH_HIGH or
  * ORBdist, 0..255 (bestDist starts at 256 with bestIdx = -1: a larger bound indexes [-1] in the reference); use_ratio = 1 for the map form (:230, mfNNratio = the matcher's ratio).

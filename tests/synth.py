@@ -81,7 +81,7 @@ def projection_case(seed, n, nq, w=752, h=480, form="map", th=1.0, flip=0.07, p_
     """One SearchByProjection call's inputs: a frame (keys, descriptors, mvuRight, occupied keys) and nq already
     projected queries that mostly re-observe the frame's keys (moved a few pixels, noisy descriptor, predicted level
     off by one now and then), with deliberate competition: p_dup of the queries copy another query's target, p_free of
-    them do not block (Observations() == 0).  form: "map" (:155-241), "last" (:1440-1593) or "keyframe" (:1595-1721)
+    them do not block (Observations() == 0).  form: "map" (:155-241), "last" (:1440-1593), "keyframe" (:1595-1721) or "sim3" (:406-518)
     chooses how radius, level range and flags are derived, as the reference's three callers derive them."""
     rng = np.random.default_rng(9000 + seed)
     F = np.float32
@@ -128,6 +128,10 @@ def projection_case(seed, n, nq, w=752, h=480, form="map", th=1.0, flip=0.07, p_
             else:
                 q["min_level"], q["max_level"] = lvl - 1, lvl + 1
             q["flags"] = 1 | 4 | np.where(rng.random(nq) < p_free, 0, 2)
+        elif form == "sim3":                                                      # :406-518: levels lvl-1 .. lvl
+            q["r"] = F(th) * scale[lvl]
+            q["min_level"], q["max_level"] = lvl - 1, lvl
+            q["flags"] = 1 | 2
         else:
             q["r"] = F(th) * scale[lvl]
             q["min_level"], q["max_level"] = lvl - 1, lvl + 1

@@ -18,6 +18,7 @@ FORMS = {                      # form -> (th_dist, use_ratio, check_ori, nnratio
     "map": (100, True, False, 0.8),
     "last": (100, False, True, 0.9),
     "keyframe": (100, False, True, 0.9),
+    "sim3": (50, False, False, 0.9),              # :406-518, loop closing: TH_LOW, no ratio, no rotation check
 }
 
 
@@ -45,7 +46,7 @@ def _check(gf, O, case, th_dist, use_ratio, ori, ratio, no_right=False, no_occ=F
     return want
 
 
-@pytest.mark.parametrize("form", ["map", "last", "keyframe"])
+@pytest.mark.parametrize("form", ["map", "last", "keyframe", "sim3"])
 def test_forms_bit_exact(gf, O, form):
     th_dist, use_ratio, ori, ratio = FORMS[form]
     for seed, n, nq, th in [(0, 1000, 1000, 1.0), (1, 2000, 1500, 3.0), (2, 700, 2500, 15.0), (3, 1000, 300, 7.0),

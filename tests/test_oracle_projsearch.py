@@ -131,6 +131,36 @@ def py_frame_form(keys, desc, ur, occupied, q, qd, th_dist, any_assigned_blocks)
     return nmatches, kq
 
 
+def py_sim3_form(keys, desc, occupied, q, qd, th_low):
+    """src/ORBmatcher.cc:406-518 (loop closing: map points into a key frame through a Sim3).  KeyFrame::GetFeaturesInArea
+    (src/KeyFrame.cc:877-916) has no level arguments; the level test sits in the candidate loop (:493-496)."""
+    grid = py_grid(keys, BOUNDS)
+    matched = [(-1 if not o else -3) for o in occupied]           # vpMatched[idx]: -1 = NULL
+    nmatches = 0
+    for iq in range(len(q)):
+        if not q[iq]["flags"] & 1:
+            continue
+        radius = F32(q[iq]["r"])
+        lvl = int(q[iq]["max_level"])                             # nPredictedLevel
+        vind = py_area(keys, grid, q[iq]["x"], q[iq]["y"], radius, -1, -1)
+        if not vind:
+            continue
+        best, bi = 256, -1
+        for idx in vind:
+            if matched[idx] != -1:
+                continue
+            kl = int(keys[idx]["octave"])
+            if kl < lvl - 1 or kl > lvl:
+                continue
+            d = ham(qd[iq], desc[idx])
+            if d < best:
+                best, bi = d, idx
+        if best <= th_low:
+            matched[bi] = iq
+            nmatches += 1
+    return nmatches, np.array([m if m >= 0 else -1 for m in matched], np.int32)
+
+
 def check_outputs(nm, kq, kd, qk, q, keys, desc, qd):
     """the convenience outputs agree with key_query: a query that still holds a key points at it"""
     for k in np.nonzero(kq >= 0)[0]:
@@ -177,3 +207,11 @@ def test_rotation_check_off_and_no_right_coordinates():
     nm2, kq2, _, _ = O.search_by_projection(keys, desc, np.full(len(keys), -1, F32), np.zeros(len(keys), np.uint8), BOUNDS, q, qd,
                                             TH_HIGH, 0.9, False, False)
     assert nm2 == nm and np.array_equal(kq, kq2)
+
+
+def test_sim3_form():
+    for seed, n, nq, th in [(40, 900, 700, 10.0), (41, 500, 900, 4.0), (42, 1200, 300, 10.0)]:
+        keys, desc, ur, occ, q, qd = projection_case(seed, n, nq, form="sim3", th=th)
+        nm, kq, kd, qk = O.search_by_projection(keys, desc, None, occ, BOUNDS, q, qd, 50, 0.9, False, False)
+        rn, rkq = py_sim3_form(keys, desc, occ, q, qd, 50)
+        assert nm == rn > nq // 10 and np.array_equal(kq, rkq)
