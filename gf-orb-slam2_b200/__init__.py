@@ -108,6 +108,10 @@ _SIGS = {
                                  C.POINTER(_i)]),
     "gforb_search_by_bow_device": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _vp,
                                         _vp, _vp]),
+    "gforb_search_for_triangulation": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i,
+                                            _vp, _i, _i, _vp, C.POINTER(_i)]),
+    "gforb_search_for_triangulation_device": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp,
+                                                   _i, _vp, _i, _i, _vp, _vp, _vp]),
     "gforb_rectifier_create": (_i, [_vp, _vp, _i, _i, C.POINTER(_vp)]),
     "gforb_rectifier_destroy": (None, [_vp]),
     "gforb_preprocess": (_i, [_vp, _vp, _i, _i, _sz, _i, _vp, _sz]),
@@ -310,6 +314,37 @@ class ORBmatcher:
                                       opt(k2), opt(d2), opt(v2), n2, opt(i2), opt(s2) if len(i2) else None, opt(x2), len(i2),
                                       int(th_dist), int(self.mbCheckOrientation), opt(m12), C.byref(nm)))
         return nm.value, m12
+
+    def SearchForTriangulation(self, keys1, desc1, valid1, stereo1, featvec1, keys2, desc2, valid2, stereo2, featvec2, F12, ex, ey,
+                               scale_factors, level_sigma2, th_low=TH_LOW):
+        """ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:770-935).  validX: feature has no MapPoint (and is
+        stereo if bOnlyStereo); stereoX: mvuRight >= 0 (None: monocular).  Returns (nmatches, vMatches12)."""
+        k1 = np.ascontiguousarray(keys1, KP_DTYPE); k2 = np.ascontiguousarray(keys2, KP_DTYPE)
+        d1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32); d2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+        u8 = lambda a: None if a is None else np.ascontiguousarray(a, np.uint8)
+        v1, s1, v2, s2 = u8(valid1), u8(stereo1), u8(valid2), u8(stereo2)
+        i1, t1, x1 = flatten_feature_vector(featvec1); i2, t2, x2 = flatten_feature_vector(featvec2)
+        ep = Epipolar()
+        ep.F12[:] = [float(v) for v in np.asarray(F12, np.float32).reshape(9)]
+        ep.ex, ep.ey = float(ex), float(ey)
+        sf = np.asarray(scale_factors, np.float32); sg = np.asarray(level_sigma2, np.float32)
+        ep.n_levels = len(sf)
+        ep.scale_factors[:len(sf)] = [float(v) for v in sf]; ep.level_sigma2[:len(sg)] = [float(v) for v in sg]
+        n1, n2 = len(k1), len(k2)
+        m12 = np.full(n1, -1, np.int32)
+        nm = _i(0)
+        opt = lambda a: _p(a) if (a is not None and len(a)) else None
+        _check(_L.gforb_search_for_triangulation(self._h, opt(k1), opt(d1), opt(v1), opt(s1), n1, opt(i1), opt(t1) if len(i1) else None,
+                                                 opt(x1), len(i1), opt(k2), opt(d2), opt(v2), opt(s2), n2, opt(i2),
+                                                 opt(t2) if len(i2) else None, opt(x2), len(i2), C.byref(ep), int(th_low),
+                                                 int(self.mbCheckOrientation), opt(m12), C.byref(nm)))
+        return nm.value, m12
+
+
+class Epipolar(C.Structure):
+    """gforb_epipolar"""
+    _fields_ = [("F12", C.c_float * 9), ("ex", C.c_float), ("ey", C.c_float), ("n_levels", C.c_int32),
+                ("scale_factors", C.c_float * 32), ("level_sigma2", C.c_float * 32)]
 
 
 def flatten_feature_vector(fv):

@@ -719,18 +719,21 @@ int gforb_search_by_projection(gforb_matcher* m, const gforb_frame_bounds* bound
     return GFORB_OK;
 }
 
-int gforb_search_by_bow_device(gforb_matcher* m, const gforb_keypoint* k1, const uint8_t* d1, const uint8_t* valid1, int n1,
-                               const int32_t* node_id1, const int32_t* node_start1, const int32_t* node_idx1, int nn1,
-                               const gforb_keypoint* k2, const uint8_t* d2, const uint8_t* valid2, int n2,
-                               const int32_t* node_id2, const int32_t* node_start2, const int32_t* node_idx2, int nn2,
-                               int th_dist, int check_orientation, int32_t* matches12, int32_t* nmatches, void* cuda_stream) {
-    const char* fn = "gforb_search_by_bow";
+namespace {
+// SearchByBoW (ep == nullptr) and SearchForTriangulation (ep != nullptr) share the node walk; all pointers device
+int bow_device_impl(const char* fn, gforb_matcher* m, const gforb_keypoint* k1, const uint8_t* d1, const uint8_t* valid1,
+                    const uint8_t* stereo1, int n1, const int32_t* node_id1, const int32_t* node_start1, const int32_t* node_idx1,
+                    int nn1, const gforb_keypoint* k2, const uint8_t* d2, const uint8_t* valid2, const uint8_t* stereo2, int n2,
+                    const int32_t* node_id2, const int32_t* node_start2, const int32_t* node_idx2, int nn2,
+                    const gforb_epipolar* ep, int th_dist, int check_orientation, int32_t* matches12, int32_t* nmatches,
+                    void* cuda_stream) {
     if (!m || n1 < 0 || n2 < 0 || nn1 < 0 || nn2 < 0 || !nmatches || (n1 > 0 && (!k1 || !d1 || !matches12)) || (n2 > 0 && (!k2 || !d2)) ||
         (nn1 > 0 && (!node_id1 || !node_start1 || !node_idx1)) || (nn2 > 0 && (!node_id2 || !node_start2 || !node_idx2))) {
         set_error(std::string(fn) + ": bad arguments");
         return GFORB_ERR_ARG;
     }
     if (th_dist < 0 || th_dist > 255) { set_error(std::string(fn) + ": th_dist outside 0..255"); return GFORB_ERR_ARG; }
+    if (ep && (ep->n_levels < 1 || ep->n_levels > 32)) { set_error(std::string(fn) + ": n_levels outside 1..32"); return GFORB_ERR_ARG; }
     if (((uintptr_t)d1 | (uintptr_t)d2) & 15) { set_error(std::string(fn) + ": descriptor arrays must be 16-byte aligned"); return GFORB_ERR_ARG; }
     cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : m->stream;
     m->last = s;
@@ -740,6 +743,15 @@ int gforb_search_by_bow_device(gforb_matcher* m, const gforb_keypoint* k1, const
     a.k1 = k1; a.d1 = d1; a.valid1 = valid1; a.n1 = n1; a.node_id1 = node_id1; a.node_start1 = node_start1; a.node_idx1 = node_idx1; a.nn1 = nn1;
     a.k2 = k2; a.d2 = d2; a.valid2 = valid2; a.n2 = n2; a.node_id2 = node_id2; a.node_start2 = node_start2; a.node_idx2 = node_idx2; a.nn2 = nn2;
     a.th_dist = th_dist; a.ratio = m->ratio; a.check_ori = check_orientation ? 1 : 0;
+    if (ep) {
+        a.tri = 1; a.stereo1 = stereo1; a.stereo2 = stereo2;
+        std::memcpy(a.F12, ep->F12, sizeof(a.F12));
+        a.ex = ep->ex; a.ey = ep->ey;
+        for (int l = 0; l < 32; ++l) {                       // levels past n_levels repeat the last one (never indexed by valid keys)
+            const int c = std::min(l, ep->n_levels - 1);
+            a.sf[l] = ep->scale_factors[c]; a.sig2[l] = ep->level_sigma2[c];
+        }
+    }
     a.matched2 = static_cast<uint8_t*>(m->scratch); a.matches12 = matches12; a.nmatches = nmatches;
     M_CUDA(cudaEventRecord(m->ev0, s));
     launch_bow_search(a, s);
@@ -749,12 +761,12 @@ int gforb_search_by_bow_device(gforb_matcher* m, const gforb_keypoint* k1, const
     return GFORB_OK;
 }
 
-int gforb_search_by_bow(gforb_matcher* m, const gforb_keypoint* k1, const uint8_t* d1, const uint8_t* valid1, int n1,
-                        const int32_t* node_id1, const int32_t* node_start1, const int32_t* node_idx1, int nn1,
-                        const gforb_keypoint* k2, const uint8_t* d2, const uint8_t* valid2, int n2,
-                        const int32_t* node_id2, const int32_t* node_start2, const int32_t* node_idx2, int nn2,
-                        int th_dist, int check_orientation, int32_t* matches12, int* nmatches) {
-    const char* fn = "gforb_search_by_bow";
+// host-pointer form: inputs packed into one pinned block (one H2D), results into another (one D2H)
+int bow_host_impl(const char* fn, gforb_matcher* m, const gforb_keypoint* k1, const uint8_t* d1, const uint8_t* valid1,
+                  const uint8_t* stereo1, int n1, const int32_t* node_id1, const int32_t* node_start1, const int32_t* node_idx1, int nn1,
+                  const gforb_keypoint* k2, const uint8_t* d2, const uint8_t* valid2, const uint8_t* stereo2, int n2,
+                  const int32_t* node_id2, const int32_t* node_start2, const int32_t* node_idx2, int nn2, const gforb_epipolar* ep,
+                  int th_dist, int check_orientation, int32_t* matches12, int* nmatches) {
     if (!m || n1 < 0 || n2 < 0 || nn1 < 0 || nn2 < 0 || !nmatches || (n1 > 0 && (!k1 || !d1 || !matches12)) || (n2 > 0 && (!k2 || !d2)) ||
         (nn1 > 0 && (!node_id1 || !node_start1 || !node_idx1)) || (nn2 > 0 && (!node_id2 || !node_start2 || !node_idx2))) {
         set_error(std::string(fn) + ": bad arguments");
@@ -765,10 +777,11 @@ int gforb_search_by_bow(gforb_matcher* m, const gforb_keypoint* k1, const uint8_
     for (int i = 0; i < e1; ++i) if (node_idx1[i] < 0 || node_idx1[i] >= n1) { set_error(std::string(fn) + ": feature index out of range"); return GFORB_ERR_ARG; }
     for (int i = 0; i < e2; ++i) if (node_idx2[i] < 0 || node_idx2[i] >= n2) { set_error(std::string(fn) + ": feature index out of range"); return GFORB_ERR_ARG; }
     struct Seg { const void* src; size_t bytes, off; };
-    Seg in[12] = {{k1, (size_t)n1 * sizeof(gforb_keypoint), 0}, {d1, (size_t)n1 * 32, 0}, {valid1, valid1 ? (size_t)n1 : 0, 0},
+    Seg in[14] = {{k1, (size_t)n1 * sizeof(gforb_keypoint), 0}, {d1, (size_t)n1 * 32, 0}, {valid1, valid1 ? (size_t)n1 : 0, 0},
                   {node_id1, (size_t)nn1 * 4, 0}, {node_start1, nn1 > 0 ? (size_t)(nn1 + 1) * 4 : 0, 0}, {node_idx1, (size_t)e1 * 4, 0},
                   {k2, (size_t)n2 * sizeof(gforb_keypoint), 0}, {d2, (size_t)n2 * 32, 0}, {valid2, valid2 ? (size_t)n2 : 0, 0},
-                  {node_id2, (size_t)nn2 * 4, 0}, {node_start2, nn2 > 0 ? (size_t)(nn2 + 1) * 4 : 0, 0}, {node_idx2, (size_t)e2 * 4, 0}};
+                  {node_id2, (size_t)nn2 * 4, 0}, {node_start2, nn2 > 0 ? (size_t)(nn2 + 1) * 4 : 0, 0}, {node_idx2, (size_t)e2 * 4, 0},
+                  {stereo1, stereo1 ? (size_t)n1 : 0, 0}, {stereo2, stereo2 ? (size_t)n2 : 0, 0}};
     size_t total = 0;
     for (Seg& g : in) { g.off = total; total += al16(std::max<size_t>(g.bytes, 16)); }
     const size_t in_bytes = total, om = total, on = om + al16((size_t)std::max(n1, 1) * 4);
@@ -784,16 +797,60 @@ int gforb_search_by_bow(gforb_matcher* m, const gforb_keypoint* k1, const uint8_
     cudaStream_t s = m->stream;
     M_CUDA(cudaMemcpyAsync(dev, pin, in_bytes, cudaMemcpyHostToDevice, s));
     auto i32 = [&](int i) { return reinterpret_cast<int32_t*>(dev + in[i].off); };
-    rc = gforb_search_by_bow_device(m, reinterpret_cast<gforb_keypoint*>(dev + in[0].off), dev + in[1].off, valid1 ? dev + in[2].off : nullptr, n1,
-                                    i32(3), i32(4), i32(5), nn1, reinterpret_cast<gforb_keypoint*>(dev + in[6].off), dev + in[7].off,
-                                    valid2 ? dev + in[8].off : nullptr, n2, i32(9), i32(10), i32(11), nn2, th_dist, check_orientation,
-                                    reinterpret_cast<int32_t*>(dev + om), reinterpret_cast<int32_t*>(dev + on), nullptr);
+    rc = bow_device_impl(fn, m, reinterpret_cast<gforb_keypoint*>(dev + in[0].off), dev + in[1].off, valid1 ? dev + in[2].off : nullptr,
+                         stereo1 ? dev + in[12].off : nullptr, n1, i32(3), i32(4), i32(5), nn1,
+                         reinterpret_cast<gforb_keypoint*>(dev + in[6].off), dev + in[7].off, valid2 ? dev + in[8].off : nullptr,
+                         stereo2 ? dev + in[13].off : nullptr, n2, i32(9), i32(10), i32(11), nn2, ep, th_dist, check_orientation,
+                         reinterpret_cast<int32_t*>(dev + om), reinterpret_cast<int32_t*>(dev + on), nullptr);
     if (rc) return rc;
     M_CUDA(cudaMemcpyAsync(pin + in_bytes, dev + in_bytes, total - in_bytes, cudaMemcpyDeviceToHost, s));
     M_CUDA(cudaStreamSynchronize(s));
     if (n1 > 0) std::memcpy(matches12, pin + om, (size_t)n1 * 4);
     *nmatches = *reinterpret_cast<const int32_t*>(pin + on);
     return GFORB_OK;
+}
+}  // namespace
+
+int gforb_search_by_bow_device(gforb_matcher* m, const gforb_keypoint* k1, const uint8_t* d1, const uint8_t* valid1, int n1,
+                               const int32_t* node_id1, const int32_t* node_start1, const int32_t* node_idx1, int nn1,
+                               const gforb_keypoint* k2, const uint8_t* d2, const uint8_t* valid2, int n2,
+                               const int32_t* node_id2, const int32_t* node_start2, const int32_t* node_idx2, int nn2,
+                               int th_dist, int check_orientation, int32_t* matches12, int32_t* nmatches, void* cuda_stream) {
+    return bow_device_impl("gforb_search_by_bow", m, k1, d1, valid1, nullptr, n1, node_id1, node_start1, node_idx1, nn1, k2, d2, valid2,
+                           nullptr, n2, node_id2, node_start2, node_idx2, nn2, nullptr, th_dist, check_orientation, matches12, nmatches,
+                           cuda_stream);
+}
+
+int gforb_search_by_bow(gforb_matcher* m, const gforb_keypoint* k1, const uint8_t* d1, const uint8_t* valid1, int n1,
+                        const int32_t* node_id1, const int32_t* node_start1, const int32_t* node_idx1, int nn1,
+                        const gforb_keypoint* k2, const uint8_t* d2, const uint8_t* valid2, int n2,
+                        const int32_t* node_id2, const int32_t* node_start2, const int32_t* node_idx2, int nn2,
+                        int th_dist, int check_orientation, int32_t* matches12, int* nmatches) {
+    return bow_host_impl("gforb_search_by_bow", m, k1, d1, valid1, nullptr, n1, node_id1, node_start1, node_idx1, nn1, k2, d2, valid2,
+                         nullptr, n2, node_id2, node_start2, node_idx2, nn2, nullptr, th_dist, check_orientation, matches12, nmatches);
+}
+
+int gforb_search_for_triangulation_device(gforb_matcher* m, const gforb_keypoint* k1, const uint8_t* d1, const uint8_t* valid1,
+                               const uint8_t* stereo1, int n1, const int32_t* node_id1, const int32_t* node_start1,
+                               const int32_t* node_idx1, int nn1, const gforb_keypoint* k2, const uint8_t* d2, const uint8_t* valid2,
+                               const uint8_t* stereo2, int n2, const int32_t* node_id2, const int32_t* node_start2,
+                               const int32_t* node_idx2, int nn2, const gforb_epipolar* ep, int th_low, int check_orientation,
+                               int32_t* matches12, int32_t* nmatches, void* cuda_stream) {
+    if (!ep) { set_error("gforb_search_for_triangulation: null epipolar geometry"); return GFORB_ERR_ARG; }
+    return bow_device_impl("gforb_search_for_triangulation", m, k1, d1, valid1, stereo1, n1, node_id1, node_start1, node_idx1, nn1, k2, d2,
+                           valid2, stereo2, n2, node_id2, node_start2, node_idx2, nn2, ep, th_low, check_orientation, matches12, nmatches,
+                           cuda_stream);
+}
+
+int gforb_search_for_triangulation(gforb_matcher* m, const gforb_keypoint* k1, const uint8_t* d1, const uint8_t* valid1,
+                               const uint8_t* stereo1, int n1, const int32_t* node_id1, const int32_t* node_start1,
+                               const int32_t* node_idx1, int nn1, const gforb_keypoint* k2, const uint8_t* d2, const uint8_t* valid2,
+                               const uint8_t* stereo2, int n2, const int32_t* node_id2, const int32_t* node_start2,
+                               const int32_t* node_idx2, int nn2, const gforb_epipolar* ep, int th_low, int check_orientation,
+                               int32_t* matches12, int* nmatches) {
+    if (!ep) { set_error("gforb_search_for_triangulation: null epipolar geometry"); return GFORB_ERR_ARG; }
+    return bow_host_impl("gforb_search_for_triangulation", m, k1, d1, valid1, stereo1, n1, node_id1, node_start1, node_idx1, nn1, k2, d2,
+                         valid2, stereo2, n2, node_id2, node_start2, node_idx2, nn2, ep, th_low, check_orientation, matches12, nmatches);
 }
 
 // ------------------------------------------------------------------------------------------- pre-processing

@@ -179,6 +179,9 @@ struct BowSearchArgs {
     const gforb_keypoint* k2; const uint8_t* d2; const uint8_t* valid2; int n2;
     const int32_t* node_id2; const int32_t* node_start2; const int32_t* node_idx2; int nn2;
     int th_dist; float ratio; int check_ori;
+    // SearchForTriangulation only (tri != 0): stereo flags, F12 row-major, epipole, pKF2's scale factors and sigma^2
+    int tri; const uint8_t* stereo1; const uint8_t* stereo2;
+    float F12[9]; float ex, ey; float sf[32]; float sig2[32];
     uint8_t* matched2;           // [n2] scratch
     int32_t* matches12;          // [n1]
     int32_t* nmatches;           // [1]

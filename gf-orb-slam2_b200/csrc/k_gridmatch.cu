@@ -618,6 +618,11 @@ proj_resolve_kernel(const ProjSearchArgs a, int topk, int qcap) {
 // matched candidate is skipped by later queries -- never crosses a node: nodes run in parallel, one warp per node of
 // frame 1 (binary search for the same id in frame 2: the reference's merge with lower_bound visits exactly the ids
 // both maps hold), the node's queries in order inside the warp, lanes over the node's candidates.
+// kTri: ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:770-935): same walk over the common nodes, but a candidate
+// must also pass the epipole distance test (:866-872) and CheckDistEpipolarLine (:251-268), there is no ratio test, the
+// LAST of several equally near candidates wins (`dist > bestDist` skips, :859) and nothing is ever marked matched
+// (the reference never sets vbMatched2), so the queries are independent.
+template <bool kTri>
 __global__ void __launch_bounds__(256)
 bow_match_kernel(const BowSearchArgs a) {
     const int lane = threadIdx.x & 31, node = blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -639,11 +644,37 @@ bow_match_kernel(const BowSearchArgs a) {
         if (a.valid1 && !__ldg(a.valid1 + idx1)) continue;              // :300-306, :679-684
         const uint4 a0 = __ldg(d1 + 2 * (size_t)idx1), a1 = __ldg(d1 + 2 * (size_t)idx1 + 1);
         uint32_t best = kNone, second = kNone;
+        float la = 0.f, lb = 0.f, lc = 0.f;
+        bool stereo1 = false;
+        if (kTri) {                                                      // epipolar line of kp1 in image 2, :254-256
+            const float x1 = __ldg(&a.k1[idx1].x), y1 = __ldg(&a.k1[idx1].y);
+            la = __fadd_rn(__fadd_rn(__fmul_rn(x1, a.F12[0]), __fmul_rn(y1, a.F12[3])), a.F12[6]);
+            lb = __fadd_rn(__fadd_rn(__fmul_rn(x1, a.F12[1]), __fmul_rn(y1, a.F12[4])), a.F12[7]);
+            lc = __fadd_rn(__fadd_rn(__fmul_rn(x1, a.F12[2]), __fmul_rn(y1, a.F12[5])), a.F12[8]);
+            stereo1 = a.stereo1 && __ldg(a.stereo1 + idx1);
+        }
         for (int b = b0 + lane; b < b1; b += 32) {
             const int idx2 = __ldg(a.node_idx2 + b);
-            if (matched2[idx2] || (a.valid2 && !__ldg(a.valid2 + idx2))) continue;      // :321, :701-706
+            if ((!kTri && matched2[idx2]) || (a.valid2 && !__ldg(a.valid2 + idx2))) continue;     // :321, :701-706, :844-851
             const int dist = hamming256(a0, a1, __ldg(d2 + 2 * (size_t)idx2), __ldg(d2 + 2 * (size_t)idx2 + 1));
             if (dist >= 256) continue;                                                   // never below the initial 256
+            if (kTri) {
+                if (dist > a.th_dist) continue;                                          // :859
+                const float x2 = __ldg(&a.k2[idx2].x), y2 = __ldg(&a.k2[idx2].y);
+                const int o2 = __ldg(&a.k2[idx2].octave) & 31;
+                if (!stereo1 && !(a.stereo2 && __ldg(a.stereo2 + idx2))) {               // :866-872
+                    const float dx = __fsub_rn(a.ex, x2), dy = __fsub_rn(a.ey, y2);
+                    if (__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)) < __fmul_rn(100.0f, a.sf[o2])) continue;
+                }
+                const float num = __fadd_rn(__fadd_rn(__fmul_rn(la, x2), __fmul_rn(lb, y2)), lc);      // :258-267
+                const float den = __fadd_rn(__fmul_rn(la, la), __fmul_rn(lb, lb));
+                if (den == 0.0f) continue;
+                const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+                if (!((double)dsqr < __dmul_rn(3.84, (double)a.sig2[o2]))) continue;
+                const uint32_t key = ((uint32_t)dist << kListBits) | (uint32_t)(((1 << kListBits) - 1) - (b - b0));   // last of equals
+                best = min(best, key);
+                continue;
+            }
             const uint32_t key = ((uint32_t)dist << kListBits) | (uint32_t)(b - b0);
             second = min(second, max(best, key));
             best = min(best, key);
@@ -653,6 +684,11 @@ bow_match_kernel(const BowSearchArgs a) {
             const uint32_t ob = __shfl_xor_sync(0xFFFFFFFFu, best, o), os = __shfl_xor_sync(0xFFFFFFFFu, second, o);
             second = min(min(second, os), max(best, ob));
             best = min(best, ob);
+        }
+        if (kTri) {
+            if (best != kNone && lane == 0)                                              // :878-882
+                a.matches12[idx1] = __ldg(a.node_idx2 + b0 + ((1 << kListBits) - 1) - (int)(best & ((1u << kListBits) - 1)));
+            continue;
         }
         if (best != kNone && lane == 0) {
             const int bd = (int)(best >> kListBits), sd = second == kNone ? 256 : (int)(second >> kListBits);
@@ -777,7 +813,10 @@ int launch_proj_search(const ProjSearchArgs& a, const float* bounds, int nframes
 void launch_bow_search(const BowSearchArgs& a, cudaStream_t s) {
     if (a.n1 > 0) cudaMemsetAsync(a.matches12, 0xFF, (size_t)a.n1 * 4, s);
     if (a.n2 > 0) cudaMemsetAsync(a.matched2, 0, (size_t)a.n2, s);
-    if (a.nn1 > 0 && a.nn2 > 0) bow_match_kernel<<<(a.nn1 + 7) / 8, 256, 0, s>>>(a);
+    if (a.nn1 > 0 && a.nn2 > 0) {
+        if (a.tri) bow_match_kernel<true><<<(a.nn1 + 7) / 8, 256, 0, s>>>(a);
+        else bow_match_kernel<false><<<(a.nn1 + 7) / 8, 256, 0, s>>>(a);
+    }
     bow_finish_kernel<<<1, 256, 0, s>>>(a);
 }
 

@@ -269,6 +269,36 @@ GFORB_API int gforb_search_by_bow_device(gforb_matcher* m,
                                   const int32_t* dev_node_id2, const int32_t* dev_node_start2, const int32_t* dev_node_idx2, int n_nodes2,
                                   int th_dist, int check_orientation, int32_t* dev_matches12, int32_t* dev_nmatches,
                                   void* cuda_stream);
+/* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo)   src/ORBmatcher.cc:770-935, with
+ * CheckDistEpipolarLine :251-268 -- LocalMapping's search for new map points between two key frames: the node walk of
+ * SearchByBoW over features WITHOUT a MapPoint, a candidate must be within TH_LOW, away from the epipole unless one
+ * side is a stereo point (:866-872) and on kp1's epipolar line within 3.84 sigma^2 of its level; no ratio test, the LAST
+ * of equally near candidates wins (:859), nothing is ever marked matched (the reference never sets vbMatched2), so the
+ * queries are independent.  Float arithmetic is the reference's, operation for operation, un-fused.
+ *   valid1[i] != 0: pKF1 feature i has no MapPoint (and is a stereo point if bOnlyStereo)  :824-831; valid2 same  :844-851
+ *   stereo1[i] / stereo2[j] != 0: mvuRight >= 0  (NULL: monocular key frame)
+ *   ep: F12 row-major, the epipole of camera 1 in image 2 (:776-783, from the poses), pKF2's mvScaleFactors / mvLevelSigma2
+ * Out: matches12[i] = feature of key frame 2 (-1 none) = vMatches12; vMatchedPairs is its list of (i, matches12[i]). */
+typedef struct gforb_epipolar {
+    float F12[9];
+    float ex, ey;
+    int32_t n_levels;               /* 1..32 */
+    float scale_factors[32];
+    float level_sigma2[32];
+} gforb_epipolar;
+GFORB_API int gforb_search_for_triangulation(gforb_matcher* m,
+                                  const gforb_keypoint* keys1, const uint8_t* desc1, const uint8_t* valid1, const uint8_t* stereo1, int n1,
+                                  const int32_t* node_id1, const int32_t* node_start1, const int32_t* node_idx1, int n_nodes1,
+                                  const gforb_keypoint* keys2, const uint8_t* desc2, const uint8_t* valid2, const uint8_t* stereo2, int n2,
+                                  const int32_t* node_id2, const int32_t* node_start2, const int32_t* node_idx2, int n_nodes2,
+                                  const gforb_epipolar* ep, int th_low, int check_orientation, int32_t* matches12, int* nmatches);
+GFORB_API int gforb_search_for_triangulation_device(gforb_matcher* m,
+                                  const gforb_keypoint* dev_keys1, const uint8_t* dev_desc1, const uint8_t* dev_valid1, const uint8_t* dev_stereo1, int n1,
+                                  const int32_t* dev_node_id1, const int32_t* dev_node_start1, const int32_t* dev_node_idx1, int n_nodes1,
+                                  const gforb_keypoint* dev_keys2, const uint8_t* dev_desc2, const uint8_t* dev_valid2, const uint8_t* dev_stereo2, int n2,
+                                  const int32_t* dev_node_id2, const int32_t* dev_node_start2, const int32_t* dev_node_idx2, int n_nodes2,
+                                  const gforb_epipolar* ep, int th_low, int check_orientation, int32_t* dev_matches12,
+                                  int32_t* dev_nmatches, void* cuda_stream);
 /* =====================================================================================================
  * Input pre-processing in front of ORBextractor::operator()   (SURVEY.md 8f row 3), one fused kernel:
  *   16-bit -> 8-bit   cv::imread(IMREAD_GRAYSCALE) of 16-bit PNGs keeps the high byte   test/test_Stereo.cpp:100-106

@@ -12,6 +12,7 @@
 #include <cstdint>
 #include <stdexcept>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../gforb.h"
@@ -205,6 +206,28 @@ public:
                                   (int)id1.size(), F2.mvKeysUn->data(), F2.mDescriptors, valid2, n2, id2.data(), st2.data(),
                                   ix2.data(), (int)id2.size(), thDist, mbCheckOrientation ? 1 : 0, vnMatches12.data(), &nmatches),
               "SearchByBoW");
+        return nmatches;
+    }
+    // SearchForTriangulation (src/ORBmatcher.cc:770-935).  valid: feature has no MapPoint (and is stereo if bOnlyStereo);
+    // stereo: mvuRight >= 0 (NULL = monocular); ep: F12, epipole, pKF2's scale factors and level sigma^2.
+    template <class FeatVecT>
+    int SearchForTriangulation(const FrameView& KF1, const uint8_t* valid1, const uint8_t* stereo1, const FeatVecT& featVec1,
+                               const FrameView& KF2, const uint8_t* valid2, const uint8_t* stereo2, const FeatVecT& featVec2,
+                               const gforb_epipolar& ep, std::vector<std::pair<size_t, size_t> >& vMatchedPairs) {
+        std::vector<int32_t> id1, st1, ix1, id2, st2, ix2;
+        flatten(featVec1, id1, st1, ix1);
+        flatten(featVec2, id2, st2, ix2);
+        const int n1 = (int)KF1.mvKeysUn->size(), n2 = (int)KF2.mvKeysUn->size();
+        std::vector<int> m12(n1 > 0 ? n1 : 1, -1);
+        int nmatches = 0;
+        check(gforb_search_for_triangulation(handle(), KF1.mvKeysUn->data(), KF1.mDescriptors, valid1, stereo1, n1, id1.data(),
+                                             st1.data(), ix1.data(), (int)id1.size(), KF2.mvKeysUn->data(), KF2.mDescriptors, valid2,
+                                             stereo2, n2, id2.data(), st2.data(), ix2.data(), (int)id2.size(), &ep, TH_LOW,
+                                             mbCheckOrientation ? 1 : 0, m12.data(), &nmatches),
+              "SearchForTriangulation");
+        vMatchedPairs.clear();
+        for (int i = 0; i < n1; ++i)                                            // :923-931
+            if (m12[i] >= 0) vMatchedPairs.push_back(std::make_pair((size_t)i, (size_t)m12[i]));
         return nmatches;
     }
     bool checkOrientation() const { return mbCheckOrientation; }

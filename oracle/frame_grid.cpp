@@ -316,6 +316,83 @@ int orc_search_by_bow(const orc_keypoint* k1, const uint8_t* d1, const uint8_t* 
     return nmatches;
 }
 
+
+// ORBmatcher::SearchForTriangulation (/root/reference/src/ORBmatcher.cc:770-935) with CheckDistEpipolarLine (:251-268),
+// statement for statement.  valid1[i] = feature i of key frame 1 has no MapPoint (and is stereo if bOnlyStereo), :824-831;
+// valid2[j] the same for key frame 2 (:844-851; vbMatched2 is never set in the reference, so it filters nothing);
+// stereoX[i] = mvuRight[i] >= 0.  F12 row-major 3x3 float, (ex, ey) the epipole in image 2 (:776-783, computed by the
+// caller from the poses), scale_factors = pKF2->mvScaleFactors, level_sigma2 = pKF2->mvLevelSigma2.
+int orc_search_for_triangulation(const orc_keypoint* k1, const uint8_t* d1, const uint8_t* valid1, const uint8_t* stereo1,
+                                 int n1, const int* node_id1, const int* node_start1, const int* node_idx1, int nn1,
+                                 const orc_keypoint* k2, const uint8_t* d2, const uint8_t* valid2, const uint8_t* stereo2,
+                                 int n2, const int* node_id2, const int* node_start2, const int* node_idx2, int nn2,
+                                 const float* F12, float ex, float ey, const float* scale_factors,
+                                 const float* level_sigma2, int th_low, int checkOri, int* matches12) {
+    (void)n2;
+    for (int i = 0; i < n1; ++i) matches12[i] = -1;
+    std::vector<int> rotHist[kHisto];
+    const float factor = 1.0f / kHisto;
+    int nmatches = 0, it1 = 0, it2 = 0;
+    while (it1 != nn1 && it2 != nn2) {
+        if (node_id1[it1] == node_id2[it2]) {
+            for (int a = node_start1[it1]; a < node_start1[it1 + 1]; ++a) {
+                const int idx1 = node_idx1[a];
+                if (valid1 && !valid1[idx1]) continue;
+                const bool bStereo1 = stereo1 && stereo1[idx1];
+                const orc_keypoint& kp1 = k1[idx1];
+                int bestDist = th_low, bestIdx2 = -1;
+                for (int b = node_start2[it2]; b < node_start2[it2 + 1]; ++b) {
+                    const int idx2 = node_idx2[b];
+                    if (valid2 && !valid2[idx2]) continue;
+                    const bool bStereo2 = stereo2 && stereo2[idx2];
+                    const int dist = orc_hamming256(d1 + 32 * (size_t)idx1, d2 + 32 * (size_t)idx2);
+                    if (dist > th_low || dist > bestDist) continue;
+                    const orc_keypoint& kp2 = k2[idx2];
+                    if (!bStereo1 && !bStereo2) {
+                        const float distex = ex - kp2.x, distey = ey - kp2.y;
+                        if (distex * distex + distey * distey < 100 * scale_factors[kp2.octave]) continue;
+                    }
+                    // CheckDistEpipolarLine, :251-268
+                    const float la = kp1.x * F12[0] + kp1.y * F12[3] + F12[6];
+                    const float lb = kp1.x * F12[1] + kp1.y * F12[4] + F12[7];
+                    const float lc = kp1.x * F12[2] + kp1.y * F12[5] + F12[8];
+                    const float num = la * kp2.x + lb * kp2.y + lc;
+                    const float den = la * la + lb * lb;
+                    if (den == 0) continue;
+                    const float dsqr = num * num / den;
+                    if (dsqr < 3.84 * level_sigma2[kp2.octave]) { bestIdx2 = idx2; bestDist = dist; }
+                }
+                if (bestIdx2 >= 0) {
+                    matches12[idx1] = bestIdx2;
+                    nmatches++;
+                    if (checkOri) {
+                        float rot = kp1.angle - k2[bestIdx2].angle;
+                        if (rot < 0.0) rot += 360.0f;
+                        int bin = (int)std::round(rot * factor);
+                        if (bin == kHisto) bin = 0;
+                        rotHist[bin].push_back(idx1);
+                    }
+                }
+            }
+            it1++; it2++;
+        } else if (node_id1[it1] < node_id2[it2]) {
+            it1 = (int)(std::lower_bound(node_id1 + it1, node_id1 + nn1, node_id2[it2]) - node_id1);
+        } else {
+            it2 = (int)(std::lower_bound(node_id2 + it2, node_id2 + nn2, node_id1[it1]) - node_id2);
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1, sizes[kHisto];
+        for (int i = 0; i < kHisto; ++i) sizes[i] = (int)rotHist[i].size();
+        three_maxima(sizes, kHisto, ind1, ind2, ind3);
+        for (int i = 0; i < kHisto; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx1 : rotHist[i]) { matches12[idx1] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}
+
 }  // extern "C"
 
 // MapPoint::ComputeDistinctiveDescriptors (/root/reference/src/MapPoint.cc:397-458), the descriptor part: for each

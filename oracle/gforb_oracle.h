@@ -100,6 +100,15 @@ int   orc_search_by_bow(const orc_keypoint* k1, const uint8_t* d1, const uint8_t
                         const uint8_t* valid2, int n2, const int* node_id2, const int* node_start2, const int* node_idx2,
                         int nn2, int th_dist, float nnratio, int checkOri, int* matches12);
 
+/* ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:770-935, CheckDistEpipolarLine :251-268); see
+ * oracle/frame_grid.cpp.  F12: 9 floats row-major; valid / stereo arrays may be NULL. */
+int   orc_search_for_triangulation(const orc_keypoint* k1, const uint8_t* d1, const uint8_t* valid1, const uint8_t* stereo1,
+                                   int n1, const int* node_id1, const int* node_start1, const int* node_idx1, int nn1,
+                                   const orc_keypoint* k2, const uint8_t* d2, const uint8_t* valid2, const uint8_t* stereo2,
+                                   int n2, const int* node_id2, const int* node_start2, const int* node_idx2, int nn2,
+                                   const float* F12, float ex, float ey, const float* scale_factors,
+                                   const float* level_sigma2, int th_low, int checkOri, int* matches12);
+
 /* Pre-processing in front of the extractor (oracle/preprocess.cpp): [16-bit -> high byte] -> cv::remap(INTER_LINEAR,
  * BORDER_CONSTANT 0, CV_32F maps; NULL maps = none, then dw x dh must equal the source size) -> cvtColor(*2GRAY).
  * fmt: 0 gray8, 1 gray16, 2 RGB8, 3 BGR8, 4 RGBA8, 5 BGRA8. */

@@ -98,6 +98,9 @@ def lib():
     L.orc_search_by_bow.argtypes = [C.c_void_p, u8p, u8p, C.c_int, ip, ip, ip, C.c_int, C.c_void_p, u8p, u8p, C.c_int, ip, ip, ip,
                                     C.c_int, C.c_int, C.c_float, C.c_int, ip]
     L.orc_search_by_bow.restype = C.c_int
+    L.orc_search_for_triangulation.argtypes = [C.c_void_p, u8p, u8p, u8p, C.c_int, ip, ip, ip, C.c_int, C.c_void_p, u8p, u8p, u8p,
+                                               C.c_int, ip, ip, ip, C.c_int, fp, C.c_float, C.c_float, fp, fp, C.c_int, C.c_int, ip]
+    L.orc_search_for_triangulation.restype = C.c_int
     L.orc_preprocess.argtypes = [C.c_void_p, C.c_int, C.c_int, sz, C.c_int, fp, fp, C.c_int, C.c_int, u8p, sz]
     L.orc_preprocess.restype = C.c_int
     L.orc_undistort_matrix.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]; L.orc_undistort_matrix.restype = None
@@ -393,4 +396,21 @@ def search_by_bow(k1, d1, valid1, fv1, k2, d2, valid2, fv2, th_dist=50, nnratio=
     m12 = np.empty(max(len(k1), 1), np.int32)
     nm = lib().orc_search_by_bow(_p(k1), _p(d1), _p(v1), len(k1), _p(i1), _p(s1), _p(x1), len(i1), _p(k2), _p(d2), _p(v2), len(k2),
                                  _p(i2), _p(s2), _p(x2), len(i2), int(th_dist), nnratio, int(bool(check_ori)), _p(m12))
+    return nm, m12[:len(k1)]
+
+
+def search_for_triangulation(k1, d1, valid1, stereo1, fv1, k2, d2, valid2, stereo2, fv2, F12, ex, ey, scale_factors, level_sigma2,
+                             th_low=50, check_ori=True):
+    """ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:770-935).  Returns (nmatches, matches12)."""
+    k1 = np.ascontiguousarray(k1); k2 = np.ascontiguousarray(k2)
+    d1 = np.ascontiguousarray(d1, np.uint8); d2 = np.ascontiguousarray(d2, np.uint8)
+    u8 = lambda a: None if a is None else np.ascontiguousarray(a, np.uint8)
+    v1, s1, v2, s2 = u8(valid1), u8(stereo1), u8(valid2), u8(stereo2)
+    i1, t1, x1 = (np.ascontiguousarray(a, np.int32) for a in fv1); i2, t2, x2 = (np.ascontiguousarray(a, np.int32) for a in fv2)
+    F = np.ascontiguousarray(F12, np.float32).reshape(9)
+    sf = np.ascontiguousarray(scale_factors, np.float32); sg = np.ascontiguousarray(level_sigma2, np.float32)
+    m12 = np.empty(max(len(k1), 1), np.int32)
+    nm = lib().orc_search_for_triangulation(_p(k1), _p(d1), _p(v1), _p(s1), len(k1), _p(i1), _p(t1), _p(x1), len(i1), _p(k2), _p(d2),
+                                            _p(v2), _p(s2), len(k2), _p(i2), _p(t2), _p(x2), len(i2), _p(F), float(ex), float(ey),
+                                            _p(sf), _p(sg), int(th_low), int(bool(check_ori)), _p(m12))
     return nm, m12[:len(k1)]

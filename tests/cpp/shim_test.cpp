@@ -77,6 +77,13 @@ int main(int argc, char** argv) {
         std::vector<int> mb;
         const int nbow = bow.SearchByBoW(F1, nullptr, fvL, F2, nullptr, fvR, mb);
         printf("bow nmatches=%d mb=%016llx\n", nbow, (unsigned long long)fnv(mb.data(), mb.size() * 4));
+        // SearchForTriangulation (src/ORBmatcher.cc:770-935): rectified pair = sideways motion, F12 = [0 0 0; 0 0 -1; 0 1 0]
+        gforb_epipolar ep = {};
+        ep.F12[5] = -1.f; ep.F12[7] = 1.f; ep.ex = 400.f; ep.ey = 240.f; ep.n_levels = 8;
+        for (int l = 0; l < 8; ++l) { ep.scale_factors[l] = l ? ep.scale_factors[l - 1] * 1.2f : 1.f; ep.level_sigma2[l] = ep.scale_factors[l] * ep.scale_factors[l]; }
+        std::vector<std::pair<size_t, size_t> > pairs;
+        const int ntri = bow.SearchForTriangulation(F1, nullptr, nullptr, fvL, F2, nullptr, nullptr, fvR, ep, pairs);
+        printf("tri nmatches=%d pairs=%016llx\n", ntri, (unsigned long long)fnv(pairs.data(), pairs.size() * sizeof(pairs[0])));
         // an empty image is the reference's silent no-op
         std::vector<gforb_keypoint> k0; std::vector<uint8_t> d0;
         exL(nullptr, 0, 0, 0, k0, d0);

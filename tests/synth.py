@@ -140,7 +140,7 @@ def projection_case(seed, n, nq, w=752, h=480, form="map", th=1.0, flip=0.07, p_
     return keys, desc, u_right, occupied, q, qdesc
 
 
-def bow_case(seed, n1, n2, nodes=400, flip=0.06, p_valid1=0.8, p_valid2=0.85, dup=0.25):
+def bow_case(seed, n1, n2, nodes=400, flip=0.06, p_valid1=0.8, p_valid2=0.85, dup=0.25, with_partner=False):
     """Inputs of one ORBmatcher::SearchByBoW call: two frames whose first min(n1, n2) features are re-observations
     (noisy descriptor, rotated a little), every feature quantised into one of `nodes` vocabulary nodes (a re-observed
     feature lands in its partner's node 9 times out of 10), near-duplicate descriptors inside nodes so that several
@@ -171,6 +171,7 @@ def bow_case(seed, n1, n2, nodes=400, flip=0.06, p_valid1=0.8, p_valid2=0.85, du
         k2["angle"][:m][wild] = (rng.random(int(wild.sum())) * 360).astype(F)
     p2 = rng.permutation(n2)
     k2, d2, node2 = k2[p2], d2[p2], node2[p2]
+    partner = np.where(p2 < m, p2, -1)                # frame-1 feature a frame-2 feature re-observes
 
     def featvec(node, n):
         fv = {}
@@ -178,4 +179,23 @@ def bow_case(seed, n1, n2, nodes=400, flip=0.06, p_valid1=0.8, p_valid2=0.85, du
             fv.setdefault(int(node[i]), []).append(int(i))
         return fv
     valid1 = (rng.random(n1) < p_valid1).astype(np.uint8); valid2 = (rng.random(n2) < p_valid2).astype(np.uint8)
-    return k1, d1, valid1, featvec(node1, n1), k2, d2, valid2, featvec(node2, n2)
+    out = (k1, d1, valid1, featvec(node1, n1), k2, d2, valid2, featvec(node2, n2))
+    return out + (partner,) if with_partner else out
+
+
+def triangulation_case(seed, n1, n2, nodes=400):
+    """Inputs of one ORBmatcher::SearchForTriangulation call: bow_case frames where a re-observed feature sits on its
+    partner's epipolar line (sideways motion: same row, one pixel of noise, a slightly perturbed F12 so every term of
+    the line equation is exercised), stereo flags on both sides, an epipole inside the image.
+    Returns (k1, d1, valid1, stereo1, fv1, k2, d2, valid2, stereo2, fv2, F12, ex, ey, scale_factors, level_sigma2)."""
+    k1, d1, v1, fv1, k2, d2, v2, fv2, partner = bow_case(seed, n1, n2, nodes, with_partner=True)
+    rng = np.random.default_rng(8000 + seed)
+    F = np.float32
+    has = partner >= 0
+    k2["x"][has] = (k1["x"][partner[has]] - rng.random(int(has.sum())) * 40).astype(F)
+    k2["y"][has] = (k1["y"][partner[has]] + rng.normal(0, 1.0, int(has.sum()))).astype(F)
+    k2["octave"][has] = k1["octave"][partner[has]]
+    F12 = np.array([[0, 0, 0], [0, 0, -1], [0, 1, 0]], F) + rng.normal(0, 2e-5, (3, 3)).astype(F)
+    stereo1 = (rng.random(n1) < 0.5).astype(np.uint8); stereo2 = (rng.random(n2) < 0.5).astype(np.uint8)
+    sf = (F(1.2) ** np.arange(8)).astype(F)
+    return k1, d1, v1, stereo1, fv1, k2, d2, v2, stereo2, fv2, F12, F(400.0), F(240.0), sf, (sf * sf).astype(F)

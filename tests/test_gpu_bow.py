@@ -75,3 +75,23 @@ def test_on_extracted_frames(gf, O, fixtures):
         want = O.search_by_bow(k1, d1, None, O.flatten_feature_vector(fv(d1)), k2, d2, None, O.flatten_feature_vector(fv(d2)), TH_LOW, 0.7, True)
         got = gf.ORBmatcher(0.7, True).SearchByBoW(k1, d1, None, fv(d1), k2, d2, None, fv(d2), TH_LOW)
         assert got[0] == want[0] > 20 and np.array_equal(got[1], want[1])
+
+
+def test_search_for_triangulation_bit_exact(gf, O):
+    """ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:770-935): float epipolar tests, last-of-equals rule"""
+    from synth import triangulation_case
+    for seed, n1, n2, nodes, ori in [(0, 1000, 1000, 300, True), (1, 2000, 1500, 100, True), (2, 1500, 1500, 600, False),
+                                     (3, 3000, 3000, 1, True), (4, 50, 0, 10, True), (5, 6000, 8000, 1500, True)]:
+        c = triangulation_case(seed, n1, n2, nodes)
+        k1, d1, v1, st1, fv1, k2, d2, v2, st2, fv2, F12, ex, ey, sf, sig2 = c
+        want = O.search_for_triangulation(k1, d1, v1, st1, O.flatten_feature_vector(fv1), k2, d2, v2, st2, O.flatten_feature_vector(fv2),
+                                          F12, ex, ey, sf, sig2, TH_LOW, ori)
+        got = gf.ORBmatcher(0.6, ori).SearchForTriangulation(k1, d1, v1, st1, fv1, k2, d2, v2, st2, fv2, F12, ex, ey, sf, sig2, TH_LOW)
+        assert got[0] == want[0] and np.array_equal(got[1], want[1]), seed
+        if n1 >= 1000 and n2 >= 1000 and nodes > 1:
+            assert want[0] > 50
+    # monocular key frames (no stereo flags), every feature without a MapPoint
+    got = gf.ORBmatcher(0.6, True).SearchForTriangulation(k1, d1, None, None, fv1, k2, d2, None, None, fv2, F12, ex, ey, sf, sig2)
+    want = O.search_for_triangulation(k1, d1, None, None, O.flatten_feature_vector(fv1), k2, d2, None, None, O.flatten_feature_vector(fv2),
+                                      F12, ex, ey, sf, sig2, TH_LOW, True)
+    assert got[0] == want[0] > 0 and np.array_equal(got[1], want[1])

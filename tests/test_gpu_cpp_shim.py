@@ -72,6 +72,17 @@ def test_cpp_shim_matches_ctypes(fixtures):
         return o
     nb, mb = gf.ORBmatcher(0.7, True).SearchByBoW(kL, dL, None, fv(dL), kR, dR, None, fv(dR))
     assert int(mbw[1]) == nb > 0 and int(hs["mb"], 16) == _fnv(mb)
+    # SearchForTriangulation through the C++ mirror == the ctypes mirror
+    mt = re.search(r"tri nmatches=(\d+) ", out.stdout)
+    sf = np.ones(8, np.float32)
+    for l in range(1, 8):
+        sf[l] = sf[l - 1] * np.float32(1.2)
+    F12 = np.array([[0, 0, 0], [0, 0, -1], [0, 1, 0]], np.float32)
+    nt, m12t = gf.ORBmatcher(0.7, True).SearchForTriangulation(kL, dL, None, None, fv(dL), kR, dR, None, None, fv(dR), F12, 400.0, 240.0,
+                                                               sf, (sf * sf).astype(np.float32))
+    idx = np.nonzero(m12t >= 0)[0]
+    pairs = np.stack([idx, m12t[idx]], axis=1).astype(np.uint64)
+    assert int(mt[1]) == nt > 0 and int(hs["pairs"], 16) == _fnv(pairs)
 
 
 def test_tma_probe():
