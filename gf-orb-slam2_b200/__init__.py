@@ -112,6 +112,7 @@ _SIGS = {
                                             _vp, _i, _i, _vp, C.POINTER(_i)]),
     "gforb_search_for_triangulation_device": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp,
                                                    _i, _vp, _i, _i, _vp, _vp, _vp]),
+    "gforb_matcher_set_inv_level_sigma2": (_i, [_vp, _vp, _i]),
     "gforb_rectifier_create": (_i, [_vp, _vp, _i, _i, C.POINTER(_vp)]),
     "gforb_rectifier_destroy": (None, [_vp]),
     "gforb_preprocess": (_i, [_vp, _vp, _i, _i, _sz, _i, _vp, _sz]),
@@ -285,6 +286,11 @@ class ORBmatcher:
                                              C.byref(nm)))
         return nm.value, kq, kd, qk
 
+    def SetInvLevelSigma2(self, inv_level_sigma2):
+        """pKF->mvInvLevelSigma2 for the reprojection-error gate of ORBmatcher::Fuse (PQ_REPROJ_GATE queries)"""
+        t = np.ascontiguousarray(inv_level_sigma2, np.float32)
+        _check(_L.gforb_matcher_set_inv_level_sigma2(self._h, _p(t), len(t)))
+
     def SearchByProjectionBatchDevice(self, bounds, n_frames, dev_keys, dev_desc, dev_u_right, dev_occupied, dev_n, key_stride,
                                       dev_queries, dev_qdesc, dev_nq, query_stride, th_dist, use_ratio, check_ori,
                                       dev_key_query, dev_key_dist, dev_query_key, dev_nmatches, stream=None):
@@ -361,7 +367,7 @@ def flatten_feature_vector(fv):
 
 PROJ_QUERY_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("r", "<f4"), ("xr", "<f4"), ("angle", "<f4"),
                              ("min_level", "<i4"), ("max_level", "<i4"), ("flags", "<i4")])
-PQ_ACTIVE, PQ_BLOCKS, PQ_RIGHT_GATE = 1, 2, 4
+PQ_ACTIVE, PQ_BLOCKS, PQ_RIGHT_GATE, PQ_REPROJ_GATE = 1, 2, 4, 8
 
 
 FRAME_GRID_COLS, FRAME_GRID_ROWS = 64, 48      # include/Frame.h:92-93

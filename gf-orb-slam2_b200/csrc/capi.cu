@@ -80,6 +80,8 @@ struct gforb_matcher {
     void* scratch = nullptr; size_t scratch_bytes = 0;   // per-segment partial results
     void* io = nullptr; size_t io_bytes = 0;             // staging of the host-pointer form
     void* pin = nullptr; size_t pin_bytes = 0;           // its pinned host mirror: one H2D and one D2H copy per call
+    float inv_sig2[32];                                  // mvInvLevelSigma2 for the Fuse gate (gforb_matcher_set_inv_level_sigma2)
+    bool have_inv_sig2 = false;
     int reserve_pin(size_t want) {
         if (want <= pin_bytes) return GFORB_OK;
         if (pin) { cudaFreeHost(pin); pin = nullptr; pin_bytes = 0; }
@@ -625,6 +627,13 @@ int gforb_search_for_initialization(gforb_matcher* m, const gforb_frame_bounds* 
     return GFORB_OK;
 }
 
+int gforb_matcher_set_inv_level_sigma2(gforb_matcher* m, const float* inv_level_sigma2, int n_levels) {
+    if (!m || !inv_level_sigma2 || n_levels < 1 || n_levels > 32) { set_error("gforb_matcher_set_inv_level_sigma2: bad arguments"); return GFORB_ERR_ARG; }
+    for (int l = 0; l < 32; ++l) m->inv_sig2[l] = inv_level_sigma2[std::min(l, n_levels - 1)];
+    m->have_inv_sig2 = true;
+    return GFORB_OK;
+}
+
 int gforb_search_by_projection_batch_device(gforb_matcher* m, const gforb_frame_bounds* bounds, int n_frames,
                                     const gforb_keypoint* keys, const uint8_t* desc, const float* u_right,
                                     const uint8_t* occupied, const int32_t* n, int key_stride,
@@ -665,6 +674,7 @@ int gforb_search_by_projection_batch_device(gforb_matcher* m, const gforb_frame_
     a.n_fixed = key_stride; a.key_stride = ks; a.nq_fixed = q_stride; a.q_stride = qs;
     a.cell_start = ds; a.cell_idx = di;
     a.ratio = m->ratio; a.th_dist = th_dist; a.use_ratio = use_ratio ? 1 : 0; a.check_ori = check_orientation ? 1 : 0;
+    for (int l = 0; l < 32; ++l) a.inv_sig2[l] = m->have_inv_sig2 ? m->inv_sig2[l] : 1.0f;
     a.spec = reinterpret_cast<uint4*>(base + bs + bi);
     a.key_query = key_query; a.key_dist = key_dist; a.query_key = query_key; a.nmatches = nmatches;
     if (launch_proj_search(a, bb, n_frames, s)) { set_error(std::string(fn) + ": shared-memory opt-in failed"); return GFORB_ERR_CUDA; }

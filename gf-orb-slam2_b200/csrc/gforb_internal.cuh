@@ -165,6 +165,7 @@ struct ProjSearchArgs {
     float min_x, min_y, w_inv, h_inv;
     float ratio;
     int th_dist, use_ratio, check_ori;
+    float inv_sig2[32];          // mvInvLevelSigma2 for GFORB_PQ_REPROJ_GATE (ORBmatcher::Fuse)
     uint4* spec;                 // [frame][q_stride][2] scratch: each query's 8 smallest candidates, packed
     int32_t* key_query;          // [frame][key_stride]
     int32_t* key_dist;           // [frame][key_stride]

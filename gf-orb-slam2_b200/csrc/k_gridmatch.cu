@@ -356,7 +356,7 @@ template <bool kByPos>
 __device__ __forceinline__ void proj_scan(const GridView& g, const gforb_keypoint* __restrict__ keys,
                                           const uint4* __restrict__ desc, const float* __restrict__ u_right,
                                           const uint8_t* blocked, const gforb_proj_query& q, const uint4& a0,
-                                          const uint4& a1, int lane, uint32_t (&top)[kTopK]) {
+                                          const uint4& a1, int lane, const float* inv_sig2, uint32_t (&top)[kTopK]) {
     uint32_t best = kNone, second = kNone;
     int cnt = 0;
     const bool gate = (q.flags & GFORB_PQ_RIGHT_GATE) && u_right;
@@ -372,6 +372,17 @@ __device__ __forceinline__ void proj_scan(const GridView& g, const gforb_keypoin
                 if (gate) {                                                            // :201-206, :1523-1529
                     const float ur = __ldg(u_right + i);
                     if (ur > 0.0f && fabsf(__fsub_rn(q.xr, ur)) > q.r) continue;
+                }
+                if (q.flags & GFORB_PQ_REPROJ_GATE) {                                  // ORBmatcher::Fuse, :1022-1046
+                    const float ex = __fsub_rn(q.x, __ldg(&keys[i].x)), ey = __fsub_rn(q.y, __ldg(&keys[i].y));
+                    const float inv = inv_sig2[__ldg(&keys[i].octave) & 31];
+                    const float ur = u_right ? __ldg(u_right + i) : -1.0f;
+                    float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                    if (ur >= 0.0f) {
+                        const float er = __fsub_rn(q.xr, ur);
+                        e2 = __fadd_rn(e2, __fmul_rn(er, er));
+                        if ((double)__fmul_rn(e2, inv) > 7.8) continue;
+                    } else if ((double)__fmul_rn(e2, inv) > 5.99) continue;
                 }
                 const int dist = hamming256(a0, a1, __ldg(desc + 2 * (size_t)i), __ldg(desc + 2 * (size_t)i + 1));
                 if (dist >= 256) continue;                                             // never below the initial 256
@@ -421,7 +432,7 @@ proj_scan_kernel(const ProjSearchArgs a) {
         proj_scan<false>(proj_grid(a, f), a.keys + (size_t)f * a.key_stride,
                          reinterpret_cast<const uint4*>(a.desc) + 2 * (size_t)f * a.key_stride,
                          a.u_right ? a.u_right + (size_t)f * a.key_stride : nullptr,
-                         a.occupied ? a.occupied + (size_t)f * a.key_stride : nullptr, q, a0, a1, lane, top);
+                         a.occupied ? a.occupied + (size_t)f * a.key_stride : nullptr, q, a0, a1, lane, a.inv_sig2, top);
     }
     if (lane == 0) {
         uint4* o = a.spec + 2 * ((size_t)f * a.q_stride + qi);
@@ -549,7 +560,7 @@ proj_resolve_kernel(const ProjSearchArgs a, int topk, int qcap) {
                 const uint4 a0 = __ldg(qd), a1 = __ldg(qd + 1);
                 uint32_t top[kTopK];
                 proj_scan<true>(g, keys, reinterpret_cast<const uint4*>(a.desc) + 2 * (size_t)f * a.key_stride,
-                                a.u_right ? a.u_right + (size_t)f * a.key_stride : nullptr, claimed, q, a0, a1, lane, top);
+                                a.u_right ? a.u_right + (size_t)f * a.key_stride : nullptr, claimed, q, a0, a1, lane, a.inv_sig2, top);
 #pragma unroll
                 for (int k = 0; k < kTopK; ++k)
                     if (lane == 0 && k < topk) lists[k * nq + qr] = top[k];

@@ -219,7 +219,15 @@ GFORB_API int gforb_search_for_initialization_batch_device(gforb_matcher* m, con
  * best / second-best is computed in parallel against the initial state, then one warp replays the queries in order,
  * 32 at a time, re-scanning only those whose best or second-best key was taken meanwhile -- bit-identical results. */
 typedef struct gforb_proj_query { float x, y, r, xr, angle; int32_t min_level, max_level, flags; } gforb_proj_query;
-enum { GFORB_PQ_ACTIVE = 1, GFORB_PQ_BLOCKS = 2, GFORB_PQ_RIGHT_GATE = 4 };
+enum { GFORB_PQ_ACTIVE = 1, GFORB_PQ_BLOCKS = 2, GFORB_PQ_RIGHT_GATE = 4, GFORB_PQ_REPROJ_GATE = 8 };
+/* The candidate search of ORBmatcher::Fuse(KeyFrame*, const vector<MapPoint*>&, th) (src/ORBmatcher.cc:937-1087) is the
+ * same entry with GFORB_PQ_ACTIVE | GFORB_PQ_REPROJ_GATE: x, y = u, v; xr = ur; r = th * mvScaleFactors[nPredictedLevel];
+ * levels nPredictedLevel - 1 .. nPredictedLevel; a candidate passes when e2 * mvInvLevelSigma2[level] <= 7.8 (key with
+ * mvuRight >= 0: e2 over u, v and the right coordinate) or <= 5.99 (:1022-1046).  Queries neither block nor see
+ * occupancy; query_key[q] = bestIdx for bestDist <= th_dist (TH_LOW), and the MapPoint replace / add logic (:1061-1081)
+ * runs on the caller's side in query order.  The Sim3 form (:1089-1212) has no error gate: plain GFORB_PQ_ACTIVE.
+ * The table is set once per matcher (pKF->mvInvLevelSigma2, 1..32 levels). */
+GFORB_API int gforb_matcher_set_inv_level_sigma2(gforb_matcher* m, const float* inv_level_sigma2, int n_levels);
 GFORB_API int gforb_search_by_projection(gforb_matcher* m, const gforb_frame_bounds* bounds,
                                     const gforb_keypoint* keys, const uint8_t* desc, const float* u_right,
                                     const uint8_t* occupied, int n,

@@ -181,13 +181,16 @@ int orc_search_for_initialization(const orc_keypoint* k1, const uint8_t* d1, int
 //   BLOCKS      pMP->Observations() > 0: a key this query takes is skipped by later queries (:197-199, :1519-1521);
 //               the third form skips ANY assigned key (:1662-1663) = every query blocks, every assigned key occupied
 //   RIGHT_GATE  the mvuRight test (:201-206, :1523-1529); its bound equals r in both forms (r * scale; radius)
+//   REPROJ_GATE (8) the candidate search of ORBmatcher::Fuse (:937-1087; the Sim3 form :1089-1212 has no such gate): a
+//               candidate's reprojection error e2 * mvInvLevelSigma2[level] must stay below 7.8 (stereo key, with the
+//               right coordinate) or 5.99 (:1022-1046); queries neither block nor see occupancy, query_key[q] = bestIdx
 // Pose projection, PredictScale and RadiusByViewingCos stay with the caller (they read MapPoint / pose state).
 // key_query[k]: query holding key k when the call returns (-1 untouched, -2 set to NULL by the rotation check);
 // key_dist[k]: mvpMatchScore (:235); query_key[q]: key taken by query q (-1 none / removed).  Returns nmatches.
 int orc_search_by_projection(const orc_keypoint* keys, const uint8_t* desc, const float* u_right,
                              const uint8_t* occupied, int n, const float* bounds, const orc_proj_query* qs,
                              const uint8_t* qdesc, int nq, int th_dist, float nnratio, int use_ratio, int checkOri,
-                             int* key_query, int* key_dist, int* query_key) {
+                             const float* inv_level_sigma2, int* key_query, int* key_dist, int* query_key) {
     if (th_dist > 255) return -1;      // bestDist starts at 256 with bestIdx = -1 (:183, :1510): the reference would index [-1]
     Grid g;
     build_grid(g, keys, n, bounds);
@@ -208,6 +211,18 @@ int orc_search_by_projection(const orc_keypoint* keys, const uint8_t* desc, cons
             if ((q.flags & 4) && u_right && u_right[idx] > 0) {
                 const float er = std::fabs(q.xr - u_right[idx]);
                 if (er > q.r) continue;
+            }
+            if ((q.flags & 8) && inv_level_sigma2) {                  // ORBmatcher::Fuse, :1022-1046: reprojection error gate
+                const orc_keypoint& kp = keys[idx];
+                if (u_right && u_right[idx] >= 0) {
+                    const float ex = q.x - kp.x, ey = q.y - kp.y, er = q.xr - u_right[idx];
+                    const float e2 = ex * ex + ey * ey + er * er;
+                    if (e2 * inv_level_sigma2[kp.octave] > 7.8) continue;
+                } else {
+                    const float ex = q.x - kp.x, ey = q.y - kp.y;
+                    const float e2 = ex * ex + ey * ey;
+                    if (e2 * inv_level_sigma2[kp.octave] > 5.99) continue;
+                }
             }
             const int dist = orc_hamming256(qdesc + 32 * (size_t)iq, desc + 32 * (size_t)idx);
             if (dist < bestDist) {

@@ -86,12 +86,13 @@ int   orc_search_for_initialization(const orc_keypoint* k1, const uint8_t* d1, i
 
 /* ORBmatcher::SearchByProjection, the three per-frame forms (src/ORBmatcher.cc:155-241, 1440-1593, 1595-1721) as one
  * loop over already-projected queries; see oracle/frame_grid.cpp.  flags: 1 active, 2 blocks later queries,
- * 4 right-coordinate gate.  u_right / occupied may be NULL. */
+ * 4 right-coordinate gate, 8 reprojection-error gate of ORBmatcher::Fuse (needs inv_level_sigma2).  u_right /
+ * occupied / inv_level_sigma2 may be NULL. */
 typedef struct orc_proj_query { float x, y, r, xr, angle; int32_t min_level, max_level, flags; } orc_proj_query;
 int   orc_search_by_projection(const orc_keypoint* keys, const uint8_t* desc, const float* u_right,
                                const uint8_t* occupied, int n, const float* bounds, const orc_proj_query* qs,
                                const uint8_t* qdesc, int nq, int th_dist, float nnratio, int use_ratio, int checkOri,
-                               int* key_query, int* key_dist, int* query_key);
+                               const float* inv_level_sigma2, int* key_query, int* key_dist, int* query_key);
 
 /* ORBmatcher::SearchByBoW, both forms (src/ORBmatcher.cc:270-404, 635-768) over flattened DBoW2 feature vectors
  * (node ids ascending, CSR offsets, feature indices); see oracle/frame_grid.cpp.  valid1 / valid2 may be NULL. */

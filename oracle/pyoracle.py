@@ -93,7 +93,7 @@ def lib():
                                                 C.c_float, C.c_int, ip]
     L.orc_search_for_initialization.restype = C.c_int
     L.orc_search_by_projection.argtypes = [C.c_void_p, u8p, fp, u8p, C.c_int, fp, C.c_void_p, u8p, C.c_int, C.c_int,
-                                           C.c_float, C.c_int, C.c_int, ip, ip, ip]
+                                           C.c_float, C.c_int, C.c_int, fp, ip, ip, ip]
     L.orc_search_by_projection.restype = C.c_int
     L.orc_search_by_bow.argtypes = [C.c_void_p, u8p, u8p, C.c_int, ip, ip, ip, C.c_int, C.c_void_p, u8p, u8p, C.c_int, ip, ip, ip,
                                     C.c_int, C.c_int, C.c_float, C.c_int, ip]
@@ -357,11 +357,11 @@ def distinctive_descriptors(desc, set_start):
 
 PROJ_QUERY = np.dtype([("x", "<f4"), ("y", "<f4"), ("r", "<f4"), ("xr", "<f4"), ("angle", "<f4"),
                        ("min_level", "<i4"), ("max_level", "<i4"), ("flags", "<i4")])
-PQ_ACTIVE, PQ_BLOCKS, PQ_RIGHT_GATE = 1, 2, 4
+PQ_ACTIVE, PQ_BLOCKS, PQ_RIGHT_GATE, PQ_REPROJ_GATE = 1, 2, 4, 8
 
 
 def search_by_projection(keys, desc, u_right, occupied, bounds, queries, qdesc, th_dist=100, nnratio=0.8, use_ratio=True,
-                         check_ori=False):
+                         check_ori=False, inv_level_sigma2=None):
     """ORBmatcher::SearchByProjection over already-projected queries (src/ORBmatcher.cc:155-241, 1440-1593, 1595-1721;
     oracle/frame_grid.cpp).  Returns (nmatches, key_query, key_dist, query_key)."""
     keys = np.ascontiguousarray(keys); desc = np.ascontiguousarray(desc, np.uint8)
@@ -370,8 +370,10 @@ def search_by_projection(keys, desc, u_right, occupied, bounds, queries, qdesc, 
     oc = None if occupied is None else np.ascontiguousarray(occupied, np.uint8)
     n, nq = len(keys), len(queries)
     kq = np.empty(max(n, 1), np.int32); kd = np.empty(max(n, 1), np.int32); qk = np.empty(max(nq, 1), np.int32)
+    inv = None if inv_level_sigma2 is None else np.ascontiguousarray(inv_level_sigma2, np.float32)
     nm = lib().orc_search_by_projection(_p(keys), _p(desc), _p(ur), _p(oc), n, _p(_bounds(bounds)), _p(queries), _p(qdesc), nq,
-                                        int(th_dist), nnratio, int(bool(use_ratio)), int(bool(check_ori)), _p(kq), _p(kd), _p(qk))
+                                        int(th_dist), nnratio, int(bool(use_ratio)), int(bool(check_ori)), _p(inv), _p(kq), _p(kd),
+                                        _p(qk))
     return nm, kq[:n], kd[:n], qk[:nq]
 
 

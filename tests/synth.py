@@ -128,6 +128,10 @@ def projection_case(seed, n, nq, w=752, h=480, form="map", th=1.0, flip=0.07, p_
             else:
                 q["min_level"], q["max_level"] = lvl - 1, lvl + 1
             q["flags"] = 1 | 4 | np.where(rng.random(nq) < p_free, 0, 2)
+        elif form == "fuse":                                                      # :937-1087: error gate, nothing blocks
+            q["r"] = F(th) * scale[lvl]
+            q["min_level"], q["max_level"] = lvl - 1, lvl
+            q["flags"] = 1 | 8
         elif form == "sim3":                                                      # :406-518: levels lvl-1 .. lvl
             q["r"] = F(th) * scale[lvl]
             q["min_level"], q["max_level"] = lvl - 1, lvl

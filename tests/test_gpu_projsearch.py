@@ -195,3 +195,19 @@ def test_device_resident_chain_from_the_batch_extractor(gf, O):
         want = O.search_by_projection(out["keypoints"][i, :n[i]], out["descriptors"][i, :n[i]], None, None, bounds,
                                       q[i, :nq[i]], qd[i, :nq[i]], 100, 0.9, False, True)
         assert nm[i] == want[0] > 20 and np.array_equal(kq[i, :n[i]], want[1]) and np.array_equal(qk[i, :nq[i]], want[3]), i
+
+
+def test_fuse_candidate_search(gf, O):
+    """ORBmatcher::Fuse (src/ORBmatcher.cc:937-1087): reprojection-error gate in the reference's float arithmetic, queries
+    neither block nor see occupancy"""
+    sf = (F32(1.2) ** np.arange(8)).astype(F32)
+    inv = (F32(1) / (sf * sf)).astype(F32)
+    for seed, n, nq, th in [(60, 1000, 1000, 3.0), (61, 2000, 1500, 3.0), (62, 700, 2500, 2.5), (63, 8192, 8192, 3.0)]:
+        keys, desc, ur, occ, q, qd = projection_case(seed, n, nq, form="fuse", th=th)
+        want = O.search_by_projection(keys, desc, ur, None, BOUNDS, q, qd, 50, 0.9, False, False, inv)
+        m = gf.ORBmatcher(0.9, False)
+        m.SetInvLevelSigma2(inv)
+        got = m.SearchByProjection(keys, desc, q, qd, ur, None, 50, False, False, bounds=BOUNDS)
+        assert got[0] == want[0] > nq // 10
+        for g, w in zip(got[1:], want[1:]):
+            assert np.array_equal(g, w)

@@ -215,3 +215,45 @@ def test_sim3_form():
         nm, kq, kd, qk = O.search_by_projection(keys, desc, None, occ, BOUNDS, q, qd, 50, 0.9, False, False)
         rn, rkq = py_sim3_form(keys, desc, occ, q, qd, 50)
         assert nm == rn > nq // 10 and np.array_equal(kq, rkq)
+
+
+def py_fuse_form(keys, desc, ur, q, qd, inv_sig2, th_low):
+    """src/ORBmatcher.cc:937-1087, the candidate search: bestIdx per map point (-1: none within TH_LOW)"""
+    grid = py_grid(keys, BOUNDS)
+    out = []
+    for iq in range(len(q)):
+        if not q[iq]["flags"] & 1:
+            out.append(-1)
+            continue
+        u, v, urq = F32(q[iq]["x"]), F32(q[iq]["y"]), F32(q[iq]["xr"])
+        lvl = int(q[iq]["max_level"])
+        best, bi = 256, -1
+        for idx in py_area(keys, grid, u, v, F32(q[iq]["r"]), -1, -1):
+            kl = int(keys[idx]["octave"])
+            if kl < lvl - 1 or kl > lvl:
+                continue
+            ex, ey = F32(u - keys[idx]["x"]), F32(v - keys[idx]["y"])
+            if ur[idx] >= 0:
+                er = F32(urq - ur[idx])
+                e2 = F32(F32(F32(ex * ex) + F32(ey * ey)) + F32(er * er))
+                if float(F32(e2 * inv_sig2[kl])) > 7.8:
+                    continue
+            else:
+                e2 = F32(F32(ex * ex) + F32(ey * ey))
+                if float(F32(e2 * inv_sig2[kl])) > 5.99:
+                    continue
+            d = ham(qd[iq], desc[idx])
+            if d < best:
+                best, bi = d, idx
+        out.append(bi if best <= th_low else -1)
+    return np.array(out, np.int32)
+
+
+def test_fuse_form():
+    sf = (F32(1.2) ** np.arange(8)).astype(F32)
+    inv = (F32(1) / (sf * sf)).astype(F32)
+    for seed, n, nq, th in [(60, 900, 700, 3.0), (61, 500, 900, 3.0), (62, 1200, 300, 2.5)]:
+        keys, desc, ur, occ, q, qd = projection_case(seed, n, nq, form="fuse", th=th)
+        nm, kq, kd, qk = O.search_by_projection(keys, desc, ur, None, BOUNDS, q, qd, 50, 0.9, False, False, inv)
+        want = py_fuse_form(keys, desc, ur, q, qd, inv, 50)
+        assert np.array_equal(qk, want) and nm == int((want >= 0).sum()) > nq // 10
