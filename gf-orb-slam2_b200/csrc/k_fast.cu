@@ -30,6 +30,16 @@
 //      {v-q+256, q-v+256} as s16x2, then a 3-input packed min/max network (VIMNMX3) serves both polarities;
 //  (4) NMS walks the same list on a zero-initialised score map.
 // Algorithmic bytes = level pixels read once + 4 B per survivor.
+//
+// Open (evaluated, not built; neither changes results):
+//  * band tiles: one warp takes a vertical band of cells and keeps the three rows above / below in registers across
+//    the cell boundary, so the +-3-row words of pass (1) and the ring rows of pass (3) are loaded once per band instead
+//    of once per cell; estimated -15 % of this kernel (-5 % of the step), at the price of per-band instead of per-cell
+//    threshold retry bookkeeping.
+//  * the minTh trip's prefilter flags could be produced during the iniTh trip (same loads, second SWAR compare) and
+//    kept as a row bitmap for the cells that turn out empty: removes the second pass (1) for ~half of the cells,
+//    adds ~28 % to pass (1) of every cell: net -6 % of this kernel; needs 512 B more shared memory per warp, which
+//    costs one resident CTA per SM.
 #include "gforb_internal.cuh"
 #include "tma.cuh"
 
