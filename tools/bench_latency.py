@@ -51,9 +51,33 @@ def timeit(fn):
     return {"median_ms": round(float(np.median(ts)), 4), "p95_ms": round(float(np.percentile(ts, 95)), 4)}
 
 
+# (d) a tracking thread's per-frame front-end: the fused one-frame entry, then TrackWithMotionModel's
+# SearchByProjection(CurrentFrame, LastFrame, th = 15) with the previous frame's left keypoints as the projected points
+matcher = gf.ORBmatcher(0.9, True)
+scale = (np.float32(bench.SCALE) ** np.arange(bench.NLEVELS)).astype(np.float32)
+last = {}
+
+
+def frame_track(i):
+    frame_batch1(i)
+    n = int(out["counts"][0])
+    keys, desc, ur = out["keypoints"][0, :n], out["descriptors"][0, :n], out["u_right"][0, :n]
+    if last:
+        matcher.SearchByProjection(keys, desc, last["q"], last["qd"], ur, None, 100, False, True, width=bench.W, height=bench.H)
+    q = np.zeros(n, gf.PROJ_QUERY_DTYPE)                      # the caller's projection step (kept outside the library)
+    o = np.clip(keys["octave"], 0, bench.NLEVELS - 1)
+    q["x"], q["y"], q["angle"] = keys["x"], keys["y"], keys["angle"]
+    q["r"] = np.float32(15.0) * scale[o]
+    q["min_level"], q["max_level"] = o - 1, o + 1
+    q["xr"] = ur
+    q["flags"] = gf.PQ_ACTIVE | gf.PQ_BLOCKS | gf.PQ_RIGHT_GATE
+    last["q"], last["qd"] = q, desc.copy()
+
+
 res = {"what": "one 752x480 stereo frame, 1000 kp, host in / host out", "frames": N,
        "two_handles_two_threads": timeit(frame_threads), "two_handles_serial": timeit(frame_serial),
-       "batch_of_one": timeit(frame_batch1)}
+       "batch_of_one": timeit(frame_batch1),
+       "batch_of_one_plus_search_by_projection": timeit(frame_track)}
 imgs = np.empty((16,) + left.shape[1:], np.uint8); imgs[0::2] = left[:8]; imgs[1::2] = right[:8]      # frame f = images 2f, 2f+1
 secs = O.bench_stereo(imgs, 32, 2, shape=1)
 res["cpu_oracle_reference_shaped_ms"] = round((secs[0] if isinstance(secs, tuple) else secs) / 32 * 1e3, 3)
