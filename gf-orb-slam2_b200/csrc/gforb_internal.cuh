@@ -215,6 +215,18 @@ size_t octree_smem_bytes(const Geom& g);
 int fast_configure(const Geom& g);     // opt in to the FAST kernel's dynamic smem; returns cudaError_t as int
 int octree_configure(const Geom& g);   // opt in to large dynamic smem; returns cudaError_t as int
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is per device: remember the opted-in size per (kernel, device), not
+// per process (one process may drive several devices).  `have` is a zero-initialised static of the call site.
+template <class K>
+inline int opt_in_smem(K kernel, size_t smem, size_t (&have)[64]) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    if (smem <= have[dev]) return 0;
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
+    have[dev] = smem;
+    return 0;
+}
+
 void upload_constants();   // pattern + umax to __constant__ (once per process/device)
 
 }  // namespace gforb

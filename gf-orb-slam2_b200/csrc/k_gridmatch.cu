@@ -773,8 +773,8 @@ void launch_grid_build(const gforb_keypoint* keys, const int32_t* counts, int n_
                        const float* bounds, int32_t* cell_start, int32_t* cell_idx, cudaStream_t s) {
     const float w_inv = 64.0f / (bounds[1] - bounds[0]), h_inv = 48.0f / (bounds[3] - bounds[2]);   // src/Frame.cc:129-130
     const int ncap = std::max(counts ? key_stride : n_fixed, 2);
-    static bool attr = false;
-    if (!attr) { cudaFuncSetAttribute(grid_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << kPosBits); attr = true; }
+    static size_t have[64] = {};
+    opt_in_smem(grid_build_kernel, (size_t)4 << kPosBits, have);
     grid_build_kernel<<<nframes, kGridThreads, (size_t)ncap * 4, s>>>(keys, counts, n_fixed, key_stride, bounds[0], bounds[2],
                                                                       w_inv, h_inv, cell_start, cell_idx, ncap);
 }
@@ -795,11 +795,8 @@ int launch_init_search(const InitSearchArgs& a, const float* bounds, int npairs,
     b.w_inv = 64.0f / (bounds[1] - bounds[0]); b.h_inv = 48.0f / (bounds[3] - bounds[2]);
     const int n1cap = std::max(a.n1 ? a.stride1 : a.n1_fixed, 1), n2cap = std::max(a.n2 ? a.stride2 : a.n2_fixed, 1);
     const size_t smem = init_search_smem(n1cap, n2cap);
-    static size_t attr_have = 0;
-    if (smem > attr_have) {
-        if (cudaFuncSetAttribute(init_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
-        attr_have = smem;
-    }
+    static size_t have[64] = {};
+    if (opt_in_smem(init_search_kernel, smem, have)) return -1;
     init_search_kernel<<<npairs, kSearchThreads, smem, s>>>(b, n1cap, n2cap);
     return 0;
 }
@@ -812,11 +809,8 @@ int launch_proj_search(const ProjSearchArgs& a, const float* bounds, int nframes
     if (qcap > 0) proj_scan_kernel<<<dim3((qcap + 7) / 8, nframes), 256, 0, s>>>(b);
     const int topk = qcap <= 4096 ? kTopK : kTopK / 2;           // lists stay within 128 KB of shared memory
     const size_t smem = (size_t)std::max(qcap, 1) * topk * 4 + (4u << kPosBits);
-    static size_t attr_have = 0;                                 // static shared memory takes 24 KB of the un-opted 48 KB
-    if (smem > attr_have) {
-        if (cudaFuncSetAttribute(proj_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
-        attr_have = smem;
-    }
+    static size_t have[64] = {};                                 // static shared memory takes 24 KB of the un-opted 48 KB
+    if (opt_in_smem(proj_resolve_kernel, smem, have)) return -1;
     proj_resolve_kernel<<<nframes, kSearchThreads, smem, s>>>(b, topk, std::max(qcap, 1));
     return 0;
 }

@@ -149,11 +149,8 @@ int launch_distinctive(const uint8_t* desc, const int32_t* set_start, int npoint
                        int32_t* best_median, cudaStream_t s) {
     if (npoints <= 0) return 0;
     const size_t smem = (size_t)kDdWarps * std::max(max_n, 1) * 32;
-    static size_t have = 48 * 1024;
-    if (smem > have) {
-        if (cudaFuncSetAttribute(distinctive_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
-        have = smem;
-    }
+    static size_t have[64] = {};
+    if (smem > 48 * 1024 && opt_in_smem(distinctive_kernel, smem, have)) return -1;
     distinctive_kernel<<<(npoints + kDdWarps - 1) / kDdWarps, kDdWarps * 32, smem, s>>>(
         reinterpret_cast<const uint4*>(desc), set_start, npoints, std::max(max_n, 1), best_idx, best_median);
     return 0;

@@ -313,11 +313,8 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K, int band
 
 void launch_stereo(const StereoView& v, const gforb_stereo_params& p, int nframes, int K, cudaStream_t s) {
     const size_t smem = sizeof(RKey) * (size_t)K + sizeof(int) * ((size_t)v.nRows + 2);
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        cudaFuncSetAttribute(stereo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        configured = smem;
-    }
+    static size_t configured[64] = {};
+    if (smem > 48 * 1024) opt_in_smem(stereo_kernel, smem, configured);
     // centre-row window that covers every band: |row - y| < 2*scale + 1  =>  |row - floor(y)| < 2*scale + 2
     float smax = 1.f;
     for (int l = 0; l < kMaxLevels; ++l) smax = v.scale[l] > smax ? v.scale[l] : smax;
