@@ -214,7 +214,8 @@ GFORB_API int gforb_search_for_initialization_batch_device(gforb_matcher* m, con
  * ORBdist, 0..255 (bestDist starts at 256 with bestIdx = -1: a larger bound indexes [-1] in the reference); use_ratio = 1 for the map form (:230, mfNNratio = the matcher's ratio).
  * Out: key_query[k] = index of the query whose map point key k holds on return (-1: untouched, -2: set to NULL by
  * the rotation check), key_dist[k] = mvpMatchScore (:235), query_key[q] = key taken by query q (-1: none or removed),
- * *nmatches = the reference's return value.  <= 8,192 keys and <= 8,192 queries per frame (GFORB_ERR_CAPACITY).
+ * *nmatches = the reference's return value.  <= 8,192 keys and <= 8,192 queries per frame (GFORB_ERR_CAPACITY); a local
+ * map larger than that is handed over without the points the preamble rejected (they would carry flags = 0 anyway).
  * The sequential dependence (a taken key disappears from later windows) is resolved on the device: every query's
  * best / second-best is computed in parallel against the initial state, then one warp replays the queries in order,
  * 32 at a time, re-scanning only those whose best or second-best key was taken meanwhile -- bit-identical results. */
