@@ -190,6 +190,9 @@ GFORB_API int gforb_search_for_initialization_batch_device(gforb_matcher* m, con
  *   SearchByProjection(CurrentFrame, LastFrame, th, bMono)                       src/ORBmatcher.cc:1440-1593
  *   SearchByProjection(CurrentFrame, KeyFrame*, sAlreadyFound, th, ORBdist)      src/ORBmatcher.cc:1595-1721
  *   SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th)  (loop closing)  src/ORBmatcher.cc:406-518
+ *   SearchByProjection_Budget(F, vpMapPoints, th, time_constr)                   src/ORBmatcher.cc:45-153  = the first
+ *       form cut off by a wall-clock budget (:141-147); the cut is where the host CPU happened to be, so it has no
+ *       device equivalent: pass the query prefix you want searched (the whole search costs ~0.1 ms here)
  * All of them walk their queries IN ORDER; per query: GetFeaturesInArea(x, y, r, minLevel, maxLevel), skip keys that
  * already hold a map point, skip keys whose mvuRight is off by more than r, best (and second-best) Hamming distance,
  * threshold, [ratio test when best and second sit on the same level], assign -- and, in the two frame forms, the
