@@ -330,19 +330,19 @@ init_search_kernel(const InitSearchArgs a, int n1cap, int n2cap) {
 //   proj_scan_kernel     warp per query, whole grid: the query's kTopK smallest candidates (distance, then window
 //                        order) against the INITIAL occupancy, each packed as dist << 19 | CSR position << 6 | level;
 //   proj_resolve_kernel  CTA per frame, lists + claims + flags in shared memory, claims indexed by CSR POSITION so the
-//                        replay chases no global pointer.  Warp 0 replays the queries in order, 32 per step: a lane
-//                        walks its list past the positions already claimed; its answer is the sequential one unless
-//                        an earlier lane of the same step takes its best (or, with the ratio test, second-best)
-//                        position (shared atomicMin of the lane number per position).  The lanes in front of the
-//                        first such lane commit together and the step restarts AT that lane, which as lane 0 sees
-//                        every claim.  When the query at the head has used its list up, all 8 warps refresh the lists
-//                        of EVERY not-yet-replayed query in that state (claims only grow, so a list made under the
+//                        replay chases no global pointer.  The CTA replays the queries in order, W per step (thread =
+//                        query): a thread walks its list past the positions already claimed; its answer is the
+//                        sequential one unless an earlier thread of the same step takes its best (or, with the ratio
+//                        test, second-best) position (shared atomicMin of the thread number per position).  The
+//                        threads in front of the first such thread commit together and the next step starts AT that
+//                        thread, which as thread 0 sees every claim.  W = 256 while steps get >= 32 queries through,
+//                        else 32.  When the query at the head has used its list up, all 8 warps refresh the lists of
+//                        EVERY not-yet-replayed query in that state (claims only grow, so a list made under the
 //                        current claims stays valid), then the replay resumes.  What a query took stays in slot 0 of
 //                        its list; key indices, holders (atomicMax = last taker), scores, rotation bins, histogram,
 //                        three maxima and removal are written afterwards by all threads.
-// Measured (B200, 1,008 keys x 1,008 queries, last-frame form): 256 frames per launch 0.37-0.39 ms = 660-700 k frames/s;
-// one frame 67-97 us (grid 7, scan 15, resolve 44-70: the replay is one warp's dependent-instruction latency,
-// ~1,100 cycles per step, 35-52 steps) against 0.55 ms for the sequential CPU oracle.
+// Measured (B200, 1,008 keys x 1,008 queries, last-frame form): 256 frames per launch 0.37-0.40 ms = 640-690 k frames/s;
+// one frame 55-96 us (grid 7, scan 15, resolve 33-70) against 0.55 ms for the sequential CPU oracle.
 namespace {
 constexpr int kTopK = 8;
 constexpr int kLvlBits = 6;                                     // levels < 64
@@ -451,7 +451,7 @@ proj_resolve_kernel(const ProjSearchArgs a, int topk, int qcap) {
     __shared__ uint8_t qflag[1 << kPosBits];
     __shared__ int hist[kHisto];
     __shared__ int keep_bin[3];
-    __shared__ int total, s_base, s_done;
+    __shared__ int total, s_base, s_done, s_first, s_win;
     const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int n = a.n ? min(a.n[f], a.key_stride) : a.n_fixed;
     const int nq = a.nq ? min(a.nq[f], a.q_stride) : a.nq_fixed;
@@ -473,7 +473,7 @@ proj_resolve_kernel(const ProjSearchArgs a, int topk, int qcap) {
         lists[k * nq + qi] = spec[qi * kTopK + k];
     }
     if (tid < kHisto) hist[tid] = 0;
-    if (tid == 0) { total = 0; s_base = 0; s_done = 0; }
+    if (tid == 0) { total = 0; s_base = 0; s_done = 0; s_first = kSearchThreads; s_win = 32; }
     __syncthreads();
 
     const uint32_t full = 0xFFFFFFFFu;
@@ -510,61 +510,65 @@ proj_resolve_kernel(const ProjSearchArgs a, int topk, int qcap) {
         }
         return need || !done;
     };
+    // Replay, the whole CTA per step.  The step covers W queries: 256 while steps get at least 32 queries through, 32 (one
+    // warp's worth of walking; the other threads only keep the barriers) while they do not, so that dense competition
+    // does not multiply the walking by eight.
     while (true) {
-        if (wid == 0) {
-            int base = s_base;
-            bool stalled = false;
-            while (base < nq) {
-                const int qi = base + lane;
-                const bool valid = qi < nq;
-                uint32_t b = kNone, s2 = kNone;
-                const bool need = valid && walk(qi, b, s2);
-                if (__shfl_sync(full, (int)need, 0)) { stalled = true; break; }         // query `base` needs a fresh list
-                const bool acc = valid && !need && accepts(b, s2);
-                const bool blocks = acc && (qflag[valid ? qi : 0] & GFORB_PQ_BLOCKS);
-                const int bpos = b < kTrunc ? key_pos(b) : -2, spos = (a.use_ratio && s2 < kTrunc) ? key_pos(s2) : -2;
-                // does an earlier lane of this step take my best or second-best position?  Each
-                // position about to be taken gets the number of its first taker in tent[]; everyone looks up its own two
-                if (blocks) atomicMin(&tent[bpos], (uint32_t)lane);
-                __syncwarp();
-                const bool bad = need || (bpos >= 0 && tent[bpos] < (uint32_t)lane) || (spos >= 0 && tent[spos] < (uint32_t)lane);
-                __syncwarp();
-                if (blocks) tent[bpos] = kNone;
-                const uint32_t badm = __ballot_sync(full, bad);  // bit 0 is clear here
-                const int nb = badm ? __ffs(badm) - 1 : 32;
-                // slot 0 of a replayed query's list now holds what it took (kNone: nothing); the global side of the
-                // assignment (key index, holder, score, rotation bin) is written after the replay, by all threads
-                if (valid && lane < nb) {
-                    lists[qi] = acc ? b : kNone;
-                    if (blocks) claimed[bpos] = 1;
+        const int base = s_base, W = s_win;
+        if (base >= nq) break;
+        const int qi = base + tid;
+        const bool valid = tid < W && qi < nq;
+        uint32_t b = kNone, s2 = kNone;
+        const bool need = valid && walk(qi, b, s2);
+        if (tid == 0) s_done = need;                                                    // query `base` needs a fresh list
+        const bool acc = valid && !need && accepts(b, s2);
+        const bool blocks = acc && (qflag[valid ? qi : 0] & GFORB_PQ_BLOCKS);
+        const int bpos = b < kTrunc ? key_pos(b) : -2, spos = (a.use_ratio && s2 < kTrunc) ? key_pos(s2) : -2;
+        // does an earlier thread of this step take my best or second-best position?  Each position about to be taken
+        // gets the number of its first taker in tent[]; everyone looks up its own two
+        if (blocks) atomicMin(&tent[bpos], (uint32_t)tid);
+        __syncthreads();
+        if (s_done) {
+            // refresh round, all warps: every query not yet replayed whose list is used up under the claims as they
+            // stand gets a new list (claims only grow, so a list made now stays a valid list later)
+            if (blocks) tent[bpos] = kNone;
+            for (int q0 = base + wid * 32; q0 < nq; q0 += kSearchThreads) {
+                const int qj = q0 + lane;
+                uint32_t tb, ts;
+                uint32_t m = __ballot_sync(full, qj < nq && walk(qj, tb, ts));
+                while (m) {
+                    const int qr = q0 + __ffs(m) - 1;
+                    m &= m - 1;
+                    const gforb_proj_query q = qs[qr];
+                    const uint4* qd = reinterpret_cast<const uint4*>(a.qdesc) + 2 * ((size_t)f * a.q_stride + qr);
+                    const uint4 a0 = __ldg(qd), a1 = __ldg(qd + 1);
+                    uint32_t top[kTopK];
+                    proj_scan<true>(g, keys, reinterpret_cast<const uint4*>(a.desc) + 2 * (size_t)f * a.key_stride,
+                                    a.u_right ? a.u_right + (size_t)f * a.key_stride : nullptr, claimed, q, a0, a1, lane, a.inv_sig2, top);
+#pragma unroll
+                    for (int k = 0; k < kTopK; ++k)
+                        if (lane == 0 && k < topk) lists[k * nq + qr] = top[k];
                 }
-                __syncwarp();
-                base += nb;
             }
-            if (lane == 0) { s_base = base; s_done = !stalled; }
+            __syncthreads();
+            continue;                                                                   // same base, fresh lists
+        }
+        const bool bad = need || (bpos >= 0 && tent[bpos] < (uint32_t)tid) || (spos >= 0 && tent[spos] < (uint32_t)tid);
+        if (bad) atomicMin(&s_first, tid);                                              // thread 0 is never bad here
+        __syncthreads();
+        const int nb = min(s_first, W);
+        if (blocks) tent[bpos] = kNone;
+        // slot 0 of a replayed query's list now holds what it took (kNone: nothing); the global side of the
+        // assignment (key index, holder, score, rotation bin) is written after the replay, by all threads
+        if (valid && tid < nb) {
+            lists[qi] = acc ? b : kNone;
+            if (blocks) claimed[bpos] = 1;
         }
         __syncthreads();
-        if (s_done) break;
-        // refresh round, all warps: every query not yet replayed whose list is used up under the claims as they
-        // stand gets a new list (claims only grow, so a list made now stays a valid list later)
-        const int base = s_base;
-        for (int q0 = base + wid * 32; q0 < nq; q0 += kSearchThreads) {
-            const int qi = q0 + lane;
-            uint32_t b, s2;
-            uint32_t m = __ballot_sync(full, qi < nq && walk(qi, b, s2));
-            while (m) {
-                const int qr = q0 + __ffs(m) - 1;
-                m &= m - 1;
-                const gforb_proj_query q = qs[qr];
-                const uint4* qd = reinterpret_cast<const uint4*>(a.qdesc) + 2 * ((size_t)f * a.q_stride + qr);
-                const uint4 a0 = __ldg(qd), a1 = __ldg(qd + 1);
-                uint32_t top[kTopK];
-                proj_scan<true>(g, keys, reinterpret_cast<const uint4*>(a.desc) + 2 * (size_t)f * a.key_stride,
-                                a.u_right ? a.u_right + (size_t)f * a.key_stride : nullptr, claimed, q, a0, a1, lane, a.inv_sig2, top);
-#pragma unroll
-                for (int k = 0; k < kTopK; ++k)
-                    if (lane == 0 && k < topk) lists[k * nq + qr] = top[k];
-            }
+        if (tid == 0) {
+            s_base = base + nb;
+            s_first = kSearchThreads;
+            s_win = nb >= 32 ? kSearchThreads : 32;                 // wide while a step gets at least a warp's worth through
         }
         __syncthreads();
     }
