@@ -220,8 +220,8 @@ GFORB_API int gforb_search_for_initialization_batch_device(gforb_matcher* m, con
  * *nmatches = the reference's return value.  <= 8,192 keys and <= 8,192 queries per frame (GFORB_ERR_CAPACITY); a local
  * map larger than that is handed over without the points the preamble rejected (they would carry flags = 0 anyway).
  * The sequential dependence (a taken key disappears from later windows) is resolved on the device: every query's
- * best / second-best is computed in parallel against the initial state, then one warp replays the queries in order,
- * 32 at a time, re-scanning only those whose best or second-best key was taken meanwhile -- bit-identical results. */
+ * eight smallest candidates are computed in parallel against the initial state, then one CTA replays the queries in
+ * order, up to 256 per step, re-scanning only those whose list was used up by keys taken meanwhile -- bit-identical results. */
 typedef struct gforb_proj_query { float x, y, r, xr, angle; int32_t min_level, max_level, flags; } gforb_proj_query;
 enum { GFORB_PQ_ACTIVE = 1, GFORB_PQ_BLOCKS = 2, GFORB_PQ_RIGHT_GATE = 4, GFORB_PQ_REPROJ_GATE = 8 };
 /* The candidate search of ORBmatcher::Fuse(KeyFrame*, const vector<MapPoint*>&, th) (src/ORBmatcher.cc:937-1087) is the
