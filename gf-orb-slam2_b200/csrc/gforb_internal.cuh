@@ -154,6 +154,7 @@ struct InitSearchArgs {
     int check_ori, th_low;
     int32_t* matches12;          // [pair][stride1]
     int32_t* nmatches;           // [pair]
+    uint2* spec;                 // [pair][stride1] scratch: speculative best / second-best of phase 1
 };
 // ORBmatcher::SearchByProjection over already-projected queries (k_gridmatch.cu); frame f reads keys + f * key_stride,
 // queries + f * q_stride; n / nq == nullptr: every frame has n_fixed / nq_fixed entries
@@ -197,7 +198,7 @@ void launch_grid_build(const gforb_keypoint* keys, const int32_t* counts, int n_
 void launch_area_query(const gforb_keypoint* keys, const float* bounds, const int32_t* cell_start, const int32_t* cell_idx,
                        const void* queries, int nq, int32_t* out_count, const int32_t* out_start, int32_t* out_idx,
                        cudaStream_t s);
-int launch_init_search(const InitSearchArgs& a, const float* bounds, int npairs, cudaStream_t s);   // 1 launch; -1: smem opt-in failed
+int launch_init_search(const InitSearchArgs& a, const float* bounds, int npairs, cudaStream_t s);   // 2 launches; -1: smem opt-in failed
 // input pre-processing (k_preprocess.cu): [16 -> 8 bit] -> remap -> gray; 1 launch.  fmt: gforb.h GFORB_PIX_*
 int preprocess_bytes_per_pixel(int fmt);
 void launch_preprocess(const uint8_t* src, int sw, int sh, size_t spitch, size_t sstride, int fmt, const float* mapx,

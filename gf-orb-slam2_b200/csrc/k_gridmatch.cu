@@ -209,6 +209,26 @@ __device__ __forceinline__ Cand scan_window(const GridView& g, const gforb_keypo
 }
 }  // namespace
 
+// phase 1, one warp per level-0 query over the whole grid (blockIdx.y = pair): speculative best / second-best
+__global__ void __launch_bounds__(256)
+init_scan_kernel(const InitSearchArgs a) {
+    const int p = blockIdx.y, lane = threadIdx.x & 31, q = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int n1 = a.n1 ? min(a.n1[p], a.stride1) : a.n1_fixed;
+    if (q >= n1) return;
+    const int n2 = a.n2 ? min(a.n2[p], a.stride2) : a.n2_fixed;
+    const gforb_keypoint* k1 = a.k1 + (size_t)p * a.stride1;
+    Cand c{kNone, kNone};
+    if (n2 > 0 && __ldg(&k1[q].octave) <= 0) {
+        const uint4* d1 = reinterpret_cast<const uint4*>(a.d1) + 2 * (size_t)p * a.stride1;
+        const float* prev = a.prev_xy + 2 * (size_t)p * a.stride1;
+        GridView g{a.cell_start + (size_t)p * (kGCells + 1), a.cell_idx + (size_t)p * a.stride2, a.min_x, a.min_y, a.w_inv, a.h_inv};
+        const uint4 a0 = __ldg(d1 + 2 * (size_t)q), a1 = __ldg(d1 + 2 * (size_t)q + 1);
+        c = scan_window<false>(g, a.k2 + (size_t)p * a.stride2, reinterpret_cast<const uint4*>(a.d2) + 2 * (size_t)p * a.stride2,
+                               prev[2 * q], prev[2 * q + 1], a.window, a0, a1, nullptr, lane);
+    }
+    if (lane == 0) reinterpret_cast<Cand*>(a.spec)[(size_t)p * a.stride1 + q] = c;
+}
+
 // dynamic shared: claim[n2cap] u32 (dist << 16 | owner, 0xFFFFFFFF = free) | spec[n1cap] Cand | bin[n1cap] u8
 __global__ void __launch_bounds__(kSearchThreads)
 init_search_kernel(const InitSearchArgs a, int n1cap, int n2cap) {
@@ -236,14 +256,10 @@ init_search_kernel(const InitSearchArgs a, int n1cap, int n2cap) {
     if (tid < kHisto) hist[tid] = 0;
     if (tid == 0) total = 0;
 
-    // phase 1: speculative best / second-best, one warp per level-0 query
-    for (int q = wid; q < n1; q += kSearchThreads / 32) {
-        Cand c{kNone, kNone};
-        if (n2 > 0 && __ldg(&k1[q].octave) <= 0) {
-            const uint4 a0 = __ldg(d1 + 2 * (size_t)q), a1 = __ldg(d1 + 2 * (size_t)q + 1);
-            c = scan_window<false>(g, k2, d2, prev[2 * q], prev[2 * q + 1], a.window, a0, a1, nullptr, lane);
-        }
-        if (lane == 0) spec[q] = c;
+    // phase 1 ran in init_scan_kernel (whole grid): fetch its speculative best / second-best per query
+    {
+        const Cand* gs = reinterpret_cast<const Cand*>(a.spec) + (size_t)p * a.stride1;
+        for (int q = tid; q < n1; q += kSearchThreads) spec[q] = gs[q];
     }
     __syncthreads();
 
@@ -801,6 +817,7 @@ int launch_init_search(const InitSearchArgs& a, const float* bounds, int npairs,
     const size_t smem = init_search_smem(n1cap, n2cap);
     static size_t have[64] = {};
     if (opt_in_smem(init_search_kernel, smem, have)) return -1;
+    init_scan_kernel<<<dim3((n1cap + 7) / 8, npairs), 256, 0, s>>>(b);
     init_search_kernel<<<npairs, kSearchThreads, smem, s>>>(b, n1cap, n2cap);
     return 0;
 }

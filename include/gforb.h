@@ -179,7 +179,8 @@ GFORB_API int gforb_search_for_initialization(gforb_matcher* m, const gforb_fram
  * own).  Pair p reads keys at dev_keysX + p * strideX (elements), descriptors at dev_descX + p * strideX * 32, counts
  * dev_nX[p] (<= strideX; NULL = every pair has strideX keys) -- the layout gforb_batch keeps its keypoints in.
  * dev_prev_xy: [pair][stride1][2] in/out, dev_matches12: [pair][stride1], dev_nmatches: [pair].  Descriptor arrays
- * must be 16-byte aligned.  2 launches (grid build, search); gforb_matcher_sync returns their device time. */
+ * must be 16-byte aligned.  3 launches (grid build, window scan, in-order search); gforb_matcher_sync returns their device
+ * time. */
 GFORB_API int gforb_search_for_initialization_batch_device(gforb_matcher* m, const gforb_frame_bounds* bounds, int n_pairs,
                                     const gforb_keypoint* dev_keys1, const uint8_t* dev_desc1, const int32_t* dev_n1, int stride1,
                                     const gforb_keypoint* dev_keys2, const uint8_t* dev_desc2, const int32_t* dev_n2, int stride2,
