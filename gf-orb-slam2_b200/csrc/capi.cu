@@ -565,7 +565,7 @@ int gforb_search_for_initialization_batch_device(gforb_matcher* m, const gforb_f
     m->last = s;
     const int cells = gridmatch_cells(), st2 = std::max(stride2, 1);
     const size_t bs = al16((size_t)n_pairs * (cells + 1) * 4), bi = al16((size_t)n_pairs * st2 * 4);
-    rc = m->reserve(m->scratch, m->scratch_bytes, bs + bi + (size_t)n_pairs * std::max(stride1, 1) * 8);
+    rc = m->reserve(m->scratch, m->scratch_bytes, bs + bi + (size_t)n_pairs * std::max(stride1, 1) * 32);
     if (rc) return rc;
     int32_t* ds = static_cast<int32_t*>(m->scratch);
     int32_t* di = reinterpret_cast<int32_t*>(static_cast<uint8_t*>(m->scratch) + bs);
@@ -579,7 +579,7 @@ int gforb_search_for_initialization_batch_device(gforb_matcher* m, const gforb_f
     a.prev_xy = prev_xy; a.window = (float)window_size; a.ratio = m->ratio;
     a.check_ori = check_orientation ? 1 : 0; a.th_low = GFORB_TH_LOW;
     a.matches12 = matches12; a.nmatches = nmatches;
-    a.spec = reinterpret_cast<uint2*>(static_cast<uint8_t*>(m->scratch) + bs + bi);
+    a.spec = reinterpret_cast<uint4*>(static_cast<uint8_t*>(m->scratch) + bs + bi);
     if (launch_init_search(a, bb, n_pairs, s)) { set_error("gforb_search_for_initialization: shared-memory opt-in failed"); return GFORB_ERR_CUDA; }
     M_CUDA(cudaEventRecord(m->ev1, s));
     M_CUDA(cudaGetLastError());

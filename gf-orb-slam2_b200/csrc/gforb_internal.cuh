@@ -154,7 +154,7 @@ struct InitSearchArgs {
     int check_ori, th_low;
     int32_t* matches12;          // [pair][stride1]
     int32_t* nmatches;           // [pair]
-    uint2* spec;                 // [pair][stride1] scratch: speculative best / second-best of phase 1
+    uint4* spec;                 // [pair][stride1][2] scratch: each query's 8 smallest candidates, packed
 };
 // ORBmatcher::SearchByProjection over already-projected queries (k_gridmatch.cu); frame f reads keys + f * key_stride,
 // queries + f * q_stride; n / nq == nullptr: every frame has n_fixed / nq_fixed entries

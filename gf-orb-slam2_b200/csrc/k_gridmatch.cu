@@ -13,16 +13,9 @@
 // contiguous CSR run.  So "candidate order" (it decides which of two equal Hamming minima wins) is the CSR position
 // and needs no per-query list, no ballot and no atomics.
 //
-// SearchForInitialization is sequential in the reference: query i1 ignores a target i2 that an earlier query already
-// holds with a distance <= its own (vMatchedDistance), and may take a target over.  Parallel restatement:
-//   phase 1 (all warps, one level-0 query per warp): best / second-best over the window IGNORING the claim table;
-//   phase 2 (one warp, queries in order): the speculative pair is the sequential answer unless the claim table
-//            hides its best or its second-best target (hiding any other candidate cannot change the two smallest);
-//            only then the warp re-walks that query's window with the claim filter.  Claims, take-overs and the
-//            rotation-bin of each accepted query are recorded exactly as the reference does;
-//   phase 3 (all threads): 30-bin rotation histogram (counts include matches that were later taken over, as
-//            rotHist[].push_back does), three maxima, removal, vbPrevMatched update, match count.
-// One CTA per frame pair; frame pairs are independent (batch dimension = grid).
+// The searches (SearchForInitialization, SearchByProjection, SearchByBoW, SearchForTriangulation) are described at their
+// sections below; the ones with a sequential rule in the reference share one scheme: a grid-wide scan kernel keeps each
+// query's 8 smallest candidates, a CTA per frame replays the queries in order against claims held in shared memory.
 #include "gforb_internal.cuh"
 
 namespace gforb {
@@ -172,173 +165,6 @@ area_query_kernel(const gforb_keypoint* __restrict__ keys, GridView g, const Are
     if (!out_start && lane == 0) out_count[q] = total;
 }
 
-// ------------------------------------------------------------------------------------ SearchForInitialization
-
-namespace {
-struct Cand { uint32_t best, second; };      // keys: dist << 13 | CSR position
-
-// best / second-best of query (x, y, descriptor a) over its window, lanes striding each CSR run.
-// kFiltered: skip targets whose claim distance is <= the candidate's (src/ORBmatcher.cc:559-560).
-template <bool kFiltered>
-__device__ __forceinline__ Cand scan_window(const GridView& g, const gforb_keypoint* __restrict__ k2,
-                                            const uint4* __restrict__ d2, float x, float y, float r, const uint4& a0,
-                                            const uint4& a1, const uint32_t* claim, int lane) {
-    uint32_t best = kNone, second = kNone;
-    int x0, x1, y0, y1;
-    if (area_window(g, x, y, r, x0, x1, y0, y1)) {
-        for (int ix = x0; ix <= x1; ++ix) {
-            const int j0 = __ldg(g.start + ix * kGRows + y0), j1 = __ldg(g.start + ix * kGRows + y1 + 1);
-            for (int j = j0 + lane; j < j1; j += 32) {
-                const int i2 = __ldg(g.idx + j);
-                if (!area_accepts(k2, i2, x, y, r, 0, 0)) continue;        // level1 == 0: minLevel = maxLevel = 0
-                const int dist = hamming256(a0, a1, __ldg(d2 + 2 * (size_t)i2), __ldg(d2 + 2 * (size_t)i2 + 1));
-                if (kFiltered && (int)(claim[i2] >> 16) <= dist) continue;
-                const uint32_t key = ((uint32_t)dist << kPosBits) | (uint32_t)j;
-                second = min(second, max(best, key));
-                best = min(best, key);
-            }
-        }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        const uint32_t ob = __shfl_xor_sync(0xFFFFFFFFu, best, o), os = __shfl_xor_sync(0xFFFFFFFFu, second, o);
-        second = min(min(second, os), max(best, ob));
-        best = min(best, ob);
-    }
-    return {best, second};
-}
-}  // namespace
-
-// phase 1, one warp per level-0 query over the whole grid (blockIdx.y = pair): speculative best / second-best
-__global__ void __launch_bounds__(256)
-init_scan_kernel(const InitSearchArgs a) {
-    const int p = blockIdx.y, lane = threadIdx.x & 31, q = blockIdx.x * 8 + (threadIdx.x >> 5);
-    const int n1 = a.n1 ? min(a.n1[p], a.stride1) : a.n1_fixed;
-    if (q >= n1) return;
-    const int n2 = a.n2 ? min(a.n2[p], a.stride2) : a.n2_fixed;
-    const gforb_keypoint* k1 = a.k1 + (size_t)p * a.stride1;
-    Cand c{kNone, kNone};
-    if (n2 > 0 && __ldg(&k1[q].octave) <= 0) {
-        const uint4* d1 = reinterpret_cast<const uint4*>(a.d1) + 2 * (size_t)p * a.stride1;
-        const float* prev = a.prev_xy + 2 * (size_t)p * a.stride1;
-        GridView g{a.cell_start + (size_t)p * (kGCells + 1), a.cell_idx + (size_t)p * a.stride2, a.min_x, a.min_y, a.w_inv, a.h_inv};
-        const uint4 a0 = __ldg(d1 + 2 * (size_t)q), a1 = __ldg(d1 + 2 * (size_t)q + 1);
-        c = scan_window<false>(g, a.k2 + (size_t)p * a.stride2, reinterpret_cast<const uint4*>(a.d2) + 2 * (size_t)p * a.stride2,
-                               prev[2 * q], prev[2 * q + 1], a.window, a0, a1, nullptr, lane);
-    }
-    if (lane == 0) reinterpret_cast<Cand*>(a.spec)[(size_t)p * a.stride1 + q] = c;
-}
-
-// dynamic shared: claim[n2cap] u32 (dist << 16 | owner, 0xFFFFFFFF = free) | spec[n1cap] Cand | bin[n1cap] u8
-__global__ void __launch_bounds__(kSearchThreads)
-init_search_kernel(const InitSearchArgs a, int n1cap, int n2cap) {
-    extern __shared__ __align__(16) uint8_t sm_raw[];
-    uint32_t* claim = reinterpret_cast<uint32_t*>(sm_raw);
-    Cand* spec = reinterpret_cast<Cand*>(claim + n2cap);
-    uint8_t* bin = reinterpret_cast<uint8_t*>(spec + n1cap);
-    __shared__ int hist[kHisto];
-    __shared__ int keep_bin[3];
-    __shared__ int total;
-
-    const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int n1 = a.n1 ? min(a.n1[p], a.stride1) : a.n1_fixed;
-    const int n2 = a.n2 ? min(a.n2[p], a.stride2) : a.n2_fixed;
-    const gforb_keypoint* k1 = a.k1 + (size_t)p * a.stride1;
-    const gforb_keypoint* k2 = a.k2 + (size_t)p * a.stride2;
-    const uint4* d1 = reinterpret_cast<const uint4*>(a.d1) + 2 * (size_t)p * a.stride1;
-    const uint4* d2 = reinterpret_cast<const uint4*>(a.d2) + 2 * (size_t)p * a.stride2;
-    float* prev = a.prev_xy + 2 * (size_t)p * a.stride1;
-    int32_t* m12 = a.matches12 + (size_t)p * a.stride1;
-    GridView g{a.cell_start + (size_t)p * (kGCells + 1), a.cell_idx + (size_t)p * a.stride2, a.min_x, a.min_y, a.w_inv, a.h_inv};
-
-    for (int i = tid; i < n2; i += kSearchThreads) claim[i] = kNone;
-    for (int i = tid; i < n1; i += kSearchThreads) { bin[i] = 0xFF; m12[i] = -1; }
-    if (tid < kHisto) hist[tid] = 0;
-    if (tid == 0) total = 0;
-
-    // phase 1 ran in init_scan_kernel (whole grid): fetch its speculative best / second-best per query
-    {
-        const Cand* gs = reinterpret_cast<const Cand*>(a.spec) + (size_t)p * a.stride1;
-        for (int q = tid; q < n1; q += kSearchThreads) spec[q] = gs[q];
-    }
-    __syncthreads();
-
-    // phase 2: the reference's sequential claim rule, queries in order, warp 0
-    if (wid == 0) {
-        for (int q = 0; q < n1; ++q) {
-            Cand c = spec[q];
-            if (c.best == kNone) continue;                                  // level > 0 or empty window
-            int ib = __ldg(g.idx + (c.best & ((1u << kPosBits) - 1)));
-            const int is = c.second == kNone ? -1 : __ldg(g.idx + (c.second & ((1u << kPosBits) - 1)));
-            const bool hidden = (int)(claim[ib] >> 16) <= (int)(c.best >> kPosBits) ||
-                                (is >= 0 && (int)(claim[is] >> 16) <= (int)(c.second >> kPosBits));
-            if (hidden) {
-                const uint4 a0 = __ldg(d1 + 2 * (size_t)q), a1 = __ldg(d1 + 2 * (size_t)q + 1);
-                c = scan_window<true>(g, k2, d2, prev[2 * q], prev[2 * q + 1], a.window, a0, a1, claim, lane);
-                if (c.best == kNone) continue;                              // bestDist stays INT_MAX
-                ib = __ldg(g.idx + (c.best & ((1u << kPosBits) - 1)));
-            }
-            const int bd = (int)(c.best >> kPosBits);
-            const int sd = c.second == kNone ? INT32_MAX : (int)(c.second >> kPosBits);
-            // src/ORBmatcher.cc:574-576
-            if (bd <= a.th_low && (float)bd < __fmul_rn((float)sd, a.ratio)) {
-                if (lane == 0) {
-                    const uint32_t old = claim[ib];
-                    if (old != kNone) m12[old & 0xFFFFu] = -1;              // take-over (:578-582)
-                    m12[q] = ib;
-                    claim[ib] = ((uint32_t)bd << 16) | (uint32_t)q;
-                    if (a.check_ori) {                                      // :588-597
-                        float rot = __fsub_rn(__ldg(&k1[q].angle), __ldg(&k2[ib].angle));
-                        if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
-                        int b = (int)roundf(__fmul_rn(rot, 1.0f / kHisto));
-                        if (b == kHisto) b = 0;
-                        bin[q] = (uint8_t)b;
-                    }
-                }
-                __syncwarp();
-            }
-        }
-    }
-    __syncthreads();
-
-    // phase 3: rotation consistency (:601-622), vbPrevMatched update (:625-627), match count
-    if (a.check_ori) {
-        for (int q = tid; q < n1; q += kSearchThreads)
-            if (bin[q] != 0xFF) atomicAdd(&hist[bin[q]], 1);
-        __syncthreads();
-        if (tid == 0) {                                                     // ComputeThreeMaxima, :1723-1764
-            int max1 = 0, max2 = 0, max3 = 0, i1 = -1, i2 = -1, i3 = -1;
-            for (int i = 0; i < kHisto; ++i) {
-                const int s = hist[i];
-                if (s > max1) { max3 = max2; max2 = max1; max1 = s; i3 = i2; i2 = i1; i1 = i; }
-                else if (s > max2) { max3 = max2; max2 = s; i3 = i2; i2 = i; }
-                else if (s > max3) { max3 = s; i3 = i; }
-            }
-            if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { i2 = -1; i3 = -1; }
-            else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { i3 = -1; }
-            keep_bin[0] = i1; keep_bin[1] = i2; keep_bin[2] = i3;
-        }
-        __syncthreads();
-    }
-    int mine = 0;
-    for (int q = tid; q < n1; q += kSearchThreads) {
-        int m = m12[q];
-        if (m >= 0 && a.check_ori) {
-            const int b = bin[q];
-            if (b != keep_bin[0] && b != keep_bin[1] && b != keep_bin[2]) { m = -1; m12[q] = -1; }
-        }
-        if (m >= 0) {
-            prev[2 * q] = __ldg(&k2[m].x);
-            prev[2 * q + 1] = __ldg(&k2[m].y);
-            ++mine;
-        }
-    }
-    mine = __reduce_add_sync(0xFFFFFFFFu, mine);
-    if (lane == 0 && mine) atomicAdd(&total, mine);
-    __syncthreads();
-    if (tid == 0) a.nmatches[p] = total;
-}
-
 // ------------------------------------------------------------------------------------------ SearchByProjection
 // src/ORBmatcher.cc:155-241 (map points), :1440-1593 (last frame), :1595-1721 (key frame), folded as include/gforb.h
 // describes.  Sequential rule in the reference: a key taken by a query whose map point has observations is skipped by
@@ -372,7 +198,8 @@ template <bool kByPos>
 __device__ __forceinline__ void proj_scan(const GridView& g, const gforb_keypoint* __restrict__ keys,
                                           const uint4* __restrict__ desc, const float* __restrict__ u_right,
                                           const uint8_t* blocked, const gforb_proj_query& q, const uint4& a0,
-                                          const uint4& a1, int lane, const float* inv_sig2, uint32_t (&top)[kTopK]) {
+                                          const uint4& a1, int lane, const float* inv_sig2, uint32_t (&top)[kTopK],
+                                          const uint16_t* cdist = nullptr, bool keep_all = false) {
     uint32_t best = kNone, second = kNone;
     int cnt = 0;
     const bool gate = (q.flags & GFORB_PQ_RIGHT_GATE) && u_right;
@@ -401,7 +228,8 @@ __device__ __forceinline__ void proj_scan(const GridView& g, const gforb_keypoin
                     } else if ((double)__fmul_rn(e2, inv) > 5.99) continue;
                 }
                 const int dist = hamming256(a0, a1, __ldg(desc + 2 * (size_t)i), __ldg(desc + 2 * (size_t)i + 1));
-                if (dist >= 256) continue;                                             // never below the initial 256
+                if (dist >= 256 && !keep_all) continue;                                // never below the initial 256
+                if (cdist && (int)cdist[j] <= dist) continue;                          // vMatchedDistance[i2] <= dist, :559-560
                 const uint32_t key = ((uint32_t)dist << kDistShift) | ((uint32_t)j << kLvlBits) |
                                      ((uint32_t)__ldg(&keys[i].octave) & ((1u << kLvlBits) - 1));
                 ++cnt;
@@ -643,6 +471,212 @@ proj_resolve_kernel(const ProjSearchArgs a, int topk, int qcap) {
     if (tid == 0) a.nmatches[f] = total;
 }
 
+// ------------------------------------------------------------------------------------ SearchForInitialization
+// src/ORBmatcher.cc:520-633.  Sequential in the reference: query i1 ignores a target i2 that an earlier query holds
+// with a distance <= its own (vMatchedDistance, :559-560) and may take a target over (:578-582).  Device restatement
+// with the machinery of SearchByProjection above:
+//   init_scan_kernel     warp per level-0 query, whole grid: its 8 smallest candidates (window vbPrevMatched +- windowSize,
+//                        level 0) against an empty claim table;
+//   init_resolve_kernel  CTA per frame pair, in-order replay W queries per step.  A claim holds the claimed DISTANCE
+//                        (cdist[position], 0xFFFF = free): a candidate is visible while its claim is larger than its
+//                        own distance, so a thread's best / second-best are the first two visible entries of its list.
+//                        Claims only get smaller, hence hidden entries stay hidden and only a claim on the thread's
+//                        best or second-best position by an earlier thread of the step invalidates its answer.
+//                        holder[position] = last taker (take-over), bins of every accepted query (rotHist counts
+//                        matches that were later taken over, as push_back does), three maxima, removal, vbPrevMatched
+//                        update and the count by all threads.
+__global__ void __launch_bounds__(256)
+init_scan_kernel(const InitSearchArgs a) {
+    const int p = blockIdx.y, lane = threadIdx.x & 31, q = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int n1 = a.n1 ? min(a.n1[p], a.stride1) : a.n1_fixed;
+    if (q >= n1) return;
+    const int n2 = a.n2 ? min(a.n2[p], a.stride2) : a.n2_fixed;
+    const gforb_keypoint* k1 = a.k1 + (size_t)p * a.stride1;
+    uint32_t top[kTopK];
+#pragma unroll
+    for (int k = 0; k < kTopK; ++k) top[k] = kNone;
+    if (n2 > 0 && __ldg(&k1[q].octave) <= 0) {                            // level1 > 0: continue (:537-538)
+        const uint4* d1 = reinterpret_cast<const uint4*>(a.d1) + 2 * (size_t)p * a.stride1;
+        const float* prev = a.prev_xy + 2 * (size_t)p * a.stride1;
+        const GridView g{a.cell_start + (size_t)p * (kGCells + 1), a.cell_idx + (size_t)p * a.stride2, a.min_x, a.min_y, a.w_inv, a.h_inv};
+        const gforb_proj_query pq{prev[2 * q], prev[2 * q + 1], a.window, 0.f, 0.f, 0, 0, GFORB_PQ_ACTIVE};   // level1, level1 = 0, 0
+        const uint4 a0 = __ldg(d1 + 2 * (size_t)q), a1 = __ldg(d1 + 2 * (size_t)q + 1);
+        proj_scan<false>(g, a.k2 + (size_t)p * a.stride2, reinterpret_cast<const uint4*>(a.d2) + 2 * (size_t)p * a.stride2, nullptr,
+                         nullptr, pq, a0, a1, lane, nullptr, top, nullptr, true);
+    }
+    if (lane == 0) {
+        uint4* o = reinterpret_cast<uint4*>(a.spec) + 2 * ((size_t)p * a.stride1 + q);
+        o[0] = make_uint4(top[0], top[1], top[2], top[3]);
+        o[1] = make_uint4(top[4], top[5], top[6], top[7]);
+    }
+}
+
+// dynamic shared: lists[topk][n1] u32 (room for qcap queries) | tent[8192] u32
+__global__ void __launch_bounds__(kSearchThreads)
+init_resolve_kernel(const InitSearchArgs a, int topk, int qcap) {
+    extern __shared__ uint32_t lists[];
+    uint32_t* tent = lists + (size_t)topk * qcap;
+    __shared__ uint16_t cdist[1 << kPosBits];                   // by CSR position: distance the position is held with
+    __shared__ uint16_t holder[1 << kPosBits];                  // by CSR position: query holding it
+    __shared__ uint8_t bin[1 << kPosBits];
+    __shared__ int hist[kHisto];
+    __shared__ int keep_bin[3];
+    __shared__ int total, s_base, s_done, s_first, s_win;
+    const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int n1 = a.n1 ? min(a.n1[p], a.stride1) : a.n1_fixed;
+    const int n2 = a.n2 ? min(a.n2[p], a.stride2) : a.n2_fixed;
+    const gforb_keypoint* k1 = a.k1 + (size_t)p * a.stride1;
+    const gforb_keypoint* k2 = a.k2 + (size_t)p * a.stride2;
+    const uint4* d1 = reinterpret_cast<const uint4*>(a.d1) + 2 * (size_t)p * a.stride1;
+    const uint4* d2 = reinterpret_cast<const uint4*>(a.d2) + 2 * (size_t)p * a.stride2;
+    float* prev = a.prev_xy + 2 * (size_t)p * a.stride1;
+    int32_t* m12 = a.matches12 + (size_t)p * a.stride1;
+    const GridView g{a.cell_start + (size_t)p * (kGCells + 1), a.cell_idx + (size_t)p * a.stride2, a.min_x, a.min_y, a.w_inv, a.h_inv};
+    const uint32_t* spec = reinterpret_cast<const uint32_t*>(a.spec) + (size_t)kTopK * p * a.stride1;
+    const int nq = n1;
+
+    const int n_in = n2 > 0 ? __ldg(g.start + kGCells) : 0;
+    for (int j = tid; j < n_in; j += kSearchThreads) { cdist[j] = 0xFFFF; tent[j] = kNone; }
+    for (int i = tid; i < nq; i += kSearchThreads) { bin[i] = 0xFF; m12[i] = -1; }
+    for (int t = tid; t < nq * topk; t += kSearchThreads) {
+        const int qi = t / topk, k = t - qi * topk;
+        lists[k * nq + qi] = spec[qi * kTopK + k];
+    }
+    if (tid < kHisto) hist[tid] = 0;
+    if (tid == 0) { total = 0; s_base = 0; s_done = 0; s_first = kSearchThreads; s_win = 32; }
+    __syncthreads();
+
+    const uint32_t full = 0xFFFFFFFFu;
+    // first and second entry of query qi's list still visible under the claims; true = the list ran out first
+    auto walk = [&](int qi, uint32_t& b, uint32_t& s2) {
+        uint32_t e[kTopK];
+        bool hid[kTopK];
+#pragma unroll
+        for (int k = 0; k < kTopK; ++k) e[k] = k < topk ? lists[k * nq + qi] : kTrunc;
+#pragma unroll
+        for (int k = 0; k < kTopK; ++k) hid[k] = e[k] < kTrunc && (uint32_t)cdist[key_pos(e[k])] <= (e[k] >> kDistShift);   // :559-560
+        b = kNone; s2 = kNone;
+        bool need = false, done = false;
+#pragma unroll
+        for (int k = 0; k < kTopK; ++k) {
+            if (done) continue;
+            if (e[k] == kNone) done = true;
+            else if (e[k] == kTrunc) { need = true; done = true; }
+            else if (!hid[k]) {
+                if (b == kNone) b = e[k];
+                else { s2 = e[k]; done = true; }
+            }
+        }
+        return need || !done;
+    };
+    // src/ORBmatcher.cc:574-576
+    auto accepts = [&](uint32_t b, uint32_t s2) {
+        if (b >= kTrunc) return false;
+        const int bd = (int)(b >> kDistShift);
+        const int sd = s2 < kTrunc ? (int)(s2 >> kDistShift) : INT32_MAX;
+        return bd <= a.th_low && (float)bd < __fmul_rn((float)sd, a.ratio);
+    };
+    while (true) {
+        const int base = s_base, W = s_win;
+        if (base >= nq) break;
+        const int qi = base + tid;
+        const bool valid = tid < W && qi < nq;
+        uint32_t b = kNone, s2 = kNone;
+        const bool need = valid && walk(qi, b, s2);
+        if (tid == 0) s_done = need;
+        const bool acc = valid && !need && accepts(b, s2);
+        const int bpos = b < kTrunc ? key_pos(b) : -2, spos = s2 < kTrunc ? key_pos(s2) : -2;
+        if (acc) atomicMin(&tent[bpos], (uint32_t)tid);
+        __syncthreads();
+        if (s_done) {                                            // refresh round: new lists under the claims as they stand
+            if (acc) tent[bpos] = kNone;
+            for (int q0 = base + wid * 32; q0 < nq; q0 += kSearchThreads) {
+                const int qj = q0 + lane;
+                uint32_t tb, ts;
+                uint32_t m = __ballot_sync(full, qj < nq && walk(qj, tb, ts));
+                while (m) {
+                    const int qr = q0 + __ffs(m) - 1;
+                    m &= m - 1;
+                    const gforb_proj_query pq{prev[2 * qr], prev[2 * qr + 1], a.window, 0.f, 0.f, 0, 0, GFORB_PQ_ACTIVE};
+                    const uint4 a0 = __ldg(d1 + 2 * (size_t)qr), a1 = __ldg(d1 + 2 * (size_t)qr + 1);
+                    uint32_t top[kTopK];
+                    proj_scan<true>(g, k2, d2, nullptr, nullptr, pq, a0, a1, lane, nullptr, top, cdist, true);
+#pragma unroll
+                    for (int k = 0; k < kTopK; ++k)
+                        if (lane == 0 && k < topk) lists[k * nq + qr] = top[k];
+                }
+            }
+            __syncthreads();
+            continue;
+        }
+        const bool bad = need || (bpos >= 0 && tent[bpos] < (uint32_t)tid) || (spos >= 0 && tent[spos] < (uint32_t)tid);
+        if (bad) atomicMin(&s_first, tid);
+        __syncthreads();
+        const int nb = min(s_first, W);
+        if (acc) tent[bpos] = kNone;
+        if (valid && tid < nb) {
+            lists[qi] = acc ? b : kNone;                         // slot 0: what the query took
+            if (acc) { cdist[bpos] = (uint16_t)(b >> kDistShift); holder[bpos] = (uint16_t)qi; }      // :578-586
+        }
+        __syncthreads();
+        if (tid == 0) {
+            s_base = base + nb;
+            s_first = kSearchThreads;
+            s_win = nb >= 32 ? kSearchThreads : 32;
+        }
+        __syncthreads();
+    }
+
+    // matches of the current holders, rotation bins of every accepted query (:588-597)
+    for (int q = tid; q < nq; q += kSearchThreads) {
+        const uint32_t e = lists[q];
+        if (e >= kTrunc) continue;
+        const int pos = key_pos(e), ib = __ldg(g.idx + pos);
+        if (holder[pos] == q) m12[q] = ib;
+        if (a.check_ori) {
+            float rot = __fsub_rn(__ldg(&k1[q].angle), __ldg(&k2[ib].angle));
+            if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+            int bb = (int)roundf(__fmul_rn(rot, 1.0f / kHisto));
+            bb = bb == kHisto ? 0 : bb;
+            bin[q] = (uint8_t)bb;
+            atomicAdd(&hist[bb], 1);
+        }
+    }
+    __syncthreads();
+    if (a.check_ori) {                                                       // :601-622
+        if (tid == 0) {                                                      // ComputeThreeMaxima, :1723-1764
+            int max1 = 0, max2 = 0, max3 = 0, i1 = -1, i2 = -1, i3 = -1;
+            for (int i = 0; i < kHisto; ++i) {
+                const int s = hist[i];
+                if (s > max1) { max3 = max2; max2 = max1; max1 = s; i3 = i2; i2 = i1; i1 = i; }
+                else if (s > max2) { max3 = max2; max2 = s; i3 = i2; i2 = i; }
+                else if (s > max3) { max3 = s; i3 = i; }
+            }
+            if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { i2 = -1; i3 = -1; }
+            else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { i3 = -1; }
+            keep_bin[0] = i1; keep_bin[1] = i2; keep_bin[2] = i3;
+        }
+        __syncthreads();
+    }
+    int mine = 0;
+    for (int q = tid; q < nq; q += kSearchThreads) {                         // :625-627 and the count
+        int m = m12[q];
+        if (m >= 0 && a.check_ori) {
+            const int bq = bin[q];
+            if (bq != keep_bin[0] && bq != keep_bin[1] && bq != keep_bin[2]) { m = -1; m12[q] = -1; }
+        }
+        if (m >= 0) {
+            prev[2 * q] = __ldg(&k2[m].x);
+            prev[2 * q + 1] = __ldg(&k2[m].y);
+            ++mine;
+        }
+    }
+    mine = __reduce_add_sync(0xFFFFFFFFu, mine);
+    if (lane == 0 && mine) atomicAdd(&total, mine);
+    __syncthreads();
+    if (tid == 0) a.nmatches[p] = total;
+}
+
 // -------------------------------------------------------------------------------------------------- SearchByBoW
 // src/ORBmatcher.cc:270-404 (key frame against a frame) and :635-768 (key frame against key frame) over flattened
 // DBoW2 feature vectors.  A feature sits in exactly one vocabulary node, so the reference's one sequential rule -- a
@@ -807,18 +841,17 @@ void launch_area_query(const gforb_keypoint* keys, const float* bounds, const in
     area_query_kernel<<<(nq + 7) / 8, 256, 0, s>>>(keys, g, static_cast<const AreaQuery*>(queries), nq, out_count, out_start, out_idx);
 }
 
-size_t init_search_smem(int n1cap, int n2cap) { return (size_t)n2cap * 4 + (size_t)n1cap * 8 + (size_t)n1cap + 16; }
-
 int launch_init_search(const InitSearchArgs& a, const float* bounds, int npairs, cudaStream_t s) {
     InitSearchArgs b = a;
     b.min_x = bounds[0]; b.min_y = bounds[2];
     b.w_inv = 64.0f / (bounds[1] - bounds[0]); b.h_inv = 48.0f / (bounds[3] - bounds[2]);
-    const int n1cap = std::max(a.n1 ? a.stride1 : a.n1_fixed, 1), n2cap = std::max(a.n2 ? a.stride2 : a.n2_fixed, 1);
-    const size_t smem = init_search_smem(n1cap, n2cap);
+    const int qcap = std::max(a.n1 ? a.stride1 : a.n1_fixed, 1);
+    init_scan_kernel<<<dim3((qcap + 7) / 8, npairs), 256, 0, s>>>(b);
+    const int topk = qcap <= 4096 ? kTopK : kTopK / 2;
+    const size_t smem = (size_t)qcap * topk * 4 + (4u << kPosBits);
     static size_t have[64] = {};
-    if (opt_in_smem(init_search_kernel, smem, have)) return -1;
-    init_scan_kernel<<<dim3((n1cap + 7) / 8, npairs), 256, 0, s>>>(b);
-    init_search_kernel<<<npairs, kSearchThreads, smem, s>>>(b, n1cap, n2cap);
+    if (opt_in_smem(init_resolve_kernel, smem, have)) return -1;
+    init_resolve_kernel<<<npairs, kSearchThreads, smem, s>>>(b, topk, qcap);
     return 0;
 }
 

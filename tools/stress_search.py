@@ -53,5 +53,20 @@ for c in range(CASES // 2):
     got = gf.ORBmatcher(0.6, ori).SearchForTriangulation(*t[:10], t[10], t[11], t[12], t[13], t[14], 50)
     if not (got[0] == want[0] and np.array_equal(got[1], want[1])):
         print("MISMATCH triangulation", c, n1, n2, nodes); bad += 1
+from test_oracle_grid import _pair
+ninit = 0
+for c in range(CASES // 2):
+    n1 = int(rng.choice([60, 400, 1000, 2500, 5000, 8192])); n2 = int(rng.choice([60, 400, 1000, 2500, 5000, 8192]))
+    r2 = np.random.default_rng(40_000 + c)
+    k1, d1, k2, d2 = _pair(r2, n1, n2, flip=float(rng.choice([0.03, 0.06, 0.12])), p0=float(rng.choice([0.3, 0.6, 1.0])))
+    prev = np.stack([k1["x"], k1["y"]], axis=1).astype(np.float32)
+    win = int(rng.choice([10, 30, 100, 400])); ratio = float(rng.choice([0.6, 0.9, 0.95])); ori = bool(c & 1)
+    wn, wm12, wprev = O.search_for_initialization(k1, d1, k2, d2, B, prev, win, ratio, ori)
+    gp = prev.copy()
+    gn, gm12 = gf.ORBmatcher(ratio, ori).SearchForInitialization(k1, d1, k2, d2, gp, win, bounds=B)
+    ninit += 1
+    if not (gn == wn and np.array_equal(gm12, wm12) and np.array_equal(gp, wprev)):
+        print("MISMATCH init", c, n1, n2, win, ratio); bad += 1
+print("init cases:", ninit)
 print("stress:", CASES, "projection +", CASES // 2, "bow +", CASES // 2, "triangulation cases,", bad, "mismatches")
 sys.exit(1 if bad else 0)
