@@ -596,35 +596,35 @@ int gforb_search_for_initialization(gforb_matcher* m, const gforb_frame_bounds* 
     }
     *nmatches = 0;
     if (n1 == 0) return check_bounds(bounds, "gforb_search_for_initialization");
-    const size_t k1b = al16((size_t)n1 * sizeof(gforb_keypoint)), k2b = al16((size_t)std::max(n2, 1) * sizeof(gforb_keypoint));
-    const size_t d1b = al16((size_t)n1 * 32), d2b = al16((size_t)std::max(n2, 1) * 32), pb = al16((size_t)n1 * 8), mb = al16((size_t)n1 * 4);
-    int rc = m->reserve(m->io, m->io_bytes, k1b + k2b + d1b + d2b + pb + mb + 16);
+    // inputs packed into one pinned block (one H2D), outputs into another (one D2H); vbPrevMatched is in both
+    struct Seg { const void* src; size_t bytes, off; };
+    Seg in[5] = {{keys1, (size_t)n1 * sizeof(gforb_keypoint), 0}, {desc1, (size_t)n1 * 32, 0}, {keys2, (size_t)n2 * sizeof(gforb_keypoint), 0},
+                 {desc2, (size_t)n2 * 32, 0}, {prev_xy, (size_t)n1 * 8, 0}};
+    size_t total = 0;
+    for (Seg& g : in) { g.off = total; total += al16(std::max<size_t>(g.bytes, 16)); }
+    const size_t in_bytes = total, om = total, on = om + al16((size_t)n1 * 4);
+    total = on + 16;
+    int rc = m->reserve(m->io, m->io_bytes, total);
     if (rc) return rc;
-    uint8_t* base = static_cast<uint8_t*>(m->io);
-    gforb_keypoint* dk1 = reinterpret_cast<gforb_keypoint*>(base);
-    gforb_keypoint* dk2 = reinterpret_cast<gforb_keypoint*>(base + k1b);
-    uint8_t* dd1 = base + k1b + k2b;
-    uint8_t* dd2 = dd1 + d1b;
-    float* dp = reinterpret_cast<float*>(dd2 + d2b);
-    int32_t* dm = reinterpret_cast<int32_t*>(dd2 + d2b + pb);
-    int32_t* dn = reinterpret_cast<int32_t*>(dd2 + d2b + pb + mb);
+    rc = m->reserve_pin(total);
+    if (rc) return rc;
+    uint8_t* dev = static_cast<uint8_t*>(m->io);
+    uint8_t* pin = static_cast<uint8_t*>(m->pin);
+    for (const Seg& g : in)
+        if (g.bytes) std::memcpy(pin + g.off, g.src, g.bytes);
     cudaStream_t s = m->stream;
-    M_CUDA(cudaMemcpyAsync(dk1, keys1, (size_t)n1 * sizeof(gforb_keypoint), cudaMemcpyHostToDevice, s));
-    M_CUDA(cudaMemcpyAsync(dd1, desc1, (size_t)n1 * 32, cudaMemcpyHostToDevice, s));
-    M_CUDA(cudaMemcpyAsync(dp, prev_xy, (size_t)n1 * 8, cudaMemcpyHostToDevice, s));
-    if (n2 > 0) {
-        M_CUDA(cudaMemcpyAsync(dk2, keys2, (size_t)n2 * sizeof(gforb_keypoint), cudaMemcpyHostToDevice, s));
-        M_CUDA(cudaMemcpyAsync(dd2, desc2, (size_t)n2 * 32, cudaMemcpyHostToDevice, s));
-    }
-    rc = gforb_search_for_initialization_batch_device(m, bounds, 1, dk1, dd1, nullptr, n1, dk2, dd2, nullptr, n2, dp, window_size,
-                                                      check_orientation, dm, dn, nullptr);
+    M_CUDA(cudaMemcpyAsync(dev, pin, in_bytes, cudaMemcpyHostToDevice, s));
+    float* dp = reinterpret_cast<float*>(dev + in[4].off);
+    rc = gforb_search_for_initialization_batch_device(m, bounds, 1, reinterpret_cast<gforb_keypoint*>(dev + in[0].off), dev + in[1].off,
+                                                      nullptr, n1, reinterpret_cast<gforb_keypoint*>(dev + in[2].off), dev + in[3].off,
+                                                      nullptr, n2, dp, window_size, check_orientation,
+                                                      reinterpret_cast<int32_t*>(dev + om), reinterpret_cast<int32_t*>(dev + on), nullptr);
     if (rc) return rc;
-    int32_t nm = 0;
-    M_CUDA(cudaMemcpyAsync(matches12, dm, (size_t)n1 * 4, cudaMemcpyDeviceToHost, s));
-    M_CUDA(cudaMemcpyAsync(prev_xy, dp, (size_t)n1 * 8, cudaMemcpyDeviceToHost, s));
-    M_CUDA(cudaMemcpyAsync(&nm, dn, 4, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaMemcpyAsync(pin + in[4].off, dp, total - in[4].off, cudaMemcpyDeviceToHost, s));       // prev_xy | matches12 | nmatches
     M_CUDA(cudaStreamSynchronize(s));
-    *nmatches = nm;
+    std::memcpy(prev_xy, pin + in[4].off, (size_t)n1 * 8);
+    std::memcpy(matches12, pin + om, (size_t)n1 * 4);
+    *nmatches = *reinterpret_cast<const int32_t*>(pin + on);
     return GFORB_OK;
 }
 
