@@ -183,8 +183,8 @@ area_query_kernel(const gforb_keypoint* __restrict__ keys, GridView g, const Are
 //                        current claims stays valid), then the replay resumes.  What a query took stays in slot 0 of
 //                        its list; key indices, holders (atomicMax = last taker), scores, rotation bins, histogram,
 //                        three maxima and removal are written afterwards by all threads.
-// Measured (B200, 1,008 keys x 1,008 queries, last-frame form): 256 frames per launch 0.37-0.40 ms = 640-690 k frames/s;
-// one frame 55-96 us (grid 7, scan 15, resolve 33-70) against 0.55 ms for the sequential CPU oracle.
+// Measured (B200, 1,008 keys x 1,008 queries, last-frame form): 256 frames per launch 0.24-0.27 ms = 0.96-1.07 M frames/s;
+// one frame 48-83 us (grid 7, scan 10, resolve 30-65) against 0.55 ms for the sequential CPU oracle.
 namespace {
 constexpr int kTopK = 8;
 constexpr int kLvlBits = 6;                                     // levels < 64
@@ -205,38 +205,69 @@ __device__ __forceinline__ void proj_scan(const GridView& g, const gforb_keypoin
     const bool gate = (q.flags & GFORB_PQ_RIGHT_GATE) && u_right;
     int x0, x1, y0, y1;
     if (area_window(g, q.x, q.y, q.r, x0, x1, y0, y1)) {
-        int off = 0;                                  // entries dealt so far: the window's entries go round the lanes
-        for (int ix = x0; ix <= x1; ++ix) {           // across its columns, so no lane holds more than its share
-            const int j0 = __ldg(g.start + ix * kGRows + y0), j1 = __ldg(g.start + ix * kGRows + y1 + 1);
-            for (int j = j0 + ((lane - off) & 31); j < j1; j += 32) {
-                const int i = __ldg(g.idx + j);
-                if (!area_accepts(keys, i, q.x, q.y, q.r, q.min_level, q.max_level)) continue;
-                if (blocked && blocked[kByPos ? j : i]) continue;                      // :197-199, :1519-1521, :1662
-                if (gate) {                                                            // :201-206, :1523-1529
-                    const float ur = __ldg(u_right + i);
-                    if (ur > 0.0f && fabsf(__fsub_rn(q.xr, ur)) > q.r) continue;
-                }
-                if (q.flags & GFORB_PQ_REPROJ_GATE) {                                  // ORBmatcher::Fuse, :1022-1046
-                    const float ex = __fsub_rn(q.x, __ldg(&keys[i].x)), ey = __fsub_rn(q.y, __ldg(&keys[i].y));
-                    const float inv = inv_sig2[__ldg(&keys[i].octave) & 31];
-                    const float ur = u_right ? __ldg(u_right + i) : -1.0f;
-                    float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
-                    if (ur >= 0.0f) {
-                        const float er = __fsub_rn(q.xr, ur);
-                        e2 = __fadd_rn(e2, __fmul_rn(er, er));
-                        if ((double)__fmul_rn(e2, inv) > 7.8) continue;
-                    } else if ((double)__fmul_rn(e2, inv) > 5.99) continue;
-                }
-                const int dist = hamming256(a0, a1, __ldg(desc + 2 * (size_t)i), __ldg(desc + 2 * (size_t)i + 1));
-                if (dist >= 256 && !keep_all) continue;                                // never below the initial 256
-                if (cdist && (int)cdist[j] <= dist) continue;                          // vMatchedDistance[i2] <= dist, :559-560
-                const uint32_t key = ((uint32_t)dist << kDistShift) | ((uint32_t)j << kLvlBits) |
-                                     ((uint32_t)__ldg(&keys[i].octave) & ((1u << kLvlBits) - 1));
-                ++cnt;
-                second = min(second, max(best, key));
-                best = min(best, key);
+        // The window's columns are CSR runs [j0, j0 + len); all of them (<= 64) are fetched at once, two per lane, and
+        // the entries of all runs are dealt round the lanes as ONE sequence t = 0 .. total-1 (column by binary search
+        // in the prefix sums, via shuffles), so the warp walks ceil(total / 32) steps instead of one step per column.
+        const int ncol = x1 - x0 + 1;
+        int j0a = 0, lena = 0, j0b = 0, lenb = 0;
+        if (lane < ncol) {
+            j0a = __ldg(g.start + (x0 + lane) * kGRows + y0);
+            lena = __ldg(g.start + (x0 + lane) * kGRows + y1 + 1) - j0a;
+        }
+        if (lane + 32 < ncol) {
+            j0b = __ldg(g.start + (x0 + lane + 32) * kGRows + y0);
+            lenb = __ldg(g.start + (x0 + lane + 32) * kGRows + y1 + 1) - j0b;
+        }
+        int pa = lena, pb = lenb;                     // inclusive prefix sums of the run lengths
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int va = __shfl_up_sync(0xFFFFFFFFu, pa, o), vb = __shfl_up_sync(0xFFFFFFFFu, pb, o);
+            if (lane >= o) { pa += va; pb += vb; }
+        }
+        const int tot_a = __shfl_sync(0xFFFFFFFFu, pa, 31);
+        pb += tot_a;
+        const int total = __shfl_sync(0xFFFFFFFFu, pb, 31);
+        for (int tb = 0; tb < total; tb += 32) {
+            const int t = tb + lane;
+            int ca = 0, cb = 0;                       // first column whose inclusive prefix exceeds t, in each half
+#pragma unroll
+            for (int step = 16; step > 0; step >>= 1) {
+                const int va = __shfl_sync(0xFFFFFFFFu, pa, ca + step - 1), vb = __shfl_sync(0xFFFFFFFFu, pb, cb + step - 1);
+                if (va <= t) ca += step;
+                if (vb <= t) cb += step;
             }
-            off = (off + j1 - j0) & 31;
+            const bool in_a = t < tot_a;
+            const int src = in_a ? ca : min(cb, 31);
+            const int ra = __shfl_sync(0xFFFFFFFFu, j0a + lena - pa, src);          // j0 - exclusive prefix of the run
+            const int rb = __shfl_sync(0xFFFFFFFFu, j0b + lenb - pb, src);
+            if (t >= total) continue;
+            const int j = (in_a ? ra : rb) + t;
+            const int i = __ldg(g.idx + j);
+            if (!area_accepts(keys, i, q.x, q.y, q.r, q.min_level, q.max_level)) continue;
+            if (blocked && blocked[kByPos ? j : i]) continue;                      // :197-199, :1519-1521, :1662
+            if (gate) {                                                            // :201-206, :1523-1529
+                const float ur = __ldg(u_right + i);
+                if (ur > 0.0f && fabsf(__fsub_rn(q.xr, ur)) > q.r) continue;
+            }
+            if (q.flags & GFORB_PQ_REPROJ_GATE) {                                  // ORBmatcher::Fuse, :1022-1046
+                const float ex = __fsub_rn(q.x, __ldg(&keys[i].x)), ey = __fsub_rn(q.y, __ldg(&keys[i].y));
+                const float inv = inv_sig2[__ldg(&keys[i].octave) & 31];
+                const float ur = u_right ? __ldg(u_right + i) : -1.0f;
+                float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                if (ur >= 0.0f) {
+                    const float er = __fsub_rn(q.xr, ur);
+                    e2 = __fadd_rn(e2, __fmul_rn(er, er));
+                    if ((double)__fmul_rn(e2, inv) > 7.8) continue;
+                } else if ((double)__fmul_rn(e2, inv) > 5.99) continue;
+            }
+            const int dist = hamming256(a0, a1, __ldg(desc + 2 * (size_t)i), __ldg(desc + 2 * (size_t)i + 1));
+            if (dist >= 256 && !keep_all) continue;                                // never below the initial 256
+            if (cdist && (int)cdist[j] <= dist) continue;                          // vMatchedDistance[i2] <= dist, :559-560
+            const uint32_t key = ((uint32_t)dist << kDistShift) | ((uint32_t)j << kLvlBits) |
+                                 ((uint32_t)__ldg(&keys[i].octave) & ((1u << kLvlBits) - 1));
+            ++cnt;
+            second = min(second, max(best, key));
+            best = min(best, key);
         }
     }
     // the warp's kTopK smallest, popped from the lanes' two smallest; a lane that gave both and had seen more may hide
