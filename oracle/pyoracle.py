@@ -24,12 +24,50 @@ class StereoParams(C.Structure):
                 ("th_high", C.c_int), ("th_low", C.c_int), ("min_x", C.c_float)]
 
 
+_VARIANT = "oracle"     # "oracle" = the restatement; "ref" / "ref_native" = the reference's own code (oracle/pyref.py)
+REFERENCE_ROOT = Path("/root/reference")
+
+
 def build(force=False):
-    so = _HERE / "_build" / "libgforb_oracle.so"
-    if force or not so.exists():
-        subprocess.check_call(["make", "-C", str(_HERE)] + (["-B"] if force else []),
+    if _VARIANT == "oracle":
+        so = _HERE / "_build" / "libgforb_oracle.so"
+        if force or not so.exists():
+            subprocess.check_call(["make", "-C", str(_HERE)] + (["-B"] if force else []),
+                                  stdout=subprocess.DEVNULL)
+        return so
+    # oracle/_ref: compiled from the reference sources where they lie; only the prebuilt files exist on the GPU box
+    so = _HERE / "_ref" / f"libgforb_{_VARIANT}.so"
+    if (force or not so.exists()) and REFERENCE_ROOT.exists():
+        subprocess.check_call(["make", "-C", str(_HERE), "ref"] + (["-B"] if force else []),
                               stdout=subprocess.DEVNULL)
+    if not so.exists():
+        raise FileNotFoundError(f"{so} is missing and {REFERENCE_ROOT} is not here to build it from")
     return so
+
+
+class _Partial:
+    """ctypes library view that tolerates entry points a variant does not export (the reference build has no
+    counterpart for the restatement-only helpers); touching a missing one raises AttributeError on use."""
+
+    def __init__(self, cdll):
+        object.__setattr__(self, "_cdll", cdll)
+
+    def __getattr__(self, name):
+        try:
+            return getattr(self._cdll, name)
+        except AttributeError:
+            if _VARIANT == "oracle":
+                raise
+            return _Missing(name)
+
+
+class _Missing:
+    def __init__(self, name):
+        self.name = name
+        self.argtypes = self.restype = None
+
+    def __call__(self, *a):
+        raise AttributeError(f"{self.name} is not exported by the '{_VARIANT}' library")
 
 
 def lib():
@@ -42,6 +80,7 @@ def lib():
     except OSError:
         so = build(force=True)
         L = C.CDLL(str(so))
+    L = _Partial(L)
     u8p, ip, fp = C.c_void_p, C.c_void_p, C.c_void_p
     sz = C.c_size_t
     L.orc_cv_round_f.argtypes = [C.c_float]; L.orc_cv_round_f.restype = C.c_int
@@ -107,6 +146,13 @@ def lib():
     L.orc_undistort_points.argtypes = [fp, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, fp]
     L.orc_undistort_points.restype = None
     L.orc_distinctive_descriptors.argtypes = [u8p, ip, C.c_int, ip, ip]; L.orc_distinctive_descriptors.restype = None
+    if _VARIANT != "oracle":
+        L.ref_stereo_match_undistorted_mp.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(StereoParams), C.c_void_p, C.c_int,
+                                                      u8p, C.c_void_p, C.c_int, u8p, fp, fp, fp]
+        L.ref_stereo_match_undistorted_mp.restype = C.c_int
+        L.ref_search_by_projection_mp.argtypes = [C.c_void_p, u8p, fp, ip, C.c_int, fp, fp, C.c_int, u8p, u8p, ip, fp, fp,
+                                                  fp, fp, ip, u8p, C.c_int, C.c_float, C.c_float, ip, ip]
+        L.ref_search_by_projection_mp.restype = C.c_int
     _LIB = L
     return L
 
@@ -416,3 +462,13 @@ def search_for_triangulation(k1, d1, valid1, stereo1, fv1, k2, d2, valid2, stere
                                             _p(v2), _p(s2), len(k2), _p(i2), _p(t2), _p(x2), len(i2), _p(F), float(ex), float(ey),
                                             _p(sf), _p(sg), int(th_low), int(bool(check_ori)), _p(m12))
     return nm, m12[:len(k1)]
+
+
+def monotonic_new(on):
+    """Reference builds only (oracle/pyref.py): strictly increasing operator-new addresses inside the entry points,
+    which turns the reference's address-ordered quadtree ties (src/ORBextractor.cc:591,684) into a function of the
+    input; see oracle/ref_shim/mono_new.cpp."""
+    L = lib()
+    L.ref_monotonic_new.argtypes = [C.c_int]
+    L.ref_monotonic_new.restype = None
+    L.ref_monotonic_new(int(bool(on)))
