@@ -255,7 +255,7 @@ static int stereo_run(const orc_extractor* exL, const orc_extractor* exR, const 
     memcpy(uRight, F.mvuRight.data(), (size_t)nL * 4);
     memcpy(depth, F.mvDepth.data(), (size_t)nL * 4);
     if (p->mode == 0) {
-        for (int i = 0; i < nL; ++i) ret += uRight[i] >= 0;      // the classic form returns void; count as the oracle does
+        for (int i = 0; i < nL; ++i) ret += depth[i] > 0;        // the classic form returns void; count as the oracle does
     }
     return ret;
 }
