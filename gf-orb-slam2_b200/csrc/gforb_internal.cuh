@@ -1,5 +1,6 @@
 // gforb internal declarations shared by the host engine and the sm_100a kernels.
 #pragma once
+#include <mutex>
 #include <cuda.h>
 #include <cuda_runtime.h>
 
@@ -216,12 +217,20 @@ size_t octree_smem_bytes(const Geom& g);
 int fast_configure(const Geom& g);     // opt in to the FAST kernel's dynamic smem; returns cudaError_t as int
 int octree_configure(const Geom& g);   // opt in to large dynamic smem; returns cudaError_t as int
 
-// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is per device: remember the opted-in size per (kernel, device), not
-// per process (one process may drive several devices).  `have` is a zero-initialised static of the call site.
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is per device and is a SET, not a raise: the opted-in size is kept
+// as a high-water mark per (kernel, device) -- `have` is a zero-initialised static of the call site -- so that a second
+// engine with a smaller footprint (another nfeatures, another image size) never lowers it under a live engine's
+// launches.  The table is shared by every handle and handles are used from concurrent host threads (the reference's
+// two-thread fork/join, src/Frame.cc:84-87): check-and-raise runs under one mutex.
+inline std::mutex& smem_opt_in_mutex() {
+    static std::mutex m;
+    return m;
+}
 template <class K>
 inline int opt_in_smem(K kernel, size_t smem, size_t (&have)[64]) {
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    std::lock_guard<std::mutex> lock(smem_opt_in_mutex());
     if (smem <= have[dev]) return 0;
     if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
     have[dev] = smem;

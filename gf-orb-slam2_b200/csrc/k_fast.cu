@@ -355,8 +355,8 @@ size_t fast_cta_smem(const FastLayout& f) { return (size_t)kWarpsPerCta * f.warp
 }  // namespace
 
 int fast_configure(const Geom& g) {
-    return (int)cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)fast_cta_smem(fast_smem_layout(g)));
+    static size_t have[64] = {};       // high-water mark: engines of different footprints share the kernel symbol
+    return opt_in_smem(fast_cells_kernel, fast_cta_smem(fast_smem_layout(g)), have) ? (int)cudaErrorInvalidValue : 0;
 }
 
 void launch_fast(const Geom& g, const TileMaps& m, const Buffers& b, int nimg, cudaStream_t s) {

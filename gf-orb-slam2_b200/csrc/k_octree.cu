@@ -344,8 +344,8 @@ octree_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_
 }
 
 int octree_configure(const Geom& g) {
-    return (int)cudaFuncSetAttribute(octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)octree_smem_bytes(g));
+    static size_t have[64] = {};       // high-water mark: engines of different footprints share the kernel symbol
+    return opt_in_smem(octree_kernel, octree_smem_bytes(g), have) ? (int)cudaErrorInvalidValue : 0;
 }
 
 void launch_octree(const Geom& g, const Buffers& b, int nimg, cudaStream_t s) {
