@@ -2,16 +2,24 @@
 // Frame::ComputeStereoMatches_Undistorted + PrepareStereoCandidates (src/Frame.cc:1167-1316,
 // include/Frame.h:230-263), with ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1768-1784) as __popc.
 //
-// kSlices CTAs per stereo frame (left keys are dealt round-robin to the slices; the last CTA of a frame to
-// finish -- ticket counter -- applies the median cut).  The reference builds a per-row table of right keys and scans it per left key;
-// since "best" is the lexicographic minimum of (Hamming distance, right index) over the gated candidates
-// (strict '<' while walking ascending iR), the table is replaced by a gate test of every right key
-// (row band, octave +-1, uR window) and a warp-wide packed-min reduction -- order-free and deterministic.
-// Right-key gate data sits in shared memory; descriptors are 2 x 128-bit loads per side.
-// Refinement (classic mode): 11x11 SAD at 11 shifts on the un-blurred pyramids at the LEFT key's octave,
-// exact in integers (the reference's float sums are integer-valued), parabola in un-fused float ops.
-// The median cut needs only the value of the (n/2)-th smallest distance: rank selection in shared memory.
+// kSlices CTAs per stereo frame, adjacent in the grid so that they share the frame's keys in L2.  A slice owns the LEFT
+// keys of one band of image rows.  The reference builds a per-row table of right keys and walks it per left key; since
+// "best" is the lexicographic minimum of (Hamming distance, right index) over the gated candidates (strict '<' while
+// walking ascending iR), no table and no sort are needed:
+//   phase 0  the slice compacts into shared memory the right keys whose row range [minr, maxr] meets its band
+//            (gate record + descriptor, ~1/6 of the frame's keys) and the indices of its own left keys;
+//   phase A  ONE THREAD PER LEFT KEY walks the compacted right keys: every lane reads the same shared-memory record
+//            (broadcast), tests its own key against it (row, octave +-1, uR window) and keeps a packed minimum -- 32
+//            searches in flight per warp and no global load inside the loop;
+//   phase B  (classic mode) the 11x11 / 11x21 patches of up to kTile matched keys are staged in shared memory with
+//            aligned 32-bit loads, all issued before any is consumed; the 11-shift SAD then runs one thread per
+//            (key, shift) out of shared memory, exact in integers (the reference's float sums are integer-valued), and
+//            one thread per key fits the parabola in un-fused float ops;
+//   phase C  the last slice of a frame to finish (ticket) applies the median cut: only the value of the (n/2)-th
+//            smallest distance matters -> radix selection in shared memory.
 // INT/LSU-bound.
+#include <algorithm>
+
 #include "gforb_internal.cuh"
 
 namespace gforb {
@@ -25,25 +33,36 @@ constexpr int kT = 256;
 #define GFORB_ST_MINB 4
 #endif
 constexpr int kSlices = GFORB_ST_SLICES;
-struct RKey { short minr, maxr; uint32_t oi; float x; };   // oi = octave << 16 | original index
+constexpr int kChunk = 512;          // right keys held in shared memory at a time (a band of a 1000-key frame needs ~170)
+constexpr int kTile = 46;            // matched keys whose patches are staged together: 46 * 11 shifts = 506 of 512 SAD tasks
+constexpr int kRowWords = 10;        // staged words per patch row: 4 (11 left bytes + alignment) + 6 (21 right bytes + alignment)
+constexpr int kKeyWords = 11 * kRowWords;
 
-__device__ __forceinline__ int hamming_u4(const uint4 a0, const uint4 a1, const uint8_t* b) {
-    const uint4 b0 = __ldg(reinterpret_cast<const uint4*>(b));
-    const uint4 b1 = __ldg(reinterpret_cast<const uint4*>(b) + 1);
+struct RGate { int rows; uint32_t oi; float x; int pad; };   // rows = minr | maxr << 16, oi = octave << 16 | original index
+struct TileKey {                                            // one matched left key of the current SAD tile
+    const uint8_t* pl; const uint8_t* pr;                   // word-aligned addresses of the top-left staged words
+    float uL, scaleduR0, minD, maxD;
+    int iL, level, phL, phR;                                // phX = byte offset of the first patch pixel inside the first staged word
+};
+
+__device__ __forceinline__ int hamming_s(const uint4 a0, const uint4 a1, const uint4 b0, const uint4 b1) {
     return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
            __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
-// (PTX vabsdiff.s32.add is emulated with 64-bit arithmetic on sm_100a, ~9 SASS instructions: the SAD uses IABS)
-__device__ __forceinline__ RKey make_rkey(const gforb_keypoint& k, int i, const float* scale, int nRows) {
-    const float r = __fmul_rn(2.0f, scale[k.octave]);
-    float hi = ceilf(__fadd_rn(k.y, r)), lo = floorf(__fsub_rn(k.y, r));
-    hi = fminf(hi, (float)(nRows - 1));   // classic reference indexes unclamped (keys sit >= 19*scale inside)
+// row range of a right key in the reference's row table (:906-916 / Frame.h:246-257); the classic reference indexes
+// unclamped (keys sit >= 19*scale inside), the restatement clamps, and so does this
+__device__ __forceinline__ void row_range(float y, float scale_oct, int nRows, int& minr, int& maxr) {
+    const float r = __fmul_rn(2.0f, scale_oct);
+    float hi = ceilf(__fadd_rn(y, r)), lo = floorf(__fsub_rn(y, r));
+    hi = fminf(hi, (float)(nRows - 1));
     lo = fmaxf(lo, 0.0f);
-    RKey q;
-    q.minr = (short)(int)lo; q.maxr = (short)(int)hi; q.oi = ((uint32_t)k.octave << 16) | (uint32_t)i; q.x = k.x;
-    return q;
+    minr = (int)lo; maxr = (int)hi;
 }
-__device__ __forceinline__ int row_bin(float y, int nRows) { return min(max((int)floorf(y), 0), nRows - 1); }
+// slice that owns a left key: the band its row (int)vL falls in, out-of-image rows going to the first / last band
+__device__ __forceinline__ int slice_of(float vL, int bandRows) {
+    const float c = fminf(fmaxf(vL, 0.f), 65535.f);
+    return min((int)c / bandRows, kSlices - 1);
+}
 
 // k-th smallest (0-based) of the non-negative entries of d[0..n) that are < 2^16, by two 256-bin histogram passes.
 // All kT threads call it; hist = 256 ints of shared memory; s_tmp = 2 ints.
@@ -88,18 +107,27 @@ __device__ int select_kth(const int* d, int n, int k, int* hist, int* s_tmp) {
 }  // namespace
 
 __global__ void __launch_bounds__(kT, GFORB_ST_MINB)
-stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K, int band) {
+stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
-    // [rs: K sorted right keys][binstart: nRows + 1][s_dist: K (aliases rs once the matching is done)]
-    RKey* rs = reinterpret_cast<RKey*>(smem_raw);
-    int* binstart = reinterpret_cast<int*>(smem_raw + sizeof(RKey) * (size_t)K);
+    // [gate: kChunk x 16 B][rdesc: kChunk x 32 B]   (phase 0 / A)
+    //   aliased by [stage: kTile x 110 words][sad: kTile x 11][tkey: kTile]   (phase B)
+    //   aliased by [s_dist: K ints]                                          (phase C)
+    // [s_best: K][s_left: K ushort][s_match: K ushort]
+    RGate* gate = reinterpret_cast<RGate*>(smem_raw);
+    uint4* rdesc = reinterpret_cast<uint4*>(smem_raw + sizeof(RGate) * kChunk);
+    uint32_t* stage = reinterpret_cast<uint32_t*>(smem_raw);
+    int* s_sad = reinterpret_cast<int*>(smem_raw + 4 * kTile * kKeyWords);
+    TileKey* tkey = reinterpret_cast<TileKey*>(smem_raw + 4 * kTile * kKeyWords + 4 * kTile * 11 + 8);
     int* s_dist = reinterpret_cast<int*>(smem_raw);
+    const size_t shared_area = max((size_t)kChunk * 48, max((size_t)K * 4, (size_t)4 * kTile * kKeyWords + 4 * kTile * 11 + 8 + sizeof(TileKey) * kTile));
+    uint32_t* s_best = reinterpret_cast<uint32_t*>(smem_raw + ((shared_area + 15) & ~(size_t)15));
+    uint16_t* s_left = reinterpret_cast<uint16_t*>(s_best + K);
+    uint16_t* s_match = s_left + K;
     __shared__ int s_hist[256];
     __shared__ int s_tmp[2];
-    __shared__ int s_cnt, s_removed, s_processed, s_last;
+    __shared__ int s_cnt, s_removed, s_processed, s_last, s_nleft, s_nright, s_nmatch;
 
-    const int f = v.f0 + blockIdx.x, slice = blockIdx.y;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int slice = blockIdx.x, f = v.f0 + blockIdx.y;
     const gforb_keypoint* kL = v.kL + (size_t)f * v.k_stride;
     const gforb_keypoint* kR = v.kR + (size_t)f * v.k_stride;
     const uint8_t* dL = v.dL + (size_t)f * v.k_stride * 32;
@@ -115,162 +143,223 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K, int band
     const bool classic = prm.mode == GFORB_STEREO_CLASSIC;
     const int th_high = prm.th_high, thOrbDist = (prm.th_high + prm.th_low) / 2;
     const int nRows = v.nRows;
-
-    // ---- right keys sorted by centre row (counting sort): a left key then scans only rows row-band .. row+band.
-    // The reference's per-row candidate table (:906-916 / Frame.h:246-257) holds key i on rows minr..maxr with
-    // |row - y| < 2*scale + 1, so the centre-row window is a superset and the exact gate test below decides.
-    for (int i = threadIdx.x; i <= nRows; i += kT) binstart[i] = 0;
-    if (threadIdx.x == 0) { s_cnt = 0; s_removed = 0; s_processed = 0; }
-    __syncthreads();
-    for (int i = threadIdx.x; i < nR; i += kT) atomicAdd(&binstart[row_bin(kR[i].y, nRows) + 1], 1);
-    __syncthreads();
-    {   // inclusive scan of binstart[1..nRows] (binstart[0] = 0): contiguous chunk per thread + block scan of chunk sums
-        const int per = (nRows + kT - 1) / kT, b0 = 1 + threadIdx.x * per, b1 = min(b0 + per, nRows + 1);
-        int sum = 0;
-        for (int i = b0; i < b1; ++i) sum += binstart[i];
-        int inc = sum;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += t;
-        }
-        if (lane == 31) s_hist[warp] = inc;
-        __syncthreads();
-        int base = 0;
-        for (int w = 0; w < warp; ++w) base += s_hist[w];
-        int run = base + inc - sum;
-        for (int i = b0; i < b1; ++i) { run += binstart[i]; binstart[i] = run; }
-        __syncthreads();
-    }
-    // scatter from the back of each bin: binstart[b + 1] is decremented down to the bin's start, i.e. afterwards
-    // binstart[b + 1] = first slot of bin b  ->  shift the view by one: bin b occupies [bs[b + 1], bs[b + 2])
-    for (int i = threadIdx.x; i < nR; i += kT) {
-        const gforb_keypoint k = kR[i];
-        const int slot = atomicSub(&binstart[row_bin(k.y, nRows) + 1], 1) - 1;
-        rs[slot] = make_rkey(k, i, v.scale, nRows);
-    }
-    __syncthreads();
-    // now bin b = [binstart[b + 1], b + 1 < nRows ? binstart[b + 2] : nR)
-
+    const int bandRows = (nRows + kSlices - 1) / kSlices;
+    const int bandLo = slice * bandRows, bandHi = min(bandLo + bandRows, nRows) - 1;    // rows a valid left key of this slice can have
     const float minZ = prm.b;
-    for (int iL = slice + kSlices * warp; iL < nL; iL += kSlices * (kT / 32)) {
-        const gforb_keypoint kp = kL[iL];
-        float minD = 0.f, maxD = __fdiv_rn(prm.bf, minZ);
-        const float vL = kp.y, uL = kp.x;
-        const int levelL = kp.octave;
-        float out_u = -1.f, out_z = -1.f;
-        int out_bd = th_high, out_bi = -1, out_sad = -1, out_dist = -1;
-        bool processed = false;
+    const float maxD0 = __fdiv_rn(prm.bf, minZ);
+    constexpr uint32_t kAny = 0x80000000u;      // s_best bit 31: some right key's row range holds this key's row
 
-        bool ok = classic ? true : !(vL < 0 || vL > (float)(nRows - 1));
-        const int row = (int)vL;
-        ok = ok && row >= 0 && row < nRows;
-        if (!classic && v.min_d != nullptr && v.max_d != nullptr) { minD = v.min_d[iL]; maxD = v.max_d[iL]; }
-        const float minU = __fsub_rn(uL, maxD), maxU = __fsub_rn(uL, minD);
+    if (threadIdx.x == 0) { s_cnt = 0; s_removed = 0; s_processed = 0; s_nleft = 0; s_nright = 0; s_nmatch = 0; }
+    __syncthreads();
 
-        if (ok) {
+    // ---- phase 0a: the left keys of this band
+    for (int i = threadIdx.x; i < nL; i += kT) {
+        if (slice_of(kL[i].y, bandRows) == slice) {
+            const int slot = atomicAdd(&s_nleft, 1);
+            s_left[slot] = (uint16_t)i;
+            s_best[slot] = ((uint32_t)th_high << 16) | 0xFFFFu;
+        }
+    }
+    __syncthreads();
+    const int nleft = s_nleft;
+
+    // ---- phase 0b + A, one chunk of right keys at a time (one chunk in practice)
+    for (int r0 = 0; r0 < nR; ) {
+        // compact right keys [r0, ...) whose row range meets the band until the chunk is full
+        int scanned_to = r0;
+        for (; scanned_to < nR; scanned_to += kT) {
+            if (s_nright > kChunk - kT) break;                     // uniform: read after the barrier below
+            const int i = scanned_to + threadIdx.x;
+            if (i < nR) {
+                const gforb_keypoint k = kR[i];
+                int minr, maxr;
+                row_range(k.y, v.scale[k.octave], nRows, minr, maxr);
+                if (maxr >= bandLo && minr <= bandHi) {
+                    const int slot = atomicAdd(&s_nright, 1);
+                    RGate g;
+                    g.rows = minr | (maxr << 16); g.oi = ((uint32_t)k.octave << 16) | (uint32_t)i; g.x = k.x; g.pad = 0;
+                    gate[slot] = g;
+                    const uint4* src = reinterpret_cast<const uint4*>(dR + (size_t)i * 32);
+                    rdesc[2 * slot] = __ldg(src);
+                    rdesc[2 * slot + 1] = __ldg(src + 1);
+                }
+            }
+            __syncthreads();
+        }
+        __syncthreads();
+        const int nright = s_nright;
+        r0 = scanned_to;
+
+        // one thread per left key of the band
+        for (int t = threadIdx.x; t < nleft; t += kT) {
+            const int iL = s_left[t];
+            const gforb_keypoint kp = kL[iL];
+            const float vL = kp.y, uL = kp.x;
+            const int levelL = kp.octave;
+            bool ok = classic ? true : !(vL < 0 || vL > (float)(nRows - 1));
+            const int row = (int)vL;
+            ok = ok && row >= 0 && row < nRows;
+            if (!ok) continue;
+            float minD = 0.f, maxD = maxD0;
+            if (!classic && v.min_d != nullptr && v.max_d != nullptr) { minD = v.min_d[iL]; maxD = v.max_d[iL]; }
+            const float minU = __fsub_rn(uL, maxD), maxU = __fsub_rn(uL, minD);
+            const bool range_ok = classic ? !(maxU < 0) : !(maxU < prm.min_x);
             const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(dL + (size_t)iL * 32));
             const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(dL + (size_t)iL * 32) + 1);
-            unsigned best = ((unsigned)th_high << 16) | 0xFFFFu;
-            bool any_row = false;
-            const bool range_ok = classic ? !(maxU < 0) : !(maxU < prm.min_x);
-            const int blo = max(row - band, 0), bhi = min(row + band, nRows - 1);
-            const int jend = bhi + 1 < nRows ? binstart[bhi + 2] : nR;
-            for (int j = binstart[blo + 1] + lane; j < jend; j += 32) {
-                const RKey q = rs[j];
-                if (row < q.minr || row > q.maxr) continue;
-                any_row = true;
+            uint32_t st = s_best[t];
+            uint32_t best = st & ~kAny, any = st & kAny;
+            for (int j = 0; j < nright; ++j) {
+                const RGate q = gate[j];                                         // broadcast
+                const int minr = q.rows & 0xFFFF, maxr = q.rows >> 16;
+                if (row < minr || row > maxr) continue;
+                any = kAny;
                 if (!range_ok) continue;
                 const int oct = (int)(q.oi >> 16);
                 if (oct < levelL - 1 || oct > levelL + 1) continue;
                 if (q.x >= minU && q.x <= maxU) {
-                    const int iR = (int)(q.oi & 0xFFFFu);
-                    const int d = hamming_u4(a0, a1, dR + (size_t)iR * 32);
-                    if (d < th_high) best = min(best, ((unsigned)d << 16) | (unsigned)iR);
+                    const int d = hamming_s(a0, a1, rdesc[2 * j], rdesc[2 * j + 1]);
+                    if (d < th_high) best = min(best, ((uint32_t)d << 16) | (q.oi & 0xFFFFu));
                 }
             }
-            any_row = __any_sync(0xffffffffu, any_row);
-            best = __reduce_min_sync(0xffffffffu, best);
-            const int bestDist = (int)(best >> 16), bestIdx = (int)(best & 0xFFFFu);
-            if (any_row && range_ok) {
-                processed = true;
-                if (bestDist < th_high) { out_bd = bestDist; out_bi = bestIdx; }
-                if (bestDist < thOrbDist) {
-                    if (!classic) {
-                        float bestuR = kR[bestIdx].x;
-                        float disparity = __fsub_rn(uL, bestuR);
-                        if (disparity >= minD && disparity < maxD) {
-                            if (disparity <= 0) { disparity = 0.01f; bestuR = (float)((double)uL - 0.01); }
-                            out_z = __fdiv_rn(prm.bf, disparity);
-                            out_u = bestuR;
-                            out_dist = bestDist;
-                        }
-                    } else {
-                        // ---- 11x11 SAD slide at the left key's octave (:976-1029) ----
-                        const float uR0 = kR[bestIdx].x;
-                        const float sf = v.inv_scale[levelL];
-                        const float scaleduL = roundf(__fmul_rn(uL, sf));
-                        const float scaledvL = roundf(__fmul_rn(vL, sf));
-                        const float scaleduR0 = roundf(__fmul_rn(uR0, sf));
-                        const float iniu = scaleduR0 + 5.f - 5.f, endu = scaleduR0 + 5.f + 5.f + 1.f;
-                        if (!(iniu < 0 || endu >= (float)v.w[levelL])) {
-                            const int pitch = v.pitch[levelL];
-                            const int cu = (int)scaleduL, cv = (int)scaledvL, cr = (int)scaleduR0;
-                            const uint8_t* pL = v.pyrL[levelL] + (size_t)f * v.frame_stride[levelL] + (ptrdiff_t)cv * pitch + cu;
-                            const uint8_t* pR = v.pyrR[levelL] + (size_t)f * v.frame_stride[levelL] + (ptrdiff_t)cv * pitch + cr;
-                            const int cL = __ldg(pL);
-                            int acc[11], dlt[11];      // dlt[s] = (right centre at shift s) - (left centre)
+            s_best[t] = best | any;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) s_nright = 0;
+        __syncthreads();
+    }
+
+    // ---- results of the search; classic mode queues the keys that go on to the SAD refinement
+    for (int t = threadIdx.x; t < nleft; t += kT) {
+        const int iL = s_left[t];
+        const gforb_keypoint kp = kL[iL];
+        const float vL = kp.y, uL = kp.x;
+        bool ok = classic ? true : !(vL < 0 || vL > (float)(nRows - 1));
+        const int row = (int)vL;
+        ok = ok && row >= 0 && row < nRows;
+        float minD = 0.f, maxD = maxD0;
+        if (!classic && v.min_d != nullptr && v.max_d != nullptr) { minD = v.min_d[iL]; maxD = v.max_d[iL]; }
+        const float maxU = __fsub_rn(uL, minD);
+        const bool range_ok = classic ? !(maxU < 0) : !(maxU < prm.min_x);
+        const uint32_t st = s_best[t];
+        const int bestDist = (int)((st & ~kAny) >> 16), bestIdx = (int)(st & 0xFFFFu);
+        float out_u = -1.f, out_z = -1.f;
+        int out_bd = th_high, out_bi = -1, out_dist = -1;
+        if (ok && (st & kAny) && range_ok) {
+            atomicAdd(&s_processed, 1);
+            if (bestDist < th_high) { out_bd = bestDist; out_bi = bestIdx; }
+            if (bestDist < thOrbDist) {
+                if (!classic) {
+                    float bestuR = kR[bestIdx].x;
+                    float disparity = __fsub_rn(uL, bestuR);
+                    if (disparity >= minD && disparity < maxD) {
+                        if (disparity <= 0) { disparity = 0.01f; bestuR = (float)((double)uL - 0.01); }
+                        out_z = __fdiv_rn(prm.bf, disparity);
+                        out_u = bestuR;
+                        out_dist = bestDist;
+                    }
+                } else {
+                    s_match[atomicAdd(&s_nmatch, 1)] = (uint16_t)t;
+                }
+            }
+        }
+        uright[iL] = out_u; depth[iL] = out_z;
+        o_bd[iL] = out_bd; o_bi[iL] = out_bi; o_sad[iL] = -1;
+        o_cut[iL] = out_dist;
+    }
+    __syncthreads();
+
+    // ---- phase B: 11x11 SAD slide at the left key's octave (:976-1029), kTile keys at a time
+    const int nmatch = classic ? s_nmatch : 0;
+    for (int m0 = 0; m0 < nmatch; m0 += kTile) {
+        const int nt = min(kTile, nmatch - m0);
+        if (threadIdx.x < nt) {
+            const int t = s_match[m0 + threadIdx.x];
+            const int iL = s_left[t];
+            const gforb_keypoint kp = kL[iL];
+            const int bestIdx = (int)(s_best[t] & 0xFFFFu);
+            const int levelL = kp.octave;
+            const float uR0 = kR[bestIdx].x;
+            const float sf = v.inv_scale[levelL];
+            const float scaleduL = roundf(__fmul_rn(kp.x, sf));
+            const float scaledvL = roundf(__fmul_rn(kp.y, sf));
+            const float scaleduR0 = roundf(__fmul_rn(uR0, sf));
+            const float iniu = scaleduR0 + 5.f - 5.f, endu = scaleduR0 + 5.f + 5.f + 1.f;
+            TileKey tk;
+            tk.iL = iL; tk.level = levelL; tk.uL = kp.x; tk.scaleduR0 = scaleduR0; tk.minD = 0.f; tk.maxD = maxD0;
+            tk.pl = nullptr; tk.pr = nullptr; tk.phL = 0; tk.phR = 0;
+            if (!(iniu < 0 || endu >= (float)v.w[levelL])) {
+                const int pitch = v.pitch[levelL];
+                const int cu = (int)scaleduL, cv = (int)scaledvL, cr = (int)scaleduR0;
+                const uint8_t* pL = v.pyrL[levelL] + (size_t)f * v.frame_stride[levelL] + (ptrdiff_t)(cv - 5) * pitch + (cu - 5);
+                const uint8_t* pR = v.pyrR[levelL] + (size_t)f * v.frame_stride[levelL] + (ptrdiff_t)(cv - 5) * pitch + (cr - 10);
+                tk.phL = (int)((uintptr_t)pL & 3); tk.phR = (int)((uintptr_t)pR & 3);
+                tk.pl = pL - tk.phL; tk.pr = pR - tk.phR;
+            }
+            tkey[threadIdx.x] = tk;
+        }
+        __syncthreads();
+        // stage: every load of the tile is independent of every other
+        for (int idx = threadIdx.x; idx < nt * kKeyWords; idx += kT) {
+            const int k = idx / kKeyWords, rem = idx - k * kKeyWords;
+            const int rowi = rem / kRowWords, wd = rem - rowi * kRowWords;
+            const TileKey& tk = tkey[k];
+            if (tk.pl == nullptr) continue;
+            const int pitch = v.pitch[tk.level];
+            const uint8_t* src = wd < 4 ? tk.pl + (ptrdiff_t)rowi * pitch + 4 * wd : tk.pr + (ptrdiff_t)rowi * pitch + 4 * (wd - 4);
+            stage[idx] = __ldg(reinterpret_cast<const uint32_t*>(src));
+        }
+        __syncthreads();
+        // one thread per (key, shift): |(L - cL) - (R_s - cR_s)| = |L + (cR_s - cL) - R_s| summed over the 11x11 window
+        for (int idx = threadIdx.x; idx < nt * 11; idx += kT) {
+            const int k = idx / 11, sft = idx - k * 11;
+            const TileKey& tk = tkey[k];
+            int acc = 0;
+            if (tk.pl != nullptr) {
+                const uint8_t* base = reinterpret_cast<const uint8_t*>(stage + k * kKeyWords);
+                const uint8_t* lb = base + tk.phL;
+                const uint8_t* rb = base + 16 + tk.phR + sft;
+                const int dlt = (int)rb[5 * 4 * kRowWords + 5] - (int)lb[5 * 4 * kRowWords + 5];
 #pragma unroll
-                            for (int s = 0; s < 11; ++s) { acc[s] = 0; dlt[s] = (int)__ldg(pR + s - 5) - cL; }
-                            for (int p = lane; p < 121; p += 32) {
-                                const int dy = p / 11 - 5, dx = p - (dy + 5) * 11 - 5;
-                                const int lpx = (int)__ldg(pL + dy * pitch + dx);
-                                const uint8_t* rrow = pR + dy * pitch + dx - 5;
-                                // |(L - cL) - (R - cR_s)| = |L + (cR_s - cL) - R|: IADD3 + IABS + IADD per pixel and shift
+                for (int dy = 0; dy < 11; ++dy) {
 #pragma unroll
-                                for (int s = 0; s < 11; ++s) acc[s] += abs(lpx + dlt[s] - (int)__ldg(rrow + s));
-                            }
-                            int bestSad = 0x7fffffff, bestInc = 0;
-                            float dists[11];
+                    for (int dx = 0; dx < 11; ++dx)
+                        acc += abs((int)lb[dy * 4 * kRowWords + dx] + dlt - (int)rb[dy * 4 * kRowWords + dx]);
+                }
+            }
+            s_sad[idx] = acc;
+        }
+        __syncthreads();
+        if (threadIdx.x < nt) {
+            const TileKey& tk = tkey[threadIdx.x];
+            if (tk.pl != nullptr) {
+                const int* sd = s_sad + threadIdx.x * 11;
+                int bestSad = 0x7fffffff, bestInc = 0;
 #pragma unroll
-                            for (int s = 0; s < 11; ++s) {
-                                const int t = __reduce_add_sync(0xffffffffu, acc[s]);
-                                dists[s] = (float)t;
-                                if (t < bestSad) { bestSad = t; bestInc = s - 5; }
-                            }
-                            if (bestInc != -5 && bestInc != 5) {
-                                float d1 = 0, d2 = 0, d3 = 0;
-#pragma unroll
-                                for (int s = 1; s < 10; ++s)
-                                    if (s == bestInc + 5) { d1 = dists[s - 1]; d2 = dists[s]; d3 = dists[s + 1]; }
-                                const float deltaR = __fdiv_rn(__fsub_rn(d1, d3),
-                                    __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1, d3), __fmul_rn(2.0f, d2))));
-                                if (!(deltaR < -1 || deltaR > 1)) {
-                                    float bestuR = __fmul_rn(v.scale[levelL],
-                                        __fadd_rn(__fadd_rn(scaleduR0, (float)bestInc), deltaR));
-                                    float disparity = __fsub_rn(uL, bestuR);
-                                    if (disparity >= minD && disparity < maxD) {
-                                        if (disparity <= 0) { disparity = 0.01f; bestuR = (float)((double)uL - 0.01); }
-                                        out_z = __fdiv_rn(prm.bf, disparity);
-                                        out_u = bestuR;
-                                        out_sad = bestSad;
-                                        out_dist = bestSad;
-                                    }
-                                }
-                            }
+                for (int s2 = 0; s2 < 11; ++s2) {
+                    const int t2 = sd[s2];
+                    if (t2 < bestSad) { bestSad = t2; bestInc = s2 - 5; }
+                }
+                if (bestInc != -5 && bestInc != 5) {
+                    const float d1 = (float)sd[bestInc + 4], d2 = (float)sd[bestInc + 5], d3 = (float)sd[bestInc + 6];
+                    const float deltaR = __fdiv_rn(__fsub_rn(d1, d3),
+                        __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1, d3), __fmul_rn(2.0f, d2))));
+                    if (!(deltaR < -1 || deltaR > 1)) {
+                        float bestuR = __fmul_rn(v.scale[tk.level], __fadd_rn(__fadd_rn(tk.scaleduR0, (float)bestInc), deltaR));
+                        float disparity = __fsub_rn(tk.uL, bestuR);
+                        if (disparity >= tk.minD && disparity < tk.maxD) {
+                            if (disparity <= 0) { disparity = 0.01f; bestuR = (float)((double)tk.uL - 0.01); }
+                            depth[tk.iL] = __fdiv_rn(prm.bf, disparity);
+                            uright[tk.iL] = bestuR;
+                            o_sad[tk.iL] = bestSad;
+                            o_cut[tk.iL] = bestSad;
                         }
                     }
                 }
             }
         }
-        if (lane == 0) {
-            uright[iL] = out_u; depth[iL] = out_z;
-            o_bd[iL] = out_bd; o_bi[iL] = out_bi; o_sad[iL] = out_sad;
-            o_cut[iL] = out_dist;
-            if (processed) atomicAdd(&s_processed, 1);
-        }
+        __syncthreads();
     }
-    __syncthreads();
+
     // ---- frame-level hand-off: the last slice to arrive owns the median cut ----
     if (threadIdx.x == 0) {
         if (s_processed) atomicAdd(&v.proc_count[f], s_processed);
@@ -289,7 +378,7 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K, int band
     __syncthreads();
 
     // ---- median cut (:1064-1077 / :1291-1313): drop matches with dist >= 1.5*1.4*median ----
-    // only the value of the (n/2)-th smallest distance matters: radix selection (SAD <= 121*255 < 2^16)
+    // only the value of the (n/2)-th smallest distance matters: radix selection (SAD <= 121*510 < 2^16)
     const int n = s_cnt;
     if (n > 0) {
         const int median = select_kth(s_dist, nL, n / 2, s_hist, s_tmp);
@@ -311,15 +400,18 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K, int band
     }
 }
 
+size_t stereo_smem_bytes(int K) {
+    size_t shared_area = (size_t)kChunk * 48;
+    shared_area = std::max(shared_area, (size_t)K * 4);
+    shared_area = std::max(shared_area, (size_t)4 * kTile * kKeyWords + 4 * kTile * 11 + 8 + sizeof(TileKey) * kTile);
+    return ((shared_area + 15) & ~(size_t)15) + (size_t)K * 4 + (size_t)K * 2 * 2;
+}
+
 void launch_stereo(const StereoView& v, const gforb_stereo_params& p, int nframes, int K, cudaStream_t s) {
-    const size_t smem = sizeof(RKey) * (size_t)K + sizeof(int) * ((size_t)v.nRows + 2);
+    const size_t smem = stereo_smem_bytes(K);
     static size_t configured[64] = {};
     if (smem > 48 * 1024) opt_in_smem(stereo_kernel, smem, configured);
-    // centre-row window that covers every band: |row - y| < 2*scale + 1  =>  |row - floor(y)| < 2*scale + 2
-    float smax = 1.f;
-    for (int l = 0; l < kMaxLevels; ++l) smax = v.scale[l] > smax ? v.scale[l] : smax;
-    const int band = (int)(2.f * smax) + 3;
-    stereo_kernel<<<dim3(nframes, kSlices), kT, smem, s>>>(v, p, K, band);
+    stereo_kernel<<<dim3(kSlices, nframes), kT, smem, s>>>(v, p, K);
 }
 
 }  // namespace gforb
