@@ -25,7 +25,11 @@
 namespace gforb {
 
 namespace {
-constexpr int kT = 256;
+#ifndef GFORB_ST_THREADS
+#define GFORB_ST_THREADS 256
+#endif
+constexpr int kT = GFORB_ST_THREADS;
+constexpr int kWarps = kT / 32;
 #ifndef GFORB_ST_SLICES
 #define GFORB_ST_SLICES 8
 #endif
@@ -70,7 +74,7 @@ __device__ int select_kth(const int* d, int n, int k, int* hist, int* s_tmp) {
     int prefix = 0;
     for (int pass = 0; pass < 2; ++pass) {
         const int shift = pass ? 0 : 8;
-        hist[threadIdx.x] = 0;
+        for (int i = threadIdx.x; i < 256; i += kT) hist[i] = 0;
         __syncthreads();
         for (int i = threadIdx.x; i < n; i += kT) {
             const int e = d[i];
@@ -121,7 +125,9 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
     int* s_dist = reinterpret_cast<int*>(smem_raw);
     const size_t shared_area = max((size_t)kChunk * 48, max((size_t)K * 4, (size_t)4 * kTile * kKeyWords + 4 * kTile * 11 + 8 + sizeof(TileKey) * kTile));
     uint32_t* s_best = reinterpret_cast<uint32_t*>(smem_raw + ((shared_area + 15) & ~(size_t)15));
-    uint16_t* s_left = reinterpret_cast<uint16_t*>(s_best + K);
+    int* s_bin = reinterpret_cast<int*>(s_best + K);          // bandRows + 2 counters of the left-key counting sort
+    uint16_t* s_wlist = reinterpret_cast<uint16_t*>(s_bin + ((v.nRows + kSlices - 1) / kSlices + 2));   // kWarps x kChunk
+    uint16_t* s_left = s_wlist + kWarps * kChunk;
     uint16_t* s_match = s_left + K;
     __shared__ int s_hist[256];
     __shared__ int s_tmp[2];
@@ -152,10 +158,35 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
     if (threadIdx.x == 0) { s_cnt = 0; s_removed = 0; s_processed = 0; s_nleft = 0; s_nright = 0; s_nmatch = 0; }
     __syncthreads();
 
-    // ---- phase 0a: the left keys of this band
+    // ---- phase 0a: the left keys of this band, counting-sorted by row so that the 32 keys of a warp span few rows
+    for (int i = threadIdx.x; i <= bandRows; i += kT) s_bin[i] = 0;
+    __syncthreads();
     for (int i = threadIdx.x; i < nL; i += kT) {
-        if (slice_of(kL[i].y, bandRows) == slice) {
-            const int slot = atomicAdd(&s_nleft, 1);
+        const float y = kL[i].y;
+        if (slice_of(y, bandRows) == slice) atomicAdd(&s_bin[min(max((int)y - bandLo, 0), bandRows - 1) + 1], 1);
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) {                                  // inclusive scan of s_bin[1..bandRows] by one warp
+        int carry = 0;
+        for (int b0 = 1; b0 <= bandRows; b0 += 32) {
+            const int b = b0 + (int)threadIdx.x;
+            int x = b <= bandRows ? s_bin[b] : 0;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, x, o);
+                if ((int)threadIdx.x >= o) x += t;
+            }
+            if (b <= bandRows) s_bin[b] = x + carry;
+            carry += __shfl_sync(0xffffffffu, x, 31);
+        }
+        if (threadIdx.x == 0) s_nleft = carry;
+    }
+    __syncthreads();
+    // scatter from the back of each bin: afterwards s_bin[b + 1] = first slot of bin b
+    for (int i = threadIdx.x; i < nL; i += kT) {
+        const float y = kL[i].y;
+        if (slice_of(y, bandRows) == slice) {
+            const int slot = atomicSub(&s_bin[min(max((int)y - bandLo, 0), bandRows - 1) + 1], 1) - 1;
             s_left[slot] = (uint16_t)i;
             s_best[slot] = ((uint32_t)th_high << 16) | 0xFFFFu;
         }
@@ -168,7 +199,9 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
         // compact right keys [r0, ...) whose row range meets the band until the chunk is full
         int scanned_to = r0;
         for (; scanned_to < nR; scanned_to += kT) {
-            if (s_nright > kChunk - kT) break;                     // uniform: read after the barrier below
+            const int held = s_nright;
+            __syncthreads();                                       // every thread has read the count before anyone adds to it
+            if (held > kChunk - kT) break;
             const int i = scanned_to + threadIdx.x;
             if (i < nR) {
                 const gforb_keypoint k = kR[i];
@@ -190,38 +223,62 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
         const int nright = s_nright;
         r0 = scanned_to;
 
-        // one thread per left key of the band
-        for (int t = threadIdx.x; t < nleft; t += kT) {
-            const int iL = s_left[t];
-            const gforb_keypoint kp = kL[iL];
+        // one thread per left key of the band; a warp first lists the right keys whose rows meet ITS keys' rows
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        uint16_t* wl = s_wlist + warp * kChunk;
+        for (int t0 = warp * 32; t0 < nleft; t0 += kT) {
+            const int t = t0 + lane;
+            const bool have = t < nleft;
+            const int iL = have ? s_left[t] : 0;
+            gforb_keypoint kp;
+            kp.x = 0.f; kp.y = 0.f; kp.octave = 0;
+            if (have) kp = kL[iL];
             const float vL = kp.y, uL = kp.x;
             const int levelL = kp.octave;
             bool ok = classic ? true : !(vL < 0 || vL > (float)(nRows - 1));
             const int row = (int)vL;
-            ok = ok && row >= 0 && row < nRows;
-            if (!ok) continue;
-            float minD = 0.f, maxD = maxD0;
-            if (!classic && v.min_d != nullptr && v.max_d != nullptr) { minD = v.min_d[iL]; maxD = v.max_d[iL]; }
-            const float minU = __fsub_rn(uL, maxD), maxU = __fsub_rn(uL, minD);
-            const bool range_ok = classic ? !(maxU < 0) : !(maxU < prm.min_x);
-            const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(dL + (size_t)iL * 32));
-            const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(dL + (size_t)iL * 32) + 1);
-            uint32_t st = s_best[t];
-            uint32_t best = st & ~kAny, any = st & kAny;
-            for (int j = 0; j < nright; ++j) {
-                const RGate q = gate[j];                                         // broadcast
-                const int minr = q.rows & 0xFFFF, maxr = q.rows >> 16;
-                if (row < minr || row > maxr) continue;
-                any = kAny;
-                if (!range_ok) continue;
-                const int oct = (int)(q.oi >> 16);
-                if (oct < levelL - 1 || oct > levelL + 1) continue;
-                if (q.x >= minU && q.x <= maxU) {
-                    const int d = hamming_s(a0, a1, rdesc[2 * j], rdesc[2 * j + 1]);
-                    if (d < th_high) best = min(best, ((uint32_t)d << 16) | (q.oi & 0xFFFFu));
+            ok = have && ok && row >= 0 && row < nRows;
+            const int rlo = __reduce_min_sync(0xffffffffu, ok ? row : 0x7fffffff);
+            const int rhi = __reduce_max_sync(0xffffffffu, ok ? row : -1);
+            int cnt = 0;
+            for (int j0 = 0; j0 < nright; j0 += 32) {
+                const int j = j0 + lane;
+                bool hit = false;
+                if (j < nright) {
+                    const int rows = gate[j].rows;
+                    hit = (rows >> 16) >= rlo && (rows & 0xFFFF) <= rhi;
                 }
+                const unsigned m = __ballot_sync(0xffffffffu, hit);
+                if (hit) wl[cnt + __popc(m & ((1u << lane) - 1u))] = (uint16_t)j;
+                cnt += __popc(m);
             }
-            s_best[t] = best | any;
+            __syncwarp();
+            if (ok) {
+                float minD = 0.f, maxD = maxD0;
+                if (!classic && v.min_d != nullptr && v.max_d != nullptr) { minD = v.min_d[iL]; maxD = v.max_d[iL]; }
+                const float minU = __fsub_rn(uL, maxD), maxU = __fsub_rn(uL, minD);
+                const bool range_ok = classic ? !(maxU < 0) : !(maxU < prm.min_x);
+                const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(dL + (size_t)iL * 32));
+                const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(dL + (size_t)iL * 32) + 1);
+                const uint32_t st = s_best[t];
+                uint32_t best = st & ~kAny, any = st & kAny;
+                for (int jj = 0; jj < cnt; ++jj) {
+                    const int j = wl[jj];                                            // broadcast
+                    const RGate q = gate[j];                                         // broadcast
+                    const int minr = q.rows & 0xFFFF, maxr = q.rows >> 16;
+                    if (row < minr || row > maxr) continue;
+                    any = kAny;
+                    if (!range_ok) continue;
+                    const int oct = (int)(q.oi >> 16);
+                    if (oct < levelL - 1 || oct > levelL + 1) continue;
+                    if (q.x >= minU && q.x <= maxU) {
+                        const int d = hamming_s(a0, a1, rdesc[2 * j], rdesc[2 * j + 1]);
+                        if (d < th_high) best = min(best, ((uint32_t)d << 16) | (q.oi & 0xFFFFu));
+                    }
+                }
+                s_best[t] = best | any;
+            }
+            __syncwarp();
         }
         __syncthreads();
         if (threadIdx.x == 0) s_nright = 0;
@@ -298,15 +355,22 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
             tkey[threadIdx.x] = tk;
         }
         __syncthreads();
-        // stage: every load of the tile is independent of every other
-        for (int idx = threadIdx.x; idx < nt * kKeyWords; idx += kT) {
-            const int k = idx / kKeyWords, rem = idx - k * kKeyWords;
-            const int rowi = rem / kRowWords, wd = rem - rowi * kRowWords;
+        // stage: one thread per (key, patch row) issues that row's 4 + 6 aligned words; nothing waits on anything
+        for (int idx = threadIdx.x; idx < nt * 11; idx += kT) {
+            const int k = idx / 11, rowi = idx - k * 11;
             const TileKey& tk = tkey[k];
             if (tk.pl == nullptr) continue;
-            const int pitch = v.pitch[tk.level];
-            const uint8_t* src = wd < 4 ? tk.pl + (ptrdiff_t)rowi * pitch + 4 * wd : tk.pr + (ptrdiff_t)rowi * pitch + 4 * (wd - 4);
-            stage[idx] = __ldg(reinterpret_cast<const uint32_t*>(src));
+            const ptrdiff_t ro = (ptrdiff_t)rowi * v.pitch[tk.level];
+            const uint32_t* gl = reinterpret_cast<const uint32_t*>(tk.pl + ro);
+            const uint32_t* gr = reinterpret_cast<const uint32_t*>(tk.pr + ro);
+            uint32_t w[kRowWords];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) w[i] = __ldg(gl + i);
+#pragma unroll
+            for (int i = 0; i < 6; ++i) w[4 + i] = __ldg(gr + i);
+            uint32_t* dst = stage + k * kKeyWords + rowi * kRowWords;
+#pragma unroll
+            for (int i = 0; i < kRowWords; ++i) dst[i] = w[i];
         }
         __syncthreads();
         // one thread per (key, shift): |(L - cL) - (R_s - cR_s)| = |L + (cR_s - cL) - R_s| summed over the 11x11 window
@@ -400,15 +464,16 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
     }
 }
 
-size_t stereo_smem_bytes(int K) {
+size_t stereo_smem_bytes(int K, int nRows) {
     size_t shared_area = (size_t)kChunk * 48;
     shared_area = std::max(shared_area, (size_t)K * 4);
     shared_area = std::max(shared_area, (size_t)4 * kTile * kKeyWords + 4 * kTile * 11 + 8 + sizeof(TileKey) * kTile);
-    return ((shared_area + 15) & ~(size_t)15) + (size_t)K * 4 + (size_t)K * 2 * 2;
+    return ((shared_area + 15) & ~(size_t)15) + (size_t)K * 4 + 4 * ((size_t)(nRows + kSlices - 1) / kSlices + 2) +
+           (size_t)kWarps * kChunk * 2 + (size_t)K * 2 * 2;
 }
 
 void launch_stereo(const StereoView& v, const gforb_stereo_params& p, int nframes, int K, cudaStream_t s) {
-    const size_t smem = stereo_smem_bytes(K);
+    const size_t smem = stereo_smem_bytes(K, v.nRows);
     static size_t configured[64] = {};
     if (smem > 48 * 1024) opt_in_smem(stereo_kernel, smem, configured);
     stereo_kernel<<<dim3(kSlices, nframes), kT, smem, s>>>(v, p, K);
