@@ -1,18 +1,28 @@
 #!/usr/bin/env python3
-"""bench.py -- stereo frames/s of the ORB stereo front-end (extract L + extract R + ComputeStereoMatches)
-at 752x480, 1000 keypoints, 8 levels, scale 1.2, FAST 20/7 (BASELINE.json configs[1]).
+"""bench.py -- stereo frames/s of the ORB stereo front-end (extract L + extract R + ComputeStereoMatches).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--frames F] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--config C] [--frames F] [--impl reference]
 
-A step = one pass of the whole hot path over one batch of F synthetic stereo frames.
+A step = one pass of the whole hot path over one batch of F stereo frames; every step runs a DIFFERENT batch of
+distinct seeded frames (tools/synthgen.cu, seed = 1234 + global frame number), generated on the device before the clock
+starts.
+  --config 1      (default) BASELINE.json configs[1]: 752x480, 1000 kp, 8 levels, 1.2, FAST 20/7, classic stereo match
+           1euroc the same on the bundled EuRoC pair (tests/data/EuRoC_{l,r}.pgm = the reference's test/EuRoC_*.png)
+           2tum   configs[2]: the bundled TUM pair (512x512 as shipped)
+           2vga   configs[2]: synthetic 640x480 (the size BASELINE.json quotes for TUM)
+           2hd    configs[2]: synthetic 1280x720, 2000 kp, 256 stereo frames per step
+           4      configs[4]: 65,536 distinct synthetic 752x480 stereo frames in ONE pass, sharded over the ranks
+                  (strong scaling: --steps is derived, 65,536 / (N * F))
   value   : device-resident inputs, CUDA-event timed on the launching stream, max over ranks.
   e2e     : the same through the C ABI with HOST (pinned) buffers: H2D of the images and D2H of
-            keypoints/descriptors/uRight/depth inside the timed region (gforb_stereo_frames_batch).
-  roofline: dominant kernel (by measured per-stage CUDA-event time) vs the measured HBM copy peak.
-  cpu_baseline: the CPU oracle (a port of the reference algorithm; the reference itself cannot be built here)
-            on the box's host cores, bounded sample, rank 0 at N=1 only.
-Multi-GPU: frames are independent -> each rank runs its own F frames (weak scaling), no collective on the
-data path; torch.distributed only provides the barrier and the max-over-ranks of the device time.
+            keypoints/descriptors/uRight/depth inside the timed region (gforb_stereo_frames_batch_async).
+  roofline: dominant kernel (by measured per-stage CUDA-event time) vs the measured HBM copy peak, with the INT-issue
+            roofline beside it; every stage carries both fractions under `stages`.
+  cpu_baseline / --impl reference: the reference's own code (oracle/_ref: its ORBextractor.cc compiled unmodified +
+            Frame::ComputeStereoMatches lifted verbatim; kind "reference") on the box's host cores, bounded sample;
+            the oracle port (kind "port") only when oracle/_ref is absent.
+Multi-GPU: frames are independent -> each rank runs its own frames, no collective on the data path;
+torch.distributed only provides the barrier and the max-over-ranks of the device time.
 """
 import argparse
 import importlib
@@ -29,41 +39,57 @@ import numpy as np
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 sys.path.insert(0, str(ROOT / "tests"))
+sys.path.insert(0, str(ROOT / "tools"))
 
-W, H, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH = 752, 480, 1000, 1.2, 8, 20, 7
+SCALE, NLEVELS, INI_TH, MIN_TH = 1.2, 8, 20, 7
 BF = 47.90639384423901
 B = BF / 435.2046959714599
-METRIC = "stereo frames/s ORB extract+match @752x480x1000kp"
 UNIT = "stereo_frames/s"
-BASE_FRAMES = 16           # distinct generated stereo frames; the batch cycles them with shifts + fresh noise
+TAIL = "8 levels, 1.2, FAST 20/7, classic stereo match"
+CONFIGS = {
+    "1": dict(w=752, h=480, nfeat=1000, source="synthetic",
+              workload="configs[1]: 752x480 stereo pair, 1000 kp, " + TAIL),
+    "1euroc": dict(w=752, h=480, nfeat=1000, source="EuRoC",
+                   workload="configs[1] on the bundled test/EuRoC_l.png + EuRoC_r.png (one pair, replicated over the batch), 1000 kp, " + TAIL),
+    "2tum": dict(w=512, h=512, nfeat=1000, source="TUM",
+                 workload="configs[2]: bundled test/TUM_l.png + TUM_r.png (512x512 as shipped, one pair replicated over the batch), 1000 kp, " + TAIL),
+    "2vga": dict(w=640, h=480, nfeat=1000, source="synthetic",
+                 workload="configs[2]: synthetic 640x480 stereo frames (the size BASELINE.json quotes for TUM), 1000 kp, " + TAIL),
+    "2hd": dict(w=1280, h=720, nfeat=2000, source="synthetic",
+                workload="configs[2]: synthetic 1280x720 x 256 stereo frames, 2000 kp, " + TAIL),
+    "4": dict(w=752, h=480, nfeat=1000, source="synthetic", total_frames=65536,
+              workload="configs[4]: 65,536 distinct synthetic 752x480 stereo frames in one pass, frame-sharded, 1000 kp, " + TAIL),
+}
+INT_PEAK_GOPS_FALLBACK = 18400.0      # IADD3 / IMAD / VABSDIFF4 thread-ops per second, profiles/int_peaks_r1.json
+STAGE_CLASS = {"pyramid": "hbm", "fast": "hbm", "blur": "hbm", "describe": "int_issue", "stereo": "int_issue",
+               "quadtree": "latency"}      # SURVEY.md 8(d) "Which roofline"
 
 
-def make_frames(n, seed0=0):
-    """n distinct synthetic rectified stereo pairs (uint8 [n,H,W] x2)."""
-    from synth import synth_stereo
-    nb = min(n, BASE_FRAMES)
-    try:
-        from concurrent.futures import ProcessPoolExecutor
-        with ProcessPoolExecutor(max_workers=min(nb, os.cpu_count() or 1)) as ex:
-            base = list(ex.map(synth_stereo, range(seed0, seed0 + nb)))
-    except Exception:
-        base = [synth_stereo(seed0 + i) for i in range(nb)]
-    left = np.empty((n, H, W), np.uint8)
-    right = np.empty((n, H, W), np.uint8)
-    rng = np.random.default_rng(99 + seed0)
-    for i in range(n):
-        l, r = base[i % nb]
-        shift = 16 * (i // nb)
-        if shift:
-            l, r = np.roll(l, shift, axis=1), np.roll(r, shift, axis=1)
-            nz = rng.integers(-1, 2, (2, H, W), dtype=np.int16)
-            l = np.clip(l.astype(np.int16) + nz[0], 0, 255).astype(np.uint8)
-            r = np.clip(r.astype(np.int16) + nz[1], 0, 255).astype(np.uint8)
-        left[i], right[i] = l, r
-    return left, right
+def metric_name(cfg):
+    return f"stereo frames/s ORB extract+match @{cfg['w']}x{cfg['h']}x{cfg['nfeat']}kp"
 
 
-def algorithmic_bytes(level_sizes, n_cand, n_kp):
+def bundled_pair(name):
+    def pgm(path):
+        raw = Path(path).read_bytes()
+        parts = raw.split(None, 4)
+        assert parts[0] == b"P5" and parts[3] == b"255"
+        w, h = int(parts[1]), int(parts[2])
+        return np.frombuffer(raw[len(raw) - w * h:], np.uint8).reshape(h, w)
+    return pgm(ROOT / "tests" / "data" / f"{name}_l.pgm"), pgm(ROOT / "tests" / "data" / f"{name}_r.pgm")
+
+
+def host_sample(cfg, n, seed0=0):
+    """n stereo frames of the config's workload on the host (the CPU arm's input): the same bytes the device generator
+    writes for the same seeds, or the bundled pair."""
+    if cfg["source"] == "synthetic":
+        import synthgen
+        return synthgen.host_frames(seed0, n, cfg["w"], cfg["h"])
+    l, r = bundled_pair(cfg["source"])
+    return np.repeat(l[None], n, 0), np.repeat(r[None], n, 0)
+
+
+def algorithmic_bytes(W, H, level_sizes, n_cand, n_kp):
     """Per EYE image, SURVEY.md 8(d) (FAST survivors are 4 B packed here, not 8)."""
     P = sum(w * h for w, h in level_sizes)
     Ppad = sum((w + 38) * (h + 38) for w, h in level_sizes)
@@ -86,7 +112,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.QUERY}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -120,53 +146,77 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def cpu_baseline(left, right, threads, target_s=15.0):
-    """Oracle port on the host cores, 'all cores' shape: every worker runs whole stereo frames."""
-    from oracle import pyoracle as O
-    n = min(len(left), 8)
-    imgs = np.empty((2 * n, H, W), np.uint8)
+def cpu_model():
+    try:
+        for line in Path("/proc/cpuinfo").read_text().splitlines():
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except Exception:
+        pass
+    return "unknown"
+
+
+def cpu_arm():
+    """(module, kind, flags): the reference's own code when oracle/_ref was built (it travels prebuilt), else the port."""
+    from oracle import pyref
+    if (ROOT / "oracle" / "_ref" / "libgforb_ref.so").exists():
+        return pyref.load("ref"), "reference", ("oracle/_ref/libgforb_ref.so: the reference's src/ORBextractor.cc unmodified + Frame::ComputeStereoMatches "
+                                                "lifted verbatim, g++ -O3 -march=x86-64-v3 -ffp-contract=off (the prebuilt library has to run on whatever "
+                                                "host the snapshot lands on; the -march=native build timed within 1 % of it where both ran)")
+    from oracle import pyoracle
+    return pyoracle, "port", "oracle/_build/libgforb_oracle.so: CPU restatement, g++ -O3 -march=x86-64-v3 -ffp-contract=off"
+
+
+def cpu_baseline(cfg, left, right, threads, target_s=15.0):
+    """The CPU arm on the host cores, 'all cores' shape: every worker runs whole stereo frames."""
+    O, kind, flags = cpu_arm()
+    n = min(len(left), 16)
+    imgs = np.empty((2 * n, cfg["h"], cfg["w"]), np.uint8)
     imgs[0::2], imgs[1::2] = left[:n], right[:n]
-    secs, _ = O.bench_stereo(imgs, max(threads, 2), threads, 0, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, BF, B)
+    a = (cfg["nfeat"], SCALE, NLEVELS, INI_TH, MIN_TH, BF, B)
+    secs, _ = O.bench_stereo(imgs, max(threads, 2), threads, 0, *a)
     per_frame = secs / max(threads, 2) * threads            # thread-seconds per frame
-    nframes = int(max(threads * 2, min(4000, target_s * threads / max(per_frame, 1e-4))))
-    secs, chk = O.bench_stereo(imgs, nframes, threads, 0, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, BF, B)
-    return nframes / secs, nframes, secs, chk
+    nframes = int(max(threads * 2, min(8000, target_s * threads / max(per_frame, 1e-4))))
+    secs, chk = O.bench_stereo(imgs, nframes, threads, 0, *a)
+    return nframes / secs, nframes, secs, kind, flags, n
 
 
-def cpu_reference_shaped(left, right, nframes=48):
+def cpu_reference_shaped(cfg, left, right, nframes=48):
     """The reference's own shape (src/Frame.cc:268-282): one frame at a time, one thread per eye, serial match."""
-    from oracle import pyoracle as O
-    n = min(len(left), 8)
-    imgs = np.empty((2 * n, H, W), np.uint8)
+    O, _, _ = cpu_arm()
+    n = min(len(left), 16)
+    imgs = np.empty((2 * n, cfg["h"], cfg["w"]), np.uint8)
     imgs[0::2], imgs[1::2] = left[:n], right[:n]
-    secs, _ = O.bench_stereo(imgs, nframes, 2, 1, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, BF, B)
+    secs, _ = O.bench_stereo(imgs, nframes, 2, 1, cfg["nfeat"], SCALE, NLEVELS, INI_TH, MIN_TH, BF, B)
     return nframes / secs
 
 
-def run_reference(args, rank, world):
-    """--impl reference: the reference algorithm's CPU path (oracle port; OpenCV C++ is not in the image so the
-    reference's own sources cannot be compiled) on all host threads, same config/metric."""
+def run_reference(args, cfg, rank, world):
+    """--impl reference: the reference's CPU implementation of the path (oracle/_ref, see cpu_arm) on all host threads,
+    same config / metric; each step is a bounded sample of the workload."""
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    left, right = make_frames(8)
+    left, right = host_sample(cfg, 16)
     t0 = time.time()
     vals, total_frames = [], 0
-    # bounded sample per step so the whole run ends within minutes
     per_step_s = max(2.0, min(15.0, 150.0 / max(args.steps + args.warmup, 1)))
+    kind = flags = None
     for i in range(args.warmup + args.steps):
-        fps, nframes, secs, _ = cpu_baseline(left, right, threads, target_s=per_step_s)
+        fps, nframes, secs, kind, flags, ndistinct = cpu_baseline(cfg, left, right, threads, target_s=per_step_s)
         if i >= args.warmup:
             vals.append((nframes, secs)); total_frames += nframes
     tot_s = sum(s for _, s in vals)
     value = total_frames / tot_s
-    sample = f"{total_frames} synthetic 752x480 stereo frames over {args.steps} steps, {threads} threads"
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+    sample = (f"{total_frames} stereo frames over {args.steps} steps ({ndistinct} distinct {cfg['w']}x{cfg['h']} frames of the workload, "
+              f"cycled), {threads} threads each running whole frames")
+    line = {"impl": "reference", "metric": metric_name(cfg), "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1000.0 * tot_s / max(args.steps, 1), "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "configs[1]: 752x480 stereo pair, 1000 kp, 8 levels, 1.2, FAST 20/7, classic stereo match",
-                       "frames_per_step": total_frames // max(args.steps, 1)},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "scaling": "strong" if "total_frames" in cfg else "weak", "vs_baseline": None, "dtype": "u8",
+            "data": "synthetic" if cfg["source"] == "synthetic" else "bundled",
+            "config": {"workload": cfg["workload"], "frames_per_step": total_frames // max(args.steps, 1)},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample,
+                             "cpu_model": cpu_model(), "build": flags},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": time.time() - t0}
     emit(line)
@@ -227,22 +277,26 @@ def emit(line):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--config", default="1", choices=sorted(CONFIGS))
     ap.add_argument("--frames", type=int, default=256, help="stereo frames per step per GPU")
+    ap.add_argument("--pool", type=int, default=8, help="distinct batches kept resident and cycled by the steps")
     ap.add_argument("--impl", default="gforb", choices=["gforb", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--chunk", type=int, default=0, help="frames per pipeline chunk of the end-to-end arm")
     args = ap.parse_args()
     quiet_stdout()
-    args.warmup = max(args.warmup, 3) if args.impl == "gforb" else args.warmup
+    cfg = CONFIGS[args.config]
+    W, H, NFEAT = cfg["w"], cfg["h"], cfg["nfeat"]
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
-        run_reference(args, rank, world)
+        run_reference(args, cfg, rank, world)
         return 0
+    args.warmup = max(args.warmup, 3)
 
     import torch
     import torch.distributed as dist
@@ -254,10 +308,18 @@ def main():
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     gf = importlib.import_module("gf-orb-slam2_b200")
-    from sharding import aggregate_throughput
+    from sharding import aggregate_throughput, frame_shard
 
     F = args.frames
-    left, right = make_frames(F, seed0=1000 * rank)
+    strong = "total_frames" in cfg
+    if strong:                                      # configs[4]: one pass over this rank's shard of the 65,536 frames
+        lo, hi = frame_shard(cfg["total_frames"], rank, world)
+        NB = (hi - lo) // F
+        args.steps = NB
+        seed_base = lo
+    else:
+        NB = max(1, args.pool) if cfg["source"] == "synthetic" else 1
+        seed_base = rank * NB * F
     full_affinity = os.sched_getaffinity(0)
     numa_node = bind_to_gpu_numa_node(local_rank)     # before the pinned buffers are allocated
     sb = gf.StereoBatch(W, H, F, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH)
@@ -265,19 +327,31 @@ def main():
     torch.cuda.set_stream(stream)
     sb.set_stream(stream.cuda_stream)
     out = sb.alloc_outputs(F)                       # pinned
-    pin_l = gf.PinnedArray((F, H, W), np.uint8); pin_r = gf.PinnedArray((F, H, W), np.uint8)
-    pin_l.array[:] = left; pin_r.array[:] = right
+
+    # ---------------- the frames: NB distinct batches resident in HBM, gforb_batch's layout (image 2f = left, 2f+1 = right)
+    pool = torch.empty((NB, 2 * F, H, W), dtype=torch.uint8, device="cuda")
+    if cfg["source"] == "synthetic":
+        import synthgen
+        for bidx in range(NB):
+            synthgen.device_batch_input(seed_base + bidx * F, F, W, H, pool[bidx].data_ptr(), stream.cuda_stream)
+    else:
+        l, r = bundled_pair(cfg["source"])
+        pool[0, 0::2] = torch.from_numpy(l.copy()).cuda()
+        pool[0, 1::2] = torch.from_numpy(r.copy()).cuda()
+    torch.cuda.synchronize()
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---------------- device-resident arm ----------------
-    sb.upload(pin_l.array, pin_r.array)
-    torch.cuda.synchronize()
-    for _ in range(args.warmup):
+    def run_step(i):
+        sb.set_device_input(pool[i % NB].data_ptr())
         sb.run(F, BF, B)
+
+    # ---------------- device-resident arm ----------------
+    for i in range(args.warmup):
+        run_step(i)
     sb.sync()
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -285,8 +359,8 @@ def main():
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
-    for _ in range(args.steps):
-        sb.run(F, BF, B)
+    for i in range(args.steps):
+        run_step(i)
     e1.record(stream)
     barrier()
     sb.sync()
@@ -299,26 +373,35 @@ def main():
     # ---------------- per-stage times (same stream, CUDA events between the stages) ----------------
     sb.stage_timing(True)
     acc = {}
-    for _ in range(max(3, min(args.steps, 10))):
-        sb.run(F, BF, B)
+    for i in range(max(3, min(args.steps, 10))):
+        run_step(i)
         for k, v in sb.stage_times().items():
             acc.setdefault(k, []).append(v)
     sb.stage_timing(False)
     stage_ms = {k: float(np.mean(v)) for k, v in acc.items()}
+    sb.set_device_input(None)
 
     # ---------------- end-to-end arm: host buffers in, host buffers out ----------------
+    NBH = min(NB, 8)                                 # pinned host copies of the first NBH batches, cycled by the steps
+    pin_l = gf.PinnedArray((NBH, F, H, W), np.uint8); pin_r = gf.PinnedArray((NBH, F, H, W), np.uint8)
+    for bidx in range(NBH):
+        pin_l.array[bidx] = pool[bidx, 0::2].cpu().numpy(); pin_r.array[bidx] = pool[bidx, 1::2].cpu().numpy()
+    frame0 = (pin_l.array[0, 0].copy(), pin_r.array[0, 0].copy())
+    del pool
+    torch.cuda.empty_cache()
     sb.set_chunk(args.chunk)
-    for _ in range(2):
-        sb.process(pin_l.array, pin_r.array, out, BF, B)
+    for i in range(2):
+        sb.process(pin_l.array[i % NBH], pin_r.array[i % NBH], out, BF, B)
+    e2e_steps = min(args.steps, 64)
     barrier()
     e0.record(stream)
-    for _ in range(args.steps):
-        sb.process(pin_l.array, pin_r.array, out, BF, B)
+    for i in range(e2e_steps):
+        sb.process(pin_l.array[i % NBH], pin_r.array[i % NBH], out, BF, B)
     e1.record(stream)
     barrier()
     ms2 = torch.tensor([e0.elapsed_time(e1)], device="cuda")
-    launches_e2e = sb.last_launches() * args.steps
-    e2e_blocking = aggregate_throughput(F, args.steps, ms2, world, dist)
+    launches_e2e = sb.last_launches() * e2e_steps
+    e2e_blocking = aggregate_throughput(F, e2e_steps, ms2, world, dist)
 
     # ---------------- end-to-end arm, streaming form: two batch handles used alternately ----------------
     # gforb_stereo_frames_batch_async: step i is submitted on handle i % 2 after that handle's previous step has
@@ -331,20 +414,19 @@ def main():
     out2 = sb2.alloc_outputs(F)
     hs, outs = (sb, sb2), (out, out2)
     for i in range(4):
-        hs[i % 2].sync(); hs[i % 2].submit(pin_l.array, pin_r.array, outs[i % 2], BF, B)
+        hs[i % 2].sync(); hs[i % 2].submit(pin_l.array[i % NBH], pin_r.array[i % NBH], outs[i % 2], BF, B)
     sb.sync(); sb2.sync()
     barrier()
     t_e2e = time.perf_counter()
     e0.record(stream)
-    for i in range(args.steps):
-        hs[i % 2].sync(); hs[i % 2].submit(pin_l.array, pin_r.array, outs[i % 2], BF, B)
+    for i in range(e2e_steps):
+        hs[i % 2].sync(); hs[i % 2].submit(pin_l.array[i % NBH], pin_r.array[i % NBH], outs[i % 2], BF, B)
     sb2.sync(); sb.sync()              # sb last: its stream carries e1
     e1.record(stream)
     barrier()
     wall_ms = (time.perf_counter() - t_e2e) * 1e3
     ms3 = torch.tensor([max(e0.elapsed_time(e1), 0.0)], device="cuda")
-    e2e_value = aggregate_throughput(F, args.steps, ms3, world, dist)
-    assert np.array_equal(out["counts"], out2["counts"]) and np.array_equal(out["depth"], out2["depth"])
+    e2e_value = aggregate_throughput(F, e2e_steps, ms3, world, dist)
     K = sb.K
     h2d = 2 * F * W * H
     d2h = 2 * F * 4 + 2 * F * K * 28 + 2 * F * K * 32 + 2 * F * K * 4
@@ -355,13 +437,15 @@ def main():
         return 0
 
     # ---------------- roofline of the dominant kernel ----------------
-    counts = out["counts"][: 2 * F]
+    counts = np.concatenate([out["counts"][: 2 * F], out2["counts"][: 2 * F]])
     n_kp = float(np.mean(counts))
     ex = gf.ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH)
-    ex(left[0])
+    n_cand = 0.0
+    for img in frame0:
+        ex(img)
+        n_cand += 0.5 * float(sum(len(ex.debug_candidates(l)) for l in range(NLEVELS)))
     sizes = [ex.level_geometry(l)[1:3] for l in range(NLEVELS)]
-    n_cand = float(sum(len(ex.debug_candidates(l)) for l in range(NLEVELS)))
-    per_img = algorithmic_bytes(sizes, n_cand, n_kp)
+    per_img = algorithmic_bytes(W, H, sizes, n_cand, n_kp)
     per_launch = {k: v * 2 * F for k, v in per_img.items()}
     per_launch["stereo"] = (60 * 2 * n_kp + 352 * n_kp + 8 * n_kp) * F
     peaks_file = ROOT / "MEASURED_PEAKS.json"
@@ -369,62 +453,90 @@ def main():
         peak, peak_src = float(json.loads(peaks_file.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    int_peak, int_src = INT_PEAK_GOPS_FALLBACK, "fallback constant"
+    ip = ROOT / "profiles" / "int_peaks_r1.json"
+    if ip.exists():
+        int_peak = float(json.loads(ip.read_text())["rates"]["IADD3"]["gops"])
+        int_src = "profiles/int_peaks_r1.json (IADD3 / IMAD / VABSDIFF4 / IDP4A thread-ops per second, microbenchmarked on this pool's B200)"
     dom = max(stage_ms, key=stage_ms.get)
     stages = {}
     for k, t in stage_ms.items():
         gbs = per_launch[k] / (t * 1e-3) / 1e9 if t > 0 else 0.0
-        stages[k] = {"ms": round(t, 4), "share": round(t / sum(stage_ms.values()), 4),
+        stages[k] = {"ms": round(t, 4), "share": round(t / sum(stage_ms.values()), 4), "class": STAGE_CLASS[k],
                      "alg_bytes": int(per_launch[k]), "gbs": round(gbs, 1), "frac_hbm": round(gbs / peak, 4)}
-    # DRAM traffic and issue-slot utilisation per stage from the committed ncu capture of this same command
-    # (profiles/ncu_latest.json, written by tools/ncu_to_json.py; only meaningful at the captured batch size)
+    # DRAM traffic, instruction counts and issue-slot utilisation per stage from the committed ncu capture of this same
+    # command (profiles/ncu_latest.json, written by tools/ncu_to_json.py; only meaningful at the captured config / batch)
     prof_file = ROOT / "profiles" / "ncu_latest.json"
     if prof_file.exists():
         prof = json.loads(prof_file.read_text())
-        if prof.get("frames_per_step") == F:
-            kmap = {"pyramid": ("pyr_level0_fast_kernel", "pyr_resize_fast_kernel"), "fast": ("fast_cells_kernel",),
-                    "quadtree": ("octree_kernel",), "blur": ("blur_kernel",), "describe": ("describe_kernel",),
+        if prof.get("frames_per_step") == F and prof.get("config", "1") == args.config:
+            kmap = {"pyramid": ("pyr_level0_fast_kernel", "pyr_resize_fast_kernel", "pyr_cascade_kernel"), "fast": ("fast_cells_kernel",),
+                    "quadtree": ("octree_kernel", "octree_small_kernel"), "blur": ("blur_kernel",), "describe": ("describe_kernel",),
                     "stereo": ("stereo_kernel",)}
             for k, names in kmap.items():
                 ks = [prof["kernels"][n] for n in names if n in prof["kernels"]]
-                if k in stages and len(ks) == len(names):
+                if k in stages and ks:
                     tt = sum(x["time_us"] for x in ks)
                     stages[k]["ncu_dram_bytes"] = int(sum(x["dram_bytes"] for x in ks))
                     stages[k]["ncu_issue_active_pct"] = round(sum(x["issue_active_pct"] * x["time_us"] for x in ks) / tt, 1)
                     stages[k]["ncu_pipe_alu_pct"] = round(sum(x["pipe_alu_pct"] * x["time_us"] for x in ks) / tt, 1)
                     stages[k]["ncu_pipe_lsu_pct"] = round(sum(x["pipe_lsu_pct"] * x["time_us"] for x in ks) / tt, 1)
+                    if all("warp_inst" in x for x in ks):
+                        # INT-issue roofline: thread-instructions per launch (ncu smsp__inst_executed x 32) over the
+                        # LIVE stage time, against the microbenchmarked INT32 thread-op rate
+                        tops = 32.0 * sum(x["warp_inst"] for x in ks)
+                        gops = tops / (stage_ms[k] * 1e-3) / 1e9
+                        stages[k]["int_issue"] = {"thread_inst_per_launch": int(tops), "gops": round(gops, 1),
+                                                  "frac": round(gops / int_peak, 4)}
     ach = stages[dom]["gbs"]
-    roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+    roofline = {"bound": STAGE_CLASS[dom], "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                 "traffic": stages[dom].get("ncu_dram_bytes"), "issue_active_pct": stages[dom].get("ncu_issue_active_pct"),
                 "int_pipe_alu_pct": stages[dom].get("ncu_pipe_alu_pct"),
-                "peak_source": peak_src, "launches_in_stage": NLEVELS if dom == "pyramid" else 1,
-                "note": "FAST/quadtree/describe/stereo are integer/LSU/latency-bound (SURVEY.md 8d): their ceiling is the "
-                        "warp-instruction issue rate (issue_active_pct = ncu smsp__issue_active; int_pipe_alu_pct = share of the INT ALU "
-                        "pipe's 64 lanes/clk/SM, measured in profiles/int_peaks_r1.json, that the kernel keeps busy), "
-                        "not HBM; the HBM fraction is still reported for every stage under 'stages'; traffic = "
+                "int_issue": dict(stages[dom].get("int_issue", {}), peak=int_peak, unit="G thread-inst/s", peak_source=int_src) if "int_issue" in stages[dom] else None,
+                "peak_source": peak_src, "launches_in_stage": "see stages",
+                "note": "bound = the stage's class in SURVEY.md 8(d) (pyramid / FAST / blur: hbm; descriptor / stereo: int_issue; quadtree: "
+                        "latency); achieved / peak / frac are algorithmic bytes over the live CUDA-event time against the measured HBM "
+                        "copy rate.  FAST is classed hbm there but measures instruction-issue bound (ncu: issue slots 80 % busy, DRAM 7 %), so "
+                        "its int_issue figure (thread-instructions from the committed ncu capture / live time / microbenchmarked INT32 "
+                        "thread-op rate) is the meaningful one; both fractions are under `stages` for every stage; traffic = "
                         "dram__bytes_read+write per launch from profiles/ncu_latest.json"}
 
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "configs[1]: 752x480 stereo pair, 1000 kp, 8 levels, 1.2, FAST 20/7, classic stereo match",
+    ceiling = None
+    cfile = ROOT / "profiles" / "h2d_ceiling_r2.json"
+    if cfile.exists() and (W, H, F) == (752, 480, 256):
+        rec = json.loads(cfile.read_text()).get(str(world))
+        if rec:
+            ceiling = float(rec["ceiling_stereo_frames_per_s"])
+    line = {"metric": metric_name(cfg), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic" if cfg["source"] == "synthetic" else "bundled",
+            "config": {"workload": cfg["workload"], "name": args.config,
                        "frames_per_step_per_gpu": F, "parallelism": f"frame-sharded x{world}, no collective",
-                       "l2": "inputs+intermediates per step (%d MB) exceed the 126 MB L2" % ((2 * F * (W * H + 3 * 1344493)) >> 20),
+                       "frames": ("%d distinct seeded frames per GPU (tools/synthgen.cu, seed 1234 + frame), %d resident batches cycled by the steps"
+                                  % (NB * F, NB)) if cfg["source"] == "synthetic" else "one bundled pair replicated over the batch",
+                       "frames_total": world * F * args.steps,
+                       "l2": "inputs+intermediates per step (%d MB) exceed the 126 MB L2; consecutive steps read different frames"
+                             % ((2 * F * (W * H + 3 * per_img["pyramid"])) >> 20),
                        "mean_keypoints_per_image": round(n_kp, 1), "fast_candidates_per_image": n_cand},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "gpu_launches": launches_e2e,
+                    "steps": e2e_steps, "gpu_launches": launches_e2e,
                     "api": "gforb_stereo_frames_batch_async on two batch handles used alternately + gforb_batch_sync",
-                    "blocking_single_handle": e2e_blocking, "numa_node_rank0": numa_node, "wall_ms_per_step": wall_ms / args.steps,
+                    "host_batches": NBH,
+                    "copy_only_ceiling": ceiling, "link_frac": (e2e_value / ceiling) if ceiling else None,
+                    "ceiling_source": "profiles/h2d_ceiling_r2.json: the same bytes moved by all ranks with no kernels (tools/h2d_ceiling.py)" if ceiling else None,
+                    "blocking_single_handle": e2e_blocking, "numa_node_rank0": numa_node, "wall_ms_per_step": wall_ms / e2e_steps,
                     "pipeline": "chunks of %s frames: H2D / kernels / D2H of successive chunks overlap (2 copy + 4 kernel streams)" % (args.chunk or "8,24,32..,16,8 (auto)")},
             "gpu_launches": launches_value,
             "clocks": clocks, "roofline": roofline, "stages": stages}
     if not args.no_cpu_baseline and world == 1:
         os.sched_setaffinity(0, full_affinity)          # the CPU baseline gets every host core back
         threads = os.cpu_count() or 1
-        fps, nframes, secs, _ = cpu_baseline(left, right, threads)
-        line["cpu_baseline"] = {"value": fps, "unit": UNIT, "cores": threads, "kind": "port",
-                                "reference_shaped_2_threads": round(cpu_reference_shaped(left, right), 1),
-                                "sample": f"{nframes} synthetic 752x480 stereo frames (same generator), oracle port, "
-                                          f"{threads} threads each running whole frames, {secs:.1f} s"}
+        hl, hr = host_sample(cfg, 16, seed_base)
+        fps, nframes, secs, kind, flags, nd = cpu_baseline(cfg, hl, hr, threads)
+        line["cpu_baseline"] = {"value": fps, "unit": UNIT, "cores": threads, "kind": kind, "cpu_model": cpu_model(), "build": flags,
+                                "reference_shaped_2_threads": round(cpu_reference_shaped(cfg, hl, hr), 1),
+                                "sample": f"{nframes} stereo frames ({nd} distinct frames of the same workload -- the bytes the GPU arm's first "
+                                          f"frames hold -- cycled), {threads} threads each running whole frames, {secs:.1f} s"}
     emit(line)
     if world > 1:
         dist.destroy_process_group()

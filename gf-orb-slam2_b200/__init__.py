@@ -78,6 +78,7 @@ _SIGS = {
     "gforb_batch_set_stream": (_i, [_vp, _vp]),
     "gforb_batch_capacity": (_i, [_vp, C.POINTER(_i), C.POINTER(_i)]),
     "gforb_batch_device_input": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz), C.POINTER(_sz)]),
+    "gforb_batch_set_device_input": (_i, [_vp, _vp]),
     "gforb_batch_device_results": (_i, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp),
                                         C.POINTER(_i)]),
     "gforb_batch_upload": (_i, [_vp, _vp, _vp, _i]),
@@ -575,6 +576,10 @@ class StereoBatch:
         _check(_L.gforb_batch_device_input(self._h, C.byref(ptr), C.byref(stride), C.byref(pitch)))
         return ptr.value, stride.value, pitch.value
 
+    def set_device_input(self, dev_ptr):
+        """run from caller-owned device images (int address, the batch's own layout); None / 0 = the batch's buffer"""
+        _check(_L.gforb_batch_set_device_input(self._h, dev_ptr or None))
+
     def device_results(self):
         """device pointers of the results of the last run, in gforb_batch_download's layout:
         dict(counts, keypoints, descriptors, u_right, depth -> int addresses, K -> key stride)"""
@@ -582,10 +587,37 @@ class StereoBatch:
         _check(_L.gforb_batch_device_results(self._h, C.byref(c), C.byref(k), C.byref(d), C.byref(u), C.byref(z), C.byref(K)))
         return dict(counts=c.value, keypoints=k.value, descriptors=d.value, u_right=u.value, depth=z.value, K=K.value)
 
-    def upload(self, left, right):
+    def _check_images(self, left, right):
+        """The C entries read n*h*w tight bytes from each pointer: anything else (a slice, a transposed view, another
+        dtype or size, more frames than the batch holds) must be an error here, not a silent out-of-bounds read."""
+        for name, a in (("left", left), ("right", right)):
+            if not isinstance(a, np.ndarray) or a.dtype != np.uint8 or a.ndim != 3 or not a.flags.c_contiguous:
+                raise ValueError(f"{name}: expected a C-contiguous uint8 array [n, {self.height}, {self.width}]")
         n = left.shape[0]
-        assert left.shape == right.shape == (n, self.height, self.width) and left.dtype == np.uint8
-        assert left.flags.c_contiguous and right.flags.c_contiguous
+        if left.shape != (n, self.height, self.width) or right.shape != left.shape:
+            raise ValueError(f"left {left.shape} / right {right.shape}: expected [n, {self.height}, {self.width}] for both")
+        if not 1 <= n <= self.max_frames:
+            raise ValueError(f"{n} frames: the batch holds 1..{self.max_frames}")
+        return n
+
+    def _check_outputs(self, out, n):
+        """out[...] are written with the batch's key stride K for 2n images / n frames: smaller buffers would overrun."""
+        K = self.K
+        need = dict(counts=((2 * n,), np.int32), keypoints=((2 * n, K), KP_DTYPE), descriptors=((2 * n, K, 32), np.uint8),
+                    u_right=((n, K), np.float32), depth=((n, K), np.float32))
+        for k, a in out.items():
+            if k not in need:
+                raise ValueError(f"out[{k!r}]: unknown output")
+            if a is None:
+                continue
+            shape, dt = need[k]
+            if (not isinstance(a, np.ndarray) or a.dtype != np.dtype(dt) or not a.flags.c_contiguous or a.ndim != len(shape)
+                    or a.shape[0] < shape[0] or a.shape[1:] != shape[1:]):
+                raise ValueError(f"out[{k!r}]: expected a C-contiguous {np.dtype(dt)} array of at least {shape}, got "
+                                 f"{getattr(a, 'shape', None)} {getattr(a, 'dtype', None)}")
+
+    def upload(self, left, right):
+        n = self._check_images(left, right)
         _check(_L.gforb_batch_upload(self._h, _p(left), _p(right), n))
 
     def run(self, n_frames, bf=None, b=None, mode=STEREO_CLASSIC, th_high=TH_HIGH, th_low=TH_LOW, min_x=0.0):
@@ -625,6 +657,7 @@ class StereoBatch:
         return {k: np.empty(s, d) for k, (s, d) in shapes.items()}
 
     def download(self, n_frames, out):
+        self._check_outputs(out, n_frames)
         _check(_L.gforb_batch_download(self._h, n_frames, _p(out.get("counts")), _p(out.get("keypoints")),
                                        _p(out.get("descriptors")), _p(out.get("u_right")), _p(out.get("depth"))))
 
@@ -633,7 +666,8 @@ class StereoBatch:
 
     def process(self, left, right, out, bf, b, mode=STEREO_CLASSIC):
         """End-to-end: host images in, host results out (upload + run + download + sync)."""
-        n = left.shape[0]
+        n = self._check_images(left, right)
+        self._check_outputs(out, n)
         prm = _stereo_params(bf, b, mode, TH_HIGH, TH_LOW, 0.0)
         _check(_L.gforb_stereo_frames_batch(self._h, _p(left), _p(right), n, C.byref(prm), _p(out.get("counts")),
                                             _p(out.get("keypoints")), _p(out.get("descriptors")),
@@ -642,7 +676,8 @@ class StereoBatch:
     def submit(self, left, right, out, bf, b, mode=STEREO_CLASSIC):
         """process() without the final wait (gforb_stereo_frames_batch_async): `left`, `right` and `out` must stay
         alive and untouched until sync() returns.  Alternate two StereoBatch objects to overlap consecutive batches."""
-        n = left.shape[0]
+        n = self._check_images(left, right)
+        self._check_outputs(out, n)
         prm = _stereo_params(bf, b, mode, TH_HIGH, TH_LOW, 0.0)
         self._inflight = (left, right, out)
         _check(_L.gforb_stereo_frames_batch_async(self._h, _p(left), _p(right), n, C.byref(prm), _p(out.get("counts")),

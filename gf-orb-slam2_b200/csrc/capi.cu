@@ -1113,8 +1113,14 @@ int gforb_batch_device_input(gforb_batch* b, uint8_t** dev_ptr, size_t* image_st
     if (pitch) *pitch = (size_t)b->eng.g.W;
     return GFORB_OK;
 }
+int gforb_batch_set_device_input(gforb_batch* b, const uint8_t* dev_images_or_null) {
+    if (!b) return GFORB_ERR_ARG;
+    b->eng.b.in_ext = dev_images_or_null;
+    return GFORB_OK;
+}
 int gforb_batch_upload(gforb_batch* b, const uint8_t* left, const uint8_t* right, int n) {
     if (!b || !left || !right || n < 1 || n > b->max_frames) { set_error("gforb_batch_upload: bad arguments"); return GFORB_ERR_ARG; }
+    if (b->eng.b.in_ext) { set_error("gforb_batch_upload: a caller-owned device input is set (gforb_batch_set_device_input)"); return GFORB_ERR_ARG; }
     int rc = b->eng.upload_images(left, (size_t)b->eng.g.W, 0, 2, n, b->stream);
     if (rc) return rc;
     return b->eng.upload_images(right, (size_t)b->eng.g.W, 1, 2, n, b->stream);
@@ -1264,6 +1270,7 @@ int gforb_stereo_frames_batch_async(gforb_batch* b, const uint8_t* left, const u
                                     const gforb_stereo_params* prm, int32_t* counts, gforb_keypoint* kps,
                                     uint8_t* desc, float* u_right, float* depth) {
     if (!b || !left || !right || n < 1 || n > b->max_frames) { set_error("gforb_stereo_frames_batch: bad arguments"); return GFORB_ERR_ARG; }
+    if (b->eng.b.in_ext) { set_error("gforb_stereo_frames_batch: a caller-owned device input is set (gforb_batch_set_device_input)"); return GFORB_ERR_ARG; }
     static const bool graphs_off = getenv("GFORB_NO_GRAPH") != nullptr;     // A/B switch for measurements
     std::vector<int> csz;
     if (graphs_off || !b->use_graphs || frames_chunks(b, n, csz) != 1)

@@ -79,6 +79,8 @@ __host__ __device__ inline int cand_r(uint32_t c) { return (int)(c >> 24); }
 // Device arenas of one engine
 struct Buffers {
     uint8_t* in = nullptr;        // nimg x H x W
+    const uint8_t* in_ext = nullptr;  // caller-owned device images in the same layout (gforb_batch_set_device_input)
+    const uint8_t* input() const { return in_ext ? in_ext : in; }
     uint8_t* pyr = nullptr;       // padded pyramid arena
     uint8_t* blur = nullptr;      // blurred arena
     int32_t* tabs = nullptr;      // resize tables

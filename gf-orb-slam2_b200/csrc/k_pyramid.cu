@@ -294,10 +294,10 @@ void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s, c
         const LevelGeom& L = g.lv[0];
         if (g.W % 4 == 0) {
             dim3 grd((g.W / 4 + 31) / 32, (g.H + 4 * kRowsPerThread - 1) / (4 * kRowsPerThread), nimg);
-            pyr_level0_fast_kernel<<<grd, fblk, 0, s>>>(b.in, b.pyr + L.off, g.W, g.H, L.pitch, L.img_stride, g.img0);
+            pyr_level0_fast_kernel<<<grd, fblk, 0, s>>>(b.input(), b.pyr + L.off, g.W, g.H, L.pitch, L.img_stride, g.img0);
         } else {
             dim3 grd((L.pitch / 4 + blk.x - 1) / blk.x, (L.rows + blk.y - 1) / blk.y, nimg);
-            pyr_level0_kernel<<<grd, blk, 0, s>>>(b.in, b.pyr + L.off, g.W, g.H, L.pitch, L.rows, L.img_stride, g.img0);
+            pyr_level0_kernel<<<grd, blk, 0, s>>>(b.input(), b.pyr + L.off, g.W, g.H, L.pitch, L.rows, L.img_stride, g.img0);
         }
     }
     for (int l = 1; l < g.nlevels; ++l) {

@@ -419,6 +419,12 @@ GFORB_API int gforb_batch_capacity(const gforb_batch* b, int* max_frames, int* m
 
 /* device-resident inputs: pointer to image 0, bytes between images and between rows (tightly packed w) */
 GFORB_API int gforb_batch_device_input(gforb_batch* b, uint8_t** dev_ptr, size_t* image_stride, size_t* pitch);
+/* run from caller-owned device memory instead (e.g. frames another kernel wrote: a decoder, gforb_preprocess_batch_device):
+ * the same layout as the batch's own buffer -- image 2f = left eye of frame f, 2f+1 = right eye, w*h tight bytes each,
+ * at least 2*n_frames images for the n_frames later given to gforb_batch_run; read-only, must stay valid until the run
+ * has finished.  NULL returns to the batch's own buffer.  While set, the host-input entries (gforb_batch_upload,
+ * gforb_stereo_frames_batch[_async]) return GFORB_ERR_ARG. */
+GFORB_API int gforb_batch_set_device_input(gforb_batch* b, const uint8_t* dev_images_or_null);
 /* async H2D of n_frames stereo pairs from (ideally pinned) host memory; left/right: n_frames x h x w, tight */
 GFORB_API int gforb_batch_upload(gforb_batch* b, const uint8_t* left, const uint8_t* right, int n_frames);
 
