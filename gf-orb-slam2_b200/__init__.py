@@ -68,6 +68,7 @@ _SIGS = {
     "gforb_pyramid_level": (_i, [_vp, _i, C.POINTER(_vp), C.POINTER(_i), C.POINTER(_i), C.POINTER(_sz)]),
     "gforb_download_pyramid": (_i, [_vp, _i, _vp, _sz, _i]),
     "gforb_debug_candidates": (_i, [_vp, _i, _vp, _i, C.POINTER(_i)]),
+    "gforb_debug_blurred_level": (_i, [_vp, _i, _vp, _sz]),
     "gforb_debug_level_counts": (_i, [_vp, _vp]),
     "gforb_hamming256": (_i, [_vp, _vp]),
     "gforb_stereo_match": (_i, [_vp, _vp, C.POINTER(StereoParams), _vp, _i, _vp, _vp, _i, _vp, _vp, _vp,
@@ -105,6 +106,8 @@ _SIGS = {
     "gforb_search_by_projection": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, C.POINTER(_i)]),
     "gforb_search_by_projection_batch_device": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _i,
                                                      _vp, _vp, _vp, _vp, _vp]),
+    "gforb_search_by_sim3": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, C.POINTER(_i)]),
+    "gforb_search_by_sim3_device": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp]),
     "gforb_search_by_bow": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _vp,
                                  C.POINTER(_i)]),
     "gforb_search_by_bow_device": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _vp,
@@ -286,6 +289,26 @@ class ORBmatcher:
                                              int(ori), _p(kq) if n else None, _p(kd) if n else None, _p(qk) if nq else None,
                                              C.byref(nm)))
         return nm.value, kq, kd, qk
+
+    def SearchBySim3(self, keys1, desc1, keys2, desc2, queries12, qdesc12, queries21, qdesc21, th_dist=TH_HIGH, bounds=None,
+                     width=None, height=None):
+        """ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1214-1438) over already-projected queries: queries12[i1] = map
+        point i1 of KF1 projected into KF2 through the Sim3 (flags = PQ_ACTIVE or 0, levels nPredictedLevel - 1 ..
+        nPredictedLevel, r = th * mvScaleFactors[level]), qdesc12 = the map points' descriptors; queries21 / qdesc21 the
+        other way round.  Returns (nFound, match12, vnMatch1, vnMatch2): match12[i1] = agreed key of KF2 or -1."""
+        b = _bounds(bounds, width, height)
+        k1 = np.ascontiguousarray(keys1, KP_DTYPE); d1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32)
+        k2 = np.ascontiguousarray(keys2, KP_DTYPE); d2 = np.ascontiguousarray(desc2, np.uint8).reshape(-1, 32)
+        q12 = np.ascontiguousarray(queries12, PROJ_QUERY_DTYPE); qd12 = np.ascontiguousarray(qdesc12, np.uint8).reshape(-1, 32)
+        q21 = np.ascontiguousarray(queries21, PROJ_QUERY_DTYPE); qd21 = np.ascontiguousarray(qdesc21, np.uint8).reshape(-1, 32)
+        n1, n2 = len(k1), len(k2)
+        assert len(d1) == len(q12) == len(qd12) == n1 and len(d2) == len(q21) == len(qd21) == n2
+        m1 = np.full(n1, -1, np.int32); m2 = np.full(n2, -1, np.int32); m12 = np.full(n1, -1, np.int32)
+        nf = _i(0)
+        P = lambda a, n: _p(a) if n else None
+        _check(_L.gforb_search_by_sim3(self._h, _p(b), P(k1, n1), P(d1, n1), n1, P(k2, n2), P(d2, n2), n2, P(q12, n1), P(qd12, n1),
+                                       P(q21, n2), P(qd21, n2), int(th_dist), P(m1, n1), P(m2, n2), P(m12, n1), C.byref(nf)))
+        return nf.value, m12, m1, m2
 
     def SetInvLevelSigma2(self, inv_level_sigma2):
         """pKF->mvInvLevelSigma2 for the reprojection-error gate of ORBmatcher::Fuse (PQ_REPROJ_GATE queries)"""
@@ -488,6 +511,13 @@ class ORBextractor:
             w, h = w + 38, h + 38
         out = np.empty((h, w), np.uint8)
         _check(_L.gforb_download_pyramid(self._h, level, _p(out), out.strides[0], int(with_border)))
+        return out
+
+    def debug_blurred_level(self, level):
+        """Host copy of the blurred level the last call's descriptors were sampled from (src/ORBextractor.cc:1153-1155)."""
+        _, w, h, _ = self.level_geometry(level)
+        out = np.empty((h, w), np.uint8)
+        _check(_L.gforb_debug_blurred_level(self._h, level, _p(out), out.strides[0]))
         return out
 
     @property

@@ -80,6 +80,8 @@ struct gforb_matcher {
     void* scratch = nullptr; size_t scratch_bytes = 0;   // per-segment partial results
     void* io = nullptr; size_t io_bytes = 0;             // staging of the host-pointer form
     void* pin = nullptr; size_t pin_bytes = 0;           // its pinned host mirror: one H2D and one D2H copy per call
+    void* aux = nullptr; size_t aux_bytes = 0;           // by-products of composed entries (gforb_search_by_sim3)
+    cudaEvent_t ev_spare = nullptr;
     float inv_sig2[32];                                  // mvInvLevelSigma2 for the Fuse gate (gforb_matcher_set_inv_level_sigma2)
     bool have_inv_sig2 = false;
     int reserve_pin(size_t want) {
@@ -101,6 +103,8 @@ struct gforb_matcher {
     ~gforb_matcher() {
         if (scratch) cudaFree(scratch);
         if (io) cudaFree(io);
+        if (aux) cudaFree(aux);
+        if (ev_spare) cudaEventDestroy(ev_spare);
         if (pin) cudaFreeHost(pin);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
@@ -278,6 +282,18 @@ int gforb_download_pyramid(gforb_extractor* ex, int level, uint8_t* host, size_t
     return e == cudaSuccess ? GFORB_OK : cuda_fail(e, "cudaStreamSynchronize");
 }
 
+int gforb_debug_blurred_level(gforb_extractor* ex, int level, uint8_t* host, size_t host_pitch) {
+    if (!ex || !host) return GFORB_ERR_ARG;
+    if (!ex->eng.ready || !ex->extracted) { set_error("gforb: no extraction yet"); return GFORB_ERR_STATE; }
+    if (level < 0 || level >= ex->eng.g.nlevels) return GFORB_ERR_ARG;
+    const LevelGeom& L = ex->eng.g.lv[level];
+    if (host_pitch < (size_t)L.w) return GFORB_ERR_ARG;
+    cudaError_t e = cudaMemcpy2DAsync(host, host_pitch, ex->eng.b.blur + L.boff, L.bpitch, L.w, L.h, cudaMemcpyDeviceToHost, ex->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy2DAsync(blurred level)");
+    e = cudaStreamSynchronize(ex->stream);
+    return e == cudaSuccess ? GFORB_OK : cuda_fail(e, "cudaStreamSynchronize");
+}
+
 int gforb_debug_candidates(gforb_extractor* ex, int level, int32_t* xyr, int cap, int* n) {
     if (!ex || !n) return GFORB_ERR_ARG;
     if (!ex->eng.ready || !ex->extracted) { set_error("gforb: no extraction yet"); return GFORB_ERR_STATE; }
@@ -374,7 +390,9 @@ int gforb_stereo_match(gforb_extractor* exL, gforb_extractor* exR, const gforb_s
     v.uright = exL->st_u; v.depth = exL->st_z; v.best_dist = exL->st_bd; v.best_idx = exL->st_bi;
     v.sad = exL->st_sad; v.nmatch = exL->st_nm; v.out_stride = 0;
     v.cut_dist = exL->st_cut; v.ticket = exL->st_ticket; v.proc_count = exL->st_ticket + 1;
+    GFORB_RANGE_PUSH("gforb ComputeStereoMatches", 5);
     launch_stereo(v, norm_params(*prm), 1, (int)K, s);
+    GFORB_RANGE_POP();
     e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "stereo launch");
     int32_t nm = 0;
@@ -411,6 +429,7 @@ int gforb_matcher_create(float nnratio, gforb_matcher** out) {
     if (rc) return rc;
     M_CUDA(cudaEventCreate(&m->ev0));
     M_CUDA(cudaEventCreate(&m->ev1));
+    M_CUDA(cudaEventCreate(&m->ev_spare));
     *out = m.release();
     return GFORB_OK;
 }
@@ -727,6 +746,106 @@ int gforb_search_by_projection(gforb_matcher* m, const gforb_frame_bounds* bound
     if (n > 0) { std::memcpy(key_query, pin + okq, (size_t)n * 4); std::memcpy(key_dist, pin + okd, (size_t)n * 4); }
     if (nq > 0) std::memcpy(query_key, pin + oqk, (size_t)nq * 4);
     *nmatches = *reinterpret_cast<const int32_t*>(pin + onm);
+    return GFORB_OK;
+}
+
+// ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1214-1438): the two windowed searches are the projection entry with plain
+// GFORB_PQ_ACTIVE queries (nothing blocks, no gate, no ratio test, first minimum in window order, bestDist <= TH_HIGH),
+// the agreement test is one more kernel; nothing returns to the host in between.
+int gforb_search_by_sim3_device(gforb_matcher* m, const gforb_frame_bounds* bounds,
+                                const gforb_keypoint* keys1, const uint8_t* desc1, int n1,
+                                const gforb_keypoint* keys2, const uint8_t* desc2, int n2,
+                                const gforb_proj_query* queries12, const uint8_t* qdesc12,
+                                const gforb_proj_query* queries21, const uint8_t* qdesc21, int th_dist,
+                                int32_t* match1, int32_t* match2, int32_t* match12, int32_t* nfound, void* cuda_stream) {
+    const char* fn = "gforb_search_by_sim3";
+    if (!m || n1 < 0 || n2 < 0 || !nfound || (n1 > 0 && (!keys1 || !desc1 || !queries12 || !qdesc12 || !match1 || !match12)) ||
+        (n2 > 0 && (!keys2 || !desc2 || !queries21 || !qdesc21 || !match2))) {
+        set_error(std::string(fn) + ": bad arguments");
+        return GFORB_ERR_ARG;
+    }
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : m->stream;
+    if (n1 == 0 || n2 == 0) {                      // one side has no keys: no window holds a candidate, nothing can agree
+        if (n1 > 0) { M_CUDA(cudaMemsetAsync(match1, 0xFF, (size_t)n1 * 4, s)); M_CUDA(cudaMemsetAsync(match12, 0xFF, (size_t)n1 * 4, s)); }
+        if (n2 > 0) M_CUDA(cudaMemsetAsync(match2, 0xFF, (size_t)n2 * 4, s));
+        M_CUDA(cudaMemsetAsync(nfound, 0, 4, s));
+        m->last = s;
+        m->timed = false;
+        return GFORB_OK;
+    }
+    // key_query / key_dist / nmatches of the two searches are by-products: they live in the aux block
+    const size_t kq = al16((size_t)std::max(std::max(n1, n2), 1) * 4);
+    int rc = m->reserve(m->aux, m->aux_bytes, 2 * kq + 16);
+    if (rc) return rc;
+    uint8_t* aux = static_cast<uint8_t*>(m->aux);
+    int32_t* key_query = reinterpret_cast<int32_t*>(aux);
+    int32_t* key_dist = reinterpret_cast<int32_t*>(aux + kq);
+    int32_t* nm = reinterpret_cast<int32_t*>(aux + 2 * kq);
+    // KF1's map points into KF2 (:1259-1337), then KF2's into KF1 (:1339-1417)
+    rc = gforb_search_by_projection_batch_device(m, bounds, 1, keys2, desc2, nullptr, nullptr, nullptr, n2, queries12, qdesc12,
+                                                 nullptr, n1, th_dist, 0, 0, key_query, key_dist, match1, nm, s);
+    if (rc) return rc;
+    cudaEvent_t first = m->ev0;                    // time the whole entry: keep the first call's start event
+    m->ev0 = m->ev_spare;
+    rc = gforb_search_by_projection_batch_device(m, bounds, 1, keys1, desc1, nullptr, nullptr, nullptr, n1, queries21, qdesc21,
+                                                 nullptr, n2, th_dist, 0, 0, key_query, key_dist, match2, nm + 1, s);
+    m->ev_spare = m->ev0;
+    m->ev0 = first;
+    if (rc) return rc;
+    launch_sim3_agree(match1, n1, match2, n2, match12, nfound, s);
+    M_CUDA(cudaEventRecord(m->ev1, s));
+    M_CUDA(cudaGetLastError());
+    m->last = s;
+    m->timed = true;
+    return GFORB_OK;
+}
+
+int gforb_search_by_sim3(gforb_matcher* m, const gforb_frame_bounds* bounds,
+                         const gforb_keypoint* keys1, const uint8_t* desc1, int n1,
+                         const gforb_keypoint* keys2, const uint8_t* desc2, int n2,
+                         const gforb_proj_query* queries12, const uint8_t* qdesc12,
+                         const gforb_proj_query* queries21, const uint8_t* qdesc21, int th_dist,
+                         int32_t* match1, int32_t* match2, int32_t* match12, int* nfound) {
+    if (!m || n1 < 0 || n2 < 0 || !nfound || (n1 > 0 && (!keys1 || !desc1 || !queries12 || !qdesc12 || !match12)) ||
+        (n2 > 0 && (!keys2 || !desc2 || !queries21 || !qdesc21))) {
+        set_error("gforb_search_by_sim3: bad arguments");
+        return GFORB_ERR_ARG;
+    }
+    *nfound = 0;
+    struct Seg { const void* src; size_t bytes, off; };
+    Seg in[8] = {{keys1, (size_t)n1 * sizeof(gforb_keypoint), 0}, {desc1, (size_t)n1 * 32, 0},
+                 {keys2, (size_t)n2 * sizeof(gforb_keypoint), 0}, {desc2, (size_t)n2 * 32, 0},
+                 {queries12, (size_t)n1 * sizeof(gforb_proj_query), 0}, {qdesc12, (size_t)n1 * 32, 0},
+                 {queries21, (size_t)n2 * sizeof(gforb_proj_query), 0}, {qdesc21, (size_t)n2 * 32, 0}};
+    size_t total = 0;
+    for (Seg& g : in) { g.off = total; total += al16(std::max<size_t>(g.bytes, 16)); }
+    const size_t in_bytes = total, o1 = total, o2 = o1 + al16((size_t)std::max(n1, 1) * 4), o12 = o2 + al16((size_t)std::max(n2, 1) * 4),
+                 onf = o12 + al16((size_t)std::max(n1, 1) * 4);
+    total = onf + 16;
+    int rc = m->reserve(m->io, m->io_bytes, total);
+    if (rc) return rc;
+    rc = m->reserve_pin(total);
+    if (rc) return rc;
+    uint8_t* dev = static_cast<uint8_t*>(m->io);
+    uint8_t* pin = static_cast<uint8_t*>(m->pin);
+    for (const Seg& g : in)
+        if (g.bytes) std::memcpy(pin + g.off, g.src, g.bytes);
+    cudaStream_t s = m->stream;
+    M_CUDA(cudaMemcpyAsync(dev, pin, in_bytes, cudaMemcpyHostToDevice, s));
+    auto K = [&](int i) { return reinterpret_cast<gforb_keypoint*>(dev + in[i].off); };
+    auto Q = [&](int i) { return reinterpret_cast<gforb_proj_query*>(dev + in[i].off); };
+    rc = gforb_search_by_sim3_device(m, bounds, K(0), dev + in[1].off, n1, K(2), dev + in[3].off, n2, Q(4), dev + in[5].off, Q(6),
+                                     dev + in[7].off, th_dist, reinterpret_cast<int32_t*>(dev + o1), reinterpret_cast<int32_t*>(dev + o2),
+                                     reinterpret_cast<int32_t*>(dev + o12), reinterpret_cast<int32_t*>(dev + onf), nullptr);
+    if (rc) return rc;
+    M_CUDA(cudaMemcpyAsync(pin + in_bytes, dev + in_bytes, total - in_bytes, cudaMemcpyDeviceToHost, s));
+    M_CUDA(cudaStreamSynchronize(s));
+    if (n1 > 0) {
+        if (match1) std::memcpy(match1, pin + o1, (size_t)n1 * 4);
+        std::memcpy(match12, pin + o12, (size_t)n1 * 4);
+    }
+    if (n2 > 0 && match2) std::memcpy(match2, pin + o2, (size_t)n2 * 4);
+    *nfound = *reinterpret_cast<const int32_t*>(pin + onf);
     return GFORB_OK;
 }
 
@@ -1146,7 +1265,9 @@ int enqueue_frames(gforb_batch* b, int f0, int n, const gforb_stereo_params* prm
         v.uright = E.b.uright; v.depth = E.b.depth; v.best_dist = E.b.st_best_dist; v.best_idx = E.b.st_best_idx;
         v.sad = E.b.st_sad; v.nmatch = E.b.st_nmatch; v.out_stride = K;
         v.cut_dist = E.b.st_cut; v.ticket = E.b.st_ticket; v.proc_count = E.b.st_ticket + n_cap;
+        GFORB_RANGE_PUSH("gforb ComputeStereoMatches", 5);
         launch_stereo(v, norm_params(*prm), n, (int)K, s);
+        GFORB_RANGE_POP();
         b->last_launches += 1;
         if (timing) cudaEventRecord(b->ev[6], s);
         cudaError_t e = cudaGetLastError();

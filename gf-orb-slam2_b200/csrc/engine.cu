@@ -193,7 +193,7 @@ int make_geometry(const Tables& t, const gforb_limits& lim, int W, int H, int ni
             if (!L.area2x && group_table(tabs, L.tab_x, L.w, grp)) {
                 L.tab_g = (int)tabs.size();
                 tabs.insert(tabs.end(), grp.begin(), grp.end());
-                // TMA box of the source level that covers any 128-pixel x 32-row output tile
+                // TMA box of the source level that covers any 128-pixel x kResizeTileRows-row output tile
                 const int ng = (L.w + 3) / 4;
                 int bw = 0, bh = 0;
                 for (int bx = 0; bx * 32 < ng; ++bx) {
@@ -202,8 +202,8 @@ int make_geometry(const Tables& t, const gforb_limits& lim, int W, int H, int ni
                     const int xb = grp[8 * g0] & ~15;
                     bw = std::max(bw, (int)align_up((size_t)(grp[8 * gl] + 12 - xb), 16));
                 }
-                for (int y0 = 0; y0 < L.h; y0 += 32) {
-                    const int yl = std::min(y0 + 31, L.h - 1);
+                for (int y0 = 0; y0 < L.h; y0 += kResizeTileRows) {
+                    const int yl = std::min(y0 + kResizeTileRows - 1, L.h - 1);
                     bh = std::max(bh, tabs[L.tab_y + 2 * yl] + 2 - tabs[L.tab_y + 2 * y0]);
                 }
                 if (bw <= 256 && bh <= 256) { L.rs_bw = bw; L.rs_bh = bh; }
@@ -388,24 +388,38 @@ int Engine::run_extract(int nimg, cudaStream_t s, cudaEvent_t* ev, int img0, boo
             return cuda_fail(cudaGetLastError(), "side stream");
     }
     if (ev) cudaEventRecord(ev[0], s);
+    GFORB_RANGE_PUSH("gforb ComputePyramid", 0);
     launch_pyramid(g, b, nimg, s, rsmaps);
+    GFORB_RANGE_POP();
     if (ev) cudaEventRecord(ev[1], s);
+    GFORB_RANGE_PUSH("gforb FAST cells", 1);
     launch_fast(g, maps, b, nimg, s);
+    GFORB_RANGE_POP();
     if (ev) cudaEventRecord(ev[2], s);
     if (fork) {
         cudaEventRecord(ev_fork, s);
         cudaStreamWaitEvent(s_aux, ev_fork, 0);
+        GFORB_RANGE_PUSH("gforb DistributeOctTree", 2);
         launch_octree(g, b, nimg, s);
+        GFORB_RANGE_POP();
+        GFORB_RANGE_PUSH("gforb GaussianBlur (side stream)", 3);
         launch_blur(g, b, nimg, s_aux);
+        GFORB_RANGE_POP();
         cudaEventRecord(ev_join, s_aux);
         cudaStreamWaitEvent(s, ev_join, 0);
     } else {
+        GFORB_RANGE_PUSH("gforb DistributeOctTree", 2);
         launch_octree(g, b, nimg, s);
+        GFORB_RANGE_POP();
         if (ev) cudaEventRecord(ev[3], s);
+        GFORB_RANGE_PUSH("gforb GaussianBlur", 3);
         launch_blur(g, b, nimg, s);
+        GFORB_RANGE_POP();
     }
     if (ev) cudaEventRecord(ev[4], s);
+    GFORB_RANGE_PUSH("gforb IC_Angle + computeOrbDescriptor", 4);
     launch_describe(g, b, nimg, s);
+    GFORB_RANGE_POP();
     if (ev) cudaEventRecord(ev[5], s);
     g.img0 = 0;
     cudaError_t e = cudaGetLastError();

@@ -11,10 +11,31 @@
 
 #include "../../include/gforb.h"
 
+// NVTX stage ranges (the reference's PUSH_RANGE / POP_RANGE, include/Util_cuda.hpp:39-67, behind its USE_NVTX flag):
+// built with `make NVTX=1` (-DGFORB_NVTX), every stage of Engine::run_extract and the stereo matcher is wrapped in a
+// named range; the default build compiles them away.  NVTX v3 is header-only (no link dependency beyond -ldl).
+#ifdef GFORB_NVTX
+#include <nvtx3/nvToolsExt.h>
+#define GFORB_RANGE_PUSH(name, cid)                                                                           \
+    do {                                                                                                      \
+        static const uint32_t gforb_nvtx_colors[] = {0x0000ff00, 0x000000ff, 0x00ffff00, 0x00ff00ff, 0x0000ffff, 0x00ff0000, 0x00ffffff}; \
+        nvtxEventAttributes_t a_ = {};                                                                        \
+        a_.version = NVTX_VERSION; a_.size = NVTX_EVENT_ATTRIB_STRUCT_SIZE;                                   \
+        a_.colorType = NVTX_COLOR_ARGB; a_.color = gforb_nvtx_colors[(cid) % 7];                              \
+        a_.messageType = NVTX_MESSAGE_TYPE_ASCII; a_.message.ascii = (name);                                  \
+        nvtxRangePushEx(&a_);                                                                                 \
+    } while (0)
+#define GFORB_RANGE_POP() nvtxRangePop()
+#else
+#define GFORB_RANGE_PUSH(name, cid) do {} while (0)
+#define GFORB_RANGE_POP() do {} while (0)
+#endif
+
 namespace gforb {
 
 constexpr int kMaxLevels = 12;
 constexpr int kEdge = 19;        // EDGE_THRESHOLD, src/ORBextractor.cc:74
+constexpr int kResizeTileRows = 32;    // output rows of one resize CTA (4 warps x 8 rows; 64 measured slower: 0.571 vs 0.534 ms): k_pyramid.cu and the TMA box in engine.cu
 constexpr int kXPad = 32;        // bytes left of the ROI in every padded row (19 of them are the frame): ROI is 32B aligned
 constexpr int kMinBorder = 16;   // EDGE_THRESHOLD - 3, src/ORBextractor.cc:775
 constexpr int kHalfPatch = 15;
@@ -192,6 +213,9 @@ struct BowSearchArgs {
     int32_t* nmatches;           // [1]
 };
 void launch_bow_search(const BowSearchArgs& a, cudaStream_t s);   // 2 memsets + 2 launches
+// SearchBySim3 agreement test over the two searches' query_key arrays (k_gridmatch.cu); 1 memset + 1 launch
+void launch_sim3_agree(const int32_t* match1, int n1, const int32_t* match2, int n2, int32_t* match12, int32_t* nfound,
+                       cudaStream_t s);
 int gridmatch_max_keys();   // 8192 keys per frame
 int gridmatch_cells();      // 64 * 48
 // bounds = {mnMinX, mnMaxX, mnMinY, mnMaxY}; counts == nullptr: every frame has n_fixed keys.  1 launch.

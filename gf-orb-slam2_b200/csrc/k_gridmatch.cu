@@ -900,6 +900,28 @@ int launch_proj_search(const ProjSearchArgs& a, const float* bounds, int nframes
     return 0;
 }
 
+// ORBmatcher::SearchBySim3, the agreement test (src/ORBmatcher.cc:1420-1435): map point i1 of KF1 found key idx2 in KF2
+// and map point idx2 of KF2 found key i1 in KF1.  match1 / match2 are the two searches' query_key arrays.
+__global__ void __launch_bounds__(256)
+sim3_agree_kernel(const int32_t* __restrict__ match1, int n1, const int32_t* __restrict__ match2, int n2,
+                  int32_t* __restrict__ match12, int32_t* __restrict__ nfound) {
+    int found = 0;
+    for (int i1 = blockIdx.x * blockDim.x + threadIdx.x; i1 < n1; i1 += gridDim.x * blockDim.x) {
+        const int idx2 = match1[i1];
+        const bool ok = idx2 >= 0 && idx2 < n2 && match2[idx2] == i1;
+        match12[i1] = ok ? idx2 : -1;
+        found += ok;
+    }
+    found = __reduce_add_sync(0xffffffffu, found);
+    if ((threadIdx.x & 31) == 0 && found) atomicAdd(nfound, found);
+}
+
+void launch_sim3_agree(const int32_t* match1, int n1, const int32_t* match2, int n2, int32_t* match12, int32_t* nfound,
+                       cudaStream_t s) {
+    cudaMemsetAsync(nfound, 0, 4, s);
+    if (n1 > 0) sim3_agree_kernel<<<std::min((n1 + 255) / 256, 64), 256, 0, s>>>(match1, n1, match2, n2, match12, nfound);
+}
+
 void launch_bow_search(const BowSearchArgs& a, cudaStream_t s) {
     if (a.n1 > 0) cudaMemsetAsync(a.matches12, 0xFF, (size_t)a.n1 * 4, s);
     if (a.n2 > 0) cudaMemsetAsync(a.matched2, 0, (size_t)a.n2, s);

@@ -99,7 +99,9 @@ pyr_resize_kernel(const uint8_t* __restrict__ src_roi, int spitch, size_t simg_s
 //    (the overlap recomputes identical words).
 // Every store is an aligned 32-bit word; interior warps run no edge code at all.
 namespace {
-constexpr int kRowsPerThread = 8;
+constexpr int kRowsPerThread = 8;                       // level 0
+constexpr int kResizeRows = kResizeTileRows / 4;        // resize: rows per thread (4 warps per CTA)
+static_assert(kResizeRows == 8, "the row table is fetched eight rows at a time");
 
 __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {   // selector nibbles <= 7 only
     uint32_t d;
@@ -149,6 +151,27 @@ struct RowStore {
         if (valid) *reinterpret_cast<uint32_t*>(r) = m;
         if (lon) *reinterpret_cast<uint32_t*>(r + loff) = lw;
         if (ron) *reinterpret_cast<uint32_t*>(r + roff) = rw;
+    }
+    // the same with the row's address already in hand: r = this thread's word on ROI row y.  The mirror rows are reached
+    // relative to r (row -y is 2y rows up, row 2(h-1)-y is 2(h-1-y) rows down), so the common case costs no multiply.
+    __device__ __forceinline__ void rows_at(uint8_t* r, uint32_t m, uint32_t lw, uint32_t rw) const {
+        if (valid) *reinterpret_cast<uint32_t*>(r) = m;
+        if (lon) *reinterpret_cast<uint32_t*>(r + loff) = lw;
+        if (ron) *reinterpret_cast<uint32_t*>(r + roff) = rw;
+    }
+    __device__ __forceinline__ void store_at(uint8_t* r, int y, uint32_t own) const {
+        uint32_t m = own, lw = 0, rw = 0;
+        if (ledge) lw = prmt(own, __shfl_down_sync(0xffffffffu, own, 1), 0x1234u);
+        if (redge) {
+            const uint32_t prev = __shfl_up_sync(0xffffffffu, own, 1);
+            m = prmt(prev, own, sel_main);
+            rw = prmt(prev, own, sel_r);
+        }
+        rows_at(r, m, lw, rw);
+        if (yedge) {
+            if (y >= 1 && y <= kEdge) rows_at(r - (ptrdiff_t)(2 * y) * pitch, m, lw, rw);
+            if (y >= h - 1 - kEdge && y <= h - 2) rows_at(r + (ptrdiff_t)(2 * (h - 1 - y)) * pitch, m, lw, rw);
+        }
     }
     // all 32 lanes of the warp must call this together (shuffles)
     __device__ __forceinline__ void store(int y, uint32_t own) const {
@@ -205,8 +228,8 @@ __device__ __forceinline__ void resize_hrow(uint32_t w0, uint32_t w1, uint32_t w
     s[3] = __dp2a_hi(cf[3], B, 0u) >> 4;
 }
 
-// level l >= 1 (not the exact-2x case): cv::resize INTER_LINEAR 8U, thread = 4 pixels x kRowsPerThread rows,
-// CTA = 128 pixels x 32 rows.  kTma: the source rows/columns the tile needs arrive as ONE TMA box
+// level l >= 1 (not the exact-2x case): cv::resize INTER_LINEAR 8U, thread = 4 pixels x kResizeRows rows,
+// CTA = 128 pixels x kResizeTileRows rows.  kTma: the source rows/columns the tile needs arrive as ONE TMA box
 // (cp.async.bulk.tensor.3d of the padded source level) on an mbarrier; the row table entries are fetched while it
 // is in flight.  Consecutive output rows share source rows (scale 1.2: the lower tap row of y is usually the
 // upper tap row of y+1), so a source row's horizontal pass is reused when the row table says so.  Weights are in
@@ -223,8 +246,8 @@ pyr_resize_fast_kernel(const __grid_constant__ CUtensorMap smap, const uint8_t* 
     const int ng = (w + 3) >> 2;
     const int g0 = min((int)blockIdx.x * 32, max(ng - 32, 0));
     const int gx = g0 + threadIdx.x;
-    const int ty0 = blockIdx.y * 32;
-    const int y0 = ty0 + threadIdx.y * kRowsPerThread;
+    const int ty0 = blockIdx.y * kResizeTileRows;
+    const int y0 = ty0 + threadIdx.y * kResizeRows;
     int xb = 0, sy0 = 0;
     if (kTma) {
         xb = (int)__ldg(tab_g + 2 * g0).x & ~15;     // tile's first source byte, 16-byte aligned (TMA rule)
@@ -237,52 +260,64 @@ pyr_resize_fast_kernel(const __grid_constant__ CUtensorMap smap, const uint8_t* 
         __syncthreads();     // barrier initialised before anyone polls it
     }
     if (y0 >= h) return;     // whole warps only: idle lanes (gx >= ng) stay for the edge shuffles
-    const int y1 = min(y0 + kRowsPerThread, h);
+    const int y1 = min(y0 + kResizeRows, h);
     const int gc = min(gx, ng - 1);
     const uint4 ga = __ldg(tab_g + 2 * gc), gb = __ldg(tab_g + 2 * gc + 1);
     const uint32_t cf[4] = {gb.x, gb.y, gb.z, gb.w};
-    int2 ty[kRowsPerThread];
-#pragma unroll
-    for (int r = 0; r < kRowsPerThread; ++r) ty[r] = __ldg(tab_y + min(y0 + r, h - 1));
     RowStore st;
     st.init(out + (size_t)img * img_stride, pitch, gx, g0, w, h, y0, y1);
     const uint8_t* s = src_roi + (size_t)img * simg_stride + ga.x;          // !kTma: global source
     const uint32_t sa = smem_u32(tile) + (uint32_t)((int)ga.x - xb);        // kTma: shared byte address of this group
     if (kTma) mbar_wait(&bar, 0);
 
-    uint32_t s0[4], s1[4] = {0u, 0u, 0u, 0u};
+    // One running row pointer (the address arithmetic per row was a third of this kernel's instructions), and the
+    // interior warps -- no ROI edge, no frame row, every lane live: warp-uniform -- store without any edge code.
+    uint8_t* p = st.p + (ptrdiff_t)y0 * pitch;
+    const bool plain = !(st.ledge | st.redge | st.yedge);
+    // The two horizontal-pass results ping-pong between sA and sB: on even rows sA is the upper tap row and sB the lower,
+    // on odd rows the other way round, so a reused row (the lower row of y is the upper row of y + 1 five times out of
+    // six at scale 1.2) costs no register moves -- the loop is fully unrolled and the roles are static.
+    uint32_t sA[4] = {0u, 0u, 0u, 0u}, sB[4] = {0u, 0u, 0u, 0u};
     int have = -1;
+    int2 ty[8];
+    auto hrow = [&](int sy, uint32_t (&dst)[4]) {
+        uint32_t w0, w1, w2;
+        if (kTma) lds3(sa + (uint32_t)((sy - sy0) * bw), w0, w1, w2);
+        else {
+            const uint32_t* p0 = reinterpret_cast<const uint32_t*>(s + (size_t)sy * spitch);
+            w0 = __ldg(p0); w1 = __ldg(p0 + 1); w2 = __ldg(p0 + 2);
+        }
+        resize_hrow(w0, w1, w2, ga, cf, dst);
+    };
+    auto row = [&](int r, int y, uint32_t (&top)[4], uint32_t (&bot)[4]) {
+        const int sy = ty[r & 7].x;
+        const uint32_t b0 = (uint32_t)ty[r & 7].y << 16, b1 = (uint32_t)ty[r & 7].y & 0xFFFF0000u;
+        if (sy != have) hrow(sy, top);
+        hrow(sy + 1, bot);
+        have = sy + 1;
+        uint32_t t[4];
 #pragma unroll
-    for (int r = 0; r < kRowsPerThread; ++r) {
-        const int y = y0 + r;
-        if (y < y1) {
-            const int sy = ty[r].x;
-            const uint32_t b0 = (uint32_t)ty[r].y << 16, b1 = (uint32_t)ty[r].y & 0xFFFF0000u;
-            uint32_t w0, w1, w2;
-            if (sy == have) {
+        for (int k = 0; k < 4; ++k) t[k] = __umulhi(b0, top[k]) + __umulhi(b1, bot[k]) + 2u;   // <= 1022
+        // (t >> 2) of pixels k, k+1 land in bytes 0 and 2 of ((t[k+1] << 16) | t[k]) >> 2
+        const uint32_t u01 = (t[1] * 65536u + t[0]) >> 2, u23 = (t[3] * 65536u + t[2]) >> 2;
+        const uint32_t word = prmt(u01, u23, 0x6420);
+        if (plain) *reinterpret_cast<uint32_t*>(p) = word;
+        else st.store_at(p, y, word);
+        p += pitch;
+    };
 #pragma unroll
-                for (int k = 0; k < 4; ++k) s0[k] = s1[k];
-            } else {
-                if (kTma) lds3(sa + (uint32_t)((sy - sy0) * bw), w0, w1, w2);
-                else {
-                    const uint32_t* p0 = reinterpret_cast<const uint32_t*>(s + (size_t)sy * spitch);
-                    w0 = __ldg(p0); w1 = __ldg(p0 + 1); w2 = __ldg(p0 + 2);
-                }
-                resize_hrow(w0, w1, w2, ga, cf, s0);
-            }
-            if (kTma) lds3(sa + (uint32_t)((sy + 1 - sy0) * bw), w0, w1, w2);
-            else {
-                const uint32_t* p1 = reinterpret_cast<const uint32_t*>(s + (size_t)(sy + 1) * spitch);
-                w0 = __ldg(p1); w1 = __ldg(p1 + 1); w2 = __ldg(p1 + 2);
-            }
-            resize_hrow(w0, w1, w2, ga, cf, s1);
-            have = sy + 1;
-            uint32_t t[4];
+    for (int q = 0; q < 8; ++q) ty[q] = __ldg(tab_y + min(y0 + q, h - 1));
+    if (y1 - y0 == kResizeRows) {            // every strip but the last of a level: no per-row bound test
 #pragma unroll
-            for (int k = 0; k < 4; ++k) t[k] = __umulhi(b0, s0[k]) + __umulhi(b1, s1[k]) + 2u;   // <= 1022
-            // (t >> 2) of pixels k, k+1 land in bytes 0 and 2 of ((t[k+1] << 16) | t[k]) >> 2
-            const uint32_t u01 = (t[1] * 65536u + t[0]) >> 2, u23 = (t[3] * 65536u + t[2]) >> 2;
-            st.store(y, prmt(u01, u23, 0x6420));
+        for (int r = 0; r < kResizeRows; r += 2) {
+            row(r, y0 + r, sA, sB);
+            row(r + 1, y0 + r + 1, sB, sA);
+        }
+    } else {
+#pragma unroll
+        for (int r = 0; r < kResizeRows; r += 2) {
+            if (y0 + r < y1) row(r, y0 + r, sA, sB);
+            if (y0 + r + 1 < y1) row(r + 1, y0 + r + 1, sB, sA);
         }
     }
 }
@@ -305,7 +340,7 @@ void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s, c
         const LevelGeom& L = g.lv[l];
         const uint8_t* src_roi = b.pyr + P.off + (size_t)kEdge * P.pitch + kXPad;
         if (L.tab_g >= 0) {
-            dim3 grd(((L.w + 3) / 4 + 31) / 32, (L.h + 4 * kRowsPerThread - 1) / (4 * kRowsPerThread), nimg);
+            dim3 grd(((L.w + 3) / 4 + 31) / 32, (L.h + kResizeTileRows - 1) / kResizeTileRows, nimg);
             const uint4* tg = reinterpret_cast<const uint4*>(b.tabs + L.tab_g);
             const int2* ty = reinterpret_cast<const int2*>(b.tabs + L.tab_y);
             if (rsmaps && L.rs_bw)

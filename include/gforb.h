@@ -111,6 +111,9 @@ GFORB_API int gforb_download_pyramid(gforb_extractor* ex, int level, uint8_t* ho
  * reference's emission order (src/ORBextractor.cc:791-829), as (x, y, response) int triples relative to the
  * 16-px min border; and the per-level kept-keypoint counts. */
 GFORB_API int gforb_debug_candidates(gforb_extractor* ex, int level, int32_t* xyr, int cap, int* n);
+/* the GaussianBlur(7x7, sigma 2, BORDER_REFLECT_101) copy of `level` the descriptors of the last extract were sampled
+ * from (src/ORBextractor.cc:1153-1155), w x h bytes to HOST */
+GFORB_API int gforb_debug_blurred_level(gforb_extractor* ex, int level, uint8_t* host, size_t host_pitch);
 GFORB_API int gforb_debug_level_counts(gforb_extractor* ex, int32_t* counts);
 
 /* =====================================================================================================
@@ -251,6 +254,36 @@ GFORB_API int gforb_search_by_projection_batch_device(gforb_matcher* m, const gf
                                     int th_dist, int use_ratio, int check_orientation,
                                     int32_t* dev_key_query, int32_t* dev_key_dist, int32_t* dev_query_key,
                                     int32_t* dev_nmatches, void* cuda_stream);
+
+/* ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th)  (src/ORBmatcher.cc:1214-1438): map points of
+ * KF1 are searched in KF2 through the Sim3 and the other way round, and a pair is kept when both searches agree.
+ * The caller derives the queries exactly as for the projection entry (the Sim3 / pose projection, IsInImage, the
+ * distance-invariance test and PredictScale need MapPoint and KeyFrame state, :1259-1292 and :1339-1372):
+ *   queries12[i1], i1 in [0, n1): map point i1 of KF1 in KF2 -- x, y = u, v; r = th * pKF2->mvScaleFactors[level];
+ *       min_level, max_level = level - 1, level (:1310 keeps kp.octave in that range); flags = GFORB_PQ_ACTIVE, or 0
+ *       where the reference `continue`s (no map point, already matched through vpMatches12, bad, behind the camera,
+ *       outside the image or the invariance range); qdesc12[i1] = pMP->GetDescriptor()
+ *   queries21[i2], qdesc21: the same for KF2's map points in KF1.
+ * keys1 / desc1 = pKF1->mvKeysUn / mDescriptors (n1 = N1), keys2 / desc2 likewise; bounds = the key frames' image bounds.
+ * Nothing blocks and there is no ratio or orientation test: each query takes the FIRST smallest distance of its window
+ * in GetFeaturesInArea order (:1303-1322) if it is <= th_dist (TH_HIGH = 100).
+ * Out: match1[i1] = vnMatch1 (key of KF2 or -1), match2[i2] = vnMatch2 (both may be NULL in the host form),
+ * match12[i1] = idx2 where vnMatch2[vnMatch1[i1]] == i1 (the reference then sets vpMatches12[i1] = vpMapPoints2[idx2]),
+ * else -1; *nfound = the reference's return value.  <= 8,192 keys per key frame.  7 launches; the device form is
+ * asynchronous on `cuda_stream` (NULL: the matcher's), descriptor arrays 16-byte aligned. */
+GFORB_API int gforb_search_by_sim3(gforb_matcher* m, const gforb_frame_bounds* bounds,
+                              const gforb_keypoint* keys1, const uint8_t* desc1, int n1,
+                              const gforb_keypoint* keys2, const uint8_t* desc2, int n2,
+                              const gforb_proj_query* queries12, const uint8_t* qdesc12,
+                              const gforb_proj_query* queries21, const uint8_t* qdesc21, int th_dist,
+                              int32_t* match1, int32_t* match2, int32_t* match12, int* nfound);
+GFORB_API int gforb_search_by_sim3_device(gforb_matcher* m, const gforb_frame_bounds* bounds,
+                              const gforb_keypoint* dev_keys1, const uint8_t* dev_desc1, int n1,
+                              const gforb_keypoint* dev_keys2, const uint8_t* dev_desc2, int n2,
+                              const gforb_proj_query* dev_queries12, const uint8_t* dev_qdesc12,
+                              const gforb_proj_query* dev_queries21, const uint8_t* dev_qdesc21, int th_dist,
+                              int32_t* dev_match1, int32_t* dev_match2, int32_t* dev_match12, int32_t* dev_nfound,
+                              void* cuda_stream);
 /* ORBmatcher::SearchByBoW, both forms:
  *   SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches)        src/ORBmatcher.cc:270-404
  *   SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12)       src/ORBmatcher.cc:635-768

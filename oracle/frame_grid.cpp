@@ -265,6 +265,51 @@ int orc_search_by_projection(const orc_keypoint* keys, const uint8_t* desc, cons
 }
 
 
+// ORBmatcher::SearchBySim3 (/root/reference/src/ORBmatcher.cc:1214-1438) over already-projected queries: the two
+// search loops (:1259-1337 KF1's map points in KF2, :1339-1417 KF2's in KF1) and the agreement test (:1420-1435),
+// literally.  What precedes GetFeaturesInArea in each iteration (pose / Sim3 projection, IsInImage, distance
+// invariance, PredictScale) needs MapPoint / KeyFrame state and arrives as q.x, q.y, q.r, q.max_level = nPredictedLevel;
+// flags & 1 == 0 where the reference `continue`s before the window.
+static void sim3_one_way(const Grid& g, const orc_keypoint* keys, const uint8_t* desc, const orc_proj_query* qs,
+                         const uint8_t* qdesc, int nq, int th_dist, int* vnMatch) {
+    for (int i = 0; i < nq; ++i) {
+        vnMatch[i] = -1;
+        const orc_proj_query& q = qs[i];
+        if (!(q.flags & 1)) continue;
+        const int nPredictedLevel = q.max_level;
+        const std::vector<int> vIndices = features_in_area(g, keys, q.x, q.y, q.r, -1, -1);       // (u, v, radius): all levels
+        if (vIndices.empty()) continue;
+        int bestDist = INT_MAX, bestIdx = -1;
+        for (int idx : vIndices) {
+            const orc_keypoint& kp = keys[idx];
+            if (kp.octave < nPredictedLevel - 1 || kp.octave > nPredictedLevel) continue;
+            const int dist = orc_hamming256(qdesc + 32 * (size_t)i, desc + 32 * (size_t)idx);
+            if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+        }
+        if (bestDist <= th_dist) vnMatch[i] = bestIdx;
+    }
+}
+
+int orc_search_by_sim3(const orc_keypoint* k1, const uint8_t* d1, int n1, const orc_keypoint* k2, const uint8_t* d2, int n2,
+                       const float* bounds, const orc_proj_query* q12, const uint8_t* qd12, const orc_proj_query* q21,
+                       const uint8_t* qd21, int th_dist, int* vnMatch1, int* vnMatch2, int* match12) {
+    Grid g1, g2;
+    build_grid(g1, k1, n1, bounds);
+    build_grid(g2, k2, n2, bounds);
+    sim3_one_way(g2, k2, d2, q12, qd12, n1, th_dist, vnMatch1);
+    sim3_one_way(g1, k1, d1, q21, qd21, n2, th_dist, vnMatch2);
+    int nFound = 0;
+    for (int i1 = 0; i1 < n1; ++i1) {
+        match12[i1] = -1;
+        const int idx2 = vnMatch1[i1];
+        if (idx2 >= 0) {
+            const int idx1 = vnMatch2[idx2];
+            if (idx1 == i1) { match12[i1] = idx2; nFound++; }
+        }
+    }
+    return nFound;
+}
+
 // ORBmatcher::SearchByBoW, both forms:
 //   (KeyFrame* pKF, Frame& F, vpMapPointMatches)        /root/reference/src/ORBmatcher.cc:270-404   bestDist1 <= TH_LOW
 //   (KeyFrame* pKF1, KeyFrame* pKF2, vpMatches12)       /root/reference/src/ORBmatcher.cc:635-768   bestDist1 <  TH_LOW

@@ -94,6 +94,13 @@ int   orc_search_by_projection(const orc_keypoint* keys, const uint8_t* desc, co
                                const uint8_t* qdesc, int nq, int th_dist, float nnratio, int use_ratio, int checkOri,
                                const float* inv_level_sigma2, int* key_query, int* key_dist, int* query_key);
 
+/* ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1214-1438) over already-projected queries: q12[i1] = map point i1 of KF1
+ * in KF2 (x, y = u, v; r = radius; max_level = nPredictedLevel; flags & 1), qd12 = the map points' descriptors; q21 /
+ * qd21 the other way round.  vnMatch1[n1], vnMatch2[n2], match12[n1] (agreed idx2 or -1); returns nFound. */
+int   orc_search_by_sim3(const orc_keypoint* k1, const uint8_t* d1, int n1, const orc_keypoint* k2, const uint8_t* d2, int n2,
+                         const float* bounds, const orc_proj_query* q12, const uint8_t* qd12, const orc_proj_query* q21,
+                         const uint8_t* qd21, int th_dist, int* vnMatch1, int* vnMatch2, int* match12);
+
 /* ORBmatcher::SearchByBoW, both forms (src/ORBmatcher.cc:270-404, 635-768) over flattened DBoW2 feature vectors
  * (node ids ascending, CSR offsets, feature indices); see oracle/frame_grid.cpp.  valid1 / valid2 may be NULL. */
 int   orc_search_by_bow(const orc_keypoint* k1, const uint8_t* d1, const uint8_t* valid1, int n1, const int* node_id1,

@@ -134,6 +134,10 @@ def lib():
     L.orc_search_by_projection.argtypes = [C.c_void_p, u8p, fp, u8p, C.c_int, fp, C.c_void_p, u8p, C.c_int, C.c_int,
                                            C.c_float, C.c_int, C.c_int, fp, ip, ip, ip]
     L.orc_search_by_projection.restype = C.c_int
+    if hasattr(L, "orc_search_by_sim3"):
+        L.orc_search_by_sim3.argtypes = [C.c_void_p, u8p, C.c_int, C.c_void_p, u8p, C.c_int, fp, C.c_void_p, u8p, C.c_void_p, u8p,
+                                         C.c_int, ip, ip, ip]
+        L.orc_search_by_sim3.restype = C.c_int
     L.orc_search_by_bow.argtypes = [C.c_void_p, u8p, u8p, C.c_int, ip, ip, ip, C.c_int, C.c_void_p, u8p, u8p, C.c_int, ip, ip, ip,
                                     C.c_int, C.c_int, C.c_float, C.c_int, ip]
     L.orc_search_by_bow.restype = C.c_int
@@ -421,6 +425,21 @@ def search_by_projection(keys, desc, u_right, occupied, bounds, queries, qdesc, 
                                         int(th_dist), nnratio, int(bool(use_ratio)), int(bool(check_ori)), _p(inv), _p(kq), _p(kd),
                                         _p(qk))
     return nm, kq[:n], kd[:n], qk[:nq]
+
+
+def search_by_sim3(k1, d1, k2, d2, bounds, q12, qd12, q21, qd21, th_dist=100):
+    """ORBmatcher::SearchBySim3 over already-projected queries (src/ORBmatcher.cc:1214-1438; oracle/frame_grid.cpp).
+    Returns (nFound, match12, vnMatch1, vnMatch2)."""
+    k1 = np.ascontiguousarray(k1); k2 = np.ascontiguousarray(k2)
+    d1 = np.ascontiguousarray(d1, np.uint8); d2 = np.ascontiguousarray(d2, np.uint8)
+    q12 = np.ascontiguousarray(q12, PROJ_QUERY); q21 = np.ascontiguousarray(q21, PROJ_QUERY)
+    qd12 = np.ascontiguousarray(qd12, np.uint8); qd21 = np.ascontiguousarray(qd21, np.uint8)
+    n1, n2 = len(k1), len(k2)
+    assert len(q12) == n1 and len(q21) == n2
+    m1 = np.empty(max(n1, 1), np.int32); m2 = np.empty(max(n2, 1), np.int32); m12 = np.empty(max(n1, 1), np.int32)
+    nf = lib().orc_search_by_sim3(_p(k1), _p(d1), n1, _p(k2), _p(d2), n2, _p(_bounds(bounds)), _p(q12), _p(qd12), _p(q21), _p(qd21),
+                                  int(th_dist), _p(m1), _p(m2), _p(m12))
+    return nf, m12[:n1], m1[:n1], m2[:n2]
 
 
 def flatten_feature_vector(fv):

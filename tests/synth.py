@@ -203,3 +203,56 @@ def triangulation_case(seed, n1, n2, nodes=400):
     stereo1 = (rng.random(n1) < 0.5).astype(np.uint8); stereo2 = (rng.random(n2) < 0.5).astype(np.uint8)
     sf = (F(1.2) ** np.arange(8)).astype(F)
     return k1, d1, v1, stereo1, fv1, k2, d2, v2, stereo2, fv2, F12, F(400.0), F(240.0), sf, (sf * sf).astype(F)
+
+
+def sim3_case(seed, n1, n2, w=752, h=480, th=7.5, flip=0.07, p_mp=0.8, p_already=0.1):
+    """Inputs of one ORBmatcher::SearchBySim3 call, already projected: two key frames (keys, descriptors) whose first
+    min(n1, n2) * 0.7 features observe the same scene points; every feature may hold a map point (p_mp) whose descriptor
+    is a noisy copy of the feature's; queries12[i1] = map point i1 of KF1 projected into KF2 (lands a few pixels from its
+    partner key when it has one, anywhere otherwise), queries21 the other way round; a share of the map points is
+    "already matched" / bad / out of view (flags = 0).  Near-duplicate descriptors and shared windows make the two
+    directions disagree now and then.  Returns (k1, d1, k2, d2, q12, qd12, q21, qd21)."""
+    rng = np.random.default_rng(12000 + seed)
+    F = np.float32
+    scale = (F(1.2) ** np.arange(8)).astype(F)
+
+    def frame(n):
+        k = np.zeros(n, KEYPOINT)
+        k["x"] = (rng.random(n) * (w + 30) - 15).astype(F); k["y"] = (rng.random(n) * (h + 30) - 15).astype(F)
+        k["angle"] = (rng.random(n) * 360).astype(F)
+        k["octave"] = np.minimum(rng.geometric(0.35, n) - 1, 7)
+        k["size"], k["class_id"] = 31, -1
+        return k, rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    k1, d1 = frame(n1)
+    k2, d2 = frame(n2)
+    m = int(0.7 * min(n1, n2))
+    partner12 = np.full(n1, -1); partner21 = np.full(n2, -1)
+    if m:
+        p2 = rng.permutation(n2)[:m]
+        partner12[:m] = p2; partner21[p2] = np.arange(m)
+        d2[p2] = d1[:m] ^ np.packbits(rng.random((m, 256)) < flip, axis=1)
+        k2["octave"][p2] = np.clip(k1["octave"][:m] + rng.choice([0, 0, 0, 1, -1], m), 0, 7)
+        nd = m // 6                                                    # near-duplicate descriptors inside KF2: rivals
+        if nd:
+            src = rng.integers(0, m, nd); dst = rng.permutation(n2)[:nd]
+            d2[dst] = d2[p2[src]] ^ np.packbits(rng.random((nd, 256)) < 0.02, axis=1)
+            k2["x"][dst] = k2["x"][p2[src]] + rng.normal(0, 3, nd).astype(F); k2["y"][dst] = k2["y"][p2[src]] + rng.normal(0, 3, nd).astype(F)
+            k2["octave"][dst] = k2["octave"][p2[src]]
+
+    def queries(n, k_other, partner, d_own):
+        q = np.zeros(n, PROJ_QUERY)
+        qd = d_own ^ np.packbits(rng.random((n, 256)) < 0.03, axis=1)    # pMP->GetDescriptor(): close to the observing feature's
+        has = partner >= 0
+        q["x"] = (rng.random(n) * w).astype(F); q["y"] = (rng.random(n) * h).astype(F)
+        lvl = rng.integers(0, 8, n)
+        if has.any():
+            q["x"][has] = k_other["x"][partner[has]] + rng.normal(0, 2.5, int(has.sum())).astype(F)
+            q["y"][has] = k_other["y"][partner[has]] + rng.normal(0, 2.5, int(has.sum())).astype(F)
+            lvl[has] = np.clip(k_other["octave"][partner[has]] + rng.choice([0, 0, 1, 1, 2, -1], int(has.sum())), 0, 7)
+        q["r"] = F(th) * scale[lvl]
+        q["min_level"], q["max_level"] = lvl - 1, lvl
+        q["flags"] = (rng.random(n) < p_mp) & ~(rng.random(n) < p_already)
+        return q, qd
+    q12, qd12 = queries(n1, k2, partner12, d1)
+    q21, qd21 = queries(n2, k1, partner21, d2)
+    return k1, d1, k2, d2, q12, qd12, q21, qd21

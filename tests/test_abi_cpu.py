@@ -84,3 +84,16 @@ def test_stereo_before_extract_is_state_error():
     with pytest.raises(gf.GforbError) as e:
         gf.ComputeStereoMatches(exL, exR, k, d, k, d, 40.0, 0.1)
     assert e.value.code == gf.ERR_STATE
+
+
+def test_nvtx_build_flag_compiles(tmp_path):
+    """`make NVTX=1` wraps every stage in a named NVTX range (the reference's USE_NVTX / PUSH_RANGE,
+    include/Util_cuda.hpp:39-67).  Compile-only check of the two translation units that carry the ranges."""
+    import subprocess
+    csrc = ROOT / "gf-orb-slam2_b200" / "csrc"
+    for tu in ("engine.cu",):
+        obj = tmp_path / (tu + ".o")
+        subprocess.check_call(["/usr/local/cuda/bin/nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O1", "-std=c++17",
+                               "--fmad=false", "-Xcompiler", "-fPIC", "-DGFORB_NVTX", "-c", str(csrc / tu), "-o", str(obj)])
+        syms = subprocess.run(["nm", "-C", str(obj)], capture_output=True, text=True).stdout
+        assert "nvtxRangePushEx" in syms or "nvtxGlobals" in syms, "NVTX ranges were compiled away"

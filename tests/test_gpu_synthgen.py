@@ -65,10 +65,10 @@ def test_batch_runs_from_external_device_input():
 @pytest.mark.gpu
 def test_python_mirror_validates_buffers():
     gf = importlib.import_module("gf-orb-slam2_b200")
-    sb = gf.StereoBatch(64, 48, 2)
+    sb = gf.StereoBatch(256, 192, 2)
     out = sb.alloc_outputs(2, pinned=False)
-    good = np.zeros((2, 48, 64), np.uint8)
-    for bad in (good[:, :, ::2], good.astype(np.float32), np.zeros((2, 64, 48), np.uint8), np.zeros((3, 48, 64), np.uint8),
+    good = np.zeros((2, 192, 256), np.uint8)
+    for bad in (good[:, :, ::2], good.astype(np.float32), np.zeros((2, 256, 192), np.uint8), np.zeros((3, 192, 256), np.uint8),
                 good.transpose(0, 2, 1)):
         with pytest.raises(ValueError):
             sb.process(bad, bad, out, BF, B)

@@ -97,3 +97,60 @@ def test_engines_of_different_footprints_coexist(gf, R, fixtures):
     for ex_params, img, k, d in ((2000, "EuRoC_l", ka2, da2), (1000, "TUM_r", kb2, db2), (500, "TUM_l", kc, dc)):
         rk, rd, _ = R.Extractor(ex_params, 1.2, 8, 20, 7).extract(fixtures[img])
         assert np.ascontiguousarray(k).tobytes() == rk.tobytes() and np.array_equal(d, rd)
+
+
+def test_blurred_levels_bit_exact(gf, fixtures):
+    """a9 (src/ORBextractor.cc:1153-1155): the GaussianBlur(7x7, sigma 2, BORDER_REFLECT_101) copy of every level, pixel for
+    pixel, against the cv2-pinned primitive the reference build links (oracle cvprim) -- directly, not only through the
+    descriptors sampled from it."""
+    from oracle import pyoracle as O
+    for name, args in (("EuRoC_l", (1000, 1.2, 8, 20, 7)), ("TUM_r", (1500, 1.3, 6, 20, 7))):
+        im = fixtures[name]
+        ex = gf.ORBextractor(*args); ox = O.Extractor(*args)
+        ex(im); ox.compute_pyramid(im)
+        for l in range(args[2]):
+            assert np.array_equal(ex.debug_blurred_level(l), O.gaussian_blur(ox.level(l))), (name, l)
+
+
+# EuRoC.yaml literature values (parameters only): cam0 / cam1 intrinsics, distortion, rectifying rotations, projection
+_EUROC = dict(
+    KL=[[458.654, 0, 367.215], [0, 457.296, 248.375], [0, 0, 1]], DL=[-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05],
+    RL=[[0.999966347530033, -0.001422739138722922, 0.008079580483432283],
+        [0.001365741834644127, 0.9999741760894847, 0.007055629199258132],
+        [-0.008089410156878961, -0.007044357138835809, 0.9999424675829176]],
+    KR=[[457.587, 0, 379.999], [0, 456.134, 255.238], [0, 0, 1]], DR=[-0.28368365, 0.07451284, -0.00010473, -3.555907e-05],
+    RR=[[0.9999633526194376, -0.003625811871560086, 0.007755443660172947],
+        [0.003680398547259526, 0.9999684752771629, -0.007035845251224894],
+        [-0.007729688520722713, 0.007064130529506649, 0.999945173484644]],
+    P=[[435.2046959714599, 0, 367.4517211914062, 0], [0, 435.2046959714599, 252.2008514404297, 0], [0, 0, 1, 0]])
+
+
+def test_undistorted_stereo_on_the_euroc_pair(gf, R, fixtures):
+    """a14 on fixture-derived keys (the default build's chain, src/Frame.cc:61-147): extract both EuRoC eyes, undistort both
+    key sets on the device (UndistortKeyPointsStereo with the EuRoC.yaml coefficients), then
+    ComputeStereoMatches_Undistorted on the undistorted keys -- against the restatement AND the reference's own lifted
+    member (oracle/_ref), bit for bit."""
+    from oracle import pyoracle as O
+    E = {k: np.asarray(v, np.float64) for k, v in _EUROC.items()}
+    left, right = fixtures["EuRoC_l"], fixtures["EuRoC_r"]
+    exL, exR = gf.ORBextractor(), gf.ORBextractor()
+    kL, dL = exL(left); kR, dR = exR(right)
+    m = gf.ORBmatcher()
+    unL = gf.UndistortKeyPoints(m, gf.Camera.make(E["KL"], E["DL"], E["RL"], E["P"]), kL)
+    unR = gf.UndistortKeyPoints(m, gf.Camera.make(E["KR"], E["DR"], E["RR"], E["P"]), kR)
+    for un, k, K, D, Rm in ((unL, kL, E["KL"], E["DL"], E["RL"]), (unR, kR, E["KR"], E["DR"], E["RR"])):
+        xy = O.undistort_points(np.stack([k["x"], k["y"]], 1), K, D, Rm, E["P"])
+        assert np.array_equal(np.stack([un["x"], un["y"]], 1), xy)
+        assert np.abs(un["x"] - k["x"]).max() > 1.0                      # the coefficients really move the keys
+    rxL, rxR = R.Extractor(), R.Extractor()
+    rxL.extract(left); rxR.extract(right)
+    oxL, oxR = O.Extractor(), O.Extractor()
+    oxL.extract(left); oxR.extract(right)
+    for min_x in (0.0, 25.0):
+        got = gf.ComputeStereoMatches(exL, exR, unL, dL, unR, dR, BF, B, mode=1, min_x=min_x)
+        for name, mod, a, b_ in (("restatement", O, oxL, oxR), ("reference", R, rxL, rxR)):
+            want = mod.stereo_match(a, b_, np.ascontiguousarray(unL), dL, np.ascontiguousarray(unR), dR, BF, B, mode=1, min_x=min_x)
+            assert want["ret"] > 50, name
+            assert np.asarray(got["mvuRight"]).tobytes() == want["uRight"].tobytes(), name
+            assert np.asarray(got["mvDepth"]).tobytes() == want["depth"].tobytes(), name
+            assert got["nmatched"] == want["ret"], name
