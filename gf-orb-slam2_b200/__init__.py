@@ -126,6 +126,18 @@ _SIGS = {
     "gforb_undistort_keypoints_batch_device": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp]),
     "gforb_compute_image_bounds": (_i, [_vp, _vp, _i, _i, _vp]),
     "gforb_distinctive_descriptors": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
+    "gforb_mih_create": (_i, [_i, _i, C.POINTER(_vp)]),
+    "gforb_mih_destroy": (None, [_vp]),
+    "gforb_mih_substring_len": (_i, [_vp]),
+    "gforb_mih_update_dynamics": (_i, [_vp, C.c_double]),
+    "gforb_mih_dynamics": (_i, [_vp]),
+    "gforb_mih_hash": (_i, [_vp, _vp, _i, _vp]),
+    "gforb_mih_insert": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
+    "gforb_mih_insert_device": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _vp]),
+    "gforb_mih_query": (_i, [_vp, _vp, _i, _i, _i, _vp, _i, _vp]),
+    "gforb_mih_query_device": (_i, [_vp, _vp, _i, _i, _i, _vp, _i, _vp, _vp]),
+    "gforb_mih_query_split": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i]),
+    "gforb_mih_sync": (_i, [_vp]),
     "gforb_device_alloc": (_i, [C.POINTER(_vp), _sz]),
     "gforb_device_free": (None, [_vp]),
     "gforb_device_copy": (_i, [_vp, _vp, _sz, _i]),
@@ -802,3 +814,75 @@ def ComputeDistinctiveDescriptors(matcher, desc, set_start):
     bi = np.empty(max(n, 1), np.int32); bm = np.empty(max(n, 1), np.int32)
     _check(_L.gforb_distinctive_descriptors(matcher._h, _p(desc) if len(desc) else None, _p(ss), n, _p(bi), _p(bm)))
     return bi[:n], bm[:n]
+
+
+class MultiIndexHashing:
+    """HASHING::MultiIndexHashing(feature_length = 256, table_num) (include/Hashing.h:171-216), the descriptor side, on the
+    device: substring keys, batched insertion, the two candidate queries.  Entries are int32 handles (MapPoint::mnId)."""
+
+    def __init__(self, table_num=32):
+        self._h = _vp()
+        _check(_L.gforb_mih_create(256, table_num, C.byref(self._h)))
+        self.table_num = table_num
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h and _L is not None:
+            _L.gforb_mih_destroy(h)
+            self._h = None
+
+    def getSubstringLen(self):
+        return _L.gforb_mih_substring_len(self._h)
+
+    def updateDynamics(self, e):
+        return _L.gforb_mih_update_dynamics(self._h, float(e))
+
+    def hash(self, desc):
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        keys = np.empty((len(d), self.table_num), np.uint32)
+        _check(_L.gforb_mih_hash(self._h, _p(d) if len(d) else None, len(d), _p(keys) if len(d) else None))
+        return keys
+
+    def insert(self, desc, entry, hashed=None):
+        """returns (insert_success[n], hashed[n] afterwards)"""
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); e = np.ascontiguousarray(entry, np.int32)
+        assert len(d) == len(e)
+        hm = np.zeros(len(d), np.uint32) if hashed is None else np.ascontiguousarray(hashed, np.uint32).copy()
+        ok = np.zeros(len(d), np.uint8)
+        if len(d):
+            _check(_L.gforb_mih_insert(self._h, _p(d), _p(e), len(d), _p(hm), _p(ok)))
+        return ok, hm
+
+    def insert_device(self, dev_desc, dev_entry, n, dev_hashed, dev_success, stream=None):
+        ptr = lambda x: None if x is None else _vp(x.ptr if isinstance(x, DeviceArray) else x)
+        _check(_L.gforb_mih_insert_device(self._h, ptr(dev_desc), ptr(dev_entry), n, ptr(dev_hashed), ptr(dev_success),
+                                          _vp(stream) if stream else None))
+
+    def query(self, qdesc, nactive, nretrieve):
+        """(cand[m, stride] padded with -1, count[m]): MultiIndexHashing::query(pDesc, candidates, nactive, nretrieve)"""
+        d = np.ascontiguousarray(qdesc, np.uint8).reshape(-1, 32)
+        stride = max(1, (nactive or self.table_num) * max(nretrieve, 0))
+        cand = np.full((len(d), stride), -1, np.int32); cnt = np.zeros(len(d), np.int32)
+        if len(d):
+            _check(_L.gforb_mih_query(self._h, _p(d), len(d), nactive, nretrieve, _p(cand), stride, _p(cnt)))
+        return cand, cnt
+
+    def query_device(self, dev_qdesc, m, nactive, nretrieve, dev_cand, stride, dev_count, stream=None):
+        ptr = lambda x: None if x is None else _vp(x.ptr if isinstance(x, DeviceArray) else x)
+        _check(_L.gforb_mih_query_device(self._h, ptr(dev_qdesc), m, nactive, nretrieve, ptr(dev_cand), stride, ptr(dev_count),
+                                         _vp(stream) if stream else None))
+
+    def query_split(self, qdesc, nfeatures):
+        """(cand, count, addi, addi_count): MultiIndexHashing::query(pDesc, candidates, addi_candidates, nfeatures)"""
+        d = np.ascontiguousarray(qdesc, np.uint8).reshape(-1, 32)
+        nf = np.ascontiguousarray(nfeatures, np.int32)
+        assert len(nf) == self.table_num
+        stride = max(1, int(np.maximum(nf, 0).sum()))
+        cand = np.full((len(d), stride), -1, np.int32); cnt = np.zeros(len(d), np.int32)
+        addi = np.full((len(d), stride), -1, np.int32); acnt = np.zeros(len(d), np.int32)
+        if len(d):
+            _check(_L.gforb_mih_query_split(self._h, _p(d), len(d), _p(nf), _p(cand), _p(cnt), _p(addi), _p(acnt), stride))
+        return cand, cnt, addi, acnt
+
+    def sync(self):
+        _check(_L.gforb_mih_sync(self._h))

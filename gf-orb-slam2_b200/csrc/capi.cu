@@ -1,5 +1,7 @@
 // C ABI of libgforb.so (declared in include/gforb.h).
 #include <algorithm>
+#include <climits>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <memory>
@@ -1511,6 +1513,242 @@ int gforb_stereo_frames_batch(gforb_batch* b, const uint8_t* left, const uint8_t
                               uint8_t* desc, float* u_right, float* depth) {
     const int rc = gforb_stereo_frames_batch_async(b, left, right, n, prm, counts, kps, desc, u_right, depth);
     return rc ? rc : gforb_batch_sync(b);
+}
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * HASHING::MultiIndexHashing, the descriptor side (include/Hashing.h:171-216, src/Hashing.cc); kernels in k_mih.cu
+ * --------------------------------------------------------------------------------------------------------------- */
+struct gforb_mih {
+    int T = 0, bits = 0, cap = 0, dynamics = 0;
+    long long upper = 0;                      // entries handed to insert so far: no table holds more slots than that
+    int32_t *head = nullptr, *pool_id = nullptr, *pool_next = nullptr, *fill = nullptr, *err = nullptr;
+    cudaStream_t stream = nullptr;
+    void* io = nullptr; size_t io_bytes = 0;
+    void* pin = nullptr; size_t pin_bytes = 0;
+    int reserve(void*& p, size_t& have, size_t want, bool host) {
+        if (want <= have) return GFORB_OK;
+        if (p) { if (host) cudaFreeHost(p); else cudaFree(p); p = nullptr; have = 0; }
+        cudaError_t e = host ? cudaHostAlloc(&p, want, cudaHostAllocDefault) : cudaMalloc(&p, want);
+        if (e != cudaSuccess) return cuda_fail(e, "gforb_mih: allocation");
+        have = want;
+        return GFORB_OK;
+    }
+    ~gforb_mih() {
+        for (void* p : {(void*)head, (void*)pool_id, (void*)pool_next, (void*)fill, (void*)err, io}) if (p) cudaFree(p);
+        if (pin) cudaFreeHost(pin);
+        if (stream) cudaStreamDestroy(stream);
+    }
+};
+
+namespace {
+// room for `more` further entries per table: pools are [T][cap]; growing re-pitches them (slots keep their numbers)
+int mih_grow(gforb_mih* h, long long more) {
+    const long long need = h->upper + more;
+    if (need <= h->cap) return GFORB_OK;
+    long long ncap = std::max<long long>(h->cap * 2LL, 4096);
+    while (ncap < need) ncap *= 2;
+    if (ncap > (1LL << 30)) { set_error("gforb_mih: more than 2^30 entries"); return GFORB_ERR_CAPACITY; }
+    int32_t *nid = nullptr, *nnext = nullptr;
+    M_CUDA(cudaMalloc(&nid, (size_t)h->T * ncap * 4));
+    cudaError_t e = cudaMalloc(&nnext, (size_t)h->T * ncap * 4);
+    if (e != cudaSuccess) { cudaFree(nid); return cuda_fail(e, "cudaMalloc(mih pool)"); }
+    if (h->cap > 0) {
+        cudaMemcpy2DAsync(nid, (size_t)ncap * 4, h->pool_id, (size_t)h->cap * 4, (size_t)h->cap * 4, h->T, cudaMemcpyDeviceToDevice, h->stream);
+        cudaMemcpy2DAsync(nnext, (size_t)ncap * 4, h->pool_next, (size_t)h->cap * 4, (size_t)h->cap * 4, h->T, cudaMemcpyDeviceToDevice, h->stream);
+        cudaStreamSynchronize(h->stream);
+        cudaFree(h->pool_id); cudaFree(h->pool_next);
+    }
+    h->pool_id = nid; h->pool_next = nnext; h->cap = (int)ncap;
+    M_CUDA(cudaGetLastError());
+    return GFORB_OK;
+}
+int mih_check_err(gforb_mih* h) {
+    int32_t bits = 0;
+    M_CUDA(cudaMemcpyAsync(&bits, h->err, 4, cudaMemcpyDeviceToHost, h->stream));
+    M_CUDA(cudaStreamSynchronize(h->stream));
+    if (bits) { cudaMemsetAsync(h->err, 0, 4, h->stream); set_error("gforb_mih: slot pool overflow"); return GFORB_ERR_OVERFLOW; }
+    return GFORB_OK;
+}
+}  // namespace
+
+int gforb_mih_create(int feature_length, int table_num, gforb_mih** out) {
+    if (!out || feature_length != 256 || table_num < 16 || table_num > 32) {
+        set_error("gforb_mih_create: 256-bit descriptors and 16..32 tables (8..16-bit substrings; MapPoint::mvbHashed holds 32 flags)");
+        return GFORB_ERR_ARG;
+    }
+    std::unique_ptr<gforb_mih> h(new (std::nothrow) gforb_mih);
+    if (!h) return GFORB_ERR_ARG;
+    h->T = table_num; h->bits = feature_length / table_num;               // bits_per_substring (src/Hashing.cc:492)
+    int rc = ensure_stream(h->stream);
+    if (rc) return rc;
+    const size_t heads = (size_t)h->T << h->bits;
+    M_CUDA(cudaMalloc(&h->head, heads * 4));
+    M_CUDA(cudaMalloc(&h->fill, 32 * 4));
+    M_CUDA(cudaMalloc(&h->err, 4));
+    M_CUDA(cudaMemsetAsync(h->head, 0xFF, heads * 4, h->stream));         // every bucket empty (initialize, :522-531)
+    M_CUDA(cudaMemsetAsync(h->fill, 0, 32 * 4, h->stream));
+    M_CUDA(cudaMemsetAsync(h->err, 0, 4, h->stream));
+    M_CUDA(cudaStreamSynchronize(h->stream));
+    *out = h.release();
+    return GFORB_OK;
+}
+void gforb_mih_destroy(gforb_mih* h) { delete h; }
+int gforb_mih_substring_len(const gforb_mih* h) { return h ? h->bits : GFORB_ERR_ARG; }
+int gforb_mih_dynamics(const gforb_mih* h) { return h ? h->dynamics : 0; }
+
+int gforb_mih_update_dynamics(gforb_mih* h, double e) {                   // updateDynamics (:957-971); host-side policy
+    if (!h) return 0;
+    if (std::fabs(e) < 0.001) return h->dynamics;                         // MIN_TIME_DIFF
+    if (e > 0 && h->dynamics + 20 > 1) h->dynamics--;                     // NUM_CANDIDATE_FEATURES, MIN_BUCKET_SIZE
+    if (e < 0 && h->dynamics + 20 < 20) h->dynamics++;                    // MAX_BUCKET_SIZE
+    return h->dynamics;
+}
+
+int gforb_mih_hash(gforb_mih* h, const uint8_t* desc, int n, uint32_t* keys) {
+    if (!h || n < 0 || (n > 0 && (!desc || !keys))) { set_error("gforb_mih_hash: bad arguments"); return GFORB_ERR_ARG; }
+    if (n == 0) return GFORB_OK;
+    const size_t in = al16((size_t)n * 32), outb = (size_t)n * h->T * 4;
+    int rc = h->reserve(h->io, h->io_bytes, in + outb, false);
+    if (rc) return rc;
+    uint8_t* dev = static_cast<uint8_t*>(h->io);
+    M_CUDA(cudaMemcpyAsync(dev, desc, (size_t)n * 32, cudaMemcpyHostToDevice, h->stream));
+    launch_mih_hash(dev, n, h->T, h->bits, reinterpret_cast<uint32_t*>(dev + in), h->stream);
+    M_CUDA(cudaMemcpyAsync(keys, dev + in, outb, cudaMemcpyDeviceToHost, h->stream));
+    M_CUDA(cudaStreamSynchronize(h->stream));
+    return GFORB_OK;
+}
+
+int gforb_mih_insert_device(gforb_mih* h, const uint8_t* dev_desc, const int32_t* dev_entry, int n, uint32_t* dev_hashed,
+                            uint8_t* dev_success, void* cuda_stream) {
+    if (!h || n < 0 || (n > 0 && (!dev_desc || !dev_entry || !dev_hashed || !dev_success))) { set_error("gforb_mih_insert: bad arguments"); return GFORB_ERR_ARG; }
+    if ((uintptr_t)dev_desc & 3) { set_error("gforb_mih_insert: descriptors must be 4-byte aligned"); return GFORB_ERR_ARG; }
+    if (n == 0) return GFORB_OK;
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
+    int rc = mih_grow(h, n);
+    if (rc) return rc;
+    M_CUDA(cudaMemsetAsync(dev_success, 0, (size_t)n, s));
+    for (int i0 = 0; i0 < n; i0 += mih_max_batch()) {                      // chunks keep the reference's insertion order
+        const int c = std::min(n - i0, mih_max_batch());
+        if (launch_mih_insert(dev_desc + 32 * (size_t)i0, dev_entry + i0, c, h->T, h->bits, h->cap, h->head, h->pool_id, h->pool_next,
+                              h->fill, dev_hashed + i0, dev_success + i0, h->err, s)) {
+            set_error("gforb_mih_insert: shared-memory opt-in failed");
+            return GFORB_ERR_CUDA;
+        }
+    }
+    h->upper += n;
+    M_CUDA(cudaGetLastError());
+    return GFORB_OK;
+}
+
+int gforb_mih_insert(gforb_mih* h, const uint8_t* desc, const int32_t* entry, int n, uint32_t* hashed, uint8_t* success) {
+    if (!h || n < 0 || (n > 0 && (!desc || !entry))) { set_error("gforb_mih_insert: bad arguments"); return GFORB_ERR_ARG; }
+    if (n == 0) return GFORB_OK;
+    const size_t od = 0, oe = al16((size_t)n * 32), oh = oe + al16((size_t)n * 4), os = oh + al16((size_t)n * 4), total = os + al16((size_t)n);
+    int rc = h->reserve(h->io, h->io_bytes, total, false);
+    if (rc) return rc;
+    rc = h->reserve(h->pin, h->pin_bytes, total, true);
+    if (rc) return rc;
+    uint8_t* dev = static_cast<uint8_t*>(h->io);
+    uint8_t* pin = static_cast<uint8_t*>(h->pin);
+    std::memcpy(pin + od, desc, (size_t)n * 32);
+    std::memcpy(pin + oe, entry, (size_t)n * 4);
+    if (hashed) std::memcpy(pin + oh, hashed, (size_t)n * 4); else std::memset(pin + oh, 0, (size_t)n * 4);
+    M_CUDA(cudaMemcpyAsync(dev, pin, os, cudaMemcpyHostToDevice, h->stream));
+    rc = gforb_mih_insert_device(h, dev + od, reinterpret_cast<int32_t*>(dev + oe), n, reinterpret_cast<uint32_t*>(dev + oh), dev + os, nullptr);
+    if (rc) return rc;
+    M_CUDA(cudaMemcpyAsync(pin + oh, dev + oh, total - oh, cudaMemcpyDeviceToHost, h->stream));
+    rc = mih_check_err(h);
+    if (rc) return rc;
+    if (hashed) std::memcpy(hashed, pin + oh, (size_t)n * 4);
+    if (success) std::memcpy(success, pin + os, (size_t)n);
+    return GFORB_OK;
+}
+
+namespace {
+int mih_query_impl(gforb_mih* h, const uint8_t* qdesc, int m, const int* take, int keep, int need, int32_t* cand, int32_t* count,
+                   int32_t* addi, int32_t* addi_count, int stride, bool device, cudaStream_t s, const char* fn) {
+    if (stride < need) { set_error(std::string(fn) + ": stride smaller than the largest possible candidate count"); return GFORB_ERR_CAPACITY; }
+    if (m == 0) return GFORB_OK;
+    if (device) {
+        launch_mih_query(qdesc, m, h->T, h->bits, h->cap, h->head, h->pool_id, h->pool_next, take, keep, cand, count, addi, addi_count, stride, s);
+        M_CUDA(cudaGetLastError());
+        return GFORB_OK;
+    }
+    const size_t oq = 0, oc = al16((size_t)m * 32), on = oc + al16((size_t)m * stride * 4), oa = on + al16((size_t)m * 4),
+                 oan = oa + (addi ? al16((size_t)m * stride * 4) : 0), total = oan + (addi ? al16((size_t)m * 4) : 0);
+    int rc = h->reserve(h->io, h->io_bytes, total, false);
+    if (rc) return rc;
+    uint8_t* dev = static_cast<uint8_t*>(h->io);
+    M_CUDA(cudaMemcpyAsync(dev + oq, qdesc, (size_t)m * 32, cudaMemcpyHostToDevice, h->stream));
+    M_CUDA(cudaMemsetAsync(dev + oc, 0xFF, on - oc, h->stream));           // unused tail of every row reads -1
+    if (addi) M_CUDA(cudaMemsetAsync(dev + oa, 0xFF, oan - oa, h->stream));
+    launch_mih_query(dev + oq, m, h->T, h->bits, h->cap, h->head, h->pool_id, h->pool_next, take, keep, reinterpret_cast<int32_t*>(dev + oc),
+                     reinterpret_cast<int32_t*>(dev + on), addi ? reinterpret_cast<int32_t*>(dev + oa) : nullptr,
+                     addi ? reinterpret_cast<int32_t*>(dev + oan) : nullptr, stride, h->stream);
+    M_CUDA(cudaMemcpyAsync(cand, dev + oc, (size_t)m * stride * 4, cudaMemcpyDeviceToHost, h->stream));
+    M_CUDA(cudaMemcpyAsync(count, dev + on, (size_t)m * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (addi) {
+        M_CUDA(cudaMemcpyAsync(addi, dev + oa, (size_t)m * stride * 4, cudaMemcpyDeviceToHost, h->stream));
+        M_CUDA(cudaMemcpyAsync(addi_count, dev + oan, (size_t)m * 4, cudaMemcpyDeviceToHost, h->stream));
+    }
+    M_CUDA(cudaStreamSynchronize(h->stream));
+    return GFORB_OK;
+}
+// Bucket::back's n per table for the plain form (:699-846): tables 0 .. nactive-1, nretrieves + dynamics each
+int mih_take_plain(const gforb_mih* h, int nactive, int nretrieves, int* take) {
+    if (nactive == 0) nactive = h->T;                                      // nactive_tables_top == NULL
+    int need = 0;
+    for (int k = 0; k < 32; ++k) {
+        take[k] = k < nactive ? std::max(nretrieves + h->dynamics, 0) : 0;  // n < 0 is undefined in the reference: nothing
+        need += take[k];
+    }
+    return need;
+}
+int mih_take_split(const gforb_mih* h, const int32_t* nfeatures, int* take) {
+    int need = 0;
+    for (int k = 0; k < 32; ++k) {
+        take[k] = (k < h->T && nfeatures[k] > 0) ? std::max(nfeatures[k] + h->dynamics, 0) : 0;     // :868-872
+        need += take[k];
+    }
+    return need;
+}
+}  // namespace
+
+int gforb_mih_query(gforb_mih* h, const uint8_t* qdesc, int m, int nactive_tables, int nretrieves, int32_t* cand, int stride, int32_t* count) {
+    if (!h || m < 0 || nactive_tables < 0 || nactive_tables > (h ? h->T : 0) || nretrieves < 0 || (m > 0 && (!qdesc || !cand || !count))) {
+        set_error("gforb_mih_query: bad arguments");
+        return GFORB_ERR_ARG;
+    }
+    int take[32];
+    const int need = mih_take_plain(h, nactive_tables, nretrieves, take);
+    return mih_query_impl(h, qdesc, m, take, INT_MAX, need, cand, count, nullptr, nullptr, stride, false, h->stream, "gforb_mih_query");
+}
+int gforb_mih_query_device(gforb_mih* h, const uint8_t* dev_qdesc, int m, int nactive_tables, int nretrieves, int32_t* dev_cand, int stride,
+                           int32_t* dev_count, void* cuda_stream) {
+    if (!h || m < 0 || nactive_tables < 0 || nactive_tables > (h ? h->T : 0) || nretrieves < 0 || (m > 0 && (!dev_qdesc || !dev_cand || !dev_count)) ||
+        ((uintptr_t)dev_qdesc & 3)) {
+        set_error("gforb_mih_query: bad arguments");
+        return GFORB_ERR_ARG;
+    }
+    int take[32];
+    const int need = mih_take_plain(h, nactive_tables, nretrieves, take);
+    return mih_query_impl(h, dev_qdesc, m, take, INT_MAX, need, dev_cand, dev_count, nullptr, nullptr, stride, true,
+                          cuda_stream ? (cudaStream_t)cuda_stream : h->stream, "gforb_mih_query");
+}
+int gforb_mih_query_split(gforb_mih* h, const uint8_t* qdesc, int m, const int32_t* nfeatures, int32_t* cand, int32_t* count,
+                          int32_t* addi, int32_t* addi_count, int stride) {
+    if (!h || m < 0 || !nfeatures || (m > 0 && (!qdesc || !cand || !count || !addi || !addi_count))) {
+        set_error("gforb_mih_query_split: bad arguments");
+        return GFORB_ERR_ARG;
+    }
+    int take[32];
+    const int need = mih_take_split(h, nfeatures, take);
+    return mih_query_impl(h, qdesc, m, take, 20 + h->dynamics, need, cand, count, addi, addi_count, stride, false, h->stream,
+                          "gforb_mih_query_split");
+}
+int gforb_mih_sync(gforb_mih* h) {
+    if (!h) return GFORB_ERR_ARG;
+    return mih_check_err(h);
 }
 
 }  // extern "C"

@@ -239,6 +239,14 @@ void launch_undistort_xy(const double* K, const double* dist, const double* R, c
 int distinctive_max_set();
 int launch_distinctive(const uint8_t* desc, const int32_t* set_start, int npoints, int max_n, int32_t* best_idx,
                        int32_t* best_median, cudaStream_t s);
+// multi-index hashing (k_mih.cu): substring keys, batched insertion (<= mih_max_batch() entries per launch), queries
+int mih_max_batch();
+void launch_mih_hash(const uint8_t* desc, int n, int T, int bits, uint32_t* keys, cudaStream_t s);
+int launch_mih_insert(const uint8_t* desc, const int32_t* entry, int n, int T, int bits, int cap, int32_t* head, int32_t* pool_id,
+                      int32_t* pool_next, int32_t* fill, uint32_t* hashed, uint8_t* success, int32_t* err, cudaStream_t s);
+void launch_mih_query(const uint8_t* qdesc, int m, int T, int bits, int cap, const int32_t* head, const int32_t* pool_id,
+                      const int32_t* pool_next, const int* take, int keep, int32_t* cand, int32_t* count, int32_t* addi,
+                      int32_t* addi_count, int stride, cudaStream_t s);
 size_t octree_smem_bytes(const Geom& g);
 int fast_configure(const Geom& g);     // opt in to the FAST kernel's dynamic smem; returns cudaError_t as int
 int octree_configure(const Geom& g);   // opt in to large dynamic smem; returns cudaError_t as int

@@ -514,6 +514,52 @@ GFORB_API int gforb_batch_launches_per_run(const gforb_batch* b, int with_stereo
 GFORB_API int gforb_batch_stage_timing(gforb_batch* b, int enable);
 GFORB_API int gforb_batch_stage_times(gforb_batch* b, float* ms6);
 
+/* =====================================================================================================
+ * Multi-index hashing of 256-bit descriptors: HASHING::MultiIndexHashing, the descriptor side
+ * (include/Hashing.h:171-216, src/Hashing.cc) -- substring keys, bucket insertion and the two candidate queries, for
+ * whole batches of descriptors.  Entries are caller-chosen int32 handles (MapPoint::mnId); what the reference keeps
+ * inside MapPoint (mvbHashed) travels as a bit mask per entry that the caller holds.  The policy around it (which map
+ * points to insert, LocalMapping.cc:619,959, Tracking.cc:1320; what to do with the candidates, Tracking.cc:3000-3060)
+ * needs the map and stays with the caller.
+ * ===================================================================================================== */
+typedef struct gforb_mih gforb_mih;
+/* MultiIndexHashing(feature_length = 256, table_num) (src/Hashing.cc:489-520).  table_num 16..32: substrings of
+ * 256 / table_num = 8..16 bits, 2^bits buckets per table (the reference's own configuration is 32 tables of 8 bits,
+ * src/System.cc:105).  Wider substrings (table_num < 16) are refused: GFORB_ERR_ARG. */
+GFORB_API int gforb_mih_create(int feature_length, int table_num, gforb_mih** out);
+GFORB_API void gforb_mih_destroy(gforb_mih* h);
+GFORB_API int gforb_mih_substring_len(const gforb_mih* h);                        /* getSubstringLen (:952-955) */
+/* updateDynamics(e) (:957-971): the retrieval-depth offset added to every query's count; returns the new value */
+GFORB_API int gforb_mih_update_dynamics(gforb_mih* h, double e);
+GFORB_API int gforb_mih_dynamics(const gforb_mih* h);
+/* hash() (:53-103) for n descriptors: keys[i * table_num + t] = bucket of descriptor i in table t.  Host pointers. */
+GFORB_API int gforb_mih_hash(gforb_mih* h, const uint8_t* desc, int n, uint32_t* keys);
+/* insert() (:533-598) for entry[0..n) in this order: table t takes entry i unless bit t of hashed[i] is set (it is set
+ * on return) or the bucket's latest entry already is entry[i]; success[i] = the reference's return value.
+ * hashed == NULL: all flags clear on entry; success may be NULL.  Buckets keep their entries newest first. */
+GFORB_API int gforb_mih_insert(gforb_mih* h, const uint8_t* desc, const int32_t* entry, int n, uint32_t* hashed_io, uint8_t* success);
+/* device pointers (descriptors 4-byte aligned, e.g. gforb_batch_device_results' descriptor rows); dev_hashed_io and
+ * dev_success are required; asynchronous on `cuda_stream` (NULL: the handle's own -- use one stream per handle);
+ * 1 launch per 8,192 entries.  gforb_mih_sync waits and reports device-side overflow. */
+GFORB_API int gforb_mih_insert_device(gforb_mih* h, const uint8_t* dev_desc, const int32_t* dev_entry, int n,
+                                 uint32_t* dev_hashed_io, uint8_t* dev_success, void* cuda_stream);
+/* query(pDesc, candidates, nactive_tables_top, nretrieves) (:699-846) for m descriptors: row q of cand (stride ints)
+ * receives, table 0 .. nactive_tables - 1 in turn (0 = all tables), the newest nretrieves + dynamics entries of the
+ * descriptor's bucket in that table, newest first; count[q] = how many.  stride >= nactive_tables * (nretrieves +
+ * dynamics) or GFORB_ERR_CAPACITY; the unused tail of a row reads -1 (host form).  Duplicates are not removed (the
+ * reference leaves that to its caller, Tracking.cc:3018-3030). */
+GFORB_API int gforb_mih_query(gforb_mih* h, const uint8_t* qdesc, int m, int nactive_tables, int nretrieves,
+                         int32_t* cand, int stride, int32_t* count);
+GFORB_API int gforb_mih_query_device(gforb_mih* h, const uint8_t* dev_qdesc, int m, int nactive_tables, int nretrieves,
+                                int32_t* dev_cand, int stride, int32_t* dev_count, void* cuda_stream);
+/* query(pDesc, candidates, addi_candidates, nfeatures) (:849-950): table k is consulted when nfeatures[k] > 0 and
+ * yields its newest nfeatures[k] + dynamics entries; of a run longer than NUM_CANDIDATE_FEATURES + dynamics (20 +
+ * dynamics) the OLDEST 20 + dynamics go to cand and the newer ones to addi, both in table order.  nfeatures: table_num
+ * ints.  stride >= sum of the per-table counts. */
+GFORB_API int gforb_mih_query_split(gforb_mih* h, const uint8_t* qdesc, int m, const int32_t* nfeatures, int32_t* cand,
+                               int32_t* count, int32_t* addi, int32_t* addi_count, int stride);
+GFORB_API int gforb_mih_sync(gforb_mih* h);
+
 /* pinned host memory helpers (cudaHostAlloc / cudaFreeHost) so callers can stage inputs for async copies */
 GFORB_API int gforb_host_alloc(void** ptr, size_t bytes);
 GFORB_API void gforb_host_free(void* ptr);
