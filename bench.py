@@ -65,6 +65,17 @@ STAGE_CLASS = {"pyramid": "hbm", "fast": "hbm", "blur": "hbm", "describe": "int_
                "quadtree": "latency"}      # SURVEY.md 8(d) "Which roofline"
 
 
+# the default configuration's constants and frame source, for the side benches under tools/
+W, H, NFEAT = CONFIGS["1"]["w"], CONFIGS["1"]["h"], CONFIGS["1"]["nfeat"]
+
+
+def make_frames(n, seed0=0):
+    """n distinct seeded synthetic 752x480 stereo frames on the host (left, right uint8 [n, H, W]) -- the bytes the
+    device generator writes for the same seeds"""
+    import synthgen
+    return synthgen.host_frames(seed0, n, W, H)
+
+
 def metric_name(cfg):
     return f"stereo frames/s ORB extract+match @{cfg['w']}x{cfg['h']}x{cfg['nfeat']}kp"
 

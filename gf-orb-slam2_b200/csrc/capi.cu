@@ -1373,10 +1373,16 @@ int gforb_batch_sync(gforb_batch* b) {
     return b->eng.check_errors(b->stream);
 }
 
+int gforb_batch_reset_graphs(gforb_batch* b) {
+    if (!b) return GFORB_ERR_ARG;
+    for (auto& gs : b->graphs) if (gs.exec) cudaGraphExecDestroy(gs.exec);
+    b->graphs.clear();
+    return GFORB_OK;
+}
 int gforb_batch_set_chunk(gforb_batch* b, int frames) {
     if (!b || frames < 0) return GFORB_ERR_ARG;
     b->chunk_frames = frames;
-    return GFORB_OK;
+    return gforb_batch_reset_graphs(b);        // the captured sequences were cut with the old chunk size
 }
 
 // Host buffers in, host buffers out.  The batch is cut into chunks; chunk c's H2D copy (upload stream), its
@@ -1399,9 +1405,15 @@ int gforb_stereo_frames_batch_async(gforb_batch* b, const uint8_t* left, const u
     if (graphs_off || !b->use_graphs || frames_chunks(b, n, csz) != 1)
         return frames_enqueue(b, left, right, n, prm, counts, kps, desc, u_right, depth);
     const void* args[8] = {left, right, counts, kps, desc, u_right, depth, nullptr};
+    auto same_prm = [](const gforb_stereo_params& x, const gforb_stereo_params& y) {      // field by field: no padding, no -0.0 / NaN surprises
+        return std::memcmp(&x.bf, &y.bf, 4) == 0 && std::memcmp(&x.b, &y.b, 4) == 0 && x.mode == y.mode && x.th_high == y.th_high &&
+               x.th_low == y.th_low && std::memcmp(&x.min_x, &y.min_x, 4) == 0;
+    };
     for (auto& gs : b->graphs) {
         if (gs.n == n && gs.has_prm == (prm != nullptr) && std::memcmp(gs.args, args, sizeof args) == 0 &&
-            (!prm || std::memcmp(&gs.prm, prm, sizeof *prm) == 0)) {
+            (!prm || same_prm(gs.prm, *prm))) {
+            if (!gs.exec)          // negative entry: this argument set could not be captured (pageable buffers): plain launches
+                return frames_enqueue(b, left, right, n, prm, counts, kps, desc, u_right, depth);
             cudaError_t e = cudaGraphLaunch(gs.exec, b->stream);
             if (e != cudaSuccess) return cuda_fail(e, "cudaGraphLaunch");
             b->last_launches = gs.launches;
@@ -1420,17 +1432,17 @@ int gforb_stereo_frames_batch_async(gforb_batch* b, const uint8_t* left, const u
     }
     if (ok) ok = cudaGraphInstantiate(&exec, graph, 0) == cudaSuccess;
     if (graph) cudaGraphDestroy(graph);
-    if (!ok) {                     // e.g. pageable host buffers cannot be captured: fall back to plain enqueue for this handle
+    if (!ok) {                     // e.g. pageable host buffers cannot be captured: THIS argument set stays on plain launches
         (void)cudaGetLastError();
-        b->use_graphs = false;
-        return frames_enqueue(b, left, right, n, prm, counts, kps, desc, u_right, depth);
+        if (exec) { cudaGraphExecDestroy(exec); exec = nullptr; }
     }
-    if (b->graphs.size() >= 8) { cudaGraphExecDestroy(b->graphs.front().exec); b->graphs.erase(b->graphs.begin()); }
+    if (b->graphs.size() >= 8) { if (b->graphs.front().exec) cudaGraphExecDestroy(b->graphs.front().exec); b->graphs.erase(b->graphs.begin()); }
     gforb_batch::GraphSlot gs{};
     std::memcpy(gs.args, args, sizeof args);
     gs.n = n; gs.has_prm = prm != nullptr; if (prm) gs.prm = *prm;
     gs.exec = exec; gs.launches = b->last_launches;
     b->graphs.push_back(gs);
+    if (!exec) return frames_enqueue(b, left, right, n, prm, counts, kps, desc, u_right, depth);
     cudaError_t e = cudaGraphLaunch(exec, b->stream);
     if (e != cudaSuccess) return cuda_fail(e, "cudaGraphLaunch");
     return GFORB_OK;

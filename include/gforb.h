@@ -501,6 +501,11 @@ GFORB_API int gforb_stereo_frames_batch_async(gforb_batch* b, const uint8_t* lef
 /* gforb_stereo_frames_batch pipelines the batch in chunks of `frames` stereo frames (H2D of chunk c+1, kernels of
  * chunk c and D2H of chunk c-1 overlap on separate streams); 0 = automatic (16 when the batch has >= 48 frames) */
 GFORB_API int gforb_batch_set_chunk(gforb_batch* b, int frames);
+/* The CUDA graphs of single-chunk calls are keyed on the host POINTER VALUES, n_frames and the parameters.  A caller
+ * that frees a buffer and later passes another allocation that happens to land on the same address (or changes a
+ * buffer from pinned to pageable) must drop the cached graphs first; an argument set that cannot be captured (pageable
+ * memory) is remembered as such and runs on plain launches without affecting the others. */
+GFORB_API int gforb_batch_reset_graphs(gforb_batch* b);
 /* kernels actually enqueued by the last gforb_batch_run / gforb_stereo_frames_batch call */
 GFORB_API int gforb_batch_last_launches(const gforb_batch* b);
 
