@@ -438,6 +438,24 @@ def main():
     wall_ms = (time.perf_counter() - t_e2e) * 1e3
     ms3 = torch.tensor([max(e0.elapsed_time(e1), 0.0)], device="cuda")
     e2e_value = aggregate_throughput(F, e2e_steps, ms3, world, dist)
+    # ---------------- the copy-only ceiling of that arm, measured on THIS box in THIS run: the same calls with the
+    # kernels switched off (gforb_batch_debug_copy_only) -- same chunks, streams, events and bytes, all ranks together
+    sb.debug_copy_only(True); sb2.debug_copy_only(True)
+    for i in range(2):
+        hs[i % 2].sync(); hs[i % 2].submit(pin_l.array[i % NBH], pin_r.array[i % NBH], outs[i % 2], BF, B)
+    sb.sync(); sb2.sync()
+    barrier()
+    e0.record(stream)
+    for i in range(e2e_steps):
+        hs[i % 2].sync(); hs[i % 2].submit(pin_l.array[i % NBH], pin_r.array[i % NBH], outs[i % 2], BF, B)
+    sb2.sync(); sb.sync()
+    e1.record(stream)
+    barrier()
+    ms4 = torch.tensor([max(e0.elapsed_time(e1), 1e-3)], device="cuda")
+    ceiling_live = aggregate_throughput(F, e2e_steps, ms4, world, dist)
+    sb.debug_copy_only(False); sb2.debug_copy_only(False)
+    hs[0].submit(pin_l.array[0], pin_r.array[0], outs[0], BF, B); hs[1].submit(pin_l.array[0], pin_r.array[0], outs[1], BF, B)
+    sb.sync(); sb2.sync()                      # real results back in the output buffers (counts feed the roofline below)
     K = sb.K
     h2d = 2 * F * W * H
     d2h = 2 * F * 4 + 2 * F * K * 28 + 2 * F * K * 32 + 2 * F * K * 4
@@ -512,12 +530,7 @@ def main():
                         "thread-op rate) is the meaningful one; both fractions are under `stages` for every stage; traffic = "
                         "dram__bytes_read+write per launch from profiles/ncu_latest.json"}
 
-    ceiling = None
-    cfile = ROOT / "profiles" / "h2d_ceiling_r2.json"
-    if cfile.exists() and (W, H, F) == (752, 480, 256):
-        rec = json.loads(cfile.read_text()).get(str(world))
-        if rec:
-            ceiling = float(rec["ceiling_stereo_frames_per_s"])
+    ceiling = ceiling_live
     line = {"metric": metric_name(cfg), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None,
             "dtype": "u8", "data": "synthetic" if cfg["source"] == "synthetic" else "bundled",
@@ -534,7 +547,9 @@ def main():
                     "api": "gforb_stereo_frames_batch_async on two batch handles used alternately + gforb_batch_sync",
                     "host_batches": NBH,
                     "copy_only_ceiling": ceiling, "link_frac": (e2e_value / ceiling) if ceiling else None,
-                    "ceiling_source": "profiles/h2d_ceiling_r2.json: the same bytes moved by all ranks with no kernels (tools/h2d_ceiling.py)" if ceiling else None,
+                    "ceiling_source": "measured in this run on this box: the same gforb_stereo_frames_batch_async calls with the kernels "
+                                      "switched off (gforb_batch_debug_copy_only), all ranks together; profiles/h2d_ceiling_r2.json "
+                                      "holds an independent torch-free copy loop (tools/h2d_ceiling.py) from another box",
                     "blocking_single_handle": e2e_blocking, "numa_node_rank0": numa_node, "wall_ms_per_step": wall_ms / e2e_steps,
                     "pipeline": "chunks of %s frames: H2D / kernels / D2H of successive chunks overlap (2 copy + 4 kernel streams)" % (args.chunk or "8,24,32..,16,8 (auto)")},
             "gpu_launches": launches_value,

@@ -92,6 +92,7 @@ _SIGS = {
     "gforb_batch_last_launches": (_i, [_vp]),
     "gforb_batch_set_chunk": (_i, [_vp, _i]),
     "gforb_batch_reset_graphs": (_i, [_vp]),
+    "gforb_batch_debug_copy_only": (_i, [_vp, _i]),
     "gforb_batch_stage_timing": (_i, [_vp, _i]),
     "gforb_batch_stage_times": (_i, [_vp, _vp]),
     "gforb_matcher_create": (_i, [C.c_float, C.POINTER(_vp)]),
@@ -677,6 +678,10 @@ class StereoBatch:
     def set_chunk(self, frames):
         """process() pipelines H2D / kernels / D2H in chunks of `frames` stereo frames (0 = automatic)"""
         _check(_L.gforb_batch_set_chunk(self._h, int(frames)))
+
+    def debug_copy_only(self, on):
+        """measurement switch: process()/submit() move their bytes as usual but launch no kernel (copy-only ceiling)"""
+        _check(_L.gforb_batch_debug_copy_only(self._h, int(bool(on))))
 
     def reset_graphs(self):
         """drop the CUDA graphs cached for single-chunk process()/submit() calls (keyed on host pointer values)"""

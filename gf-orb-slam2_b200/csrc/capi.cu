@@ -51,6 +51,7 @@ struct gforb_batch {
     std::vector<cudaEvent_t> ev_up, ev_done;
     cudaEvent_t ev_start = nullptr, ev_down = nullptr;
     int chunk_frames = 0;        // 0 = automatic
+    bool copy_only = false;      // measurement switch: the pipeline's copies without its kernels (gforb_batch_debug_copy_only)
     int last_launches = 0;       // kernels enqueued by the last run / frames_batch call
     // Single-chunk calls (a frame or a few at a time: what a live Tracking does) are launch-bound -- 15 kernels, 7 copies
     // and a dozen event operations for ~0.25 ms of device work -- so their whole H2D -> kernels -> D2H sequence is
@@ -1373,6 +1374,11 @@ int gforb_batch_sync(gforb_batch* b) {
     return b->eng.check_errors(b->stream);
 }
 
+int gforb_batch_debug_copy_only(gforb_batch* b, int on) {
+    if (!b) return GFORB_ERR_ARG;
+    b->copy_only = on != 0;
+    return gforb_batch_reset_graphs(b);
+}
 int gforb_batch_reset_graphs(gforb_batch* b) {
     if (!b) return GFORB_ERR_ARG;
     for (auto& gs : b->graphs) if (gs.exec) cudaGraphExecDestroy(gs.exec);
@@ -1501,8 +1507,10 @@ int frames_enqueue(gforb_batch* b, const uint8_t* left, const uint8_t* right, in
         const int ks = c % b->kstreams;
         cudaStream_t sk = ks ? b->s_alt[ks - 1] : b->stream;
         GB(cudaStreamWaitEvent(sk, b->ev_up[c], 0), "cudaStreamWaitEvent");
-        int rc = enqueue_frames(b, f0, m, prm, sk, false);
-        if (rc) return rc;
+        if (!b->copy_only) {
+            int rc = enqueue_frames(b, f0, m, prm, sk, false);
+            if (rc) return rc;
+        }
         GB(cudaEventRecord(b->ev_done[c], sk), "cudaEventRecord");
         GB(cudaStreamWaitEvent(b->s_down, b->ev_done[c], 0), "cudaStreamWaitEvent");
         const size_t i0 = 2 * (size_t)f0, ni = 2 * (size_t)m;

@@ -35,7 +35,7 @@ struct Smem {
     uint32_t* key;      // [NC] sort keys
     int* order;         // [NC] node index by sorted rank
     uint8_t* split;     // [NC]
-    int* warp;          // [40] scan scratch
+    int* warp;          // [128] scan scratch
 };
 
 __device__ __forceinline__ Smem carve(uint8_t* base, int max_cand, int NC) {
@@ -54,7 +54,7 @@ __device__ __forceinline__ Smem carve(uint8_t* base, int max_cand, int NC) {
     s.key = (uint32_t*)take(4 * (size_t)NC);
     s.order = (int*)take(4 * (size_t)NC);
     s.split = (uint8_t*)take((size_t)NC);
-    s.warp = (int*)take(4 * 40);
+    s.warp = (int*)take(4 * 128);      // [0, 64): block_scan_pair's two buffers; [64, 104): block_excl_scan
     return s;
 }
 
@@ -93,6 +93,36 @@ __device__ int block_excl_scan(int* v, int n, int* scratch) {
     return total;
 }
 
+// One value per thread: exclusive prefix of v over the block, the block totals of v and of a second value w, ONE barrier.
+// scratch holds two buffers of 2 * kT / 32 ints used alternately (parity), so a warp that runs ahead into the next call
+// writes the other buffer while slower warps still read this one; a third call cannot start before every warp has
+// passed the second call's barrier.
+__device__ __forceinline__ int block_scan_pair(int v, int w, int* scratch, int& parity, int& v_total, int& w_total) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    constexpr int kW = kT / 32;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    const int wsum = __reduce_add_sync(0xffffffffu, w);
+    int* sc = scratch + parity * 2 * kW;
+    parity ^= 1;
+    if (lane == 31) { sc[wid] = inc; sc[kW + wid] = wsum; }
+    __syncthreads();
+    const int x = lane < kW ? sc[lane] : 0, y = lane < kW ? sc[kW + lane] : 0;
+    int xinc = x;
+#pragma unroll
+    for (int o = 1; o < kW; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, xinc, o);
+        if (lane >= o) xinc += t;
+    }
+    v_total = __shfl_sync(0xffffffffu, xinc, kW - 1);
+    w_total = __reduce_add_sync(0xffffffffu, y);
+    return __shfl_sync(0xffffffffu, xinc - x, wid) + inc - v;
+}
+
 __device__ __forceinline__ int quadrant(uint32_t p, short4 bx) {
     const int sx = bx.x + ((bx.y - bx.x + 1) >> 1);   // UL.x + ceil((UR.x-UL.x)/2)   (:483)
     const int sy = bx.z + ((bx.w - bx.z + 1) >> 1);   // UL.y + ceil((BR.y-UL.y)/2)   (:484)
@@ -112,18 +142,24 @@ namespace {
 size_t smem_bytes_for(int cap, int max_nodes) {
     auto r = [](size_t b) { return (b + 15) & ~(size_t)15; };
     const size_t mc = (size_t)cap, nc = (size_t)max_nodes;
-    return r(4 * mc) + r(2 * mc) + 2 * r(8 * nc) + 2 * r(4 * nc) + 2 * r(16 * nc) + 5 * r(4 * nc) + r(nc) + r(160);
+    return r(4 * mc) + r(2 * mc) + 2 * r(8 * nc) + 2 * r(4 * nc) + 2 * r(16 * nc) + 5 * r(4 * nc) + r(nc) + r(512);
 }
 }  // namespace
 
 // Two tiers: every (image, level) first runs with room for kSmallCap candidates (about 44 KB of shared memory: five
 // CTAs per SM instead of two -- the kernel is latency-bound, so residency is throughput); the rare pair that holds
 // more flags itself and is redone by a second launch with the full max_cand working set.
-constexpr int kSmallCap = 4096;
+#ifndef GFORB_OCT_SMALLCAP
+#define GFORB_OCT_SMALLCAP 4096
+#endif
+#ifndef GFORB_OCT_MINB
+#define GFORB_OCT_MINB 5
+#endif
+constexpr int kSmallCap = GFORB_OCT_SMALLCAP;
 int octree_small_cap(const Geom& g) { return g.max_cand > kSmallCap ? kSmallCap : g.max_cand; }
 size_t octree_smem_bytes(const Geom& g) { return smem_bytes_for(g.max_cand, g.max_nodes); }
 
-__global__ void __launch_bounds__(kT)
+__global__ void __launch_bounds__(kT, GFORB_OCT_MINB)
 octree_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_t* __restrict__ cell_pts,
               int32_t* __restrict__ lvl_cnt, uint32_t* __restrict__ lvl_pts, int32_t* __restrict__ err,
               int32_t* __restrict__ retry, int cap, int tier) {
@@ -143,20 +179,17 @@ octree_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_
     // ---- gather this level's FAST survivors in reference order (cell row-major, row-major inside) ----
     const uint32_t* ccnt = cell_cnt + (size_t)img * g.cells_total + L.cell_base;
     const uint32_t* cpts = cell_pts + ((size_t)img * g.cells_total + L.cell_base) * (size_t)g.cell_cap;
-    int n = 0;
+    int n = 0, parity = 0;
     for (int c0 = 0; c0 < L.ncells; c0 += kT) {
         const int c = c0 + threadIdx.x;
         const int mine = c < L.ncells ? (int)ccnt[c] : 0;
-        // block exclusive scan of `mine` through smem scratch s.a[0..kT)
-        s.a[threadIdx.x] = mine;
-        __syncthreads();
-        const int tot = block_excl_scan(s.a, kT, s.warp);
-        const int at = n + s.a[threadIdx.x];
+        int tot, unused;
+        const int at = n + block_scan_pair(mine, 0, s.warp, parity, tot, unused);      // one barrier per 256 cells
         if (n + tot <= cap)
             for (int k = 0; k < mine; ++k) s.pts[at + k] = cpts[(size_t)c * g.cell_cap + k];
         n += tot;
-        __syncthreads();
     }
+    __syncthreads();
     int32_t* out_cnt = lvl_cnt + (size_t)img * g.nlevels + l;
     uint32_t* out_pts = lvl_pts + (size_t)img * g.kstage + L.kbase;
     if (n > cap) {
@@ -192,7 +225,7 @@ octree_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_
     __syncthreads();
     for (int i = threadIdx.x; i < L.nIni; i += kT) s.a[i] = s.cnt[1][i] > 0 ? 1 : 0;
     __syncthreads();
-    S = block_excl_scan(s.a, L.nIni, s.warp);     // empty initial nodes are erased (:585-586)
+    S = block_excl_scan(s.a, L.nIni, s.warp + 64);// empty initial nodes are erased (:585-586)
     for (int i = threadIdx.x; i < L.nIni; i += kT)
         if (s.cnt[1][i] > 0) { s.box[0][s.a[i]] = s.box[1][i]; s.cnt[0][s.a[i]] = s.cnt[1][i]; }
     __syncthreads();
@@ -200,34 +233,75 @@ octree_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_
     __syncthreads();
 
     // ---- split passes ----
+    // Barriers are what this kernel waits on (ncu: 7 barrier-stall cycles per issued instruction), so a pass of the regular
+    // regime is four of them: count, one scan that carries (children before | unsplit before | nodes to expand) in a
+    // single sweep, build, move.  The child counters are cleared by the move step of the pass before.
     bool largest_first = false;
+    for (int i = threadIdx.x; i < 4 * S; i += kT) s.cnt4[i] = 0;
+    __syncthreads();
     for (;;) {
         short4* box = s.box[cur]; int* cnt = s.cnt[cur];
         short4* nbox = s.box[cur ^ 1]; int* ncnt = s.cnt[cur ^ 1];
 
         // A. speculative child counts of every splittable node
-        for (int i = threadIdx.x; i < 4 * S; i += kT) s.cnt4[i] = 0;
-        __syncthreads();
         for (int p = threadIdx.x; p < n; p += kT) {
             const int nd = s.pnode[p];
             if (cnt[nd] > 1) atomicAdd(&s.cnt4[4 * nd + quadrant(s.pts[p], box[nd])], 1);
         }
         __syncthreads();
 
-        // B. which nodes split, and in which creation order
-        int C, nsplit;
+        int C, S_new, nToExpand;
         if (!largest_first) {
-            for (int i = threadIdx.x; i < S; i += kT) {
+            // B + C. every node with more than one point splits, in list order (:606-665): a thread owns a contiguous run
+            // of nodes, the scan gives the children created / the unsplit nodes before its run
+            const int per = (S + kT - 1) / kT;
+            const int i0 = min((int)threadIdx.x * per, S), i1 = min(i0 + per, S);
+            int nch = 0, uns = 0, nexp = 0;
+            for (int i = i0; i < i1; ++i) {
+                if (cnt[i] > 1) {
+                    const int* c4 = s.cnt4 + 4 * i;
+                    nch += (c4[0] > 0) + (c4[1] > 0) + (c4[2] > 0) + (c4[3] > 0);
+                    nexp += (c4[0] > 1) + (c4[1] > 1) + (c4[2] > 1) + (c4[3] > 1);
+                } else ++uns;
+            }
+            int tot;
+            const int pre = block_scan_pair(nch | (uns << 16), nexp, s.warp, parity, tot, nToExpand);
+            C = tot & 0xFFFF;
+            S_new = C + (tot >> 16);
+            if (S_new > NC) {
+                if (threadIdx.x == 0) { atomicOr(err, kErrNodeOverflow); *out_cnt = 0; }
+                return;
+            }
+            int c = pre & 0xFFFF, u = pre >> 16;
+            for (int i = i0; i < i1; ++i) {
                 const bool sp = cnt[i] > 1;
                 s.split[i] = sp;
-                const int* c4 = s.cnt4 + 4 * i;
-                s.a[i] = sp ? (c4[0] > 0) + (c4[1] > 0) + (c4[2] > 0) + (c4[3] > 0) : 0;
+                if (sp) {
+                    const short4 bx = box[i];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int k = s.cnt4[4 * i + q];
+                        if (k > 0) {
+                            const int idx = C - 1 - c;
+                            nbox[idx] = child_box(bx, q);
+                            ncnt[idx] = k;
+                            s.remap[4 * i + q] = idx;
+                            ++c;
+                        }
+                    }
+                } else {
+                    const int idx = C + u;
+                    nbox[idx] = box[i];
+                    ncnt[idx] = cnt[i];
+                    s.keepmap[i] = idx;
+                    ++u;
+                }
             }
             __syncthreads();
-            C = block_excl_scan(s.a, S, s.warp);          // a[i] = children created before node i's
         } else {
             // candidates = nodes with >1 point (all were created by the previous pass), ordered by
             // (count desc, newest = smaller index first)  (:684-686)
+            int nsplit;
             for (int i = threadIdx.x; i < S; i += kT) {
                 s.key[i] = cnt[i] > 1 ? ((uint32_t)cnt[i] << 16) | (uint32_t)(0xFFFF - i) : 0u;
                 s.split[i] = 0;
@@ -256,7 +330,7 @@ octree_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_
             }
             if (threadIdx.x == 0) sh_flag = M;            // first rank whose commit reaches N
             __syncthreads();
-            block_excl_scan(s.b, M, s.warp);
+            block_excl_scan(s.b, M, s.warp + 64);
             for (int r = threadIdx.x; r < M; r += kT) {
                 const int after = S + s.b[r] + (s.a[r] - 1);
                 if (after >= N) atomicMin(&sh_flag, r);
@@ -265,58 +339,57 @@ octree_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_
             nsplit = min(sh_flag + 1, M);                 // break right after the split that reaches N (:729-730)
             for (int r = threadIdx.x; r < M; r += kT) if (r >= nsplit) s.a[r] = 0;
             __syncthreads();
-            C = block_excl_scan(s.a, M, s.warp);          // a[r] = children created before rank r's
+            C = block_excl_scan(s.a, M, s.warp + 64);     // a[r] = children created before rank r's
             // scatter creation prefix back to node indexing (keepmap doubles as scratch here)
             for (int r = threadIdx.x; r < nsplit; r += kT) { s.split[s.order[r]] = 1; s.keepmap[s.order[r]] = s.a[r]; }
             __syncthreads();
-            for (int i = threadIdx.x; i < S; i += kT) s.a[i] = s.split[i] ? s.keepmap[i] : 0;
+            for (int i = threadIdx.x; i < S; i += kT) { s.a[i] = s.split[i] ? s.keepmap[i] : 0; s.b[i] = s.split[i] ? 0 : 1; }
             __syncthreads();
-        }
-        for (int i = threadIdx.x; i < S; i += kT) s.b[i] = s.split[i] ? 0 : 1;
-        __syncthreads();
-        const int U = block_excl_scan(s.b, S, s.warp);    // b[i] = unsplit nodes before i
-        const int S_new = C + U;
-        if (S_new > NC) {
-            if (threadIdx.x == 0) { atomicOr(err, kErrNodeOverflow); *out_cnt = 0; }
-            return;
-        }
-
-        // C. build the next table in list order: children reversed, then unsplit nodes in old order
-        if (threadIdx.x == 0) sh_n = 0;
-        __syncthreads();
-        int expand_local = 0;
-        for (int i = threadIdx.x; i < S; i += kT) {
-            if (s.split[i]) {
-                int c = s.a[i];
-                const short4 bx = box[i];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int k = s.cnt4[4 * i + q];
-                    if (k > 0) {
-                        const int idx = C - 1 - c;
-                        nbox[idx] = child_box(bx, q);
-                        ncnt[idx] = k;
-                        s.remap[4 * i + q] = idx;
-                        expand_local += k > 1;
-                        ++c;
-                    }
-                }
-            } else {
-                const int idx = C + s.b[i];
-                nbox[idx] = box[i];
-                ncnt[idx] = cnt[i];
-                s.keepmap[i] = idx;
+            const int U = block_excl_scan(s.b, S, s.warp + 64);    // b[i] = unsplit nodes before i
+            S_new = C + U;
+            if (S_new > NC) {
+                if (threadIdx.x == 0) { atomicOr(err, kErrNodeOverflow); *out_cnt = 0; }
+                return;
             }
+            // C. build the next table in list order: children reversed, then unsplit nodes in old order
+            if (threadIdx.x == 0) sh_n = 0;
+            __syncthreads();
+            int expand_local = 0;
+            for (int i = threadIdx.x; i < S; i += kT) {
+                if (s.split[i]) {
+                    int c = s.a[i];
+                    const short4 bx = box[i];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int k = s.cnt4[4 * i + q];
+                        if (k > 0) {
+                            const int idx = C - 1 - c;
+                            nbox[idx] = child_box(bx, q);
+                            ncnt[idx] = k;
+                            s.remap[4 * i + q] = idx;
+                            expand_local += k > 1;
+                            ++c;
+                        }
+                    }
+                } else {
+                    const int idx = C + s.b[i];
+                    nbox[idx] = box[i];
+                    ncnt[idx] = cnt[i];
+                    s.keepmap[i] = idx;
+                }
+            }
+            if (expand_local) atomicAdd(&sh_n, expand_local);
+            __syncthreads();
+            nToExpand = sh_n;
         }
-        if (expand_local) atomicAdd(&sh_n, expand_local);
-        __syncthreads();
-        // D. move the points
+        // D. move the points; clear the child counters of the next pass (the old ones have been consumed)
         for (int p = threadIdx.x; p < n; p += kT) {
             const int nd = s.pnode[p];
             s.pnode[p] = (uint16_t)(s.split[nd] ? s.remap[4 * nd + quadrant(s.pts[p], box[nd])] : s.keepmap[nd]);
         }
-        const int nToExpand = sh_n;
         __syncthreads();
+        for (int i = threadIdx.x; i < 4 * S_new; i += kT) s.cnt4[i] = 0;
+        // (no barrier: the next reader of cnt4 is pass A's atomicAdd, behind the barrier below or the loop's first one)
 
         // E. termination (:667-672, :733-735)
         const int prevSize = S;
@@ -324,7 +397,9 @@ octree_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_
         cur ^= 1;
         if (S >= N || S == prevSize) break;
         if (!largest_first && S + 3 * nToExpand > N) largest_first = true;
+        __syncthreads();
     }
+    __syncthreads();
 
     // ---- best response per node, first in candidate order wins ties (:744-760) ----
     int* best_r = s.cnt4; int* best_i = s.remap;

@@ -506,6 +506,10 @@ GFORB_API int gforb_batch_set_chunk(gforb_batch* b, int frames);
  * buffer from pinned to pageable) must drop the cached graphs first; an argument set that cannot be captured (pageable
  * memory) is remembered as such and runs on plain launches without affecting the others. */
 GFORB_API int gforb_batch_reset_graphs(gforb_batch* b);
+/* measurement switch: gforb_stereo_frames_batch[_async] moves its chunks host -> device and the (stale) results device
+ * -> host exactly as usual -- same chunks, same streams, same events -- but launches no kernel.  What that runs at is
+ * the copy-only ceiling of the end-to-end path on the box at hand (bench.py reports e2e against it as e2e.link_frac). */
+GFORB_API int gforb_batch_debug_copy_only(gforb_batch* b, int on);
 /* kernels actually enqueued by the last gforb_batch_run / gforb_stereo_frames_batch call */
 GFORB_API int gforb_batch_last_launches(const gforb_batch* b);
 
