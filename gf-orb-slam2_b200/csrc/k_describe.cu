@@ -16,6 +16,10 @@
 // memory-level parallelism.
 // Also measured: the pattern as float in shared memory plus one 32-bit offset per gather -- 32 fewer I2F and ~50 fewer
 // address instructions per key, yet 0.59 ms against 0.54 ms (kept: int8 pattern, 64-bit IMAD.WIDE addressing).
+// Also measured (round 2): the 31 x 31 box staged in shared memory first (lane = row, three aligned LDG.128 per row, then
+// lane = column reading bytes at compile-time offsets: 130 fewer instructions per key, bit-identical) -- 0.655 ms against
+// 0.538 ms: the load -> store -> barrier -> load chain serialises what the 31 independent global loads overlap; CTAs
+// of 4 / 16 warps instead of 8: 0.68 / 0.65 ms.
 // LSU/gather-bound (SURVEY.md 8d K4+K5): algorithmic bytes = 961 (31x31 raw) + 1369 (37x37 blurred) + 60 out per key.
 #include <cfloat>
 
