@@ -487,6 +487,10 @@ def main():
     if ip.exists():
         int_peak = float(json.loads(ip.read_text())["rates"]["IADD3"]["gops"])
         int_src = "profiles/int_peaks_r1.json (IADD3 / IMAD / VABSDIFF4 / IDP4A thread-ops per second, microbenchmarked on this pool's B200)"
+    # instruction-issue ceiling: 4 schedulers x 32 lanes per SM and clock; the INT32 ALU pipe alone takes half of it
+    # (64 lanes/clk/SM: the microbenchmarked IADD3 / IMAD / VABSDIFF4 rate in profiles/int_peaks_r1.json)
+    sms = torch.cuda.get_device_properties(local_rank).multi_processor_count
+    issue_peak = sms * 128 * float((clocks or {}).get("sm_max_mhz") or 1965.0) * 1e6 / 1e9
     dom = max(stage_ms, key=stage_ms.get)
     stages = {}
     for k, t in stage_ms.items():
@@ -516,18 +520,21 @@ def main():
                         tops = 32.0 * sum(x["warp_inst"] for x in ks)
                         gops = tops / (stage_ms[k] * 1e-3) / 1e9
                         stages[k]["int_issue"] = {"thread_inst_per_launch": int(tops), "gops": round(gops, 1),
-                                                  "frac": round(gops / int_peak, 4)}
+                                                  "frac": round(gops / issue_peak, 4),
+                                                  "alu_pipe_frac": round(stages[k]["ncu_pipe_alu_pct"] / 100.0, 4)}
     ach = stages[dom]["gbs"]
     roofline = {"bound": STAGE_CLASS[dom], "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                 "traffic": stages[dom].get("ncu_dram_bytes"), "issue_active_pct": stages[dom].get("ncu_issue_active_pct"),
                 "int_pipe_alu_pct": stages[dom].get("ncu_pipe_alu_pct"),
-                "int_issue": dict(stages[dom].get("int_issue", {}), peak=int_peak, unit="G thread-inst/s", peak_source=int_src) if "int_issue" in stages[dom] else None,
+                "int_issue": dict(stages[dom].get("int_issue", {}), peak=round(issue_peak, 1), unit="G thread-inst/s",
+                                  peak_source="%d SMs x 4 schedulers x 32 lanes x max SM clock (issue slots)" % sms,
+                                  alu_pipe_peak=int_peak, alu_pipe_peak_source=int_src) if "int_issue" in stages[dom] else None,
                 "peak_source": peak_src, "launches_in_stage": "see stages",
                 "note": "bound = the stage's class in SURVEY.md 8(d) (pyramid / FAST / blur: hbm; descriptor / stereo: int_issue; quadtree: "
                         "latency); achieved / peak / frac are algorithmic bytes over the live CUDA-event time against the measured HBM "
                         "copy rate.  FAST is classed hbm there but measures instruction-issue bound (ncu: issue slots 80 % busy, DRAM 7 %), so "
-                        "its int_issue figure (thread-instructions from the committed ncu capture / live time / microbenchmarked INT32 "
-                        "thread-op rate) is the meaningful one; both fractions are under `stages` for every stage; traffic = "
+                        "its int_issue figure (thread-instructions from the committed ncu capture over the live time, against the "
+                        "issue-slot ceiling; alu_pipe_frac = share of the INT32 ALU pipe, whose own ceiling is half of that) is the meaningful one; both fractions are under `stages` for every stage; traffic = "
                         "dram__bytes_read+write per launch from profiles/ncu_latest.json"}
 
     ceiling = ceiling_live
