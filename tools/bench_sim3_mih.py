@@ -4,7 +4,8 @@
   * HASHING::MultiIndexHashing (gforb_mih_*): batched insertion and the Tracking-shaped query (8 active tables, 20
     entries each, src/Tracking.cc:3015) over descriptor batches.
 Prints one JSON line.  usage: python tools/bench_sim3_mih.py > profiles/sim3_mih_r2.json"""
-import importlib, json, sys, time
+import importlib, json, os, sys, time
+_OUT = os.dup(1); os.dup2(2, 1)      # the reference's MultiIndexHashing constructor prints on stdout: keep it to the one JSON line
 from pathlib import Path
 import numpy as np
 ROOT = Path(__file__).resolve().parent.parent
@@ -67,4 +68,4 @@ for T in (32, 16):
         assert np.array_equal(ok, ook) and np.array_equal(dn.to_host(), no) and np.array_equal(dc.to_host(), co)
         rec[f"cpu_{variant}_insert_ms"] = round(t_oi * 1e3, 1); rec[f"cpu_{variant}_query_ms"] = round(t_oq * 1e3, 1)
     out[f"mih_T{T}"] = rec
-print(json.dumps(out))
+os.write(_OUT, (json.dumps(out) + "\n").encode())
