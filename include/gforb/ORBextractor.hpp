@@ -189,6 +189,25 @@ public:
         if (vQueryKey) vQueryKey->assign(qkey.begin(), qkey.begin() + nq);
         return nmatches;
     }
+    // SearchBySim3 (src/ORBmatcher.cc:1214-1438) over queries the caller's preamble derives (Sim3 projection, IsInImage,
+    // distance invariance, PredictScale: :1259-1292, :1339-1372): queries12[i1] = map point i1 of KF1 in KF2
+    // (GFORB_PQ_ACTIVE or 0; levels nPredictedLevel - 1 .. nPredictedLevel; r = th * mvScaleFactors[level]), desc12 = the
+    // map points' descriptors; queries21 / desc21 the other way round.  vnMatches12[i1] = agreed key of KF2 or -1 (the
+    // reference then sets vpMatches12[i1] = vpMapPoints2[idx2]); returns nFound.
+    int SearchBySim3(const FrameView& KF1, const FrameView& KF2, const std::vector<gforb_proj_query>& queries12,
+                     const uint8_t* desc12, const std::vector<gforb_proj_query>& queries21, const uint8_t* desc21,
+                     std::vector<int>& vnMatches12, int thDist = TH_HIGH) {
+        const int n1 = (int)KF1.mvKeysUn->size(), n2 = (int)KF2.mvKeysUn->size();
+        if ((int)queries12.size() != n1 || (int)queries21.size() != n2)
+            throw std::invalid_argument("SearchBySim3: one query per map-point slot of each key frame");
+        vnMatches12.assign(n1, -1);
+        int nfound = 0;
+        check(gforb_search_by_sim3(handle(), &KF1.bounds, KF1.mvKeysUn->data(), KF1.mDescriptors, n1, KF2.mvKeysUn->data(),
+                                   KF2.mDescriptors, n2, queries12.data(), desc12, queries21.data(), desc21, thDist, nullptr,
+                                   nullptr, vnMatches12.data(), &nfound),
+              "SearchBySim3");
+        return nfound;
+    }
     // SearchByBoW (src/ORBmatcher.cc:270-404: valid2 = NULL, thDist = TH_LOW; :635-768: thDist = TH_LOW - 1).
     // FeatVecT = DBoW2::FeatureVector or any ordered map NodeId -> vector<unsigned>.  valid1 / valid2: one byte per
     // feature, != 0 where the MapPoint exists and is not bad (NULL = all).  vnMatches12[i] = feature of frame 2 matched
@@ -296,6 +315,41 @@ inline gforb_frame_bounds ComputeImageBounds(ORBmatcher& m, const gforb_camera& 
 
 // The pre-processing in front of the extractor: [16-bit -> 8-bit] -> cv::remap(M1, M2, INTER_LINEAR) -> cvtColor(*2GRAY)
 // (ros_stereo.cc:290-295, test_Stereo.cpp:197-210, src/Tracking.cc:366-382).  M1/M2: CV_32F maps of one camera.
+// HASHING::MultiIndexHashing (include/Hashing.h:171-216), the descriptor side, on the device.  Entries are int handles
+// (MapPoint::mnId); the caller keeps MapPoint::mvbHashed as one uint32_t per map point.
+class MultiIndexHashing {
+public:
+    explicit MultiIndexHashing(unsigned feature_length = 256, unsigned table_num = 32) : h_(nullptr), tables_((int)table_num) {
+        check(gforb_mih_create((int)feature_length, (int)table_num, &h_), "MultiIndexHashing");
+    }
+    ~MultiIndexHashing() { gforb_mih_destroy(h_); }
+    MultiIndexHashing(const MultiIndexHashing&) = delete;
+    MultiIndexHashing& operator=(const MultiIndexHashing&) = delete;
+    unsigned getSubstringLen() const { return (unsigned)gforb_mih_substring_len(h_); }
+    int updateDynamics(double e) { return gforb_mih_update_dynamics(h_, e); }
+    // insert(feature) for a batch, in order: desc = n x 32 bytes, ids[i] = mnId, hashed[i] = mvbHashed as bits (updated)
+    std::vector<uint8_t> insert(const uint8_t* desc, const std::vector<int32_t>& ids, std::vector<uint32_t>& hashed) {
+        std::vector<uint8_t> ok(ids.size());
+        hashed.resize(ids.size(), 0u);
+        if (!ids.empty()) check(gforb_mih_insert(h_, desc, ids.data(), (int)ids.size(), hashed.data(), ok.data()), "MultiIndexHashing::insert");
+        return ok;
+    }
+    // query(pDesc, candidates, nactive_tables, nretrieves) for m descriptors: candidates[q] = entry ids, table by table, newest first
+    void query(const uint8_t* desc, int m, std::vector<std::vector<int32_t> >& candidates, unsigned nactive_tables = 0,
+               unsigned nretrieves = 20) {
+        const int stride = (int)((nactive_tables ? nactive_tables : (unsigned)tables_) * nretrieves) + 1;
+        std::vector<int32_t> cand((size_t)m * stride), cnt(m > 0 ? m : 1);
+        if (m > 0) check(gforb_mih_query(h_, desc, m, (int)nactive_tables, (int)nretrieves, cand.data(), stride, cnt.data()), "MultiIndexHashing::query");
+        candidates.resize(m);
+        for (int q = 0; q < m; ++q) candidates[q].assign(cand.begin() + (size_t)q * stride, cand.begin() + (size_t)q * stride + cnt[q]);
+    }
+    gforb_mih* handle() const { return h_; }
+
+private:
+    gforb_mih* h_;
+    int tables_;
+};
+
 class Rectifier {
 public:
     Rectifier(const float* M1, const float* M2, int w, int h) : w_(w), h_(h) { check(gforb_rectifier_create(M1, M2, w, h, &h_r), "Rectifier"); }

@@ -84,6 +84,32 @@ int main(int argc, char** argv) {
         std::vector<std::pair<size_t, size_t> > pairs;
         const int ntri = bow.SearchForTriangulation(F1, nullptr, nullptr, fvL, F2, nullptr, nullptr, fvR, ep, pairs);
         printf("tri nmatches=%d pairs=%016llx\n", ntri, (unsigned long long)fnv(pairs.data(), pairs.size() * sizeof(pairs[0])));
+        // SearchBySim3 (src/ORBmatcher.cc:1214-1438): every key's own descriptor as its map point's, the two eyes as the two
+        // key frames, "projected" 25 px sideways, r = 30 * scale, levels octave - 1 .. octave
+        std::vector<gforb_proj_query> q12(kL.size()), q21(kR.size());
+        auto fill = [](const std::vector<gforb_keypoint>& k, float shift, std::vector<gforb_proj_query>& q) {
+            for (size_t i = 0; i < k.size(); ++i) {
+                float sc = 1.f;
+                for (int l = 0; l < k[i].octave; ++l) sc *= 1.2f;
+                q[i] = {k[i].x + shift, k[i].y, 30.f * sc, 0.f, 0.f, k[i].octave - 1, k[i].octave, GFORB_PQ_ACTIVE};
+            }
+        };
+        fill(kL, -25.f, q12); fill(kR, 25.f, q21);
+        std::vector<int> ms;
+        const int nsim = matcher.SearchBySim3(F1, F2, q12, dL.data(), q21, dR.data(), ms);
+        printf("sim3 nfound=%d ms=%016llx\n", nsim, (unsigned long long)fnv(ms.data(), ms.size() * 4));
+        // HASHING::MultiIndexHashing (include/Hashing.h:171-216): insert the left descriptors, query with the right ones
+        gforb::MultiIndexHashing mih(256, 32);
+        std::vector<int32_t> ids(kL.size());
+        for (size_t i = 0; i < ids.size(); ++i) ids[i] = (int32_t)(1000 + i);
+        std::vector<uint32_t> hashed;
+        const std::vector<uint8_t> okh = mih.insert(dL.data(), ids, hashed);
+        std::vector<std::vector<int32_t> > cands;
+        mih.query(dR.data(), (int)kR.size(), cands, 8, 20);
+        std::vector<int32_t> flat;
+        for (const auto& c : cands) { flat.push_back((int32_t)c.size()); flat.insert(flat.end(), c.begin(), c.end()); }
+        printf("mih bits=%u inserted=%d okh=%016llx cands=%016llx\n", mih.getSubstringLen(), (int)okh.size(),
+               (unsigned long long)fnv(okh.data(), okh.size()), (unsigned long long)fnv(flat.data(), flat.size() * 4));
         // an empty image is the reference's silent no-op
         std::vector<gforb_keypoint> k0; std::vector<uint8_t> d0;
         exL(nullptr, 0, 0, 0, k0, d0);

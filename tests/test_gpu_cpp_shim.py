@@ -83,6 +83,29 @@ def test_cpp_shim_matches_ctypes(fixtures):
     idx = np.nonzero(m12t >= 0)[0]
     pairs = np.stack([idx, m12t[idx]], axis=1).astype(np.uint64)
     assert int(mt[1]) == nt > 0 and int(hs["pairs"], 16) == _fnv(pairs)
+    # SearchBySim3 through the C++ mirror == the ctypes mirror
+    ms = re.search(r"sim3 nfound=(\d+) ", out.stdout)
+
+    def sq(k, shift):
+        o = np.zeros(len(k), gf.PROJ_QUERY_DTYPE)
+        scl = np.ones(len(k), np.float32)
+        for lvl in range(1, 8):
+            scl[k["octave"] >= lvl] *= np.float32(1.2)
+        o["x"], o["y"] = k["x"] + np.float32(shift), k["y"]
+        o["r"] = np.float32(30.0) * scl
+        o["min_level"], o["max_level"] = k["octave"] - 1, k["octave"]
+        o["flags"] = gf.PQ_ACTIVE
+        return o
+    nf, m12s, _, _ = gf.ORBmatcher(0.9, True).SearchBySim3(kL, dL, kR, dR, sq(kL, -25.0), dL, sq(kR, 25.0), dR, width=752, height=480)
+    assert int(ms[1]) == nf > 0 and int(hs["ms"], 16) == _fnv(m12s)
+    # MultiIndexHashing through the C++ mirror == the ctypes mirror
+    mm = re.search(r"mih bits=(\d+) inserted=(\d+) ", out.stdout)
+    g = gf.MultiIndexHashing(32)
+    okh, _ = g.insert(dL, np.arange(len(kL), dtype=np.int32) + 1000)
+    cand, cnt = g.query(dR, 8, 20)
+    flat = np.concatenate([np.concatenate([[c], row[:c]]) for row, c in zip(cand, cnt)]).astype(np.int32)
+    assert (int(mm[1]), int(mm[2])) == (8, len(kL))
+    assert int(hs["okh"], 16) == _fnv(okh) and int(hs["cands"], 16) == _fnv(flat)
 
 
 def test_tma_probe():
