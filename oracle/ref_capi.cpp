@@ -26,11 +26,15 @@ using namespace std;   // the reference's Frame.h is written under `using namesp
 namespace ORB_SLAM2 {
 float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv;
 float Frame::mnMinX, Frame::mnMaxX, Frame::mnMinY, Frame::mnMaxY;
+float Frame::fx, Frame::fy, Frame::cx, Frame::cy;
 #include "_ref/gen/frame_methods.inc"
+#include "_ref/gen/mappoint_methods.inc"
+#include "_ref/gen/keyframe_methods.inc"
 #include "_ref/gen/matcher_methods.inc"
 }  // namespace ORB_SLAM2
 
 using ORB_SLAM2::Frame;
+using ORB_SLAM2::KeyFrame;
 using ORB_SLAM2::MapPoint;
 using ORB_SLAM2::ORBmatcher;
 
@@ -434,6 +438,269 @@ int ref_search_by_projection_mp(const orc_keypoint* keys, const uint8_t* desc, c
         key_dist[k] = F.mvpMatchScore[k];
     }
     return nm;
+}
+
+}  // extern "C"
+
+// =====================================================================================================================
+// The pose-driven searches (round 2).  Everything the reference derives from poses and map points -- projections,
+// PredictScale, windows -- is derived HERE by the reference's own text from the scene the test hands over (camera,
+// poses, world points, per-point distance limits); tests/test_oracle_vs_ref_matchers.py derives the same queries in
+// numpy float32 for the restatement and the two must agree on every key.
+// Scene conventions: cam = {fx, fy, cx, cy, mbf, mb}; poses are 4x4 row-major float Tcw; a map point p has world xyz
+// wpos[3p..], descriptor pdesc[32p..], flags pflag[p] (1 = exists, 2 = bad, 4 = has observations), and distance limits
+// pdist[2p] = mfMinDistance, pdist[2p + 1] = mfMaxDistance.
+// =====================================================================================================================
+namespace {
+struct Scene {
+    vector<MapPoint> pts;
+    Scene(const float* wpos, const uint8_t* pdesc, const uint8_t* pflag, const float* pdist, const float* pnormal, int np) : pts((size_t)np) {
+        for (int p = 0; p < np; ++p) {
+            MapPoint& m = pts[p];
+            m.world_ = cv::Mat(3, 1, CV_32F);
+            for (int k = 0; k < 3; ++k) m.world_.at<float>(k) = wpos[3 * p + k];
+            if (pnormal) { m.normal_ = cv::Mat(3, 1, CV_32F); for (int k = 0; k < 3; ++k) m.normal_.at<float>(k) = pnormal[3 * p + k]; }
+            m.desc_ = cv::Mat(1, 32, CV_8UC1, (void*)(pdesc + 32 * (size_t)p), 32);
+            m.bad_ = (pflag[p] & 2) != 0;
+            m.nobs_ = (pflag[p] & 4) ? 1 : 0;
+            if (pdist) { m.mfMinDistance = pdist[2 * p]; m.mfMaxDistance = pdist[2 * p + 1]; }
+            m.tag_ = p;
+        }
+    }
+    MapPoint* at(int p, const uint8_t* pflag) { return (p >= 0 && (pflag[p] & 1)) ? &pts[p] : static_cast<MapPoint*>(NULL); }
+};
+cv::Mat pose(const float* T) {
+    cv::Mat m(4, 4, CV_32F);
+    for (int i = 0; i < 16; ++i) m.at<float>(i / 4, i % 4) = T[i];
+    return m;
+}
+void set_camera(const float* cam) { Frame::fx = cam[0]; Frame::fy = cam[1]; Frame::cx = cam[2]; Frame::cy = cam[3]; }
+void frame_scale(Frame& F, const float* sf, int nl) {
+    F.mvScaleFactors.assign(sf, sf + nl);
+    F.mnScaleLevels = nl;
+    F.mfLogScaleFactor = logf(sf[1]);                   // src/Frame.cc: mfLogScaleFactor = log(mfScaleFactor)
+}
+// src/KeyFrame.cc:36-67: the key frame copies the frame's keys, grid and scale tables
+void fill_keyframe(KeyFrame& K, const orc_keypoint* keys, const uint8_t* desc, int n, const float* cam, const float* sf, int nl) {
+    Frame F;
+    fill_frame(F, keys, desc, n);
+    K.N = n; K.mvKeysUn = F.mvKeysUn; K.mDescriptors = F.mDescriptors;
+    K.fx = cam[0]; K.fy = cam[1]; K.cx = cam[2]; K.cy = cam[3];
+    K.mfGridElementWidthInv = Frame::mfGridElementWidthInv; K.mfGridElementHeightInv = Frame::mfGridElementHeightInv;
+    K.mnMinX = (int)Frame::mnMinX; K.mnMinY = (int)Frame::mnMinY; K.mnMaxX = (int)Frame::mnMaxX; K.mnMaxY = (int)Frame::mnMaxY;
+    K.mGrid.resize(K.mnGridCols);
+    for (int i = 0; i < K.mnGridCols; ++i) {
+        K.mGrid[i].resize(K.mnGridRows);
+        for (int j = 0; j < K.mnGridRows; ++j) K.mGrid[i][j] = F.mGrid[i][j];
+    }
+    K.mvScaleFactors.assign(sf, sf + nl);
+    K.mvLevelSigma2.resize(nl);
+    for (int l = 0; l < nl; ++l) K.mvLevelSigma2[l] = sf[l] * sf[l];
+    K.mnScaleLevels = nl;
+    K.mfLogScaleFactor = logf(sf[1]);
+    K.mvuRight.assign((size_t)n, -1.f);
+}
+void set_pose(KeyFrame& K, const float* T) {            // src/KeyFrame.cc:84-103 (SetPose): Ow = -Rcw.t() * tcw
+    K.Tcw = pose(T);
+    cv::Mat Rcw = K.Tcw.rowRange(0, 3).colRange(0, 3), tcw = K.Tcw.rowRange(0, 3).col(3);
+    K.Ow = -Rcw.t() * tcw;
+}
+void featvec(DBoW2::FeatureVector& fv, const int* node_id, const int* node_start, const int* node_idx, int nn) {
+    for (int a = 0; a < nn; ++a)
+        fv[(unsigned)node_id[a]] = vector<unsigned>(node_idx + node_start[a], node_idx + node_start[a + 1]);
+}
+}  // namespace
+
+extern "C" {
+
+// SearchByProjection(CurrentFrame, LastFrame, th, bMono, numVisibleMpt) (src/ORBmatcher.cc:1440-1593).
+// last_point[i] = map point held by key i of the last frame (-1 none), last_outlier[i]; cur_point[k] = the point key k of the
+// current frame already holds (-1 none).  Out: key_point[k] = point held by key k afterwards (-1 none).
+int ref_search_by_projection_last(const orc_keypoint* ckeys, const uint8_t* cdesc, const float* cu_right, const int* cur_point, int n,
+                                  const orc_keypoint* lkeys, const int* last_point, const uint8_t* last_outlier, int nlast,
+                                  const float* bounds, const float* cam, const float* sf, int nl, const float* Tcw, const float* Tlw,
+                                  const float* wpos, const uint8_t* pdesc, const uint8_t* pflag, int np, float th, int bMono,
+                                  int checkOri, int* key_point) {
+    std::lock_guard<std::mutex> lock(g_frame_statics);
+    set_bounds(bounds);
+    set_camera(cam);
+    Scene S(wpos, pdesc, pflag, nullptr, nullptr, np);
+    Frame C, L;
+    fill_frame(C, ckeys, cdesc, n);
+    frame_scale(C, sf, nl);
+    C.mbf = cam[4]; C.mb = cam[5];
+    C.mTcw = pose(Tcw);
+    C.mvuRight.assign(cu_right, cu_right + n);
+    C.mvpMapPoints.resize((size_t)n);
+    for (int k = 0; k < n; ++k) C.mvpMapPoints[k] = S.at(cur_point[k], pflag);
+    fill_frame(L, lkeys, nullptr, nlast);
+    L.mTcw = pose(Tlw);
+    L.mvpMapPoints.resize((size_t)nlast);
+    L.mvbOutlier.resize((size_t)nlast);
+    for (int i = 0; i < nlast; ++i) { L.mvpMapPoints[i] = S.at(last_point[i], pflag); L.mvbOutlier[i] = last_outlier[i] != 0; }
+    ORBmatcher matcher(0.9f, checkOri != 0);
+    double vis = 0;
+    const int nm = matcher.SearchByProjection(C, L, th, bMono != 0, vis);
+    for (int k = 0; k < n; ++k) key_point[k] = C.mvpMapPoints[k] ? C.mvpMapPoints[k]->tag_ : -1;
+    return nm;
+}
+
+// SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (:1595-1721).  kf_point[i] = point of key i of the
+// key frame; already[p] != 0: in sAlreadyFound.
+int ref_search_by_projection_kf(const orc_keypoint* ckeys, const uint8_t* cdesc, const int* cur_point, int n,
+                                const orc_keypoint* kkeys, const int* kf_point, int nkf, const uint8_t* already,
+                                const float* bounds, const float* cam, const float* sf, int nl, const float* Tcw,
+                                const float* wpos, const uint8_t* pdesc, const uint8_t* pflag, const float* pdist, int np,
+                                float th, int ORBdist, int checkOri, int* key_point) {
+    std::lock_guard<std::mutex> lock(g_frame_statics);
+    set_bounds(bounds);
+    set_camera(cam);
+    Scene S(wpos, pdesc, pflag, pdist, nullptr, np);
+    Frame C;
+    fill_frame(C, ckeys, cdesc, n);
+    frame_scale(C, sf, nl);
+    C.mTcw = pose(Tcw);
+    C.mvpMapPoints.resize((size_t)n);
+    for (int k = 0; k < n; ++k) C.mvpMapPoints[k] = S.at(cur_point[k], pflag);
+    KeyFrame K;
+    fill_keyframe(K, kkeys, nullptr, nkf, cam, sf, nl);
+    K.mvpMapPoints.resize((size_t)nkf);
+    for (int i = 0; i < nkf; ++i) K.mvpMapPoints[i] = S.at(kf_point[i], pflag);
+    std::set<MapPoint*> found;
+    for (int p = 0; p < np; ++p) if (already[p]) found.insert(&S.pts[p]);
+    ORBmatcher matcher(0.9f, checkOri != 0);
+    const int nm = matcher.SearchByProjection(C, &K, found, th, ORBdist);
+    for (int k = 0; k < n; ++k) key_point[k] = C.mvpMapPoints[k] ? C.mvpMapPoints[k]->tag_ : -1;
+    return nm;
+}
+
+// SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (:406-518, loop closing).  points[j] = candidate map points in
+// order; matched_in[k] = point already matched to key k (-1 none).  Out: matched[k].
+int ref_search_by_projection_loop(const orc_keypoint* kkeys, const uint8_t* kdesc, int nkf, const float* bounds, const float* cam,
+                                  const float* sf, int nl, const float* Scw, const int* points, int npts, const int* matched_in,
+                                  const float* wpos, const uint8_t* pdesc, const uint8_t* pflag, const float* pdist,
+                                  const float* pnormal, int np, int th, int* matched) {
+    std::lock_guard<std::mutex> lock(g_frame_statics);
+    set_bounds(bounds);
+    Scene S(wpos, pdesc, pflag, pdist, pnormal, np);
+    KeyFrame K;
+    fill_keyframe(K, kkeys, kdesc, nkf, cam, sf, nl);
+    vector<MapPoint*> vp((size_t)npts), vm((size_t)nkf);
+    for (int j = 0; j < npts; ++j) vp[j] = S.at(points[j], pflag);
+    for (int k = 0; k < nkf; ++k) vm[k] = S.at(matched_in[k], pflag);
+    ORBmatcher matcher(0.75f, true);
+    const int nm = matcher.SearchByProjection(&K, pose(Scw), vp, vm, th);
+    for (int k = 0; k < nkf; ++k) matched[k] = vm[k] ? vm[k]->tag_ : -1;
+    return nm;
+}
+
+// SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th) (:1214-1438).  kfX_point[i] = point of key i; matches_in[i1] =
+// point already matched to key i1 of KF1 (-1), whose index in KF2 is its obs2[p] (-1: not observed there).
+int ref_search_by_sim3(const orc_keypoint* k1, const uint8_t* d1, const int* kf1_point, int n1, const orc_keypoint* k2,
+                       const uint8_t* d2, const int* kf2_point, int n2, const float* bounds, const float* cam, const float* sf, int nl,
+                       const float* T1w, const float* T2w, float s12, const float* R12, const float* t12, const int* matches_in,
+                       const int* obs2, const float* wpos, const uint8_t* pdesc, const uint8_t* pflag, const float* pdist, int np,
+                       float th, int* matches12) {
+    std::lock_guard<std::mutex> lock(g_frame_statics);
+    set_bounds(bounds);
+    Scene S(wpos, pdesc, pflag, pdist, nullptr, np);
+    KeyFrame K1, K2;
+    fill_keyframe(K1, k1, d1, n1, cam, sf, nl);
+    fill_keyframe(K2, k2, d2, n2, cam, sf, nl);
+    set_pose(K1, T1w); set_pose(K2, T2w);
+    K1.mvpMapPoints.resize((size_t)n1); K2.mvpMapPoints.resize((size_t)n2);
+    for (int i = 0; i < n1; ++i) K1.mvpMapPoints[i] = S.at(kf1_point[i], pflag);
+    for (int i = 0; i < n2; ++i) K2.mvpMapPoints[i] = S.at(kf2_point[i], pflag);
+    for (int p = 0; p < np; ++p) if (obs2[p] >= 0) S.pts[p].obs_[&K2] = (size_t)obs2[p];
+    vector<MapPoint*> vm((size_t)n1);
+    for (int i = 0; i < n1; ++i) vm[i] = S.at(matches_in[i], pflag);
+    cv::Mat R(3, 3, CV_32F), t(3, 1, CV_32F);
+    for (int i = 0; i < 9; ++i) R.at<float>(i / 3, i % 3) = R12[i];
+    for (int i = 0; i < 3; ++i) t.at<float>(i) = t12[i];
+    ORBmatcher matcher(0.75f, true);
+    const int nf = matcher.SearchBySim3(&K1, &K2, vm, s12, R, t, th);
+    for (int i = 0; i < n1; ++i) matches12[i] = vm[i] ? vm[i]->tag_ : -1;
+    return nf;
+}
+
+// SearchByBoW(pKF, F, vpMapPointMatches) (:270-404): kf_point[i] = point of key i of the key frame; out f_point[k].
+int ref_search_by_bow_kf_f(const orc_keypoint* kk, const uint8_t* kd, const int* kf_point, int nkf, const int* id1, const int* st1,
+                           const int* ix1, int nn1, const orc_keypoint* fk, const uint8_t* fd, int nf, const int* id2,
+                           const int* st2, const int* ix2, int nn2, const float* bounds, const uint8_t* pdesc,
+                           const uint8_t* pflag, int np, float nnratio, int checkOri, int* f_point) {
+    std::lock_guard<std::mutex> lock(g_frame_statics);
+    set_bounds(bounds);
+    vector<float> zero((size_t)3 * (np > 0 ? np : 1), 0.f);
+    Scene S(zero.data(), pdesc, pflag, nullptr, nullptr, np);
+    const float cam[6] = {1, 1, 0, 0, 0, 0}, sf[2] = {1.f, 1.2f};
+    KeyFrame K;
+    fill_keyframe(K, kk, kd, nkf, cam, sf, 2);
+    K.mvpMapPoints.resize((size_t)nkf);
+    for (int i = 0; i < nkf; ++i) K.mvpMapPoints[i] = S.at(kf_point[i], pflag);
+    featvec(K.mFeatVec, id1, st1, ix1, nn1);
+    Frame F;
+    fill_frame(F, fk, fd, nf);
+    featvec(F.mFeatVec, id2, st2, ix2, nn2);
+    vector<MapPoint*> vm;
+    ORBmatcher matcher(nnratio, checkOri != 0);
+    const int nm = matcher.SearchByBoW(&K, F, vm);
+    for (int k = 0; k < nf; ++k) f_point[k] = vm[k] ? vm[k]->tag_ : -1;
+    return nm;
+}
+
+// SearchByBoW(pKF1, pKF2, vpMatches12) (:635-768): out matches12[i1] = point of KF2 matched to key i1.
+int ref_search_by_bow_kf_kf(const orc_keypoint* k1, const uint8_t* d1, const int* kf1_point, int n1, const int* id1, const int* st1,
+                            const int* ix1, int nn1, const orc_keypoint* k2, const uint8_t* d2, const int* kf2_point, int n2,
+                            const int* id2, const int* st2, const int* ix2, int nn2, const float* bounds, const uint8_t* pdesc,
+                            const uint8_t* pflag, int np, float nnratio, int checkOri, int* matches12) {
+    std::lock_guard<std::mutex> lock(g_frame_statics);
+    set_bounds(bounds);
+    vector<float> zero((size_t)3 * (np > 0 ? np : 1), 0.f);
+    Scene S(zero.data(), pdesc, pflag, nullptr, nullptr, np);
+    const float cam[6] = {1, 1, 0, 0, 0, 0}, sf[2] = {1.f, 1.2f};
+    KeyFrame K1, K2;
+    fill_keyframe(K1, k1, d1, n1, cam, sf, 2);
+    fill_keyframe(K2, k2, d2, n2, cam, sf, 2);
+    K1.mvpMapPoints.resize((size_t)n1); K2.mvpMapPoints.resize((size_t)n2);
+    for (int i = 0; i < n1; ++i) K1.mvpMapPoints[i] = S.at(kf1_point[i], pflag);
+    for (int i = 0; i < n2; ++i) K2.mvpMapPoints[i] = S.at(kf2_point[i], pflag);
+    featvec(K1.mFeatVec, id1, st1, ix1, nn1);
+    featvec(K2.mFeatVec, id2, st2, ix2, nn2);
+    vector<MapPoint*> vm;
+    ORBmatcher matcher(nnratio, checkOri != 0);
+    const int nm = matcher.SearchByBoW(&K1, &K2, vm);
+    for (int i = 0; i < n1; ++i) matches12[i] = vm[i] ? vm[i]->tag_ : -1;
+    return nm;
+}
+
+// SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (:770-935).  kfX_has_point[i] != 0: the key holds a map
+// point (it is skipped); out pairs[2j], pairs[2j + 1]; returns the number of pairs.
+int ref_search_for_triangulation(const orc_keypoint* k1, const uint8_t* d1, const uint8_t* has1, const float* ur1, int n1,
+                                 const int* id1, const int* st1, const int* ix1, int nn1, const orc_keypoint* k2, const uint8_t* d2,
+                                 const uint8_t* has2, const float* ur2, int n2, const int* id2, const int* st2, const int* ix2, int nn2,
+                                 const float* bounds, const float* cam, const float* sf, int nl, const float* T1w, const float* T2w,
+                                 const float* F12, int bOnlyStereo, int checkOri, int* pairs, int cap) {
+    std::lock_guard<std::mutex> lock(g_frame_statics);
+    set_bounds(bounds);
+    KeyFrame K1, K2;
+    fill_keyframe(K1, k1, d1, n1, cam, sf, nl);
+    fill_keyframe(K2, k2, d2, n2, cam, sf, nl);
+    set_pose(K1, T1w); set_pose(K2, T2w);
+    MapPoint held;
+    K1.mvpMapPoints.resize((size_t)n1); K2.mvpMapPoints.resize((size_t)n2);
+    for (int i = 0; i < n1; ++i) K1.mvpMapPoints[i] = has1[i] ? &held : static_cast<MapPoint*>(NULL);
+    for (int i = 0; i < n2; ++i) K2.mvpMapPoints[i] = has2[i] ? &held : static_cast<MapPoint*>(NULL);
+    K1.mvuRight.assign(ur1, ur1 + n1); K2.mvuRight.assign(ur2, ur2 + n2);
+    featvec(K1.mFeatVec, id1, st1, ix1, nn1);
+    featvec(K2.mFeatVec, id2, st2, ix2, nn2);
+    cv::Mat F(3, 3, CV_32F);
+    for (int i = 0; i < 9; ++i) F.at<float>(i / 3, i % 3) = F12[i];
+    vector<pair<size_t, size_t> > vp;
+    ORBmatcher matcher(0.6f, checkOri != 0);
+    const int nm = matcher.SearchForTriangulation(&K1, &K2, F, vp, bOnlyStereo != 0);
+    for (int j = 0; j < (int)vp.size() && j < cap; ++j) { pairs[2 * j] = (int)vp[j].first; pairs[2 * j + 1] = (int)vp[j].second; }
+    (void)nm;
+    return (int)vp.size();
 }
 
 }  // extern "C"

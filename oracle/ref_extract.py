@@ -2,7 +2,7 @@
 """ORACLE -- TEST INFRASTRUCTURE ONLY.
 
 Lifts whole member-function definitions, by line range and verbatim, out of the reference's src/Frame.cc,
-include/Frame.h and src/ORBmatcher.cc into include files under oracle/_ref/gen/ (git-ignored: reference TEXT never
+include/Frame.h, src/ORBmatcher.cc, src/MapPoint.cc and src/KeyFrame.cc into include files under oracle/_ref/gen/ (git-ignored: reference TEXT never
 enters the repository).  oracle/ref_capi.cpp compiles them against the stand-in class declarations of
 oracle/ref_stub.hpp.  Those two translation-unit-sized files cannot be compiled whole here: they pull in DBoW2,
 Eigen, Armadillo, g2o and ROS headers through Tracking.h / KeyFrame.h, none of which this image has.
@@ -32,8 +32,23 @@ RANGES = [
     ("matcher_methods.inc", "src/ORBmatcher.cc", 155, 241, "int ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint *> &vpMapPoints, const float th)", "}"),
     ("matcher_methods.inc", "src/ORBmatcher.cc", 243, 249, "float ORBmatcher::RadiusByViewingCos(", "}"),
     ("matcher_methods.inc", "src/ORBmatcher.cc", 520, 633, "int ORBmatcher::SearchForInitialization(", "}"),
+    ("matcher_methods.inc", "src/ORBmatcher.cc", 251, 268, "bool ORBmatcher::CheckDistEpipolarLine(", "}"),
+    ("matcher_methods.inc", "src/ORBmatcher.cc", 270, 404, "int ORBmatcher::SearchByBoW(KeyFrame *pKF, Frame &F, vector<MapPoint *> &vpMapPointMatches)", "}"),
+    ("matcher_methods.inc", "src/ORBmatcher.cc", 406, 518, "int ORBmatcher::SearchByProjection(KeyFrame *pKF, cv::Mat Scw, const vector<MapPoint *> &vpPoints, vector<MapPoint *> &vpMatched, int th)", "}"),
+    ("matcher_methods.inc", "src/ORBmatcher.cc", 635, 768, "int ORBmatcher::SearchByBoW(KeyFrame *pKF1, KeyFrame *pKF2, vector<MapPoint *> &vpMatches12)", "}"),
+    ("matcher_methods.inc", "src/ORBmatcher.cc", 770, 935, "int ORBmatcher::SearchForTriangulation(KeyFrame *pKF1, KeyFrame *pKF2, cv::Mat F12,", "}"),
+    ("matcher_methods.inc", "src/ORBmatcher.cc", 1214, 1438, "int ORBmatcher::SearchBySim3(KeyFrame *pKF1, KeyFrame *pKF2, vector<MapPoint *> &vpMatches12,", "}"),
+    ("matcher_methods.inc", "src/ORBmatcher.cc", 1440, 1593, "int ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame,", "}"),
+    ("matcher_methods.inc", "src/ORBmatcher.cc", 1595, 1721, "int ORBmatcher::SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, const set<MapPoint *> &sAlreadyFound, const float th, const int ORBdist)", "}"),
     ("matcher_methods.inc", "src/ORBmatcher.cc", 1723, 1764, "void ORBmatcher::ComputeThreeMaxima(", "}"),
     ("matcher_methods.inc", "src/ORBmatcher.cc", 1768, 1784, "int ORBmatcher::DescriptorDistance(", "}"),
+    # --- src/MapPoint.cc, src/KeyFrame.cc: the small accessors the lifted searches call
+    ("mappoint_methods.inc", "src/MapPoint.cc", 530, 534, "float MapPoint::GetMinDistanceInvariance()", "}"),
+    ("mappoint_methods.inc", "src/MapPoint.cc", 536, 540, "float MapPoint::GetMaxDistanceInvariance()", "}"),
+    ("mappoint_methods.inc", "src/MapPoint.cc", 542, 557, "int MapPoint::PredictScale(const float &currentDist, KeyFrame* pKF)", "}"),
+    ("mappoint_methods.inc", "src/MapPoint.cc", 559, 574, "int MapPoint::PredictScale(const float &currentDist, Frame* pF)", "}"),
+    ("keyframe_methods.inc", "src/KeyFrame.cc", 877, 916, "vector<size_t> KeyFrame::GetFeaturesInArea(const float &x, const float &y, const float &r) const", "}"),
+    ("keyframe_methods.inc", "src/KeyFrame.cc", 918, 921, "bool KeyFrame::IsInImage(const float &x, const float &y) const", "}"),
 ]
 
 

@@ -140,6 +140,22 @@ public:
     Mat rowRange(int a, int b) const { return view(a, b, 0, cols); }
     Mat colRange(int a, int b) const { return view(0, rows, a, b); }
     Mat row(int y) const { return view(y, y + 1, 0, cols); }
+    Mat col(int x) const { return view(0, rows, x, x + 1); }
+    // CV_32F only, as the pose algebra of src/ORBmatcher.cc needs it (-Rcw.t() * tcw, sRcw.row(0).dot(sRcw.row(0)), ...)
+    Mat t() const {
+        assert(type_ == CV_32F);
+        Mat m(cols, rows, CV_32F);
+        for (int y = 0; y < rows; ++y)
+            for (int x = 0; x < cols; ++x) m.at<float>(x, y) = at<float>(y, x);
+        return m;
+    }
+    double dot(const Mat& o) const {           // cv::Mat::dot on CV_32F accumulates in double
+        assert(type_ == CV_32F && o.type_ == CV_32F && rows * cols == o.rows * o.cols);
+        double s = 0;
+        for (int y = 0; y < rows; ++y)
+            for (int x = 0; x < cols; ++x) s += (double)at<float>(y, x) * (double)o.at<float>(rows == o.rows ? y : x, rows == o.rows ? x : y);
+        return s;
+    }
     Mat clone() const {
         Mat m(rows, cols, type_);
         for (int y = 0; y < rows; ++y) std::memcpy(m.data + (size_t)y * m.step, data + (size_t)y * step, (size_t)cols * elemSize());
@@ -227,6 +243,44 @@ inline Mat operator+(const Mat& a, const Mat& b) {
     for (int y = 0; y < a.rows; ++y)
         for (int x = 0; x < a.cols; ++x) out.at<float>(y, x) = a.at<float>(y, x) + b.at<float>(y, x);
     return out;
+}
+
+inline Mat operator-(const Mat& a) {
+    assert(a.type() == CV_32F);
+    Mat out(a.rows, a.cols, CV_32F);
+    for (int y = 0; y < a.rows; ++y)
+        for (int x = 0; x < a.cols; ++x) out.at<float>(y, x) = -a.at<float>(y, x);
+    return out;
+}
+inline Mat operator-(const Mat& a, const Mat& b) {
+    assert(a.type() == CV_32F && b.type() == CV_32F && a.rows == b.rows && a.cols == b.cols);
+    Mat out(a.rows, a.cols, CV_32F);
+    for (int y = 0; y < a.rows; ++y)
+        for (int x = 0; x < a.cols; ++x) out.at<float>(y, x) = a.at<float>(y, x) - b.at<float>(y, x);
+    return out;
+}
+// scalar * matrix and matrix / scalar on CV_32F: the element times (divided by) the double scalar, rounded to float
+inline Mat operator*(double s, const Mat& a) {
+    assert(a.type() == CV_32F);
+    Mat out(a.rows, a.cols, CV_32F);
+    for (int y = 0; y < a.rows; ++y)
+        for (int x = 0; x < a.cols; ++x) out.at<float>(y, x) = (float)((double)a.at<float>(y, x) * s);
+    return out;
+}
+inline Mat operator/(const Mat& a, double s) {
+    assert(a.type() == CV_32F);
+    Mat out(a.rows, a.cols, CV_32F);
+    for (int y = 0; y < a.rows; ++y)
+        for (int x = 0; x < a.cols; ++x) out.at<float>(y, x) = (float)((double)a.at<float>(y, x) / s);
+    return out;
+}
+// cv::norm(a) = NORM_L2 on CV_32F: square root of the sum of squares accumulated in double
+inline double norm(const Mat& a) {
+    assert(a.type() == CV_32F);
+    double s = 0;
+    for (int y = 0; y < a.rows; ++y)
+        for (int x = 0; x < a.cols; ++x) s += (double)a.at<float>(y, x) * (double)a.at<float>(y, x);
+    return std::sqrt(s);
 }
 
 // cv::norm(a, b, NORM_L1) on CV_32F: sum of |a - b| accumulated in double (src/Frame.cc:1021)
