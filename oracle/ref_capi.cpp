@@ -623,6 +623,60 @@ int ref_search_by_sim3(const orc_keypoint* k1, const uint8_t* d1, const int* kf1
     return nf;
 }
 
+// Fuse(pKF, vpMapPoints, th) (:937-1087).  points[j] = candidate map points in order (-1 = NULL); kf_point[k] = point key k
+// holds; in_kf[p] != 0: the point is already observed by the key frame.  The surgery at the end is logged:
+// events[3e..] = {kind (0 AddObservation, 1 Replace), point, key index / other point}; returns nFused, *nevents.
+int ref_fuse(const orc_keypoint* kkeys, const uint8_t* kdesc, const float* ur, const int* kf_point, int nkf, const float* bounds,
+             const float* cam, const float* sf, int nl, const float* Tcw, const int* points, int npts, const uint8_t* in_kf,
+             const float* wpos, const uint8_t* pdesc, const uint8_t* pflag, const float* pdist, const float* pnormal, int np,
+             float th, int* events, int cap, int* nevents) {
+    std::lock_guard<std::mutex> lock(g_frame_statics);
+    set_bounds(bounds);
+    Scene S(wpos, pdesc, pflag, pdist, pnormal, np);
+    KeyFrame K;
+    fill_keyframe(K, kkeys, kdesc, nkf, cam, sf, nl);
+    set_pose(K, Tcw);
+    K.mbf = cam[4];
+    K.mvuRight.assign(ur, ur + nkf);
+    K.mvInvLevelSigma2.resize(nl);
+    for (int l = 0; l < nl; ++l) K.mvInvLevelSigma2[l] = 1.0f / K.mvLevelSigma2[l];      // src/ORBextractor.cc:429
+    K.mvpMapPoints.resize((size_t)nkf);
+    for (int k = 0; k < nkf; ++k) K.mvpMapPoints[k] = S.at(kf_point[k], pflag);
+    for (int p = 0; p < np; ++p) if (in_kf[p]) S.pts[p].obs_[&K] = 0;
+    vector<MapPoint*> vp((size_t)npts);
+    for (int j = 0; j < npts; ++j) vp[j] = S.at(points[j], pflag);
+    MapPoint::fuse_log().clear();
+    ORBmatcher matcher(0.6f, true);
+    const int nf = matcher.Fuse(&K, vp, th);
+    const vector<MapPoint::FuseEvent>& log = MapPoint::fuse_log();
+    *nevents = (int)log.size();
+    for (int e = 0; e < (int)log.size() && e < cap; ++e) { events[3 * e] = log[e].kind; events[3 * e + 1] = log[e].point; events[3 * e + 2] = log[e].other; }
+    return nf;
+}
+
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:397-462) for npoints map points: point p is observed by
+// set_start[p + 1] - set_start[p] key frames, observation j holding descriptor desc[32 * (set_start[p] + j)] (kf_bad[...]
+// != 0: that key frame is bad and skipped).  The reference walks std::map<KeyFrame*, size_t>, i.e. by key-frame address:
+// the stand-in key frames live in one vector, so that order is the caller's.  Out: best[32p..] = mDescriptor (zeros when
+// the reference returns early), has[p].
+int ref_distinctive_descriptors(const uint8_t* desc, const int* set_start, const uint8_t* kf_bad, int npoints, uint8_t* best, uint8_t* has) {
+    for (int p = 0; p < npoints; ++p) {
+        const int a = set_start[p], n = set_start[p + 1] - a;
+        vector<KeyFrame> kfs((size_t)(n > 0 ? n : 1));
+        MapPoint mp;
+        for (int j = 0; j < n; ++j) {
+            kfs[j].mDescriptors = cv::Mat(1, 32, CV_8UC1, (void*)(desc + 32 * (size_t)(a + j)), 32);
+            kfs[j].bad_ = kf_bad && kf_bad[a + j];
+            mp.mObservations[&kfs[j]] = 0;
+        }
+        mp.ComputeDistinctiveDescriptors();
+        has[p] = !mp.mDescriptor.empty();
+        std::memset(best + 32 * (size_t)p, 0, 32);
+        if (has[p]) std::memcpy(best + 32 * (size_t)p, mp.mDescriptor.ptr(0), 32);
+    }
+    return 0;
+}
+
 // SearchByBoW(pKF, F, vpMapPointMatches) (:270-404): kf_point[i] = point of key i of the key frame; out f_point[k].
 int ref_search_by_bow_kf_f(const orc_keypoint* kk, const uint8_t* kd, const int* kf_point, int nkf, const int* id1, const int* st1,
                            const int* ix1, int nn1, const orc_keypoint* fk, const uint8_t* fd, int nf, const int* id2,

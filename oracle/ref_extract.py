@@ -37,12 +37,14 @@ RANGES = [
     ("matcher_methods.inc", "src/ORBmatcher.cc", 406, 518, "int ORBmatcher::SearchByProjection(KeyFrame *pKF, cv::Mat Scw, const vector<MapPoint *> &vpPoints, vector<MapPoint *> &vpMatched, int th)", "}"),
     ("matcher_methods.inc", "src/ORBmatcher.cc", 635, 768, "int ORBmatcher::SearchByBoW(KeyFrame *pKF1, KeyFrame *pKF2, vector<MapPoint *> &vpMatches12)", "}"),
     ("matcher_methods.inc", "src/ORBmatcher.cc", 770, 935, "int ORBmatcher::SearchForTriangulation(KeyFrame *pKF1, KeyFrame *pKF2, cv::Mat F12,", "}"),
+    ("matcher_methods.inc", "src/ORBmatcher.cc", 937, 1087, "int ORBmatcher::Fuse(KeyFrame *pKF, const vector<MapPoint *> &vpMapPoints, const float th)", "}"),
     ("matcher_methods.inc", "src/ORBmatcher.cc", 1214, 1438, "int ORBmatcher::SearchBySim3(KeyFrame *pKF1, KeyFrame *pKF2, vector<MapPoint *> &vpMatches12,", "}"),
     ("matcher_methods.inc", "src/ORBmatcher.cc", 1440, 1593, "int ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame,", "}"),
     ("matcher_methods.inc", "src/ORBmatcher.cc", 1595, 1721, "int ORBmatcher::SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, const set<MapPoint *> &sAlreadyFound, const float th, const int ORBdist)", "}"),
     ("matcher_methods.inc", "src/ORBmatcher.cc", 1723, 1764, "void ORBmatcher::ComputeThreeMaxima(", "}"),
     ("matcher_methods.inc", "src/ORBmatcher.cc", 1768, 1784, "int ORBmatcher::DescriptorDistance(", "}"),
     # --- src/MapPoint.cc, src/KeyFrame.cc: the small accessors the lifted searches call
+    ("mappoint_methods.inc", "src/MapPoint.cc", 397, 462, "void MapPoint::ComputeDistinctiveDescriptors()", "}"),
     ("mappoint_methods.inc", "src/MapPoint.cc", 530, 534, "float MapPoint::GetMinDistanceInvariance()", "}"),
     ("mappoint_methods.inc", "src/MapPoint.cc", 536, 540, "float MapPoint::GetMaxDistanceInvariance()", "}"),
     ("mappoint_methods.inc", "src/MapPoint.cc", 542, 557, "int MapPoint::PredictScale(const float &currentDist, KeyFrame* pKF)", "}"),

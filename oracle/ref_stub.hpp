@@ -49,17 +49,27 @@ public:
         std::map<KeyFrame*, size_t>::iterator it = obs_.find(pKF);
         return it == obs_.end() ? -1 : (int)it->second;
     }
+    bool IsInKeyFrame(KeyFrame* pKF) { return obs_.count(pKF) != 0; }                 // src/MapPoint.cc:479-483
+    // the map surgery at the end of ORBmatcher::Fuse (:1061-1081) is recorded, not performed: {kind, this point, other / key}
+    struct FuseEvent { int kind, point, other; };       // kind 0: AddObservation(pKF, other = idx); 1: this->Replace(other point)
+    static std::vector<FuseEvent>& fuse_log() { static thread_local std::vector<FuseEvent> log; return log; }
+    void AddObservation(KeyFrame* pKF, size_t idx) { obs_[pKF] = idx; fuse_log().push_back(FuseEvent{0, tag_, (int)idx}); }
+    void Replace(MapPoint* pMP) { fuse_log().push_back(FuseEvent{1, tag_, pMP->tag_}); }
     // lifted verbatim from src/MapPoint.cc (oracle/_ref/gen/mappoint_methods.inc)
+    void ComputeDistinctiveDescriptors();
     float GetMinDistanceInvariance();
     float GetMaxDistanceInvariance();
     int PredictScale(const float& currentDist, KeyFrame* pKF);
     int PredictScale(const float& currentDist, Frame* pF);
     float mfMinDistance = 0.f, mfMaxDistance = 0.f;     // include/MapPoint.h:178-179
+    bool mbBad = false;                                 // :170; what ComputeDistinctiveDescriptors reads and writes (:164-167)
+    std::map<KeyFrame*, size_t> mObservations;
+    cv::Mat mDescriptor;
     struct Mutex : std::mutex {        // a std::mutex that lets the stand-in live in std::vector (copies get their own)
         Mutex() {}
         Mutex(const Mutex&) {}
         Mutex& operator=(const Mutex&) { return *this; }
-    } mMutexPos;
+    } mMutexPos, mMutexFeatures;
 
     bool bad_ = false;
     int nobs_ = 0;
@@ -118,12 +128,16 @@ public:
 
     std::vector<MapPoint*> GetMapPointMatches() { return mvpMapPoints; }
     MapPoint* GetMapPoint(const size_t& idx) { return mvpMapPoints[idx]; }
+    bool isBad() { return bad_; }
+    bool bad_ = false;
+    void AddMapPoint(MapPoint* pMP, const size_t& idx) { mvpMapPoints[idx] = pMP; }     // src/KeyFrame.cc:229-233
     cv::Mat GetRotation() { return Tcw.rowRange(0, 3).colRange(0, 3).clone(); }        // src/KeyFrame.cc:126-136
     cv::Mat GetTranslation() { return Tcw.rowRange(0, 3).col(3).clone(); }
     cv::Mat GetCameraCenter() { return Ow.clone(); }
 
-    float fx, fy, cx, cy;
+    float fx, fy, cx, cy, mbf = 0.f;
     int N;
+    std::vector<float> mvInvLevelSigma2;
     std::vector<cv::KeyPoint> mvKeysUn;
     std::vector<float> mvuRight;
     cv::Mat mDescriptors;
@@ -151,6 +165,7 @@ public:
     int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12);
     int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t> >& vMatchedPairs,
                                const bool bOnlyStereo);
+    int Fuse(KeyFrame* pKF, const std::vector<MapPoint*>& vpMapPoints, const float th = 3.0);
     int SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12, const float& s12, const cv::Mat& R12,
                      const cv::Mat& t12, const float th);
     int SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched,

@@ -468,3 +468,120 @@ def test_search_by_projection_loop_closing(L, seed, th):
     assert (q["flags"] != 0).sum() > 120 and onm > 40
     assert onm == nm
     assert np.array_equal(expected_points(kq, order, matched_in), matched)
+
+
+@pytest.mark.parametrize("seed,th", [(0, 3.0), (1, 3.0), (2, 6.0), (3, 1.5)])
+def test_fuse_candidate_search(L, seed, th):
+    """ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:937-1087): which key each candidate point lands on (the
+    reprojection-error gate in float, 7.8 / 5.99 compared in double).  The reference's map surgery behind it (AddObservation /
+    AddMapPoint / Replace) is recorded by the stand-ins and has to name exactly the keys the restatement reports."""
+    L.ref_fuse.argtypes = [vp, vp, vp, vp, i32, vp, vp, vp, i32, vp, vp, i32, vp, vp, vp, vp, vp, vp, i32, f32, vp, i32, vp]
+    S = Scene(500 + seed)
+    rng = S.rng
+    sf = S.sf
+    Rcw, tcw = S.Tcw[:3, :3], S.Tcw[:3, 3]
+    Ow = mm(-Rcw.T, tcw)[:, 0]
+    pdist = np.zeros((S.npts, 2), F32); pnormal = np.zeros((S.npts, 3), F32)
+    for p in range(S.npts):
+        PO = (S.wpos[p] - Ow).astype(F32)
+        dist = F32(norm2(PO))
+        pdist[p, 1] = F32(float(dist) * float(sf[1]) ** (S.level[p] - 0.5))
+        pdist[p, 0] = F32(0.2 * float(dist) if rng.random() > 0.06 else 3.0 * float(dist))
+        n = PO.astype(np.float64) / max(float(dist), 1e-9)
+        if rng.random() < 0.1:
+            n = np.cross(n, [0.3, 1.0, 0.2]); n /= np.linalg.norm(n)
+        pnormal[p] = n.astype(F32)
+    # keys sit ~2 px from the projections (Scene): tighten a share of them so the error gate passes and fails both ways
+    ur = np.full(S.n, -1, F32)
+    for p in range(S.npts):
+        k = S.key_of_point[p]
+        if k < 0:
+            continue
+        c, invz, u, v = project(S.Tcw, S.wpos[p])
+        if not np.isfinite(u) or c[2] <= 0:
+            continue
+        if rng.random() < 0.6:
+            S.keys["x"][k] = u + F32(rng.normal(0, 0.7)); S.keys["y"][k] = v + F32(rng.normal(0, 0.7))
+        if rng.random() < 0.5:
+            ur[k] = F32(u - F32(CAM[4] * invz)) + F32(rng.normal(0, 1.0))
+    kf_point = np.where(rng.random(S.n) < 0.3, rng.integers(0, S.npts, S.n), -1).astype(np.int32)
+    order = rng.permutation(S.npts)[: int(0.9 * S.npts)].astype(np.int32)
+    order[rng.random(len(order)) < 0.03] = -1
+    in_kf = (rng.random(S.npts) < 0.08).astype(np.uint8)
+    events = np.zeros((len(order) + 8, 3), np.int32); nev = C.c_int(0)
+    nf = L.ref_fuse(P(S.keys), P(S.desc), P(ur), P(kf_point), S.n, P(A(BOUNDS, F32)), P(CAM), P(sf), 8, P(A(S.Tcw, F32)), P(order), len(order),
+                    P(in_kf), P(S.wpos), P(S.pdesc), P(S.pflag), P(pdist), P(pnormal), S.npts, th, P(events), len(events), C.byref(nev))
+    q = np.zeros(len(order), PROJ_QUERY); qd = np.zeros((len(order), 32), np.uint8)
+    for j, p in enumerate(order):
+        if p < 0 or (S.pflag[p] & 2) or in_kf[p]:
+            continue
+        c = (mm(Rcw, S.wpos[p])[:, 0] + tcw).astype(F32)
+        if c[2] < 0.0:
+            continue
+        invz = F32(F32(1) / c[2])
+        u = F32(F32(CAM[0] * F32(c[0] * invz)) + CAM[2]); v = F32(F32(CAM[1] * F32(c[1] * invz)) + CAM[3])
+        if not (u >= 0 and u < 752 and v >= 0 and v < 480):
+            continue
+        xr = F32(u - F32(CAM[4] * invz))
+        PO = (S.wpos[p] - Ow).astype(F32)
+        dist = F32(norm2(PO))
+        if dist < F32(F32(0.8) * pdist[p, 0]) or dist > F32(F32(1.2) * pdist[p, 1]):
+            continue
+        dot = 0.0
+        for a, b in zip(PO, pnormal[p]):
+            dot += float(a) * float(b)
+        if dot < 0.5 * float(dist):
+            continue
+        lvl = predict_scale(pdist[p, 1], dist, 8, sf[1])
+        q[j] = (u, v, F32(F32(th) * sf[lvl]), xr, 0, lvl - 1, lvl, O.PQ_ACTIVE | O.PQ_REPROJ_GATE)
+        qd[j] = S.pdesc[p]
+    inv_sig2 = (F32(1.0) / (sf * sf).astype(F32)).astype(F32)
+    onm, _, _, qk = O.search_by_projection(S.keys, S.desc, ur, None, BOUNDS, q, qd, 50, 0.6, False, False, inv_sig2)
+    assert (q["flags"] != 0).sum() > 120 and onm > 40
+    assert onm == nf
+    # replay the surgery the reference would have done, from the restatement's keys
+    held = kf_point.copy()
+    want = []
+    for j, p in enumerate(order):
+        k = qk[j]
+        if k < 0:
+            continue
+        other = held[k]
+        if other >= 0:
+            if not (S.pflag[other] & 2):
+                obs_other, obs_p = (1 if S.pflag[other] & 4 else 0), (1 if S.pflag[p] & 4 else 0)
+                want.append((1, p, other) if obs_other > obs_p else (1, other, p))
+        else:
+            want.append((0, p, k)); held[k] = p
+    assert nev.value == len(want)
+    assert [tuple(e) for e in events[:nev.value].tolist()] == [tuple(int(x) for x in w) for w in want]
+
+
+def test_compute_distinctive_descriptors(L):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:397-462), lifted verbatim: the descriptor with the least
+    median distance to the others, first on ties -- sets of 1 .. 60 observations, near-duplicates, bad key frames."""
+    L.ref_distinctive_descriptors.argtypes = [vp, vp, vp, i32, vp, vp]
+    rng = np.random.default_rng(77)
+    sizes = np.concatenate([[1, 2, 2, 3, 60], rng.integers(1, 40, 200), [0]])
+    start = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    desc = np.zeros((int(start[-1]), 32), np.uint8)
+    for p, n in enumerate(sizes):
+        if n:
+            centre = rng.integers(0, 256, 32, dtype=np.uint8)
+            desc[start[p]:start[p + 1]] = centre ^ np.packbits(rng.random((n, 256)) < rng.choice([0.02, 0.1, 0.4]), axis=1)
+            if n > 3 and rng.random() < 0.3:
+                desc[start[p] + 1] = desc[start[p]]                       # exact duplicates: ties
+    bad = (rng.random(len(desc)) < 0.1).astype(np.uint8)
+    best = np.zeros((len(sizes), 32), np.uint8); has = np.zeros(len(sizes), np.uint8)
+    L.ref_distinctive_descriptors(P(desc), P(start), P(bad), len(sizes), P(best), P(has))
+    # the product / restatement entry takes the descriptors of the good key frames only (the caller's filter, :418-424)
+    keep = bad == 0
+    kstart = np.concatenate([[0], np.cumsum([int(keep[start[p]:start[p + 1]].sum()) for p in range(len(sizes))])]).astype(np.int32)
+    kdesc = np.ascontiguousarray(desc[keep])
+    bi, bm = O.distinctive_descriptors(kdesc, kstart)
+    for p in range(len(sizes)):
+        n = kstart[p + 1] - kstart[p]
+        assert bool(has[p]) == (n > 0), p
+        if n:
+            assert np.array_equal(best[p], kdesc[kstart[p] + bi[p]]), p
+    assert has.sum() > 190
