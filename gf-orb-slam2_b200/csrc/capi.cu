@@ -446,6 +446,19 @@ int gforb_match_bruteforce_device(gforb_matcher* m, const uint8_t* dA, int nA, c
     if (((uintptr_t)dA | (uintptr_t)dB) & 15) { set_error("gforb_match_bruteforce: descriptor arrays must be 16-byte aligned"); return GFORB_ERR_ARG; }
     cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : m->stream;
     m->last = s;
+    if (match_tc_eligible(nA, nB)) {                 // large sets: the contraction runs on the tensor cores (k_match_tc.cu)
+        const int tseg = match_tc_segments(nA, nB, m->sms);
+        int rct = m->reserve(m->scratch, m->scratch_bytes, match_tc_scratch_bytes(nA, nB, tseg));
+        if (rct) return rct;
+        M_CUDA(cudaEventRecord(m->ev0, s));
+        if (launch_match_tc(dA, nA, dB, nB, m->ratio, threshold, tseg, m->scratch, best_idx, best_dist, second_dist, match, s) == 0) {
+            M_CUDA(cudaEventRecord(m->ev1, s));
+            M_CUDA(cudaGetLastError());
+            m->timed = true;
+            return GFORB_OK;
+        }
+        (void)cudaGetLastError();                    // tensor map / opt-in refused: the POPC kernels below
+    }
     const int nseg = match_segments(nA, nB, m->sms);
     int rc = m->reserve(m->scratch, m->scratch_bytes, match_scratch_bytes(nA, nseg));
     if (rc) return rc;

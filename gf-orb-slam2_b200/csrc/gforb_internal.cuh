@@ -163,6 +163,14 @@ void build_fast_cell_table(const Geom& g, std::vector<uint32_t>& tab);
 int match_segments(int nA, int nB, int sm_count);
 size_t match_scratch_bytes(int nA, int nseg);
 int match_max_train();
+void launch_match_merge(const void* part, int nA, int nseg, float ratio, int threshold, int32_t* best_idx, int32_t* best_dist,
+                        int32_t* second_dist, int32_t* match, cudaStream_t s);
+// tensor-core form of the brute-force matcher (k_match_tc.cu): tcgen05.mma kind::i8 over the bits expanded to +-1
+bool match_tc_eligible(int nA, int nB);
+int match_tc_segments(int nA, int nB, int sm_count);
+size_t match_tc_scratch_bytes(int nA, int nB, int nseg);
+int launch_match_tc(const uint8_t* dA, int nA, const uint8_t* dB, int nB, float ratio, int threshold, int nseg, void* scratch,
+                    int32_t* best_idx, int32_t* best_dist, int32_t* second_dist, int32_t* match, cudaStream_t s);
 void launch_match(const uint8_t* dA, int nA, const uint8_t* dB, int nB, float ratio, int threshold, int nseg,
                   void* scratch, int32_t* best_idx, int32_t* best_dist, int32_t* second_dist, int32_t* match,
                   cudaStream_t s);

@@ -104,6 +104,14 @@ void launch_match(const uint8_t* dA, int nA, const uint8_t* dB, int nB, float ra
                                                         best_idx, best_dist, second_dist, match);
 }
 
+// the merge + acceptance tests alone: the tensor-core path (k_match_tc.cu) writes the same per-segment key pairs
+void launch_match_merge(const void* part, int nA, int nseg, float ratio, int threshold, int32_t* best_idx, int32_t* best_dist,
+                        int32_t* second_dist, int32_t* match, cudaStream_t s) {
+    if (nA <= 0) return;
+    match_merge_kernel<<<(nA + 255) / 256, 256, 0, s>>>(reinterpret_cast<const uint2*>(part), nA, nseg, ratio, threshold,
+                                                        best_idx, best_dist, second_dist, match);
+}
+
 // ------------------------------------------------------------------------------------------------------------------
 // MapPoint::ComputeDistinctiveDescriptors (reference src/MapPoint.cc:397-458), the descriptor part: per map point, the
 // N observed descriptors' pairwise distances, per row the median sorted[int(0.5 * (N - 1))] (the row includes its own

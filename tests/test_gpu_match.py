@@ -109,3 +109,22 @@ def test_distinctive_descriptors_vs_oracle(gf, O):
     assert bi[5] == -1 and bm[5] == np.iinfo(np.int32).max
     with pytest.raises(gf.GforbError):
         gf.ComputeDistinctiveDescriptors(m, np.zeros((1025, 32), np.uint8), np.array([0, 1025], np.int32))
+
+
+@pytest.mark.parametrize("n,m", [(2048, 2048), (4100, 3000), (2500, 10007), (8192, 8192), (2048, 70000)])
+def test_tensor_core_path_vs_oracle(gf, O, n, m):
+    """Sets of >= 2,048 descriptors a side take the tcgen05 path (k_match_tc.cu: bits expanded to +-1 int8, dot product on the
+    tensor cores, best / second-best off TMEM): the same four outputs, bit for bit, incl. ragged last tiles and row blocks."""
+    a, b = make_sets(n, m, 7 * n + m)
+    for ratio, th in ((0.6, 50), (0.9, 100)):
+        check(gf, O, a, b, ratio, th)
+
+
+def test_tensor_core_path_ties(gf, O):
+    """few distinct descriptors: equal minima everywhere, across tiles, segments and accumulator stages -- first index wins"""
+    rng = np.random.default_rng(11)
+    vals = rng.integers(0, 256, (5, 32), dtype=np.uint8)
+    a = vals[rng.integers(0, 5, 3000)]
+    b = vals[rng.integers(0, 5, 5000)]
+    got = check(gf, O, a, b, 0.6, 50)
+    assert (got["best_dist"] == 0).all() and (got["second_dist"] == 0).all()
