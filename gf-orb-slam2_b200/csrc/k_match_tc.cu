@@ -11,10 +11,15 @@
 //               (2 x [256 rows x 128 B]) into a 2-stage ring, completing on mbarriers;
 //   warp 1      MMA issuer (one elected lane): 8 x tcgen05.mma (M 128, N 256, K 32) per tile into one of two 256-column
 //               TMEM accumulator stages; tcgen05.commit releases the smem stage and publishes the accumulator;
-//   warps 2-5   epilogue: thread = query row = TMEM lane; tcgen05.ld 32 columns at a time, key = distance << 8 | column
+//   warps 2-9   epilogue: thread = query row = TMEM lane, two warps per lane group each scanning one half of the tile's
+//               columns; tcgen05.ld 32 columns at a time, key = distance << 8 | column
 //               (one IMAD from the dot product), running (best, second) by the min / max recurrence of k_match.cu, folded
 //               into global keys distance << 22 | train index per tile.
 // The per-segment (best, second) pairs go through the same match_merge_kernel as the POPC path: identical outputs.
+// Measured on B200, 64k x 64k (round 2): 1.10 ms = 3.9 T pairs/s (POPC kernel: 8.07 ms).  ncu: the epilogue's ALU pipe is the
+// bound (57 % busy with four epilogue warps, tensor pipe 32 %): four epilogue warps 1.37 ms, eight 1.10 ms, sixteen 1.16 ms;
+// two columns per register as packed 16-bit keys scanned with VIMNMX.U16x2 (half the ALU instructions, bit-identical):
+// 1.92 ms -- the packed form issues at a fraction of the 32-bit rate.
 #include "gforb_internal.cuh"
 #include "tma.cuh"
 
@@ -30,7 +35,13 @@ constexpr int kIdxBitsTc = 22;       // as k_match.cu: train index bits inside a
 constexpr uint32_t kNoKeyTc = 0xFFFFFFFFu;
 constexpr uint32_t kABytes = kBM * kRowBytes;       // 32 KB
 constexpr uint32_t kBBytes = kBN * kRowBytes;       // 64 KB per stage
-constexpr int kTcThreads = 192;
+#ifndef GFORB_TC_EPI_WARPS
+#define GFORB_TC_EPI_WARPS 8
+#endif
+constexpr int kEpiWarps = GFORB_TC_EPI_WARPS;      // kColSplit per TMEM lane group: each takes one slice of a tile's columns
+constexpr int kColSplit = kEpiWarps / 4;
+constexpr int kColsPerWarp = kBN / kColSplit;
+constexpr int kTcThreads = 64 + 32 * kEpiWarps;
 
 // ---- PTX wrappers (sm_100a) ----
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
@@ -89,7 +100,7 @@ match_expand_kernel(const uint8_t* __restrict__ desc, int n, int8_t* __restrict_
     reinterpret_cast<uint2*>(out)[i] = make_uint2(lo, hi);
 }
 
-// part: [nA][nseg] uint2 {best key, second key}, keys = distance << 22 | train index (as match_scan_kernel writes them)
+// part: [nA][nseg][kColSplit column slices] uint2 {best key, second key}, keys = distance << 22 | train index (as match_scan_kernel writes them)
 __global__ void __launch_bounds__(kTcThreads, 1)
 match_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, int nA, int nB,
                 int tiles_per_seg, uint2* __restrict__ part) {
@@ -114,7 +125,7 @@ match_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
     if (threadIdx.x == 0) {
         mbar_init(bar_a, 1);
         for (int s = 0; s < kStages; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(tfull + s, 1); mbar_init(tempty + s, 4); }
+        for (int s = 0; s < 2; ++s) { mbar_init(tfull + s, 1); mbar_init(tempty + s, kEpiWarps); }
     }
     if (warp == 1) {                                         // TMEM: both accumulator stages = all 512 columns
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
@@ -165,7 +176,7 @@ match_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
         }
     } else {
         // ===== epilogue: thread = query row; warp w may touch TMEM lanes 32 * (w % 4) .. + 31 =====
-        const int lg = warp & 3;
+        const int lg = warp & 3, ch = (warp - 2) >> 2;                // lane group; column half of every tile this warp scans
         const int row = row0 + lg * 32 + lane;
         uint32_t best = kNoKeyTc, second = kNoKeyTc;                  // global keys
         for (int t = t0; t < t1; ++t) {
@@ -176,7 +187,7 @@ match_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
             uint32_t b0 = kNoKeyTc, s0 = kNoKeyTc, b1 = kNoKeyTc, s1 = kNoKeyTc;      // tile-local keys: distance << 8 | column
             const uint32_t taddr = tmem + ((uint32_t)(lg * 32) << 16) + (uint32_t)(as * kBN);
 #pragma unroll 1
-            for (int c0 = 0; c0 < kBN; c0 += 32) {
+            for (int c0 = ch * kColsPerWarp; c0 < (ch + 1) * kColsPerWarp; c0 += 32) {
                 uint32_t r[32];
                 GFORB_TMEM_LD32(taddr + (uint32_t)c0, r);
                 tc_wait_ld();
@@ -210,7 +221,7 @@ match_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
             second = min(min(second, gs), max(best, gb));
             best = min(best, gb);
         }
-        if (row < nA) part[(size_t)row * nseg + seg] = make_uint2(best, second);
+        if (row < nA) part[((size_t)row * nseg + seg) * kColSplit + ch] = make_uint2(best, second);     // the two halves merge like two segments
     }
 
     tc_fence_before();
@@ -255,7 +266,7 @@ int match_tc_segments(int nA, int nB, int sm_count) {
 }
 size_t match_tc_scratch_bytes(int nA, int nB, int nseg) {
     const size_t pa = (size_t)((nA + kBM - 1) / kBM) * kBM, pb = (size_t)((nB + kBN - 1) / kBN) * kBN;
-    return (((size_t)nA * nseg * sizeof(uint2) + 1023) & ~(size_t)1023) + (pa + pb) * kRowBytes;
+    return (((size_t)nA * nseg * kColSplit * sizeof(uint2) + 1023) & ~(size_t)1023) + (pa + pb) * kRowBytes;
 }
 
 // returns 0, or -1 when the tensor maps / shared-memory opt-in cannot be set up (the caller falls back to the POPC kernels)
@@ -264,7 +275,7 @@ int launch_match_tc(const uint8_t* dA, int nA, const uint8_t* dB, int nB, float 
     const size_t pa = (size_t)((nA + kBM - 1) / kBM) * kBM, pb = (size_t)((nB + kBN - 1) / kBN) * kBN;
     uint8_t* base = static_cast<uint8_t*>(scratch);
     uint2* part = reinterpret_cast<uint2*>(base);
-    int8_t* eA = reinterpret_cast<int8_t*>(base + (((size_t)nA * nseg * sizeof(uint2) + 1023) & ~(size_t)1023));
+    int8_t* eA = reinterpret_cast<int8_t*>(base + (((size_t)nA * nseg * kColSplit * sizeof(uint2) + 1023) & ~(size_t)1023));
     int8_t* eB = eA + pa * kRowBytes;
     CUtensorMap mapA, mapB;
     if (encode_desc_map(&mapA, eA, pa, kBM) || encode_desc_map(&mapB, eB, pb, kBN)) return -1;
@@ -278,7 +289,7 @@ int launch_match_tc(const uint8_t* dA, int nA, const uint8_t* dB, int nB, float 
     const int ntiles = (int)(pb / kBN), tiles_per_seg = (ntiles + nseg - 1) / nseg;
     dim3 grd((unsigned)(pa / kBM), (unsigned)nseg);
     match_tc_kernel<<<grd, kTcThreads, tc_smem_bytes(), s>>>(mapA, mapB, nA, nB, tiles_per_seg, part);
-    launch_match_merge(part, nA, nseg, ratio, threshold, best_idx, best_dist, second_dist, match, s);
+    launch_match_merge(part, nA, kColSplit * nseg, ratio, threshold, best_idx, best_dist, second_dist, match, s);
     return 0;
 }
 
