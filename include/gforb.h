@@ -133,7 +133,10 @@ GFORB_API int gforb_hamming256(const void* a32, const void* b32);   /* host inli
  *   best_dist[i]   its distance (INT32_MAX if nB = 0, the reference's initial value)
  *   second_dist[i] second smallest distance of the multiset (INT32_MAX if nB < 2)
  *   match[i]       best_idx[i] if it passes both tests, else -1
- * nB <= 4,194,304.  Host-pointer and device-pointer (asynchronous, on `cuda_stream` or the matcher's own) forms. */
+ * nB <= 4,194,304.  Host-pointer and device-pointer (asynchronous, on `cuda_stream` or the matcher's own) forms.
+ * Sets of >= 2,048 descriptors a side run as an int8 contraction on the tensor cores (bits expanded to +-1, a . b = 256 - 2 *
+ * distance, tcgen05.mma kind::i8; k_match_tc.cu), smaller ones on the POPC kernels: identical outputs (GFORB_NO_TC=1 in the
+ * environment forces the POPC kernels, for A/B measurements). */
 typedef struct gforb_matcher gforb_matcher;
 GFORB_API int gforb_matcher_create(float nnratio, gforb_matcher** out);
 GFORB_API void gforb_matcher_destroy(gforb_matcher* m);
