@@ -11,6 +11,8 @@ starts.
            2tum   configs[2]: the bundled TUM pair (512x512 as shipped)
            2vga   configs[2]: synthetic 640x480 (the size BASELINE.json quotes for TUM)
            2hd    configs[2]: synthetic 1280x720, 2000 kp, 256 stereo frames per step
+           3      configs[3]: the brute-force Hamming matcher at --match-n x --match-n descriptors (default 64k x 64k; its own
+                  metric, G pairs/s; roofline.bound = "tensor": the kernel is a tcgen05 int8 contraction)
            4      configs[4]: 65,536 distinct synthetic 752x480 stereo frames in ONE pass, sharded over the ranks
                   (strong scaling: --steps is derived, 65,536 / (N * F))
   value   : device-resident inputs, CUDA-event timed on the launching stream, max over ranks.
@@ -233,6 +235,89 @@ def run_reference(args, cfg, rank, world):
     emit(line)
 
 
+def run_config3(args):
+    """--config 3: BASELINE.json configs[3], the brute-force 256-bit Hamming matcher (best / second-best + ratio test) at
+    N x N descriptors (default 64k x 64k, the sweep's largest; the whole sweep is tools/bench_match.py).  A step = one
+    gforb_match_bruteforce call; value = device-resident descriptors, e2e = host descriptors in, host results out.  The
+    kernel is a tensor-core contraction (k_match_tc.cu): roofline.bound = "tensor", 2 * 256 int8 ops per pair against
+    twice the measured dense bf16 rate.  Replicas only: the matcher does not shard (one rank runs; others exit)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    n = args.match_n
+    rng = np.random.default_rng(1234)
+    A = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    Bd = A[rng.permutation(n)] ^ np.packbits(rng.random((n, 256)) < 0.1, axis=1)        # SURVEY.md 8(d) config 3 input
+    metric = f"G descriptor pairs/s brute-force Hamming {n}x{n}"
+    if args.impl == "reference":
+        from oracle import pyoracle as O
+        threads = os.cpu_count() or 1
+        rows = min(n, max(256, int(2.0e10 / n / 8)))                  # bounded sample: a slice of the query set against all of B
+        vals = []
+        for i in range(args.warmup + args.steps):
+            t0 = time.perf_counter(); O.match_bruteforce(A[:rows], Bd, 0.6, 50, nthreads=threads); dt = time.perf_counter() - t0
+            if i >= args.warmup:
+                vals.append(dt)
+        v = rows * n / float(np.mean(vals)) / 1e9
+        emit({"impl": "reference", "metric": metric, "value": v, "unit": "Gpairs/s", "n_gpus": args.gpus, "steps": args.steps,
+              "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(vals)), "higher_is_better": True, "scaling": "weak",
+              "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": {"workload": f"configs[3]: {n} x {n} descriptors, ratio 0.6, TH_LOW 50"},
+              "cpu_baseline": {"value": v, "unit": "Gpairs/s", "cores": threads, "kind": "port", "cpu_model": cpu_model(),
+                               "sample": f"{rows} query descriptors against all {n} train descriptors per step (the reference's nearest-neighbour loop, src/ORBmatcher.cc:562-576, over all train descriptors)"},
+              "e2e": {"value": v, "unit": "Gpairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0})
+        return 0
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; gforb has no CPU fallback (use --impl reference for the CPU arm)")
+    gf = importlib.import_module("gf-orb-slam2_b200")
+    m = gf.ORBmatcher(0.6)
+    dA, dB = gf.DeviceArray.from_host(A), gf.DeviceArray.from_host(Bd)
+    outs = [gf.DeviceArray((n,), np.int32) for _ in range(4)]
+    sampler = ClockSampler(0)
+    for _ in range(max(args.warmup, 3)):
+        m.BruteForceDevice(dA, n, dB, n, 50, *outs)
+    m.sync()
+    sampler.start()
+    ms = []
+    for _ in range(args.steps):
+        m.BruteForceDevice(dA, n, dB, n, 50, *outs)
+        ms.append(m.sync())                                            # CUDA events around the call's kernels, on its stream
+    clocks = sampler.stop()
+    t = float(np.mean(ms))
+    e = []
+    for i in range(min(args.steps, 10) + 1):
+        t0 = time.perf_counter(); r = m.BruteForce(A, Bd, 50); dt = time.perf_counter() - t0
+        if i:
+            e.append(dt)
+    peaks_file = ROOT / "MEASURED_PEAKS.json"
+    bf16 = float(json.loads(peaks_file.read_text())["bf16_tflops"]) if peaks_file.exists() else 1600.0
+    tops = 2.0 * 256 * n * n / (t * 1e-3) / 1e12
+    tc = n >= 2048 and not os.environ.get("GFORB_NO_TC")
+    line = {"metric": metric, "value": n * n / (t * 1e-3) / 1e9, "unit": "Gpairs/s", "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": t, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "s8 x s8 -> s32" if tc else "u32 popc",
+            "data": "synthetic", "config": {"workload": f"configs[3]: {n} x {n} descriptors, ratio 0.6, TH_LOW 50", "name": "3",
+                                            "l2": "the expanded train set (%d MB) is re-streamed by every query block" % ((n * 256) >> 20),
+                                            "matched_frac": float((r["match"] >= 0).mean())},
+            "e2e": {"value": n * n / float(np.mean(e)) / 1e9, "unit": "Gpairs/s", "h2d_bytes_per_step": 2 * n * 32, "d2h_bytes_per_step": 4 * n * 4,
+                    "api": "gforb_match_bruteforce (pageable host arrays in, host results out)"},
+            "gpu_launches": (5 if tc else 2) * args.steps, "clocks": clocks,
+            "roofline": {"bound": "tensor", "kernel": "match_tc_kernel" if tc else "match_scan_kernel", "achieved": tops, "peak": 2.0 * bf16,
+                         "unit": "TOP/s (int8)", "frac": tops / (2.0 * bf16), "traffic": None,
+                         "peak_source": "2 x MEASURED_PEAKS.json bf16_tflops (dense int8 runs at twice the dense bf16 rate)",
+                         "note": "algorithmic ops = 2 * 256 per descriptor pair; the kernel is bound by its epilogue's ALU pipe "
+                                 "(best / second-best scan off TMEM), see DESIGN.md section 8"}}
+    if not args.no_cpu_baseline:
+        from oracle import pyoracle as O
+        threads = os.cpu_count() or 1
+        rows = min(n, max(256, int(2.0e10 / n / 8)))
+        t0 = time.perf_counter(); ref = O.match_bruteforce(A[:rows], Bd, 0.6, 50, nthreads=threads); dt = time.perf_counter() - t0
+        ok = all(np.array_equal(r[k][:rows], ref[k]) for k in ref)
+        line["cpu_baseline"] = {"value": rows * n / dt / 1e9, "unit": "Gpairs/s", "cores": threads, "kind": "port", "cpu_model": cpu_model(),
+                                "sample": f"{rows} of the {n} query descriptors against all train descriptors, {dt:.1f} s; GPU == CPU on them: {ok}"}
+    emit(line)
+    return 0
+
+
 def bind_to_gpu_numa_node(index):
     """Pin this rank (and the pinned host buffers it is about to allocate: first touch) to the NUMA node its GPU hangs
     off, so that the end-to-end arm's H2D / D2H traffic does not cross the socket interconnect.  Best effort: returns
@@ -290,7 +375,8 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--config", default="1", choices=sorted(CONFIGS))
+    ap.add_argument("--config", default="1", choices=sorted(CONFIGS) + ["3"])
+    ap.add_argument("--match-n", type=int, default=65536, help="--config 3: descriptors a side")
     ap.add_argument("--frames", type=int, default=256, help="stereo frames per step per GPU")
     ap.add_argument("--pool", type=int, default=8, help="distinct batches kept resident and cycled by the steps")
     ap.add_argument("--impl", default="gforb", choices=["gforb", "reference"])
@@ -298,6 +384,8 @@ def main():
     ap.add_argument("--chunk", type=int, default=0, help="frames per pipeline chunk of the end-to-end arm")
     args = ap.parse_args()
     quiet_stdout()
+    if args.config == "3":
+        return run_config3(args)
     cfg = CONFIGS[args.config]
     W, H, NFEAT = cfg["w"], cfg["h"], cfg["nfeat"]
 
