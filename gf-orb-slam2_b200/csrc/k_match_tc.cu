@@ -12,14 +12,18 @@
 //   warp 1      MMA issuer (one elected lane): 8 x tcgen05.mma (M 128, N 256, K 32) per tile into one of two 256-column
 //               TMEM accumulator stages; tcgen05.commit releases the smem stage and publishes the accumulator;
 //   warps 2-9   epilogue: thread = query row = TMEM lane, two warps per lane group each scanning one half of the tile's
-//               columns; tcgen05.ld 32 columns at a time, key = distance << 8 | column
-//               (one IMAD from the dot product), running (best, second) by the min / max recurrence of k_match.cu, folded
-//               into global keys distance << 22 | train index per tile.
+//               columns; tcgen05.ld 32 columns at a time; eight columns are screened against the running second-best with
+//               four 3-input max, and only groups that hold a candidate run the (best, second) min / max recurrence of
+//               k_match.cu on keys distance << 22 | train index.
 // The per-segment (best, second) pairs go through the same match_merge_kernel as the POPC path: identical outputs.
-// Measured on B200, 64k x 64k (round 2): 1.10 ms = 3.9 T pairs/s (POPC kernel: 8.07 ms).  ncu: the epilogue's ALU pipe is the
-// bound (57 % busy with four epilogue warps, tensor pipe 32 %): four epilogue warps 1.37 ms, eight 1.10 ms, sixteen 1.16 ms;
-// two columns per register as packed 16-bit keys scanned with VIMNMX.U16x2 (half the ALU instructions, bit-identical):
-// 1.92 ms -- the packed form issues at a fraction of the 32-bit rate.
+// Measured on B200, 64k x 64k (round 2): 0.81 ms = 5.3 T pairs/s = 2.7 P int8 op/s (POPC kernel: 8.07 ms), the tensor pipe
+// 48 % busy in the ncu capture (profiles/ncu_r2_match_tc.json).  How it got there: scanning every column, the epilogue's ALU pipe was the
+// bound (four epilogue warps 1.37 ms, eight 1.10 ms, sixteen 1.16 ms); the threshold screen above took it to 0.85 ms and the
+// wave-aware segment count below to 0.81 ms.  Tried and not kept: two columns per register as packed 16-bit keys scanned
+// with VIMNMX.U16x2 (1.92 ms: the packed form issues at a fraction of the 32-bit rate); tcgen05.ld of the next 32 columns in
+// flight during the screen (0.86 ms, 168 registers); 256 query rows per CTA against 128-row train tiles in a 4-stage ring,
+// i.e. half the L2 -> shared-memory traffic (0.82 ms: that traffic, 36 % of the L2 peak, is not what the kernel waits for).
+#include <climits>
 #include "gforb_internal.cuh"
 #include "tma.cuh"
 
@@ -178,48 +182,51 @@ match_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
         // ===== epilogue: thread = query row; warp w may touch TMEM lanes 32 * (w % 4) .. + 31 =====
         const int lg = warp & 3, ch = (warp - 2) >> 2;                // lane group; column half of every tile this warp scans
         const int row = row0 + lg * 32 + lane;
-        uint32_t best = kNoKeyTc, second = kNoKeyTc;                  // global keys
+        uint32_t best = kNoKeyTc, second = kNoKeyTc;                  // global keys: distance << 22 | train index
+        // A column can only change (best, second) if its key is below `second`.  This thread meets its columns in rising
+        // index order, so a column whose distance merely EQUALS the second's cannot (its index is larger): the test is
+        // dot > thr with thr = 256 - 2 * distance(second).  Eight columns are screened with four 3-input max; the full
+        // key arithmetic runs only for the groups that hold a candidate -- after the first tiles, a few per cent of them.
+        int thr = -100000;                                            // nothing seen yet: every group is scanned
         for (int t = t0; t < t1; ++t) {
             const int j = t - t0, as = j & 1;
             mbar_wait(tfull + as, (j >> 1) & 1);
             tc_fence_after();
             const int valid = min(kBN, nB - t * kBN);                 // train rows of this tile that exist
-            uint32_t b0 = kNoKeyTc, s0 = kNoKeyTc, b1 = kNoKeyTc, s1 = kNoKeyTc;      // tile-local keys: distance << 8 | column
+            const uint32_t gbase = (uint32_t)(t * kBN);
             const uint32_t taddr = tmem + ((uint32_t)(lg * 32) << 16) + (uint32_t)(as * kBN);
+            auto scan32 = [&](const uint32_t (&r)[32], int c0) {
+#pragma unroll
+                for (int g = 0; g < 32; g += 8) {
+                    int m = __vimax3_s32((int)r[g], (int)r[g + 1], (int)r[g + 2]);
+                    m = __vimax3_s32(m, (int)r[g + 3], (int)r[g + 4]);
+                    m = __vimax3_s32(m, (int)r[g + 5], (int)r[g + 6]);
+                    m = max(m, (int)r[g + 7]);
+                    if (m > thr) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int col = c0 + g + i;
+                            if (col < valid) {
+                                // distance << 22 | index = (256 - dot) << 21 | index   (256 - dot is even)
+                                const uint32_t key = ((uint32_t)(256 - (int)r[g + i]) << (kIdxBitsTc - 1)) + gbase + (uint32_t)col;
+                                second = min(second, max(best, key));
+                                best = min(best, key);
+                            }
+                        }
+                        thr = second == kNoKeyTc ? -100000 : 256 - 2 * (int)(second >> kIdxBitsTc);
+                    }
+                }
+            };
 #pragma unroll 1
             for (int c0 = ch * kColsPerWarp; c0 < (ch + 1) * kColsPerWarp; c0 += 32) {
                 uint32_t r[32];
                 GFORB_TMEM_LD32(taddr + (uint32_t)c0, r);
                 tc_wait_ld();
-                if (c0 + 32 <= valid) {
-#pragma unroll
-                    for (int i = 0; i < 32; i += 2) {
-                        // distance * 256 + column = (256 - dot) * 128 + column
-                        const uint32_t k0 = (uint32_t)((int)r[i] * -128 + (32768 + c0 + i));
-                        const uint32_t k1 = (uint32_t)((int)r[i + 1] * -128 + (32768 + c0 + i + 1));
-                        s0 = min(s0, max(b0, k0)); b0 = min(b0, k0);
-                        s1 = min(s1, max(b1, k1)); b1 = min(b1, k1);
-                    }
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        if (c0 + i < valid) {
-                            const uint32_t k0 = (uint32_t)((int)r[i] * -128 + (32768 + c0 + i));
-                            s0 = min(s0, max(b0, k0)); b0 = min(b0, k0);
-                        }
-                    }
-                }
+                scan32(r, c0);
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty + as);                  // this warp's lanes of the stage are read
-            // fold the tile into the running global keys
-            const uint32_t tb = min(b0, b1), ts = min(min(s0, s1), max(b0, b1));
-            const uint32_t gbase = (uint32_t)(t * kBN);
-            const uint32_t gb = tb == kNoKeyTc ? kNoKeyTc : (((tb >> 8) << kIdxBitsTc) | (gbase + (tb & 255u)));
-            const uint32_t gs = ts == kNoKeyTc ? kNoKeyTc : (((ts >> 8) << kIdxBitsTc) | (gbase + (ts & 255u)));
-            second = min(min(second, gs), max(best, gb));
-            best = min(best, gb);
         }
         if (row < nA) part[((size_t)row * nseg + seg) * kColSplit + ch] = make_uint2(best, second);     // the two halves merge like two segments
     }
@@ -259,10 +266,21 @@ bool match_tc_eligible(int nA, int nB) {
     return !off && nA >= 2048 && nB >= 2048;
 }
 int match_tc_segments(int nA, int nB, int sm_count) {
+    // One CTA per SM at a time (161 KB of shared memory), so the grid runs in waves of sm_count CTAs, and every CTA pays a
+    // start-up of about a dozen tile times: pipeline fill, and -- the larger part -- its first tiles run the epilogue's
+    // slow path until the running second-best has settled (measured: 64k x 64k 0.834 ms with 1 segment, 0.809 with 4;
+    // 32k x 32k 0.279 ms with 2, 0.295 with 4).  Cost of n segments = waves x (tiles per CTA + 12); a tie goes to fewer segments.
     const int mblocks = (nA + kBM - 1) / kBM, ntiles = (nB + kBN - 1) / kBN;
-    int nseg = (2 * sm_count + mblocks - 1) / mblocks;                 // about two CTAs' worth of work per SM
-    nseg = std::min(nseg, std::max(ntiles / 4, 1));                     // at least four tiles per segment
-    return std::max(nseg, 1);
+    const int cap = std::max(std::min(ntiles / 4, 64), 1);
+    int best = 1;
+    long best_cost = LONG_MAX;
+    for (int n = 1; n <= cap; ++n) {
+        const int per = (ntiles + n - 1) / n, used = (ntiles + per - 1) / per;         // segments that get tiles
+        const long ctas = (long)mblocks * used, waves = (ctas + sm_count - 1) / sm_count;
+        const long cost = waves * (per + 12);
+        if (cost < best_cost) { best_cost = cost; best = n; }
+    }
+    return best;
 }
 size_t match_tc_scratch_bytes(int nA, int nB, int nseg) {
     const size_t pa = (size_t)((nA + kBM - 1) / kBM) * kBM, pb = (size_t)((nB + kBN - 1) / kBN) * kBN;

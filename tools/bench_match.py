@@ -55,7 +55,6 @@ def main():
             row.update(path="popc")
         if a.cpu and n <= 8192:
             from oracle import pyoracle as O
-            import os
             th = os.cpu_count() or 1
             t0 = time.perf_counter(); ref = O.match_bruteforce(A, B, 0.6, 50, nthreads=th); c = time.perf_counter() - t0
             row.update(cpu_ms=round(c * 1e3, 2), cpu_threads=th, cpu_gpairs_s=round(n * n / c / 1e9, 3),
