@@ -757,4 +757,60 @@ int ref_search_for_triangulation(const orc_keypoint* k1, const uint8_t* d1, cons
     return (int)vp.size();
 }
 
+
+// ---- Frame::UndistortKeyPoints / UndistortKeyPointsStereo / ComputeImageBounds / ComputeImageBoundsStereo (src/Frame.cc:670-887)
+// cam: K[9], dist[8], R[9], P[12] as float (the reference keeps all four CV_32F), nd = distortion coefficients in use (4, 5 or 8);
+// mono uses K and dist only (cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK)).
+namespace {
+struct RefCam { cv::Mat K, D, R, P; };
+RefCam ref_cam(const float* K9, const float* dist, int nd, const float* R9, const float* P12) {
+    RefCam c;
+    c.K = cv::Mat(3, 3, CV_32F); c.D = cv::Mat(nd, 1, CV_32F);
+    for (int i = 0; i < 9; ++i) c.K.at<float>(i / 3, i % 3) = K9[i];
+    for (int i = 0; i < nd; ++i) c.D.at<float>(i) = dist[i];
+    if (R9) { c.R = cv::Mat(3, 3, CV_32F); for (int i = 0; i < 9; ++i) c.R.at<float>(i / 3, i % 3) = R9[i]; }
+    if (P12) { c.P = cv::Mat(3, 4, CV_32F); for (int i = 0; i < 12; ++i) c.P.at<float>(i / 4, i % 4) = P12[i]; }
+    return c;
+}
+void from_keys(const vector<cv::KeyPoint>& v, orc_keypoint* out) {
+    for (size_t i = 0; i < v.size(); ++i) {
+        out[i].x = v[i].pt.x; out[i].y = v[i].pt.y; out[i].size = v[i].size; out[i].angle = v[i].angle;
+        out[i].response = v[i].response; out[i].octave = v[i].octave; out[i].class_id = v[i].class_id;
+    }
+}
+}  // namespace
+
+void ref_undistort_keypoints(const float* K9, const float* dist, int nd, const orc_keypoint* keys, int n, orc_keypoint* out) {
+    Frame F;
+    const RefCam c = ref_cam(K9, dist, nd, nullptr, nullptr);
+    F.mK = c.K; F.mDistCoef = c.D;
+    F.N = n; F.mvKeys = to_keys(keys, n);
+    F.UndistortKeyPoints();
+    from_keys(F.mvKeysUn, out);
+}
+void ref_undistort_keypoints_stereo(const float* KL, const float* distL, int ndL, const float* RL, const float* PL,
+                                    const float* KR, const float* distR, int ndR, const float* RR, const float* PR,
+                                    const orc_keypoint* keysL, int nL, const orc_keypoint* keysR, int nR,
+                                    orc_keypoint* outL, orc_keypoint* outR) {
+    Frame F;
+    const RefCam l = ref_cam(KL, distL, ndL, RL, PL), r = ref_cam(KR, distR, ndR, RR, PR);
+    F.mK_ori = l.K; F.mDistCoef = l.D; F.mR = l.R; F.mP = l.P;
+    F.mK_right = r.K; F.mDistCoef_right = r.D; F.mR_right = r.R; F.mP_right = r.P;
+    F.N = nL; F.mvKeys = to_keys(keysL, nL); F.mvKeysRight = to_keys(keysR, nR);
+    F.UndistortKeyPointsStereo();
+    from_keys(F.mvKeysUn, outL);
+    from_keys(F.mvKeysRightUn, outR);
+}
+// out4 = mnMinX, mnMaxX, mnMinY, mnMaxY; stereo != 0: ComputeImageBoundsStereo (K_ori, dist, R, P), else ComputeImageBounds (K, dist)
+void ref_compute_image_bounds(int stereo, const float* K9, const float* dist, int nd, const float* R9, const float* P12,
+                              int cols, int rows, float* out4) {
+    std::lock_guard<std::mutex> lock(g_frame_statics);
+    Frame F;
+    const RefCam c = ref_cam(K9, dist, nd, stereo ? R9 : nullptr, stereo ? P12 : nullptr);
+    F.mK = c.K; F.mK_ori = c.K; F.mDistCoef = c.D; F.mR = c.R; F.mP = c.P;
+    cv::Mat im(rows, cols, CV_8UC1);
+    if (stereo) F.ComputeImageBoundsStereo(im); else F.ComputeImageBounds(im);
+    out4[0] = Frame::mnMinX; out4[1] = Frame::mnMaxX; out4[2] = Frame::mnMinY; out4[3] = Frame::mnMaxY;
+}
+
 }  // extern "C"

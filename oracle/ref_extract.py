@@ -25,6 +25,10 @@ RANGES = [
     ("frame_methods.inc", "src/Frame.cc", 461, 476, "void Frame::AssignFeaturesToGrid()", "}"),
     ("frame_methods.inc", "src/Frame.cc", 593, 646, "vector<size_t> Frame::GetFeaturesInArea(", "}"),
     ("frame_methods.inc", "src/Frame.cc", 648, 658, "bool Frame::PosInGrid(", "}"),
+    ("frame_methods.inc", "src/Frame.cc", 670, 722, "void Frame::UndistortKeyPointsStereo()", "}"),
+    ("frame_methods.inc", "src/Frame.cc", 724, 758, "void Frame::UndistortKeyPoints()", "}"),
+    ("frame_methods.inc", "src/Frame.cc", 760, 828, "void Frame::ComputeImageBounds(const cv::Mat &imLeft)", "}"),
+    ("frame_methods.inc", "src/Frame.cc", 830, 887, "void Frame::ComputeImageBoundsStereo(const cv::Mat &imLeft) {", "}"),
     ("frame_methods.inc", "src/Frame.cc", 889, 1078, "void Frame::ComputeStereoMatches()", "}"),
     ("frame_methods.inc", "src/Frame.cc", 1167, 1316, "int Frame::ComputeStereoMatches_Undistorted(bool isOnline)", "}"),
     # --- src/ORBmatcher.cc

@@ -3,6 +3,10 @@
 // destination, in-place operation, cleared output vector).
 #include "cvshim.hpp"
 
+#include <vector>
+
+#include "../gforb_oracle.h"   // orc_undistort_matrix / orc_undistort_points (oracle/undistort.cpp)
+
 namespace cv {
 
 thread_local FastLog* g_fast_log = nullptr;
@@ -61,6 +65,40 @@ void GaussianBlur(InputArray src_, OutputArray dst_, Size ksize, double sigmaX, 
     dst_.create(src.rows, src.cols, src.type());
     Mat dst = dst_.getMat();
     orc::gaussian_blur_7x7_s2(src.data, src.cols, src.rows, src.step, dst.data, dst.step);
+}
+
+// cv::undistortPoints(src, dst, K, D, R, P): N x 1 two-channel CV_32F points, every matrix CV_32F as the reference holds them
+// (src/Tracking.cc:144-168 converts the yaml's doubles to CV_32F).  OpenCV converts K, D, R, P to double, multiplies P(3x3) * R
+// in double and iterates in double: oracle/undistort.cpp, pinned against cv2.undistortPoints by tests/test_oracle_cv2.py.
+// Call sites: src/Frame.cc:688,710,745,795,858.
+void undistortPoints(InputArray src_, OutputArray dst_, InputArray K_, InputArray D_, InputArray R_, InputArray P_) {
+    const Mat src = src_.getMat(), K = K_.getMat(), D = D_.getMat();
+    assert(src.type() == CV_32F && src.channels() == 2 && src.cols == 1);
+    assert(K.type() == CV_32F && K.rows == 3 && K.cols == 3 && D.type() == CV_32F);
+    const int n = src.rows, nd = D.rows * D.cols;
+    assert(nd == 4 || nd == 5 || nd == 8);
+    double K9[9], d8[8] = {0, 0, 0, 0, 0, 0, 0, 0}, R9[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, P9[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, RR[9];
+    for (int i = 0; i < 9; ++i) K9[i] = (double)K.at<float>(i / 3, i % 3);
+    for (int i = 0; i < nd; ++i) d8[i] = (double)D.at<float>(i);
+    if (!R_.empty()) {
+        const Mat R = R_.getMat();
+        assert(R.type() == CV_32F && R.rows == 3 && R.cols == 3);
+        for (int i = 0; i < 9; ++i) R9[i] = (double)R.at<float>(i / 3, i % 3);
+    }
+    if (!P_.empty()) {
+        const Mat P = P_.getMat();
+        assert(P.type() == CV_32F && P.rows == 3 && (P.cols == 3 || P.cols == 4));
+        for (int i = 0; i < 9; ++i) P9[i] = (double)P.at<float>(i / 3, i % 3);
+    }
+    orc_undistort_matrix(P9, R9, RR);
+    std::vector<float> in((size_t)2 * n + 2), out((size_t)2 * n + 2);
+    for (int i = 0; i < n; ++i) { in[2 * i] = src.ptr<float>(i)[0]; in[2 * i + 1] = src.ptr<float>(i)[1]; }
+    orc_undistort_points(in.data(), n, K9, d8, RR, out.data());
+    Mat* dm = dst_.mat_ptr();
+    if (!(dm->data && dm->rows == n && dm->cols == 1 && dm->channels() == 2 && dm->type() == CV_32F))
+        dst_.assign(Mat(n, 2, CV_32F).reshape(2));
+    Mat dst = dst_.getMat();
+    for (int i = 0; i < n; ++i) { dst.ptr<float>(i)[0] = out[2 * i]; dst.ptr<float>(i)[1] = out[2 * i + 1]; }
 }
 
 }  // namespace cv

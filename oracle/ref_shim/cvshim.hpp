@@ -107,14 +107,14 @@ public:
     Mat(int r, int c, int t) { create(r, c, t); }
     Mat(Size s, int t) { create(s.height, s.width, t); }
     Mat(int r, int c, int t, void* ext, size_t st) : rows(r), cols(c), data((uchar*)ext), step(st), type_(t) {}
-    Mat(const Mat& o) : rows(o.rows), cols(o.cols), data(o.data), step(o.step), type_(o.type_), blk_(o.blk_) { retain(); }
+    Mat(const Mat& o) : rows(o.rows), cols(o.cols), data(o.data), step(o.step), type_(o.type_), cn_(o.cn_), blk_(o.blk_) { retain(); }
     Mat(const MatExpr& e) { *this = e; }
     ~Mat() { drop(); }
     Mat& operator=(const Mat& o) {
         if (this != &o) {
             o.retain();
             drop();
-            rows = o.rows; cols = o.cols; data = o.data; step = o.step; type_ = o.type_; blk_ = o.blk_;
+            rows = o.rows; cols = o.cols; data = o.data; step = o.step; type_ = o.type_; cn_ = o.cn_; blk_ = o.blk_;
         }
         return *this;
     }
@@ -123,7 +123,7 @@ public:
     void create(int r, int c, int t) {
         if (data && rows == r && cols == c && type_ == t) return;   // cv::Mat::create: matching shape -> untouched
         drop();
-        rows = r; cols = c; type_ = t;
+        rows = r; cols = c; type_ = t; cn_ = 1;
         step = (size_t)c * elemSize();
         const size_t bytes = step * (size_t)r;
         blk_ = (Block*)std::malloc(sizeof(Block) + bytes + 64);
@@ -133,7 +133,16 @@ public:
     void release() { drop(); rows = cols = 0; data = nullptr; step = 0; }
     int type() const { return type_; }
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
-    size_t elemSize() const { return type_ == CV_32F ? 4 : 1; }
+    size_t elemSize() const { return (type_ == CV_32F ? 4 : 1) * (size_t)cn_; }
+    int channels() const { return cn_; }
+    // cv::Mat::reshape(cn) with the row count kept: an N x 2 one-channel matrix <-> N x 1 two-channel points (src/Frame.cc:687,689)
+    // on a continuous matrix; the view shares the buffer, so an in-place call through the reshaped header lands in the original
+    Mat reshape(int cn) const {
+        assert(step == (size_t)cols * elemSize() && (cols * cn_) % cn == 0);
+        Mat m(*this);
+        m.cols = cols * cn_ / cn; m.cn_ = cn;
+        return m;
+    }
     size_t step1() const { return step / elemSize(); }
 
     Mat operator()(const Rect& r) const { return view(r.y, r.y + r.height, r.x, r.x + r.width); }
@@ -184,7 +193,7 @@ public:
 
 private:
     struct Block { long refs; long pad; };
-    int type_ = 0;
+    int type_ = 0, cn_ = 1;
     Block* blk_ = nullptr;
     void retain() const { if (blk_) __atomic_add_fetch(&blk_->refs, 1, __ATOMIC_RELAXED); }
     void drop() {
@@ -308,6 +317,8 @@ public:
     _OutputArray(Mat& m) : _InputArray(m) {}
     void create(int r, int c, int t) const { m_->create(r, c, t); }
     void release() const { if (m_) m_->release(); }
+    void assign(const Mat& m) const { *m_ = m; }
+    Mat* mat_ptr() const { return m_; }
 };
 typedef const _InputArray& InputArray;
 typedef const _OutputArray& OutputArray;
@@ -326,5 +337,11 @@ void copyMakeBorder(InputArray src, OutputArray dst, int top, int bottom, int le
 void GaussianBlur(InputArray src, OutputArray dst, Size ksize, double sigmaX, double sigmaY = 0,
                   int borderType = BORDER_DEFAULT);
 inline float fastAtan2(float y, float x) { return orc::fast_atan2(y, x); }
+inline _InputArray noArray() { return _InputArray(); }
+// cv::undistortPoints on N x 1 two-channel CV_32F points, CV_32F camera matrices (src/Frame.cc:688,710,745,795,858): forwards to the
+// restated primitive of oracle/undistort.cpp, which tests/test_oracle_cv2.py holds bit-identical to the genuine cv2.undistortPoints.
+// R empty -> identity; P 3x3 or 3x4 (left 3x3 used), empty -> identity; in place allowed.
+void undistortPoints(InputArray src, OutputArray dst, InputArray cameraMatrix, InputArray distCoeffs,
+                     InputArray R = _InputArray(), InputArray P = _InputArray());
 
 }  // namespace cv

@@ -90,6 +90,11 @@ public:
     bool PosInGrid(const cv::KeyPoint& kp, int& posX, int& posY);
     void ComputeStereoMatches();
     int ComputeStereoMatches_Undistorted(bool isOnline = false);
+    // src/Frame.cc:670-887, lifted verbatim; cv::undistortPoints is the shim's (ref_shim/cvshim.cpp)
+    void UndistortKeyPointsStereo();
+    void UndistortKeyPoints();
+    void ComputeImageBounds(const cv::Mat& imLeft);
+    void ComputeImageBoundsStereo(const cv::Mat& imLeft);
 
     ORBextractor *mpORBextractorLeft, *mpORBextractorRight;
     float mbf, mb;
@@ -110,6 +115,7 @@ public:
     // what the frame-to-frame / key-frame searches read in addition (include/Frame.h:290-293, 344, 355, 372, 382-384)
     static float fx, fy, cx, cy;
     cv::Mat mTcw;
+    cv::Mat mK, mK_ori, mDistCoef, mR, mP, mK_right, mDistCoef_right, mR_right, mP_right;     // include/Frame.h:295-307, all CV_32F
     std::vector<bool> mvbOutlier;
     DBoW2::FeatureVector mFeatVec;
     int mnScaleLevels = 8;
