@@ -99,6 +99,7 @@ _SIGS = {
     "gforb_matcher_destroy": (None, [_vp]),
     "gforb_match_bruteforce": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "gforb_match_bruteforce_device": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "gforb_match_bruteforce_static": (_i, [_vp, _i, _vp, _i, C.c_float, _i, _vp, _vp, _vp, _vp, _vp]),
     "gforb_matcher_sync": (_i, [_vp, C.POINTER(C.c_float)]),
     "gforb_assign_features_to_grid": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "gforb_features_in_area": (_i, [_vp, _vp, _vp, _i, _vp, _i, _vp, _vp, _i]),
@@ -208,6 +209,9 @@ class DeviceArray:
             self._ptr = None
 
 
+MATCH_STATIC_MAX_QUERIES = 65536      # GFORB_MATCH_STATIC_MAX_QUERIES (include/gforb.h)
+
+
 class ORBmatcher:
     """ORB_SLAM2::ORBmatcher(float nnratio = 0.6, bool checkOri = true) (include/ORBmatcher.h:46).  Carries
     mfNNratio; BruteForce() is the matcher's nearest / second-nearest loop (src/ORBmatcher.cc:562-576) over all
@@ -241,6 +245,17 @@ class ORBmatcher:
         """device pointers (ints or DeviceArray); asynchronous on `stream` (a cudaStream_t value) or the matcher's own"""
         ptr = lambda x: None if x is None else _vp(x.ptr if isinstance(x, DeviceArray) else x)
         _check(_L.gforb_match_bruteforce_device(self._h, ptr(dev_a), n_a, ptr(dev_b), n_b, th, ptr(dev_best_idx),
+                                                ptr(dev_best_dist), ptr(dev_second_dist), ptr(dev_match),
+                                                _vp(stream) if stream else None))
+
+    @staticmethod
+    def BruteForceStatic(dev_a, n_a, dev_b, n_b, nnratio, th, dev_best_idx, dev_best_dist, dev_second_dist, dev_match,
+                         stream=None):
+        """gforb_match_bruteforce_static: the same matcher without a handle and without any allocation -- its scratch is a
+        fixed 4 MiB device array inside the library (n_a <= MATCH_STATIC_MAX_QUERIES; overlapping calls race).  No
+        counterpart in the reference.  Device pointers; asynchronous on `stream` (None = the default stream)."""
+        ptr = lambda x: None if x is None else _vp(x.ptr if isinstance(x, DeviceArray) else x)
+        _check(_L.gforb_match_bruteforce_static(ptr(dev_a), n_a, ptr(dev_b), n_b, nnratio, th, ptr(dev_best_idx),
                                                 ptr(dev_best_dist), ptr(dev_second_dist), ptr(dev_match),
                                                 _vp(stream) if stream else None))
 

@@ -147,6 +147,20 @@ GFORB_API int gforb_match_bruteforce_device(gforb_matcher* m, const uint8_t* dev
                                   int32_t* dev_second_dist, int32_t* dev_match, void* cuda_stream);
 /* wait for the last device-form call and return its device time (CUDA events around its two kernels) */
 GFORB_API int gforb_matcher_sync(gforb_matcher* m, float* last_ms_or_null);
+/* The same matcher for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * It takes no handle and calls no cudaMalloc / cudaFree / stream or event creation: the per-segment scratch that
+ * gforb_match_bruteforce_device keeps in a cudaMalloc'ed, growing buffer lives in a fixed 4 MiB device array inside the
+ * library (held by every GPU that loads it until the process exits; csrc/k_match_static.cu).  Same kernels (the POPC
+ * pair of k_match.cu), same outputs as gforb_match_bruteforce_device; all pointers are device pointers (outputs may be
+ * NULL); asynchronous on `cuda_stream` (NULL = the default stream); nnratio is ORBmatcher's mfNNratio.
+ * Limits: n_a <= GFORB_MATCH_STATIC_MAX_QUERIES, n_b <= 4,194,304 -- beyond either: GFORB_ERR_CAPACITY, nothing launched.
+ * All calls on one device share the array: calls whose kernels may overlap on the GPU (different streams without a
+ * dependency) race on it -- serialise them.  Nothing needs clearing between calls. */
+#define GFORB_MATCH_STATIC_MAX_QUERIES 65536
+GFORB_API int gforb_match_bruteforce_static(const uint8_t* dev_desc_a, int n_a, const uint8_t* dev_desc_b, int n_b,
+                                  float nnratio, int threshold, int32_t* dev_best_idx, int32_t* dev_best_dist,
+                                  int32_t* dev_second_dist, int32_t* dev_match, void* cuda_stream);
 /* =====================================================================================================
  * Frame feature grid and ORBmatcher::SearchForInitialization   
  *   Frame::AssignFeaturesToGrid / PosInGrid   src/Frame.cc:461-476, 645-656; mGrid include/Frame.h:369
