@@ -105,7 +105,8 @@ def host_sample(cfg, n, seed0=0):
 def algorithmic_bytes(W, H, level_sizes, n_cand, n_kp):
     """Per EYE image, SURVEY.md 8(d) (FAST survivors are 4 B packed here, not 8)."""
     P = sum(w * h for w, h in level_sizes)
-    Ppad = sum((w + 38) * (h + 38) for w, h in level_sizes)
+    # the batch path writes each level's ROI plus the 3-px frame the blur reads (k_pyramid.cu v3), not the 19-px frame of 8(d)
+    Ppad = sum((w + 6) * (h + 6) for w, h in level_sizes)
     return {
         "pyramid": W * H + Ppad,
         "fast": P + 4 * n_cand,

@@ -1223,6 +1223,7 @@ int gforb_batch_create(const gforb_params* p, const gforb_limits* lim, int w, in
     b->stream = b->own;
     b->max_frames = max_frames;
     if (const char* ks = std::getenv("GFORB_KSTREAMS")) b->kstreams = std::min(std::max(std::atoi(ks), 1), 4);   // tuning knob
+    b->eng.full_frames = false;      // no entry point of the batch handle exposes the padded pyramid levels
     rc = b->eng.init(b->tab, b->lim, w, h, 2 * max_frames, max_frames);
     if (rc) return rc;
     *out = b.release();

@@ -1,4 +1,6 @@
 // Host engine: constructor tables, level geometry, arenas, stage sequencing.
+#include <cstdlib>
+
 #include "engine.hpp"
 #include "tma.cuh"
 
@@ -274,7 +276,9 @@ int Engine::init(const Tables& t, const gforb_limits& lim, int W, int H, int nim
     GFORB_CUDA(cudaMalloc(&b.in, NI * W * H));
     pyr_bytes += 64;    // the right frame word of a row may run 2 bytes past the pitch (into row padding)
     GFORB_CUDA(cudaMalloc(&b.pyr, pyr_bytes));
-    GFORB_CUDA(cudaMemset(b.pyr, 0, pyr_bytes));     // alignment bytes outside the 19-px frame are never written
+    // alignment bytes outside the 19-px frame are never written, nor (without full_frames) its outer 16 px: nothing reads them.
+    // GFORB_POISON_PYR=1 fills the arena with 0xCD instead, so that a test run proves it (tools / parity suites).
+    GFORB_CUDA(cudaMemset(b.pyr, getenv("GFORB_POISON_PYR") ? 0xCD : 0, pyr_bytes));
     GFORB_CUDA(cudaMalloc(&b.blur, blur_bytes));
     GFORB_CUDA(cudaMalloc(&b.tabs, std::max<size_t>(tabs.size(), 2) * 4));
     GFORB_CUDA(cudaMalloc(&b.cell_cnt, NI * g.cells_total * 4));
@@ -368,7 +372,7 @@ int Engine::upload_images(const uint8_t* host, size_t pitch, int first_img, int 
 
 int Engine::run_pyramid(int nimg, cudaStream_t s) {
     g.img0 = 0;
-    launch_pyramid(g, b, nimg, s, rsmaps);
+    launch_pyramid(g, b, nimg, s, rsmaps, full_frames);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "pyramid launch");
     pyramid_valid = true;
@@ -389,7 +393,7 @@ int Engine::run_extract(int nimg, cudaStream_t s, cudaEvent_t* ev, int img0, boo
     }
     if (ev) cudaEventRecord(ev[0], s);
     GFORB_RANGE_PUSH("gforb ComputePyramid", 0);
-    launch_pyramid(g, b, nimg, s, rsmaps);
+    launch_pyramid(g, b, nimg, s, rsmaps, full_frames);
     GFORB_RANGE_POP();
     if (ev) cudaEventRecord(ev[1], s);
     GFORB_RANGE_PUSH("gforb FAST cells", 1);

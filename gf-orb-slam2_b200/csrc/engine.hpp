@@ -48,6 +48,8 @@ public:
     int nframes_cap = 0;
     bool ready = false;
     bool pyramid_valid = false;
+    bool full_frames = true;               // write all 19 px of every level's frame (handles that expose the padded levels); the
+                                           // batch path clears it: its kernels read the ROI and 3 px of frame (k_pyramid.cu)
     cudaStream_t s_aux = nullptr;          // side stream of run_extract(fork_blur)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int32_t* h_small = nullptr;   // pinned: counts / flags read-back

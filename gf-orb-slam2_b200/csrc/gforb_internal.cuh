@@ -149,7 +149,10 @@ enum ErrBits { kErrCandOverflow = 1, kErrCellOverflow = 2, kErrNodeOverflow = 4,
 
 // ---- kernel launchers (each enqueues on `s`; defined in the per-stage .cu files) ----
 // images [g.img0, g.img0+nimg); rsmaps[l] = TMA map of level l-1 with level l's resize box (null: no TMA path)
-void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s, const CUtensorMap* rsmaps = nullptr);
+// full_frames: also write the 16 outer pixels of every level's 19-px frame (one more launch); without it the levels carry the
+// ROI and the 3-px frame the blur reads -- all any kernel of this library looks at
+void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s, const CUtensorMap* rsmaps = nullptr,
+                    bool full_frames = true);
 int octree_small_cap(const Geom& g);
 // kernels one extraction enqueues: nlevels pyramid + fast, quadtree (2 tiers when max_cand exceeds the small cap), blur, describe
 inline int extract_launches(const Geom& g) { return g.nlevels + 4 + (octree_small_cap(g) < g.max_cand ? 1 : 0); }

@@ -2,8 +2,8 @@
 //
 // Level 0 = input copied into a padded buffer; level l = cv::resize(level l-1, INTER_LINEAR) in OpenCV's
 // 11-bit fixed point, cascaded; every level gets a 19-px BORDER_REFLECT_101 frame.  The frame is a pure
-// function of the ROI, so each kernel writes the WHOLE padded level in one pass: a frame pixel is the
-// resize evaluated at the reflected coordinate.  The source level is itself padded, so the +1 taps never
+// function of the ROI: a frame pixel is the resize evaluated at the reflected coordinate (generic kernels below: the WHOLE
+// padded level in one pass; fast path: see there).  The source level is itself padded, so the +1 taps never
 // leave valid memory and need no clamp (their weight is 0 exactly when OpenCV clamps).
 //
 // Memory: one thread produces 4 horizontally adjacent bytes and stores one 32-bit word; pitch is a multiple
@@ -93,19 +93,30 @@ pyr_resize_kernel(const uint8_t* __restrict__ src_roi, int spitch, size_t simg_s
 
 
 // ------------------------------------------------------------------------------------------------
-// Fast path (v2).  A thread owns 4 horizontally adjacent ROI pixels (one aligned 32-bit word) and walks down
-// kRowsPerThread rows; a warp owns 32 adjacent groups.  The frame is not computed: frame pixel == ROI pixel at
-// the REFLECT_101 coordinate (copyMakeBorder after resize, src/ORBextractor.cc:1189-1197), so
-//  * every word is also stored at its mirror rows inside the top/bottom frame;
-//  * the warp that holds the left edge builds the five frame words left of the ROI from its own words
-//    (SHFL.DOWN + PRMT), the warp that holds the right edge builds the frame words right of it (SHFL.UP + PRMT);
-//    the last warp column is shifted left to start at group ng-32, so the right edge never straddles two warps
-//    (the overlap recomputes identical words).
+// Fast path (v3).  A thread owns 4 horizontally adjacent ROI pixels (one aligned 32-bit word) and walks down
+// kRowsPerThread rows; a warp owns 32 adjacent groups; the last warp column is shifted left to start at group ng-32
+// (the overlap recomputes identical words), so an ROI edge never straddles two warps.
+//
+// Who reads the 19-px BORDER_REFLECT_101 frame (copyMakeBorder after resize, src/ORBextractor.cc:1189-1197)?  The next
+// level's resize does not (its taps outside the ROI carry weight 0); FAST, the orientation patch and the stereo windows
+// stay >= 16 px inside the ROI; the descriptor reads the blurred level, which has no frame.  Only the 7x7 blur does, and it
+// reaches 3 px.  So the level kernels write the ROI plus a kBlurFrame = 3 px frame, and the other 16 px are written by
+// pyr_frame_kernel only where somebody can look at them: the single-image extractor handles, whose
+// gforb_pyramid_level / gforb_download_pyramid expose the padded level (mvImagePyramid).  The batch path skips them.
+// The 3-px frame is not computed either: frame pixel == ROI pixel at the reflected coordinate, so
+//  * lane 0 of the left-edge warp stores {-, p3, p2, p1} (one PRMT of its own word) in the word left of the ROI;
+//  * the lane of the last group stores, from (previous lane's word, own word) with two PRMT, its own word completed with
+//    mirrored pixels (w % 4 != 0) and the word after it;
+//  * rows 1..3 and h-4..h-2 are stored a second time at their mirror rows.
 // Every store is an aligned 32-bit word; interior warps run no edge code at all.
+// v2 wrote all 19 px this way (5 + 5 side words per row, 2 x 19 mirror rows): 0.534 ms per 512 images, v3 0.467 ms; measured on the way
+// here: no frame at all 0.402 ms, the whole frame in a separate kernel 0.86 ms (side strips = two cold 20-byte accesses
+// per row), side words in the level kernels + top / bottom rows in a separate kernel 0.515 ms.
 namespace {
 constexpr int kRowsPerThread = 8;                       // level 0
 constexpr int kResizeRows = kResizeTileRows / 4;        // resize: rows per thread (4 warps per CTA)
 static_assert(kResizeRows == 8, "the row table is fetched eight rows at a time");
+constexpr int kBlurFrame = 3;                           // frame pixels the blur reads (7 taps)
 
 __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {   // selector nibbles <= 7 only
     uint32_t d;
@@ -113,92 +124,71 @@ __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
     return d;
 }
 
-struct RowStore {
-    uint8_t* p;            // this thread's word on ROI row 0
-    int pitch, h;
-    int loff, roff;        // byte offset of the left / right frame word this thread writes, relative to p
-    uint32_t sel_main, sel_r;
-    bool valid, lon, ron;  // thread owns ROI pixels / writes a left / right frame word
-    bool ledge, redge;     // warp-uniform: warp holds the left / right ROI edge
-    bool yedge;            // warp-uniform: strip touches the top or bottom frame
+// PRMT selectors of the last group's two words over (previous lane's word, own word): byte i of that pair = pixel
+// XG - 4 + i (XG = first pixel of the last group); word 0 = columns XG..XG+3, word 1 = the following four; a column inside the
+// ROI takes its pixel, a frame column up to w + 2 its REFLECT_101 image, columns past that are nobody's (byte 0)
+inline uint2 edge_selectors(int w) {
+    const int ng = (w + 3) >> 2, q = 2 * (w - 1), XG = 4 * (ng - 1);
+    uint2 sel = make_uint2(0u, 0u);
+    for (int i = 0; i < 8; ++i) {
+        const int c = XG + i;
+        const int src = c < w ? c : q - c;
+        const uint32_t idx = c < w + kBlurFrame ? (uint32_t)(src - XG + 4) : 0u;
+        if (i < 4) sel.x |= idx << (4 * i);
+        else sel.y |= idx << (4 * (i - 4));
+    }
+    return sel;
+}
 
-    // gx = group index (may be >= ng: idle lane kept alive for the shuffles), g0 = first group of the warp
-    __device__ __forceinline__ void init(uint8_t* lvl, int pitch_, int gx, int g0, int w, int h_, int y0, int y1) {
-        const int ng = (w + 3) >> 2, X = gx * 4, q = 2 * (w - 1);
+struct RowStore {
+    int pitch, h;
+    uint32_t sel_m, sel_f;   // last group: own word / following word out of (previous lane's word, own word)
+    bool valid, lon, last;   // thread owns ROI pixels / is lane 0 of the left-edge warp / owns the last group
+    bool ledge, redge;       // warp-uniform: warp holds the left / right ROI edge
+    bool yedge;              // warp-uniform: the strip holds rows that are mirrored into the 3-px frame
+    bool plain;              // warp-uniform: none of the above
+
+    // gx = group index (may be >= ng: idle lane kept alive for the shuffle), g0 = first group of the warp
+    // sels = the level's two selectors (edge_selectors, computed on the host once per launch)
+    __device__ __forceinline__ void init(int pitch_, int gx, int g0, int w, int h_, int y0, int y1, uint2 sels) {
+        const int ng = (w + 3) >> 2;
         pitch = pitch_; h = h_;
-        p = lvl + (size_t)kEdge * pitch_ + kXPad + X;
+        sel_m = sels.x; sel_f = sels.y;
         valid = gx < ng;
         ledge = g0 == 0;
         redge = g0 + 32 >= ng;
-        yedge = y0 <= kEdge || y1 - 1 >= h - 1 - kEdge;
-        // left: group j in 0..4 writes columns [-4(j+1), -4j-1] = pixels 4(j+1), 4j+3, 4j+2, 4j+1
-        lon = ledge && gx < 5;
-        loff = -(8 * gx + 4);
-        // right: group gx writes frame word d = (q >> 2) - gx = pixels 4gx+e-i (i = 0..3), e = q & 3, from (prev, own)
-        const int d = (q >> 2) - gx;
-        ron = redge && valid && 4 * d >= w && 4 * d <= w + kEdge - 1;
-        roff = 4 * d - X;
-        sel_r = (q & 3) ? 0x3456u : 0x1234u;
-        // the last group when w % 4 != 0: its word runs into the frame; those bytes take their mirrored pixels
-        sel_main = 0x7654u;
-        if (valid && X + 3 >= w) {
-            sel_main = 0;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int c = X + i;
-                sel_main |= (uint32_t)(c < w ? 4 + i : q - c - (X - 4)) << (4 * i);
-            }
-        }
+        yedge = y0 <= kBlurFrame || y1 - 1 >= h - 1 - kBlurFrame;
+        plain = !(ledge | redge | yedge);
+        lon = gx == 0;
+        last = gx == ng - 1;
     }
-    __device__ __forceinline__ void rows(int y, uint32_t m, uint32_t lw, uint32_t rw) const {
-        uint8_t* r = p + (ptrdiff_t)y * pitch;
+    // r = this thread's word on some padded row
+    __device__ __forceinline__ void put(uint8_t* r, uint32_t m, uint32_t lw, uint32_t rw) const {
         if (valid) *reinterpret_cast<uint32_t*>(r) = m;
-        if (lon) *reinterpret_cast<uint32_t*>(r + loff) = lw;
-        if (ron) *reinterpret_cast<uint32_t*>(r + roff) = rw;
+        if (ledge && lon) *reinterpret_cast<uint32_t*>(r - 4) = lw;
+        if (redge && last) *reinterpret_cast<uint32_t*>(r + 4) = rw;
     }
-    // the same with the row's address already in hand: r = this thread's word on ROI row y.  The mirror rows are reached
-    // relative to r (row -y is 2y rows up, row 2(h-1)-y is 2(h-1-y) rows down), so the common case costs no multiply.
-    __device__ __forceinline__ void rows_at(uint8_t* r, uint32_t m, uint32_t lw, uint32_t rw) const {
-        if (valid) *reinterpret_cast<uint32_t*>(r) = m;
-        if (lon) *reinterpret_cast<uint32_t*>(r + loff) = lw;
-        if (ron) *reinterpret_cast<uint32_t*>(r + roff) = rw;
-    }
+    // all 32 lanes of a non-plain warp call this together (shuffle); r = this thread's word on ROI row y
     __device__ __forceinline__ void store_at(uint8_t* r, int y, uint32_t own) const {
         uint32_t m = own, lw = 0, rw = 0;
-        if (ledge) lw = prmt(own, __shfl_down_sync(0xffffffffu, own, 1), 0x1234u);
+        if (ledge) lw = prmt(own, own, 0x1230u);                           // columns -3..-1 = pixels 3, 2, 1
         if (redge) {
             const uint32_t prev = __shfl_up_sync(0xffffffffu, own, 1);
-            m = prmt(prev, own, sel_main);
-            rw = prmt(prev, own, sel_r);
+            if (last) { m = prmt(prev, own, sel_m); rw = prmt(prev, own, sel_f); }
         }
-        rows_at(r, m, lw, rw);
+        put(r, m, lw, rw);
         if (yedge) {
-            if (y >= 1 && y <= kEdge) rows_at(r - (ptrdiff_t)(2 * y) * pitch, m, lw, rw);
-            if (y >= h - 1 - kEdge && y <= h - 2) rows_at(r + (ptrdiff_t)(2 * (h - 1 - y)) * pitch, m, lw, rw);
-        }
-    }
-    // all 32 lanes of the warp must call this together (shuffles)
-    __device__ __forceinline__ void store(int y, uint32_t own) const {
-        uint32_t m = own, lw = 0, rw = 0;
-        if (ledge) lw = prmt(own, __shfl_down_sync(0xffffffffu, own, 1), 0x1234u);
-        if (redge) {
-            const uint32_t prev = __shfl_up_sync(0xffffffffu, own, 1);
-            m = prmt(prev, own, sel_main);
-            rw = prmt(prev, own, sel_r);
-        }
-        rows(y, m, lw, rw);
-        if (yedge) {
-            if (y >= 1 && y <= kEdge) rows(-y, m, lw, rw);
-            if (y >= h - 1 - kEdge && y <= h - 2) rows(2 * (h - 1) - y, m, lw, rw);
+            if (y >= 1 && y <= kBlurFrame) put(r - (ptrdiff_t)(2 * y) * pitch, m, lw, rw);
+            if (y >= h - 1 - kBlurFrame && y <= h - 2) put(r + (ptrdiff_t)(2 * (h - 1 - y)) * pitch, m, lw, rw);
         }
     }
 };
 }  // namespace
 
-// level 0: input (tight, W % 4 == 0) -> padded level; thread = 4 pixels x kRowsPerThread rows
+// level 0: input (tight, W % 4 == 0) -> ROI + 3-px frame of the padded level; thread = 4 pixels x kRowsPerThread rows
 __global__ void __launch_bounds__(128)
 pyr_level0_fast_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int W, int H, int pitch,
-                       size_t img_stride, int img0) {
+                       size_t img_stride, int img0, uint2 sels) {
     const int img = img0 + blockIdx.z;
     const int ng = W >> 2;
     const int g0 = min((int)blockIdx.x * 32, max(ng - 32, 0));
@@ -208,14 +198,60 @@ pyr_level0_fast_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out
     const int y1 = min(y0 + kRowsPerThread, H);
     const uint8_t* src = in + (size_t)img * W * H + 4 * min(gx, ng - 1);
     RowStore st;
-    st.init(out + (size_t)img * img_stride, pitch, gx, g0, W, H, y0, y1);
+    st.init(pitch, gx, g0, W, H, y0, y1, sels);
+    uint8_t* p = out + (size_t)img * img_stride + (size_t)(kEdge + y0) * pitch + kXPad + 4 * gx;
     uint32_t v[kRowsPerThread];
 #pragma unroll
     for (int r = 0; r < kRowsPerThread; ++r)
         v[r] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)min(y0 + r, H - 1) * W));
 #pragma unroll
-    for (int r = 0; r < kRowsPerThread; ++r)
-        if (y0 + r < y1) st.store(y0 + r, v[r]);
+    for (int r = 0; r < kRowsPerThread; ++r) {
+        if (y0 + r < y1) {
+            if (st.plain) *reinterpret_cast<uint32_t*>(p) = v[r];
+            else st.store_at(p, y0 + r, v[r]);
+        }
+        p += pitch;
+    }
+}
+
+// The rest of the 19-px frame of ALL levels of an image, for the handles that expose the padded levels.  Thread = one
+// aligned 32-bit word of a frame: 2 x 19 top / bottom rows (words from ROI column -20 up to the one that holds column
+// w + 18), and on the h ROI rows the 5 words of columns [-20, -1] plus the words from w & ~3 to the one holding column
+// w + 18.  A byte takes the ROI pixel at the reflected coordinate (bytes outside [-19, w + 19) take 0; ROI bytes of a
+// partial last word are copied onto themselves; the 3-px frame of the level kernels is rewritten with the same values).
+struct FrameItems { int base[kMaxLevels + 1]; };
+__global__ void __launch_bounds__(256)
+pyr_frame_kernel(const Geom g, uint8_t* pyr, const FrameItems fi) {
+    const int img = g.img0 + blockIdx.y;
+    int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= fi.base[g.nlevels]) return;
+    int l = 0;
+    while (i >= fi.base[l + 1]) ++l;
+    i -= fi.base[l];
+    const LevelGeom& L = g.lv[l];
+    const int w = L.w, h = L.h, pitch = L.pitch;
+    const int nW = ((w + 38) >> 2) + 1, XR0 = w & ~3, nS = 5 + ((w + 18 - XR0) >> 2) + 1;
+    int py, X;                                            // padded row; ROI column of the word's first byte
+    const int ntb = 2 * kEdge * nW;
+    if (i < ntb) {
+        const int r = i / nW;
+        X = -20 + 4 * (i - r * nW);
+        py = r < kEdge ? r : h + r;
+    } else {
+        i -= ntb;
+        const int r = i / nS, k = i - r * nS;
+        py = kEdge + r;
+        X = k < 5 ? -20 + 4 * k : XR0 + 4 * (k - 5);
+    }
+    uint8_t* lvl = pyr + L.off + (size_t)img * L.img_stride;
+    const uint8_t* src = lvl + (size_t)(kEdge + reflect101(py - kEdge, h)) * pitch + kXPad;
+    uint32_t word = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int c = X + k;
+        if (c >= -kEdge && c < w + kEdge) word |= (uint32_t)src[reflect101(c, w)] << (8 * k);
+    }
+    *reinterpret_cast<uint32_t*>(lvl + (size_t)py * pitch + kXPad + X) = word;
 }
 
 __device__ __forceinline__ void lds3(uint32_t addr, uint32_t& a, uint32_t& b, uint32_t& c) {
@@ -243,7 +279,7 @@ template <bool kTma>
 __global__ void __launch_bounds__(128)
 pyr_resize_fast_kernel(const __grid_constant__ CUtensorMap smap, const uint8_t* __restrict__ src_roi, int spitch,
                        size_t simg_stride, uint8_t* __restrict__ out, int w, int h, int pitch, size_t img_stride,
-                       const uint4* __restrict__ tab_g, const int2* __restrict__ tab_y, int bw, int bh, int img0) {
+                       const uint4* __restrict__ tab_g, const int2* __restrict__ tab_y, int bw, int bh, int img0, uint2 sels) {
     extern __shared__ __align__(128) uint8_t tile[];
     __shared__ __align__(8) uint64_t bar;
     const int img = img0 + blockIdx.z;
@@ -269,15 +305,15 @@ pyr_resize_fast_kernel(const __grid_constant__ CUtensorMap smap, const uint8_t* 
     const uint4 ga = __ldg(tab_g + 2 * gc), gb = __ldg(tab_g + 2 * gc + 1);
     const uint32_t cf[4] = {gb.x, gb.y, gb.z, gb.w};
     RowStore st;
-    st.init(out + (size_t)img * img_stride, pitch, gx, g0, w, h, y0, y1);
+    st.init(pitch, gx, g0, w, h, y0, y1, sels);
     const uint8_t* s = src_roi + (size_t)img * simg_stride + ga.x;          // !kTma: global source
     const uint32_t sa = smem_u32(tile) + (uint32_t)((int)ga.x - xb);        // kTma: shared byte address of this group
     if (kTma) mbar_wait(&bar, 0);
 
     // One running row pointer (the address arithmetic per row was a third of this kernel's instructions), and the
     // interior warps -- no ROI edge, no frame row, every lane live: warp-uniform -- store without any edge code.
-    uint8_t* p = st.p + (ptrdiff_t)y0 * pitch;
-    const bool plain = !(st.ledge | st.redge | st.yedge);
+    uint8_t* p = out + (size_t)img * img_stride + (size_t)(kEdge + y0) * pitch + kXPad + 4 * gx;
+    const bool plain = st.plain;
     // The two horizontal-pass results ping-pong between sA and sB: on even rows sA is the upper tap row and sB the lower,
     // on odd rows the other way round, so a reused row (the lower row of y is the upper row of y + 1 five times out of
     // six at scale 1.2) costs no register moves -- the loop is fully unrolled and the roles are static.
@@ -326,14 +362,15 @@ pyr_resize_fast_kernel(const __grid_constant__ CUtensorMap smap, const uint8_t* 
     }
 }
 
-void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s, const CUtensorMap* rsmaps) {
+void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s, const CUtensorMap* rsmaps, bool full_frames) {
     const dim3 blk(32, 8);
     const dim3 fblk(32, 4);
     {
         const LevelGeom& L = g.lv[0];
         if (g.W % 4 == 0) {
             dim3 grd((g.W / 4 + 31) / 32, (g.H + 4 * kRowsPerThread - 1) / (4 * kRowsPerThread), nimg);
-            pyr_level0_fast_kernel<<<grd, fblk, 0, s>>>(b.input(), b.pyr + L.off, g.W, g.H, L.pitch, L.img_stride, g.img0);
+            pyr_level0_fast_kernel<<<grd, fblk, 0, s>>>(b.input(), b.pyr + L.off, g.W, g.H, L.pitch, L.img_stride, g.img0,
+                                                        edge_selectors(g.W));
         } else {
             dim3 grd((L.pitch / 4 + blk.x - 1) / blk.x, (L.rows + blk.y - 1) / blk.y, nimg);
             pyr_level0_kernel<<<grd, blk, 0, s>>>(b.input(), b.pyr + L.off, g.W, g.H, L.pitch, L.rows, L.img_stride, g.img0);
@@ -350,11 +387,11 @@ void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s, c
             if (rsmaps && L.rs_bw)
                 pyr_resize_fast_kernel<true><<<grd, fblk, (size_t)L.rs_bw * L.rs_bh, s>>>(
                     rsmaps[l], src_roi, P.pitch, P.img_stride, b.pyr + L.off, L.w, L.h, L.pitch, L.img_stride, tg, ty,
-                    L.rs_bw, L.rs_bh, g.img0);
+                    L.rs_bw, L.rs_bh, g.img0, edge_selectors(L.w));
             else
                 pyr_resize_fast_kernel<false><<<grd, fblk, 0, s>>>(
                     CUtensorMap{}, src_roi, P.pitch, P.img_stride, b.pyr + L.off, L.w, L.h, L.pitch, L.img_stride, tg, ty,
-                    0, 0, g.img0);
+                    0, 0, g.img0, edge_selectors(L.w));
             continue;
         }
         dim3 grd((L.pitch / 4 + blk.x - 1) / blk.x, (L.rows + blk.y - 1) / blk.y, nimg);
@@ -362,6 +399,19 @@ void launch_pyramid(const Geom& g, const Buffers& b, int nimg, cudaStream_t s, c
                                               L.rows, L.img_stride,
                                               reinterpret_cast<const int2*>(b.tabs + L.tab_x),
                                               reinterpret_cast<const int2*>(b.tabs + L.tab_y), L.area2x, g.img0);
+    }
+    if (full_frames) {
+        FrameItems fi;
+        fi.base[0] = 0;
+        for (int l = 0; l < kMaxLevels; ++l) {
+            fi.base[l + 1] = fi.base[l];
+            if (l >= g.nlevels) continue;
+            const int w = g.lv[l].w, h = g.lv[l].h;
+            const int nW = ((w + 38) >> 2) + 1, nS = 5 + ((w + 18 - (w & ~3)) >> 2) + 1;
+            fi.base[l + 1] += 2 * kEdge * nW + h * nS;
+        }
+        dim3 grd((fi.base[g.nlevels] + 255) / 256, nimg);
+        pyr_frame_kernel<<<grd, 256, 0, s>>>(g, b.pyr, fi);
     }
 }
 
