@@ -31,6 +31,11 @@
 //  (4) NMS walks the same list on a zero-initialised score map.
 // Algorithmic bytes = level pixels read once + 4 B per survivor.
 //
+// Round 2, late: grid = (cell groups, images) instead of one linear index split by a 64-bit division; both halves of the row
+// count scan in one register; pass 1a branch-free up to the ballot with the column limits moved to pass 1b and the word
+// list holding tile word indices (57 -> 47 instructions per 32 words): 1.075 -> 1.039 ms per 512 images.  ncu: issue slots
+// 80 % busy, ALU pipe 70 %, math-pipe throttle the first stall reason -- what is left is instruction count on the ALU pipe.
+//
 // Open (evaluated, not built; neither changes results):
 //  * band tiles: one warp takes a vertical band of cells and keeps the three rows above / below in registers across
 //    the cell boundary, so the +-3-row words of pass (1) and the ring rows of pass (3) are loaded once per band instead
@@ -40,6 +45,8 @@
 //    kept as a row bitmap for the cells that turn out empty: removes the second pass (1) for ~half of the cells,
 //    adds ~28 % to pass (1) of every cell: net -6 % of this kernel; needs 512 B more shared memory per warp, which
 //    costs one resident CTA per SM.
+#include <type_traits>
+
 #include "gforb_internal.cuh"
 #include "tma.cuh"
 
@@ -116,10 +123,9 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
     extern __shared__ __align__(128) uint8_t smem[];
 
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const long long gcell = (long long)blockIdx.x * kWarpsPerCta + wid;      // (image, cell) pair
-    if (gcell >= (long long)a.nimg * a.cells_total) return;
-    const int iimg = (int)(gcell / a.cells_total), cell = (int)(gcell - (long long)iimg * a.cells_total);
-    const int img = a.img0 + iimg;
+    const int cell = blockIdx.x * kWarpsPerCta + wid;       // grid = (cell groups, images): no division to split a linear index
+    if (cell >= a.cells_total) return;
+    const int img = a.img0 + blockIdx.y;
     const size_t out_cell = (size_t)img * a.cells_total + cell;
     const uint4 ca = __ldg(a.cell_tab + 2 * cell), cb = __ldg(a.cell_tab + 2 * cell + 1);
     const int cw = (ca.y >> 8) & 0xFF, ch = (ca.y >> 16) & 0xFF;
@@ -154,8 +160,9 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
     const int nitems = dh * nw;                         // item = one 32-bit word of a domain row
     const int qs = (int)(cb.y & 0xFF), rs = (int)(cb.y >> 8);         // 32 = qs * nw + rs
     const int ir0 = (lane * (int)cb.x) >> 16, iw0 = lane - ir0 * nw;  // cb.x = ceil(65536 / nw): lane -> (row, word)
-    const uint32_t cm_first = 0xFFFFFFFFu << (8 * (xlo & 3));
-    const uint32_t cm_last = 0xFFFFFFFFu >> (8 * (3 - ((xhi - 1) & 3)));
+    const uint32_t c4_first = (0xFu << (xlo & 3)) & 0xFu;            // pixels of the first / last word column inside [xlo, xhi)
+    const uint32_t c4_last = 0xFu >> (3 - ((xhi - 1) & 3));
+    const uint32_t inv_tpw = cb.z;                                     // ceil(65536 / tpw)
     const uint32_t lt = (1u << lane) - 1u;
     const int pstep = qs * tpw + rs, pwrap = tpw - nw;
     __syncwarp();                                       // barrier init + clears visible to the whole warp
@@ -174,51 +181,63 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
         const uint32_t pmask = (~(uint32_t)((1 << (31 - __clz(min(tc, 127) + 1))) - 1) & 0xFFu) * 0x01010101u;
 
         // ---- pass 1a: 4-pixel prefilter, 32 words per step; words with any flagged pixel are compacted by ONE ballot
-        //      into a word list (row << 9 | word column << 4 | 4-bit pixel mask) ----
-        int iw = iw0;
-        uint32_t ent = ((uint32_t)(3 + ir0) << 9) | ((uint32_t)(w0 + iw0) << 4);      // word-list entry of the lane's current item
-        const uint32_t ent_step = ((uint32_t)qs << 9) + ((uint32_t)rs << 4), ent_wrap = (1u << 9) - ((uint32_t)nw << 4);
-        const uint32_t* p = reinterpret_cast<const uint32_t*>(tile) + (3 + ir0) * tpw + w0 + iw0;
-        const bool list_all = tc == 0;                  // "> 0" has no cleared-low-bit form: list the whole domain
+        //      into a word list (tile word index << 4 | 4-bit pixel mask).  Branch-free up to the ballot: a lane past the
+        //      last item reads a safe word and drops its flags; the domain's column limits are applied in pass 1b, on the
+        //      listed words only.  tc == 0 ("> 0" has no cleared-low-bit form) lists the whole domain: its own loop ----
+        const uint32_t* const tile32 = reinterpret_cast<const uint32_t*>(tile);
+        const uint32_t* const psafe = tile32 + 3 * tpw + 1;                 // rows 0..6, words 0..2: inside every tile
         int nwl = 0;
-        for (int i0 = 0; i0 < nitems; i0 += 32) {
-            uint32_t f = 0;
-            if (i0 + lane < nitems) {
-                const uint32_t C = p[0], Wm = p[-1], Wp = p[1], U = p[-3 * tpw], D = p[3 * tpw];
-                const uint32_t Lw = __funnelshift_r(Wm, C, 8), Rw = __funnelshift_r(C, Wp, 24);
-                const uint32_t v = (__vabsdiffu4(C, U) | __vabsdiffu4(C, D)) & pmask;
-                const uint32_t h = (__vabsdiffu4(C, Lw) | __vabsdiffu4(C, Rw)) & pmask;
-                f = list_all ? 0x80808080u : (nz_lanes(v) & nz_lanes(h) & 0x80808080u);
-                // columns outside [xlo, xhi) (first / last word of the row)
-                if (iw == 0) f &= cm_first;
-                if (iw == nw - 1) f &= cm_last;
+        auto prefilter = [&](auto all_tag) {
+            constexpr bool kAll = decltype(all_tag)::value;
+            int iw = iw0;
+            const uint32_t* p = tile32 + (3 + ir0) * tpw + w0 + iw0;
+            for (int i0 = 0; i0 < nitems; i0 += 32) {
+                const bool ok = i0 + lane < nitems;
+                uint32_t f;
+                if (kAll) f = ok ? 0x80808080u : 0u;
+                else {
+                    const uint32_t* q = ok ? p : psafe;
+                    const uint32_t C = q[0], Wm = q[-1], Wp = q[1], U = q[-3 * tpw], D = q[3 * tpw];
+                    const uint32_t Lw = __funnelshift_r(Wm, C, 8), Rw = __funnelshift_r(C, Wp, 24);
+                    const uint32_t v = (__vabsdiffu4(C, U) | __vabsdiffu4(C, D)) & pmask;
+                    const uint32_t h = (__vabsdiffu4(C, Lw) | __vabsdiffu4(C, Rw)) & pmask;
+                    f = ok ? (nz_lanes(v) & nz_lanes(h) & 0x80808080u) : 0u;
+                }
+                const uint32_t m = __ballot_sync(0xffffffffu, f != 0);
+                if (f != 0) {
+                    // flag bits 7, 15, 23, 31 -> mask bits 0..3: the four 0/1 bytes times 0x01020408 meet in the top byte
+                    const uint32_t m4 = (((f >> 7) & 0x01010101u) * 0x01020408u) >> 24;
+                    wlist[nwl + __popc(m & lt)] = (uint16_t)(((uint32_t)(p - tile32) << 4) | m4);
+                }
+                nwl += __popc(m);
+                iw += rs; p += pstep;
+                if (iw >= nw) { iw -= nw; p += pwrap; }
             }
-            const uint32_t m = __ballot_sync(0xffffffffu, f != 0);
-            if (f != 0) {
-                // flag bits 7, 15, 23, 31 -> mask bits 0..3: the four 0/1 bytes times 0x01020408 meet in the top byte
-                const uint32_t m4 = (((f >> 7) & 0x01010101u) * 0x01020408u) >> 24;
-                wlist[nwl + __popc(m & lt)] = (uint16_t)(ent | m4);
-            }
-            nwl += __popc(m);
-            iw += rs; p += pstep; ent += ent_step;
-            if (iw >= nw) { iw -= nw; p += pwrap; ent += ent_wrap; }
-        }
+        };
+        if (tc == 0) prefilter(std::true_type{});
+        else prefilter(std::false_type{});
         __syncwarp();
         // ---- pass 1b: expand the word list into the pixel list ((row << 8) | tile column); order is irrelevant.
+        //      Columns outside [xlo, xhi) leave here (first / last word column of the domain).
         //      Per-lane counts are <= 4: three ballots give the exclusive prefix ----
         int nlist = 0;
         for (int k0 = 0; k0 < nwl; k0 += 32) {
             const uint32_t we = k0 + lane < nwl ? wlist[k0 + lane] : 0u;
-            const int c = __popc(we & 15u);
+            const uint32_t widx = we >> 4;
+            const uint32_t row = (widx * inv_tpw) >> 16, wc = widx - row * (uint32_t)tpw;     // exact: widx < 66 * 64
+            uint32_t m4 = we & 15u;
+            if ((int)wc == w0) m4 &= c4_first;
+            if ((int)wc == w0 + nw - 1) m4 &= c4_last;
+            const int c = __popc(m4);
             const uint32_t b0 = __ballot_sync(0xffffffffu, c & 1), b1 = __ballot_sync(0xffffffffu, c & 2);
             const uint32_t b2 = __ballot_sync(0xffffffffu, c & 4);
             uint16_t* out = list + nlist + __popc(b0 & lt) + 2 * __popc(b1 & lt) + 4 * __popc(b2 & lt);
             nlist += __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
-            const uint32_t e = ((we >> 9) << 8) | (((we >> 4) & 31u) << 2);
-            if (we & 1u) *out++ = (uint16_t)e;
-            if (we & 2u) *out++ = (uint16_t)(e + 1);
-            if (we & 4u) *out++ = (uint16_t)(e + 2);
-            if (we & 8u) *out++ = (uint16_t)(e + 3);
+            const uint32_t e = (row << 8) | (wc << 2);
+            if (m4 & 1u) *out++ = (uint16_t)e;
+            if (m4 & 2u) *out++ = (uint16_t)(e + 1);
+            if (m4 & 4u) *out++ = (uint16_t)(e + 2);
+            if (m4 & 8u) *out++ = (uint16_t)(e + 3);
         }
         __syncwarp();
         {   // the word list is dead: clear the score map (domain + zero ring) it shared
@@ -268,15 +287,16 @@ fast_cells_kernel(const FastArgs a, const __grid_constant__ TileMaps maps) {
         if (lane + 32 < dh) m1 = (unsigned long long)keep_lo[2 * lane + 64] | ((unsigned long long)keep_lo[2 * lane + 65] << 32);
         if (__any_sync(0xffffffffu, (m0 | m1) != 0) || t_min == t_ini) break;     // keypoints found: no retry (:813)
     }
-    // exclusive scan of the <= 59 row counts
+    // exclusive scan of the <= 59 row counts; both halves ride in one register (a half's total is <= 32 * 59 < 65536)
     const int c0 = __popcll(m0), c1 = __popcll(m1);
-    int i0 = c0, i1 = c1;
+    int i01 = c0 | (c1 << 16);
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-        const int t0 = __shfl_up_sync(0xffffffffu, i0, o), t1 = __shfl_up_sync(0xffffffffu, i1, o);
-        if (lane >= o) { i0 += t0; i1 += t1; }
+        const int t = __shfl_up_sync(0xffffffffu, i01, o);
+        if (lane >= o) i01 += t;
     }
-    const int tot0 = __shfl_sync(0xffffffffu, i0, 31), tot1 = __shfl_sync(0xffffffffu, i1, 31);
+    const int tot01 = __shfl_sync(0xffffffffu, i01, 31);
+    const int i0 = i01 & 0xFFFF, i1 = i01 >> 16, tot0 = tot01 & 0xFFFF, tot1 = tot01 >> 16;
     int total = tot0 + tot1;
     if (total > a.cell_cap) {
         if (lane == 0) atomicOr(a.err, kErrCellOverflow);
@@ -328,6 +348,7 @@ void build_fast_cell_table(const Geom& g, std::vector<uint32_t>& tab) {
             e[3] = (uint32_t)L.fast_bw | ((uint32_t)L.fast_bh << 8) | ((uint32_t)R << 16) | ((uint32_t)nw << 24);
             e[4] = (uint32_t)((65536 + nw - 1) / nw);
             e[5] = (uint32_t)(32 / nw) | ((uint32_t)(32 % nw) << 8);
+            e[6] = (uint32_t)((65536 + L.fast_bw / 4 - 1) / (L.fast_bw / 4));
         }
     }
 }
@@ -367,9 +388,8 @@ void launch_fast(const Geom& g, const TileMaps& m, const Buffers& b, int nimg, c
     a.tile_bytes = f.tile_bytes; a.sc_bytes = f.sc_bytes; a.plist_bytes = f.plist_bytes; a.warp_bytes = f.warp_bytes;
     a.cell_tab = reinterpret_cast<const uint4*>(b.cell_tab);
     a.cell_cnt = b.cell_cnt; a.cell_pts = b.cell_pts; a.err = b.err;
-    const long long ncell = (long long)nimg * g.cells_total;
-    if (ncell == 0) return;
-    const unsigned grd = (unsigned)((ncell + kWarpsPerCta - 1) / kWarpsPerCta);
+    if (nimg <= 0 || g.cells_total == 0) return;
+    const dim3 grd((unsigned)((g.cells_total + kWarpsPerCta - 1) / kWarpsPerCta), (unsigned)nimg);
     fast_cells_kernel<<<grd, kWarpsPerCta * 32, fast_cta_smem(f), s>>>(a, m);
 }
 
