@@ -20,6 +20,9 @@
 // lane = column reading bytes at compile-time offsets: 130 fewer instructions per key, bit-identical) -- 0.655 ms against
 // 0.538 ms: the load -> store -> barrier -> load chain serialises what the 31 independent global loads overlap; CTAs
 // of 4 / 16 warps instead of 8: 0.68 / 0.65 ms.
+// Also measured (round 2): the table read straight into registers (two LDG.128 per lane, no per-CTA shared copy + barrier):
+// 0.541 -> 0.531 ms, kept; the moments' row addresses as col +- v * pitch (one IMAD.WIDE each instead of two IADD3 of a
+// running pointer): 0.577 ms, rejected -- the 30 address multiplies sit in front of the loads they feed.
 // LSU/gather-bound (SURVEY.md 8d K4+K5): algorithmic bytes = 961 (31x31 raw) + 1369 (37x37 blurred) + 60 out per key.
 #include <cfloat>
 
@@ -28,7 +31,7 @@
 namespace gforb {
 
 namespace {
-__device__ const int8_t d_pattern[1024] = {
+__device__ __align__(16) const int8_t d_pattern[1024] = {
 #include "orb_pattern_31.inc"
 };
 // circular patch half-widths for HALF_PATCH_SIZE = 15 (src/ORBextractor.cc:453-468)
@@ -62,12 +65,6 @@ __global__ void __launch_bounds__(kWarps * 32)
 describe_kernel(const Geom g, const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
                 const int32_t* __restrict__ lvl_cnt, const uint32_t* __restrict__ lvl_pts,
                 gforb_keypoint* __restrict__ kps, uint8_t* __restrict__ desc, int32_t* __restrict__ nkp) {
-    __shared__ int8_t spx[16][32], spy[16][32];   // pattern transposed: [point within byte][byte] -> conflict-free
-    for (int t = threadIdx.x; t < 512; t += kWarps * 32) {
-        spx[t & 15][t >> 4] = d_pattern[2 * t];
-        spy[t & 15][t >> 4] = d_pattern[2 * t + 1];
-    }
-    __syncthreads();
 
     const int img = g.img0 + blockIdx.y;
     const int lane = threadIdx.x & 31;
@@ -131,13 +128,18 @@ describe_kernel(const Geom g, const uint8_t* __restrict__ pyr, const uint8_t* __
     sincos((double)ang, &sd, &cd);                     // one shared range reduction; each result correctly rounded to float below
     const float a = (float)cd, b = (float)sd;
     const uint8_t* bc = blur + L.boff + (size_t)img * L.bimg_stride + (size_t)y * L.bpitch + x;
+    // lane i computes descriptor byte i from pattern points 16 i .. 16 i + 15 = bytes 32 i .. 32 i + 31 of the table: two
+    // coalesced 16-byte loads per lane (L1-resident after the first warps) instead of a shared copy of the table per CTA
+    const uint4 pa = __ldg(reinterpret_cast<const uint4*>(d_pattern) + 2 * lane);
+    const uint4 pb = __ldg(reinterpret_cast<const uint4*>(d_pattern) + 2 * lane + 1);
+    const uint32_t pw[8] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w};       // word j = {x, y} of points 2 j, 2 j + 1
     uint32_t val = 0;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         int t[2];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-            const float px = (float)spx[2 * j + h][lane], py = (float)spy[2 * j + h][lane];
+            const float px = (float)(int)(int8_t)(pw[j] >> (16 * h)), py = (float)(int)(int8_t)(pw[j] >> (16 * h + 8));
             const int r = __float2int_rn(__fadd_rn(__fmul_rn(px, b), __fmul_rn(py, a)));
             const int c = __float2int_rn(__fsub_rn(__fmul_rn(px, a), __fmul_rn(py, b)));
             t[h] = __ldg(bc + (ptrdiff_t)r * L.bpitch + c);

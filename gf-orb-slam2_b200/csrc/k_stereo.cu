@@ -20,6 +20,12 @@
 // INT/LSU-bound.
 #include <algorithm>
 
+// Measured and rejected (round 2, late): the SAD of phase B on VABSDIFF4.U8.ACC -- |L + dlt - R| = |(L + da) - (R + db)| with
+// da = max(dlt, 0), db = max(-dlt, 0) on funnel-shifted aligned words, four pixels per instruction -- is exact only while
+// neither sum leaves a byte.  With that path forced the kernel runs in 0.201 ms (scalar loop: 0.222 ms); with the exact
+// guard (largest staged byte of the key + da <= 255, else the scalar loop) the synthetic frames, whose corners saturate,
+// fall back so often that both paths run in most warps: 0.248 ms.  An always-exact SIMD form needs a per-byte saturating
+// add, which sm_100a emulates in seven instructions (2.75 instructions per pixel against the scalar loop's 4.5).
 #include "gforb_internal.cuh"
 
 namespace gforb {

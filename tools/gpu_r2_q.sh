@@ -1,0 +1,2 @@
+export GFORB_LIBRARY=$PWD/gf-orb-slam2_b200/variants/libgforb_stff.so
+python bench.py --steps 40 --no-cpu-baseline 2>/dev/null | python -c "import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(d['value'], d['ms_per_step'], {k:v['ms'] for k,v in d['stages'].items()})"
