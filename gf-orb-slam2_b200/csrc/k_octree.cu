@@ -164,7 +164,9 @@ octree_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_
               int32_t* __restrict__ lvl_cnt, uint32_t* __restrict__ lvl_pts, int32_t* __restrict__ err,
               int32_t* __restrict__ retry, int cap, int tier) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
-    const int l = blockIdx.x, img = g.img0 + blockIdx.y;
+    // grid = (images, levels): the block scheduler hands out x first, so the large levels of every image start before the
+    // small ones (longest job first: the launch's tail is a level-7 CTA, not a level-0 one)
+    const int l = blockIdx.y, img = g.img0 + blockIdx.x;
     int32_t* my_retry = retry + (size_t)img * g.nlevels + l;
     if (tier == 1) {                      // second tier: only the pairs the first one could not hold
         if (*my_retry == 0) return;
@@ -424,7 +426,7 @@ int octree_configure(const Geom& g) {
 }
 
 void launch_octree(const Geom& g, const Buffers& b, int nimg, cudaStream_t s) {
-    dim3 grd(g.nlevels, nimg);
+    dim3 grd(nimg, g.nlevels);
     const int small = octree_small_cap(g);
     octree_kernel<<<grd, kT, smem_bytes_for(small, g.max_nodes), s>>>(g, b.cell_cnt, b.cell_pts, b.lvl_cnt, b.lvl_pts, b.err,
                                                                     b.oct_retry, small, 0);
