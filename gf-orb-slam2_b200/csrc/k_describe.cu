@@ -37,7 +37,13 @@ __device__ __align__(16) const int8_t d_pattern[1024] = {
 // circular patch half-widths for HALF_PATCH_SIZE = 15 (src/ORBextractor.cc:453-468)
 __constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
 
-constexpr int kWarps = 8;
+#ifndef GFORB_DESC_WARPS
+#define GFORB_DESC_WARPS 4      // measured with the staged box: 8 warps 0.489 ms, 4 warps 0.471, 2 warps 0.472
+#endif
+constexpr int kWarps = GFORB_DESC_WARPS;
+#ifndef GFORB_DESC_MINB
+#define GFORB_DESC_MINB 10     // CTAs per SM the register allocation must allow: 40 warps = 48 registers (32 warps: 0.538 ms, 48: 0.507)
+#endif
 
 // cv::fastAtan2 (OpenCV mathfuncs_core atan_f32), degrees
 __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
@@ -61,7 +67,7 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 }
 }  // namespace
 
-__global__ void __launch_bounds__(kWarps * 32)
+__global__ void __launch_bounds__(kWarps * 32, GFORB_DESC_MINB)
 describe_kernel(const Geom g, const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
                 const int32_t* __restrict__ lvl_cnt, const uint32_t* __restrict__ lvl_pts,
                 gforb_keypoint* __restrict__ kps, uint8_t* __restrict__ desc, int32_t* __restrict__ nkp) {
@@ -86,6 +92,25 @@ describe_kernel(const Geom g, const uint8_t* __restrict__ pyr, const uint8_t* __
     const uint32_t pk = lvl_pts[(size_t)img * g.kstage + slot];
     const int x = cand_x(pk) + kMinBorder, y = cand_y(pk) + kMinBorder;   // pt += minBorder (:845-846)
 
+    // The 37 x 37 blurred box the rotated pattern can reach (|r|, |c| <= 18), staged in shared memory with coalesced aligned
+    // word loads (10 words per row from the 4-byte boundary below x - 18; lanes 0..29 take three rows per step), issued
+    // before the moments so that they fly together.  The 16 gathers per lane then hit shared memory instead of costing
+    // ~25 L1 wavefronts each (ncu before: L1 data pipe 77 % busy, the kernel's first limiter): 0.531 -> 0.471 ms with 4-warp CTAs at 40 warps per SM.
+    __shared__ uint32_t s_box[kWarps][37 * 10];
+    uint32_t* const sbx = s_box[threadIdx.x >> 5];
+    const uint8_t* const bx0 = blur + L.boff + (size_t)img * L.bimg_stride + (size_t)(y - 18) * L.bpitch + (x - 18);
+    const int bph = (int)((uintptr_t)bx0 & 3);
+    {
+        const int br = lane >= 20 ? 2 : (lane >= 10 ? 1 : 0), bw = lane - 10 * br;       // lane -> (row of the step, word)
+        const int bpw = L.bpitch >> 2;
+        const uint32_t* gsrc = reinterpret_cast<const uint32_t*>(bx0 - bph) + (size_t)br * bpw + bw;
+        uint32_t* sdst = sbx + br * 10 + bw;
+#pragma unroll
+        for (int it = 0; it < 13; ++it) {
+            if (lane < 30 && 3 * it + br < 37) *sdst = __ldg(gsrc);
+            gsrc += 3 * bpw; sdst += 30;
+        }
+    }
     // ---- intensity centroid over the 749-px disc ----
     // lane = column u; the disc is symmetric (umax[|u|] is also the last row of column u), so the column's rows are
     // |v| <= umax[|u|].  All 31 byte loads are issued before any is used (fully unrolled, predicated);
@@ -127,12 +152,12 @@ describe_kernel(const Geom g, const uint8_t* __restrict__ pyr, const uint8_t* __
     double sd, cd;
     sincos((double)ang, &sd, &cd);                     // one shared range reduction; each result correctly rounded to float below
     const float a = (float)cd, b = (float)sd;
-    const uint8_t* bc = blur + L.boff + (size_t)img * L.bimg_stride + (size_t)y * L.bpitch + x;
     // lane i computes descriptor byte i from pattern points 16 i .. 16 i + 15 = bytes 32 i .. 32 i + 31 of the table: two
     // coalesced 16-byte loads per lane (L1-resident after the first warps) instead of a shared copy of the table per CTA
     const uint4 pa = __ldg(reinterpret_cast<const uint4*>(d_pattern) + 2 * lane);
     const uint4 pb = __ldg(reinterpret_cast<const uint4*>(d_pattern) + 2 * lane + 1);
     const uint32_t pw[8] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w};       // word j = {x, y} of points 2 j, 2 j + 1
+    __syncwarp();                                      // the staged box is complete
     uint32_t val = 0;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -142,7 +167,7 @@ describe_kernel(const Geom g, const uint8_t* __restrict__ pyr, const uint8_t* __
             const float px = (float)(int)(int8_t)(pw[j] >> (16 * h)), py = (float)(int)(int8_t)(pw[j] >> (16 * h + 8));
             const int r = __float2int_rn(__fadd_rn(__fmul_rn(px, b), __fmul_rn(py, a)));
             const int c = __float2int_rn(__fsub_rn(__fmul_rn(px, a), __fmul_rn(py, b)));
-            t[h] = __ldg(bc + (ptrdiff_t)r * L.bpitch + c);
+            t[h] = reinterpret_cast<const uint8_t*>(sbx)[(r + 18) * 40 + (c + 18 + bph)];
         }
         val |= (uint32_t)(t[0] < t[1]) << j;
     }
