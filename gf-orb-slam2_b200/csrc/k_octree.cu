@@ -159,20 +159,12 @@ constexpr int kSmallCap = GFORB_OCT_SMALLCAP;
 int octree_small_cap(const Geom& g) { return g.max_cand > kSmallCap ? kSmallCap : g.max_cand; }
 size_t octree_smem_bytes(const Geom& g) { return smem_bytes_for(g.max_cand, g.max_nodes); }
 
-__global__ void __launch_bounds__(kT, GFORB_OCT_MINB)
-octree_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_t* __restrict__ cell_pts,
-              int32_t* __restrict__ lvl_cnt, uint32_t* __restrict__ lvl_pts, int32_t* __restrict__ err,
-              int32_t* __restrict__ retry, int cap, int tier) {
-    extern __shared__ __align__(16) uint8_t smem_raw[];
-    // grid = (images, levels): the block scheduler hands out x first, so the large levels of every image start before the
-    // small ones (longest job first: the launch's tail is a level-7 CTA, not a level-0 one)
-    const int l = blockIdx.y, img = g.img0 + blockIdx.x;
+// one (image, level) pair by the whole CTA; every return is block-uniform
+__device__ __forceinline__ void octree_pair(const Geom& g, const uint32_t* __restrict__ cell_cnt,
+                                            const uint32_t* __restrict__ cell_pts, int32_t* __restrict__ lvl_cnt,
+                                            uint32_t* __restrict__ lvl_pts, int32_t* __restrict__ err,
+                                            int32_t* __restrict__ retry, int cap, int l, int img, uint8_t* smem_raw) {
     int32_t* my_retry = retry + (size_t)img * g.nlevels + l;
-    if (tier == 1) {                      // second tier: only the pairs the first one could not hold
-        if (*my_retry == 0) return;
-        __syncthreads();
-        if (threadIdx.x == 0) *my_retry = 0;
-    }
     const LevelGeom& L = g.lv[l];
     const int NC = g.max_nodes;
     Smem s = carve(smem_raw, cap, NC);
@@ -420,19 +412,60 @@ octree_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_
     if (threadIdx.x == 0) *out_cnt = S;
 }
 
+__global__ void __launch_bounds__(kT, GFORB_OCT_MINB)
+octree_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_t* __restrict__ cell_pts,
+              int32_t* __restrict__ lvl_cnt, uint32_t* __restrict__ lvl_pts, int32_t* __restrict__ err,
+              int32_t* __restrict__ retry, int cap) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    // grid = (images, levels): the block scheduler hands out x first, so the large levels of every image start before the
+    // small ones (longest job first: the launch's tail is a level-7 CTA, not a level-0 one)
+    octree_pair(g, cell_cnt, cell_pts, lvl_cnt, lvl_pts, err, retry, cap, blockIdx.y, g.img0 + blockIdx.x, smem_raw);
+}
+
+// Second tier: the pairs the first one could not hold, with the full working set.  Almost always there are none, so the
+// launch is a few hundred CTAs that each look at a slice of the retry flags in parallel (one flag per thread) and leave;
+// one CTA per pair with the full shared-memory footprint cost 12 us per step just to read 4,096 flags two CTAs per SM at a time.
+__global__ void __launch_bounds__(kT, 1)
+octree_redo_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_t* __restrict__ cell_pts,
+                   int32_t* __restrict__ lvl_cnt, uint32_t* __restrict__ lvl_pts, int32_t* __restrict__ err,
+                   int32_t* __restrict__ retry, int cap, int npairs, int per) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    __shared__ int s_todo[kT], s_ntodo;
+    if (threadIdx.x == 0) s_ntodo = 0;
+    __syncthreads();
+    const int p = blockIdx.x * per + threadIdx.x;            // per <= kT
+    if ((int)threadIdx.x < per && p < npairs) {
+        int32_t* f = retry + (size_t)g.img0 * g.nlevels + p;
+        if (*f) { *f = 0; s_todo[atomicAdd(&s_ntodo, 1)] = p; }
+    }
+    __syncthreads();
+    const int ntodo = s_ntodo;
+    for (int i = 0; i < ntodo; ++i) {
+        const int q = s_todo[i];
+        octree_pair(g, cell_cnt, cell_pts, lvl_cnt, lvl_pts, err, retry, cap, q % g.nlevels, g.img0 + q / g.nlevels, smem_raw);
+        __syncthreads();                                     // the working set is reused by the next pair
+    }
+}
+
 int octree_configure(const Geom& g) {
     static size_t have[64] = {};       // high-water mark: engines of different footprints share the kernel symbol
-    return opt_in_smem(octree_kernel, octree_smem_bytes(g), have) ? (int)cudaErrorInvalidValue : 0;
+    static size_t have_redo[64] = {};
+    if (opt_in_smem(octree_kernel, smem_bytes_for(octree_small_cap(g), g.max_nodes), have)) return (int)cudaErrorInvalidValue;
+    return opt_in_smem(octree_redo_kernel, octree_smem_bytes(g), have_redo) ? (int)cudaErrorInvalidValue : 0;
 }
 
 void launch_octree(const Geom& g, const Buffers& b, int nimg, cudaStream_t s) {
     dim3 grd(nimg, g.nlevels);
     const int small = octree_small_cap(g);
     octree_kernel<<<grd, kT, smem_bytes_for(small, g.max_nodes), s>>>(g, b.cell_cnt, b.cell_pts, b.lvl_cnt, b.lvl_pts, b.err,
-                                                                    b.oct_retry, small, 0);
-    if (small < g.max_cand)
-        octree_kernel<<<grd, kT, octree_smem_bytes(g), s>>>(g, b.cell_cnt, b.cell_pts, b.lvl_cnt, b.lvl_pts, b.err,
-                                                           b.oct_retry, g.max_cand, 1);
+                                                                    b.oct_retry, small);
+    if (small < g.max_cand) {
+        const int npairs = nimg * g.nlevels;
+        const int ctas = std::max(std::min(npairs, 296), (npairs + kT - 1) / kT);      // about two per SM; a slice <= kT flags
+        const int per = (npairs + ctas - 1) / ctas;
+        octree_redo_kernel<<<ctas, kT, octree_smem_bytes(g), s>>>(g, b.cell_cnt, b.cell_pts, b.lvl_cnt, b.lvl_pts, b.err,
+                                                                 b.oct_retry, g.max_cand, npairs, per);
+    }
 }
 
 }  // namespace gforb
