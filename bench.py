@@ -593,7 +593,7 @@ def main():
         prof = json.loads(prof_file.read_text())
         if prof.get("frames_per_step") == F and prof.get("config", "1") == args.config:
             kmap = {"pyramid": ("pyr_level0_fast_kernel", "pyr_resize_fast_kernel", "pyr_cascade_kernel"), "fast": ("fast_cells_kernel",),
-                    "quadtree": ("octree_kernel", "octree_small_kernel"), "blur": ("blur_kernel",), "describe": ("describe_kernel",),
+                    "quadtree": ("octree_kernel", "octree_redo_kernel"), "blur": ("blur_kernel",), "describe": ("describe_kernel",),
                     "stereo": ("stereo_kernel",)}
             for k, names in kmap.items():
                 ks = [prof["kernels"][n] for n in names if n in prof["kernels"]]
