@@ -21,7 +21,7 @@
 // 0.538 ms: the load -> store -> barrier -> load chain serialises what the 31 independent global loads overlap; CTAs
 // of 4 / 16 warps instead of 8: 0.68 / 0.65 ms.
 // Also measured (round 2): the table read straight into registers (two LDG.128 per lane, no per-CTA shared copy + barrier):
-// 0.541 -> 0.531 ms, kept; the moments' row addresses as col +- v * pitch (one IMAD.WIDE each instead of two IADD3 of a
+// 0.541 -> 0.531 ms; then as a float table, one LDG.128 per comparison (no byte extraction / I2F): 0.471 -> 0.447 ms, kept; the moments' row addresses as col +- v * pitch (one IMAD.WIDE each instead of two IADD3 of a
 // running pointer): 0.577 ms, rejected -- the 30 address multiplies sit in front of the loads they feed.
 // LSU/gather-bound (SURVEY.md 8d K4+K5): algorithmic bytes = 961 (31x31 raw) + 1369 (37x37 blurred) + 60 out per key.
 #include <cfloat>
@@ -31,9 +31,20 @@
 namespace gforb {
 
 namespace {
-__device__ __align__(16) const int8_t d_pattern[1024] = {
+// The pattern as floats, laid out [comparison j of the byte][lane = byte][x0, y0, x1, y1]: one coalesced LDG.128 per
+// comparison brings both points of lane i's j-th test, already converted (32 I2F + byte extractions per key less).
+struct PatternF { float v[1024]; };
+constexpr PatternF make_pattern_f() {
+    constexpr int8_t src[1024] = {
 #include "orb_pattern_31.inc"
-};
+    };
+    PatternF p{};
+    for (int lane = 0; lane < 32; ++lane)
+        for (int j = 0; j < 8; ++j)
+            for (int e = 0; e < 4; ++e) p.v[(j * 32 + lane) * 4 + e] = (float)src[32 * lane + 4 * j + e];
+    return p;
+}
+__device__ __align__(16) const PatternF d_pattern_f = make_pattern_f();
 // circular patch half-widths for HALF_PATCH_SIZE = 15 (src/ORBextractor.cc:453-468)
 __constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
 
@@ -152,19 +163,17 @@ describe_kernel(const Geom g, const uint8_t* __restrict__ pyr, const uint8_t* __
     double sd, cd;
     sincos((double)ang, &sd, &cd);                     // one shared range reduction; each result correctly rounded to float below
     const float a = (float)cd, b = (float)sd;
-    // lane i computes descriptor byte i from pattern points 16 i .. 16 i + 15 = bytes 32 i .. 32 i + 31 of the table: two
-    // coalesced 16-byte loads per lane (L1-resident after the first warps) instead of a shared copy of the table per CTA
-    const uint4 pa = __ldg(reinterpret_cast<const uint4*>(d_pattern) + 2 * lane);
-    const uint4 pb = __ldg(reinterpret_cast<const uint4*>(d_pattern) + 2 * lane + 1);
-    const uint32_t pw[8] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w};       // word j = {x, y} of points 2 j, 2 j + 1
+    // lane i computes descriptor byte i from pattern points 16 i .. 16 i + 15
+    const float4* const pat = reinterpret_cast<const float4*>(d_pattern_f.v) + lane;
     __syncwarp();                                      // the staged box is complete
     uint32_t val = 0;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         int t[2];
+        const float4 pq = __ldg(pat + 32 * j);
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-            const float px = (float)(int)(int8_t)(pw[j] >> (16 * h)), py = (float)(int)(int8_t)(pw[j] >> (16 * h + 8));
+            const float px = h ? pq.z : pq.x, py = h ? pq.w : pq.y;
             const int r = __float2int_rn(__fadd_rn(__fmul_rn(px, b), __fmul_rn(py, a)));
             const int c = __float2int_rn(__fsub_rn(__fmul_rn(px, a), __fmul_rn(py, b)));
             t[h] = reinterpret_cast<const uint8_t*>(sbx)[(r + 18) * 40 + (c + 18 + bph)];
