@@ -393,7 +393,7 @@ stereo_kernel(const StereoView v, const gforb_stereo_params prm, int K) {
                 for (int dy = 0; dy < 11; ++dy) {
 #pragma unroll
                     for (int dx = 0; dx < 11; ++dx)
-                        acc += abs((int)lb[dy * 4 * kRowWords + dx] + dlt - (int)rb[dy * 4 * kRowWords + dx]);
+                        acc = (int)__sad((int)lb[dy * 4 * kRowWords + dx] + dlt, (int)rb[dy * 4 * kRowWords + dx], (unsigned)acc);   // |a - b| + c: one VABSDIFF
                 }
             }
             s_sad[idx] = acc;
