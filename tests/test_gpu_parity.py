@@ -259,6 +259,34 @@ def test_chunked_pipeline_equals_whole_batch(gf):
             assert np.array_equal(out["depth"][f, :c], ref["depth"][f, :c])
 
 
+def test_batch_reads_only_roi_and_blur_frame(gf, monkeypatch):
+    """The batch path writes each pyramid level's ROI plus the 3-px frame the blur reads and leaves the outer 16 px of the
+    19-px frame unwritten (k_pyramid.cu v3; SURVEY.md Appendix A.1: the frame is never read on the path).  With the
+    pyramid arena pre-filled with 0xCD (GFORB_POISON_PYR, read when a handle allocates) every output byte must equal a
+    clean handle's: nothing downstream looks at the unwritten frame.  Sizes with w % 4 != 0 on most levels included."""
+    for (w, h), seed in (((752, 480), 70), ((644, 478), 71), ((642, 478), 72)):
+        n = 3
+        pairs = [synth_stereo(seed + i, h=h, w=w, nshapes=220) for i in range(n)]
+        left = np.stack([p[0] for p in pairs]); right = np.stack([p[1] for p in pairs])
+        monkeypatch.delenv("GFORB_POISON_PYR", raising=False)
+        clean = gf.StereoBatch(w, h, n)
+        ref = clean.alloc_outputs(n)
+        clean.process(left, right, ref, BF, B)
+        monkeypatch.setenv("GFORB_POISON_PYR", "1")
+        dirty = gf.StereoBatch(w, h, n)
+        out = dirty.alloc_outputs(n)
+        dirty.process(left, right, out, BF, B)
+        assert np.array_equal(out["counts"], ref["counts"]) and ref["counts"].min() > 300
+        for i in range(2 * n):
+            c = ref["counts"][i]
+            assert out["keypoints"][i, :c].tobytes() == ref["keypoints"][i, :c].tobytes()
+            assert np.array_equal(out["descriptors"][i, :c], ref["descriptors"][i, :c])
+        for f in range(n):
+            c = ref["counts"][2 * f]
+            assert np.array_equal(out["u_right"][f, :c], ref["u_right"][f, :c])
+            assert np.array_equal(out["depth"][f, :c], ref["depth"][f, :c])
+
+
 def test_config2_1280x720_batch256_2000kp(gf, O):
     """BASELINE.json configs[2] at full size: 256 stereo frames of 1280x720, 2000 keypoints, one batch call.
     8 distinct synthetic pairs are scattered over the 256 slots; two of them are checked bit-for-bit against the

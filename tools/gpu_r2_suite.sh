@@ -1,1 +1,2 @@
 GFORB_POISON_PYR=1 timeout -s KILL 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+timeout -s KILL 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2
