@@ -123,28 +123,42 @@ describe_kernel(const Geom g, const uint8_t* __restrict__ pyr, const uint8_t* __
         }
     }
     // ---- intensity centroid over the 749-px disc ----
-    // lane = column u; the disc is symmetric (umax[|u|] is also the last row of column u), so the column's rows are
-    // |v| <= umax[|u|].  All 31 byte loads are issued before any is used (fully unrolled, predicated);
-    // m10 = u * column sum, m01 = sum_v v * (I(+v) - I(-v)): exact int32, order-free.
+    // The 31 x 31 raw box is staged like the blurred one (9 aligned words per row from the 4-byte boundary below x - 15; lanes
+    // 0..26 take three rows per step, one running pointer per lane).  Then lane = column u; the disc is symmetric (umax[|u|] is
+    // also the last row of column u), so the column's rows are |v| <= umax[|u|]: 31 predicated LDS.U8 at compile-time row
+    // offsets.  m10 = u * column sum, m01 = sum_v v * (I(+v) - I(-v)): exact int32, order-free.
+    // (The direct form -- 31 predicated LDG.U8 per lane -- cost three to four address instructions per load: the compiler
+    // re-derived every row address from the kernel argument, LDC.64 + 64-bit add, to stay inside 48 registers.)
+    __shared__ uint32_t s_raw[kWarps][31 * 9];
+    uint32_t* const srw = s_raw[threadIdx.x >> 5];
     const int pitch = L.pitch;
-    const uint8_t* ctr = pyr + L.off + (size_t)img * L.img_stride + (size_t)(kEdge + y) * pitch + kXPad + x;
+    const uint8_t* const rx0 = pyr + L.off + (size_t)img * L.img_stride + (size_t)(kEdge + y - kHalfPatch) * pitch + kXPad + (x - kHalfPatch);
+    const int rph = (int)((uintptr_t)rx0 & 3);
+    {
+        const int rr = lane >= 18 ? 2 : (lane >= 9 ? 1 : 0), rw = lane - 9 * rr;       // lane -> (row of the step, word)
+        const int ppw = pitch >> 2;
+        const uint32_t* gsrc = reinterpret_cast<const uint32_t*>(rx0 - rph) + (size_t)rr * ppw + rw;
+        uint32_t* sdst = srw + rr * 9 + rw;
+#pragma unroll
+        for (int it = 0; it < 11; ++it) {
+            if (lane < 27 && 3 * it + rr < 31) *sdst = __ldg(gsrc);
+            gsrc += 3 * ppw; sdst += 27;
+        }
+    }
+    __syncwarp();
     const int u = lane - kHalfPatch;
     int m10 = 0, m01 = 0;
     {
         // umax[|u|] out of a 64-bit immediate (4 bits per entry) instead of a lane-indexed (divergent) __constant__ load
         const int vl = lane < 31 ? (int)((0x3689ABCDDEEEFFFFull >> (4 * abs(u))) & 15ull) : -1;
-        const uint8_t* col = ctr + u;
+        const uint8_t* col = reinterpret_cast<const uint8_t*>(srw) + kHalfPatch * 36 + min(lane, 30) + rph;    // (row 0, column u)
         int up[kHalfPatch + 1], dn[kHalfPatch + 1];
-        // running row pointers (one 64-bit add per load) instead of col +- v * pitch re-derived from the kernel arguments
-        const uint8_t* pu = col;
-        const uint8_t* pd = col;
-        up[0] = 0 <= vl ? (int)__ldg(col) : 0;
+        up[0] = 0 <= vl ? (int)col[0] : 0;
         dn[0] = 0;
 #pragma unroll
         for (int v = 1; v <= kHalfPatch; ++v) {
-            pu -= pitch; pd += pitch;
-            up[v] = v <= vl ? (int)__ldg(pu) : 0;
-            dn[v] = v <= vl ? (int)__ldg(pd) : 0;
+            up[v] = v <= vl ? (int)col[-36 * v] : 0;
+            dn[v] = v <= vl ? (int)col[36 * v] : 0;
         }
         int sum = up[0];
 #pragma unroll
