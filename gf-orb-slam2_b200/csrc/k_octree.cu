@@ -55,6 +55,12 @@ __device__ __forceinline__ Smem carve(uint8_t* base, int max_cand, int NC) {
     s.order = (int*)take(4 * (size_t)NC);
     s.split = (uint8_t*)take((size_t)NC);
     s.warp = (int*)take(4 * 128);      // [0, 64): block_scan_pair's two buffers; [64, 104): block_excl_scan
+    // the pointers come out of a struct: without the hint every access through them is a generic LD / ST / ATOM
+    __builtin_assume(__isShared(s.pts));   __builtin_assume(__isShared(s.pnode));  __builtin_assume(__isShared(s.box[0]));
+    __builtin_assume(__isShared(s.box[1])); __builtin_assume(__isShared(s.cnt[0])); __builtin_assume(__isShared(s.cnt[1]));
+    __builtin_assume(__isShared(s.cnt4));  __builtin_assume(__isShared(s.remap));  __builtin_assume(__isShared(s.keepmap));
+    __builtin_assume(__isShared(s.a));     __builtin_assume(__isShared(s.b));      __builtin_assume(__isShared(s.key));
+    __builtin_assume(__isShared(s.order)); __builtin_assume(__isShared(s.split));  __builtin_assume(__isShared(s.warp));
     return s;
 }
 
@@ -163,7 +169,8 @@ size_t octree_smem_bytes(const Geom& g) { return smem_bytes_for(g.max_cand, g.ma
 __device__ __forceinline__ void octree_pair(const Geom& g, const uint32_t* __restrict__ cell_cnt,
                                             const uint32_t* __restrict__ cell_pts, int32_t* __restrict__ lvl_cnt,
                                             uint32_t* __restrict__ lvl_pts, int32_t* __restrict__ err,
-                                            int32_t* __restrict__ retry, int cap, int l, int img, uint8_t* smem_raw) {
+                                            int32_t* __restrict__ retry, int cap, int l, int img) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];      // declared here, not passed in: keeps every access an LDS / ATOMS
     int32_t* my_retry = retry + (size_t)img * g.nlevels + l;
     const LevelGeom& L = g.lv[l];
     const int NC = g.max_nodes;
@@ -234,8 +241,10 @@ __device__ __forceinline__ void octree_pair(const Geom& g, const uint32_t* __res
     for (int i = threadIdx.x; i < 4 * S; i += kT) s.cnt4[i] = 0;
     __syncthreads();
     for (;;) {
-        short4* box = s.box[cur]; int* cnt = s.cnt[cur];
-        short4* nbox = s.box[cur ^ 1]; int* ncnt = s.cnt[cur ^ 1];
+        // selects, not s.box[cur]: a dynamically indexed member sends the whole pointer struct to local memory, and every access
+        // through a pointer re-loaded from there is a generic LD / ST / ATOM instead of LDS / STS / ATOMS
+        short4* box = cur ? s.box[1] : s.box[0]; int* cnt = cur ? s.cnt[1] : s.cnt[0];
+        short4* nbox = cur ? s.box[0] : s.box[1]; int* ncnt = cur ? s.cnt[0] : s.cnt[1];
 
         // A. speculative child counts of every splittable node
         for (int p = threadIdx.x; p < n; p += kT) {
@@ -416,10 +425,9 @@ __global__ void __launch_bounds__(kT, GFORB_OCT_MINB)
 octree_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_t* __restrict__ cell_pts,
               int32_t* __restrict__ lvl_cnt, uint32_t* __restrict__ lvl_pts, int32_t* __restrict__ err,
               int32_t* __restrict__ retry, int cap) {
-    extern __shared__ __align__(16) uint8_t smem_raw[];
     // grid = (images, levels): the block scheduler hands out x first, so the large levels of every image start before the
     // small ones (longest job first: the launch's tail is a level-7 CTA, not a level-0 one)
-    octree_pair(g, cell_cnt, cell_pts, lvl_cnt, lvl_pts, err, retry, cap, blockIdx.y, g.img0 + blockIdx.x, smem_raw);
+    octree_pair(g, cell_cnt, cell_pts, lvl_cnt, lvl_pts, err, retry, cap, blockIdx.y, g.img0 + blockIdx.x);
 }
 
 // Second tier: the pairs the first one could not hold, with the full working set.  Almost always there are none, so the
@@ -429,7 +437,6 @@ __global__ void __launch_bounds__(kT, 1)
 octree_redo_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const uint32_t* __restrict__ cell_pts,
                    int32_t* __restrict__ lvl_cnt, uint32_t* __restrict__ lvl_pts, int32_t* __restrict__ err,
                    int32_t* __restrict__ retry, int cap, int npairs, int per) {
-    extern __shared__ __align__(16) uint8_t smem_raw[];
     __shared__ int s_todo[kT], s_ntodo;
     if (threadIdx.x == 0) s_ntodo = 0;
     __syncthreads();
@@ -442,7 +449,7 @@ octree_redo_kernel(const Geom g, const uint32_t* __restrict__ cell_cnt, const ui
     const int ntodo = s_ntodo;
     for (int i = 0; i < ntodo; ++i) {
         const int q = s_todo[i];
-        octree_pair(g, cell_cnt, cell_pts, lvl_cnt, lvl_pts, err, retry, cap, q % g.nlevels, g.img0 + q / g.nlevels, smem_raw);
+        octree_pair(g, cell_cnt, cell_pts, lvl_cnt, lvl_pts, err, retry, cap, q % g.nlevels, g.img0 + q / g.nlevels);
         __syncthreads();                                     // the working set is reused by the next pair
     }
 }
