@@ -158,7 +158,7 @@ int launch_distinctive(const uint8_t* desc, const int32_t* set_start, int npoint
     if (npoints <= 0) return 0;
     const size_t smem = (size_t)kDdWarps * std::max(max_n, 1) * 32;
     static size_t have[64] = {};
-    if (smem > 48 * 1024 && opt_in_smem(distinctive_kernel, smem, have)) return -1;
+    if (smem > 32 * 1024 && opt_in_smem(distinctive_kernel, smem, have)) return -1;      // static + dynamic share the 48 KB default
     distinctive_kernel<<<(npoints + kDdWarps - 1) / kDdWarps, kDdWarps * 32, smem, s>>>(
         reinterpret_cast<const uint4*>(desc), set_start, npoints, std::max(max_n, 1), best_idx, best_median);
     return 0;

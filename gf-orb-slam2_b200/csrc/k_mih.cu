@@ -149,7 +149,7 @@ int launch_mih_insert(const uint8_t* desc, const int32_t* entry, int n, int T, i
     while (n2 < n) n2 <<= 1;
     static size_t have[64] = {};
     const size_t smem = (size_t)n2 * 4;
-    if (smem > 48 * 1024 && opt_in_smem(mih_insert_kernel, smem, have)) return -1;
+    if (smem > 32 * 1024 && opt_in_smem(mih_insert_kernel, smem, have)) return -1;       // static + dynamic share the 48 KB default
     mih_insert_kernel<<<T, kInsertThreads, smem, s>>>(reinterpret_cast<const uint32_t*>(desc), entry, n, n2, bits, 1u << bits, cap, head,
                                                       pool_id, pool_next, fill, hashed, success, err);
     return 0;

@@ -481,7 +481,9 @@ size_t stereo_smem_bytes(int K, int nRows) {
 void launch_stereo(const StereoView& v, const gforb_stereo_params& p, int nframes, int K, cudaStream_t s) {
     const size_t smem = stereo_smem_bytes(K, v.nRows);
     static size_t configured[64] = {};
-    if (smem > 48 * 1024) opt_in_smem(stereo_kernel, smem, configured);
+    // the 48 KB a launch gets without the opt-in covers static + dynamic shared memory together, and the kernel holds ~1 KB of
+    // static: a dynamic size just under 48 KB (K around 2,000 keys) failed to launch -- opt in from 32 KB on
+    if (smem > 32 * 1024) opt_in_smem(stereo_kernel, smem, configured);
     stereo_kernel<<<dim3(kSlices, nframes), kT, smem, s>>>(v, p, K);
 }
 

@@ -1,0 +1,85 @@
+#!/usr/bin/env python3
+"""Randomised parity stress of the extraction + stereo path: random image sizes (every w % 4, sizes down to the smallest the
+pyramid accepts), extractor parameters and stereo pairs, through the single-image handles AND the batch handles, against the
+oracle (bit-exact keypoints, angles, descriptors, uRight, depth).  The kernels branch on w % 4, on warps that hold an ROI
+edge, on levels narrower than one warp column, on cells cut by the border ...: this walks those cases at random instead of
+at the handful of sizes the test-suite fixes.
+
+usage: python tools/stress_extract.py [cases] [seed]   -> one JSON line {cases, keypoints, mismatches}; exit 1 on a mismatch
+"""
+import importlib
+import json
+import sys
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT)); sys.path.insert(0, str(ROOT / "tests"))
+from oracle import pyoracle as O                     # noqa: E402  (test tooling: the checker)
+from synth import synth_stereo                       # noqa: E402
+
+BF = 47.90639384423901
+B = BF / 458.654
+
+
+def same_extract(k, d, ok, od):
+    if len(k) != len(ok):
+        return f"{len(k)} vs {len(ok)} keypoints"
+    for f in ("x", "y", "size", "angle", "response", "octave", "class_id"):
+        if not np.array_equal(k[f], ok[f]):
+            return f"field {f}"
+    if not np.array_equal(d, od):
+        return "descriptors"
+    return None
+
+
+def main():
+    cases = int(sys.argv[1]) if len(sys.argv) > 1 else 40
+    rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 2024)
+    gf = importlib.import_module("gf-orb-slam2_b200")
+    bad, nkp = [], 0
+    for c in range(cases):
+        nlevels = int(rng.integers(1, 9))
+        scale = float(rng.choice([1.2, 1.2, 1.2, 1.1, 1.3, 1.5, 2.0]))
+        while 48 * scale ** (nlevels - 1) > 600:                  # the last level must stay >= 40 px inside a <= 760-px image
+            nlevels -= 1
+        smallest = 48 * scale ** (nlevels - 1)
+        w = int(rng.integers(max(int(smallest) + 8, 96), 1000))
+        h = int(rng.integers(max(int(smallest) + 8, 96), 760))
+        nfeat = int(rng.choice([50, 300, 1000, 2000]))
+        ini = int(rng.choice([20, 20, 12, 40])); mn = int(rng.choice([7, 7, 5, ini]))
+        args = (nfeat, scale, nlevels, ini, min(mn, ini))
+        left, right = synth_stereo(1000 + c, w, h, nshapes=int(rng.integers(60, 400)))
+        what = f"case {c}: {w}x{h} {args}"
+        try:
+            oxL, oxR = O.Extractor(*args), O.Extractor(*args)
+            okL, odL, _ = oxL.extract(left); okR, odR, _ = oxR.extract(right)
+            ost = O.stereo_match(oxL, oxR, okL, odL, okR, odR, BF, B)
+            # single-image handles (full 19-px frames)
+            exL, exR = gf.ORBextractor(*args), gf.ORBextractor(*args)
+            kL, dL = exL(left); kR, dR = exR(right)
+            for side, k, d, ok, od in (("L", kL, dL, okL, odL), ("R", kR, dR, okR, odR)):
+                e = same_extract(k, d, ok, od)
+                if e:
+                    bad.append(f"{what} single {side}: {e}")
+            # batch handle (ROI + 3-px frame), two frames: the pair and the pair swapped
+            sb = gf.StereoBatch(w, h, 2, nfeatures=nfeat, scaleFactor=scale, nlevels=nlevels, iniThFAST=ini, minThFAST=min(mn, ini))
+            out = sb.alloc_outputs(2)
+            sb.process(np.stack([left, right]), np.stack([right, left]), out, BF, B)
+            n0, n1 = out["counts"][0], out["counts"][1]
+            e = same_extract(out["keypoints"][0, :n0], out["descriptors"][0, :n0], okL, odL) or \
+                same_extract(out["keypoints"][1, :n1], out["descriptors"][1, :n1], okR, odR)
+            if e:
+                bad.append(f"{what} batch: {e}")
+            elif not (np.array_equal(out["u_right"][0, :n0], ost["uRight"]) and np.array_equal(out["depth"][0, :n0], ost["depth"])):
+                bad.append(f"{what} batch: stereo")
+            nkp += len(okL) + len(okR)
+        except Exception as ex:                      # an error on one side only is a mismatch too
+            bad.append(f"{what}: {type(ex).__name__}: {ex}")
+    print(json.dumps({"cases": cases, "keypoints": int(nkp), "mismatches": len(bad), "first": bad[:5]}))
+    return 1 if bad else 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
