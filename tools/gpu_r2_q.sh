@@ -1,1 +1,1 @@
-timeout -s KILL 900 python -m pytest tests/test_gpu_stress.py -m gpu -x -q 2>&1 | tail -3
+timeout -s KILL 900 python tools/stress_extract.py 80 31337 2>&1 | tail -2

@@ -38,17 +38,20 @@ def main():
     cases = int(sys.argv[1]) if len(sys.argv) > 1 else 40
     rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 2024)
     gf = importlib.import_module("gf-orb-slam2_b200")
-    bad, nkp = [], 0
+    bad, nkp, declined = [], 0, 0
     for c in range(cases):
         nlevels = int(rng.integers(1, 9))
         scale = float(rng.choice([1.2, 1.2, 1.2, 1.1, 1.3, 1.5, 2.0]))
         while 48 * scale ** (nlevels - 1) > 600:                  # the last level must stay >= 40 px inside a <= 760-px image
             nlevels -= 1
         smallest = 48 * scale ** (nlevels - 1)
-        w = int(rng.integers(max(int(smallest) + 8, 96), 1000))
-        h = int(rng.integers(max(int(smallest) + 8, 96), 760))
-        nfeat = int(rng.choice([50, 300, 1000, 2000]))
-        ini = int(rng.choice([20, 20, 12, 40])); mn = int(rng.choice([7, 7, 5, ini]))
+        big = rng.random() < 0.08                                 # now and then a large image
+        w = int(rng.integers(max(int(smallest) + 8, 96), 1700 if big else 1000))
+        h = int(rng.integers(max(int(smallest) + 8, 96), 1300 if big else 760))
+        nfeat = int(rng.choice([10, 50, 300, 1000, 2000, 4000]))
+        ini = int(rng.choice([20, 20, 12, 40, 3, 0, 120])); mn = int(rng.choice([7, 7, 5, ini, 0, 1]))      # 0: the list-everything path of FAST
+        if min(ini, mn) <= 3:                                     # dense corners: stay inside the default candidate capacity
+            w, h = min(w, int(smallest) + 8 + 200), min(h, int(smallest) + 8 + 140)
         args = (nfeat, scale, nlevels, ini, min(mn, ini))
         left, right = synth_stereo(1000 + c, w, h, nshapes=int(rng.integers(60, 400)))
         what = f"case {c}: {w}x{h} {args}"
@@ -75,9 +78,14 @@ def main():
             elif not (np.array_equal(out["u_right"][0, :n0], ost["uRight"]) and np.array_equal(out["depth"][0, :n0], ost["depth"])):
                 bad.append(f"{what} batch: stereo")
             nkp += len(okL) + len(okR)
-        except Exception as ex:                      # an error on one side only is a mismatch too
-            bad.append(f"{what}: {type(ex).__name__}: {ex}")
-    print(json.dumps({"cases": cases, "keypoints": int(nkp), "mismatches": len(bad), "first": bad[:5]}))
+        except Exception as ex:                      # an error on one side only is a mismatch too ...
+            # ... except the library's documented, loud capacity limits (gforb_limits: candidates per level; the quadtree's
+            # shared-memory working set): dense-corner cases (thresholds near 0, large images) are declined, never truncated
+            if type(ex).__name__ == "GforbError" and ("working set" in str(ex)):
+                declined += 1
+            else:
+                bad.append(f"{what}: {type(ex).__name__}: {ex}")
+    print(json.dumps({"cases": cases, "keypoints": int(nkp), "declined_capacity": declined, "mismatches": len(bad), "first": bad[:5]}))
     return 1 if bad else 0
 
 
