@@ -106,7 +106,10 @@ struct FastArgs {
 };
 
 namespace {
-constexpr int kWarpsPerCta = 4;
+#ifndef GFORB_FAST_WARPS
+#define GFORB_FAST_WARPS 4      // measured: 2 warps 1.048 ms, 4 warps 1.040, 8 warps 1.064
+#endif
+constexpr int kWarpsPerCta = GFORB_FAST_WARPS;
 constexpr int kBitmapBytes = 64 * 2 * 4;         // keep@tlo, 64 rows x 2 x 32 bits
 // Per-warp shared layout: [tile (TMA, 128-byte aligned)][score map][row bitmap 512 B][pixel list][mbarrier 8 B],
 // regions rounded to 16 bytes, the whole to 128.  The score map covers the FAST domain plus a one-pixel zero ring
