@@ -32,7 +32,7 @@ namespace gforb {
 
 namespace {
 #ifndef GFORB_ST_THREADS
-#define GFORB_ST_THREADS 256
+#define GFORB_ST_THREADS 256     // re-measured late in round 2 (with the cheaper SAD): 128 threads x 8 CTAs 0.229 ms, 256 x 4 0.219, 256 x 5 0.284, 512 x 2 0.288
 #endif
 constexpr int kT = GFORB_ST_THREADS;
 constexpr int kWarps = kT / 32;
