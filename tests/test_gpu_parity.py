@@ -140,6 +140,25 @@ def test_candidate_overflow_is_loud(gf, O):
     _assert_extract_equal(k, d, ok, od, "noise, large bound")
 
 
+def test_quadtree_second_tier_in_chunked_batches(gf, O):
+    """Dense-corner images whose level 0 holds more candidates than the quadtree's first tier has room for (4,096) are redone
+    by the second-tier launch; in a chunked batch that launch works on images [img0, img0 + n) of the arena.  Every chunking
+    must give the oracle's keypoints for every image."""
+    rng = np.random.default_rng(5)
+    n, w, h = 3, 400, 300
+    left = rng.integers(0, 256, (n, h, w), dtype=np.uint8); right = rng.integers(0, 256, (n, h, w), dtype=np.uint8)
+    want = [O.Extractor().extract(im)[:2] for im in list(left) + list(right)]
+    sb = gf.StereoBatch(w, h, n, max_candidates_per_level=30000)
+    for chunk in (0, 1, 2):
+        out = sb.alloc_outputs(n)
+        sb.set_chunk(chunk)
+        sb.process(left, right, out, BF, B)
+        for f in range(n):
+            for eye, (ok, od) in ((0, want[f]), (1, want[n + f])):
+                c = out["counts"][2 * f + eye]
+                _assert_extract_equal(out["keypoints"][2 * f + eye, :c], out["descriptors"][2 * f + eye, :c], ok, od, f"chunk {chunk} frame {f} eye {eye}")
+
+
 def _stereo_both(gf, O, l, r, mode=0, **kw):
     exL, exR = gf.ORBextractor(), gf.ORBextractor()
     oxL, oxR = O.Extractor(), O.Extractor()
